@@ -1,0 +1,167 @@
+"""TEST INFRASTRUCTURE — ctypes binding of the CPU oracle (oracle/liborb_oracle.so).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module; the product package never does.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_SO = os.path.join(ROOT, "oracle", "liborb_oracle.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4")])
+
+_u8p = C.POINTER(C.c_uint8)
+_i32p = C.POINTER(C.c_int32)
+_f32p = C.POINTER(C.c_float)
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
+
+
+def _load():
+    if not os.path.exists(_SO):
+        build()
+    lib = C.CDLL(_SO)
+    lib.orc_extractor_create.restype = C.c_void_p
+    lib.orc_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+    lib.orc_extractor_destroy.argtypes = [C.c_void_p]
+    lib.orc_extractor_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+    lib.orc_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+    lib.orc_level.restype = C.c_void_p
+    lib.orc_level.argtypes = [C.c_void_p, C.c_int, _i32p, _i32p, _i32p]
+    lib.orc_blurred_level.restype = C.c_void_p
+    lib.orc_blurred_level.argtypes = [C.c_void_p, C.c_int, _i32p, _i32p, _i32p]
+    lib.orc_level_candidates.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    lib.orc_level_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    lib.orc_fast_atan2.restype = C.c_float
+    lib.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+    return lib
+
+
+lib = _load()
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def resize_linear(src, dw, dh):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.empty((dh, dw), np.uint8)
+    lib.orc_resize_linear_u8(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dw, dh, dw)
+    return dst
+
+
+def gauss7(src):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.empty_like(src)
+    lib.orc_gauss7_u8(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dst.strides[0])
+    return dst
+
+
+def border101(src, b):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.empty((src.shape[0] + 2 * b, src.shape[1] + 2 * b), np.uint8)
+    lib.orc_border101(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dst.strides[0], b)
+    return dst
+
+
+def fast9_16(img, th):
+    img = np.ascontiguousarray(img, np.uint8)
+    cap = img.size // 4 + 16
+    out = np.empty((cap, 3), np.int32)
+    n = lib.orc_fast9_16(_p(img), img.shape[1], img.shape[0], img.strides[0], th, _p(out), cap)
+    return out[:n].copy()
+
+
+def fast_score_map(img):
+    img = np.ascontiguousarray(img, np.uint8)
+    out = np.empty(img.shape, np.int32)
+    lib.orc_fast_score_map(_p(img), img.shape[1], img.shape[0], img.strides[0], _p(out))
+    return out
+
+
+def fast_atan2(y, x):
+    return lib.orc_fast_atan2(float(y), float(x))
+
+
+def sincosf(x):
+    s = C.c_float(); c = C.c_float()
+    lib.orc_sincosf(C.c_float(x), C.byref(s), C.byref(c))
+    return s.value, c.value
+
+
+def distribute(cands, min_x, max_x, min_y, max_y, n_features):
+    cands = np.ascontiguousarray(cands, np.int32)
+    cap = len(cands) + 8
+    out = np.empty(cap, np.int32)
+    n = lib.orc_distribute(_p(cands), len(cands), min_x, max_x, min_y, max_y, n_features, _p(out), cap)
+    return out[:n].copy()
+
+
+def descriptor_distance(a, b):
+    a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+    return lib.orc_descriptor_distance(_p(a), _p(b))
+
+
+class Extractor:
+    """Oracle restatement of ORB_SLAM2::ORBextractor (reference src/ORBextractor.cc)."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.nlevels = nlevels
+        self.h = lib.orc_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
+        assert self.h
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib.orc_extractor_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        L = self.nlevels
+        sf, inv, s2, inv2 = (np.empty(L, np.float32) for _ in range(4))
+        npl = np.empty(L, np.int32); umax = np.empty(16, np.int32)
+        lib.orc_extractor_tables(self.h, _p(sf), _p(inv), _p(s2), _p(inv2), _p(npl), _p(umax))
+        return dict(sf=sf, inv_sf=inv, sigma2=s2, inv_sigma2=inv2, n_per_level=npl, umax=umax)
+
+    def extract(self, img, cap=None):
+        img = np.ascontiguousarray(img, np.uint8)
+        self._img = img
+        cap = cap or 200000
+        kps = np.empty(cap, KP_DTYPE); desc = np.empty((cap, 32), np.uint8)
+        if img.size == 0:
+            return kps[:0], desc[:0]
+        n = lib.orc_extract(self.h, _p(img), img.shape[1], img.shape[0], img.strides[0], _p(kps), _p(desc), cap)
+        assert n >= 0, "capacity"
+        return kps[:n].copy(), desc[:n].copy()
+
+    def _lvl(self, fn, l):
+        w = C.c_int32(); h = C.c_int32(); s = C.c_int32()
+        p = fn(self.h, l, C.byref(w), C.byref(h), C.byref(s))
+        if not p:
+            return None
+        buf = (C.c_uint8 * (s.value * h.value)).from_address(p)
+        return np.frombuffer(buf, np.uint8).reshape(h.value, s.value)[:, :w.value].copy()
+
+    def level(self, l):
+        return self._lvl(lib.orc_level, l)
+
+    def blurred_level(self, l):
+        return self._lvl(lib.orc_blurred_level, l)
+
+    def level_candidates(self, l):
+        cap = 1 << 20
+        out = np.empty((cap, 3), np.int32)
+        n = lib.orc_level_candidates(self.h, l, _p(out), cap)
+        return out[:n].copy()
+
+    def level_keypoints(self, l):
+        cap = 1 << 16
+        out = np.empty(cap, KP_DTYPE)
+        n = lib.orc_level_keypoints(self.h, l, _p(out), cap)
+        return out[:n].copy()

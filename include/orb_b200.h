@@ -1,0 +1,235 @@
+/* orb_b200.h — C ABI of the B200-native ORB-SLAM2 front-end hot path.
+ *
+ * Every entry point replaces one piece of the reference's C++ front end (paths are relative to
+ * the reference tree yg838457845/ORB_SLAM2-Chinese-annotation):
+ *
+ *   orb_extractor_create / destroy      ORBextractor::ORBextractor            src/ORBextractor.cc:428-489
+ *   orb_extractor_tables                GetScaleFactors() & friends           include/ORBextractor.h:63-83
+ *   orb_extract / orb_extract_batch     ORBextractor::operator()              src/ORBextractor.cc:1091-1169
+ *   orb_extract_device                  same, inputs already resident in HBM (bench "value" path)
+ *   orb_get_level                       public member mvImagePyramid          include/ORBextractor.h:85
+ *   orb_descriptor_distance             ORBmatcher::DescriptorDistance        src/ORBmatcher.cc:1814-1830
+ *   orb_match_bruteforce                all-pairs best / second-best Hamming  (inner loop of every Search*)
+ *   orb_assign_features_to_grid         Frame::AssignFeaturesToGrid           src/Frame.cc:261-276, 426-436
+ *   orb_search_by_projection_mappoints  ORBmatcher::SearchByProjection(F,MPs) src/ORBmatcher.cc:47-133
+ *   orb_search_by_projection_lastframe  ORBmatcher::SearchByProjection(C,L)   src/ORBmatcher.cc:1460-1619
+ *   orb_search_by_bow                   ORBmatcher::SearchByBoW(KF,F)         src/ORBmatcher.cc:164-306
+ *   orb_search_for_triangulation        ORBmatcher::SearchForTriangulation    src/ORBmatcher.cc:718-900
+ *   orb_stereo_match                    Frame::ComputeStereoMatches           src/Frame.cc:516-704
+ *
+ * Conventions: plain pointers and sizes only; the library never allocates caller-visible memory
+ * (the caller passes capacities); every function returns an orb_status (0 = ok).  All pointers are
+ * HOST pointers unless the parameter name starts with d_.  A handle owns its device buffers and
+ * one CUDA stream; distinct handles may be used concurrently from different threads (the
+ * reference runs the left and right extractor on two threads, src/Frame.cc:81-84), one handle is
+ * not re-entrant.  There is no CPU fallback: without a usable CUDA device every call fails with
+ * ORB_ERR_CUDA.
+ */
+#ifndef ORB_B200_H
+#define ORB_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    ORB_OK = 0,
+    ORB_ERR_BAD_ARG = 1,   /* null pointer, non-positive size, unsupported geometry */
+    ORB_ERR_CAPACITY = 2,  /* caller buffer or handle capacity too small */
+    ORB_ERR_CUDA = 3,      /* CUDA runtime error (orb_last_error() has the text) */
+    ORB_ERR_INTERNAL = 4   /* device-side overflow of an internal bound */
+} orb_status;
+
+/* Same 28-byte layout as cv::KeyPoint (pt.x, pt.y, size, angle, response, octave, class_id). */
+typedef struct {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orb_keypoint;
+
+typedef struct orb_extractor orb_extractor;
+
+const char* orb_last_error(void);
+int orb_device_count(void);
+
+/* ---------------------------------------------------------------- extractor */
+/* nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast: the reference constructor's
+ * arguments (include/ORBextractor.h:51-52).  max_batch images of at most max_w x max_h can be
+ * processed per call on CUDA device `device`. */
+int orb_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th_fast, int min_th_fast,
+                         int max_w, int max_h, int max_batch, int device, orb_extractor** out);
+void orb_extractor_destroy(orb_extractor* e);
+/* Per-level tables (nlevels entries each; any pointer may be NULL); umax has 16 entries. */
+int orb_extractor_tables(const orb_extractor* e, float* scale_factors, float* inv_scale_factors, float* sigma2,
+                         float* inv_sigma2, int32_t* features_per_level, int32_t* umax);
+/* Upper bound on keypoints one image can produce (>= nfeatures; the quadtree may overshoot). */
+int orb_extractor_max_keypoints(const orb_extractor* e);
+
+/* operator(): one 8-bit single-channel image (row stride in bytes).  Writes *n keypoints and
+ * n*32 descriptor bytes.  An empty image (w or h == 0) yields *n = 0 like the reference (:1095). */
+int orb_extract(orb_extractor* e, const uint8_t* img, int w, int h, int stride, orb_keypoint* kps,
+                uint8_t* desc, int cap, int32_t* n);
+/* A batch of same-sized images laid out img_stride bytes apart.  Image b writes at kps + b*cap,
+ * desc + b*cap*32, counts[b]. */
+int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, int h, int stride, size_t img_stride,
+                      orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts);
+/* Same, but the images are already in device memory and the results stay in the handle's device
+ * buffers (see orb_extractor_device_results).  Asynchronous on the handle's stream. */
+int orb_extract_device(orb_extractor* e, const uint8_t* d_imgs, int batch, int w, int h, int stride, size_t img_stride);
+/* Device views of the last batch's results: keypoints [batch][kp_cap], descriptors [batch][kp_cap][32],
+ * counts [batch].  Valid until the next extract call on this handle. */
+int orb_extractor_device_results(const orb_extractor* e, const orb_keypoint** d_kps, const uint8_t** d_desc,
+                                 const int32_t** d_counts, int* kp_cap);
+/* Copies the last batch's results to the host (synchronises the handle's stream). */
+int orb_extractor_download(orb_extractor* e, int batch, orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts);
+int orb_extractor_sync(orb_extractor* e);
+/* CUDA stream (cudaStream_t) the handle launches on; for event timing by the caller. */
+void* orb_extractor_stream(const orb_extractor* e);
+/* Number of kernel launches issued by the handle since creation. */
+long long orb_extractor_launch_count(const orb_extractor* e);
+
+/* Pyramid level `level` of image `image` of the last call (mvImagePyramid[level]).  border = 0
+ * copies the w x h level, border = 19 reproduces the reference's REFLECT_101 bordered buffer
+ * (src/ORBextractor.cc:1181-1203).  blurred != 0 returns the 7x7 Gaussian-blurred level the
+ * descriptors were sampled from instead.  *w, *h receive the unbordered level size. */
+int orb_get_level(orb_extractor* e, int image, int level, int blurred, int border, uint8_t* dst, int dst_stride,
+                  int dst_cap_bytes, int* w, int* h);
+/* Stage outputs of the last call, for stage-level parity tests: FAST candidates fed to the
+ * quadtree (x, y, score triples, window-relative, reference order) and the per-level keypoints
+ * chosen by the quadtree, level coordinates (x, y, score). */
+int orb_get_level_candidates(orb_extractor* e, int image, int level, int32_t* xys, int cap, int32_t* n);
+int orb_get_level_keypoints(orb_extractor* e, int image, int level, int32_t* xys, int cap, int32_t* n);
+
+/* ------------------------------------------------------------------ stereo */
+/* Frame::ComputeStereoMatches for image `image` of the last batches of the two extractor handles
+ * (left and right pyramids stay device-resident).  Keypoints/descriptors are the extractors' own
+ * outputs, re-read from device memory.  max_d = mbf / mb (src/Frame.cc:549; passed explicitly
+ * because the reference reads Frame::mb before it is assigned), min_d = 0 in the reference.
+ * u_right, depth: n_left floats each (-1 = no match). */
+int orb_stereo_match(orb_extractor* left, orb_extractor* right, int image, float mbf, float min_d, float max_d,
+                     float* u_right, float* depth, int cap, int32_t* n_left);
+/* Whole batch: outputs at u_right + b*cap, depth + b*cap.  Asynchronous variant keeps results on
+ * the device (d_u_right / d_depth: [batch][kp_cap] device buffers owned by `left`). */
+int orb_stereo_match_batch(orb_extractor* left, orb_extractor* right, int batch, float mbf, float min_d, float max_d,
+                           float* u_right, float* depth, int cap, int32_t* n_left);
+int orb_stereo_match_device(orb_extractor* left, orb_extractor* right, int batch, float mbf, float min_d, float max_d);
+int orb_stereo_device_results(const orb_extractor* left, const float** d_u_right, const float** d_depth);
+
+/* ----------------------------------------------------------------- matcher */
+typedef struct orb_matcher orb_matcher;
+/* Workspace for up to max_pairs frame pairs per call, each with at most max_n features per side. */
+int orb_matcher_create(int max_pairs, int max_n, int device, orb_matcher** out);
+void orb_matcher_destroy(orb_matcher* m);
+void* orb_matcher_stream(const orb_matcher* m);
+long long orb_matcher_launch_count(const orb_matcher* m);
+int orb_matcher_sync(orb_matcher* m);
+
+/* DescriptorDistance for n descriptor pairs (a[i], b[i]); 32 bytes each. */
+int orb_descriptor_distance(orb_matcher* m, const uint8_t* a, const uint8_t* b, int n, int32_t* dist);
+
+/* Brute force: for every row of A (n_a x 32) the best and second-best Hamming distance over all
+ * rows of B (n_b x 32) with the reference's scan semantics (strict <, first index wins):
+ * best_idx/best_dist/second_dist arrays of n_a entries per pair; pairs are laid out
+ * max-size apart (a + p*stride_a*32 ...).  */
+int orb_match_bruteforce(orb_matcher* m, const uint8_t* a, const uint8_t* b, int pairs, int n_a, int n_b,
+                         int32_t* best_idx, int32_t* best_dist, int32_t* second_dist);
+int orb_match_bruteforce_device(orb_matcher* m, const uint8_t* d_a, const uint8_t* d_b, int pairs, int n_a, int n_b,
+                                int32_t* d_best_idx, int32_t* d_best_dist, int32_t* d_second_dist);
+
+/* Frame grid (include/Frame.h:39-40: 64 x 48 cells).  Bounds and inverse cell sizes as the Frame
+ * stores them (mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv). */
+typedef struct {
+    float min_x, min_y, max_x, max_y;
+    float inv_w, inv_h;
+} orb_grid_params;
+/* cell_start: 64*48+1 offsets, cell_items: n indices; cell (ix, iy) is entry ix*48+iy, items in
+ * insertion order (ascending keypoint index), keypoints outside the grid are dropped. */
+int orb_assign_features_to_grid(orb_matcher* m, const float* kp_x, const float* kp_y, int n, const orb_grid_params* g,
+                                int32_t* cell_start, int32_t* cell_items, int32_t* n_items);
+
+/* One frame's features as SoA (undistorted keypoints mvKeysUn, mvuRight, mDescriptors). */
+typedef struct {
+    int32_t n;
+    const float* x;
+    const float* y;
+    const int32_t* octave;
+    const float* angle;
+    const float* u_right;      /* may be NULL: monocular (all -1) */
+    const uint8_t* desc;       /* n x 32 */
+    orb_grid_params grid;
+    const float* scale_factors; /* mvScaleFactors */
+    int32_t n_levels;
+} orb_frame_view;
+
+/* SearchByProjection(Frame&, vector<MapPoint*>&, th) (src/ORBmatcher.cc:47-133).  Per MapPoint:
+ * valid (mbTrackInView && !isBad()), projection (mTrackProjX/Y/XR), predicted level, view cosine,
+ * descriptor, blocks (Observations() > 0: a keypoint this point claims is skipped by later points).
+ * occupied[i] != 0: keypoint i already holds a MapPoint with observations (:90-93).
+ * match[i] receives the index of the MapPoint assigned to keypoint i or -1; returns nmatches. */
+typedef struct {
+    int32_t n;
+    const uint8_t* valid;
+    const float* proj_x;
+    const float* proj_y;
+    const float* proj_xr;
+    const int32_t* level;
+    const float* view_cos;
+    const uint8_t* desc;
+    const uint8_t* blocks;
+} orb_mappoint_view;
+int orb_search_by_projection_mappoints(orb_matcher* m, const orb_frame_view* f, const orb_mappoint_view* mps, float th,
+                                       float nn_ratio, const uint8_t* occupied, int32_t* match, int32_t* nmatches);
+
+/* SearchByProjection(Frame& Cur, const Frame& Last, th, bMono) (src/ORBmatcher.cc:1460-1619).
+ * Per Last-frame feature: valid (has a MapPoint and is not an outlier), camera-frame position of
+ * its MapPoint in the CURRENT frame (x3Dc = Rcw*x3Dw + tcw, computed by the caller with the
+ * reference's cv::Mat float algebra), octave and angle in the last frame, descriptor of the MapPoint,
+ * blocks (Observations() > 0).  forward/backward as computed at :1486-1487. */
+typedef struct {
+    int32_t n;
+    const uint8_t* valid;
+    const float* xc;
+    const float* yc;
+    const float* zc;
+    const int32_t* octave;
+    const float* angle;
+    const uint8_t* desc;
+    const uint8_t* blocks;
+} orb_lastframe_view;
+typedef struct {
+    float fx, fy, cx, cy, mbf;
+} orb_camera;
+int orb_search_by_projection_lastframe(orb_matcher* m, const orb_frame_view* cur, const orb_lastframe_view* last,
+                                       const orb_camera* cam, float th, int forward, int backward,
+                                       int check_orientation, const uint8_t* occupied, int32_t* match,
+                                       int32_t* nmatches);
+
+/* FeatureVector (DBoW2::FeatureVector = std::map<NodeId, vector<unsigned>>) flattened as CSR in
+ * ascending node id: node_ids[n_nodes], start[n_nodes+1], items[start[n_nodes]]. */
+typedef struct {
+    int32_t n_nodes;
+    const uint32_t* node_ids;
+    const int32_t* start;
+    const uint32_t* items;
+} orb_featvec_view;
+
+/* SearchByBoW(KeyFrame*, Frame&, matches) (src/ORBmatcher.cc:164-306).  kf_has_mappoint[i] != 0:
+ * KeyFrame feature i has a good MapPoint.  match_f[j] = KeyFrame feature index matched to Frame
+ * feature j or -1. */
+int orb_search_by_bow(orb_matcher* m, const orb_frame_view* kf, const orb_featvec_view* kf_fv,
+                      const uint8_t* kf_has_mappoint, const orb_frame_view* f, const orb_featvec_view* f_fv,
+                      float nn_ratio, int check_orientation, int32_t* match_f, int32_t* nmatches);
+
+/* SearchForTriangulation (src/ORBmatcher.cc:718-900).  f12: 3x3 row-major fundamental matrix;
+ * (ex, ey): epipole in KF2 (:728-730); *_has_mappoint: feature already has a MapPoint;
+ * level_sigma2: pKF2->mvLevelSigma2.  match12[i] = index in KF2 or -1 (pairs = ascending i). */
+int orb_search_for_triangulation(orb_matcher* m, const orb_frame_view* kf1, const orb_featvec_view* fv1,
+                                 const uint8_t* kf1_has_mappoint, const orb_frame_view* kf2,
+                                 const orb_featvec_view* fv2, const uint8_t* kf2_has_mappoint, const float* f12,
+                                 float ex, float ey, const float* level_sigma2, int only_stereo,
+                                 int check_orientation, int32_t* match12, int32_t* nmatches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORB_B200_H */

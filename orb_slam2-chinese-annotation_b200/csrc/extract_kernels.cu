@@ -1,0 +1,838 @@
+// sm_100a kernels of the ORB extractor (reference src/ORBextractor.cc).  Integer/byte work,
+// HBM- and ALU-bound; no tensor cores by design.
+//
+//   k_resize_level     ComputePyramid's cv::resize(INTER_LINEAR) 8u fixed point      :1172-1207
+//   k_gauss7           GaussianBlur(7x7, sigma 2, REFLECT_101) 8u fixed point         :1143-1145
+//   k_fast_cells       per-cell FAST-9/16 + NMS + iniTh->minTh retry                  :785-865
+//   k_quadtree         DistributeOctTree / DivideNode as array-backed list emulation  :500-782
+//   k_orient_describe  IC_Angle + fastAtan2 + rBRIEF + final keypoint assembly        :77-164, 1141-1167
+#include "orb_internal.h"
+#include "sincosf_glibc.h"
+
+__constant__ __align__(16) signed char c_pattern[1024] = {
+#include "../../include/orb_pattern_31.inc"
+};
+
+// ------------------------------------------------------------------------------------------
+// Pyramid: level l <- level l-1, OpenCV 8u INTER_LINEAR (11-bit coefficients).  One thread
+// produces 4 horizontally adjacent pixels and stores them as one 32-bit word.
+__global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr, const LevelGeom src, const LevelGeom dst) {
+    const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4;
+    const int y = blockIdx.y * 4 + threadIdx.y;
+    if (x4 >= dst.w || y >= dst.h) return;
+    const uint8_t* S = pyr + src.off + (size_t)blockIdx.z * src.img_stride;
+    uint8_t* D = pyr + dst.off + (size_t)blockIdx.z * dst.img_stride;
+    int sy0 = dst.yofs[y], sy1 = sy0 + 1;
+    sy0 = min(max(sy0, 0), src.h - 1);
+    sy1 = min(max(sy1, 0), src.h - 1);
+    const int b0 = dst.beta[2 * y], b1 = dst.beta[2 * y + 1];
+    const uint8_t* r0 = S + (size_t)sy0 * src.pitch;
+    const uint8_t* r1 = S + (size_t)sy1 * src.pitch;
+    uint32_t out = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int x = min(x4 + i, dst.w - 1);
+        const int sx = dst.xofs[x];
+        const int sx1 = min(sx + 1, src.w - 1);
+        const int a0 = dst.alpha[2 * x], a1 = dst.alpha[2 * x + 1];
+        const int h0 = r0[sx] * a0 + r0[sx1] * a1;
+        const int h1 = r1[sx] * a0 + r1[sx1] * a1;
+        int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+        v = min(max(v, 0), 255);
+        out |= (uint32_t)v << (8 * i);
+    }
+    // rows are pitch-padded to a multiple of 64 bytes, so the full word is always in bounds
+    *reinterpret_cast<uint32_t*>(D + (size_t)y * dst.pitch + x4) = out;
+}
+
+// ------------------------------------------------------------------------------------------
+// 7x7 Gaussian, sigma 2, BORDER_REFLECT_101 at the level's own edge, OpenCV >= 4 fixed point:
+// Q0.8 taps {18,34,48,56,48,34,18}; horizontal Q8.8 (u16), vertical Q16.16, (v + 2^15) >> 16.
+#define BLUR_TW 128
+#define BLUR_TH 32
+__device__ __forceinline__ int reflect101(int p, int len) {
+    if (len == 1) return 0;
+    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
+    return p;
+}
+
+__global__ void __launch_bounds__(256) k_gauss7(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, const Plan P) {
+    __shared__ uint8_t raw[BLUR_TH + 6][BLUR_TW + 8];
+    __shared__ uint16_t hor[BLUR_TH + 6][BLUR_TW];
+    int l = 0;
+    while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].tile_off) ++l;
+    const LevelGeom& G = P.lv[l];
+    const int t = blockIdx.x - G.tile_off;
+    const int tx = (t % G.tiles_x) * BLUR_TW, ty = (t / G.tiles_x) * BLUR_TH;
+    const uint8_t* S = pyr + G.off + (size_t)blockIdx.y * G.img_stride;
+    uint8_t* D = blur + G.off + (size_t)blockIdx.y * G.img_stride;
+    const int tid = threadIdx.x;
+    // stage the (TH+6) x (TW+6) source window with reflection
+    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW + 6); i += 256) {
+        const int ry = i / (BLUR_TW + 6), rx = i - ry * (BLUR_TW + 6);
+        const int sy = reflect101(min(ty + ry - 3, G.h + 2), G.h);
+        const int sx = reflect101(min(tx + rx - 3, G.w + 2), G.w);
+        raw[ry][rx] = S[(size_t)sy * G.pitch + sx];
+    }
+    __syncthreads();
+    for (int i = tid; i < (BLUR_TH + 6) * BLUR_TW; i += 256) {
+        const int ry = i / BLUR_TW, rx = i - ry * BLUR_TW;
+        const uint8_t* r = &raw[ry][rx];
+        hor[ry][rx] = (uint16_t)(18 * (r[0] + r[6]) + 34 * (r[1] + r[5]) + 48 * (r[2] + r[4]) + 56 * r[3]);
+    }
+    __syncthreads();
+    // each thread: 4 adjacent columns of 4 rows
+    for (int i = tid; i < BLUR_TH * (BLUR_TW / 4); i += 256) {
+        const int oy = i / (BLUR_TW / 4), ox = (i - oy * (BLUR_TW / 4)) * 4;
+        if (ty + oy >= G.h || tx + ox >= G.w) continue;
+        uint32_t out = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t v = 18u * (hor[oy][ox + k] + hor[oy + 6][ox + k]) + 34u * (hor[oy + 1][ox + k] + hor[oy + 5][ox + k]) +
+                               48u * (hor[oy + 2][ox + k] + hor[oy + 4][ox + k]) + 56u * hor[oy + 3][ox + k];
+            out |= ((v + 32768u) >> 16) << (8 * k);
+        }
+        *reinterpret_cast<uint32_t*>(D + (size_t)(ty + oy) * G.pitch + tx + ox) = out;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// FAST-9/16.  cv::FAST(cell, th, nms=true) on a cell view is equivalent to: threshold-free score
+// s = max(bright, dark) - 1 per interior pixel; corner at th <=> s >= th; a corner survives NMS
+// iff s is strictly greater than the raw scores of its 8 neighbours inside the cell interior
+// (outside counts as 0).  The set of strict local maxima does not depend on th, so the
+// iniTh -> minTh retry only re-filters the same list.
+#define FAST_THREADS 256
+__device__ __forceinline__ int fast_corner_score(const int v, const int (&p)[16], const int t) {
+    int d[25];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) d[k] = v - p[k];
+#pragma unroll
+    for (int k = 16; k < 25; ++k) d[k] = d[k - 16];
+    int a0 = t;
+#pragma unroll
+    for (int k = 0; k < 16; k += 2) {
+        int a = min(d[k + 1], d[k + 2]);
+        a = min(a, d[k + 3]); a = min(a, d[k + 4]); a = min(a, d[k + 5]);
+        a = min(a, d[k + 6]); a = min(a, d[k + 7]); a = min(a, d[k + 8]);
+        a0 = max(a0, min(a, d[k]));
+        a0 = max(a0, min(a, d[k + 9]));
+    }
+    int b0 = -a0;
+#pragma unroll
+    for (int k = 0; k < 16; k += 2) {
+        int b = max(d[k + 1], d[k + 2]);
+        b = max(b, d[k + 3]); b = max(b, d[k + 4]); b = max(b, d[k + 5]);
+        b = max(b, d[k + 6]); b = max(b, d[k + 7]); b = max(b, d[k + 8]);
+        b0 = min(b0, max(b, d[k]));
+        b0 = min(b0, max(b, d[k + 9]));
+    }
+    return -b0 - 1;  // max(t, bright, dark) - 1
+}
+
+// Dynamic shared memory: tile (tile_h x tile_p bytes) | scores ((ih+2) x (iw+2) bytes) | survivors (u16)
+__global__ void __launch_bounds__(FAST_THREADS)
+k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
+             const int smem_tile_bytes, const int smem_score_bytes) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ int s_nsurv;
+    __shared__ int s_wcnt[FAST_THREADS / 32][2];
+    __shared__ int s_woff[FAST_THREADS / 32];
+    __shared__ int s_sel;
+
+    int l = 0;
+    while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].cell_off) ++l;
+    const LevelGeom& G = P.lv[l];
+    const int cell = blockIdx.x - G.cell_off;
+    const int ci = cell / G.n_cols, cj = cell - ci * G.n_cols;
+    const int b = blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int* out_cnt = cell_cnt + (size_t)b * P.total_cells + blockIdx.x;
+
+    // cell view [iniX, maxX) x [iniY, maxY) (reference :819-839)
+    const int iniY = ORB_WIN + ci * G.h_cell, iniX = ORB_WIN + cj * G.w_cell;
+    int maxY = iniY + G.h_cell + 6, maxX = iniX + G.w_cell + 6;
+    if (iniY >= G.max_by - 3 || iniX >= G.max_bx - 6) { if (tid == 0) *out_cnt = 0; return; }
+    maxY = min(maxY, G.max_by);
+    maxX = min(maxX, G.max_bx);
+    const int tw = maxX - iniX, th = maxY - iniY;
+    const int iw = tw - 6, ih = th - 6;  // interior = tested pixels
+    if (iw <= 0 || ih <= 0) { if (tid == 0) *out_cnt = 0; return; }
+
+    uint8_t* tile = smem;
+    uint8_t* sc = smem + smem_tile_bytes;
+    uint16_t* surv = reinterpret_cast<uint16_t*>(smem + smem_tile_bytes + smem_score_bytes);
+    const int tp = G.w_cell + 6 + 2;  // tile pitch (>= tw)
+    const int sp = iw + 2;            // score pitch
+    const uint8_t* S = pyr + G.off + (size_t)b * G.img_stride + (size_t)iniY * G.pitch + iniX;
+    for (int i = tid; i < tw * th; i += FAST_THREADS) {
+        const int y = i / tw, x = i - y * tw;
+        tile[y * tp + x] = S[(size_t)y * G.pitch + x];
+    }
+    for (int i = tid; i < (ih + 2) * sp; i += FAST_THREADS) sc[i] = 0;
+    if (tid == 0) s_nsurv = 0;
+    __syncthreads();
+
+    // phase 1: cheap necessary test at the LOWER threshold; survivors are compacted so that the
+    // exact score (phase 2) runs on dense warps
+    const int t = P.min_th;
+    for (int base = 0; base < iw * ih; base += FAST_THREADS) {
+        const int i = base + tid;
+        bool pass = false;
+        if (i < iw * ih) {
+            const int y = i / iw, x = i - y * iw;
+            const uint8_t* c = tile + (y + 3) * tp + x + 3;
+            const int v = c[0], lo = v - t, hi = v + t;
+            const int p0 = c[3 * tp], p8 = c[-3 * tp], p4 = c[3], p12 = c[-3];
+            const int p2 = c[2 * tp + 2], p10 = c[-2 * tp - 2], p6 = c[-2 * tp + 2], p14 = c[2 * tp - 2];
+            const bool dark = (p0 < lo || p8 < lo) && (p4 < lo || p12 < lo) && (p2 < lo || p10 < lo) && (p6 < lo || p14 < lo);
+            const bool brt = (p0 > hi || p8 > hi) && (p4 > hi || p12 > hi) && (p2 > hi || p10 > hi) && (p6 > hi || p14 > hi);
+            pass = dark || brt;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        int wbase = 0;
+        if (lane == 0 && m) wbase = atomicAdd(&s_nsurv, __popc(m));
+        wbase = __shfl_sync(0xffffffffu, wbase, 0);
+        if (pass) surv[wbase + __popc(m & ((1u << lane) - 1))] = (uint16_t)i;
+    }
+    __syncthreads();
+    const int nsurv = s_nsurv;
+    for (int k = tid; k < nsurv; k += FAST_THREADS) {
+        const int i = surv[k];
+        const int y = i / iw, x = i - y * iw;
+        const uint8_t* c = tile + (y + 3) * tp + x + 3;
+        int p[16];
+        p[0] = c[3 * tp];          p[1] = c[3 * tp + 1];   p[2] = c[2 * tp + 2];   p[3] = c[tp + 3];
+        p[4] = c[3];               p[5] = c[-tp + 3];      p[6] = c[-2 * tp + 2];  p[7] = c[-3 * tp + 1];
+        p[8] = c[-3 * tp];         p[9] = c[-3 * tp - 1];  p[10] = c[-2 * tp - 2]; p[11] = c[-tp - 3];
+        p[12] = c[-3];             p[13] = c[tp - 3];      p[14] = c[2 * tp - 2];  p[15] = c[3 * tp - 1];
+        const int s = fast_corner_score(c[0], p, t);
+        if (s >= t) sc[(y + 1) * sp + x + 1] = (uint8_t)s;
+    }
+    __syncthreads();
+
+    // phase 3: strict local maxima, ordered (row-major) compaction.  Each warp owns a contiguous
+    // run of pixels; pass A counts, pass B writes.
+    const int npix = iw * ih;
+    const int per_warp = ((npix + FAST_THREADS - 1) / FAST_THREADS) * 32;  // multiple of 32
+    const int w_begin = warp * per_warp, w_end = min(w_begin + per_warp, npix);
+    int cnt_min = 0, cnt_ini = 0;
+    for (int i0 = w_begin; i0 < w_end; i0 += 32) {
+        const int i = i0 + lane;
+        int s = 0;
+        if (i < w_end) {
+            const int y = i / iw, x = i - y * iw;
+            const uint8_t* q = sc + (y + 1) * sp + x + 1;
+            s = q[0];
+            if (s && !(s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] && s > q[sp - 1] && s > q[sp] && s > q[sp + 1]))
+                s = 0;
+        }
+        cnt_min += __popc(__ballot_sync(0xffffffffu, s != 0));
+        cnt_ini += __popc(__ballot_sync(0xffffffffu, s >= P.ini_th));
+    }
+    if (lane == 0) { s_wcnt[warp][0] = cnt_min; s_wcnt[warp][1] = cnt_ini; }
+    __syncthreads();
+    if (tid == 0) {
+        int tot_ini = 0;
+        for (int w = 0; w < FAST_THREADS / 32; ++w) tot_ini += s_wcnt[w][1];
+        const int sel = tot_ini > 0 ? 1 : 0;  // empty at iniThFAST -> retry with minThFAST (:843-850)
+        int run = 0;
+        for (int w = 0; w < FAST_THREADS / 32; ++w) { s_woff[w] = run; run += s_wcnt[w][sel]; }
+        s_sel = sel;
+        *out_cnt = run;
+    }
+    __syncthreads();
+    const int th_sel = s_sel ? P.ini_th : 1;
+    uint32_t* out = stage + (size_t)b * P.stage_per_image + G.stage_off + (size_t)cell * G.cell_cap;
+    int off = s_woff[warp];
+    for (int i0 = w_begin; i0 < w_end; i0 += 32) {
+        const int i = i0 + lane;
+        int s = 0, x = 0, y = 0;
+        if (i < w_end) {
+            y = i / iw; x = i - y * iw;
+            const uint8_t* q = sc + (y + 1) * sp + x + 1;
+            s = q[0];
+            if (s < th_sel || !(s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] && s > q[sp - 1] && s > q[sp] && s > q[sp + 1]))
+                s = 0;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, s != 0);
+        if (s) {
+            // window-relative level coordinates: cell-view coords + 3 + (j*wCell, i*hCell)
+            const int kx = x + 3 + cj * G.w_cell, ky = y + 3 + ci * G.h_cell;
+            out[off + __popc(m & ((1u << lane) - 1))] = ((uint32_t)s << 24) | ((uint32_t)ky << 12) | (uint32_t)kx;
+        }
+        off += __popc(m);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Quadtree.  One CTA per (level, image).  The reference's std::list<ExtractorNode> is emulated
+// with an array R holding the list in REVERSE order (push_front == append), compacted after
+// every pass; a node's keys are a contiguous run of packed candidates that is stably 4-way
+// partitioned between two ping-pong key buffers.  Equal-size ties of the sorted expansion phase
+// (reference :703 sorts pair<int, ExtractorNode*>, i.e. by heap address) use the canonical rule
+// "later-created node first" == higher index in R.
+#define QT_THREADS 512
+#define QT_WARPS (QT_THREADS / 32)
+#define QT_BIG 1024  // nodes with more keys are partitioned by the whole CTA
+
+struct QNode {
+    int start;             // first key (bit 31: which key buffer holds the keys)
+    int count;
+    short x0, x1, y0, y1;  // UL.x, UR.x, UL.y, BL.y
+};
+
+struct QtShared {
+    int warp_sums[QT_WARPS + 1];
+    int scal[8];
+    int big_cnt[4];
+    int big_wc[QT_WARPS][4];
+};
+
+// exclusive scan over the CTA of one value per thread; returns the exclusive prefix, total in *total
+__device__ __forceinline__ int block_excl_scan(int v, int* total, int* warp_sums) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < QT_WARPS ? warp_sums[lane] : 0;
+        int winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += n;
+        }
+        if (lane < QT_WARPS) warp_sums[lane] = winc - w;
+        if (lane == 31) warp_sums[QT_WARPS] = winc;
+    }
+    __syncthreads();
+    const int res = inc - v + warp_sums[warp];
+    *total = warp_sums[QT_WARPS];
+    __syncthreads();
+    return res;
+}
+
+__device__ __forceinline__ int key_quadrant(uint32_t k, int sx, int sy) {
+    return (ORB_KEY_X(k) < sx ? 0 : 1) + (ORB_KEY_Y(k) < sy ? 0 : 2);
+}
+
+// stable 4-way partition of src[0..n) into dst by quadrant, done by one warp; returns counts in c[4]
+__device__ __forceinline__ void warp_partition4(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, int n, int sx, int sy, int (&c)[4]) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1;
+    c[0] = c[1] = c[2] = c[3] = 0;
+    if (n <= 32) {
+        uint32_t k = 0; int q = -1;
+        if (lane < n) { k = src[lane]; q = key_quadrant(k, sx, sy); }
+        unsigned m[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { m[j] = __ballot_sync(0xffffffffu, q == j); c[j] = __popc(m[j]); }
+        if (q >= 0) {
+            int pos = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) if (j < q) pos += c[j];
+            unsigned mq = q == 0 ? m[0] : q == 1 ? m[1] : q == 2 ? m[2] : m[3];
+            dst[pos + __popc(mq & lt)] = k;
+        }
+        return;
+    }
+    for (int i0 = 0; i0 < n; i0 += 32) {
+        const int i = i0 + lane;
+        const int q = i < n ? key_quadrant(src[i], sx, sy) : -1;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) c[j] += __popc(__ballot_sync(0xffffffffu, q == j));
+    }
+    int o[4] = {0, c[0], c[0] + c[1], c[0] + c[1] + c[2]};
+    for (int i0 = 0; i0 < n; i0 += 32) {
+        const int i = i0 + lane;
+        uint32_t k = 0; int q = -1;
+        if (i < n) { k = src[i]; q = key_quadrant(k, sx, sy); }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const unsigned m = __ballot_sync(0xffffffffu, q == j);
+            if (q == j) dst[o[j] + __popc(m & lt)] = k;
+            o[j] += __popc(m);
+        }
+    }
+}
+
+// same, by the whole CTA (all threads must call); counts returned in sh.big_cnt
+__device__ void block_partition4(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, int n, int sx, int sy, QtShared& sh) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt = (1u << lane) - 1;
+    if (tid < 4) sh.big_cnt[tid] = 0;
+    __syncthreads();
+    int c[4] = {0, 0, 0, 0};
+    for (int i = tid; i < n; i += QT_THREADS) c[key_quadrant(src[i], sx, sy)]++;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        int v = c[j];
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0 && v) atomicAdd(&sh.big_cnt[j], v);
+    }
+    __syncthreads();
+    int base[4] = {0, sh.big_cnt[0], sh.big_cnt[0] + sh.big_cnt[1], sh.big_cnt[0] + sh.big_cnt[1] + sh.big_cnt[2]};
+    for (int i0 = 0; i0 < n; i0 += QT_THREADS) {
+        const int i = i0 + tid;
+        uint32_t k = 0; int q = -1;
+        if (i < n) { k = src[i]; q = key_quadrant(k, sx, sy); }
+        unsigned m[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { m[j] = __ballot_sync(0xffffffffu, q == j); if (lane == 0) sh.big_wc[warp][j] = __popc(m[j]); }
+        __syncthreads();
+        if (q >= 0) {
+            int pos = base[q];
+            for (int w = 0; w < warp; ++w) pos += sh.big_wc[w][q];
+            const unsigned mq = q == 0 ? m[0] : q == 1 ? m[1] : q == 2 ? m[2] : m[3];
+            dst[pos + __popc(mq & lt)] = k;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int s = 0;
+            for (int w = 0; w < QT_WARPS; ++w) s += sh.big_wc[w][j];
+            base[j] += s;
+        }
+        __syncthreads();
+    }
+}
+
+// bitonic sort, descending, of n (power of two) 64-bit keys in shared memory
+__device__ void block_sort_desc(unsigned long long* a, int n) {
+    for (int k = 2; k <= n; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < n; i += QT_THREADS) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const unsigned long long x = a[i], y = a[ixj];
+                    const bool up = (i & k) == 0;  // descending overall: "up" blocks keep larger first
+                    if (up ? (x < y) : (x > y)) { a[i] = y; a[ixj] = x; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// Dynamic shared memory layout (cap = node_cap_max, p2 = next pow2 >= cap):
+//   QNode nodeA[cap] | QNode nodeB[cap] | int par[cap] | int cc[cap*4] | int pre_ne[cap+1] | int pre_g[cap] |
+//   int flag[cap] | u64 sortk[p2]
+__global__ void __launch_bounds__(QT_THREADS)
+k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, const uint32_t* __restrict__ stage,
+           uint32_t* __restrict__ keys, uint32_t* __restrict__ lvl_kp, int* __restrict__ lvl_cnt, int* __restrict__ lvl_ncand,
+           int* __restrict__ status, const Plan P, const int cap, const int p2) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ QtShared sh;
+    const int l = blockIdx.x, b = blockIdx.y;
+    const LevelGeom& G = P.lv[l];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    QNode* cur = reinterpret_cast<QNode*>(smem);
+    QNode* nxt = cur + cap;
+    int* par = reinterpret_cast<int*>(nxt + cap);
+    int* cc = par + cap;
+    int* pre_ne = cc + 4 * cap;
+    int* pre_g = pre_ne + cap + 1;
+    int* flag = pre_g + cap;
+    unsigned long long* sortk = reinterpret_cast<unsigned long long*>(smem + (((size_t)((uint8_t*)(flag + cap) - smem) + 7) & ~(size_t)7));
+
+    const int n_cells = G.n_cols * G.n_rows;
+    const int* ccnt = cell_cnt + (size_t)b * P.total_cells + G.cell_off;
+    int* cpre = cell_prefix + (size_t)b * P.total_cells + G.cell_off;
+    const uint32_t* stg = stage + (size_t)b * P.stage_per_image + G.stage_off;
+    uint32_t* kbuf0 = keys + (size_t)b * 2 * P.stage_per_image + G.stage_off;
+    uint32_t* kbuf1 = kbuf0 + P.stage_per_image;
+    uint32_t* out = lvl_kp + (size_t)b * P.kp_cap + G.kp_off;
+
+    // ---- 0. ordered gather of the per-cell FAST lists (cells row-major) into key buffer 0
+    int carry = 0;
+    for (int c0 = 0; c0 < n_cells; c0 += QT_THREADS) {
+        const int c = c0 + tid;
+        const int v = c < n_cells ? ccnt[c] : 0;
+        int tot;
+        const int ex = block_excl_scan(v, &tot, sh.warp_sums);
+        if (c < n_cells) cpre[c] = carry + ex;
+        carry += tot;
+    }
+    const int n = carry;
+    __syncthreads();
+    for (int c = warp; c < n_cells; c += QT_WARPS) {
+        const int cnt = ccnt[c], o = cpre[c];
+        const uint32_t* s = stg + (size_t)c * G.cell_cap;
+        for (int i = lane; i < cnt; i += 32) kbuf0[o + i] = s[i];
+    }
+    if (tid == 0) lvl_ncand[b * ORB_MAX_LEVELS + l] = n;
+    __syncthreads();
+    if (n == 0) { if (tid == 0) lvl_cnt[b * ORB_MAX_LEVELS + l] = 0; return; }
+
+    // ---- 1. root nodes (reference :562-607): key -> root (int)(x / hX), stable
+    const int N = G.n_feat;
+    int size = 0;
+    {
+        const int n_ini = G.n_ini;
+        const float hX = G.h_x;
+        int run = 0;
+        for (int r = 0; r < n_ini; ++r) {
+            int seg_begin = run;
+            for (int i0 = 0; i0 < n; i0 += QT_THREADS) {
+                const int i = i0 + tid;
+                uint32_t k = 0; int f = 0;
+                if (i < n) { k = kbuf0[i]; f = ((int)((float)ORB_KEY_X(k) / hX) == r); }
+                int tot;
+                const int ex = block_excl_scan(f, &tot, sh.warp_sums);
+                if (f) kbuf1[run + ex] = k;
+                run += tot;
+            }
+            if (tid == 0) {
+                QNode nd;
+                nd.start = seg_begin | (int)0x80000000;
+                nd.count = run - seg_begin;
+                nd.x0 = (short)(int)(hX * (float)r);
+                nd.x1 = (short)(int)(hX * (float)(r + 1));
+                nd.y0 = 0;
+                nd.y1 = (short)G.win_h;
+                nxt[r] = nd;  // list order; reversed below
+            }
+        }
+        __syncthreads();
+        // drop empty roots, reverse into cur
+        if (tid == 0) {
+            int m = 0;
+            for (int r = n_ini - 1; r >= 0; --r) if (nxt[r].count > 0) cur[m++] = nxt[r];
+            sh.scal[0] = m;
+        }
+        __syncthreads();
+        size = sh.scal[0];
+    }
+
+    // ---- 2. expansion passes
+    bool sorted_phase = false;
+    bool finish = false;
+    while (!finish) {
+        // a. parents in processing order
+        int np = 0;
+        if (!sorted_phase) {
+            int carry2 = 0;
+            for (int i0 = 0; i0 < size; i0 += QT_THREADS) {
+                const int i = i0 + tid;
+                const int f = (i < size && cur[i].count > 1) ? 1 : 0;
+                int tot;
+                const int ex = block_excl_scan(f, &tot, sh.warp_sums);
+                if (f) flag[i] = carry2 + ex;  // ascending rank, flipped below
+                carry2 += tot;
+            }
+            np = carry2;
+            __syncthreads();
+            for (int i = tid; i < size; i += QT_THREADS)
+                if (cur[i].count > 1) par[np - 1 - flag[i]] = i;
+        } else {
+            int carry2 = 0;
+            for (int i0 = 0; i0 < size; i0 += QT_THREADS) {
+                const int i = i0 + tid;
+                const int f = (i < size && cur[i].count > 1) ? 1 : 0;
+                int tot;
+                const int ex = block_excl_scan(f, &tot, sh.warp_sums);
+                if (f) sortk[carry2 + ex] = ((unsigned long long)(unsigned)cur[i].count << 32) | (unsigned)i;
+                carry2 += tot;
+            }
+            np = carry2;
+            int np2 = 1;
+            while (np2 < np) np2 <<= 1;
+            for (int i = np + tid; i < np2; i += QT_THREADS) sortk[i] = 0ull;
+            __syncthreads();
+            block_sort_desc(sortk, np2);
+            for (int i = tid; i < np; i += QT_THREADS) par[i] = (int)(sortk[i] & 0xffffffffu);
+        }
+        __syncthreads();
+        if (np == 0) break;  // every node holds one key: list cannot grow
+
+        // b. partition every parent's keys into the other key buffer
+        for (int k = 0; k < np; ++k) {  // big nodes: whole CTA (uniform branch)
+            const QNode nd = cur[par[k]];
+            if (nd.count <= QT_BIG) continue;
+            const int st = nd.start & 0x7fffffff;
+            const bool in1 = nd.start < 0;
+            const uint32_t* src = (in1 ? kbuf1 : kbuf0) + st;
+            uint32_t* dst = (in1 ? kbuf0 : kbuf1) + st;
+            const int sx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), sy = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
+            block_partition4(src, dst, nd.count, sx, sy, sh);
+            if (tid < 4) cc[4 * k + tid] = sh.big_cnt[tid];
+            __syncthreads();
+        }
+        for (int k = warp; k < np; k += QT_WARPS) {
+            const QNode nd = cur[par[k]];
+            if (nd.count > QT_BIG) continue;
+            const int st = nd.start & 0x7fffffff;
+            const bool in1 = nd.start < 0;
+            const uint32_t* src = (in1 ? kbuf1 : kbuf0) + st;
+            uint32_t* dst = (in1 ? kbuf0 : kbuf1) + st;
+            const int sx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), sy = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
+            int c[4];
+            warp_partition4(src, dst, nd.count, sx, sy, c);
+            if (lane < 4) cc[4 * k + lane] = lane == 0 ? c[0] : lane == 1 ? c[1] : lane == 2 ? c[2] : c[3];
+        }
+        __syncthreads();
+
+        // c. prefix of non-empty children and of list growth, in processing order
+        int carry_ne = 0;
+        for (int k0 = 0; k0 < np; k0 += QT_THREADS) {
+            const int k = k0 + tid;
+            int ne = 0;
+            if (k < np) ne = (cc[4 * k] > 0) + (cc[4 * k + 1] > 0) + (cc[4 * k + 2] > 0) + (cc[4 * k + 3] > 0);
+            int tot;
+            const int ex = block_excl_scan(ne, &tot, sh.warp_sums);
+            if (k < np) { pre_ne[k] = carry_ne + ex; pre_g[k] = carry_ne + ex + ne - (k + 1); }
+            carry_ne += tot;
+        }
+        if (tid == 0) { pre_ne[np] = carry_ne; sh.scal[1] = np; }
+        __syncthreads();
+        // pre_g[k] = size growth after dividing parents 0..k (inclusive)
+        int ncom = np;
+        if (sorted_phase) {
+            for (int k = tid; k < np; k += QT_THREADS)
+                if (size + pre_g[k] >= N && (k == 0 || size + pre_g[k - 1] < N)) atomicMin(&sh.scal[1], k + 1);
+            __syncthreads();
+            ncom = sh.scal[1];
+        }
+
+        // d. next list = surviving nodes (same relative order) ++ children in creation order
+        for (int i = tid; i < size; i += QT_THREADS) flag[i] = 1;
+        __syncthreads();
+        for (int k = tid; k < ncom; k += QT_THREADS) flag[par[k]] = 0;
+        __syncthreads();
+        int n_surv = 0;
+        for (int i0 = 0; i0 < size; i0 += QT_THREADS) {
+            const int i = i0 + tid;
+            const int f = i < size ? flag[i] : 0;
+            int tot;
+            const int ex = block_excl_scan(f, &tot, sh.warp_sums);
+            if (f) nxt[n_surv + ex] = cur[i];
+            n_surv += tot;
+        }
+        const int n_children = pre_ne[ncom];
+        int my_expand = 0;
+        for (int k = tid; k < ncom; k += QT_THREADS) {
+            const QNode nd = cur[par[k]];
+            const int hx = (nd.x1 - nd.x0 + 1) >> 1, hy = (nd.y1 - nd.y0 + 1) >> 1;
+            const int sx = nd.x0 + hx, sy = nd.y0 + hy;
+            const int flip = (nd.start & 0x80000000) ^ 0x80000000;
+            int st = nd.start & 0x7fffffff;
+            int pos = n_surv + pre_ne[k];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = cc[4 * k + q];
+                if (c > 0) {
+                    QNode ch;
+                    ch.start = st | flip;
+                    ch.count = c;
+                    ch.x0 = (short)((q & 1) ? sx : nd.x0);
+                    ch.x1 = (short)((q & 1) ? nd.x1 : sx);
+                    ch.y0 = (short)((q & 2) ? sy : nd.y0);
+                    ch.y1 = (short)((q & 2) ? nd.y1 : sy);
+                    nxt[pos++] = ch;
+                    my_expand += c > 1;
+                }
+                st += c;
+            }
+        }
+        int n_expand;
+        block_excl_scan(my_expand, &n_expand, sh.warp_sums);
+        const int new_size = n_surv + n_children;
+        if (new_size > cap) { if (tid == 0) atomicExch(status, ORB_ERR_INTERNAL); break; }
+        { QNode* t = cur; cur = nxt; nxt = t; }
+        __syncthreads();
+
+        // e. termination (reference :688-757)
+        if (new_size >= N || new_size == size) finish = true;
+        else if (!sorted_phase && new_size + 3 * n_expand > N) sorted_phase = true;
+        size = new_size;
+    }
+
+    // ---- 3. best response per node (first maximum wins), emitted in list order
+    for (int i = warp; i < size; i += QT_WARPS) {
+        const QNode nd = cur[i];
+        const uint32_t* src = ((nd.start < 0) ? kbuf1 : kbuf0) + (nd.start & 0x7fffffff);
+        unsigned long long best = 0ull;
+        for (int j = lane; j < nd.count; j += 32) {
+            const uint32_t k = src[j];
+            const unsigned long long v = ((unsigned long long)(k >> 24) << 32) | (unsigned)(0x7fffffff - j);
+            best = v > best ? v : best;
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            const unsigned long long v = __shfl_xor_sync(0xffffffffu, best, o);
+            best = v > best ? v : best;
+        }
+        if (lane == 0) out[size - 1 - i] = src[0x7fffffff - (int)(best & 0xffffffffu)];
+    }
+    if (tid == 0) lvl_cnt[b * ORB_MAX_LEVELS + l] = size;
+}
+
+// ------------------------------------------------------------------------------------------
+// Orientation + descriptor + final keypoint record.  One warp per keypoint slot.
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+    // cv::fastAtan2, float32, every operation individually rounded
+    const float k180pi = (float)(180.0 / 3.14159265358979323846);
+    const float p1 = 0.9997878412794807f * k180pi, p3 = -0.3258083974640975f * k180pi;
+    const float p5 = 0.1555786518463281f * k180pi, p7 = -0.04432655554792128f * k180pi;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, 2.2204460492503131e-16f));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, 2.2204460492503131e-16f));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+#define OD_WARPS 8
+__global__ void __launch_bounds__(OD_WARPS * 32)
+k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur, const uint32_t* __restrict__ lvl_kp,
+                  const int* __restrict__ lvl_cnt, orb_keypoint* __restrict__ kps, uint8_t* __restrict__ desc,
+                  int* __restrict__ counts, const Plan P) {
+    __shared__ signed char s_pat[1024];
+    reinterpret_cast<int*>(s_pat)[threadIdx.x] = reinterpret_cast<const int*>(c_pattern)[threadIdx.x];
+    __syncthreads();
+    const int b = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * OD_WARPS + (threadIdx.x >> 5);
+    const int* cnt = lvl_cnt + b * ORB_MAX_LEVELS;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        int t = 0;
+        for (int l = 0; l < P.nlevels; ++l) t += cnt[l];
+        counts[b] = t;
+    }
+    if (slot >= P.kp_cap) return;
+    int l = 0;
+    while (l + 1 < P.nlevels && slot >= P.lv[l + 1].kp_off) ++l;
+    const LevelGeom& G = P.lv[l];
+    const int idx = slot - G.kp_off;
+    if (idx >= cnt[l]) return;
+    int out_idx = idx;
+    for (int j = 0; j < l; ++j) out_idx += cnt[j];
+
+    const uint32_t key = lvl_kp[(size_t)b * P.kp_cap + slot];
+    const int px = ORB_KEY_X(key) + ORB_WIN, py = ORB_KEY_Y(key) + ORB_WIN;
+    const uint8_t* img = pyr + G.off + (size_t)b * G.img_stride + (size_t)py * G.pitch + px;
+
+    // IC_Angle (reference :77-113): integer moments over the radius-15 disc, lane = row
+    int m10 = 0, m01 = 0;
+    if (lane < 31) {
+        const int v = lane - ORB_HALF_PATCH;
+        const int d = P.umax[v < 0 ? -v : v];
+        const uint8_t* r = img + v * G.pitch;
+        int rs = 0;
+        for (int u = -d; u <= d; ++u) { const int val = r[u]; m10 += u * val; rs += val; }
+        m01 = v * rs;
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // rBRIEF (reference :119-164): lane = descriptor byte, 8 comparisons
+    const float rad = __fmul_rn(angle, 0.017453292519943295f);  // factorPI = (float)(CV_PI/180.f)
+    float a, bsin;
+    orb_sincosf(rad, &bsin, &a);
+    const uint8_t* c = blur + G.off + (size_t)b * G.img_stride + (size_t)py * G.pitch + px;
+    int val = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int i0 = (lane * 16 + 2 * k) * 2;
+        const float x0 = (float)s_pat[i0], y0 = (float)s_pat[i0 + 1];
+        const float x1 = (float)s_pat[i0 + 2], y1 = (float)s_pat[i0 + 3];
+        const int r0 = __float2int_rn(__fmaf_rn(x0, bsin, __fmul_rn(y0, a)));
+        const int q0 = __float2int_rn(__fmaf_rn(x0, a, -__fmul_rn(y0, bsin)));
+        const int r1 = __float2int_rn(__fmaf_rn(x1, bsin, __fmul_rn(y1, a)));
+        const int q1 = __float2int_rn(__fmaf_rn(x1, a, -__fmul_rn(y1, bsin)));
+        const int t0 = c[r0 * G.pitch + q0], t1 = c[r1 * G.pitch + q1];
+        val |= (t0 < t1) << k;
+    }
+    desc[((size_t)b * P.kp_cap + out_idx) * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        orb_keypoint kp;
+        kp.x = (float)px; kp.y = (float)py;
+        if (l != 0) { kp.x = __fmul_rn(kp.x, G.sf); kp.y = __fmul_rn(kp.y, G.sf); }
+        kp.size = G.patch_size;
+        kp.angle = angle;
+        kp.response = (float)ORB_KEY_S(key);
+        kp.octave = l;
+        kp.class_id = -1;
+        kps[(size_t)b * P.kp_cap + out_idx] = kp;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host-callable launchers (used by extractor.cu)
+void launch_resize(cudaStream_t s, uint8_t* pyr, const LevelGeom& src, const LevelGeom& dst, int batch) {
+    dim3 block(64, 4), grid((dst.w + 255) / 256, (dst.h + 3) / 4, batch);
+    k_resize_level<<<grid, block, 0, s>>>(pyr, src, dst);
+}
+void launch_gauss(cudaStream_t s, const uint8_t* pyr, uint8_t* blur, const Plan& P, int batch) {
+    dim3 grid(P.total_tiles, batch);
+    k_gauss7<<<grid, 256, 0, s>>>(pyr, blur, P);
+}
+static void fast_smem(const Plan& P, int* tile_bytes, int* score_bytes, int* total) {
+    int mt = 0, ms = 0, mv = 0;
+    for (int l = 0; l < P.nlevels; ++l) {
+        const LevelGeom& G = P.lv[l];
+        const int tp = G.w_cell + 8, th = G.h_cell + 6;
+        mt = max(mt, tp * th);
+        ms = max(ms, (G.w_cell + 2) * (G.h_cell + 2));
+        mv = max(mv, G.w_cell * G.h_cell);
+    }
+    *tile_bytes = (mt + 15) & ~15;
+    *score_bytes = (ms + 15) & ~15;
+    *total = *tile_bytes + *score_bytes + 2 * mv + 16;
+}
+cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch) {
+    int tb, sb, tot;
+    fast_smem(P, &tb, &sb, &tot);
+    if (tot > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, tot);
+        if (e != cudaSuccess) return e;
+    }
+    dim3 grid(P.total_cells, batch);
+    k_fast_cells<<<grid, FAST_THREADS, tot, s>>>(pyr, cell_cnt, stage, P, tb, sb);
+    return cudaSuccess;
+}
+size_t quadtree_smem(int cap, int* p2_out) {
+    int p2 = 1;
+    while (p2 < cap) p2 <<= 1;
+    *p2_out = p2;
+    size_t bytes = (size_t)cap * (2 * sizeof(QNode) + 4 + 16 + 4 + 4 + 4) + 4 + 8;
+    bytes = (bytes + 7) & ~(size_t)7;
+    return bytes + (size_t)p2 * 8;
+}
+cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefix, const uint32_t* stage, uint32_t* keys,
+                            uint32_t* lvl_kp, int* lvl_cnt, int* lvl_ncand, int* status, const Plan& P, int batch) {
+    int cap = 0;
+    for (int l = 0; l < P.nlevels; ++l) cap = max(cap, P.lv[l].node_cap);
+    int p2;
+    const size_t bytes = quadtree_smem(cap, &p2);
+    if (bytes > 200 * 1024) return cudaErrorInvalidConfiguration;
+    cudaError_t e = cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) return e;
+    dim3 grid(P.nlevels, batch);
+    k_quadtree<<<grid, QT_THREADS, bytes, s>>>(cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, status, P, cap, p2);
+    return cudaSuccess;
+}
+void launch_orient_describe(cudaStream_t s, const uint8_t* pyr, const uint8_t* blur, const uint32_t* lvl_kp, const int* lvl_cnt,
+                            orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int batch) {
+    dim3 grid((P.kp_cap + OD_WARPS - 1) / OD_WARPS, batch);
+    k_orient_describe<<<grid, OD_WARPS * 32, 0, s>>>(pyr, blur, lvl_kp, lvl_cnt, kps, desc, counts, P);
+}

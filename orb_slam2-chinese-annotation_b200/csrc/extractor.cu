@@ -1,0 +1,489 @@
+// Host side of the extractor C ABI (include/orb_b200.h): planning, buffers, launches, copies.
+// Mirrors ORB_SLAM2::ORBextractor (reference include/ORBextractor.h:45-114, src/ORBextractor.cc).
+#include "orb_internal.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+void launch_resize(cudaStream_t s, uint8_t* pyr, const LevelGeom& src, const LevelGeom& dst, int batch);
+void launch_gauss(cudaStream_t s, const uint8_t* pyr, uint8_t* blur, const Plan& P, int batch);
+cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch);
+cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefix, const uint32_t* stage, uint32_t* keys,
+                            uint32_t* lvl_kp, int* lvl_cnt, int* lvl_ncand, int* status, const Plan& P, int batch);
+size_t quadtree_smem(int cap, int* p2_out);
+void launch_orient_describe(cudaStream_t s, const uint8_t* pyr, const uint8_t* blur, const uint32_t* lvl_kp, const int* lvl_cnt,
+                            orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int batch);
+
+static thread_local std::string g_err;
+void orb_set_error(const std::string& s) { g_err = s; }
+extern "C" const char* orb_last_error(void) { return g_err.c_str(); }
+extern "C" int orb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+namespace {
+
+inline int cv_round_f(float v) { return (int)lrintf(v); }
+inline int cv_round_d(double v) { return (int)lrint(v); }
+inline int cv_floor_d(double v) { int i = (int)v; return i - (i > v); }
+inline int cv_ceil_d(double v) { int i = (int)v; return i + (i < v); }
+
+// Scale / feature tables (reference src/ORBextractor.cc:433-488)
+void make_tables(orb_extractor& e) {
+    const int L = e.nlevels;
+    e.sf.assign(L, 1.f); e.sigma2.assign(L, 1.f); e.inv_sf.assign(L, 1.f); e.inv_sigma2.assign(L, 1.f);
+    for (int i = 1; i < L; ++i) {
+        e.sf[i] = (float)((double)e.sf[i - 1] * e.scale_factor);  // float member * double member
+        e.sigma2[i] = e.sf[i] * e.sf[i];
+    }
+    for (int i = 0; i < L; ++i) { e.inv_sf[i] = 1.0f / e.sf[i]; e.inv_sigma2[i] = 1.0f / e.sigma2[i]; }
+    e.n_per_level.assign(L, 0);
+    const float factor = (float)(1.0 / e.scale_factor);
+    float want = (float)e.nfeatures * (1.f - factor) / (1.f - (float)std::pow((double)factor, (double)L));
+    int sum = 0;
+    for (int l = 0; l + 1 < L; ++l) {
+        e.n_per_level[l] = cv_round_f(want);
+        sum += e.n_per_level[l];
+        want *= factor;
+    }
+    e.n_per_level[L - 1] = std::max(e.nfeatures - sum, 0);
+    // rows of the radius-15 disc
+    int um[ORB_HALF_PATCH + 2] = {0};
+    const int vmax = cv_floor_d(ORB_HALF_PATCH * std::sqrt(2.f) / 2 + 1);
+    const int vmin = cv_ceil_d(ORB_HALF_PATCH * std::sqrt(2.f) / 2);
+    const double hp2 = ORB_HALF_PATCH * ORB_HALF_PATCH;
+    for (int v = 0; v <= vmax; ++v) um[v] = cv_round_d(std::sqrt(hp2 - v * v));
+    for (int v = ORB_HALF_PATCH, v0 = 0; v >= vmin; --v) {
+        while (um[v0] == um[v0 + 1]) ++v0;
+        um[v] = v0;
+        ++v0;
+    }
+    for (int v = 0; v < 16; ++v) e.umax[v] = um[v];
+}
+
+struct HostTables {
+    std::vector<int> xofs, yofs;
+    std::vector<short> alpha, beta;
+};
+
+// Per-axis INTER_LINEAR source index and 11-bit weights (OpenCV resize, 8u)
+void axis_table(int src, int dst, bool clamp_frac, std::vector<int>& ofs, std::vector<short>& w) {
+    const double scale = (double)src / dst;
+    ofs.resize(dst); w.resize(2 * (size_t)dst);
+    for (int d = 0; d < dst; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = cv_floor_d(f);
+        f -= s;
+        if (clamp_frac) {
+            if (s < 0) { f = 0; s = 0; }
+            if (s >= src - 1) { f = 0; s = src - 1; }
+        }
+        ofs[d] = s;
+        w[2 * d] = (short)cv_round_f((1.f - f) * 2048);
+        w[2 * d + 1] = (short)cv_round_f(f * 2048);
+    }
+}
+
+// Geometry of every level for a w x h input.  Returns bytes / slots needed per image.
+struct Needs { size_t pyr_bytes, cells, stage, tables_bytes; int kp_cap, node_cap_max; };
+
+int build_plan(const orb_extractor& e, int w, int h, Plan& P, Needs& need, std::vector<HostTables>* tabs) {
+    std::memset(&P, 0, sizeof(P));
+    P.nlevels = e.nlevels; P.w = w; P.h = h; P.ini_th = e.ini_th; P.min_th = e.min_th;
+    for (int v = 0; v < 16; ++v) P.umax[v] = e.umax[v];
+    size_t off = 0, stage = 0, tbytes = 0;
+    int cells = 0, tiles = 0, kp = 0, ncap_max = 0;
+    if (tabs) tabs->assign(e.nlevels, HostTables());
+    for (int l = 0; l < e.nlevels; ++l) {
+        LevelGeom& G = P.lv[l];
+        G.w = cv_round_f((float)w * e.inv_sf[l]);
+        G.h = cv_round_f((float)h * e.inv_sf[l]);
+        if (G.w < 1 || G.h < 1 || G.w > ORB_MAX_DIM || G.h > ORB_MAX_DIM) return ORB_ERR_BAD_ARG;
+        G.pitch = (G.w + 63) & ~63;
+        G.off = off;
+        G.img_stride = (size_t)G.pitch * G.h;
+        G.sf = e.sf[l];
+        G.patch_size = (float)(int)((float)ORB_PATCH * e.sf[l]);
+        G.n_feat = e.n_per_level[l];
+        G.max_bx = G.w - ORB_EDGE + 3;
+        G.max_by = G.h - ORB_EDGE + 3;
+        G.win_w = G.max_bx - ORB_WIN;
+        G.win_h = G.max_by - ORB_WIN;
+        G.cell_off = cells;
+        G.stage_off = stage;
+        G.kp_off = kp;
+        G.tile_off = tiles;
+        const float width = (float)G.win_w, height = (float)G.win_h;
+        const int n_cols = (int)(width / 30.f), n_rows = (int)(height / 30.f);
+        if (G.win_w > 0 && G.win_h > 0 && n_cols > 0 && n_rows > 0) {
+            G.n_cols = n_cols; G.n_rows = n_rows;
+            G.w_cell = (int)std::ceil(width / n_cols);
+            G.h_cell = (int)std::ceil(height / n_rows);
+            G.cell_cap = ((G.w_cell + 1) / 2) * ((G.h_cell + 1) / 2);  // strict local maxima cannot be 8-adjacent
+            G.n_ini = (int)std::round((float)G.win_w / (float)G.win_h);
+            if (G.n_ini < 1) return ORB_ERR_BAD_ARG;  // reference divides by zero here (aspect < 1:2)
+            G.h_x = (float)G.win_w / (float)G.n_ini;
+            G.node_cap = std::max(G.n_feat + 3, 4 * G.n_ini) + 1;
+        } else {  // level too small for a single cell: the reference's loops do not execute
+            G.n_cols = G.n_rows = 0; G.w_cell = G.h_cell = 1; G.cell_cap = 0; G.n_ini = 1; G.h_x = 1.f; G.node_cap = 1;
+        }
+        G.tiles_x = (G.w + 127) / 128;
+        G.tiles_y = (G.h + 31) / 32;
+        cells += G.n_cols * G.n_rows;
+        stage += (size_t)G.n_cols * G.n_rows * G.cell_cap;
+        kp += G.node_cap;
+        tiles += G.tiles_x * G.tiles_y;
+        off += G.img_stride;  // scaled by batch when laid out (levels are batch-major, see layout())
+        ncap_max = std::max(ncap_max, G.node_cap);
+        if (l > 0) {
+            tbytes += ((size_t)G.w * 8 + (size_t)G.h * 8 + 63) & ~(size_t)63;
+            if (tabs) {
+                HostTables& T = (*tabs)[l];
+                axis_table(P.lv[l - 1].w, G.w, true, T.xofs, T.alpha);
+                axis_table(P.lv[l - 1].h, G.h, false, T.yofs, T.beta);
+            }
+        }
+    }
+    P.total_cells = cells; P.total_tiles = tiles; P.kp_cap = kp; P.stage_per_image = stage;
+    need.pyr_bytes = off; need.cells = (size_t)cells; need.stage = stage; need.kp_cap = kp;
+    need.node_cap_max = ncap_max; need.tables_bytes = tbytes + 256;
+    return ORB_OK;
+}
+
+// Levels are stored batch-major: level l occupies [lvl_base(l) * batch, ...) so that one launch
+// walks all images of a level with a fixed stride.
+void layout_for_batch(Plan& P, int batch) {
+    size_t off = 0;
+    for (int l = 0; l < P.nlevels; ++l) {
+        P.lv[l].off = off;
+        off += P.lv[l].img_stride * (size_t)batch;
+    }
+}
+
+void free_buffers(orb_extractor* e) {
+    cudaFree(e->d_pyr); cudaFree(e->d_blur); cudaFree(e->d_cell_cnt); cudaFree(e->d_cell_prefix); cudaFree(e->d_stage);
+    cudaFree(e->d_keys); cudaFree(e->d_lvl_kp); cudaFree(e->d_lvl_cnt); cudaFree(e->d_lvl_ncand); cudaFree(e->d_kps);
+    cudaFree(e->d_desc); cudaFree(e->d_counts); cudaFree(e->d_status); cudaFree(e->d_tables); cudaFree(e->d_u_right);
+    cudaFree(e->d_depth); cudaFree(e->d_sad);
+    if (e->h_pin) cudaFreeHost(e->h_pin);
+    if (e->h_counts) cudaFreeHost(e->h_counts);
+    if (e->stream) cudaStreamDestroy(e->stream);
+}
+
+int ensure_plan(orb_extractor* e, int w, int h, int batch) {
+    if (w > e->max_w || h > e->max_h || batch > e->max_batch) {
+        orb_set_error("image or batch larger than the capacity given to orb_extractor_create");
+        return ORB_ERR_CAPACITY;
+    }
+    if (e->plan_w == w && e->plan_h == h) {
+        if (e->last_batch != batch) layout_for_batch(e->plan, batch);
+        e->last_batch = batch;
+        return ORB_OK;
+    }
+    Plan P; Needs need; std::vector<HostTables> tabs;
+    const int st = build_plan(*e, w, h, P, need, &tabs);
+    if (st != ORB_OK) { orb_set_error("unsupported image geometry"); return st; }
+    if (need.pyr_bytes > e->pyr_cap || need.cells > e->cells_cap || need.stage > e->stage_cap || need.kp_cap > e->kp_cap_max ||
+        need.tables_bytes > e->tables_cap) {
+        orb_set_error("geometry exceeds reserved capacity");
+        return ORB_ERR_CAPACITY;
+    }
+    // upload the resize coefficient tables
+    std::vector<uint8_t> blob(need.tables_bytes, 0);
+    size_t o = 0;
+    for (int l = 1; l < P.nlevels; ++l) {
+        LevelGeom& G = P.lv[l];
+        const HostTables& T = tabs[l];
+        uint8_t* base = (uint8_t*)e->d_tables;
+        G.xofs = (const int*)(base + o); std::memcpy(&blob[o], T.xofs.data(), (size_t)G.w * 4); o += (size_t)G.w * 4;
+        G.yofs = (const int*)(base + o); std::memcpy(&blob[o], T.yofs.data(), (size_t)G.h * 4); o += (size_t)G.h * 4;
+        G.alpha = (const short*)(base + o); std::memcpy(&blob[o], T.alpha.data(), (size_t)G.w * 4); o += (size_t)G.w * 4;
+        G.beta = (const short*)(base + o); std::memcpy(&blob[o], T.beta.data(), (size_t)G.h * 4); o += (size_t)G.h * 4;
+        o = (o + 63) & ~(size_t)63;
+    }
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    ORB_CUDA(cudaMemcpyAsync(e->d_tables, blob.data(), o, cudaMemcpyHostToDevice, e->stream));
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    layout_for_batch(P, batch);
+    e->plan = P; e->plan_w = w; e->plan_h = h; e->last_batch = batch;
+    return ORB_OK;
+}
+
+int run_pipeline(orb_extractor* e, int batch) {
+    Plan& P = e->plan;
+    cudaStream_t s = e->stream;
+    for (int l = 1; l < P.nlevels; ++l) { launch_resize(s, e->d_pyr, P.lv[l - 1], P.lv[l], batch); e->launches++; }
+    if (P.total_cells > 0) {
+        ORB_CUDA(launch_fast(s, e->d_pyr, e->d_cell_cnt, e->d_stage, P, batch)); e->launches++;
+    }
+    ORB_CUDA(launch_quadtree(s, e->d_cell_cnt, e->d_cell_prefix, e->d_stage, e->d_keys, e->d_lvl_kp, e->d_lvl_cnt, e->d_lvl_ncand,
+                             e->d_status, P, batch));
+    e->launches++;
+    launch_gauss(s, e->d_pyr, e->d_blur, P, batch); e->launches++;
+    launch_orient_describe(s, e->d_pyr, e->d_blur, e->d_lvl_kp, e->d_lvl_cnt, e->d_kps, e->d_desc, e->d_counts, P, batch);
+    e->launches++;
+    ORB_CUDA(cudaGetLastError());
+    return ORB_OK;
+}
+
+int check_status(orb_extractor* e) {
+    int st = 0;
+    ORB_CUDA(cudaMemcpyAsync(&st, e->d_status, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    if (st != 0) {
+        cudaMemsetAsync(e->d_status, 0, sizeof(int), e->stream);
+        orb_set_error("device-side bound exceeded");
+        return st;
+    }
+    return ORB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orb_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th, int max_w, int max_h,
+                         int max_batch, int device, orb_extractor** out) {
+    if (!out) return ORB_ERR_BAD_ARG;
+    *out = nullptr;
+    if (nfeatures < 1 || nlevels < 1 || nlevels > ORB_MAX_LEVELS || !(scale_factor > 1.0f) || ini_th < 1 || min_th < 1 ||
+        ini_th > 254 || min_th > 254 || max_w < 1 || max_h < 1 || max_batch < 1) {
+        orb_set_error("bad extractor parameters");
+        return ORB_ERR_BAD_ARG;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        orb_set_error("no CUDA device: this library has no CPU fallback");
+        return ORB_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) { orb_set_error("bad device index"); return ORB_ERR_BAD_ARG; }
+    ORB_CUDA(cudaSetDevice(device));
+    orb_extractor* e = new orb_extractor();
+    e->nfeatures = nfeatures; e->scale_factor = (double)scale_factor; e->nlevels = nlevels; e->ini_th = ini_th; e->min_th = min_th;
+    e->max_w = max_w; e->max_h = max_h; e->max_batch = max_batch; e->device = device;
+    make_tables(*e);
+    Plan P; Needs need;
+    int st = build_plan(*e, max_w, max_h, P, need, nullptr);
+    if (st != ORB_OK) { delete e; orb_set_error("unsupported maximum geometry (level size must be <= 4096, aspect >= 1:2)"); return st; }
+    int p2;
+    if (quadtree_smem(need.node_cap_max, &p2) > 200 * 1024) {
+        delete e; orb_set_error("nfeatures too large for the on-chip quadtree"); return ORB_ERR_BAD_ARG;
+    }
+    // Smaller images of a different aspect can need slightly more of some resources; keep slack.
+    e->pyr_cap = need.pyr_bytes + 4096;
+    e->cells_cap = need.cells + need.cells / 8 + 64;
+    e->stage_cap = need.stage + need.stage / 8 + 1024;
+    e->kp_cap_max = need.kp_cap + 64;
+    e->tables_cap = need.tables_bytes + 4096;
+    const size_t B = (size_t)max_batch;
+#define ALLOC(ptr, bytes) do { cudaError_t er = cudaMalloc((void**)&(ptr), (bytes)); if (er != cudaSuccess) { \
+        orb_set_error(std::string("cudaMalloc: ") + cudaGetErrorString(er)); free_buffers(e); delete e; return ORB_ERR_CUDA; } } while (0)
+    if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) { delete e; orb_set_error("stream"); return ORB_ERR_CUDA; }
+    ALLOC(e->d_pyr, e->pyr_cap * B);
+    ALLOC(e->d_blur, e->pyr_cap * B);
+    ALLOC(e->d_cell_cnt, e->cells_cap * B * sizeof(int));
+    ALLOC(e->d_cell_prefix, e->cells_cap * B * sizeof(int));
+    ALLOC(e->d_stage, e->stage_cap * B * sizeof(uint32_t));
+    ALLOC(e->d_keys, e->stage_cap * B * 2 * sizeof(uint32_t));
+    ALLOC(e->d_lvl_kp, (size_t)e->kp_cap_max * B * sizeof(uint32_t));
+    ALLOC(e->d_lvl_cnt, B * ORB_MAX_LEVELS * sizeof(int));
+    ALLOC(e->d_lvl_ncand, B * ORB_MAX_LEVELS * sizeof(int));
+    ALLOC(e->d_kps, (size_t)e->kp_cap_max * B * sizeof(orb_keypoint));
+    ALLOC(e->d_desc, (size_t)e->kp_cap_max * B * 32);
+    ALLOC(e->d_counts, B * sizeof(int));
+    ALLOC(e->d_status, sizeof(int));
+    ALLOC(e->d_tables, e->tables_cap);
+    ALLOC(e->d_u_right, (size_t)e->kp_cap_max * B * sizeof(float));
+    ALLOC(e->d_depth, (size_t)e->kp_cap_max * B * sizeof(float));
+    ALLOC(e->d_sad, (size_t)e->kp_cap_max * B * sizeof(int));
+#undef ALLOC
+    cudaMemset(e->d_status, 0, sizeof(int));
+    cudaMemset(e->d_lvl_cnt, 0, B * ORB_MAX_LEVELS * sizeof(int));
+    cudaMemset(e->d_counts, 0, B * sizeof(int));
+    cudaMemset(e->d_pyr, 0, e->pyr_cap * B);
+    cudaMemset(e->d_blur, 0, e->pyr_cap * B);
+    if (cudaMallocHost((void**)&e->h_counts, B * 2 * sizeof(int)) != cudaSuccess) { free_buffers(e); delete e; orb_set_error("pinned alloc"); return ORB_ERR_CUDA; }
+    *out = e;
+    return ORB_OK;
+}
+
+void orb_extractor_destroy(orb_extractor* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    free_buffers(e);
+    delete e;
+}
+
+int orb_extractor_tables(const orb_extractor* e, float* sf, float* inv_sf, float* s2, float* inv_s2, int32_t* npl, int32_t* umax) {
+    if (!e) return ORB_ERR_BAD_ARG;
+    for (int i = 0; i < e->nlevels; ++i) {
+        if (sf) sf[i] = e->sf[i];
+        if (inv_sf) inv_sf[i] = e->inv_sf[i];
+        if (s2) s2[i] = e->sigma2[i];
+        if (inv_s2) inv_s2[i] = e->inv_sigma2[i];
+        if (npl) npl[i] = e->n_per_level[i];
+    }
+    if (umax) for (int i = 0; i < 16; ++i) umax[i] = e->umax[i];
+    return ORB_OK;
+}
+
+int orb_extractor_max_keypoints(const orb_extractor* e) { return e ? e->kp_cap_max : 0; }
+void* orb_extractor_stream(const orb_extractor* e) { return e ? (void*)e->stream : nullptr; }
+long long orb_extractor_launch_count(const orb_extractor* e) { return e ? e->launches : 0; }
+
+int orb_extractor_sync(orb_extractor* e) {
+    if (!e) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(e->device));
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    return ORB_OK;
+}
+
+int orb_extract_device(orb_extractor* e, const uint8_t* d_imgs, int batch, int w, int h, int stride, size_t img_stride) {
+    if (!e || !d_imgs || batch < 1 || w < 1 || h < 1 || stride < w) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(e->device));
+    int st = ensure_plan(e, w, h, batch);
+    if (st != ORB_OK) return st;
+    const LevelGeom& G0 = e->plan.lv[0];
+    if (img_stride == (size_t)stride * h || batch == 1) {
+        ORB_CUDA(cudaMemcpy2DAsync(e->d_pyr + G0.off, G0.pitch, d_imgs, stride, w, (size_t)h * (batch == 1 ? 1 : batch),
+                                   cudaMemcpyDeviceToDevice, e->stream));
+    } else {
+        for (int b = 0; b < batch; ++b)
+            ORB_CUDA(cudaMemcpy2DAsync(e->d_pyr + G0.off + (size_t)b * G0.img_stride, G0.pitch, d_imgs + (size_t)b * img_stride, stride,
+                                       w, h, cudaMemcpyDeviceToDevice, e->stream));
+    }
+    return run_pipeline(e, batch);
+}
+
+int orb_extractor_device_results(const orb_extractor* e, const orb_keypoint** d_kps, const uint8_t** d_desc, const int32_t** d_counts,
+                                 int* kp_cap) {
+    if (!e) return ORB_ERR_BAD_ARG;
+    if (d_kps) *d_kps = e->d_kps;
+    if (d_desc) *d_desc = e->d_desc;
+    if (d_counts) *d_counts = e->d_counts;
+    if (kp_cap) *kp_cap = e->plan.kp_cap;
+    return ORB_OK;
+}
+
+int orb_extractor_download(orb_extractor* e, int batch, orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts) {
+    if (!e || !kps || !desc || !counts || batch < 1 || batch > e->last_batch) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(e->device));
+    ORB_CUDA(cudaMemcpyAsync(e->h_counts, e->d_counts, (size_t)batch * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    int st = check_status(e);
+    if (st != ORB_OK) return st;
+    const int kc = e->plan.kp_cap;
+    int rc = ORB_OK;
+    for (int b = 0; b < batch; ++b) {
+        const int n = e->h_counts[b];
+        counts[b] = n;
+        if (n > cap) { rc = ORB_ERR_CAPACITY; continue; }
+        if (n == 0) continue;
+        ORB_CUDA(cudaMemcpyAsync(kps + (size_t)b * cap, e->d_kps + (size_t)b * kc, (size_t)n * sizeof(orb_keypoint), cudaMemcpyDeviceToHost, e->stream));
+        ORB_CUDA(cudaMemcpyAsync(desc + (size_t)b * cap * 32, e->d_desc + (size_t)b * kc * 32, (size_t)n * 32, cudaMemcpyDeviceToHost, e->stream));
+    }
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    if (rc != ORB_OK) orb_set_error("keypoint capacity too small");
+    return rc;
+}
+
+int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, int h, int stride, size_t img_stride, orb_keypoint* kps,
+                      uint8_t* desc, int cap, int32_t* counts) {
+    if (!e || !counts || batch < 0) return ORB_ERR_BAD_ARG;
+    if (batch == 0) return ORB_OK;
+    if (w == 0 || h == 0) {  // _image.empty() -> return (reference :1095)
+        for (int b = 0; b < batch; ++b) counts[b] = 0;
+        return ORB_OK;
+    }
+    if (!imgs || !kps || !desc || w < 0 || h < 0 || stride < w) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(e->device));
+    int st = ensure_plan(e, w, h, batch);
+    if (st != ORB_OK) return st;
+    const LevelGeom& G0 = e->plan.lv[0];
+    for (int b = 0; b < batch; ++b)
+        ORB_CUDA(cudaMemcpy2DAsync(e->d_pyr + G0.off + (size_t)b * G0.img_stride, G0.pitch, imgs + (size_t)b * img_stride, stride, w, h,
+                                   cudaMemcpyHostToDevice, e->stream));
+    st = run_pipeline(e, batch);
+    if (st != ORB_OK) return st;
+    return orb_extractor_download(e, batch, kps, desc, cap, counts);
+}
+
+int orb_extract(orb_extractor* e, const uint8_t* img, int w, int h, int stride, orb_keypoint* kps, uint8_t* desc, int cap, int32_t* n) {
+    return orb_extract_batch(e, img, 1, w, h, stride, (size_t)stride * (size_t)(h > 0 ? h : 0), kps, desc, cap, n);
+}
+
+int orb_get_level(orb_extractor* e, int image, int level, int blurred, int border, uint8_t* dst, int dst_stride, int dst_cap_bytes,
+                  int* w, int* h) {
+    if (!e || !dst || e->plan_w < 0 || level < 0 || level >= e->nlevels || image < 0 || image >= e->last_batch || border < 0)
+        return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(e->device));
+    const LevelGeom& G = e->plan.lv[level];
+    if (w) *w = G.w;
+    if (h) *h = G.h;
+    const int bw = G.w + 2 * border, bh = G.h + 2 * border;
+    if (dst_stride < bw || (size_t)dst_stride * (bh - 1) + bw > (size_t)dst_cap_bytes) return ORB_ERR_CAPACITY;
+    const uint8_t* src = (blurred ? e->d_blur : e->d_pyr) + G.off + (size_t)image * G.img_stride;
+    ORB_CUDA(cudaMemcpy2DAsync(dst + (size_t)border * dst_stride + border, dst_stride, src, G.pitch, G.w, G.h, cudaMemcpyDeviceToHost, e->stream));
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    if (border > 0) {  // copyMakeBorder(BORDER_REFLECT_101) around the level (reference :1197-1203); never read by the hot path
+        auto refl = [](int p, int len) { if (len == 1) return 0; while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p; return p; };
+        for (int y = 0; y < bh; ++y) {
+            const int sy = refl(y - border, G.h) + border;
+            uint8_t* D = dst + (size_t)y * dst_stride;
+            const uint8_t* S = dst + (size_t)sy * dst_stride;
+            if (sy != y) std::memcpy(D + border, S + border, G.w);
+            for (int x = 0; x < border; ++x) {
+                D[x] = S[border + refl(x - border, G.w)];
+                D[border + G.w + x] = S[border + refl(G.w + x, G.w)];
+            }
+        }
+    }
+    return ORB_OK;
+}
+
+int orb_get_level_candidates(orb_extractor* e, int image, int level, int32_t* xys, int cap, int32_t* n) {
+    if (!e || !xys || !n || e->plan_w < 0 || level < 0 || level >= e->nlevels || image < 0 || image >= e->last_batch) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(e->device));
+    const Plan& P = e->plan;
+    const LevelGeom& G = P.lv[level];
+    const int nc = G.n_cols * G.n_rows;
+    std::vector<int> cnt(std::max(nc, 1));
+    ORB_CUDA(cudaMemcpyAsync(cnt.data(), e->d_cell_cnt + (size_t)image * P.total_cells + G.cell_off, (size_t)nc * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    std::vector<uint32_t> st((size_t)nc * G.cell_cap + 1);
+    ORB_CUDA(cudaMemcpyAsync(st.data(), e->d_stage + (size_t)image * P.stage_per_image + G.stage_off, (size_t)nc * G.cell_cap * 4, cudaMemcpyDeviceToHost, e->stream));
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    int m = 0;
+    for (int c = 0; c < nc; ++c)
+        for (int i = 0; i < cnt[c]; ++i) {
+            if (m < cap) {
+                const uint32_t k = st[(size_t)c * G.cell_cap + i];
+                xys[3 * m] = ORB_KEY_X(k); xys[3 * m + 1] = ORB_KEY_Y(k); xys[3 * m + 2] = ORB_KEY_S(k);
+            }
+            ++m;
+        }
+    *n = m;
+    return m > cap ? ORB_ERR_CAPACITY : ORB_OK;
+}
+
+int orb_get_level_keypoints(orb_extractor* e, int image, int level, int32_t* xys, int cap, int32_t* n) {
+    if (!e || !xys || !n || e->plan_w < 0 || level < 0 || level >= e->nlevels || image < 0 || image >= e->last_batch) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(e->device));
+    const Plan& P = e->plan;
+    const LevelGeom& G = P.lv[level];
+    int cnt = 0;
+    ORB_CUDA(cudaMemcpyAsync(&cnt, e->d_lvl_cnt + image * ORB_MAX_LEVELS + level, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    std::vector<uint32_t> k(std::max(cnt, 1));
+    ORB_CUDA(cudaMemcpyAsync(k.data(), e->d_lvl_kp + (size_t)image * P.kp_cap + G.kp_off, (size_t)cnt * 4, cudaMemcpyDeviceToHost, e->stream));
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    *n = cnt;
+    if (cnt > cap) return ORB_ERR_CAPACITY;
+    for (int i = 0; i < cnt; ++i) { xys[3 * i] = ORB_KEY_X(k[i]) + ORB_WIN; xys[3 * i + 1] = ORB_KEY_Y(k[i]) + ORB_WIN; xys[3 * i + 2] = ORB_KEY_S(k[i]); }
+    return ORB_OK;
+}
+
+}  // extern "C"

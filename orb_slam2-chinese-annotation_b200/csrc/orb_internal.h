@@ -1,0 +1,120 @@
+// Internal definitions shared by the extractor, stereo and matcher translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <string>
+#include <vector>
+#include "../../include/orb_b200.h"
+
+#define ORB_MAX_LEVELS 16
+#define ORB_EDGE 19        // EDGE_THRESHOLD   (reference src/ORBextractor.cc:74)
+#define ORB_HALF_PATCH 15  // HALF_PATCH_SIZE  (:73)
+#define ORB_PATCH 31       // PATCH_SIZE       (:72)
+#define ORB_WIN 16         // minBorderX = EDGE_THRESHOLD - 3 (:797)
+
+// Candidate / keypoint packing used between FAST, the quadtree and the descriptor stage:
+// bits 0..11 x, 12..23 y (window-relative level coordinates), 24..31 FAST score (<= 254).
+#define ORB_KEY_X(k) ((int)((k) & 0xfffu))
+#define ORB_KEY_Y(k) ((int)(((k) >> 12) & 0xfffu))
+#define ORB_KEY_S(k) ((int)((k) >> 24))
+#define ORB_MAX_DIM 4096  // largest level width/height representable in a packed key
+
+struct LevelGeom {
+    int w, h, pitch;            // level size and row pitch in bytes
+    unsigned long long off;     // byte offset of image 0 of this level inside the pyramid buffer
+    unsigned long long img_stride;  // bytes between consecutive images of this level
+    // FAST cell grid (reference src/ORBextractor.cc:797-814)
+    int n_cols, n_rows, w_cell, h_cell;
+    int max_bx, max_by;         // maxBorderX, maxBorderY
+    int cell_off;               // first cell of this level in the per-image cell arrays
+    int cell_cap;               // staging slots per cell
+    unsigned long long stage_off;   // first staging slot (u32 units) of this level within one image
+    // quadtree (reference :558-782)
+    int win_w, win_h;           // maxBorderX-minBorderX, maxBorderY-minBorderY
+    int n_ini;
+    float h_x;
+    int n_feat;                 // mnFeaturesPerLevel[level]
+    int node_cap;               // bound on list nodes == bound on keypoints of this level
+    int kp_off;                 // first slot of this level in the per-image level-keypoint arrays
+    // tiles of the blur kernel
+    int tiles_x, tiles_y, tile_off;
+    // resize coefficient tables (device pointers; level l is resampled from level l-1)
+    const int* xofs;
+    const short* alpha;
+    const int* yofs;
+    const short* beta;
+    float sf;                   // mvScaleFactor[level]
+    float patch_size;           // (float)(int)(PATCH_SIZE * sf)
+};
+
+struct Plan {
+    int nlevels, w, h;
+    int total_cells, total_tiles, kp_cap;
+    unsigned long long stage_per_image;   // u32 slots
+    unsigned long long pyr_bytes_per_batch_unit;  // unused by kernels
+    int ini_th, min_th;
+    int umax[16];
+    LevelGeom lv[ORB_MAX_LEVELS];
+};
+
+struct orb_extractor {
+    int nfeatures = 0, nlevels = 0, ini_th = 0, min_th = 0;
+    double scale_factor = 0;
+    int max_w = 0, max_h = 0, max_batch = 0, device = 0;
+    std::vector<float> sf, inv_sf, sigma2, inv_sigma2;
+    std::vector<int> n_per_level;
+    int umax[16];
+    cudaStream_t stream = nullptr;
+    long long launches = 0;
+
+    // geometry currently planned (w, h) and capacities reserved for (max_w, max_h)
+    Plan plan;
+    int plan_w = -1, plan_h = -1;
+    int last_batch = 0;
+
+    // device buffers (sized for max geometry x max_batch)
+    uint8_t* d_pyr = nullptr;
+    uint8_t* d_blur = nullptr;
+    size_t pyr_cap = 0;             // bytes
+    int* d_cell_cnt = nullptr;      // [batch][total_cells]
+    int* d_cell_prefix = nullptr;   // [batch][total_cells]
+    size_t cells_cap = 0;           // per image
+    uint32_t* d_stage = nullptr;    // [batch][stage_per_image]
+    uint32_t* d_keys = nullptr;     // [batch][2][stage_per_image]
+    size_t stage_cap = 0;           // per image (u32)
+    uint32_t* d_lvl_kp = nullptr;   // [batch][kp_cap]
+    int* d_lvl_cnt = nullptr;       // [batch][ORB_MAX_LEVELS]
+    int* d_lvl_ncand = nullptr;     // [batch][ORB_MAX_LEVELS]
+    int kp_cap_max = 0;
+    orb_keypoint* d_kps = nullptr;  // [batch][kp_cap]
+    uint8_t* d_desc = nullptr;      // [batch][kp_cap][32]
+    int* d_counts = nullptr;        // [batch]
+    int* d_status = nullptr;        // device-side error flag
+    void* d_tables = nullptr;       // resize coefficient tables
+    size_t tables_cap = 0;
+    // stereo outputs (owned by the LEFT handle)
+    float* d_u_right = nullptr;     // [batch][kp_cap]
+    float* d_depth = nullptr;
+    int* d_sad = nullptr;           // [batch][kp_cap] best SAD per left keypoint (-1 none)
+    // pinned host staging
+    uint8_t* h_pin = nullptr;
+    size_t h_pin_cap = 0;
+    int* h_counts = nullptr;        // pinned [max_batch * 2]
+};
+
+void orb_set_error(const std::string& s);
+#define ORB_CUDA(call)                                                                      \
+    do {                                                                                    \
+        cudaError_t err__ = (call);                                                         \
+        if (err__ != cudaSuccess) {                                                         \
+            orb_set_error(std::string(#call) + ": " + cudaGetErrorString(err__));          \
+            return ORB_ERR_CUDA;                                                            \
+        }                                                                                   \
+    } while (0)
+
+// Popcount Hamming distance of two 256-bit descriptors held as 8 x u32.
+__device__ __forceinline__ int orb_hamming256(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}

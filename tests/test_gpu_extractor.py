@@ -1,0 +1,112 @@
+"""GPU parity: the CUDA extractor (through the C ABI) against the CPU oracle, stage by stage and
+end to end.  Bit-exact for pyramid, blur, FAST candidates, quadtree selection, keypoints,
+descriptors; the angle is compared bit-exactly too (north_star allows 1e-5 relative)."""
+import importlib
+import numpy as np
+import pytest
+import orc
+
+pkg = importlib.import_module("orb_slam2-chinese-annotation_b200")
+synth = importlib.import_module("orb_slam2-chinese-annotation_b200.synth")
+pytestmark = pytest.mark.gpu
+
+CONFIGS = [  # (w, h, nfeatures)  BASELINE.json configs 1, 2, 3 + small/odd shapes
+    (640, 480, 1000),
+    (1241, 376, 2000),
+    (752, 480, 1200),
+    (333, 257, 500),
+    (200, 120, 300),
+]
+
+
+def _gpu_extractor(w, h, nf, batch=1):
+    ext = importlib.import_module("orb_slam2-chinese-annotation_b200.extractor")
+    return ext.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=batch)
+
+
+def _compare(img, g, o, nlevels=8):
+    kps, desc = g(img)
+    okps, odesc = o.extract(img)
+    for l in range(nlevels):
+        assert np.array_equal(g.image_pyramid(l), o.level(l)), "pyramid level %d" % l
+        oc = o.level_candidates(l); gc = g.level_candidates(l)
+        assert oc.shape == gc.shape and np.array_equal(oc, gc), "FAST candidates level %d (%d vs %d)" % (l, len(gc), len(oc))
+        ok = o.level_keypoints(l); gk = g.level_keypoints(l)
+        assert len(ok) == len(gk), "quadtree count level %d: %d vs %d" % (l, len(gk), len(ok))
+        assert np.array_equal(gk[:, 0], ok["x"].astype(np.int32)) and np.array_equal(gk[:, 1], ok["y"].astype(np.int32)), "quadtree level %d" % l
+        ob = o.blurred_level(l)
+        if ob is not None:
+            assert np.array_equal(g.image_pyramid(l, blurred=True), ob), "blur level %d" % l
+    assert len(kps) == len(okps)
+    for f in ("x", "y", "size", "response", "octave"):
+        assert np.array_equal(kps[f], okps[f]), f
+    assert np.all(kps["class_id"] == -1)
+    assert np.array_equal(kps["angle"].view(np.uint32), okps["angle"].view(np.uint32)), "angle bits"
+    assert np.array_equal(desc, odesc), "descriptors: %d rows differ" % int(np.any(desc != odesc, axis=1).sum())
+    return len(kps)
+
+
+@pytest.mark.parametrize("w,h,nf", CONFIGS)
+def test_extractor_matches_oracle(w, h, nf):
+    g = _gpu_extractor(w, h, nf)
+    o = orc.Extractor(nf, 1.2, 8, 20, 7)
+    for idx in range(3):
+        n = _compare(synth.make_image(w, h, idx), g, o)
+        assert n > 0
+
+
+def test_tables_match_oracle():
+    g = _gpu_extractor(640, 480, 1000)
+    o = orc.Extractor(1000, 1.2, 8, 20, 7)
+    tg, to = g._tables(), o.tables()
+    for k in to:
+        assert np.array_equal(tg[k], to[k]), k
+    assert list(tg["umax"]) == [15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3]
+    assert list(tg["n_per_level"]) == [217, 181, 151, 126, 105, 87, 73, 60]
+
+
+def test_noise_and_flat_images():
+    w, h = 400, 300
+    g = _gpu_extractor(w, h, 800)
+    o = orc.Extractor(800, 1.2, 8, 20, 7)
+    rng = np.random.default_rng(3)
+    _compare(rng.integers(0, 256, (h, w), dtype=np.uint8), g, o)          # dense corners: sorted-phase quadtree
+    flat = np.full((h, w), 90, np.uint8)
+    kps, desc = g(flat)
+    assert len(kps) == 0 and desc.shape == (0, 32)
+    sparse = flat.copy(); sparse[100:104, 150:154] = 255; sparse[200:203, 50:53] = 0
+    _compare(sparse, g, o)                                                   # few corners: quadtree stops without growth
+    low = (128 + (rng.integers(0, 256, (h, w)) - 128) // 12).astype(np.uint8)
+    _compare(low, g, o)                                                      # only the minThFAST retry fires
+
+
+def test_empty_image_and_bad_type():
+    g = _gpu_extractor(64, 64, 100)
+    kps, desc = g(np.empty((0, 0), np.uint8))
+    assert len(kps) == 0 and desc.shape == (0, 32)
+    with pytest.raises(ValueError):
+        g(np.zeros((64, 64), np.float32))
+
+
+def test_batch_equals_single():
+    w, h, nf, B = 752, 480, 1200, 5
+    g = _gpu_extractor(w, h, nf, batch=B)
+    imgs = np.stack([synth.make_image(w, h, 10 + i) for i in range(B)])
+    kps, desc, counts = g.extract_batch(imgs)
+    o = orc.Extractor(nf, 1.2, 8, 20, 7)
+    for b in range(B):
+        ok, od = o.extract(imgs[b])
+        assert counts[b] == len(ok)
+        for f in ("x", "y", "angle", "response", "octave"):
+            assert np.array_equal(kps[b][:counts[b]][f], ok[f])
+        assert np.array_equal(desc[b][:counts[b]], od)
+
+
+def test_bordered_pyramid_matches_reference_layout():
+    w, h = 333, 257
+    g = _gpu_extractor(w, h, 500)
+    img = synth.make_image(w, h, 2)
+    g(img)
+    o = orc.Extractor(500, 1.2, 8, 20, 7); o.extract(img)
+    for l in (0, 3, 7):
+        assert np.array_equal(g.image_pyramid(l, border=19), orc.border101(o.level(l), 19))

@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""Benchmark of the ORB front-end hot path (BASELINE.json: "ORB extract+match frames/s @1241x376
+2000kp").  One step = one batch of KITTI-shape stereo frames through: extract(left), extract(right),
+ComputeStereoMatches.  A frame is one stereo pair.
+
+  python bench.py --gpus N --steps K --warmup W              our CUDA path (N>1: under torchrun)
+  python bench.py --impl reference ...                        the reference's CPU path on host cores
+
+Prints ONE JSON line (see the keys below).  `value` is measured with inputs resident in HBM,
+`e2e` through the C ABI with host buffers (pinned H2D and D2H inside the timed region).
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "orb_slam2-chinese-annotation_b200"
+
+W, H, NFEAT = 1241, 376, 2000            # Examples/Stereo/KITTI00-02.yaml
+MBF, FX = 386.1448, 718.856
+N_LEVELS, SCALE, INI_TH, MIN_TH = 8, 1.2, 20, 7
+WORKLOAD = "kitti_stereo_1241x376_2000kp (BASELINE.json configs[1])"
+METRIC = "ORB extract+match frames/s @1241x376 2000kp"
+POOL = 16                                # distinct synthetic stereo pairs, tiled to the batch
+
+
+def algorithmic_bytes_per_image(n_kp):
+    """sum(levels) read + levels 1..7 written + blurred levels written + per-keypoint patches."""
+    sizes = [(1241, 376), (1034, 313), (862, 261), (718, 218), (598, 181), (499, 151), (416, 126), (346, 105)]
+    s = sum(w * h for w, h in sizes)
+    return s + (s - W * H) + s + n_kp * (749 + 961 + 32 + 28)
+
+
+def synth_pool():
+    synth = importlib.import_module(PKG + ".synth")
+    pairs = [synth.make_stereo_pair(W, H, i, fx=FX) for i in range(POOL)]
+    return np.stack([p[0] for p in pairs]), np.stack([p[1] for p in pairs])
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=2)
+        except Exception:
+            self.p.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------ CPU
+def cpu_pairs_per_s(n_pairs, threads, left, right):
+    """Times the CPU oracle (restatement of the reference's ORBextractor + ComputeStereoMatches) on
+    n_pairs stereo frames using `threads` host threads (ctypes releases the GIL)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import orc  # TEST INFRASTRUCTURE used here only as the timed CPU baseline
+
+    def work(tid, out):
+        ol = orc.Extractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH); orr = orc.Extractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH)
+        n = 0
+        for i in range(tid, n_pairs, threads):
+            kl, dl = ol.extract(left[i % POOL]); kr, dr = orr.extract(right[i % POOL])
+            orc.stereo_match(ol, orr, kl, dl, kr, dr, MBF, 0.0, FX)
+            n += 1
+        out[tid] = n
+
+    out = [0] * threads
+    ts = [threading.Thread(target=work, args=(t, out)) for t in range(threads)]
+    t0 = time.perf_counter()
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    dt = time.perf_counter() - t0
+    return sum(out) / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    left, right = synth_pool()
+    cores = os.cpu_count() or 1
+    per_step = max(16, 2 * cores)
+    cpu_pairs_per_s(min(per_step, cores), cores, left, right)  # page in
+    for _ in range(args.warmup):
+        cpu_pairs_per_s(per_step, cores, left, right)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_pairs_per_s(per_step, cores, left, right)
+    dt = time.perf_counter() - t0
+    val = per_step * args.steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frame": "stereo pair", "pairs_per_step": per_step},
+        "cpu_baseline": {"value": val, "unit": "frames/s", "cores": cores, "kind": "port",
+                         "sample": "%d stereo pairs per step x %d steps, %d host threads, CPU oracle (restatement of the reference's "
+                                   "ORBextractor + ComputeStereoMatches; the reference needs OpenCV C++ and cannot be built here)"
+                                   % (per_step, args.steps, cores)},
+        "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ GPU
+def run_ours(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    ext = importlib.import_module(PKG + ".extractor")
+    stereo = importlib.import_module(PKG + ".stereo")
+    capi = importlib.import_module(PKG + ".capi")
+    B = args.batch
+    left, right = synth_pool()
+    reps = (B + POOL - 1) // POOL
+    # every rank works on its own frames (weak scaling); rotate the pool so ranks differ
+    hl = np.roll(np.tile(left, (reps, 1, 1))[:B], rank, axis=0)
+    hr = np.roll(np.tile(right, (reps, 1, 1))[:B], rank, axis=0)
+
+    gl = ext.ORBextractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH, max_width=W, max_height=H, max_batch=B, device=local)
+    gr = ext.ORBextractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH, max_width=W, max_height=H, max_batch=B, device=local)
+    cap = gl.kp_cap
+
+    # ---- device-resident inputs for `value`
+    dl = torch.from_numpy(hl).cuda(); dr = torch.from_numpy(hr).cuda()
+    torch.cuda.synchronize()
+
+    def step_device():
+        gl.extract_device(dl.data_ptr(), B, W, H)
+        gr.extract_device(dr.data_ptr(), B, W, H)
+        stereo.compute_stereo_matches_device(gl, gr, MBF, FX, 0.0, batch=B)
+
+    def sync_all():
+        gl.sync(); gr.sync(); torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    sl = torch.cuda.ExternalStream(gl.stream, device=local)
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    sync_all()
+    l0 = gl.launch_count + gr.launch_count
+    sampler = ClockSampler(local)
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    sync_all()
+    # the stereo stage makes the left stream wait for the right stream, and the next step's right
+    # extraction waits for the left stream: timing on the left stream covers the whole step chain
+    e0.record(sl)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(sl)
+    gr.sync()
+    sync_all()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    launches = (gl.launch_count + gr.launch_count - l0)
+    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    value = world * B * args.steps / (ms_total * 1e-3)
+
+    # ---- per-stage event timing (separate, untimed-for-value pass) for the roofline object
+    gl.set_timing(True); gr.set_timing(True)
+    acc = {}
+    n_prof = 3
+    for _ in range(n_prof):
+        step_device()
+        sl_ms = gl.stage_ms(); sr_ms = gr.stage_ms()
+        for k in sl_ms:
+            acc[k] = acc.get(k, 0.0) + sl_ms[k] + (sr_ms[k] if not k.startswith("stereo") else 0.0)
+    gl.set_timing(False); gr.set_timing(False)
+    stages = {k: v / n_prof for k, v in acc.items()}   # ms per step, both images of the pairs
+    _, _, counts = gl.download(B)
+    n_kp = float(np.mean(counts))
+
+    # ---- e2e through the C ABI with pinned host buffers
+    pl = torch.from_numpy(hl).pin_memory(); pr = torch.from_numpy(hr).pin_memory()
+    kp_dt = capi.KP_DTYPE
+    o_k = [torch.empty((B, cap, kp_dt.itemsize), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    o_d = [torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    o_n = [np.zeros(B, np.int32) for _ in range(3)]
+    o_u = torch.empty((B, cap), dtype=torch.float32).pin_memory(); o_z = torch.empty((B, cap), dtype=torch.float32).pin_memory()
+    L = capi.lib()
+
+    def step_host():
+        capi.check(L.orb_extract_batch(gl.handle, C.c_void_p(pl.data_ptr()), B, W, H, W, C.c_size_t(W * H), C.c_void_p(o_k[0].data_ptr()),
+                                       C.c_void_p(o_d[0].data_ptr()), cap, capi.ptr(o_n[0])))
+        capi.check(L.orb_extract_batch(gr.handle, C.c_void_p(pr.data_ptr()), B, W, H, W, C.c_size_t(W * H), C.c_void_p(o_k[1].data_ptr()),
+                                       C.c_void_p(o_d[1].data_ptr()), cap, capi.ptr(o_n[1])))
+        capi.check(L.orb_stereo_match_batch(gl.handle, gr.handle, B, C.c_float(MBF), C.c_float(0.0), C.c_float(FX),
+                                            C.c_void_p(o_u.data_ptr()), C.c_void_p(o_z.data_ptr()), cap, capi.ptr(o_n[2])))
+
+    for _ in range(3):
+        step_host()
+    sync_all()
+    e_steps = max(3, args.steps // 2)
+    t0 = time.perf_counter()
+    for _ in range(e_steps):
+        step_host()
+    sync_all()
+    e_ms = (time.perf_counter() - t0) * 1e3
+    t = torch.tensor([e_ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e_val = world * B * e_steps / (float(t.item()) * 1e-3)
+    h2d = 2 * B * W * H
+    d2h = int((o_n[0].sum() + o_n[1].sum()) * (kp_dt.itemsize + 32) + o_n[2].sum() * 8 + 3 * B * 4)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+        ext_stages = {k: v for k, v in stages.items()}
+        dom = max(ext_stages, key=lambda k: ext_stages[k])
+        # algorithmic bytes of the whole extraction of one image x images per launch,
+        # attributed to the pipeline; the dominant kernel's own share is reported next to it
+        alg_img = algorithmic_bytes_per_image(n_kp)
+        per_kernel_bytes = {
+            "pyramid": lambda: (1444097 - W * H) * 2 + W * H,       # read levels 0..6 once, write levels 1..7
+            "fast_cells": lambda: 1444097 + 4 * 16000,               # read every level once, write candidate keys
+            "quadtree": lambda: 3 * 4 * 16000,                        # gather + partition passes over candidate keys (lower bound)
+            "blur": lambda: 2 * 1444097,                              # read + write every level
+            "orient_describe": lambda: n_kp * (749 + 961 + 32 + 28),
+        }
+        dom_bytes = per_kernel_bytes.get(dom, lambda: alg_img)() * B  # per launch (one image side)
+        dom_ms_launch = ext_stages[dom] / (1 if dom.startswith("stereo") else 2)
+        achieved = dom_bytes / (dom_ms_launch * 1e-3) / 1e9
+        pipe_ms = sum(v for k, v in stages.items())
+        cores = os.cpu_count() or 1
+        cpu_n = max(16, 2 * cores)
+        cpu_val, cpu_dt = cpu_pairs_per_s(cpu_n, cores, left, right)
+        line = {
+            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "frame": "stereo pair (2 images)", "pairs_per_step_per_gpu": B, "nfeatures": NFEAT,
+                       "levels": N_LEVELS, "l2": "inputs larger than L2: %d MB of images + %d MB of intermediates per step"
+                       % (2 * B * W * H >> 20, int(2 * B * 9.5)), "avg_keypoints": n_kp},
+            "e2e": {"value": e_val, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e_steps},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src,
+                         "pipeline_achieved": 2 * B * alg_img / (pipe_ms * 1e-3) / 1e9,
+                         "stage_ms_per_step": stages},
+            "cpu_baseline": {"value": cpu_val, "unit": "frames/s", "cores": cores, "kind": "port",
+                             "sample": "%d stereo pairs on %d host threads in %.1f s (CPU oracle: restatement of the reference "
+                                       "ORBextractor + ComputeStereoMatches)" % (cpu_n, cores, cpu_dt)},
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=256, help="stereo pairs per step per GPU")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

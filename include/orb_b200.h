@@ -87,6 +87,11 @@ int orb_extractor_sync(orb_extractor* e);
 void* orb_extractor_stream(const orb_extractor* e);
 /* Number of kernel launches issued by the handle since creation. */
 long long orb_extractor_launch_count(const orb_extractor* e);
+/* Optional CUDA-event timing of the stages of the LAST run on this handle (measurement aid, no
+ * reference counterpart).  ms[8]: pyramid, FAST cells, quadtree, blur, orient+describe, stereo
+ * rows, stereo match, stereo median (the stereo entries belong to the left handle). */
+int orb_extractor_set_timing(orb_extractor* e, int on);
+int orb_extractor_stage_ms(orb_extractor* e, float* ms);
 
 /* Pyramid level `level` of image `image` of the last call (mvImagePyramid[level]).  border = 0
  * copies the w x h level, border = 19 reproduces the reference's REFLECT_101 bordered buffer

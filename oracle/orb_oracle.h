@@ -50,8 +50,15 @@ int orc_level_keypoints(const orc_extractor*, int level, orc_keypoint* kps, int 
 int orc_distribute(const int32_t* xys, int n, int min_x, int max_x, int min_y, int max_y, int n_features,
                    int32_t* kept_idx, int cap);
 
-/* ---- matcher (reference src/ORBmatcher.cc) ---- */
+/* ---- matcher (reference src/ORBmatcher.cc) and stereo (src/Frame.cc:516-704); match_oracle.cpp ----
+ * The view structs (orb_frame_view, ...) are the plain C types of include/orb_b200.h. */
 int orc_descriptor_distance(const uint8_t* a, const uint8_t* b);
+/* Frame::ComputeStereoMatches; the two oracle extractors hold the pyramids of their last call.
+ * Returns the number of matches kept after the median cut. best_sad may be NULL. */
+int orc_stereo_match(const orc_extractor* L, const orc_extractor* R, const orc_keypoint* kpL, const uint8_t* dL, int nL,
+                     const orc_keypoint* kpR, const uint8_t* dR, int nR, const float* sf, const float* inv_sf, float mbf, float minD,
+                     float maxD, float* uRight, float* depth, int32_t* best_sad);
+void orc_match_bruteforce(const uint8_t* a, const uint8_t* b, int n_a, int n_b, int32_t* best_idx, int32_t* best_dist, int32_t* second_dist);
 
 #ifdef __cplusplus
 }

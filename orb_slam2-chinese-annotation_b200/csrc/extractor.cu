@@ -167,7 +167,9 @@ void free_buffers(orb_extractor* e) {
     cudaFree(e->d_pyr); cudaFree(e->d_blur); cudaFree(e->d_cell_cnt); cudaFree(e->d_cell_prefix); cudaFree(e->d_stage);
     cudaFree(e->d_keys); cudaFree(e->d_lvl_kp); cudaFree(e->d_lvl_cnt); cudaFree(e->d_lvl_ncand); cudaFree(e->d_kps);
     cudaFree(e->d_desc); cudaFree(e->d_counts); cudaFree(e->d_status); cudaFree(e->d_tables); cudaFree(e->d_u_right);
-    cudaFree(e->d_depth); cudaFree(e->d_sad);
+    cudaFree(e->d_depth); cudaFree(e->d_sad); cudaFree(e->d_row_start); cudaFree(e->d_row_items);
+    if (e->ev_done) cudaEventDestroy(e->ev_done);
+    for (int i = 0; i < ORB_N_STAGES + 4; ++i) if (e->ev_stage[i]) cudaEventDestroy(e->ev_stage[i]);
     if (e->h_pin) cudaFreeHost(e->h_pin);
     if (e->h_counts) cudaFreeHost(e->h_counts);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -215,16 +217,24 @@ int ensure_plan(orb_extractor* e, int w, int h, int batch) {
 int run_pipeline(orb_extractor* e, int batch) {
     Plan& P = e->plan;
     cudaStream_t s = e->stream;
+    const bool T = e->timing;
+    // event i is recorded BEFORE stage i; event 5 after the last extractor stage
+    if (T) cudaEventRecord(e->ev_stage[0], s);
     for (int l = 1; l < P.nlevels; ++l) { launch_resize(s, e->d_pyr, P.lv[l - 1], P.lv[l], batch); e->launches++; }
+    if (T) cudaEventRecord(e->ev_stage[1], s);
     if (P.total_cells > 0) {
         ORB_CUDA(launch_fast(s, e->d_pyr, e->d_cell_cnt, e->d_stage, P, batch)); e->launches++;
     }
+    if (T) cudaEventRecord(e->ev_stage[2], s);
     ORB_CUDA(launch_quadtree(s, e->d_cell_cnt, e->d_cell_prefix, e->d_stage, e->d_keys, e->d_lvl_kp, e->d_lvl_cnt, e->d_lvl_ncand,
                              e->d_status, P, batch));
     e->launches++;
+    if (T) cudaEventRecord(e->ev_stage[3], s);
     launch_gauss(s, e->d_pyr, e->d_blur, P, batch); e->launches++;
+    if (T) cudaEventRecord(e->ev_stage[4], s);
     launch_orient_describe(s, e->d_pyr, e->d_blur, e->d_lvl_kp, e->d_lvl_cnt, e->d_kps, e->d_desc, e->d_counts, P, batch);
     e->launches++;
+    if (T) { cudaEventRecord(e->ev_stage[5], s); for (int i = 0; i < 5; ++i) e->stage_valid[i] = true; }
     ORB_CUDA(cudaGetLastError());
     return ORB_OK;
 }
@@ -300,6 +310,10 @@ int orb_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini
     ALLOC(e->d_u_right, (size_t)e->kp_cap_max * B * sizeof(float));
     ALLOC(e->d_depth, (size_t)e->kp_cap_max * B * sizeof(float));
     ALLOC(e->d_sad, (size_t)e->kp_cap_max * B * sizeof(int));
+    e->row_items_cap = e->kp_cap_max * (2 * (int)std::ceil(2.0f * e->sf[nlevels - 1]) + 3);
+    ALLOC(e->d_row_start, B * (ORB_MAX_DIM + 1) * sizeof(int));
+    ALLOC(e->d_row_items, B * (size_t)e->row_items_cap * sizeof(int));
+    if (cudaEventCreateWithFlags(&e->ev_done, cudaEventDisableTiming) != cudaSuccess) { free_buffers(e); delete e; orb_set_error("event"); return ORB_ERR_CUDA; }
 #undef ALLOC
     cudaMemset(e->d_status, 0, sizeof(int));
     cudaMemset(e->d_lvl_cnt, 0, B * ORB_MAX_LEVELS * sizeof(int));
@@ -329,6 +343,30 @@ int orb_extractor_tables(const orb_extractor* e, float* sf, float* inv_sf, float
         if (npl) npl[i] = e->n_per_level[i];
     }
     if (umax) for (int i = 0; i < 16; ++i) umax[i] = e->umax[i];
+    return ORB_OK;
+}
+
+int orb_extractor_set_timing(orb_extractor* e, int on) {
+    if (!e) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(e->device));
+    if (on && !e->ev_stage[0])
+        for (int i = 0; i < ORB_N_STAGES + 4; ++i) ORB_CUDA(cudaEventCreate(&e->ev_stage[i]));
+    e->timing = on != 0;
+    for (int i = 0; i < ORB_N_STAGES; ++i) e->stage_valid[i] = false;
+    return ORB_OK;
+}
+
+int orb_extractor_stage_ms(orb_extractor* e, float* ms) {
+    if (!e || !ms) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(e->device));
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    for (int i = 0; i < ORB_N_STAGES; ++i) {
+        ms[i] = 0.f;
+        if (!e->stage_valid[i]) continue;
+        // extractor stages use events 0..5, stereo stages events 6..9
+        const int a = i < 5 ? i : i + 1, b = a + 1;
+        ORB_CUDA(cudaEventElapsedTime(&ms[i], e->ev_stage[a], e->ev_stage[b]));
+    }
     return ORB_OK;
 }
 

@@ -8,6 +8,9 @@
 #include "../../include/orb_b200.h"
 
 #define ORB_MAX_LEVELS 16
+// timed stages: 0 pyramid (7 resize launches) 1 FAST cells 2 quadtree 3 blur 4 orient+describe
+//               5 stereo rows 6 stereo match 7 stereo median
+#define ORB_N_STAGES 8
 #define ORB_EDGE 19        // EDGE_THRESHOLD   (reference src/ORBextractor.cc:74)
 #define ORB_HALF_PATCH 15  // HALF_PATCH_SIZE  (:73)
 #define ORB_PATCH 31       // PATCH_SIZE       (:72)
@@ -97,6 +100,14 @@ struct orb_extractor {
     float* d_u_right = nullptr;     // [batch][kp_cap]
     float* d_depth = nullptr;
     int* d_sad = nullptr;           // [batch][kp_cap] best SAD per left keypoint (-1 none)
+    int* d_row_start = nullptr;     // [batch][ORB_MAX_DIM + 1] vRowIndices as CSR
+    int* d_row_items = nullptr;     // [batch][row_items_cap]
+    int row_items_cap = 0;
+    cudaEvent_t ev_done = nullptr;
+    // optional per-stage event timing of the last pipeline run (bench.py roofline numbers)
+    bool timing = false;
+    cudaEvent_t ev_stage[ORB_N_STAGES + 4] = {nullptr};
+    bool stage_valid[ORB_N_STAGES] = {false};
     // pinned host staging
     uint8_t* h_pin = nullptr;
     size_t h_pin_cap = 0;

@@ -1,7 +1,311 @@
+// Frame::ComputeStereoMatches (reference src/Frame.cc:516-704) on the device-resident outputs of
+// two extractor handles.
+//
+//   k_stereo_rows    vRowIndices: right keypoint -> rows floor(y - 2 sf) .. ceil(y + 2 sf)      :527-544
+//   k_stereo_match   per left keypoint (one warp): row-band Hamming search, 11x11 SAD over
+//                    +-5 px on the pyramid level of the left keypoint, parabola sub-pixel fit    :558-689
+//   k_stereo_median  threshold 1.5 * 1.4 * median(SAD), invalidate outliers                      :690-703
+//
+// The per-row lists are built with atomics (unordered): the reference keeps the first candidate
+// on equal distance, i.e. the lowest right index, which a (distance, index) minimum reproduces.
 #include "orb_internal.h"
-extern "C" {
-int orb_stereo_match(orb_extractor*, orb_extractor*, int, float, float, float, float*, float*, int, int32_t*) { orb_set_error("wip"); return ORB_ERR_INTERNAL; }
-int orb_stereo_match_batch(orb_extractor*, orb_extractor*, int, float, float, float, float*, float*, int, int32_t*) { orb_set_error("wip"); return ORB_ERR_INTERNAL; }
-int orb_stereo_match_device(orb_extractor*, orb_extractor*, int, float, float, float) { orb_set_error("wip"); return ORB_ERR_INTERNAL; }
-int orb_stereo_device_results(const orb_extractor*, const float**, const float**) { orb_set_error("wip"); return ORB_ERR_INTERNAL; }
+
+#define ST_TH_HIGH 100
+#define ST_TH_ORB 75  // (TH_HIGH + TH_LOW) / 2
+
+struct StereoGeom {
+    int nlevels;
+    int h0;              // rows of level 0
+    int kp_cap_l, kp_cap_r;
+    int items_cap;       // per image
+    float sf[ORB_MAX_LEVELS], inv_sf[ORB_MAX_LEVELS];
+    LevelGeom lvl_l[ORB_MAX_LEVELS], lvl_r[ORB_MAX_LEVELS];
+};
+
+__global__ void __launch_bounds__(512)
+k_stereo_rows(const orb_keypoint* __restrict__ kps_r, const int* __restrict__ counts_r, int* __restrict__ row_start,
+              int* __restrict__ row_items, int* __restrict__ status, const StereoGeom S) {
+    extern __shared__ int s_rows[];  // h0 + 1 counters, then h0 + 1 cursors
+    __shared__ int s_warp[17];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int H = S.h0;
+    int* cnt = s_rows;
+    int* cur = s_rows + H + 1;
+    for (int i = tid; i <= H; i += 512) cnt[i] = 0;
+    __syncthreads();
+    const int nR = counts_r[b];
+    const orb_keypoint* K = kps_r + (size_t)b * S.kp_cap_r;
+    for (int i = tid; i < nR; i += 512) {
+        const float y = K[i].y, r = __fmul_rn(2.0f, S.sf[K[i].octave]);
+        const int maxr = min((int)ceilf(__fadd_rn(y, r)), H - 1), minr = max((int)floorf(__fsub_rn(y, r)), 0);
+        for (int yi = minr; yi <= maxr; ++yi) atomicAdd(&cnt[yi], 1);
+    }
+    __syncthreads();
+    // exclusive scan of cnt[0..H) -> cur, row_start
+    int carry = 0;
+    for (int i0 = 0; i0 < H; i0 += 512) {
+        const int i = i0 + tid;
+        const int v = i < H ? cnt[i] : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int n = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += n; }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = lane < 16 ? s_warp[lane] : 0, wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int n = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += n; }
+            if (lane < 16) s_warp[lane] = wi - w;
+            if (lane == 31) s_warp[16] = wi;
+        }
+        __syncthreads();
+        if (i < H) cur[i] = carry + inc - v + s_warp[warp];
+        carry += s_warp[16];
+        __syncthreads();
+    }
+    if (tid == 0) cur[H] = carry;
+    __syncthreads();
+    int* rs = row_start + (size_t)b * (ORB_MAX_DIM + 1);
+    for (int i = tid; i <= H; i += 512) rs[i] = cur[i];
+    if (carry > S.items_cap) { if (tid == 0) atomicExch(status, ORB_ERR_INTERNAL); return; }
+    __syncthreads();
+    int* items = row_items + (size_t)b * S.items_cap;
+    for (int i = tid; i < nR; i += 512) {
+        const float y = K[i].y, r = __fmul_rn(2.0f, S.sf[K[i].octave]);
+        const int maxr = min((int)ceilf(__fadd_rn(y, r)), H - 1), minr = max((int)floorf(__fsub_rn(y, r)), 0);
+        for (int yi = minr; yi <= maxr; ++yi) items[atomicAdd(&cur[yi], 1)] = i;
+    }
 }
+
+#define SM_WARPS 8
+__global__ void __launch_bounds__(SM_WARPS * 32)
+k_stereo_match(const orb_keypoint* __restrict__ kps_l, const uint8_t* __restrict__ desc_l, const int* __restrict__ counts_l,
+               const orb_keypoint* __restrict__ kps_r, const uint8_t* __restrict__ desc_r, const uint8_t* __restrict__ pyr_l,
+               const uint8_t* __restrict__ pyr_r, const int* __restrict__ row_start, const int* __restrict__ row_items,
+               float* __restrict__ u_right, float* __restrict__ depth, int* __restrict__ sad, const StereoGeom S, const float mbf,
+               const float min_d, const float max_d) {
+    __shared__ int s_l[SM_WARPS][11][12];
+    __shared__ int s_r[SM_WARPS][11][22];
+    const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int iL = blockIdx.x * SM_WARPS + warp;
+    if (iL >= counts_l[b]) return;
+    const size_t oL = (size_t)b * S.kp_cap_l + iL;
+    if (lane == 0) { u_right[oL] = -1.0f; depth[oL] = -1.0f; sad[oL] = -1; }
+    const orb_keypoint kl = kps_l[oL];
+    const float uL = kl.x, vL = kl.y;
+    const int row = (int)vL;
+    if (row < 0 || row >= S.h0) return;
+    const int* rs = row_start + (size_t)b * (ORB_MAX_DIM + 1);
+    const int c0 = rs[row], c1 = rs[row + 1];
+    if (c0 == c1) return;
+    const float minU = __fsub_rn(uL, max_d), maxU = __fsub_rn(uL, min_d);
+    if (maxU < 0) return;
+
+    const uint4* dl = reinterpret_cast<const uint4*>(desc_l + oL * 32);
+    const uint4 a0 = dl[0], a1 = dl[1];
+    const int* items = row_items + (size_t)b * S.items_cap;
+    const orb_keypoint* KR = kps_r + (size_t)b * S.kp_cap_r;
+    const uint8_t* DR = desc_r + (size_t)b * S.kp_cap_r * 32;
+    unsigned best = ((unsigned)ST_TH_HIGH << 20);  // (dist << 20) | iR ; strict < against TH_HIGH
+    for (int c = c0 + lane; c < c1; c += 32) {
+        const int iR = items[c];
+        const orb_keypoint kr = KR[iR];
+        if (kr.octave < kl.octave - 1 || kr.octave > kl.octave + 1) continue;
+        if (kr.x >= minU && kr.x <= maxU) {
+            const uint4* dr = reinterpret_cast<const uint4*>(DR + (size_t)iR * 32);
+            const unsigned d = (unsigned)orb_hamming256(a0, a1, dr[0], dr[1]);
+            best = min(best, (d << 20) | (unsigned)iR);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    const int bestDist = (int)(best >> 20);
+    if (bestDist >= ST_TH_ORB) return;
+    const int bestR = (int)(best & 0xfffffu);
+
+    // sub-pixel refinement by sliding an 11x11 window on the left keypoint's pyramid level
+    const int oct = kl.octave;
+    const float isf = S.inv_sf[oct];
+    const float uR0 = KR[bestR].x;
+    const int su = (int)roundf(__fmul_rn(kl.x, isf)), sv = (int)roundf(__fmul_rn(kl.y, isf)), sr = (int)roundf(__fmul_rn(uR0, isf));
+    const LevelGeom& GL = S.lvl_l[oct];
+    const LevelGeom& GR = S.lvl_r[oct];
+    const int w = 5, L = 5;
+    if (sr + L - w < 0 || sr + L + w + 1 >= GR.w) return;            // reference :633
+    // the reference would throw from cv::Mat::rowRange/colRange on these; they cannot occur for
+    // keypoints produced by the extractor (>= 19 px from every level edge)
+    if (sv - w < 0 || sv + w >= GL.h || sv + w >= GR.h || su - w < 0 || su + w >= GL.w || sr - L - w < 0 || sr + L + w >= GR.w) return;
+    const uint8_t* PL = pyr_l + GL.off + (size_t)b * GL.img_stride + (size_t)(sv - w) * GL.pitch + (su - w);
+    const uint8_t* PR = pyr_r + GR.off + (size_t)b * GR.img_stride + (size_t)(sv - w) * GR.pitch + (sr - L - w);
+    for (int i = lane; i < 11 * 11; i += 32) { const int y = i / 11, x = i - y * 11; s_l[warp][y][x] = PL[(size_t)y * GL.pitch + x]; }
+    for (int i = lane; i < 11 * 21; i += 32) { const int y = i / 21, x = i - y * 21; s_r[warp][y][x] = PR[(size_t)y * GR.pitch + x]; }
+    __syncwarp();
+    int dist = 0;
+    if (lane < 22) {
+        const int s = lane >> 1, half = lane & 1;  // shift index 0..10 (incR = s - 5)
+        const int cl = s_l[warp][5][5], cr = s_r[warp][5][s + 5];
+        const int y0 = half ? 6 : 0, y1 = half ? 11 : 6;
+        for (int y = y0; y < y1; ++y)
+#pragma unroll
+            for (int x = 0; x < 11; ++x) dist += abs((s_l[warp][y][x] - cl) - (s_r[warp][y][s + x] - cr));
+    }
+    dist += __shfl_xor_sync(0xffffffffu, dist, 1);  // lanes 2s, 2s+1 now hold SAD(s)
+    // first minimum over s = 0..10
+    unsigned key = lane < 22 ? (((unsigned)dist << 8) | (unsigned)(lane >> 1)) : 0xffffffffu;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
+    const int bs = (int)(key & 0xffu), bestSad = (int)(key >> 8);
+    const int bestinc = bs - L;
+    const float d1 = (float)__shfl_sync(0xffffffffu, dist, max(2 * (bs - 1), 0));
+    const float d2 = (float)bestSad;
+    const float d3 = (float)__shfl_sync(0xffffffffu, dist, min(2 * (bs + 1), 20));
+    if (bestinc == -L || bestinc == L) return;
+    if (lane != 0) return;
+    const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+    if (deltaR < -1 || deltaR > 1) return;
+    float bestuR = __fmul_rn(S.sf[oct], __fadd_rn(__fadd_rn((float)sr, (float)bestinc), deltaR));
+    float disparity = __fsub_rn(uL, bestuR);
+    if (disparity >= min_d && disparity < max_d) {
+        if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }
+        depth[oL] = __fdiv_rn(mbf, disparity);
+        u_right[oL] = bestuR;
+        sad[oL] = bestSad;
+    }
+}
+
+__global__ void __launch_bounds__(512)
+k_stereo_median(const int* __restrict__ counts_l, float* __restrict__ u_right, float* __restrict__ depth, const int* __restrict__ sad,
+                const int kp_cap) {
+    __shared__ int hist[256];
+    __shared__ int s_sel[3];
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int n = counts_l[b];
+    const int* sd = sad + (size_t)b * kp_cap;
+    // SAD <= 121 * 510 < 2^16: two-pass radix select of the element at sorted position size/2
+    if (tid < 256) hist[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += 512) { const int v = sd[i]; if (v >= 0) atomicAdd(&hist[(v >> 8) & 0xff], 1); }
+    __syncthreads();
+    if (tid == 0) {
+        int total = 0;
+        for (int i = 0; i < 256; ++i) total += hist[i];
+        int k = total / 2, hi = 0;
+        if (total > 0) { while (k >= hist[hi]) { k -= hist[hi]; ++hi; } }
+        s_sel[0] = total; s_sel[1] = hi; s_sel[2] = k;
+    }
+    __syncthreads();
+    if (s_sel[0] == 0) return;  // reference indexes an empty vector here (undefined); nothing to invalidate
+    const int hi = s_sel[1];
+    if (tid < 256) hist[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += 512) { const int v = sd[i]; if (v >= 0 && ((v >> 8) & 0xff) == hi) atomicAdd(&hist[v & 0xff], 1); }
+    __syncthreads();
+    if (tid == 0) {
+        int k = s_sel[2], lo = 0;
+        while (k >= hist[lo]) { k -= hist[lo]; ++lo; }
+        s_sel[1] = (hi << 8) | lo;
+    }
+    __syncthreads();
+    const float median = (float)s_sel[1];
+    const float th = __fmul_rn(1.5f * 1.4f, median);
+    for (int i = tid; i < n; i += 512) {
+        const int v = sd[i];
+        if (v >= 0 && !((float)v < th)) { u_right[(size_t)b * kp_cap + i] = -1.0f; depth[(size_t)b * kp_cap + i] = -1.0f; }
+    }
+}
+
+static int stereo_launch(orb_extractor* l, orb_extractor* r, int batch, float mbf, float min_d, float max_d) {
+    if (!l || !r || batch < 1 || l->plan_w < 0 || r->plan_w < 0 || batch > l->last_batch || batch > r->last_batch) return ORB_ERR_BAD_ARG;
+    if (l->device != r->device || l->nlevels != r->nlevels || l->plan_w != r->plan_w || l->plan_h != r->plan_h) {
+        orb_set_error("left and right extractor must share device, level count and image size");
+        return ORB_ERR_BAD_ARG;
+    }
+    ORB_CUDA(cudaSetDevice(l->device));
+    StereoGeom S;
+    S.nlevels = l->nlevels; S.h0 = l->plan.lv[0].h; S.kp_cap_l = l->plan.kp_cap; S.kp_cap_r = r->plan.kp_cap;
+    S.items_cap = l->row_items_cap;
+    for (int i = 0; i < l->nlevels; ++i) { S.sf[i] = l->sf[i]; S.inv_sf[i] = l->inv_sf[i]; S.lvl_l[i] = l->plan.lv[i]; S.lvl_r[i] = r->plan.lv[i]; }
+    // the right handle's stream must have finished producing its outputs
+    ORB_CUDA(cudaEventRecord(r->ev_done, r->stream));
+    ORB_CUDA(cudaStreamWaitEvent(l->stream, r->ev_done, 0));
+    const size_t smem = (size_t)(S.h0 + 1) * 2 * sizeof(int);
+    if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_stereo_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const bool T = l->timing;
+    if (T) cudaEventRecord(l->ev_stage[6], l->stream);
+    k_stereo_rows<<<batch, 512, smem, l->stream>>>(r->d_kps, r->d_counts, l->d_row_start, l->d_row_items, l->d_status, S);
+    if (T) cudaEventRecord(l->ev_stage[7], l->stream);
+    dim3 grid((l->plan.kp_cap + SM_WARPS - 1) / SM_WARPS, batch);
+    k_stereo_match<<<grid, SM_WARPS * 32, 0, l->stream>>>(l->d_kps, l->d_desc, l->d_counts, r->d_kps, r->d_desc, l->d_pyr, r->d_pyr,
+                                                         l->d_row_start, l->d_row_items, l->d_u_right, l->d_depth, l->d_sad, S, mbf, min_d, max_d);
+    if (T) cudaEventRecord(l->ev_stage[8], l->stream);
+    k_stereo_median<<<batch, 512, 0, l->stream>>>(l->d_counts, l->d_u_right, l->d_depth, l->d_sad, l->plan.kp_cap);
+    if (T) { cudaEventRecord(l->ev_stage[9], l->stream); l->stage_valid[5] = l->stage_valid[6] = l->stage_valid[7] = true; }
+    l->launches += 3;
+    ORB_CUDA(cudaGetLastError());
+    // later work on the right stream must not overwrite its buffers before we are done
+    ORB_CUDA(cudaEventRecord(l->ev_done, l->stream));
+    ORB_CUDA(cudaStreamWaitEvent(r->stream, l->ev_done, 0));
+    return ORB_OK;
+}
+
+extern "C" {
+
+int orb_stereo_match_device(orb_extractor* l, orb_extractor* r, int batch, float mbf, float min_d, float max_d) {
+    return stereo_launch(l, r, batch, mbf, min_d, max_d);
+}
+
+int orb_stereo_device_results(const orb_extractor* l, const float** d_u_right, const float** d_depth) {
+    if (!l) return ORB_ERR_BAD_ARG;
+    if (d_u_right) *d_u_right = l->d_u_right;
+    if (d_depth) *d_depth = l->d_depth;
+    return ORB_OK;
+}
+
+int orb_stereo_match_batch(orb_extractor* l, orb_extractor* r, int batch, float mbf, float min_d, float max_d, float* u_right, float* depth,
+                           int cap, int32_t* n_left) {
+    if (!u_right || !depth || !n_left) return ORB_ERR_BAD_ARG;
+    int st = stereo_launch(l, r, batch, mbf, min_d, max_d);
+    if (st != ORB_OK) return st;
+    ORB_CUDA(cudaMemcpyAsync(l->h_counts, l->d_counts, (size_t)batch * sizeof(int), cudaMemcpyDeviceToHost, l->stream));
+    int dst = 0;
+    ORB_CUDA(cudaMemcpyAsync(&dst, l->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->stream));
+    ORB_CUDA(cudaStreamSynchronize(l->stream));
+    if (dst != 0) { cudaMemsetAsync(l->d_status, 0, sizeof(int), l->stream); orb_set_error("device-side bound exceeded"); return dst; }
+    int rc = ORB_OK;
+    for (int b = 0; b < batch; ++b) {
+        const int n = l->h_counts[b];
+        n_left[b] = n;
+        if (n > cap) { rc = ORB_ERR_CAPACITY; continue; }
+        if (n == 0) continue;
+        ORB_CUDA(cudaMemcpyAsync(u_right + (size_t)b * cap, l->d_u_right + (size_t)b * l->plan.kp_cap, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, l->stream));
+        ORB_CUDA(cudaMemcpyAsync(depth + (size_t)b * cap, l->d_depth + (size_t)b * l->plan.kp_cap, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, l->stream));
+    }
+    ORB_CUDA(cudaStreamSynchronize(l->stream));
+    if (rc != ORB_OK) orb_set_error("stereo output capacity too small");
+    return rc;
+}
+
+int orb_stereo_match(orb_extractor* l, orb_extractor* r, int image, float mbf, float min_d, float max_d, float* u_right, float* depth, int cap,
+                     int32_t* n_left) {
+    // single image of the last batch: run the batch prefix up to `image` is wasteful, so the
+    // kernels are launched for the whole last batch only when image == 0 and batch == 1;
+    // otherwise compute all and copy the requested one.
+    if (!l || !u_right || !depth || !n_left || image < 0 || image >= l->last_batch) return ORB_ERR_BAD_ARG;
+    int st = stereo_launch(l, r, l->last_batch, mbf, min_d, max_d);
+    if (st != ORB_OK) return st;
+    int n = 0, dst = 0;
+    ORB_CUDA(cudaMemcpyAsync(&n, l->d_counts + image, sizeof(int), cudaMemcpyDeviceToHost, l->stream));
+    ORB_CUDA(cudaMemcpyAsync(&dst, l->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->stream));
+    ORB_CUDA(cudaStreamSynchronize(l->stream));
+    if (dst != 0) { cudaMemsetAsync(l->d_status, 0, sizeof(int), l->stream); orb_set_error("device-side bound exceeded"); return dst; }
+    *n_left = n;
+    if (n > cap) { orb_set_error("stereo output capacity too small"); return ORB_ERR_CAPACITY; }
+    if (n > 0) {
+        ORB_CUDA(cudaMemcpyAsync(u_right, l->d_u_right + (size_t)image * l->plan.kp_cap, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, l->stream));
+        ORB_CUDA(cudaMemcpyAsync(depth, l->d_depth + (size_t)image * l->plan.kp_cap, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, l->stream));
+        ORB_CUDA(cudaStreamSynchronize(l->stream));
+    }
+    return ORB_OK;
+}
+
+}  // extern "C"

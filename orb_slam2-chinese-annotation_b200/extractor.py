@@ -105,6 +105,16 @@ class ORBextractor:
     def launch_count(self):
         return lib().orb_extractor_launch_count(self._h)
 
+    STAGES = ("pyramid", "fast_cells", "quadtree", "blur", "orient_describe", "stereo_rows", "stereo_match", "stereo_median")
+
+    def set_timing(self, on=True):
+        check(lib().orb_extractor_set_timing(self._h, int(on)))
+
+    def stage_ms(self):
+        ms = np.zeros(8, np.float32)
+        check(lib().orb_extractor_stage_ms(self._h, ptr(ms)))
+        return dict(zip(self.STAGES, (float(v) for v in ms)))
+
     # ---- mvImagePyramid and stage outputs
     def image_pyramid(self, level, image=0, blurred=False, border=0):
         B, W, H = self._last

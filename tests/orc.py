@@ -165,3 +165,24 @@ class Extractor:
         out = np.empty(cap, KP_DTYPE)
         n = lib.orc_level_keypoints(self.h, l, _p(out), cap)
         return out[:n].copy()
+
+
+def stereo_match(oL, oR, kpL, dL, kpR, dR, mbf, min_d, max_d):
+    """Frame::ComputeStereoMatches on two oracle extractors (their last extract() call)."""
+    t = oL.tables()
+    nL, nR = len(kpL), len(kpR)
+    kpL = np.ascontiguousarray(kpL); kpR = np.ascontiguousarray(kpR)
+    dL = np.ascontiguousarray(dL); dR = np.ascontiguousarray(dR)
+    ur = np.empty(max(nL, 1), np.float32); dp = np.empty(max(nL, 1), np.float32); sad = np.empty(max(nL, 1), np.int32)
+    lib.orc_stereo_match.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                                       C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    kept = lib.orc_stereo_match(oL.h, oR.h, _p(kpL), _p(dL), nL, _p(kpR), _p(dR), nR, _p(t["sf"]), _p(t["inv_sf"]),
+                                mbf, min_d, max_d, _p(ur), _p(dp), _p(sad))
+    return ur[:nL], dp[:nL], sad[:nL], kept
+
+
+def match_bruteforce(a, b):
+    a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+    bi = np.empty(len(a), np.int32); bd = np.empty(len(a), np.int32); sd = np.empty(len(a), np.int32)
+    lib.orc_match_bruteforce(_p(a), _p(b), len(a), len(b), _p(bi), _p(bd), _p(sd))
+    return bi, bd, sd

@@ -1,16 +1,887 @@
+// ORBmatcher hot paths (reference src/ORBmatcher.cc) and the Frame grid (src/Frame.cc:261-276,
+// 368-436) on the GPU.  XOR + POPC over 256-bit descriptors; no tensor cores by design.
+//
+// Structure shared by the claim-based searches (SearchByProjection x2, SearchByBoW): the Hamming
+// distances of every (query, candidate) pair are computed in parallel into per-query candidate
+// lists that keep the reference's candidate ORDER; a single warp then replays the reference's
+// sequential loop over the queries (skip already-claimed keypoints, strict-< best / second best,
+// thresholds, ratio test, claim), so match indices are identical to the CPU code including ties.
 #include "orb_internal.h"
-extern "C" {
-int orb_matcher_create(int, int, int, orb_matcher**) { orb_set_error("wip"); return ORB_ERR_INTERNAL; }
-void orb_matcher_destroy(orb_matcher*) {}
-void* orb_matcher_stream(const orb_matcher*) { return nullptr; }
-long long orb_matcher_launch_count(const orb_matcher*) { return 0; }
-int orb_matcher_sync(orb_matcher*) { return ORB_ERR_INTERNAL; }
-int orb_descriptor_distance(orb_matcher*, const uint8_t*, const uint8_t*, int, int32_t*) { return ORB_ERR_INTERNAL; }
-int orb_match_bruteforce(orb_matcher*, const uint8_t*, const uint8_t*, int, int, int, int32_t*, int32_t*, int32_t*) { return ORB_ERR_INTERNAL; }
-int orb_match_bruteforce_device(orb_matcher*, const uint8_t*, const uint8_t*, int, int, int, int32_t*, int32_t*, int32_t*) { return ORB_ERR_INTERNAL; }
-int orb_assign_features_to_grid(orb_matcher*, const float*, const float*, int, const orb_grid_params*, int32_t*, int32_t*, int32_t*) { return ORB_ERR_INTERNAL; }
-int orb_search_by_projection_mappoints(orb_matcher*, const orb_frame_view*, const orb_mappoint_view*, float, float, const uint8_t*, int32_t*, int32_t*) { return ORB_ERR_INTERNAL; }
-int orb_search_by_projection_lastframe(orb_matcher*, const orb_frame_view*, const orb_lastframe_view*, const orb_camera*, float, int, int, int, const uint8_t*, int32_t*, int32_t*) { return ORB_ERR_INTERNAL; }
-int orb_search_by_bow(orb_matcher*, const orb_frame_view*, const orb_featvec_view*, const uint8_t*, const orb_frame_view*, const orb_featvec_view*, float, int, int32_t*, int32_t*) { return ORB_ERR_INTERNAL; }
-int orb_search_for_triangulation(orb_matcher*, const orb_frame_view*, const orb_featvec_view*, const uint8_t*, const orb_frame_view*, const orb_featvec_view*, const uint8_t*, const float*, float, float, const float*, int, int, int32_t*, int32_t*) { return ORB_ERR_INTERNAL; }
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#define GRID_COLS 64
+#define GRID_ROWS 48
+#define GRID_CELLS (GRID_COLS * GRID_ROWS)
+#define M_TH_HIGH 100
+#define M_TH_LOW 50
+#define M_HISTO 30
+
+struct orb_matcher {
+    int device = 0, max_pairs = 0, max_n = 0;
+    cudaStream_t stream = nullptr;
+    long long launches = 0;
+    uint8_t* d_ws = nullptr;   // bump-allocated workspace, reset per call
+    size_t ws_cap = 0, ws_off = 0;
+    uint32_t* d_cands = nullptr;
+    size_t cands_cap = 0;
+    int* d_scal = nullptr;     // small device scalars
+};
+
+namespace {
+
+struct DFrame {
+    int n;
+    const float *x, *y, *angle, *u_right;
+    const int* octave;
+    const uint8_t* desc;
+    orb_grid_params grid;
+    float sf[ORB_MAX_LEVELS];
+    const int* cell_start;
+    const int* cell_items;
+};
+
+struct Query {
+    float x, y, r, xr;
+    int min_level, max_level;
+    int valid;
+    int pad;
+};
+
+template <typename T>
+int ws_alloc(orb_matcher* m, T** p, size_t count) {
+    const size_t bytes = (count * sizeof(T) + 255) & ~(size_t)255;
+    if (m->ws_off + bytes > m->ws_cap) { orb_set_error("matcher workspace too small (raise max_n / max_pairs)"); return ORB_ERR_CAPACITY; }
+    *p = reinterpret_cast<T*>(m->d_ws + m->ws_off);
+    m->ws_off += bytes;
+    return ORB_OK;
 }
+
+template <typename T>
+int ws_upload(orb_matcher* m, const T** dp, const T* host, size_t count) {
+    T* p = nullptr;
+    int st = ws_alloc(m, &p, std::max<size_t>(count, 1));
+    if (st != ORB_OK) return st;
+    if (count) ORB_CUDA(cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, m->stream));
+    *dp = p;
+    return ORB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void k_distance_pairs(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, int n, int* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4* pa = reinterpret_cast<const uint4*>(a + (size_t)i * 32);
+    const uint4* pb = reinterpret_cast<const uint4*>(b + (size_t)i * 32);
+    out[i] = orb_hamming256(pa[0], pa[1], pb[0], pb[1]);
+}
+
+// Brute force: thread = one row of A (descriptor in registers), B streamed through shared memory
+// in tiles that every thread reads at the same address (broadcast).  Scan order over B is
+// ascending, so "strict <, first wins" is the natural loop.
+#define BF_THREADS 128
+#define BF_TILE 256
+__global__ void __launch_bounds__(BF_THREADS)
+k_bruteforce(const uint8_t* __restrict__ A, const uint8_t* __restrict__ Bm, int n_a, int n_b, int* __restrict__ best_idx,
+             int* __restrict__ best_dist, int* __restrict__ second_dist) {
+    __shared__ uint4 tile[BF_TILE * 2];
+    const int pair = blockIdx.y;
+    const uint8_t* a = A + (size_t)pair * n_a * 32;
+    const uint8_t* b = Bm + (size_t)pair * n_b * 32;
+    const int i = blockIdx.x * BF_THREADS + threadIdx.x;
+    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+    if (i < n_a) { const uint4* pa = reinterpret_cast<const uint4*>(a + (size_t)i * 32); a0 = pa[0]; a1 = pa[1]; }
+    int b1 = 256, b2 = 256, bi = -1;
+    for (int j0 = 0; j0 < n_b; j0 += BF_TILE) {
+        const int m = min(BF_TILE, n_b - j0);
+        __syncthreads();
+        for (int t = threadIdx.x; t < 2 * m; t += BF_THREADS) tile[t] = reinterpret_cast<const uint4*>(b + (size_t)j0 * 32)[t];
+        __syncthreads();
+#pragma unroll 4
+        for (int j = 0; j < m; ++j) {
+            const int d = orb_hamming256(a0, a1, tile[2 * j], tile[2 * j + 1]);
+            if (d < b1) { b2 = b1; b1 = d; bi = j0 + j; }
+            else if (d < b2) b2 = d;
+        }
+    }
+    if (i < n_a) {
+        const size_t o = (size_t)pair * n_a + i;
+        best_idx[o] = bi; best_dist[o] = b1; second_dist[o] = b2;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Frame::AssignFeaturesToGrid: cell = round((x - minX) * invW), round((y - minY) * invH); lists in
+// ascending keypoint index (insertion order).  One CTA: bitonic sort of (cell << 16 | index).
+__global__ void __launch_bounds__(1024)
+k_grid_build(const float* __restrict__ x, const float* __restrict__ y, int n, int p2, orb_grid_params g, int* __restrict__ cell_start,
+             int* __restrict__ cell_items, int* __restrict__ n_items) {
+    extern __shared__ uint32_t keys[];
+    __shared__ int cnt[GRID_CELLS + 1];
+    const int tid = threadIdx.x;
+    for (int i = tid; i <= GRID_CELLS; i += 1024) cnt[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < p2; i += 1024) {
+        uint32_t k = 0xffffffffu;
+        if (i < n) {
+            const int px = (int)roundf(__fmul_rn(__fsub_rn(x[i], g.min_x), g.inv_w));
+            const int py = (int)roundf(__fmul_rn(__fsub_rn(y[i], g.min_y), g.inv_h));
+            if (px >= 0 && px < GRID_COLS && py >= 0 && py < GRID_ROWS) {
+                const int c = px * GRID_ROWS + py;
+                k = ((uint32_t)c << 16) | (uint32_t)i;
+                atomicAdd(&cnt[c], 1);
+            }
+        }
+        keys[i] = k;
+    }
+    __syncthreads();
+    for (int k = 2; k <= p2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < p2; i += 1024) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const uint32_t a = keys[i], b = keys[ixj];
+                    const bool up = (i & k) == 0;
+                    if (up ? (a > b) : (a < b)) { keys[i] = b; keys[ixj] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    if (tid == 0) {  // 3072-entry exclusive scan
+        int run = 0;
+        for (int c = 0; c < GRID_CELLS; ++c) { const int v = cnt[c]; cnt[c] = run; run += v; }
+        cnt[GRID_CELLS] = run;
+        *n_items = run;
+    }
+    __syncthreads();
+    for (int i = tid; i <= GRID_CELLS; i += 1024) cell_start[i] = cnt[i];
+    const int total = cnt[GRID_CELLS];
+    for (int i = tid; i < total; i += 1024) cell_items[i] = (int)(keys[i] & 0xffffu);
+}
+
+// ------------------------------------------------------------------------------------------
+// Query records.
+__global__ void k_prep_mappoints(int n, const uint8_t* __restrict__ valid, const float* __restrict__ px, const float* __restrict__ py,
+                                 const float* __restrict__ pxr, const int* __restrict__ level, const float* __restrict__ view_cos,
+                                 float th, DFrame F, Query* __restrict__ q) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Query Q;
+    Q.valid = valid[i];
+    const int lv = level[i];
+    float r = ((double)view_cos[i] > 0.998) ? 2.5f : 4.0f;     // RadiusByViewingCos (reference :135-141)
+    if (th != 1.0f) r = __fmul_rn(r, th);
+    Q.x = px[i]; Q.y = py[i]; Q.xr = pxr ? pxr[i] : 0.f;
+    Q.r = __fmul_rn(r, F.sf[min(max(lv, 0), ORB_MAX_LEVELS - 1)]);
+    Q.min_level = lv - 1; Q.max_level = lv; Q.pad = 0;
+    q[i] = Q;
+}
+
+__global__ void k_prep_lastframe(int n, const uint8_t* __restrict__ valid, const float* __restrict__ xc, const float* __restrict__ yc,
+                                 const float* __restrict__ zc, const int* __restrict__ octave, orb_camera cam, float th, int forward,
+                                 int backward, DFrame F, Query* __restrict__ q) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Query Q;
+    Q.valid = valid[i]; Q.pad = 0; Q.x = Q.y = Q.r = Q.xr = 0.f; Q.min_level = Q.max_level = 0;
+    if (Q.valid) {
+        const float invzc = (float)(1.0 / (double)zc[i]);      // reference :1507 (double division)
+        if (invzc < 0) Q.valid = 0;
+        else {
+            // x*a + y, fused as GCC does for the reference's flags on FMA hardware
+            const float u = __fmaf_rn(__fmul_rn(cam.fx, xc[i]), invzc, cam.cx);
+            const float v = __fmaf_rn(__fmul_rn(cam.fy, yc[i]), invzc, cam.cy);
+            if (u < F.grid.min_x || u > F.grid.max_x || v < F.grid.min_y || v > F.grid.max_y) Q.valid = 0;
+            else {
+                const int lo = octave[i];
+                Q.x = u; Q.y = v;
+                Q.r = __fmul_rn(th, F.sf[min(max(lo, 0), ORB_MAX_LEVELS - 1)]);
+                Q.xr = __fmaf_rn(-cam.mbf, invzc, u);
+                if (forward) { Q.min_level = lo; Q.max_level = -1; }
+                else if (backward) { Q.min_level = 0; Q.max_level = lo; }
+                else { Q.min_level = lo - 1; Q.max_level = lo + 1; }
+            }
+        }
+    }
+    q[i] = Q;
+}
+
+// Frame::GetFeaturesInArea + the static candidate filters, one warp per query, in the
+// reference's order (ix, then iy, then insertion order).  FILL=false counts, FILL=true writes
+// packed candidates: index (16 bits) | distance << 16 (9 bits) | octave << 25.
+template <bool FILL>
+__global__ void __launch_bounds__(256)
+k_area_candidates(int nq, const Query* __restrict__ q, const uint8_t* __restrict__ qdesc, DFrame F, int* __restrict__ counts,
+                  const int* __restrict__ starts, uint32_t* __restrict__ cands) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= nq) return;
+    const Query Q = q[w];
+    int total = 0;
+    if (Q.valid) {
+        const float x = Q.x, y = Q.y, r = Q.r;
+        const int nMinCellX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, F.grid.min_x), r), F.grid.inv_w)));
+        const int nMaxCellX = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, F.grid.min_x), r), F.grid.inv_w)));
+        const int nMinCellY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, F.grid.min_y), r), F.grid.inv_h)));
+        const int nMaxCellY = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, F.grid.min_y), r), F.grid.inv_h)));
+        if (!(nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0)) {
+            const bool check_levels = (Q.min_level > 0) || (Q.max_level >= 0);
+            uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+            uint32_t* out = nullptr;
+            if (FILL) {
+                const uint4* pa = reinterpret_cast<const uint4*>(qdesc + (size_t)w * 32);
+                a0 = pa[0]; a1 = pa[1];
+                out = cands + starts[w];
+            }
+            for (int ix = nMinCellX; ix <= nMaxCellX; ++ix) {
+                // cells (ix, nMinCellY..nMaxCellY) are consecutive in the CSR
+                const int c0 = F.cell_start[ix * GRID_ROWS + nMinCellY], c1 = F.cell_start[ix * GRID_ROWS + nMaxCellY + 1];
+                for (int p0 = c0; p0 < c1; p0 += 32) {
+                    const int p = p0 + lane;
+                    bool ok = false;
+                    int idx = 0, oct = 0;
+                    if (p < c1) {
+                        idx = F.cell_items[p];
+                        oct = F.octave[idx];
+                        ok = true;
+                        if (check_levels) {
+                            if (oct < Q.min_level) ok = false;
+                            if (Q.max_level >= 0 && oct > Q.max_level) ok = false;
+                        }
+                        if (ok) {
+                            const float dx = __fsub_rn(F.x[idx], x), dy = __fsub_rn(F.y[idx], y);
+                            ok = fabsf(dx) < r && fabsf(dy) < r;
+                        }
+                        if (ok && F.u_right) {
+                            const float ur = F.u_right[idx];
+                            if (ur > 0 && fabsf(__fsub_rn(Q.xr, ur)) > r) ok = false;
+                        }
+                    }
+                    const unsigned m = __ballot_sync(0xffffffffu, ok);
+                    if (FILL && ok) {
+                        const uint4* pb = reinterpret_cast<const uint4*>(F.desc + (size_t)idx * 32);
+                        const unsigned d = (unsigned)orb_hamming256(a0, a1, pb[0], pb[1]);
+                        out[total + __popc(m & ((1u << lane) - 1))] = (uint32_t)idx | (d << 16) | ((uint32_t)oct << 25);
+                    }
+                    total += __popc(m);
+                }
+            }
+        }
+    }
+    if (!FILL && lane == 0) counts[w] = total;
+}
+
+// single-CTA exclusive scan: starts[0..n] from counts[0..n)
+__global__ void __launch_bounds__(1024) k_scan(const int* __restrict__ counts, int n, int* __restrict__ starts) {
+    __shared__ int ws[33];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int carry = 0;
+    for (int i0 = 0; i0 < n; i0 += 1024) {
+        const int i = i0 + tid;
+        const int v = i < n ? counts[i] : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+        if (lane == 31) ws[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int wv = ws[lane], wi = wv;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+            ws[lane] = wi - wv;
+            if (lane == 31) ws[32] = wi;
+        }
+        __syncthreads();
+        if (i < n) starts[i] = carry + inc - v + ws[warp];
+        carry += ws[32];
+        __syncthreads();
+    }
+    if (tid == 0) starts[n] = carry;
+}
+
+// ------------------------------------------------------------------------------------------
+// Sequential replay helpers (one warp).  A candidate key is (dist << 16 | position): the
+// minimum is the reference's "strict <, first wins" best; the minimum of the rest its second best.
+struct Best2 { unsigned b, s; };
+__device__ __forceinline__ Best2 merge2(Best2 a, Best2 o) {
+    Best2 r;
+    r.b = min(a.b, o.b);
+    r.s = min(min(a.s, o.s), max(a.b, o.b));
+    return r;
+}
+__device__ __forceinline__ Best2 warp_best2(Best2 v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        Best2 t;
+        t.b = __shfl_xor_sync(0xffffffffu, v.b, o);
+        t.s = __shfl_xor_sync(0xffffffffu, v.s, o);
+        v = merge2(v, t);
+    }
+    return v;
+}
+
+__device__ __forceinline__ int rot_bin(float a1, float a2) {
+    float rot = __fsub_rn(a1, a2);
+    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+    int bin = (int)roundf(__fmul_rn(rot, 1.0f / M_HISTO));
+    if (bin == M_HISTO) bin = 0;
+    return bin;
+}
+
+// ComputeThreeMaxima (reference :1765-1809) over bin counts
+__device__ void three_maxima(const int* cnt, int& ind1, int& ind2, int& ind3) {
+    int max1 = 0, max2 = 0, max3 = 0;
+    ind1 = ind2 = ind3 = -1;
+    for (int i = 0; i < M_HISTO; ++i) {
+        const int s = cnt[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+    else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
+}
+
+// rotation-histogram cull shared by the searches: entries (target index, bin); clears match[target]
+__device__ void rot_cull_warp(const int* __restrict__ hist_idx, const int* __restrict__ hist_bin, int n_hist, int* __restrict__ match,
+                              int* nmatches_io, int* s_cnt /* 32 ints shared */) {
+    const int lane = threadIdx.x & 31;
+    if (lane < M_HISTO + 2) s_cnt[lane] = 0;
+    __syncwarp();
+    for (int i = lane; i < n_hist; i += 32) atomicAdd(&s_cnt[hist_bin[i]], 1);
+    __syncwarp();
+    int i1, i2, i3;
+    three_maxima(s_cnt, i1, i2, i3);
+    int removed = 0;
+    for (int i = lane; i < n_hist; i += 32) {
+        const int b = hist_bin[i];
+        if (b != i1 && b != i2 && b != i3) { match[hist_idx[i]] = -1; ++removed; }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) removed += __shfl_xor_sync(0xffffffffu, removed, o);
+    if (lane == 0) *nmatches_io -= removed;
+}
+
+// MODE 0: SearchByProjection(Frame, MapPoints)  -- best + second best with levels, ratio test
+// MODE 1: SearchByProjection(Cur, Last)         -- best only, rotation histogram
+__global__ void __launch_bounds__(32)
+k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* __restrict__ starts, const uint32_t* __restrict__ cands,
+                     const uint8_t* __restrict__ blocks, const float* __restrict__ q_angle, DFrame F, const uint8_t* __restrict__ occupied,
+                     uint8_t* __restrict__ occ, float nn_ratio, int check_ori, int* __restrict__ match, int* __restrict__ hist_idx,
+                     int* __restrict__ hist_bin, int* __restrict__ nmatches_out) {
+    __shared__ int s_cnt[32];
+    const int lane = threadIdx.x;
+    for (int i = lane; i < F.n; i += 32) { match[i] = -1; occ[i] = occupied ? occupied[i] : 0; }
+    __syncwarp();
+    int nmatches = 0, n_hist = 0;
+    for (int w = 0; w < nq; ++w) {
+        const int c0 = starts[w], c1 = starts[w + 1];
+        if (c0 == c1) continue;
+        Best2 v; v.b = 0xffffffffu; v.s = 0xffffffffu;
+        for (int p = c0 + lane; p < c1; p += 32) {
+            const uint32_t c = cands[p];
+            if (occ[c & 0xffffu]) continue;
+            Best2 t; t.b = (((c >> 16) & 0x1ffu) << 16) | (unsigned)(p - c0); t.s = 0xffffffffu;
+            v = merge2(v, t);
+        }
+        v = warp_best2(v);
+        if (v.b == 0xffffffffu) continue;
+        const int bestDist = (int)(v.b >> 16);
+        const uint32_t cb = cands[c0 + (v.b & 0xffffu)];
+        const int bestIdx = (int)(cb & 0xffffu);
+        if (mode == 0) {
+            if (bestDist <= M_TH_HIGH) {
+                bool reject = false;
+                if (v.s != 0xffffffffu) {
+                    const uint32_t cs = cands[c0 + (v.s & 0xffffu)];
+                    const int bestDist2 = (int)(v.s >> 16);
+                    if ((cb >> 25) == (cs >> 25) && (float)bestDist > __fmul_rn(nn_ratio, (float)bestDist2)) reject = true;
+                }
+                // no second candidate: bestLevel2 = -1 never equals a real octave
+                if (!reject) {
+                    if (lane == 0) { match[bestIdx] = w; occ[bestIdx] = blocks[w]; }
+                    ++nmatches;
+                }
+            }
+        } else {
+            if (bestDist <= M_TH_HIGH) {
+                if (lane == 0) {
+                    match[bestIdx] = w; occ[bestIdx] = blocks[w];
+                    if (check_ori) { hist_idx[n_hist] = bestIdx; hist_bin[n_hist] = rot_bin(q_angle[w], F.angle[bestIdx]); }
+                }
+                ++nmatches; ++n_hist;
+            }
+        }
+        __syncwarp();
+    }
+    if (lane == 0) *nmatches_out = nmatches;
+    __syncwarp();
+    if (mode == 1 && check_ori) rot_cull_warp(hist_idx, hist_bin, n_hist, match, nmatches_out, s_cnt);
+}
+
+// ------------------------------------------------------------------------------------------
+// BoW-guided searches.  Work entries (built on the host by the FeatureVector merge-join, in the
+// reference's processing order): query feature, candidate range [f0, f1) inside items2.
+struct BowEntry { int q_idx, f0, f1, c_start; };
+
+__global__ void __launch_bounds__(256)
+k_bow_distances(int n_entries, const BowEntry* __restrict__ e, const uint8_t* __restrict__ qdesc, const uint8_t* __restrict__ fdesc,
+                const uint32_t* __restrict__ items2, uint32_t* __restrict__ cands) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= n_entries) return;
+    const BowEntry E = e[w];
+    const uint4* pa = reinterpret_cast<const uint4*>(qdesc + (size_t)E.q_idx * 32);
+    const uint4 a0 = pa[0], a1 = pa[1];
+    for (int p = E.f0 + lane; p < E.f1; p += 32) {
+        const uint32_t idx = items2[p];
+        const uint4* pb = reinterpret_cast<const uint4*>(fdesc + (size_t)idx * 32);
+        cands[E.c_start + (p - E.f0)] = idx | ((uint32_t)orb_hamming256(a0, a1, pb[0], pb[1]) << 16);
+    }
+}
+
+__global__ void __launch_bounds__(32)
+k_resolve_bow(int n_entries, const BowEntry* __restrict__ e, const uint32_t* __restrict__ cands, const float* __restrict__ kf_angle,
+              const float* __restrict__ f_angle, int n_f, float nn_ratio, int check_ori, int* __restrict__ match_f,
+              int* __restrict__ hist_idx, int* __restrict__ hist_bin, int* __restrict__ nmatches_out) {
+    __shared__ int s_cnt[32];
+    const int lane = threadIdx.x;
+    for (int i = lane; i < n_f; i += 32) match_f[i] = -1;
+    __syncwarp();
+    int nmatches = 0, n_hist = 0;
+    for (int w = 0; w < n_entries; ++w) {
+        const BowEntry E = e[w];
+        const int cnt = E.f1 - E.f0;
+        Best2 v; v.b = 0xffffffffu; v.s = 0xffffffffu;
+        for (int p = lane; p < cnt; p += 32) {
+            const uint32_t c = cands[E.c_start + p];
+            if (match_f[c & 0xffffu] >= 0) continue;
+            Best2 t; t.b = (((c >> 16) & 0x1ffu) << 16) | (unsigned)p; t.s = 0xffffffffu;
+            v = merge2(v, t);
+        }
+        v = warp_best2(v);
+        if (v.b == 0xffffffffu) continue;
+        const int d1 = (int)(v.b >> 16), d2 = v.s == 0xffffffffu ? 256 : (int)(v.s >> 16);
+        if (d1 <= M_TH_LOW && (float)d1 < __fmul_rn(nn_ratio, (float)d2)) {
+            const int idxF = (int)(cands[E.c_start + (v.b & 0xffffu)] & 0xffffu);
+            if (lane == 0) {
+                match_f[idxF] = E.q_idx;
+                if (check_ori) { hist_idx[n_hist] = idxF; hist_bin[n_hist] = rot_bin(kf_angle[E.q_idx], f_angle[idxF]); }
+            }
+            ++nmatches; ++n_hist;
+        }
+        __syncwarp();
+    }
+    if (lane == 0) *nmatches_out = nmatches;
+    __syncwarp();
+    if (check_ori) rot_cull_warp(hist_idx, hist_bin, n_hist, match_f, nmatches_out, s_cnt);
+}
+
+// SearchForTriangulation: no claiming in the reference (vbMatched2 is never set), so every query
+// is independent.  The sequential rule "skip if dist > TH_LOW or dist > best; accept if the
+// epipolar tests pass" ends on the LAST candidate holding the minimum distance among those that
+// pass the tests.
+struct TriParams {
+    float f12[9];
+    float ex, ey;
+    float sigma2[ORB_MAX_LEVELS];
+    int only_stereo;
+};
+__global__ void __launch_bounds__(256)
+k_triangulation(int n_entries, const BowEntry* __restrict__ e, DFrame K1, DFrame K2, const uint32_t* __restrict__ items2,
+                const uint8_t* __restrict__ has_mp2, TriParams T, int* __restrict__ match12) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= n_entries) return;
+    const BowEntry E = e[w];
+    const int idx1 = E.q_idx;
+    const bool stereo1 = K1.u_right && K1.u_right[idx1] >= 0;
+    const uint4* pa = reinterpret_cast<const uint4*>(K1.desc + (size_t)idx1 * 32);
+    const uint4 a0 = pa[0], a1 = pa[1];
+    const float x1 = K1.x[idx1], y1 = K1.y[idx1];
+    // epipolar line of kp1 in image 2 (reference :146-148), GCC-style contraction
+    const float la = __fadd_rn(__fmaf_rn(x1, T.f12[0], __fmul_rn(y1, T.f12[3])), T.f12[6]);
+    const float lb = __fadd_rn(__fmaf_rn(x1, T.f12[1], __fmul_rn(y1, T.f12[4])), T.f12[7]);
+    const float lc = __fadd_rn(__fmaf_rn(x1, T.f12[2], __fmul_rn(y1, T.f12[5])), T.f12[8]);
+    const float den = __fmaf_rn(la, la, __fmul_rn(lb, lb));
+    unsigned best = 0xffffffffu;  // (dist << 16) | (0xffff - position): min -> smallest dist, last position
+    for (int p = E.f0 + lane; p < E.f1; p += 32) {
+        const int idx2 = (int)items2[p];
+        if (has_mp2[idx2]) continue;
+        const bool stereo2 = K2.u_right && K2.u_right[idx2] >= 0;
+        if (T.only_stereo && !stereo2) continue;
+        const uint4* pb = reinterpret_cast<const uint4*>(K2.desc + (size_t)idx2 * 32);
+        const int dist = orb_hamming256(a0, a1, pb[0], pb[1]);
+        if (dist > M_TH_LOW) continue;
+        const float x2 = K2.x[idx2], y2 = K2.y[idx2];
+        const int oct2 = K2.octave[idx2];
+        if (!stereo1 && !stereo2) {
+            const float dex = __fsub_rn(T.ex, x2), dey = __fsub_rn(T.ey, y2);
+            if (__fmaf_rn(dex, dex, __fmul_rn(dey, dey)) < __fmul_rn(100.f, K2.sf[oct2])) continue;
+        }
+        const float num = __fadd_rn(__fmaf_rn(la, x2, __fmul_rn(lb, y2)), lc);
+        if (den == 0) continue;
+        const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+        if (!((double)dsqr < 3.84 * (double)T.sigma2[oct2])) continue;
+        best = min(best, ((unsigned)dist << 16) | (unsigned)(0xffff - (p - E.f0)));
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane == 0 && best != 0xffffffffu) match12[idx1] = (int)items2[E.f0 + (0xffff - (int)(best & 0xffffu))];
+}
+
+__global__ void __launch_bounds__(32)
+k_tri_rot_cull(int n1, const float* __restrict__ a1, const float* __restrict__ a2, int check_ori, int* __restrict__ match12,
+               int* __restrict__ hist_idx, int* __restrict__ hist_bin, int* __restrict__ nmatches_out) {
+    __shared__ int s_cnt[32];
+    const int lane = threadIdx.x;
+    int n = 0;
+    for (int i0 = 0; i0 < n1; i0 += 32) {  // ordered compaction of matched idx1 (order is irrelevant to the cull)
+        const int i = i0 + lane;
+        const int m = i < n1 ? match12[i] : -1;
+        const unsigned bal = __ballot_sync(0xffffffffu, m >= 0);
+        if (m >= 0 && check_ori) {
+            const int pos = n + __popc(bal & ((1u << lane) - 1));
+            hist_idx[pos] = i; hist_bin[pos] = rot_bin(a1[i], a2[m]);
+        }
+        n += __popc(bal);
+    }
+    if (lane == 0) *nmatches_out = n;
+    __syncwarp();
+    if (check_ori) rot_cull_warp(hist_idx, hist_bin, n, match12, nmatches_out, s_cnt);
+}
+
+// ------------------------------------------------------------------------------------------ host helpers
+int upload_frame(orb_matcher* m, const orb_frame_view* f, DFrame* D, bool need_grid) {
+    if (!f || f->n < 0 || f->n > m->max_n || f->n > 65535 || (f->n > 0 && (!f->x || !f->y || !f->octave || !f->desc))) {
+        orb_set_error("bad frame view (n must be <= min(max_n, 65535))");
+        return ORB_ERR_BAD_ARG;
+    }
+    std::memset(D, 0, sizeof(*D));
+    D->n = f->n; D->grid = f->grid;
+    for (int i = 0; i < ORB_MAX_LEVELS; ++i) D->sf[i] = (f->scale_factors && i < f->n_levels) ? f->scale_factors[i] : 1.f;
+    int st;
+    if ((st = ws_upload(m, &D->x, f->x, f->n)) != ORB_OK) return st;
+    if ((st = ws_upload(m, &D->y, f->y, f->n)) != ORB_OK) return st;
+    if ((st = ws_upload(m, &D->octave, f->octave, f->n)) != ORB_OK) return st;
+    if (f->angle) { if ((st = ws_upload(m, &D->angle, f->angle, f->n)) != ORB_OK) return st; }
+    if (f->u_right) { if ((st = ws_upload(m, &D->u_right, f->u_right, f->n)) != ORB_OK) return st; }
+    if ((st = ws_upload(m, &D->desc, f->desc, (size_t)f->n * 32)) != ORB_OK) return st;
+    if (need_grid) {
+        int *cs, *ci, *ni;
+        if ((st = ws_alloc(m, &cs, GRID_CELLS + 1)) != ORB_OK) return st;
+        if ((st = ws_alloc(m, &ci, std::max(f->n, 1))) != ORB_OK) return st;
+        if ((st = ws_alloc(m, &ni, 1)) != ORB_OK) return st;
+        int p2 = 1;
+        while (p2 < std::max(f->n, 1)) p2 <<= 1;
+        const size_t smem = (size_t)p2 * 4;
+        if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_grid_build<<<1, 1024, smem, m->stream>>>(D->x, D->y, f->n, p2, f->grid, cs, ci, ni);
+        m->launches++;
+        D->cell_start = cs; D->cell_items = ci;
+    }
+    return ORB_OK;
+}
+
+// FeatureVector merge-join (reference :187-282): matched node pairs in ascending node id
+void merge_join(const orb_featvec_view* a, const orb_featvec_view* b, std::vector<std::pair<int, int>>& out) {
+    int i = 0, j = 0;
+    while (i < a->n_nodes && j < b->n_nodes) {
+        if (a->node_ids[i] == b->node_ids[j]) { out.push_back(std::make_pair(i, j)); ++i; ++j; }
+        else if (a->node_ids[i] < b->node_ids[j]) i = (int)(std::lower_bound(a->node_ids, a->node_ids + a->n_nodes, b->node_ids[j]) - a->node_ids);
+        else j = (int)(std::lower_bound(b->node_ids, b->node_ids + b->n_nodes, a->node_ids[i]) - b->node_ids);
+    }
+}
+
+int begin_call(orb_matcher* m) {
+    if (!m) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(m->device));
+    m->ws_off = 0;
+    return ORB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orb_matcher_create(int max_pairs, int max_n, int device, orb_matcher** out) {
+    if (!out) return ORB_ERR_BAD_ARG;
+    *out = nullptr;
+    if (max_pairs < 1 || max_n < 1) { orb_set_error("bad matcher capacities"); return ORB_ERR_BAD_ARG; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        orb_set_error("no CUDA device: this library has no CPU fallback");
+        return ORB_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) { orb_set_error("bad device index"); return ORB_ERR_BAD_ARG; }
+    ORB_CUDA(cudaSetDevice(device));
+    orb_matcher* m = new orb_matcher();
+    m->device = device; m->max_pairs = max_pairs; m->max_n = max_n;
+    m->ws_cap = (size_t)max_pairs * max_n * (2 * 32 + 3 * 4) + (size_t)max_n * 512 + (8u << 20);
+    m->cands_cap = std::min<size_t>((size_t)max_n * max_n, (size_t)128 << 20);
+    m->cands_cap = std::max<size_t>(m->cands_cap, 1 << 16);
+    if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc((void**)&m->d_ws, m->ws_cap) != cudaSuccess ||
+        cudaMalloc((void**)&m->d_cands, m->cands_cap * 4) != cudaSuccess || cudaMalloc((void**)&m->d_scal, 64) != cudaSuccess) {
+        orb_set_error(std::string("matcher allocation: ") + cudaGetErrorString(cudaGetLastError()));
+        orb_matcher_destroy(m);
+        return ORB_ERR_CUDA;
+    }
+    *out = m;
+    return ORB_OK;
+}
+
+void orb_matcher_destroy(orb_matcher* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    cudaFree(m->d_ws); cudaFree(m->d_cands); cudaFree(m->d_scal);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    delete m;
+}
+
+void* orb_matcher_stream(const orb_matcher* m) { return m ? (void*)m->stream : nullptr; }
+long long orb_matcher_launch_count(const orb_matcher* m) { return m ? m->launches : 0; }
+int orb_matcher_sync(orb_matcher* m) {
+    if (!m) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(m->device));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+
+int orb_descriptor_distance(orb_matcher* m, const uint8_t* a, const uint8_t* b, int n, int32_t* dist) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!a || !b || !dist || n < 0) return ORB_ERR_BAD_ARG;
+    if (n == 0) return ORB_OK;
+    const uint8_t *da, *db; int* dd;
+    if ((st = ws_upload(m, &da, a, (size_t)n * 32)) != ORB_OK) return st;
+    if ((st = ws_upload(m, &db, b, (size_t)n * 32)) != ORB_OK) return st;
+    if ((st = ws_alloc(m, &dd, n)) != ORB_OK) return st;
+    k_distance_pairs<<<(n + 255) / 256, 256, 0, m->stream>>>(da, db, n, dd);
+    m->launches++;
+    ORB_CUDA(cudaMemcpyAsync(dist, dd, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+
+int orb_match_bruteforce_device(orb_matcher* m, const uint8_t* d_a, const uint8_t* d_b, int pairs, int n_a, int n_b, int32_t* d_best_idx,
+                                int32_t* d_best_dist, int32_t* d_second_dist) {
+    if (!m || !d_a || !d_b || !d_best_idx || !d_best_dist || !d_second_dist || pairs < 1 || n_a < 1 || n_b < 0) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(m->device));
+    dim3 grid((n_a + BF_THREADS - 1) / BF_THREADS, pairs);
+    k_bruteforce<<<grid, BF_THREADS, 0, m->stream>>>(d_a, d_b, n_a, n_b, d_best_idx, d_best_dist, d_second_dist);
+    m->launches++;
+    ORB_CUDA(cudaGetLastError());
+    return ORB_OK;
+}
+
+int orb_match_bruteforce(orb_matcher* m, const uint8_t* a, const uint8_t* b, int pairs, int n_a, int n_b, int32_t* best_idx,
+                         int32_t* best_dist, int32_t* second_dist) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!a || !b || !best_idx || !best_dist || !second_dist || pairs < 1 || n_a < 1 || n_b < 0) return ORB_ERR_BAD_ARG;
+    const uint8_t *da, *db; int *bi, *bd, *sd;
+    const size_t na = (size_t)pairs * n_a, nb = (size_t)pairs * n_b;
+    if ((st = ws_upload(m, &da, a, na * 32)) != ORB_OK) return st;
+    if ((st = ws_upload(m, &db, b, nb * 32)) != ORB_OK) return st;
+    if ((st = ws_alloc(m, &bi, na)) != ORB_OK || (st = ws_alloc(m, &bd, na)) != ORB_OK || (st = ws_alloc(m, &sd, na)) != ORB_OK) return st;
+    st = orb_match_bruteforce_device(m, da, db, pairs, n_a, n_b, bi, bd, sd);
+    if (st != ORB_OK) return st;
+    ORB_CUDA(cudaMemcpyAsync(best_idx, bi, na * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(best_dist, bd, na * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(second_dist, sd, na * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+
+int orb_assign_features_to_grid(orb_matcher* m, const float* kp_x, const float* kp_y, int n, const orb_grid_params* g, int32_t* cell_start,
+                                int32_t* cell_items, int32_t* n_items) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!g || !cell_start || !cell_items || !n_items || n < 0 || n > 65535 || n > m->max_n || (n > 0 && (!kp_x || !kp_y))) return ORB_ERR_BAD_ARG;
+    const float *dx, *dy; int *cs, *ci, *ni;
+    if ((st = ws_upload(m, &dx, kp_x, n)) != ORB_OK || (st = ws_upload(m, &dy, kp_y, n)) != ORB_OK) return st;
+    if ((st = ws_alloc(m, &cs, GRID_CELLS + 1)) != ORB_OK || (st = ws_alloc(m, &ci, std::max(n, 1))) != ORB_OK || (st = ws_alloc(m, &ni, 1)) != ORB_OK) return st;
+    int p2 = 1;
+    while (p2 < std::max(n, 1)) p2 <<= 1;
+    const size_t smem = (size_t)p2 * 4;
+    if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_grid_build<<<1, 1024, smem, m->stream>>>(dx, dy, n, p2, *g, cs, ci, ni);
+    m->launches++;
+    ORB_CUDA(cudaMemcpyAsync(cell_start, cs, (GRID_CELLS + 1) * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(n_items, ni, 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    if (*n_items > 0) {
+        ORB_CUDA(cudaMemcpyAsync(cell_items, ci, (size_t)*n_items * 4, cudaMemcpyDeviceToHost, m->stream));
+        ORB_CUDA(cudaStreamSynchronize(m->stream));
+    }
+    return ORB_OK;
+}
+
+// shared tail of the two projection searches: count -> scan -> fill -> sequential resolve
+static int projection_common(orb_matcher* m, int mode, int nq, const Query* dq, const uint8_t* d_qdesc, const uint8_t* d_blocks,
+                             const float* d_qangle, const DFrame& F, const uint8_t* occupied, float nn_ratio, int check_ori,
+                             int32_t* match, int32_t* nmatches) {
+    int st;
+    int *counts, *starts, *dmatch, *hidx, *hbin;
+    uint8_t* occ; const uint8_t* d_occupied = nullptr;
+    if ((st = ws_alloc(m, &counts, std::max(nq, 1))) != ORB_OK || (st = ws_alloc(m, &starts, nq + 1)) != ORB_OK) return st;
+    if ((st = ws_alloc(m, &dmatch, std::max(F.n, 1))) != ORB_OK || (st = ws_alloc(m, &occ, std::max(F.n, 1))) != ORB_OK) return st;
+    if ((st = ws_alloc(m, &hidx, std::max(nq, 1))) != ORB_OK || (st = ws_alloc(m, &hbin, std::max(nq, 1))) != ORB_OK) return st;
+    if (occupied) { if ((st = ws_upload(m, &d_occupied, occupied, F.n)) != ORB_OK) return st; }
+    if (nq > 0) {
+        const int blocks = (nq * 32 + 255) / 256;
+        k_area_candidates<false><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, counts, nullptr, nullptr);
+        k_scan<<<1, 1024, 0, m->stream>>>(counts, nq, starts);
+        int total = 0;
+        ORB_CUDA(cudaMemcpyAsync(&total, starts + nq, 4, cudaMemcpyDeviceToHost, m->stream));
+        ORB_CUDA(cudaStreamSynchronize(m->stream));
+        if ((size_t)total > m->cands_cap) { orb_set_error("candidate workspace too small"); return ORB_ERR_CAPACITY; }
+        k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, nullptr, starts, m->d_cands);
+        m->launches += 3;
+    } else {
+        ORB_CUDA(cudaMemsetAsync(starts, 0, 4, m->stream));
+    }
+    k_resolve_projection<<<1, 32, 0, m->stream>>>(mode, nq, dq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied, occ, nn_ratio, check_ori,
+                                                  dmatch, hidx, hbin, m->d_scal);
+    m->launches++;
+    ORB_CUDA(cudaGetLastError());
+    if (F.n > 0) ORB_CUDA(cudaMemcpyAsync(match, dmatch, (size_t)F.n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+
+int orb_search_by_projection_mappoints(orb_matcher* m, const orb_frame_view* f, const orb_mappoint_view* mps, float th, float nn_ratio,
+                                       const uint8_t* occupied, int32_t* match, int32_t* nmatches) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!f || !mps || !match || !nmatches || mps->n < 0 || (mps->n > 0 && (!mps->valid || !mps->proj_x || !mps->proj_y || !mps->level ||
+        !mps->view_cos || !mps->desc || !mps->blocks))) return ORB_ERR_BAD_ARG;
+    DFrame F;
+    if ((st = upload_frame(m, f, &F, true)) != ORB_OK) return st;
+    const int nq = mps->n;
+    const uint8_t *dv, *dd, *db; const float *dx, *dy, *dxr = nullptr, *dvc; const int* dl; Query* dq;
+    if ((st = ws_upload(m, &dv, mps->valid, nq)) != ORB_OK || (st = ws_upload(m, &dx, mps->proj_x, nq)) != ORB_OK ||
+        (st = ws_upload(m, &dy, mps->proj_y, nq)) != ORB_OK || (st = ws_upload(m, &dl, mps->level, nq)) != ORB_OK ||
+        (st = ws_upload(m, &dvc, mps->view_cos, nq)) != ORB_OK || (st = ws_upload(m, &dd, mps->desc, (size_t)nq * 32)) != ORB_OK ||
+        (st = ws_upload(m, &db, mps->blocks, nq)) != ORB_OK || (st = ws_alloc(m, &dq, std::max(nq, 1))) != ORB_OK) return st;
+    if (mps->proj_xr) { if ((st = ws_upload(m, &dxr, mps->proj_xr, nq)) != ORB_OK) return st; }
+    if (nq > 0) { k_prep_mappoints<<<(nq + 255) / 256, 256, 0, m->stream>>>(nq, dv, dx, dy, dxr, dl, dvc, th, F, dq); m->launches++; }
+    return projection_common(m, 0, nq, dq, dd, db, nullptr, F, occupied, nn_ratio, 0, match, nmatches);
+}
+
+int orb_search_by_projection_lastframe(orb_matcher* m, const orb_frame_view* cur, const orb_lastframe_view* last, const orb_camera* cam,
+                                       float th, int forward, int backward, int check_orientation, const uint8_t* occupied, int32_t* match,
+                                       int32_t* nmatches) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!cur || !last || !cam || !match || !nmatches || last->n < 0 || (last->n > 0 && (!last->valid || !last->xc || !last->yc || !last->zc ||
+        !last->octave || !last->angle || !last->desc || !last->blocks)) || (check_orientation && cur->n > 0 && !cur->angle)) return ORB_ERR_BAD_ARG;
+    DFrame F;
+    if ((st = upload_frame(m, cur, &F, true)) != ORB_OK) return st;
+    const int nq = last->n;
+    const uint8_t *dv, *dd, *db; const float *dx, *dy, *dz, *da; const int* doct; Query* dq;
+    if ((st = ws_upload(m, &dv, last->valid, nq)) != ORB_OK || (st = ws_upload(m, &dx, last->xc, nq)) != ORB_OK ||
+        (st = ws_upload(m, &dy, last->yc, nq)) != ORB_OK || (st = ws_upload(m, &dz, last->zc, nq)) != ORB_OK ||
+        (st = ws_upload(m, &doct, last->octave, nq)) != ORB_OK || (st = ws_upload(m, &da, last->angle, nq)) != ORB_OK ||
+        (st = ws_upload(m, &dd, last->desc, (size_t)nq * 32)) != ORB_OK || (st = ws_upload(m, &db, last->blocks, nq)) != ORB_OK ||
+        (st = ws_alloc(m, &dq, std::max(nq, 1))) != ORB_OK) return st;
+    if (nq > 0) { k_prep_lastframe<<<(nq + 255) / 256, 256, 0, m->stream>>>(nq, dv, dx, dy, dz, doct, *cam, th, forward, backward, F, dq); m->launches++; }
+    return projection_common(m, 1, nq, dq, dd, db, da, F, occupied, 0.f, check_orientation, match, nmatches);
+}
+
+static int check_fv(const orb_featvec_view* v) {
+    return v && v->n_nodes >= 0 && (v->n_nodes == 0 || (v->node_ids && v->start && v->items));
+}
+
+int orb_search_by_bow(orb_matcher* m, const orb_frame_view* kf, const orb_featvec_view* kf_fv, const uint8_t* kf_has_mappoint,
+                      const orb_frame_view* f, const orb_featvec_view* f_fv, float nn_ratio, int check_orientation, int32_t* match_f,
+                      int32_t* nmatches) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!kf || !f || !check_fv(kf_fv) || !check_fv(f_fv) || !kf_has_mappoint || !match_f || !nmatches ||
+        (check_orientation && (!kf->angle || !f->angle))) return ORB_ERR_BAD_ARG;
+    DFrame K, F;
+    if ((st = upload_frame(m, kf, &K, false)) != ORB_OK || (st = upload_frame(m, f, &F, false)) != ORB_OK) return st;
+    std::vector<std::pair<int, int>> nodes;
+    merge_join(kf_fv, f_fv, nodes);
+    std::vector<BowEntry> entries;
+    size_t total = 0;
+    for (auto& ab : nodes) {
+        const int f0 = f_fv->start[ab.second], f1 = f_fv->start[ab.second + 1];
+        for (int p = kf_fv->start[ab.first]; p < kf_fv->start[ab.first + 1]; ++p) {
+            const int qi = (int)kf_fv->items[p];
+            if (qi < 0 || qi >= kf->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
+            if (!kf_has_mappoint[qi] || f1 == f0) continue;
+            BowEntry e; e.q_idx = qi; e.f0 = f0; e.f1 = f1; e.c_start = (int)total;
+            entries.push_back(e);
+            total += (size_t)(f1 - f0);
+        }
+    }
+    if (total > m->cands_cap) { orb_set_error("candidate workspace too small"); return ORB_ERR_CAPACITY; }
+    const int ne = (int)entries.size();
+    const int n_items2 = f_fv->n_nodes ? f_fv->start[f_fv->n_nodes] : 0;
+    for (int i = 0; i < n_items2; ++i) if (f_fv->items[i] >= (uint32_t)f->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
+    const BowEntry* de; const uint32_t* ditems; int *dmatch, *hidx, *hbin;
+    if ((st = ws_upload(m, &de, entries.data(), ne)) != ORB_OK || (st = ws_upload(m, &ditems, f_fv->items, n_items2)) != ORB_OK ||
+        (st = ws_alloc(m, &dmatch, std::max(f->n, 1))) != ORB_OK || (st = ws_alloc(m, &hidx, std::max(ne, 1))) != ORB_OK ||
+        (st = ws_alloc(m, &hbin, std::max(ne, 1))) != ORB_OK) return st;
+    if (ne > 0) { k_bow_distances<<<(ne * 32 + 255) / 256, 256, 0, m->stream>>>(ne, de, K.desc, F.desc, ditems, m->d_cands); m->launches++; }
+    k_resolve_bow<<<1, 32, 0, m->stream>>>(ne, de, m->d_cands, K.angle, F.angle, f->n, nn_ratio, check_orientation, dmatch, hidx, hbin, m->d_scal);
+    m->launches++;
+    ORB_CUDA(cudaGetLastError());
+    if (f->n > 0) ORB_CUDA(cudaMemcpyAsync(match_f, dmatch, (size_t)f->n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+
+int orb_search_for_triangulation(orb_matcher* m, const orb_frame_view* kf1, const orb_featvec_view* fv1, const uint8_t* kf1_has_mappoint,
+                                 const orb_frame_view* kf2, const orb_featvec_view* fv2, const uint8_t* kf2_has_mappoint, const float* f12,
+                                 float ex, float ey, const float* level_sigma2, int only_stereo, int check_orientation, int32_t* match12,
+                                 int32_t* nmatches) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!kf1 || !kf2 || !check_fv(fv1) || !check_fv(fv2) || !kf1_has_mappoint || !kf2_has_mappoint || !f12 || !level_sigma2 || !match12 ||
+        !nmatches || (check_orientation && (!kf1->angle || !kf2->angle))) return ORB_ERR_BAD_ARG;
+    DFrame K1, K2;
+    if ((st = upload_frame(m, kf1, &K1, false)) != ORB_OK || (st = upload_frame(m, kf2, &K2, false)) != ORB_OK) return st;
+    std::vector<std::pair<int, int>> nodes;
+    merge_join(fv1, fv2, nodes);
+    std::vector<BowEntry> entries;
+    for (auto& ab : nodes) {
+        const int f0 = fv2->start[ab.second], f1 = fv2->start[ab.second + 1];
+        if (f1 - f0 > 65535) { orb_set_error("FeatureVector node too large"); return ORB_ERR_CAPACITY; }
+        for (int p = fv1->start[ab.first]; p < fv1->start[ab.first + 1]; ++p) {
+            const int qi = (int)fv1->items[p];
+            if (qi < 0 || qi >= kf1->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
+            if (kf1_has_mappoint[qi]) continue;
+            if (only_stereo && !(kf1->u_right && kf1->u_right[qi] >= 0)) continue;
+            BowEntry e; e.q_idx = qi; e.f0 = f0; e.f1 = f1; e.c_start = 0;
+            entries.push_back(e);
+        }
+    }
+    const int ne = (int)entries.size();
+    const int n_items2 = fv2->n_nodes ? fv2->start[fv2->n_nodes] : 0;
+    for (int i = 0; i < n_items2; ++i) if (fv2->items[i] >= (uint32_t)kf2->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
+    const BowEntry* de; const uint32_t* ditems; const uint8_t* dmp2; int *dmatch, *hidx, *hbin;
+    if ((st = ws_upload(m, &de, entries.data(), ne)) != ORB_OK || (st = ws_upload(m, &ditems, fv2->items, n_items2)) != ORB_OK ||
+        (st = ws_upload(m, &dmp2, kf2_has_mappoint, kf2->n)) != ORB_OK || (st = ws_alloc(m, &dmatch, std::max(kf1->n, 1))) != ORB_OK ||
+        (st = ws_alloc(m, &hidx, std::max(kf1->n, 1))) != ORB_OK || (st = ws_alloc(m, &hbin, std::max(kf1->n, 1))) != ORB_OK) return st;
+    ORB_CUDA(cudaMemsetAsync(dmatch, 0xff, (size_t)std::max(kf1->n, 1) * 4, m->stream));
+    TriParams T;
+    for (int i = 0; i < 9; ++i) T.f12[i] = f12[i];
+    T.ex = ex; T.ey = ey; T.only_stereo = only_stereo;
+    for (int i = 0; i < ORB_MAX_LEVELS; ++i) T.sigma2[i] = i < kf2->n_levels ? level_sigma2[i] : 1.f;
+    if (ne > 0) { k_triangulation<<<(ne * 32 + 255) / 256, 256, 0, m->stream>>>(ne, de, K1, K2, ditems, dmp2, T, dmatch); m->launches++; }
+    k_tri_rot_cull<<<1, 32, 0, m->stream>>>(kf1->n, K1.angle, K2.angle, check_orientation, dmatch, hidx, hbin, m->d_scal);
+    m->launches++;
+    ORB_CUDA(cudaGetLastError());
+    if (kf1->n > 0) ORB_CUDA(cudaMemcpyAsync(match12, dmatch, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+
+}  // extern "C"

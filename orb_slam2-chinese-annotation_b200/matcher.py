@@ -1,0 +1,116 @@
+"""Host-side mirror of ORB_SLAM2::ORBmatcher (reference include/ORBmatcher.h:37-102) over the C
+ABI: same constructor (nnratio, checkOri), same constants, same search entry points.  MapPoint /
+KeyFrame objects of the reference become flat arrays (views.py); the returned match arrays carry
+indices where the reference stores MapPoint pointers."""
+import ctypes as C
+import numpy as np
+from .capi import check, lib, ptr
+from .views import Camera, Frame, FeatureVector, LastFrameView, MapPointView, GridParams, u8, _addr
+
+
+class ORBmatcher:
+    TH_LOW = 50
+    TH_HIGH = 100
+    HISTO_LENGTH = 30
+
+    def __init__(self, nnratio=0.6, checkOri=True, max_n=8192, max_pairs=1, device=0):
+        self.mfNNratio = float(nnratio)
+        self.mbCheckOrientation = bool(checkOri)
+        self._h = C.c_void_p()
+        check(lib().orb_matcher_create(int(max_pairs), int(max_n), int(device), C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().orb_matcher_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    @property
+    def launch_count(self):
+        return lib().orb_matcher_launch_count(self._h)
+
+    # static int DescriptorDistance(const cv::Mat &a, const cv::Mat &b)
+    def DescriptorDistance(self, a, b):
+        a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32); b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+        out = np.empty(len(a), np.int32)
+        check(lib().orb_descriptor_distance(self._h, ptr(a), ptr(b), len(a), ptr(out)))
+        return int(out[0]) if len(out) == 1 else out
+
+    def match_bruteforce(self, a, b):
+        """a: (pairs, n_a, 32) or (n_a, 32); b likewise -> best_idx, best_dist, second_dist."""
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        single = a.ndim == 2
+        if single:
+            a = a[None]; b = b[None]
+        P, na, _ = a.shape; nb = b.shape[1]
+        bi = np.empty((P, na), np.int32); bd = np.empty((P, na), np.int32); sd = np.empty((P, na), np.int32)
+        check(lib().orb_match_bruteforce(self._h, ptr(a), ptr(b), P, na, nb, ptr(bi), ptr(bd), ptr(sd)))
+        return (bi[0], bd[0], sd[0]) if single else (bi, bd, sd)
+
+    def assign_features_to_grid(self, frame):
+        """Frame::AssignFeaturesToGrid -> (cell_start[64*48+1], cell_items)."""
+        cs = np.empty(64 * 48 + 1, np.int32); ci = np.empty(max(frame.N, 1), np.int32); n = C.c_int32()
+        g = frame.view().grid
+        check(lib().orb_assign_features_to_grid(self._h, ptr(frame.x), ptr(frame.y), frame.N, C.byref(g), ptr(cs), ptr(ci), C.byref(n)))
+        return cs, ci[:n.value].copy()
+
+    # int SearchByProjection(Frame &F, const std::vector<MapPoint*> &vpMapPoints, const float th=3)
+    def SearchByProjection(self, F, mappoints, th=3.0, occupied=None):
+        """mappoints: dict with valid, proj_x, proj_y, proj_xr, level, view_cos, desc, blocks."""
+        mp = _mp_view(mappoints)
+        match = np.empty(max(F.N, 1), np.int32); n = C.c_int32()
+        occ = None if occupied is None else u8(occupied)
+        fv = F.view()
+        check(lib().orb_search_by_projection_mappoints(self._h, C.byref(fv), C.byref(mp[0]), C.c_float(th), C.c_float(self.mfNNratio),
+                                                       ptr(occ), ptr(match), C.byref(n)))
+        return n.value, match[:F.N]
+
+    # int SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, const float th, const bool bMono)
+    def SearchByProjectionLastFrame(self, Cur, last, cam, th, forward=False, backward=False, occupied=None):
+        """last: dict with valid, xc, yc, zc, octave, angle, desc, blocks; cam: (fx, fy, cx, cy, mbf)."""
+        lv = _last_view(last)
+        match = np.empty(max(Cur.N, 1), np.int32); n = C.c_int32()
+        occ = None if occupied is None else u8(occupied)
+        cv = Cur.view(); c = Camera(*[float(v) for v in cam])
+        check(lib().orb_search_by_projection_lastframe(self._h, C.byref(cv), C.byref(lv[0]), C.byref(c), C.c_float(th), int(forward),
+                                                       int(backward), int(self.mbCheckOrientation), ptr(occ), ptr(match), C.byref(n)))
+        return n.value, match[:Cur.N]
+
+    # int SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint*> &vpMapPointMatches)
+    def SearchByBoW(self, KF, kf_featvec, kf_has_mappoint, F, f_featvec):
+        match = np.empty(max(F.N, 1), np.int32); n = C.c_int32()
+        hm = u8(kf_has_mappoint)
+        kv = KF.view(); fv = F.view(); a = kf_featvec.view(); b = f_featvec.view()
+        check(lib().orb_search_by_bow(self._h, C.byref(kv), C.byref(a), ptr(hm), C.byref(fv), C.byref(b), C.c_float(self.mfNNratio),
+                                      int(self.mbCheckOrientation), ptr(match), C.byref(n)))
+        return n.value, match[:F.N]
+
+    # int SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12, vector<pair<size_t,size_t>> &vMatchedPairs, bOnlyStereo)
+    def SearchForTriangulation(self, KF1, fv1, has_mp1, KF2, fv2, has_mp2, F12, epipole, level_sigma2, bOnlyStereo=False):
+        match = np.empty(max(KF1.N, 1), np.int32); n = C.c_int32()
+        h1 = u8(has_mp1); h2 = u8(has_mp2)
+        f12 = np.ascontiguousarray(F12, np.float32).reshape(9); s2 = np.ascontiguousarray(level_sigma2, np.float32)
+        k1 = KF1.view(); k2 = KF2.view(); a = fv1.view(); b = fv2.view()
+        check(lib().orb_search_for_triangulation(self._h, C.byref(k1), C.byref(a), ptr(h1), C.byref(k2), C.byref(b), ptr(h2), ptr(f12),
+                                                 C.c_float(epipole[0]), C.c_float(epipole[1]), ptr(s2), int(bOnlyStereo),
+                                                 int(self.mbCheckOrientation), ptr(match), C.byref(n)))
+        m = match[:KF1.N]
+        pairs = [(int(i), int(m[i])) for i in np.nonzero(m >= 0)[0]]
+        return n.value, pairs
+
+
+def _mp_view(d):
+    keep = dict(valid=u8(d["valid"]), proj_x=np.ascontiguousarray(d["proj_x"], np.float32), proj_y=np.ascontiguousarray(d["proj_y"], np.float32),
+                proj_xr=np.ascontiguousarray(d["proj_xr"], np.float32), level=np.ascontiguousarray(d["level"], np.int32),
+                view_cos=np.ascontiguousarray(d["view_cos"], np.float32), desc=np.ascontiguousarray(d["desc"], np.uint8), blocks=u8(d["blocks"]))
+    v = MapPointView(len(keep["valid"]), *[_addr(keep[k]) for k in ("valid", "proj_x", "proj_y", "proj_xr", "level", "view_cos", "desc", "blocks")])
+    return v, keep
+
+
+def _last_view(d):
+    keep = dict(valid=u8(d["valid"]), xc=np.ascontiguousarray(d["xc"], np.float32), yc=np.ascontiguousarray(d["yc"], np.float32),
+                zc=np.ascontiguousarray(d["zc"], np.float32), octave=np.ascontiguousarray(d["octave"], np.int32),
+                angle=np.ascontiguousarray(d["angle"], np.float32), desc=np.ascontiguousarray(d["desc"], np.uint8), blocks=u8(d["blocks"]))
+    v = LastFrameView(len(keep["valid"]), *[_addr(keep[k]) for k in ("valid", "xc", "yc", "zc", "octave", "angle", "desc", "blocks")])
+    return v, keep

@@ -77,3 +77,99 @@ def make_descriptor_sets(n_a, n_b, idx=0, match_frac=0.7, flip_p=0.08):
     perm = np.full(n_b, -1, np.int64)
     perm[dst] = src
     return A, B, perm
+
+
+# ------------------------------------------------------------------------------------------
+# Matcher scenarios: SoA stand-ins for Frame / KeyFrame / MapPoint state.
+def _scale_factors(n_levels=8, s=1.2):
+    sf = np.ones(n_levels, np.float32)
+    for i in range(1, n_levels):
+        sf[i] = np.float32(np.float64(sf[i - 1]) * np.float64(np.float32(s)))
+    return sf
+
+
+def make_frame_arrays(n, idx=0, w=1241, h=376, n_levels=8, stereo=True, coarse_desc=False):
+    """Random frame: keypoints uniform in the image, octaves by the per-level quota, random angles."""
+    rng = np.random.default_rng(SEED_BASE + 0x300000 + int(idx))
+    x = rng.uniform(20, w - 20, n).astype(np.float32); y = rng.uniform(20, h - 20, n).astype(np.float32)
+    quota = np.array([1.2 ** -l for l in range(n_levels)]); quota /= quota.sum()
+    octave = rng.choice(n_levels, n, p=quota).astype(np.int32)
+    angle = rng.uniform(0, 360, n).astype(np.float32)
+    desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    if coarse_desc:  # few distinct bit patterns -> many equal distances (tie-breaking paths)
+        desc = np.repeat(rng.integers(0, 2, (n, 4), dtype=np.uint8) * 255, 8, axis=1)
+    u_right = None
+    if stereo:
+        u_right = np.where(rng.random(n) < 0.6, x - rng.uniform(1, 60, n), -1.0).astype(np.float32)
+    return dict(x=x, y=y, octave=octave, angle=angle, desc=desc, u_right=u_right, sf=_scale_factors(n_levels),
+                bounds=(0.0, 0.0, float(w), float(h)))
+
+
+def perturb_descriptors(rng, desc, flip_p=0.08):
+    flips = rng.random((len(desc), 256)) < flip_p
+    return desc ^ np.packbits(flips, axis=1, bitorder="little")
+
+
+def make_projection_scenario(n_kp=2000, n_mp=2000, idx=0, match_frac=0.7, coarse_desc=False, **kw):
+    """Frame + MapPoints whose projections fall near frame keypoints (SearchByProjection(F, MPs))."""
+    rng = np.random.default_rng(SEED_BASE + 0x400000 + int(idx))
+    f = make_frame_arrays(n_kp, idx, coarse_desc=coarse_desc, **kw)
+    src = rng.integers(0, n_kp, n_mp)
+    matched = rng.random(n_mp) < match_frac
+    px = np.where(matched, f["x"][src] + rng.normal(0, 2, n_mp), rng.uniform(0, f["bounds"][2], n_mp)).astype(np.float32)
+    py = np.where(matched, f["y"][src] + rng.normal(0, 2, n_mp), rng.uniform(0, f["bounds"][3], n_mp)).astype(np.float32)
+    desc = np.where(matched[:, None], perturb_descriptors(rng, f["desc"][src]), rng.integers(0, 256, (n_mp, 32), dtype=np.uint8)).astype(np.uint8)
+    if coarse_desc:
+        desc = f["desc"][src]
+    level = np.clip(f["octave"][src] + rng.integers(0, 2, n_mp), 0, len(f["sf"]) - 1).astype(np.int32)
+    ur = f["u_right"][src] if f["u_right"] is not None else np.full(n_mp, -1.0)
+    mps = dict(valid=(rng.random(n_mp) < 0.9), proj_x=px, proj_y=py,
+               proj_xr=np.where(ur > 0, ur + rng.normal(0, 2, n_mp), px - 10).astype(np.float32), level=level,
+               view_cos=np.where(rng.random(n_mp) < 0.5, 0.9995, 0.95).astype(np.float32), desc=desc,
+               blocks=(rng.random(n_mp) < 0.9))
+    occupied = rng.random(n_kp) < 0.1
+    return f, mps, occupied
+
+
+def make_lastframe_scenario(n_kp=2000, idx=0, cam=(718.856, 718.856, 607.19, 185.2, 386.1448), **kw):
+    """Current frame + last-frame MapPoints given in the current camera frame (SearchByProjection(Cur, Last))."""
+    rng = np.random.default_rng(SEED_BASE + 0x500000 + int(idx))
+    f = make_frame_arrays(n_kp, idx, **kw)
+    fx, fy, cx, cy, mbf = cam
+    n = n_kp
+    src = rng.permutation(n_kp)
+    z = rng.uniform(4, 60, n).astype(np.float32)
+    u = f["x"][src] + rng.normal(0, 3, n); v = f["y"][src] + rng.normal(0, 3, n)
+    xc = ((u - cx) * z / fx).astype(np.float32); yc = ((v - cy) * z / fy).astype(np.float32)
+    z[rng.random(n) < 0.03] *= -1  # behind the camera -> invzc < 0
+    dangle = np.where(rng.random(n) < 0.8, rng.normal(0, 5, n), rng.uniform(0, 360, n))
+    last = dict(valid=(rng.random(n) < 0.8), xc=xc, yc=yc, zc=z, octave=f["octave"][src].copy(),
+                angle=np.mod(f["angle"][src] + dangle, 360).astype(np.float32), desc=perturb_descriptors(rng, f["desc"][src]),
+                blocks=(rng.random(n) < 0.85))
+    return f, last, cam
+
+
+def make_bow_scenario(n1=2000, n2=2000, idx=0, n_nodes=120, coarse_desc=False, **kw):
+    """Two feature sets with FeatureVectors: matched features mostly share a vocabulary node."""
+    rng = np.random.default_rng(SEED_BASE + 0x600000 + int(idx))
+    a = make_frame_arrays(n1, 2 * idx, coarse_desc=coarse_desc, **kw)
+    b = make_frame_arrays(n2, 2 * idx + 1, coarse_desc=coarse_desc, **kw)
+    nm = min(n1, n2) * 7 // 10
+    ia = rng.permutation(n1)[:nm]; ib = rng.permutation(n2)[:nm]
+    if not coarse_desc:
+        b["desc"][ib] = perturb_descriptors(rng, a["desc"][ia], 0.05)
+    b["angle"][ib] = np.mod(a["angle"][ia] + np.where(rng.random(nm) < 0.8, rng.normal(20, 4, nm), rng.uniform(0, 360, nm)), 360).astype(np.float32)
+    b["x"][ib] = np.clip(a["x"][ia] + rng.normal(0, 15, nm), 20, 1220).astype(np.float32)
+    b["y"][ib] = np.clip(a["y"][ia] + rng.normal(0, 1.0, nm), 20, 355).astype(np.float32)
+    b["octave"][ib] = a["octave"][ia]
+    node_a = rng.integers(0, n_nodes, n1) * 3 + 7
+    node_b = rng.integers(0, n_nodes, n2) * 3 + 7
+    same = rng.random(nm) < 0.9
+    node_b[ib[same]] = node_a[ia[same]]
+    node_b[node_b % 5 == 0] += 1      # some nodes exist on one side only (merge-join skips)
+    fva = {}; fvb = {}
+    for i in range(n1):
+        fva.setdefault(int(node_a[i]), []).append(i)
+    for i in range(n2):
+        fvb.setdefault(int(node_b[i]), []).append(i)
+    return a, fva, b, fvb, (rng.random(n1) < 0.6), (rng.random(n2) < 0.3)

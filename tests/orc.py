@@ -186,3 +186,57 @@ def match_bruteforce(a, b):
     bi = np.empty(len(a), np.int32); bd = np.empty(len(a), np.int32); sd = np.empty(len(a), np.int32)
     lib.orc_match_bruteforce(_p(a), _p(b), len(a), len(b), _p(bi), _p(bd), _p(sd))
     return bi, bd, sd
+
+
+# ---- matcher oracle (oracle/match_oracle.cpp) over the same plain view structs as the C ABI
+import importlib as _il
+_views = _il.import_module("orb_slam2-chinese-annotation_b200.views")
+_mt = _il.import_module("orb_slam2-chinese-annotation_b200.matcher")   # only for the struct packers _mp_view/_last_view
+
+
+def assign_features_to_grid(frame):
+    cs = np.empty(64 * 48 + 1, np.int32); ci = np.empty(max(frame.N, 1), np.int32); n = C.c_int32()
+    g = frame.view().grid
+    lib.orc_assign_features_to_grid(_p(frame.x), _p(frame.y), frame.N, C.byref(g), _p(cs), _p(ci), C.byref(n))
+    return cs, ci[:n.value].copy()
+
+
+def search_by_projection_mps(F, mappoints, th, nn_ratio, occupied=None):
+    mp, keep = _mt._mp_view(mappoints)
+    match = np.empty(max(F.N, 1), np.int32)
+    occ = None if occupied is None else _views.u8(occupied)
+    fv = F.view()
+    lib.orc_search_by_projection_mps.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+    n = lib.orc_search_by_projection_mps(C.byref(fv), C.byref(mp), th, nn_ratio, None if occ is None else occ.ctypes.data, _p(match))
+    return n, match[:F.N]
+
+
+def search_by_projection_last(Cur, last, cam, th, forward, backward, check_ori, occupied=None):
+    lv, keep = _mt._last_view(last)
+    match = np.empty(max(Cur.N, 1), np.int32)
+    occ = None if occupied is None else _views.u8(occupied)
+    cv = Cur.view(); c = _views.Camera(*[float(v) for v in cam])
+    lib.orc_search_by_projection_last.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    n = lib.orc_search_by_projection_last(C.byref(cv), C.byref(lv), C.byref(c), th, int(forward), int(backward), int(check_ori),
+                                          None if occ is None else occ.ctypes.data, _p(match))
+    return n, match[:Cur.N]
+
+
+def search_by_bow(KF, kfv, kf_has_mp, F, ffv, nn_ratio, check_ori):
+    match = np.empty(max(F.N, 1), np.int32)
+    hm = _views.u8(kf_has_mp)
+    kv = KF.view(); fv = F.view(); a = kfv.view(); b = ffv.view()
+    lib.orc_search_by_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p]
+    n = lib.orc_search_by_bow(C.byref(kv), C.byref(a), _p(hm), C.byref(fv), C.byref(b), nn_ratio, int(check_ori), _p(match))
+    return n, match[:F.N]
+
+
+def search_for_triangulation(KF1, fv1, has1, KF2, fv2, has2, F12, epipole, sigma2, only_stereo, check_ori):
+    match = np.empty(max(KF1.N, 1), np.int32)
+    h1 = _views.u8(has1); h2 = _views.u8(has2)
+    f12 = np.ascontiguousarray(F12, np.float32).reshape(9); s2 = np.ascontiguousarray(sigma2, np.float32)
+    k1 = KF1.view(); k2 = KF2.view(); a = fv1.view(); b = fv2.view()
+    lib.orc_search_for_triangulation.argtypes = [C.c_void_p] * 7 + [C.c_float, C.c_float, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    n = lib.orc_search_for_triangulation(C.byref(k1), C.byref(a), _p(h1), C.byref(k2), C.byref(b), _p(h2), _p(f12), float(epipole[0]),
+                                         float(epipole[1]), _p(s2), int(only_stereo), int(check_ori), _p(match))
+    return n, match[:KF1.N]

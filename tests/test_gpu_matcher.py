@@ -1,0 +1,111 @@
+"""GPU parity of the ORBmatcher paths against the CPU oracle: match indices and counts identical,
+including tie-heavy descriptor sets, occupied keypoints and non-blocking MapPoints."""
+import importlib
+import numpy as np
+import pytest
+import orc
+
+synth = importlib.import_module("orb_slam2-chinese-annotation_b200.synth")
+views = importlib.import_module("orb_slam2-chinese-annotation_b200.views")
+matcher = importlib.import_module("orb_slam2-chinese-annotation_b200.matcher")
+pytestmark = pytest.mark.gpu
+
+
+def _frame(d):
+    return views.Frame(d["x"], d["y"], d["octave"], d["angle"], d["desc"], d["sf"], d["bounds"], d["u_right"])
+
+
+@pytest.fixture(scope="module")
+def gm():
+    return matcher.ORBmatcher(0.8, True, max_n=4096, max_pairs=8)
+
+
+def test_descriptor_distance(gm):
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 256, (500, 32), dtype=np.uint8); b = rng.integers(0, 256, (500, 32), dtype=np.uint8)
+    b[:5] = a[:5]; b[5] = ~a[5]
+    d = gm.DescriptorDistance(a, b)
+    assert list(d) == [orc.descriptor_distance(a[i], b[i]) for i in range(500)]
+    assert d[0] == 0 and d[5] == 256
+
+
+@pytest.mark.parametrize("na,nb", [(2000, 2000), (1, 1), (257, 63), (130, 1000)])
+def test_bruteforce(gm, na, nb):
+    A, B, _ = synth.make_descriptor_sets(na, nb, 1)
+    gi, gd, gs = gm.match_bruteforce(A, B)
+    oi, od, os_ = orc.match_bruteforce(A, B)
+    assert np.array_equal(gi, oi) and np.array_equal(gd, od) and np.array_equal(gs, os_)
+
+
+def test_bruteforce_batch_and_ties(gm):
+    rng = np.random.default_rng(2)
+    A = np.repeat(rng.integers(0, 2, (4, 300, 4), dtype=np.uint8) * 255, 8, axis=2)
+    B = np.repeat(rng.integers(0, 2, (4, 280, 4), dtype=np.uint8) * 255, 8, axis=2)
+    gi, gd, gs = gm.match_bruteforce(A, B)
+    for p in range(4):
+        oi, od, os_ = orc.match_bruteforce(A[p], B[p])
+        assert np.array_equal(gi[p], oi) and np.array_equal(gd[p], od) and np.array_equal(gs[p], os_)
+
+
+def test_grid_assignment(gm):
+    for idx, n in [(0, 2000), (1, 1), (2, 777)]:
+        d = synth.make_frame_arrays(n, idx)
+        d["x"][: n // 10] = np.float32(d["bounds"][2]) - 0.2   # round() lands on column 64 -> dropped
+        f = _frame(d)
+        gs, gi = gm.assign_features_to_grid(f)
+        os_, oi = orc.assign_features_to_grid(f)
+        assert np.array_equal(gs, os_) and np.array_equal(gi, oi)
+
+
+@pytest.mark.parametrize("idx,th,coarse", [(0, 1.0, False), (1, 3.0, False), (2, 5.0, False), (3, 3.0, True), (4, 1.0, True)])
+def test_search_by_projection_mappoints(gm, idx, th, coarse):
+    f, mps, occ = synth.make_projection_scenario(2000, 2000, idx, coarse_desc=coarse)
+    F = _frame(f)
+    for use_occ in (False, True):
+        n_g, m_g = gm.SearchByProjection(F, mps, th, occupied=occ if use_occ else None)
+        n_o, m_o = orc.search_by_projection_mps(F, mps, th, gm.mfNNratio, occ if use_occ else None)
+        assert n_g == n_o and np.array_equal(m_g, m_o), (idx, th, n_g, n_o, int((m_g != m_o).sum()))
+    assert n_o > 100
+
+
+@pytest.mark.parametrize("idx,th,fwd,bwd", [(0, 7.0, False, False), (1, 15.0, False, False), (2, 7.0, True, False), (3, 15.0, False, True)])
+def test_search_by_projection_lastframe(gm, idx, th, fwd, bwd):
+    f, last, cam = synth.make_lastframe_scenario(2000, idx)
+    F = _frame(f)
+    for check_ori in (True, False):
+        gm.mbCheckOrientation = check_ori
+        n_g, m_g = gm.SearchByProjectionLastFrame(F, last, cam, th, fwd, bwd)
+        n_o, m_o = orc.search_by_projection_last(F, last, cam, th, fwd, bwd, check_ori)
+        assert n_g == n_o and np.array_equal(m_g, m_o), (idx, n_g, n_o, int((m_g != m_o).sum()))
+    gm.mbCheckOrientation = True
+    assert n_o > 100
+
+
+@pytest.mark.parametrize("idx,coarse,ratio", [(0, False, 0.7), (1, False, 0.75), (2, True, 0.9), (3, False, 0.6)])
+def test_search_by_bow(gm, idx, coarse, ratio):
+    a, fva, b, fvb, has_a, _ = synth.make_bow_scenario(2000, 1900, idx, coarse_desc=coarse)
+    KF, F = _frame(a), _frame(b)
+    va, vb = views.FeatureVector(fva), views.FeatureVector(fvb)
+    gm.mfNNratio = ratio
+    n_g, m_g = gm.SearchByBoW(KF, va, has_a, F, vb)
+    n_o, m_o = orc.search_by_bow(KF, va, has_a, F, vb, ratio, True)
+    gm.mfNNratio = 0.8
+    assert n_g == n_o and np.array_equal(m_g, m_o), (idx, n_g, n_o)
+    if not coarse:
+        assert n_o > 50
+
+
+@pytest.mark.parametrize("idx,only_stereo,coarse", [(0, False, False), (1, True, False), (2, False, True)])
+def test_search_for_triangulation(gm, idx, only_stereo, coarse):
+    a, fva, b, fvb, has_a, has_b = synth.make_bow_scenario(2000, 2000, 10 + idx, coarse_desc=coarse)
+    KF1, KF2 = _frame(a), _frame(b)
+    va, vb = views.FeatureVector(fva), views.FeatureVector(fvb)
+    # pure x-translation: F12 = [t]_x up to scale -> epipolar lines are horizontal (y2 = y1)
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32)
+    sigma2 = (a["sf"] * a["sf"]).astype(np.float32)
+    n_g, pairs = gm.SearchForTriangulation(KF1, va, has_a, KF2, vb, has_b, F12, (2000.0, 188.0), sigma2, only_stereo)
+    n_o, m_o = orc.search_for_triangulation(KF1, va, has_a, KF2, vb, has_b, F12, (2000.0, 188.0), sigma2, only_stereo, True)
+    assert n_g == n_o, (n_g, n_o)
+    assert pairs == [(int(i), int(m_o[i])) for i in np.nonzero(m_o >= 0)[0]]
+    if not coarse:
+        assert n_o > 20

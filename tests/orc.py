@@ -240,3 +240,44 @@ def search_for_triangulation(KF1, fv1, has1, KF2, fv2, has2, F12, epipole, sigma
     n = lib.orc_search_for_triangulation(C.byref(k1), C.byref(a), _p(h1), C.byref(k2), C.byref(b), _p(h2), _p(f12), float(epipole[0]),
                                          float(epipole[1]), _p(s2), int(only_stereo), int(check_ori), _p(match))
     return n, match[:KF1.N]
+
+
+# ---- the reference's own ORBextractor.cc compiled verbatim (oracle/_ref; built only where /root/reference exists)
+_REF_SO = os.path.join(ROOT, "oracle", "_ref", "libref_orbextractor.so")
+
+
+def ref_available():
+    return os.path.exists(_REF_SO)
+
+
+class RefExtractor:
+    """ORB_SLAM2::ORBextractor from /root/reference/src/ORBextractor.cc (verbatim) behind oracle/ref_wrap.cpp."""
+    _lib = None
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        if RefExtractor._lib is None:
+            L = C.CDLL(_REF_SO)
+            L.ref_extractor_create.restype = C.c_void_p
+            L.ref_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+            L.ref_extractor_destroy.argtypes = [C.c_void_p]
+            L.ref_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+            L.ref_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, _i32p, _i32p]
+            RefExtractor._lib = L
+        self.h = RefExtractor._lib.ref_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            RefExtractor._lib.ref_extractor_destroy(self.h)
+            self.h = None
+
+    def extract(self, img, cap=200000):
+        img = np.ascontiguousarray(img, np.uint8)
+        kps = np.empty(cap, KP_DTYPE); desc = np.empty((cap, 32), np.uint8)
+        n = RefExtractor._lib.ref_extract(self.h, _p(img), img.shape[1], img.shape[0], img.strides[0], _p(kps), _p(desc), cap)
+        assert n >= 0
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, l):
+        buf = np.empty(1 << 24, np.uint8); w = C.c_int32(); h = C.c_int32()
+        assert RefExtractor._lib.ref_level(self.h, l, _p(buf), buf.size, C.byref(w), C.byref(h)) == 0
+        return buf[:w.value * h.value].reshape(h.value, w.value).copy()

@@ -93,14 +93,16 @@ inline int rot_bin(float a1, float a2) {
 
 extern "C" {
 
-int orc_stereo_match(const orc_extractor* L, const orc_extractor* R, const orc_keypoint* kpL, const uint8_t* dL, int nL,
-                     const orc_keypoint* kpR, const uint8_t* dR, int nR, const float* sf, const float* inv_sf, float mbf, float minD,
-                     float maxD, float* uRight, float* depth, int32_t* best_sad) {
+// Pyramid levels are passed as plain views so that the same code serves the oracle extractor
+// (orc_stereo_match below) and the verbatim reference extractor of oracle/_ref.
+int orc_stereo_match_levels(int nlevels, const uint8_t* const* lvL, const int32_t* lwA, const int32_t* lhA, const int32_t* lsA,
+                            const uint8_t* const* lvR, const int32_t* rwA, const int32_t* rhA, const int32_t* rsA,
+                            const orc_keypoint* kpL, const uint8_t* dL, int nL, const orc_keypoint* kpR, const uint8_t* dR, int nR,
+                            const float* sf, const float* inv_sf, float mbf, float minD, float maxD, float* uRight, float* depth,
+                            int32_t* best_sad) {
     for (int i = 0; i < nL; ++i) { uRight[i] = -1.0f; depth[i] = -1.0f; if (best_sad) best_sad[i] = -1; }
     const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
-    int w0, h0, s0;
-    orc_level(L, 0, &w0, &h0, &s0);
-    const int nRows = h0;
+    const int nRows = lhA[0];
     std::vector<std::vector<int>> vRowIndices(nRows);
     for (int iR = 0; iR < nR; ++iR) {
         const float kpY = kpR[iR].y;
@@ -134,9 +136,10 @@ int orc_stereo_match(const orc_extractor* L, const orc_extractor* R, const orc_k
         const float scaleFactor = inv_sf[levelL];
         const float scaleduL = std::round(kl.x * scaleFactor), scaledvL = std::round(kl.y * scaleFactor), scaleduR0 = std::round(uR0 * scaleFactor);
         const int w = 5, LL = 5;
-        int lw, lh, ls, rw, rh, rs;
-        const uint8_t* imL = orc_level(L, levelL, &lw, &lh, &ls);
-        const uint8_t* imR = orc_level(R, levelL, &rw, &rh, &rs);
+        if (levelL < 0 || levelL >= nlevels) continue;
+        const int lw = lwA[levelL], lh = lhA[levelL], ls = lsA[levelL], rw = rwA[levelL], rh = rhA[levelL], rs = rsA[levelL];
+        const uint8_t* imL = lvL[levelL];
+        const uint8_t* imR = lvR[levelL];
         const float iniu = scaleduR0 + LL - w, endu = scaleduR0 + LL + w + 1;
         if (iniu < 0 || endu >= rw) continue;
         const int su = (int)scaleduL, sv = (int)scaledvL, sr = (int)scaleduR0;
@@ -182,6 +185,16 @@ int orc_stereo_match(const orc_extractor* L, const orc_extractor* R, const orc_k
         uRight[vDistIdx[i].second] = -1; depth[vDistIdx[i].second] = -1; --kept;
     }
     return kept;
+}
+
+int orc_stereo_match(const orc_extractor* L, const orc_extractor* R, const orc_keypoint* kpL, const uint8_t* dL, int nL,
+                     const orc_keypoint* kpR, const uint8_t* dR, int nR, const float* sf, const float* inv_sf, float mbf, float minD,
+                     float maxD, float* uRight, float* depth, int32_t* best_sad) {
+    const uint8_t *pl[32], *pr[32];
+    int32_t lw[32], lh[32], ls[32], rw[32], rh[32], rs[32];
+    int n = 0;
+    while (n < 32 && (pl[n] = orc_level(L, n, &lw[n], &lh[n], &ls[n])) != nullptr && (pr[n] = orc_level(R, n, &rw[n], &rh[n], &rs[n])) != nullptr) ++n;
+    return orc_stereo_match_levels(n, pl, lw, lh, ls, pr, rw, rh, rs, kpL, dL, nL, kpR, dR, nR, sf, inv_sf, mbf, minD, maxD, uRight, depth, best_sad);
 }
 
 void orc_match_bruteforce(const uint8_t* a, const uint8_t* b, int n_a, int n_b, int32_t* best_idx, int32_t* best_dist, int32_t* second_dist) {

@@ -87,6 +87,14 @@ int ref_level(void* ev, int level, uint8_t* dst, int cap, int* w, int* h) {
     for (int y = 0; y < m.rows; ++y) std::memcpy(dst + (size_t)y * m.cols, m.ptr(y), (size_t)m.cols);
     return 0;
 }
+// pointer view of mvImagePyramid[level] (valid until the next ref_extract on this handle)
+const uint8_t* ref_level_ptr(void* ev, int level, int* w, int* h, int* stride) {
+    ORB_SLAM2::ORBextractor* e = (ORB_SLAM2::ORBextractor*)ev;
+    if (level < 0 || level >= (int)e->mvImagePyramid.size()) return nullptr;
+    const cv::Mat& m = e->mvImagePyramid[level];
+    *w = m.cols; *h = m.rows; *stride = (int)m.step;
+    return m.data;
+}
 int ref_levels(void* ev) { return ((ORB_SLAM2::ORBextractor*)ev)->GetLevels(); }
 void ref_scale_factors(void* ev, float* sf) {
     std::vector<float> v = ((ORB_SLAM2::ORBextractor*)ev)->GetScaleFactors();

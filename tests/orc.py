@@ -262,6 +262,9 @@ class RefExtractor:
             L.ref_extractor_destroy.argtypes = [C.c_void_p]
             L.ref_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
             L.ref_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, _i32p, _i32p]
+            L.ref_levels.argtypes = [C.c_void_p]
+            L.ref_level_ptr.restype = C.c_void_p
+            L.ref_level_ptr.argtypes = [C.c_void_p, C.c_int, _i32p, _i32p, _i32p]
             RefExtractor._lib = L
         self.h = RefExtractor._lib.ref_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
 
@@ -281,3 +284,27 @@ class RefExtractor:
         buf = np.empty(1 << 24, np.uint8); w = C.c_int32(); h = C.c_int32()
         assert RefExtractor._lib.ref_level(self.h, l, _p(buf), buf.size, C.byref(w), C.byref(h)) == 0
         return buf[:w.value * h.value].reshape(h.value, w.value).copy()
+
+
+    def level_views(self):
+        """(ptrs, w, h, stride) ctypes arrays of mvImagePyramid for orc_stereo_match_levels."""
+        L = RefExtractor._lib
+        n = L.ref_levels(self.h)
+        ptrs = (C.c_void_p * n)(); w = (C.c_int32 * n)(); h = (C.c_int32 * n)(); s = (C.c_int32 * n)()
+        for l in range(n):
+            a = C.c_int32(); b = C.c_int32(); c = C.c_int32()
+            ptrs[l] = L.ref_level_ptr(self.h, l, C.byref(a), C.byref(b), C.byref(c)); w[l] = a.value; h[l] = b.value; s[l] = c.value
+        return n, ptrs, w, h, s
+
+
+def stereo_match_ref(rL, rR, kpL, dL, kpR, dR, sf, inv_sf, mbf, min_d, max_d):
+    """ComputeStereoMatches (oracle port) on the pyramids held by two RefExtractor handles."""
+    n, pl, lw, lh, ls = rL.level_views(); _, pr, rw, rh, rs = rR.level_views()
+    nL, nR = len(kpL), len(kpR)
+    kpL = np.ascontiguousarray(kpL); kpR = np.ascontiguousarray(kpR); dL = np.ascontiguousarray(dL); dR = np.ascontiguousarray(dR)
+    ur = np.empty(max(nL, 1), np.float32); dp = np.empty(max(nL, 1), np.float32); sad = np.empty(max(nL, 1), np.int32)
+    lib.orc_stereo_match_levels.argtypes = [C.c_int] + [C.c_void_p] * 10 + [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                                                         C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    kept = lib.orc_stereo_match_levels(n, pl, lw, lh, ls, pr, rw, rh, rs, _p(kpL), _p(dL), nL, _p(kpR), _p(dR), nR, _p(sf), _p(inv_sf),
+                                       mbf, min_d, max_d, _p(ur), _p(dp), _p(sad))
+    return ur[:nL], dp[:nL], sad[:nL], kept

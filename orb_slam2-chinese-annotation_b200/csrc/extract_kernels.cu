@@ -15,7 +15,17 @@ __constant__ __align__(16) signed char c_pattern[1024] = {
 
 // ------------------------------------------------------------------------------------------
 // Pyramid: level l <- level l-1, OpenCV 8u INTER_LINEAR (11-bit coefficients).  One thread
-// produces 4 horizontally adjacent pixels and stores them as one 32-bit word.
+// produces 4 horizontally adjacent pixels of one row and stores them as one 32-bit word.  The
+// two source rows are read as aligned words; a (pixel, right neighbour) byte pair is pulled out
+// with one PRMT and weighted with one DP2A (the two 16-bit horizontal coefficients of a pixel are
+// stored as one 32-bit word).
+__device__ __forceinline__ unsigned pick_pair(unsigned w0, unsigned w1, unsigned w2, int idx) {
+    // bytes idx, idx+1 of the 12-byte window (w0,w1,w2), idx in [0, 7]
+    const unsigned lo = idx < 4 ? w0 : w1, hi = idx < 4 ? w1 : w2;
+    const unsigned j = idx & 3;
+    return __byte_perm(lo, hi, j | ((j + 1) << 4));
+}
+
 __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr, const LevelGeom src, const LevelGeom dst) {
     const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4;
     const int y = blockIdx.y * 4 + threadIdx.y;
@@ -25,21 +35,41 @@ __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr,
     int sy0 = dst.yofs[y], sy1 = sy0 + 1;
     sy0 = min(max(sy0, 0), src.h - 1);
     sy1 = min(max(sy1, 0), src.h - 1);
-    const int b0 = dst.beta[2 * y], b1 = dst.beta[2 * y + 1];
+    const unsigned bw = reinterpret_cast<const unsigned*>(dst.beta)[y];
+    const int b0 = (int)(bw & 0xffffu), b1 = (int)(bw >> 16);
     const uint8_t* r0 = S + (size_t)sy0 * src.pitch;
     const uint8_t* r1 = S + (size_t)sy1 * src.pitch;
+    // tables are padded to a multiple of 4 entries and 16-byte aligned
+    const int4 xo = reinterpret_cast<const int4*>(dst.xofs)[x4 >> 2];
+    const uint4 al = reinterpret_cast<const uint4*>(dst.alpha)[x4 >> 2];
+    const int base = xo.x & ~3;
+    const int sxs[4] = {xo.x, xo.y, xo.z, xo.w};
+    const unsigned als[4] = {al.x, al.y, al.z, al.w};
     uint32_t out = 0;
+    if (xo.w - base <= 7) {
+        const unsigned* p0 = reinterpret_cast<const unsigned*>(r0 + base);
+        const unsigned* p1 = reinterpret_cast<const unsigned*>(r1 + base);
+        const unsigned u0 = p0[0], u1 = p0[1], u2 = p0[2], v0 = p1[0], v1 = p1[1], v2 = p1[2];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int x = min(x4 + i, dst.w - 1);
-        const int sx = dst.xofs[x];
-        const int sx1 = min(sx + 1, src.w - 1);
-        const int a0 = dst.alpha[2 * x], a1 = dst.alpha[2 * x + 1];
-        const int h0 = r0[sx] * a0 + r0[sx1] * a1;
-        const int h1 = r1[sx] * a0 + r1[sx1] * a1;
-        int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-        v = min(max(v, 0), 255);
-        out |= (uint32_t)v << (8 * i);
+        for (int i = 0; i < 4; ++i) {
+            const int idx = sxs[i] - base;
+            const int h0 = (int)__dp2a_lo(als[i], pick_pair(u0, u1, u2, idx), 0u);
+            const int h1 = (int)__dp2a_lo(als[i], pick_pair(v0, v1, v2, idx), 0u);
+            int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+            v = min(max(v, 0), 255);
+            out |= (uint32_t)v << (8 * i);
+        }
+    } else {  // generic path (scale factors whose 4-pixel footprint exceeds the 12-byte window)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int sx = sxs[i], sx1 = min(sx + 1, src.w - 1);
+            const int a0 = (int)(als[i] & 0xffffu), a1 = (int)(als[i] >> 16);
+            const int h0 = r0[sx] * a0 + r0[sx1] * a1;
+            const int h1 = r1[sx] * a0 + r1[sx1] * a1;
+            int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+            v = min(max(v, 0), 255);
+            out |= (uint32_t)v << (8 * i);
+        }
     }
     // rows are pitch-padded to a multiple of 64 bytes, so the full word is always in bounds
     *reinterpret_cast<uint32_t*>(D + (size_t)y * dst.pitch + x4) = out;
@@ -48,8 +78,12 @@ __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr,
 // ------------------------------------------------------------------------------------------
 // 7x7 Gaussian, sigma 2, BORDER_REFLECT_101 at the level's own edge, OpenCV >= 4 fixed point:
 // Q0.8 taps {18,34,48,56,48,34,18}; horizontal Q8.8 (u16), vertical Q16.16, (v + 2^15) >> 16.
+// CTA tile 128 x 64; a thread owns a 4-pixel-wide strip of 8 rows and slides a 7-row window of
+// horizontal sums held in registers down its strip.  Horizontal sums are two DP4A per pixel on
+// byte windows assembled with PRMT from three aligned shared-memory words.
 #define BLUR_TW 128
-#define BLUR_TH 32
+#define BLUR_TH 64
+#define BLUR_RW ((BLUR_TW + 8) / 4)  // words per staged row: 4 bytes of halo (3 used) on each side
 __device__ __forceinline__ int reflect101(int p, int len) {
     if (len == 1) return 0;
     while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
@@ -57,42 +91,63 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 }
 
 __global__ void __launch_bounds__(256) k_gauss7(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, const Plan P) {
-    __shared__ uint8_t raw[BLUR_TH + 6][BLUR_TW + 8];
-    __shared__ uint16_t hor[BLUR_TH + 6][BLUR_TW];
+    __shared__ uint32_t raw[BLUR_TH + 6][BLUR_RW];
     int l = 0;
     while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].tile_off) ++l;
     const LevelGeom& G = P.lv[l];
     const int t = blockIdx.x - G.tile_off;
-    const int tx = (t % G.tiles_x) * BLUR_TW, ty = (t / G.tiles_x) * BLUR_TH;
+    const int tyi = t / G.tiles_x;
+    const int tx = (t - tyi * G.tiles_x) * BLUR_TW, ty = tyi * BLUR_TH;
     const uint8_t* S = pyr + G.off + (size_t)blockIdx.y * G.img_stride;
     uint8_t* D = blur + G.off + (size_t)blockIdx.y * G.img_stride;
     const int tid = threadIdx.x;
-    // stage the (TH+6) x (TW+6) source window with reflection
-    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW + 6); i += 256) {
-        const int ry = i / (BLUR_TW + 6), rx = i - ry * (BLUR_TW + 6);
-        const int sy = reflect101(min(ty + ry - 3, G.h + 2), G.h);
-        const int sx = reflect101(min(tx + rx - 3, G.w + 2), G.w);
-        raw[ry][rx] = S[(size_t)sy * G.pitch + sx];
+    const int W = G.w, H = G.h;
+    for (int i = tid; i < (BLUR_TH + 6) * BLUR_RW; i += 256) {
+        const int ry = i / BLUR_RW, j = i - ry * BLUR_RW;
+        const int gy = reflect101(min(ty + ry - 3, H + 2), H);
+        const int gx = tx - 4 + 4 * j;
+        const uint8_t* row = S + (size_t)gy * G.pitch;
+        uint32_t v;
+        if (gx >= 0 && gx + 3 < W) v = *reinterpret_cast<const uint32_t*>(row + gx);
+        else {
+            v = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v |= (uint32_t)row[reflect101(min(gx + k, W + 2), W)] << (8 * k);
+        }
+        raw[ry][j] = v;
     }
     __syncthreads();
-    for (int i = tid; i < (BLUR_TH + 6) * BLUR_TW; i += 256) {
-        const int ry = i / BLUR_TW, rx = i - ry * BLUR_TW;
-        const uint8_t* r = &raw[ry][rx];
-        hor[ry][rx] = (uint16_t)(18 * (r[0] + r[6]) + 34 * (r[1] + r[5]) + 48 * (r[2] + r[4]) + 56 * r[3]);
-    }
-    __syncthreads();
-    // each thread: 4 adjacent columns of 4 rows
-    for (int i = tid; i < BLUR_TH * (BLUR_TW / 4); i += 256) {
-        const int oy = i / (BLUR_TW / 4), ox = (i - oy * (BLUR_TW / 4)) * 4;
-        if (ty + oy >= G.h || tx + ox >= G.w) continue;
-        uint32_t out = 0;
+    const int cx = tid & 31, r0 = (tid >> 5) * 8;
+    const int ox = tx + 4 * cx;
+    if (ox >= W || ty + r0 >= H) return;
+    const unsigned wA = 18u | (34u << 8) | (48u << 16) | (56u << 24), wB = 48u | (34u << 8) | (18u << 16);
+    uint32_t hs[7][4];
+#pragma unroll
+    for (int i = 0; i < 14; ++i) {
+        const uint32_t w0 = raw[r0 + i][cx], w1 = raw[r0 + i][cx + 1], w2 = raw[r0 + i][cx + 2];
+        uint32_t hn[4];
+        hn[0] = __dp4a(__byte_perm(w0, w1, 0x4321), wA, __dp4a(__byte_perm(w1, 0u, 0x4321), wB, 0u));
+        hn[1] = __dp4a(__byte_perm(w0, w1, 0x5432), wA, __dp4a(__byte_perm(w1, w2, 0x4432), wB, 0u));
+        hn[2] = __dp4a(__byte_perm(w0, w1, 0x6543), wA, __dp4a(__byte_perm(w1, w2, 0x5543), wB, 0u));
+        hn[3] = __dp4a(w1, wA, __dp4a(w2, wB, 0u));
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const uint32_t v = 18u * (hor[oy][ox + k] + hor[oy + 6][ox + k]) + 34u * (hor[oy + 1][ox + k] + hor[oy + 5][ox + k]) +
-                               48u * (hor[oy + 2][ox + k] + hor[oy + 4][ox + k]) + 56u * hor[oy + 3][ox + k];
-            out |= ((v + 32768u) >> 16) << (8 * k);
+#pragma unroll
+            for (int j = 0; j < 6; ++j) hs[j][k] = hs[j + 1][k];
+            hs[6][k] = hn[k];
         }
-        *reinterpret_cast<uint32_t*>(D + (size_t)(ty + oy) * G.pitch + tx + ox) = out;
+        if (i >= 6) {
+            const int oy = ty + r0 + i - 6;
+            if (oy < H) {
+                uint32_t out = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t v = 18u * (hs[0][k] + hs[6][k]) + 34u * (hs[1][k] + hs[5][k]) + 48u * (hs[2][k] + hs[4][k]) + 56u * hs[3][k];
+                    out |= ((v + 32768u) >> 16) << (8 * k);
+                }
+                *reinterpret_cast<uint32_t*>(D + (size_t)oy * G.pitch + ox) = out;
+            }
+        }
     }
 }
 
@@ -698,16 +753,18 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 #define OD_WARPS 8
+#define OD_PP 40  // pitch of the staged 37 x 37 descriptor patch
 __global__ void __launch_bounds__(OD_WARPS * 32)
 k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur, const uint32_t* __restrict__ lvl_kp,
                   const int* __restrict__ lvl_cnt, orb_keypoint* __restrict__ kps, uint8_t* __restrict__ desc,
                   int* __restrict__ counts, const Plan P) {
-    __shared__ signed char s_pat[1024];
-    reinterpret_cast<int*>(s_pat)[threadIdx.x] = reinterpret_cast<const int*>(c_pattern)[threadIdx.x];
+    __shared__ float2 s_pat[512];
+    __shared__ uint8_t s_patch[OD_WARPS][37 * OD_PP];
+    for (int i = threadIdx.x; i < 512; i += OD_WARPS * 32) s_pat[i] = make_float2((float)c_pattern[2 * i], (float)c_pattern[2 * i + 1]);
     __syncthreads();
     const int b = blockIdx.y;
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * OD_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slot = blockIdx.x * OD_WARPS + warp;
     const int* cnt = lvl_cnt + b * ORB_MAX_LEVELS;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         int t = 0;
@@ -725,17 +782,35 @@ k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ b
 
     const uint32_t key = lvl_kp[(size_t)b * P.kp_cap + slot];
     const int px = ORB_KEY_X(key) + ORB_WIN, py = ORB_KEY_Y(key) + ORB_WIN;
-    const uint8_t* img = pyr + G.off + (size_t)b * G.img_stride + (size_t)py * G.pitch + px;
+    const int pitch = G.pitch;
+    const uint8_t* img = pyr + G.off + (size_t)b * G.img_stride + (size_t)py * pitch + px;
+    const uint8_t* c = blur + G.off + (size_t)b * G.img_stride + (size_t)py * pitch + px;
 
-    // IC_Angle (reference :77-113): integer moments over the radius-15 disc, lane = row
+    // stage the 37 x 37 blurred patch (max |rotated offset| is 18): two row segments per row
+    uint8_t* sp = s_patch[warp];
+    {
+        const int c0 = lane - 18, c1 = lane + 14;
+#pragma unroll 4
+        for (int r = -18; r <= 18; ++r) {
+            const uint8_t* row = c + r * pitch;
+            sp[(r + 18) * OD_PP + lane] = row[c0];
+            if (lane < 5) sp[(r + 18) * OD_PP + 32 + lane] = row[c1];
+        }
+    }
+
+    // IC_Angle (reference :77-113): integer moments over the radius-15 disc; lane = column u
     int m10 = 0, m01 = 0;
-    if (lane < 31) {
-        const int v = lane - ORB_HALF_PATCH;
-        const int d = P.umax[v < 0 ? -v : v];
-        const uint8_t* r = img + v * G.pitch;
-        int rs = 0;
-        for (int u = -d; u <= d; ++u) { const int val = r[u]; m10 += u * val; rs += val; }
-        m01 = v * rs;
+    {
+        const int u = lane - ORB_HALF_PATCH;
+        const int au = u < 0 ? -u : u;
+#pragma unroll
+        for (int v = -ORB_HALF_PATCH; v <= ORB_HALF_PATCH; ++v) {
+            const int d = P.umax[v < 0 ? -v : v];
+            int val = 0;
+            if (lane < 31 && au <= d) val = img[v * pitch + u];
+            m10 += u * val;
+            m01 += v * val;
+        }
     }
 #pragma unroll
     for (int o = 16; o; o >>= 1) {
@@ -744,22 +819,21 @@ k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ b
     }
     const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-    // rBRIEF (reference :119-164): lane = descriptor byte, 8 comparisons
+    // rBRIEF (reference :119-164): lane = descriptor byte, 8 comparisons on the staged patch
     const float rad = __fmul_rn(angle, 0.017453292519943295f);  // factorPI = (float)(CV_PI/180.f)
     float a, bsin;
     orb_sincosf(rad, &bsin, &a);
-    const uint8_t* c = blur + G.off + (size_t)b * G.img_stride + (size_t)py * G.pitch + px;
+    __syncwarp();
+    const uint8_t* spc = sp + 18 * OD_PP + 18;
     int val = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const int i0 = (lane * 16 + 2 * k) * 2;
-        const float x0 = (float)s_pat[i0], y0 = (float)s_pat[i0 + 1];
-        const float x1 = (float)s_pat[i0 + 2], y1 = (float)s_pat[i0 + 3];
-        const int r0 = __float2int_rn(__fmaf_rn(x0, bsin, __fmul_rn(y0, a)));
-        const int q0 = __float2int_rn(__fmaf_rn(x0, a, -__fmul_rn(y0, bsin)));
-        const int r1 = __float2int_rn(__fmaf_rn(x1, bsin, __fmul_rn(y1, a)));
-        const int q1 = __float2int_rn(__fmaf_rn(x1, a, -__fmul_rn(y1, bsin)));
-        const int t0 = c[r0 * G.pitch + q0], t1 = c[r1 * G.pitch + q1];
+        const float2 p0 = s_pat[lane * 16 + 2 * k], p1 = s_pat[lane * 16 + 2 * k + 1];
+        const int r0 = __float2int_rn(__fmaf_rn(p0.x, bsin, __fmul_rn(p0.y, a)));
+        const int q0 = __float2int_rn(__fmaf_rn(p0.x, a, -__fmul_rn(p0.y, bsin)));
+        const int r1 = __float2int_rn(__fmaf_rn(p1.x, bsin, __fmul_rn(p1.y, a)));
+        const int q1 = __float2int_rn(__fmaf_rn(p1.x, a, -__fmul_rn(p1.y, bsin)));
+        const int t0 = spc[r0 * OD_PP + q0], t1 = spc[r1 * OD_PP + q1];
         val |= (t0 < t1) << k;
     }
     desc[((size_t)b * P.kp_cap + out_idx) * 32 + lane] = (uint8_t)val;

@@ -131,7 +131,7 @@ int build_plan(const orb_extractor& e, int w, int h, Plan& P, Needs& need, std::
             G.n_cols = G.n_rows = 0; G.w_cell = G.h_cell = 1; G.cell_cap = 0; G.n_ini = 1; G.h_x = 1.f; G.node_cap = 1;
         }
         G.tiles_x = (G.w + 127) / 128;
-        G.tiles_y = (G.h + 31) / 32;
+        G.tiles_y = (G.h + 63) / 64;
         cells += G.n_cols * G.n_rows;
         stage += (size_t)G.n_cols * G.n_rows * G.cell_cap;
         kp += G.node_cap;
@@ -139,7 +139,7 @@ int build_plan(const orb_extractor& e, int w, int h, Plan& P, Needs& need, std::
         off += G.img_stride;  // scaled by batch when laid out (levels are batch-major, see layout())
         ncap_max = std::max(ncap_max, G.node_cap);
         if (l > 0) {
-            tbytes += ((size_t)G.w * 8 + (size_t)G.h * 8 + 63) & ~(size_t)63;
+            tbytes += 4 * 64 + (((size_t)G.w + 3) & ~(size_t)3) * 8 + (size_t)G.h * 8 + 64;
             if (tabs) {
                 HostTables& T = (*tabs)[l];
                 axis_table(P.lv[l - 1].w, G.w, true, T.xofs, T.alpha);
@@ -200,11 +200,11 @@ int ensure_plan(orb_extractor* e, int w, int h, int batch) {
         LevelGeom& G = P.lv[l];
         const HostTables& T = tabs[l];
         uint8_t* base = (uint8_t*)e->d_tables;
-        G.xofs = (const int*)(base + o); std::memcpy(&blob[o], T.xofs.data(), (size_t)G.w * 4); o += (size_t)G.w * 4;
-        G.yofs = (const int*)(base + o); std::memcpy(&blob[o], T.yofs.data(), (size_t)G.h * 4); o += (size_t)G.h * 4;
-        G.alpha = (const short*)(base + o); std::memcpy(&blob[o], T.alpha.data(), (size_t)G.w * 4); o += (size_t)G.w * 4;
-        G.beta = (const short*)(base + o); std::memcpy(&blob[o], T.beta.data(), (size_t)G.h * 4); o += (size_t)G.h * 4;
-        o = (o + 63) & ~(size_t)63;
+        const size_t w4 = ((size_t)G.w + 3) & ~(size_t)3;   // int4 loads: pad to 4 entries, keep 64-byte alignment
+        G.xofs = (const int*)(base + o); std::memcpy(&blob[o], T.xofs.data(), (size_t)G.w * 4); o = (o + w4 * 4 + 63) & ~(size_t)63;
+        G.alpha = (const short*)(base + o); std::memcpy(&blob[o], T.alpha.data(), (size_t)G.w * 4); o = (o + w4 * 4 + 63) & ~(size_t)63;
+        G.yofs = (const int*)(base + o); std::memcpy(&blob[o], T.yofs.data(), (size_t)G.h * 4); o = (o + (size_t)G.h * 4 + 63) & ~(size_t)63;
+        G.beta = (const short*)(base + o); std::memcpy(&blob[o], T.beta.data(), (size_t)G.h * 4); o = (o + (size_t)G.h * 4 + 63) & ~(size_t)63;
     }
     ORB_CUDA(cudaStreamSynchronize(e->stream));
     ORB_CUDA(cudaMemcpyAsync(e->d_tables, blob.data(), o, cudaMemcpyHostToDevice, e->stream));

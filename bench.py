@@ -234,7 +234,11 @@ def run_ours(args):
     acc = {}
     n_prof = 3
     for _ in range(n_prof):
-        step_device()
+        # serialised (one handle at a time) so that the per-stage event times are not inflated by
+        # the other stream's kernels sharing the SMs
+        gl.extract_device(dl.data_ptr(), B, W, H); gl.sync()
+        gr.extract_device(dr.data_ptr(), B, W, H); gr.sync()
+        stereo.compute_stereo_matches_device(gl, gr, MBF, FX, 0.0, batch=B); gl.sync()
         sl_ms = gl.stage_ms(); sr_ms = gr.stage_ms()
         for k in sl_ms:
             acc[k] = acc.get(k, 0.0) + sl_ms[k] + (sr_ms[k] if not k.startswith("stereo") else 0.0)

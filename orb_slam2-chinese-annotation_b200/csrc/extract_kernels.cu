@@ -157,42 +157,45 @@ __global__ void __launch_bounds__(256) k_gauss7(const uint8_t* __restrict__ pyr,
 // iff s is strictly greater than the raw scores of its 8 neighbours inside the cell interior
 // (outside counts as 0).  The set of strict local maxima does not depend on th, so the
 // iniTh -> minTh retry only re-filters the same list.
+//
+// One CTA per cell.  Phases: (1) stage the cell view in shared memory, (2) cheap necessary test
+// at minTh on every interior pixel, survivors compacted, (3) exact score on dense warps with
+// 3-input min/max, (4) local-maximum map + counts, (5) ordered (row-major) write.
 #define FAST_THREADS 256
-__device__ __forceinline__ int fast_corner_score(const int v, const int (&p)[16], const int t) {
-    int d[25];
+#define FAST_WARPS (FAST_THREADS / 32)
+
+__device__ __forceinline__ int min3i(int a, int b, int c) { return min(min(a, b), c); }
+__device__ __forceinline__ int max3i(int a, int b, int c) { return max(max(a, b), c); }
+
+// max over the 16 arcs of 9 contiguous ring pixels of min(d) and of min(-d):  returns
+// max(bright, dark) - 1, the largest threshold at which the pixel is a FAST-9 corner.
+__device__ __forceinline__ int fast_corner_score(const int v, const int (&p)[16]) {
+    int d[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) d[k] = v - p[k];
+    int lo3[16], hi3[16];
 #pragma unroll
-    for (int k = 16; k < 25; ++k) d[k] = d[k - 16];
-    int a0 = t;
-#pragma unroll
-    for (int k = 0; k < 16; k += 2) {
-        int a = min(d[k + 1], d[k + 2]);
-        a = min(a, d[k + 3]); a = min(a, d[k + 4]); a = min(a, d[k + 5]);
-        a = min(a, d[k + 6]); a = min(a, d[k + 7]); a = min(a, d[k + 8]);
-        a0 = max(a0, min(a, d[k]));
-        a0 = max(a0, min(a, d[k + 9]));
+    for (int k = 0; k < 16; ++k) {
+        lo3[k] = min3i(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+        hi3[k] = max3i(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
     }
-    int b0 = -a0;
+    int bright = -512, dark = 512;
 #pragma unroll
-    for (int k = 0; k < 16; k += 2) {
-        int b = max(d[k + 1], d[k + 2]);
-        b = max(b, d[k + 3]); b = max(b, d[k + 4]); b = max(b, d[k + 5]);
-        b = max(b, d[k + 6]); b = max(b, d[k + 7]); b = max(b, d[k + 8]);
-        b0 = min(b0, max(b, d[k]));
-        b0 = min(b0, max(b, d[k + 9]));
+    for (int k = 0; k < 16; ++k) {
+        bright = max(bright, min3i(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]));
+        dark = min(dark, max3i(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]));
     }
-    return -b0 - 1;  // max(t, bright, dark) - 1
+    return max(bright, -dark) - 1;
 }
 
-// Dynamic shared memory: tile (tile_h x tile_p bytes) | scores ((ih+2) x (iw+2) bytes) | survivors (u16)
+// Dynamic shared memory: tile (th x tp bytes) | scores ((ih+2) x sp bytes) | local maxima (ih x iw bytes) | survivors (u16)
 __global__ void __launch_bounds__(FAST_THREADS)
 k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
-             const int smem_tile_bytes, const int smem_score_bytes) {
+             const int smem_tile_bytes, const int smem_score_bytes, const int smem_lm_bytes) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ int s_nsurv;
-    __shared__ int s_wcnt[FAST_THREADS / 32][2];
-    __shared__ int s_woff[FAST_THREADS / 32];
+    __shared__ int s_wcnt[FAST_WARPS][2];
+    __shared__ int s_woff[FAST_WARPS];
     __shared__ int s_sel;
 
     int l = 0;
@@ -216,59 +219,73 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
 
     uint8_t* tile = smem;
     uint8_t* sc = smem + smem_tile_bytes;
-    uint16_t* surv = reinterpret_cast<uint16_t*>(smem + smem_tile_bytes + smem_score_bytes);
+    uint8_t* lm = sc + smem_score_bytes;
+    uint16_t* surv = reinterpret_cast<uint16_t*>(lm + smem_lm_bytes);
     const int tp = G.w_cell + 6 + 2;  // tile pitch (>= tw)
     const int sp = iw + 2;            // score pitch
+    const int npix = iw * ih;
+    const unsigned magic = (1u << 20) / (unsigned)iw + 1u;  // i / iw == (i * magic) >> 20 for i < 2^20 / iw
+
+    // (1) stage: warp per row, lanes along x
     const uint8_t* S = pyr + G.off + (size_t)b * G.img_stride + (size_t)iniY * G.pitch + iniX;
-    for (int i = tid; i < tw * th; i += FAST_THREADS) {
-        const int y = i / tw, x = i - y * tw;
-        tile[y * tp + x] = S[(size_t)y * G.pitch + x];
+    for (int y = warp; y < th; y += FAST_WARPS) {
+        const uint8_t* row = S + (size_t)y * G.pitch;
+        for (int x = lane; x < tw; x += 32) tile[y * tp + x] = row[x];
     }
     for (int i = tid; i < (ih + 2) * sp; i += FAST_THREADS) sc[i] = 0;
     if (tid == 0) s_nsurv = 0;
     __syncthreads();
 
-    // phase 1: cheap necessary test at the LOWER threshold; survivors are compacted so that the
-    // exact score (phase 2) runs on dense warps
+    // (2) necessary test at the LOWER threshold: a 9-arc contains one pixel of every opposite pair
     const int t = P.min_th;
-    for (int base = 0; base < iw * ih; base += FAST_THREADS) {
+    for (int base = 0; base < npix; base += FAST_THREADS) {
         const int i = base + tid;
         bool pass = false;
-        if (i < iw * ih) {
-            const int y = i / iw, x = i - y * iw;
+        if (i < npix) {
+            const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
             const uint8_t* c = tile + (y + 3) * tp + x + 3;
             const int v = c[0], lo = v - t, hi = v + t;
-            const int p0 = c[3 * tp], p8 = c[-3 * tp], p4 = c[3], p12 = c[-3];
-            const int p2 = c[2 * tp + 2], p10 = c[-2 * tp - 2], p6 = c[-2 * tp + 2], p14 = c[2 * tp - 2];
-            const bool dark = (p0 < lo || p8 < lo) && (p4 < lo || p12 < lo) && (p2 < lo || p10 < lo) && (p6 < lo || p14 < lo);
-            const bool brt = (p0 > hi || p8 > hi) && (p4 > hi || p12 > hi) && (p2 > hi || p10 > hi) && (p6 > hi || p14 > hi);
-            pass = dark || brt;
+            const int p0 = c[3 * tp], p8 = c[-3 * tp];
+            bool dark = p0 < lo || p8 < lo, brt = p0 > hi || p8 > hi;
+            if (dark || brt) {
+                const int p4 = c[3], p12 = c[-3];
+                dark = dark && (p4 < lo || p12 < lo); brt = brt && (p4 > hi || p12 > hi);
+                if (dark || brt) {
+                    const int p2 = c[2 * tp + 2], p10 = c[-2 * tp - 2], p6 = c[-2 * tp + 2], p14 = c[2 * tp - 2];
+                    dark = dark && (p2 < lo || p10 < lo) && (p6 < lo || p14 < lo);
+                    brt = brt && (p2 > hi || p10 > hi) && (p6 > hi || p14 > hi);
+                    pass = dark || brt;
+                }
+            }
         }
         const unsigned m = __ballot_sync(0xffffffffu, pass);
-        int wbase = 0;
-        if (lane == 0 && m) wbase = atomicAdd(&s_nsurv, __popc(m));
-        wbase = __shfl_sync(0xffffffffu, wbase, 0);
-        if (pass) surv[wbase + __popc(m & ((1u << lane) - 1))] = (uint16_t)i;
+        if (m) {
+            int wbase = 0;
+            if (lane == 0) wbase = atomicAdd(&s_nsurv, __popc(m));
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            if (pass) surv[wbase + __popc(m & ((1u << lane) - 1))] = (uint16_t)i;
+        }
     }
     __syncthreads();
+
+    // (3) exact score of the survivors
     const int nsurv = s_nsurv;
     for (int k = tid; k < nsurv; k += FAST_THREADS) {
         const int i = surv[k];
-        const int y = i / iw, x = i - y * iw;
+        const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
         const uint8_t* c = tile + (y + 3) * tp + x + 3;
         int p[16];
         p[0] = c[3 * tp];          p[1] = c[3 * tp + 1];   p[2] = c[2 * tp + 2];   p[3] = c[tp + 3];
         p[4] = c[3];               p[5] = c[-tp + 3];      p[6] = c[-2 * tp + 2];  p[7] = c[-3 * tp + 1];
         p[8] = c[-3 * tp];         p[9] = c[-3 * tp - 1];  p[10] = c[-2 * tp - 2]; p[11] = c[-tp - 3];
         p[12] = c[-3];             p[13] = c[tp - 3];      p[14] = c[2 * tp - 2];  p[15] = c[3 * tp - 1];
-        const int s = fast_corner_score(c[0], p, t);
+        const int s = fast_corner_score(c[0], p);
         if (s >= t) sc[(y + 1) * sp + x + 1] = (uint8_t)s;
     }
     __syncthreads();
 
-    // phase 3: strict local maxima, ordered (row-major) compaction.  Each warp owns a contiguous
-    // run of pixels; pass A counts, pass B writes.
-    const int npix = iw * ih;
+    // (4) strict local maxima -> lm (score or 0); each warp owns a contiguous run of pixels so
+    // that the ordered write below needs a single cross-warp prefix
     const int per_warp = ((npix + FAST_THREADS - 1) / FAST_THREADS) * 32;  // multiple of 32
     const int w_begin = warp * per_warp, w_end = min(w_begin + per_warp, npix);
     int cnt_min = 0, cnt_ini = 0;
@@ -276,11 +293,12 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
         const int i = i0 + lane;
         int s = 0;
         if (i < w_end) {
-            const int y = i / iw, x = i - y * iw;
+            const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
             const uint8_t* q = sc + (y + 1) * sp + x + 1;
             s = q[0];
             if (s && !(s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] && s > q[sp - 1] && s > q[sp] && s > q[sp + 1]))
                 s = 0;
+            lm[i] = (uint8_t)s;
         }
         cnt_min += __popc(__ballot_sync(0xffffffffu, s != 0));
         cnt_ini += __popc(__ballot_sync(0xffffffffu, s >= P.ini_th));
@@ -289,32 +307,29 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
     __syncthreads();
     if (tid == 0) {
         int tot_ini = 0;
-        for (int w = 0; w < FAST_THREADS / 32; ++w) tot_ini += s_wcnt[w][1];
+        for (int w = 0; w < FAST_WARPS; ++w) tot_ini += s_wcnt[w][1];
         const int sel = tot_ini > 0 ? 1 : 0;  // empty at iniThFAST -> retry with minThFAST (:843-850)
         int run = 0;
-        for (int w = 0; w < FAST_THREADS / 32; ++w) { s_woff[w] = run; run += s_wcnt[w][sel]; }
+        for (int w = 0; w < FAST_WARPS; ++w) { s_woff[w] = run; run += s_wcnt[w][sel]; }
         s_sel = sel;
         *out_cnt = run;
     }
     __syncthreads();
+
+    // (5) ordered write of the selected list
+    if (s_wcnt[warp][s_sel] == 0) return;
     const int th_sel = s_sel ? P.ini_th : 1;
     uint32_t* out = stage + (size_t)b * P.stage_per_image + G.stage_off + (size_t)cell * G.cell_cap;
     int off = s_woff[warp];
+    const int kx0 = 3 + cj * G.w_cell, ky0 = 3 + ci * G.h_cell;  // window-relative coords of interior (0, 0)
     for (int i0 = w_begin; i0 < w_end; i0 += 32) {
         const int i = i0 + lane;
-        int s = 0, x = 0, y = 0;
-        if (i < w_end) {
-            y = i / iw; x = i - y * iw;
-            const uint8_t* q = sc + (y + 1) * sp + x + 1;
-            s = q[0];
-            if (s < th_sel || !(s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] && s > q[sp - 1] && s > q[sp] && s > q[sp + 1]))
-                s = 0;
-        }
+        int s = 0;
+        if (i < w_end) { s = lm[i]; if (s < th_sel) s = 0; }
         const unsigned m = __ballot_sync(0xffffffffu, s != 0);
         if (s) {
-            // window-relative level coordinates: cell-view coords + 3 + (j*wCell, i*hCell)
-            const int kx = x + 3 + cj * G.w_cell, ky = y + 3 + ci * G.h_cell;
-            out[off + __popc(m & ((1u << lane) - 1))] = ((uint32_t)s << 24) | ((uint32_t)ky << 12) | (uint32_t)kx;
+            const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
+            out[off + __popc(m & ((1u << lane) - 1))] = ((uint32_t)s << 24) | ((uint32_t)(y + ky0) << 12) | (uint32_t)(x + kx0);
         }
         off += __popc(m);
     }
@@ -760,7 +775,8 @@ k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ b
                   int* __restrict__ counts, const Plan P) {
     __shared__ float2 s_pat[512];
     __shared__ uint8_t s_patch[OD_WARPS][37 * OD_PP];
-    for (int i = threadIdx.x; i < 512; i += OD_WARPS * 32) s_pat[i] = make_float2((float)c_pattern[2 * i], (float)c_pattern[2 * i + 1]);
+    for (int i = threadIdx.x; i < 512; i += OD_WARPS * 32)  // point i = byte (i / 16), sample (i % 16); stored [sample][byte]: conflict-free
+        s_pat[(i & 15) * 32 + (i >> 4)] = make_float2((float)c_pattern[2 * i], (float)c_pattern[2 * i + 1]);
     __syncthreads();
     const int b = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -828,7 +844,7 @@ k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ b
     int val = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const float2 p0 = s_pat[lane * 16 + 2 * k], p1 = s_pat[lane * 16 + 2 * k + 1];
+        const float2 p0 = s_pat[(2 * k) * 32 + lane], p1 = s_pat[(2 * k + 1) * 32 + lane];
         const int r0 = __float2int_rn(__fmaf_rn(p0.x, bsin, __fmul_rn(p0.y, a)));
         const int q0 = __float2int_rn(__fmaf_rn(p0.x, a, -__fmul_rn(p0.y, bsin)));
         const int r1 = __float2int_rn(__fmaf_rn(p1.x, bsin, __fmul_rn(p1.y, a)));
@@ -860,7 +876,7 @@ void launch_gauss(cudaStream_t s, const uint8_t* pyr, uint8_t* blur, const Plan&
     dim3 grid(P.total_tiles, batch);
     k_gauss7<<<grid, 256, 0, s>>>(pyr, blur, P);
 }
-static void fast_smem(const Plan& P, int* tile_bytes, int* score_bytes, int* total) {
+static void fast_smem(const Plan& P, int* tile_bytes, int* score_bytes, int* lm_bytes, int* total) {
     int mt = 0, ms = 0, mv = 0;
     for (int l = 0; l < P.nlevels; ++l) {
         const LevelGeom& G = P.lv[l];
@@ -871,17 +887,18 @@ static void fast_smem(const Plan& P, int* tile_bytes, int* score_bytes, int* tot
     }
     *tile_bytes = (mt + 15) & ~15;
     *score_bytes = (ms + 15) & ~15;
-    *total = *tile_bytes + *score_bytes + 2 * mv + 16;
+    *lm_bytes = (mv + 15) & ~15;
+    *total = *tile_bytes + *score_bytes + *lm_bytes + 2 * mv + 16;
 }
 cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch) {
-    int tb, sb, tot;
-    fast_smem(P, &tb, &sb, &tot);
+    int tb, sb, lb, tot;
+    fast_smem(P, &tb, &sb, &lb, &tot);
     if (tot > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, tot);
         if (e != cudaSuccess) return e;
     }
     dim3 grid(P.total_cells, batch);
-    k_fast_cells<<<grid, FAST_THREADS, tot, s>>>(pyr, cell_cnt, stage, P, tb, sb);
+    k_fast_cells<<<grid, FAST_THREADS, tot, s>>>(pyr, cell_cnt, stage, P, tb, sb, lb);
     return cudaSuccess;
 }
 size_t quadtree_smem(int cap, int* p2_out) {

@@ -257,12 +257,13 @@ def run_ours(args):
     L = capi.lib()
 
     def step_host():
-        capi.check(L.orb_extract_batch(gl.handle, C.c_void_p(pl.data_ptr()), B, W, H, W, C.c_size_t(W * H), C.c_void_p(o_k[0].data_ptr()),
-                                       C.c_void_p(o_d[0].data_ptr()), cap, capi.ptr(o_n[0])))
-        capi.check(L.orb_extract_batch(gr.handle, C.c_void_p(pr.data_ptr()), B, W, H, W, C.c_size_t(W * H), C.c_void_p(o_k[1].data_ptr()),
-                                       C.c_void_p(o_d[1].data_ptr()), cap, capi.ptr(o_n[1])))
-        capi.check(L.orb_stereo_match_batch(gl.handle, gr.handle, B, C.c_float(MBF), C.c_float(0.0), C.c_float(FX),
-                                            C.c_void_p(o_u.data_ptr()), C.c_void_p(o_z.data_ptr()), cap, capi.ptr(o_n[2])))
+        # the call a user of the reference makes for a stereo frame: Frame::Frame(left, right, ...) =
+        # ExtractORB x2 + ComputeStereoMatches (src/Frame.cc:60-115), batched, host buffers in and out
+        capi.check(L.orb_stereo_frames(gl.handle, gr.handle, C.c_void_p(pl.data_ptr()), C.c_void_p(pr.data_ptr()), B, W, H, W,
+                                       C.c_size_t(W * H), C.c_float(MBF), C.c_float(0.0), C.c_float(FX),
+                                       C.c_void_p(o_k[0].data_ptr()), C.c_void_p(o_d[0].data_ptr()), capi.ptr(o_n[0]),
+                                       C.c_void_p(o_k[1].data_ptr()), C.c_void_p(o_d[1].data_ptr()), capi.ptr(o_n[1]),
+                                       C.c_void_p(o_u.data_ptr()), C.c_void_p(o_z.data_ptr()), cap))
 
     for _ in range(3):
         step_host()
@@ -278,7 +279,8 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e_val = world * B * e_steps / (float(t.item()) * 1e-3)
     h2d = 2 * B * W * H
-    d2h = int((o_n[0].sum() + o_n[1].sum()) * (kp_dt.itemsize + 32) + o_n[2].sum() * 8 + 3 * B * 4)
+    # slot rows are downloaded whole (cap == the handle's kp_cap here): keypoints + descriptors of both sides, uRight, depth, counts
+    d2h = int(B * cap * (2 * (kp_dt.itemsize + 32) + 8) + 2 * B * 4 + 8)
 
     if rank == 0:
         peaks = {}

@@ -117,6 +117,16 @@ int orb_stereo_match(orb_extractor* left, orb_extractor* right, int image, float
  * the device (d_u_right / d_depth: [batch][kp_cap] device buffers owned by `left`). */
 int orb_stereo_match_batch(orb_extractor* left, orb_extractor* right, int batch, float mbf, float min_d, float max_d,
                            float* u_right, float* depth, int cap, int32_t* n_left);
+/* The stereo Frame constructor (src/Frame.cc:60-115): ExtractORB on the left and right image
+ * (two threads in the reference, :81-84), then ComputeStereoMatches (:95), for a batch of stereo
+ * pairs held in HOST memory.  The batch is cut into chunks of image slots whose upload, kernels
+ * and download overlap on three streams.  Outputs as orb_extract_batch (per side) and
+ * orb_stereo_match_batch; all arrays are [batch][cap] and rows are written whole (the tail beyond
+ * n_l[b] / n_r[b] is unspecified).  Pinned host buffers are needed for the copies to overlap. */
+int orb_stereo_frames(orb_extractor* left, orb_extractor* right, const uint8_t* imgs_l, const uint8_t* imgs_r, int batch,
+                      int w, int h, int stride, size_t img_stride, float mbf, float min_d, float max_d,
+                      orb_keypoint* kps_l, uint8_t* desc_l, int32_t* n_l, orb_keypoint* kps_r, uint8_t* desc_r, int32_t* n_r,
+                      float* u_right, float* depth, int cap);
 int orb_stereo_match_device(orb_extractor* left, orb_extractor* right, int batch, float mbf, float min_d, float max_d);
 int orb_stereo_device_results(const orb_extractor* left, const float** d_u_right, const float** d_depth);
 

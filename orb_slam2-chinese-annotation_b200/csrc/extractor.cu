@@ -172,6 +172,9 @@ void free_buffers(orb_extractor* e) {
     for (int i = 0; i < ORB_N_STAGES + 4; ++i) if (e->ev_stage[i]) cudaEventDestroy(e->ev_stage[i]);
     if (e->h_pin) cudaFreeHost(e->h_pin);
     if (e->h_counts) cudaFreeHost(e->h_counts);
+    for (cudaEvent_t ev : e->ev_pool) cudaEventDestroy(ev);
+    if (e->s_h2d) cudaStreamDestroy(e->s_h2d);
+    if (e->s_d2h) cudaStreamDestroy(e->s_d2h);
     if (e->stream) cudaStreamDestroy(e->stream);
 }
 
@@ -214,8 +217,23 @@ int ensure_plan(orb_extractor* e, int w, int h, int batch) {
     return ORB_OK;
 }
 
-int run_pipeline(orb_extractor* e, int batch) {
-    Plan& P = e->plan;
+// Runs the extractor stages for image slots [b0, b0 + batch) of the handle's buffers (planned for
+// e->last_batch images) on e->stream.  Slot addressing is done on the host: level offsets and the
+// per-image arrays are shifted, the kernels always see "their" batch starting at 0.
+int run_pipeline(orb_extractor* e, int b0, int batch) {
+    Plan P = e->plan;
+    for (int l = 0; l < P.nlevels; ++l) P.lv[l].off += (unsigned long long)b0 * P.lv[l].img_stride;
+    const Plan& Q = e->plan;
+    int* cell_cnt = e->d_cell_cnt + (size_t)b0 * Q.total_cells;
+    int* cell_prefix = e->d_cell_prefix + (size_t)b0 * Q.total_cells;
+    uint32_t* stage = e->d_stage + (size_t)b0 * Q.stage_per_image;
+    uint32_t* keys = e->d_keys + (size_t)b0 * 2 * Q.stage_per_image;
+    uint32_t* lvl_kp = e->d_lvl_kp + (size_t)b0 * Q.kp_cap;
+    int* lvl_cnt = e->d_lvl_cnt + (size_t)b0 * ORB_MAX_LEVELS;
+    int* lvl_ncand = e->d_lvl_ncand + (size_t)b0 * ORB_MAX_LEVELS;
+    orb_keypoint* kps = e->d_kps + (size_t)b0 * Q.kp_cap;
+    uint8_t* desc = e->d_desc + (size_t)b0 * Q.kp_cap * 32;
+    int* counts = e->d_counts + b0;
     cudaStream_t s = e->stream;
     const bool T = e->timing;
     // event i is recorded BEFORE stage i; event 5 after the last extractor stage
@@ -223,21 +241,21 @@ int run_pipeline(orb_extractor* e, int batch) {
     for (int l = 1; l < P.nlevels; ++l) { launch_resize(s, e->d_pyr, P.lv[l - 1], P.lv[l], batch); e->launches++; }
     if (T) cudaEventRecord(e->ev_stage[1], s);
     if (P.total_cells > 0) {
-        ORB_CUDA(launch_fast(s, e->d_pyr, e->d_cell_cnt, e->d_stage, P, batch)); e->launches++;
+        ORB_CUDA(launch_fast(s, e->d_pyr, cell_cnt, stage, P, batch)); e->launches++;
     }
     if (T) cudaEventRecord(e->ev_stage[2], s);
-    ORB_CUDA(launch_quadtree(s, e->d_cell_cnt, e->d_cell_prefix, e->d_stage, e->d_keys, e->d_lvl_kp, e->d_lvl_cnt, e->d_lvl_ncand,
-                             e->d_status, P, batch));
+    ORB_CUDA(launch_quadtree(s, cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, e->d_status, P, batch));
     e->launches++;
     if (T) cudaEventRecord(e->ev_stage[3], s);
     launch_gauss(s, e->d_pyr, e->d_blur, P, batch); e->launches++;
     if (T) cudaEventRecord(e->ev_stage[4], s);
-    launch_orient_describe(s, e->d_pyr, e->d_blur, e->d_lvl_kp, e->d_lvl_cnt, e->d_kps, e->d_desc, e->d_counts, P, batch);
+    launch_orient_describe(s, e->d_pyr, e->d_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, batch);
     e->launches++;
     if (T) { cudaEventRecord(e->ev_stage[5], s); for (int i = 0; i < 5; ++i) e->stage_valid[i] = true; }
     ORB_CUDA(cudaGetLastError());
     return ORB_OK;
 }
+int run_pipeline(orb_extractor* e, int batch) { return run_pipeline(e, 0, batch); }
 
 int check_status(orb_extractor* e) {
     int st = 0;
@@ -252,6 +270,58 @@ int check_status(orb_extractor* e) {
 }
 
 }  // namespace
+
+// ---- slot-wise building blocks of the host-buffer entry points (shared with stereo.cu) ----
+int orb_ensure_plan(orb_extractor* e, int w, int h, int batch) { return ensure_plan(e, w, h, batch); }
+int orb_run_slots(orb_extractor* e, int b0, int n) { return run_pipeline(e, b0, n); }
+
+int orb_pipe_streams(orb_extractor* e) {
+    if (!e->s_h2d) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_h2d, cudaStreamNonBlocking));
+    if (!e->s_d2h) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_d2h, cudaStreamNonBlocking));
+    return ORB_OK;
+}
+cudaEvent_t orb_pool_event(orb_extractor* e, int i) {
+    while ((int)e->ev_pool.size() <= i) {
+        cudaEvent_t ev = nullptr;
+        if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        e->ev_pool.push_back(ev);
+    }
+    return e->ev_pool[i];
+}
+// Chunks are large enough to fill the GPU several times over and small enough that a batch has
+// ~8 of them in flight between the upload, kernel and download streams.
+int orb_chunk_size(int batch) {
+    if (batch <= 8) return batch;
+    const int c = (batch + 7) / 8;
+    return c < 8 ? 8 : c;
+}
+// Host images [b0, b0 + n) of a batch -> level 0 of the same slots.
+int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, int stride, size_t img_stride, cudaStream_t st) {
+    const LevelGeom& G0 = e->plan.lv[0];
+    uint8_t* dst = e->d_pyr + G0.off + (size_t)b0 * G0.img_stride;
+    const uint8_t* src = imgs + (size_t)b0 * img_stride;
+    if (img_stride == (size_t)stride * h && G0.img_stride == (unsigned long long)G0.pitch * h) {
+        ORB_CUDA(cudaMemcpy2DAsync(dst, G0.pitch, src, stride, w, (size_t)h * n, cudaMemcpyHostToDevice, st));
+    } else {
+        for (int b = 0; b < n; ++b)
+            ORB_CUDA(cudaMemcpy2DAsync(dst + (size_t)b * G0.img_stride, G0.pitch, src + (size_t)b * img_stride, stride, w, h, cudaMemcpyHostToDevice, st));
+    }
+    return ORB_OK;
+}
+// Results of slots [b0, b0 + n) -> the caller's [batch][cap] arrays; counts land in e->h_counts.
+// Whole slot rows are copied (one strided copy per array): the tail beyond counts[b] is unspecified.
+int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st) {
+    const int kc = e->plan.kp_cap;
+    const int m = cap < kc ? cap : kc;
+    ORB_CUDA(cudaMemcpyAsync(e->h_counts + b0, e->d_counts + b0, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (m > 0) {
+        ORB_CUDA(cudaMemcpy2DAsync(kps + (size_t)b0 * cap, (size_t)cap * sizeof(orb_keypoint), e->d_kps + (size_t)b0 * kc, (size_t)kc * sizeof(orb_keypoint),
+                                   (size_t)m * sizeof(orb_keypoint), n, cudaMemcpyDeviceToHost, st));
+        ORB_CUDA(cudaMemcpy2DAsync(desc + (size_t)b0 * cap * 32, (size_t)cap * 32, e->d_desc + (size_t)b0 * kc * 32, (size_t)kc * 32, (size_t)m * 32, n,
+                                   cudaMemcpyDeviceToHost, st));
+    }
+    return ORB_OK;
+}
 
 extern "C" {
 
@@ -441,13 +511,34 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, i
     ORB_CUDA(cudaSetDevice(e->device));
     int st = ensure_plan(e, w, h, batch);
     if (st != ORB_OK) return st;
-    const LevelGeom& G0 = e->plan.lv[0];
-    for (int b = 0; b < batch; ++b)
-        ORB_CUDA(cudaMemcpy2DAsync(e->d_pyr + G0.off + (size_t)b * G0.img_stride, G0.pitch, imgs + (size_t)b * img_stride, stride, w, h,
-                                   cudaMemcpyHostToDevice, e->stream));
-    st = run_pipeline(e, batch);
+    st = orb_pipe_streams(e);
     if (st != ORB_OK) return st;
-    return orb_extractor_download(e, batch, kps, desc, cap, counts);
+    const int chunk = orb_chunk_size(batch), nch = (batch + chunk - 1) / chunk;
+    if (!orb_pool_event(e, 2 * nch)) { orb_set_error("event"); return ORB_ERR_CUDA; }
+    // uploads must not overtake work already queued on the kernel stream
+    ORB_CUDA(cudaEventRecord(e->ev_pool[2 * nch], e->stream));
+    ORB_CUDA(cudaStreamWaitEvent(e->s_h2d, e->ev_pool[2 * nch], 0));
+    for (int c = 0; c < nch; ++c) {
+        const int b0 = c * chunk, n = batch - b0 < chunk ? batch - b0 : chunk;
+        st = orb_upload_slots(e, imgs, b0, n, w, h, stride, img_stride, e->s_h2d);
+        if (st != ORB_OK) return st;
+        ORB_CUDA(cudaEventRecord(e->ev_pool[2 * c], e->s_h2d));
+        ORB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_pool[2 * c], 0));
+        st = run_pipeline(e, b0, n);
+        if (st != ORB_OK) return st;
+        ORB_CUDA(cudaEventRecord(e->ev_pool[2 * c + 1], e->stream));
+        ORB_CUDA(cudaStreamWaitEvent(e->s_d2h, e->ev_pool[2 * c + 1], 0));
+        st = orb_download_slots(e, b0, n, kps, desc, cap, e->s_d2h);
+        if (st != ORB_OK) return st;
+    }
+    int dst = 0;
+    ORB_CUDA(cudaMemcpyAsync(&dst, e->d_status, sizeof(int), cudaMemcpyDeviceToHost, e->s_d2h));
+    ORB_CUDA(cudaStreamSynchronize(e->s_d2h));
+    if (dst != 0) { cudaMemsetAsync(e->d_status, 0, sizeof(int), e->stream); orb_set_error("device-side bound exceeded"); return dst; }
+    int rc = ORB_OK;
+    for (int b = 0; b < batch; ++b) { counts[b] = e->h_counts[b]; if (counts[b] > cap) rc = ORB_ERR_CAPACITY; }
+    if (rc != ORB_OK) orb_set_error("keypoint capacity too small");
+    return rc;
 }
 
 int orb_extract(orb_extractor* e, const uint8_t* img, int w, int h, int stride, orb_keypoint* kps, uint8_t* desc, int cap, int32_t* n) {

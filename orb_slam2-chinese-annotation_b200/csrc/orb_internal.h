@@ -104,6 +104,10 @@ struct orb_extractor {
     int* d_row_items = nullptr;     // [batch][row_items_cap]
     int row_items_cap = 0;
     cudaEvent_t ev_done = nullptr;
+    // host-buffer batches are cut into chunks of image slots: upload (s_h2d), kernels (stream) and
+    // download (s_d2h) of consecutive chunks overlap
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+    std::vector<cudaEvent_t> ev_pool;
     // optional per-stage event timing of the last pipeline run (bench.py roofline numbers)
     bool timing = false;
     cudaEvent_t ev_stage[ORB_N_STAGES + 4] = {nullptr};
@@ -115,6 +119,14 @@ struct orb_extractor {
 };
 
 void orb_set_error(const std::string& s);
+// slot-wise building blocks (extractor.cu) used by the chunk-pipelined host entry points
+int orb_ensure_plan(orb_extractor* e, int w, int h, int batch);
+int orb_run_slots(orb_extractor* e, int b0, int n);
+int orb_pipe_streams(orb_extractor* e);
+cudaEvent_t orb_pool_event(orb_extractor* e, int i);
+int orb_chunk_size(int batch);
+int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, int stride, size_t img_stride, cudaStream_t st);
+int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st);
 #define ORB_CUDA(call)                                                                      \
     do {                                                                                    \
         cudaError_t err__ = (call);                                                         \

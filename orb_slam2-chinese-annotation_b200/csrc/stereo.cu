@@ -214,8 +214,10 @@ k_stereo_median(const int* __restrict__ counts_l, float* __restrict__ u_right, f
     }
 }
 
-static int stereo_launch(orb_extractor* l, orb_extractor* r, int batch, float mbf, float min_d, float max_d) {
-    if (!l || !r || batch < 1 || l->plan_w < 0 || r->plan_w < 0 || batch > l->last_batch || batch > r->last_batch) return ORB_ERR_BAD_ARG;
+// Image slots [b0, b0 + batch) of the two handles' last batches.  fence_right: make later work on
+// the right stream wait for this stereo pass (needed when the next call reuses the same slots).
+static int stereo_launch(orb_extractor* l, orb_extractor* r, int b0, int batch, float mbf, float min_d, float max_d, bool fence_right = true) {
+    if (!l || !r || batch < 1 || b0 < 0 || l->plan_w < 0 || r->plan_w < 0 || b0 + batch > l->last_batch || b0 + batch > r->last_batch) return ORB_ERR_BAD_ARG;
     if (l->device != r->device || l->nlevels != r->nlevels || l->plan_w != r->plan_w || l->plan_h != r->plan_h) {
         orb_set_error("left and right extractor must share device, level count and image size");
         return ORB_ERR_BAD_ARG;
@@ -224,7 +226,14 @@ static int stereo_launch(orb_extractor* l, orb_extractor* r, int batch, float mb
     StereoGeom S;
     S.nlevels = l->nlevels; S.h0 = l->plan.lv[0].h; S.kp_cap_l = l->plan.kp_cap; S.kp_cap_r = r->plan.kp_cap;
     S.items_cap = l->row_items_cap;
-    for (int i = 0; i < l->nlevels; ++i) { S.sf[i] = l->sf[i]; S.inv_sf[i] = l->inv_sf[i]; S.lvl_l[i] = l->plan.lv[i]; S.lvl_r[i] = r->plan.lv[i]; }
+    for (int i = 0; i < l->nlevels; ++i) {
+        S.sf[i] = l->sf[i]; S.inv_sf[i] = l->inv_sf[i]; S.lvl_l[i] = l->plan.lv[i]; S.lvl_r[i] = r->plan.lv[i];
+        S.lvl_l[i].off += (unsigned long long)b0 * S.lvl_l[i].img_stride;
+        S.lvl_r[i].off += (unsigned long long)b0 * S.lvl_r[i].img_stride;
+    }
+    const size_t kl = (size_t)b0 * S.kp_cap_l, kr = (size_t)b0 * S.kp_cap_r;
+    int* row_start = l->d_row_start + (size_t)b0 * (ORB_MAX_DIM + 1);
+    int* row_items = l->d_row_items + (size_t)b0 * S.items_cap;
     // the right handle's stream must have finished producing its outputs
     ORB_CUDA(cudaEventRecord(r->ev_done, r->stream));
     ORB_CUDA(cudaStreamWaitEvent(l->stream, r->ev_done, 0));
@@ -232,20 +241,26 @@ static int stereo_launch(orb_extractor* l, orb_extractor* r, int batch, float mb
     if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_stereo_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const bool T = l->timing;
     if (T) cudaEventRecord(l->ev_stage[6], l->stream);
-    k_stereo_rows<<<batch, 512, smem, l->stream>>>(r->d_kps, r->d_counts, l->d_row_start, l->d_row_items, l->d_status, S);
+    k_stereo_rows<<<batch, 512, smem, l->stream>>>(r->d_kps + kr, r->d_counts + b0, row_start, row_items, l->d_status, S);
     if (T) cudaEventRecord(l->ev_stage[7], l->stream);
     dim3 grid((l->plan.kp_cap + SM_WARPS - 1) / SM_WARPS, batch);
-    k_stereo_match<<<grid, SM_WARPS * 32, 0, l->stream>>>(l->d_kps, l->d_desc, l->d_counts, r->d_kps, r->d_desc, l->d_pyr, r->d_pyr,
-                                                         l->d_row_start, l->d_row_items, l->d_u_right, l->d_depth, l->d_sad, S, mbf, min_d, max_d);
+    k_stereo_match<<<grid, SM_WARPS * 32, 0, l->stream>>>(l->d_kps + kl, l->d_desc + kl * 32, l->d_counts + b0, r->d_kps + kr, r->d_desc + kr * 32,
+                                                         l->d_pyr, r->d_pyr, row_start, row_items, l->d_u_right + kl, l->d_depth + kl,
+                                                         l->d_sad + kl, S, mbf, min_d, max_d);
     if (T) cudaEventRecord(l->ev_stage[8], l->stream);
-    k_stereo_median<<<batch, 512, 0, l->stream>>>(l->d_counts, l->d_u_right, l->d_depth, l->d_sad, l->plan.kp_cap);
+    k_stereo_median<<<batch, 512, 0, l->stream>>>(l->d_counts + b0, l->d_u_right + kl, l->d_depth + kl, l->d_sad + kl, l->plan.kp_cap);
     if (T) { cudaEventRecord(l->ev_stage[9], l->stream); l->stage_valid[5] = l->stage_valid[6] = l->stage_valid[7] = true; }
     l->launches += 3;
     ORB_CUDA(cudaGetLastError());
-    // later work on the right stream must not overwrite its buffers before we are done
-    ORB_CUDA(cudaEventRecord(l->ev_done, l->stream));
-    ORB_CUDA(cudaStreamWaitEvent(r->stream, l->ev_done, 0));
+    if (fence_right) {
+        // later work on the right stream must not overwrite its buffers before we are done
+        ORB_CUDA(cudaEventRecord(l->ev_done, l->stream));
+        ORB_CUDA(cudaStreamWaitEvent(r->stream, l->ev_done, 0));
+    }
     return ORB_OK;
+}
+static int stereo_launch(orb_extractor* l, orb_extractor* r, int batch, float mbf, float min_d, float max_d) {
+    return stereo_launch(l, r, 0, batch, mbf, min_d, max_d, true);
 }
 
 extern "C" {
@@ -282,6 +297,76 @@ int orb_stereo_match_batch(orb_extractor* l, orb_extractor* r, int batch, float 
     }
     ORB_CUDA(cudaStreamSynchronize(l->stream));
     if (rc != ORB_OK) orb_set_error("stereo output capacity too small");
+    return rc;
+}
+
+int orb_stereo_frames(orb_extractor* l, orb_extractor* r, const uint8_t* imgs_l, const uint8_t* imgs_r, int batch, int w, int h, int stride,
+                      size_t img_stride, float mbf, float min_d, float max_d, orb_keypoint* kps_l, uint8_t* desc_l, int32_t* n_l,
+                      orb_keypoint* kps_r, uint8_t* desc_r, int32_t* n_r, float* u_right, float* depth, int cap) {
+    if (!l || !r || l == r || batch < 0 || !n_l || !n_r) return ORB_ERR_BAD_ARG;
+    if (batch == 0) return ORB_OK;
+    if (w == 0 || h == 0) {  // empty images: no keypoints, nothing to match (reference src/ORBextractor.cc:1095)
+        for (int b = 0; b < batch; ++b) n_l[b] = n_r[b] = 0;
+        return ORB_OK;
+    }
+    if (!imgs_l || !imgs_r || !kps_l || !desc_l || !kps_r || !desc_r || !u_right || !depth || w < 0 || h < 0 || stride < w) return ORB_ERR_BAD_ARG;
+    if (l->device != r->device) { orb_set_error("left and right extractor must share a device"); return ORB_ERR_BAD_ARG; }
+    ORB_CUDA(cudaSetDevice(l->device));
+    int st = orb_ensure_plan(l, w, h, batch);
+    if (st == ORB_OK) st = orb_ensure_plan(r, w, h, batch);
+    if (st == ORB_OK) st = orb_pipe_streams(l);
+    if (st != ORB_OK) return st;
+    const int chunk = orb_chunk_size(batch), nch = (batch + chunk - 1) / chunk;
+    if (!orb_pool_event(l, 3 * nch + 1)) { orb_set_error("event"); return ORB_ERR_CUDA; }
+    // uploads must not overtake work already queued on the two kernel streams
+    ORB_CUDA(cudaEventRecord(l->ev_pool[3 * nch], l->stream));
+    ORB_CUDA(cudaEventRecord(l->ev_pool[3 * nch + 1], r->stream));
+    ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, l->ev_pool[3 * nch], 0));
+    ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, l->ev_pool[3 * nch + 1], 0));
+    const int kc = l->plan.kp_cap, m = cap < kc ? cap : kc;
+    for (int c = 0; c < nch; ++c) {
+        const int b0 = c * chunk, n = batch - b0 < chunk ? batch - b0 : chunk;
+        cudaEvent_t up_l = l->ev_pool[3 * c], up_r = l->ev_pool[3 * c + 1], done = l->ev_pool[3 * c + 2];
+        // Frame::Frame: ExtractORB(0, left) and ExtractORB(1, right) run side by side (src/Frame.cc:81-84) ...
+        if ((st = orb_upload_slots(l, imgs_l, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) return st;
+        ORB_CUDA(cudaEventRecord(up_l, l->s_h2d));
+        if ((st = orb_upload_slots(r, imgs_r, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) return st;
+        ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
+        ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
+        if ((st = orb_run_slots(l, b0, n)) != ORB_OK) return st;
+        ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
+        if ((st = orb_run_slots(r, b0, n)) != ORB_OK) return st;
+        // ... then ComputeStereoMatches (:95)
+        if ((st = stereo_launch(l, r, b0, n, mbf, min_d, max_d, false)) != ORB_OK) return st;
+        ORB_CUDA(cudaEventRecord(done, l->stream));
+        ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, done, 0));
+        if ((st = orb_download_slots(l, b0, n, kps_l, desc_l, cap, l->s_d2h)) != ORB_OK) return st;
+        if ((st = orb_download_slots(r, b0, n, kps_r, desc_r, cap, l->s_d2h)) != ORB_OK) return st;
+        if (m > 0) {
+            ORB_CUDA(cudaMemcpy2DAsync(u_right + (size_t)b0 * cap, (size_t)cap * 4, l->d_u_right + (size_t)b0 * kc, (size_t)kc * 4, (size_t)m * 4, n,
+                                       cudaMemcpyDeviceToHost, l->s_d2h));
+            ORB_CUDA(cudaMemcpy2DAsync(depth + (size_t)b0 * cap, (size_t)cap * 4, l->d_depth + (size_t)b0 * kc, (size_t)kc * 4, (size_t)m * 4, n,
+                                       cudaMemcpyDeviceToHost, l->s_d2h));
+        }
+    }
+    int st_l = 0, st_r = 0;
+    ORB_CUDA(cudaMemcpyAsync(&st_l, l->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->s_d2h));
+    ORB_CUDA(cudaMemcpyAsync(&st_r, r->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->s_d2h));
+    ORB_CUDA(cudaStreamSynchronize(l->s_d2h));
+    // the right stream has nothing queued beyond what the downloads waited for, but later calls on
+    // the right handle alone must see it idle
+    ORB_CUDA(cudaStreamSynchronize(r->stream));
+    if (st_l != 0 || st_r != 0) {
+        cudaMemsetAsync(l->d_status, 0, sizeof(int), l->stream); cudaMemsetAsync(r->d_status, 0, sizeof(int), r->stream);
+        orb_set_error("device-side bound exceeded");
+        return st_l ? st_l : st_r;
+    }
+    int rc = ORB_OK;
+    for (int b = 0; b < batch; ++b) {
+        n_l[b] = l->h_counts[b]; n_r[b] = r->h_counts[b];
+        if (n_l[b] > cap || n_r[b] > cap) rc = ORB_ERR_CAPACITY;
+    }
+    if (rc != ORB_OK) orb_set_error("keypoint capacity too small");
     return rc;
 }
 

@@ -6,7 +6,7 @@ function takes the handles plus the camera constants (mbf, and max_d = mbf / mb,
 reference computes from Frame::mb before it is assigned; pass fx for the upstream intent)."""
 import ctypes as C
 import numpy as np
-from .capi import check, lib, ptr
+from .capi import KP_DTYPE, check, lib, ptr
 
 
 def compute_stereo_matches(left, right, mbf, max_d, min_d=0.0, batch=1):
@@ -21,3 +21,27 @@ def compute_stereo_matches(left, right, mbf, max_d, min_d=0.0, batch=1):
 def compute_stereo_matches_device(left, right, mbf, max_d, min_d=0.0, batch=1):
     """Asynchronous; results stay in the left handle's device buffers."""
     check(lib().orb_stereo_match_device(left.handle, right.handle, batch, C.c_float(mbf), C.c_float(min_d), C.c_float(max_d)))
+
+
+def stereo_frames(left, right, images_l, images_r, mbf, max_d, min_d=0.0, out=None):
+    """The stereo Frame constructor (reference src/Frame.cc:60-115) for a batch of host image pairs
+    (B, H, W) uint8: ExtractORB left + right, then ComputeStereoMatches, chunk-pipelined on the
+    device.  -> dict(kps_l, desc_l, n_l, kps_r, desc_r, n_r, u_right, depth); arrays are
+    (B, cap, ...) and valid up to n_l[b] / n_r[b].  `out` may hold preallocated (pinned) arrays."""
+    images_l = np.ascontiguousarray(images_l, np.uint8); images_r = np.ascontiguousarray(images_r, np.uint8)
+    if images_l.shape != images_r.shape or images_l.ndim != 3:
+        raise ValueError("left/right batches must both be (B, H, W)")
+    B, H, W = images_l.shape
+    cap = left.kp_cap
+    o = out or {}
+    for k, shape, dt in (("kps_l", (B, cap), KP_DTYPE), ("desc_l", (B, cap, 32), np.uint8), ("n_l", (B,), np.int32),
+                         ("kps_r", (B, cap), KP_DTYPE), ("desc_r", (B, cap, 32), np.uint8), ("n_r", (B,), np.int32),
+                         ("u_right", (B, cap), np.float32), ("depth", (B, cap), np.float32)):
+        if k not in o:
+            o[k] = np.empty(shape, dt)
+    check(lib().orb_stereo_frames(left.handle, right.handle, ptr(images_l), ptr(images_r), B, W, H, images_l.strides[1],
+                                  C.c_size_t(images_l.strides[0]), C.c_float(mbf), C.c_float(min_d), C.c_float(max_d),
+                                  ptr(o["kps_l"]), ptr(o["desc_l"]), ptr(o["n_l"]), ptr(o["kps_r"]), ptr(o["desc_r"]), ptr(o["n_r"]),
+                                  ptr(o["u_right"]), ptr(o["depth"]), cap))
+    left._last = right._last = (B, W, H)
+    return o

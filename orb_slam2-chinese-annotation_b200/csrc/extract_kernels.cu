@@ -188,15 +188,18 @@ __device__ __forceinline__ int fast_corner_score(const int v, const int (&p)[16]
     return max(bright, -dark) - 1;
 }
 
-// Dynamic shared memory: tile (th x tp bytes) | scores ((ih+2) x sp bytes) | local maxima (ih x iw bytes) | survivors (u16)
+// Dynamic shared memory: tile (th x tp bytes, rows word-aligned like the level) | scores
+// ((ih+2) x sp bytes, zero frame) | survivors (u16 pixel index) | final list (u32: index << 8 | score)
+//
+// The reference runs FAST at iniThFAST and only when the post-NMS list of the cell is empty again
+// at minThFAST.  Same here: pass 0 tests, scores and suppresses at ini_th (few survivors); pass 1
+// runs only for cells that came out empty.  Suppression at threshold t compares against neighbour
+// scores that are themselves >= t, which is what the score map holds during that pass.
 __global__ void __launch_bounds__(FAST_THREADS)
 k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
-             const int smem_tile_bytes, const int smem_score_bytes, const int smem_lm_bytes) {
+             const int smem_tile_bytes, const int smem_score_bytes, const int smem_surv_bytes) {
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int s_nsurv;
-    __shared__ int s_wcnt[FAST_WARPS][2];
-    __shared__ int s_woff[FAST_WARPS];
-    __shared__ int s_sel;
+    __shared__ int s_nsurv, s_nfin;
 
     int l = 0;
     while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].cell_off) ++l;
@@ -217,121 +220,111 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
     const int iw = tw - 6, ih = th - 6;  // interior = tested pixels
     if (iw <= 0 || ih <= 0) { if (tid == 0) *out_cnt = 0; return; }
 
-    uint8_t* tile = smem;
     uint8_t* sc = smem + smem_tile_bytes;
-    uint8_t* lm = sc + smem_score_bytes;
-    uint16_t* surv = reinterpret_cast<uint16_t*>(lm + smem_lm_bytes);
-    const int tp = G.w_cell + 6 + 2;  // tile pitch (>= tw)
-    const int sp = iw + 2;            // score pitch
+    uint16_t* surv = reinterpret_cast<uint16_t*>(sc + smem_score_bytes);
+    uint32_t* fin = reinterpret_cast<uint32_t*>(sc + smem_score_bytes + smem_surv_bytes);
+    const int tpw = (G.w_cell + 6 + 3 + 3) >> 2, tp = tpw * 4;  // tile pitch in words / bytes
+    const int sp = iw + 2;                                     // score pitch
     const int npix = iw * ih;
     const unsigned magic = (1u << 20) / (unsigned)iw + 1u;  // i / iw == (i * magic) >> 20 for i < 2^20 / iw
 
-    // (1) stage: warp per row, lanes along x
-    const uint8_t* S = pyr + G.off + (size_t)b * G.img_stride + (size_t)iniY * G.pitch + iniX;
-    for (int y = warp; y < th; y += FAST_WARPS) {
-        const uint8_t* row = S + (size_t)y * G.pitch;
-        for (int x = lane; x < tw; x += 32) tile[y * tp + x] = row[x];
+    // (1) stage with aligned 32-bit loads: the tile keeps the level's word alignment (view starts at byte `shift`)
+    const int shift = iniX & 3;
+    {
+        const uint8_t* S = pyr + G.off + (size_t)b * G.img_stride + (size_t)iniY * G.pitch + (iniX - shift);
+        const int nw = (tw + shift + 3) >> 2;
+        uint32_t* tw32 = reinterpret_cast<uint32_t*>(smem);
+        const unsigned wmagic = (1u << 20) / (unsigned)nw + 1u;
+        for (int i = tid; i < nw * th; i += FAST_THREADS) {
+            const int y = (int)(((unsigned)i * wmagic) >> 20), x = i - y * nw;
+            tw32[y * tpw + x] = __ldg(reinterpret_cast<const uint32_t*>(S + (size_t)y * G.pitch) + x);
+        }
+        uint32_t* sc32 = reinterpret_cast<uint32_t*>(sc);
+        for (int i = tid; i < (((ih + 2) * sp + 3) >> 2); i += FAST_THREADS) sc32[i] = 0u;
     }
-    for (int i = tid; i < (ih + 2) * sp; i += FAST_THREADS) sc[i] = 0;
-    if (tid == 0) s_nsurv = 0;
-    __syncthreads();
+    const uint8_t* tile = smem + shift;
 
-    // (2) necessary test at the LOWER threshold: a 9-arc contains one pixel of every opposite pair
-    const int t = P.min_th;
-    for (int base = 0; base < npix; base += FAST_THREADS) {
-        const int i = base + tid;
-        bool pass = false;
-        if (i < npix) {
-            const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
-            const uint8_t* c = tile + (y + 3) * tp + x + 3;
-            const int v = c[0], lo = v - t, hi = v + t;
-            const int p0 = c[3 * tp], p8 = c[-3 * tp];
-            bool dark = p0 < lo || p8 < lo, brt = p0 > hi || p8 > hi;
-            if (dark || brt) {
-                const int p4 = c[3], p12 = c[-3];
-                dark = dark && (p4 < lo || p12 < lo); brt = brt && (p4 > hi || p12 > hi);
+    for (int pass = 0; pass < 2; ++pass) {
+        const int t = pass == 0 ? P.ini_th : P.min_th;
+        if (tid == 0) { s_nsurv = 0; s_nfin = 0; }
+        __syncthreads();
+
+        // (2) necessary test: a 9-arc contains one pixel of every opposite pair of the ring
+        for (int base = 0; base < npix; base += FAST_THREADS) {
+            const int i = base + tid;
+            bool pass_t = false;
+            if (i < npix) {
+                const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
+                const uint8_t* c = tile + (y + 3) * tp + x + 3;
+                const int v = c[0], lo = v - t, hi = v + t;
+                const int p0 = c[3 * tp], p8 = c[-3 * tp];
+                bool dark = p0 < lo || p8 < lo, brt = p0 > hi || p8 > hi;
                 if (dark || brt) {
-                    const int p2 = c[2 * tp + 2], p10 = c[-2 * tp - 2], p6 = c[-2 * tp + 2], p14 = c[2 * tp - 2];
-                    dark = dark && (p2 < lo || p10 < lo) && (p6 < lo || p14 < lo);
-                    brt = brt && (p2 > hi || p10 > hi) && (p6 > hi || p14 > hi);
-                    pass = dark || brt;
+                    const int p4 = c[3], p12 = c[-3];
+                    dark = dark && (p4 < lo || p12 < lo); brt = brt && (p4 > hi || p12 > hi);
+                    if (dark || brt) {
+                        const int p2 = c[2 * tp + 2], p10 = c[-2 * tp - 2], p6 = c[-2 * tp + 2], p14 = c[2 * tp - 2];
+                        dark = dark && (p2 < lo || p10 < lo) && (p6 < lo || p14 < lo);
+                        brt = brt && (p2 > hi || p10 > hi) && (p6 > hi || p14 > hi);
+                        pass_t = dark || brt;
+                    }
                 }
             }
+            const unsigned m = __ballot_sync(0xffffffffu, pass_t);
+            if (m) {
+                int wbase = 0;
+                if (lane == 0) wbase = atomicAdd(&s_nsurv, __popc(m));
+                wbase = __shfl_sync(0xffffffffu, wbase, 0);
+                if (pass_t) surv[wbase + __popc(m & ((1u << lane) - 1))] = (uint16_t)i;
+            }
         }
-        const unsigned m = __ballot_sync(0xffffffffu, pass);
-        if (m) {
-            int wbase = 0;
-            if (lane == 0) wbase = atomicAdd(&s_nsurv, __popc(m));
-            wbase = __shfl_sync(0xffffffffu, wbase, 0);
-            if (pass) surv[wbase + __popc(m & ((1u << lane) - 1))] = (uint16_t)i;
+        __syncthreads();
+
+        // (3) exact score of the survivors (dense warps); kept in a register for (4)
+        const int nsurv = s_nsurv;
+        if (nsurv == 0) { if (pass == 0) continue; break; }   // uniform: nothing can appear at this threshold
+        for (int k0 = 0; k0 < nsurv; k0 += FAST_THREADS) {
+            const int k = k0 + tid;
+            if (k < nsurv) {
+                const int i = surv[k];
+                const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
+                const uint8_t* c = tile + (y + 3) * tp + x + 3;
+                int p[16];
+                p[0] = c[3 * tp];          p[1] = c[3 * tp + 1];   p[2] = c[2 * tp + 2];   p[3] = c[tp + 3];
+                p[4] = c[3];               p[5] = c[-tp + 3];      p[6] = c[-2 * tp + 2];  p[7] = c[-3 * tp + 1];
+                p[8] = c[-3 * tp];         p[9] = c[-3 * tp - 1];  p[10] = c[-2 * tp - 2]; p[11] = c[-tp - 3];
+                p[12] = c[-3];             p[13] = c[tp - 3];      p[14] = c[2 * tp - 2];  p[15] = c[3 * tp - 1];
+                const int s = fast_corner_score(c[0], p);
+                if (s >= t) sc[(y + 1) * sp + x + 1] = (uint8_t)s;
+            }
         }
-    }
-    __syncthreads();
+        __syncthreads();
 
-    // (3) exact score of the survivors
-    const int nsurv = s_nsurv;
-    for (int k = tid; k < nsurv; k += FAST_THREADS) {
-        const int i = surv[k];
-        const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
-        const uint8_t* c = tile + (y + 3) * tp + x + 3;
-        int p[16];
-        p[0] = c[3 * tp];          p[1] = c[3 * tp + 1];   p[2] = c[2 * tp + 2];   p[3] = c[tp + 3];
-        p[4] = c[3];               p[5] = c[-tp + 3];      p[6] = c[-2 * tp + 2];  p[7] = c[-3 * tp + 1];
-        p[8] = c[-3 * tp];         p[9] = c[-3 * tp - 1];  p[10] = c[-2 * tp - 2]; p[11] = c[-tp - 3];
-        p[12] = c[-3];             p[13] = c[tp - 3];      p[14] = c[2 * tp - 2];  p[15] = c[3 * tp - 1];
-        const int s = fast_corner_score(c[0], p);
-        if (s >= t) sc[(y + 1) * sp + x + 1] = (uint8_t)s;
-    }
-    __syncthreads();
-
-    // (4) strict local maxima -> lm (score or 0); each warp owns a contiguous run of pixels so
-    // that the ordered write below needs a single cross-warp prefix
-    const int per_warp = ((npix + FAST_THREADS - 1) / FAST_THREADS) * 32;  // multiple of 32
-    const int w_begin = warp * per_warp, w_end = min(w_begin + per_warp, npix);
-    int cnt_min = 0, cnt_ini = 0;
-    for (int i0 = w_begin; i0 < w_end; i0 += 32) {
-        const int i = i0 + lane;
-        int s = 0;
-        if (i < w_end) {
+        // (4) strict local maxima among the survivors -> final list (unordered)
+        for (int k = tid; k < nsurv; k += FAST_THREADS) {
+            const int i = surv[k];
             const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
             const uint8_t* q = sc + (y + 1) * sp + x + 1;
-            s = q[0];
-            if (s && !(s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] && s > q[sp - 1] && s > q[sp] && s > q[sp + 1]))
-                s = 0;
-            lm[i] = (uint8_t)s;
+            const int s = q[0];
+            if (s >= t && s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] && s > q[sp - 1] && s > q[sp] && s > q[sp + 1])
+                fin[atomicAdd(&s_nfin, 1)] = ((uint32_t)i << 8) | (uint32_t)s;
         }
-        cnt_min += __popc(__ballot_sync(0xffffffffu, s != 0));
-        cnt_ini += __popc(__ballot_sync(0xffffffffu, s >= P.ini_th));
+        __syncthreads();
+        if (s_nfin > 0) break;   // uniform.  Empty at iniThFAST -> retry with minThFAST (:843-850)
     }
-    if (lane == 0) { s_wcnt[warp][0] = cnt_min; s_wcnt[warp][1] = cnt_ini; }
-    __syncthreads();
-    if (tid == 0) {
-        int tot_ini = 0;
-        for (int w = 0; w < FAST_WARPS; ++w) tot_ini += s_wcnt[w][1];
-        const int sel = tot_ini > 0 ? 1 : 0;  // empty at iniThFAST -> retry with minThFAST (:843-850)
-        int run = 0;
-        for (int w = 0; w < FAST_WARPS; ++w) { s_woff[w] = run; run += s_wcnt[w][sel]; }
-        s_sel = sel;
-        *out_cnt = run;
-    }
-    __syncthreads();
 
-    // (5) ordered write of the selected list
-    if (s_wcnt[warp][s_sel] == 0) return;
-    const int th_sel = s_sel ? P.ini_th : 1;
+    // (5) ordered write: rank of a keypoint = number of keypoints at a smaller row-major index
+    const int nfin = s_nfin;
+    if (tid == 0) *out_cnt = nfin;
     uint32_t* out = stage + (size_t)b * P.stage_per_image + G.stage_off + (size_t)cell * G.cell_cap;
-    int off = s_woff[warp];
     const int kx0 = 3 + cj * G.w_cell, ky0 = 3 + ci * G.h_cell;  // window-relative coords of interior (0, 0)
-    for (int i0 = w_begin; i0 < w_end; i0 += 32) {
-        const int i = i0 + lane;
-        int s = 0;
-        if (i < w_end) { s = lm[i]; if (s < th_sel) s = 0; }
-        const unsigned m = __ballot_sync(0xffffffffu, s != 0);
-        if (s) {
-            const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
-            out[off + __popc(m & ((1u << lane) - 1))] = ((uint32_t)s << 24) | ((uint32_t)(y + ky0) << 12) | (uint32_t)(x + kx0);
-        }
-        off += __popc(m);
+    for (int k = tid; k < nfin; k += FAST_THREADS) {
+        const uint32_t e = fin[k];
+        int rank = 0;
+        for (int j = 0; j < nfin; ++j) rank += fin[j] < e;
+        const int i = (int)(e >> 8), s = (int)(e & 0xffu);
+        const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
+        out[rank] = ((uint32_t)s << 24) | ((uint32_t)(y + ky0) << 12) | (uint32_t)(x + kx0);
     }
 }
 
@@ -876,29 +869,30 @@ void launch_gauss(cudaStream_t s, const uint8_t* pyr, uint8_t* blur, const Plan&
     dim3 grid(P.total_tiles, batch);
     k_gauss7<<<grid, 256, 0, s>>>(pyr, blur, P);
 }
-static void fast_smem(const Plan& P, int* tile_bytes, int* score_bytes, int* lm_bytes, int* total) {
-    int mt = 0, ms = 0, mv = 0;
+static void fast_smem(const Plan& P, int* tile_bytes, int* score_bytes, int* surv_bytes, int* total) {
+    int mt = 0, ms = 0, mv = 0, mf = 0;
     for (int l = 0; l < P.nlevels; ++l) {
         const LevelGeom& G = P.lv[l];
-        const int tp = G.w_cell + 8, th = G.h_cell + 6;
+        const int tp = ((G.w_cell + 6 + 3 + 3) >> 2) * 4, th = G.h_cell + 6;
         mt = max(mt, tp * th);
         ms = max(ms, (G.w_cell + 2) * (G.h_cell + 2));
         mv = max(mv, G.w_cell * G.h_cell);
+        mf = max(mf, G.cell_cap);
     }
     *tile_bytes = (mt + 15) & ~15;
     *score_bytes = (ms + 15) & ~15;
-    *lm_bytes = (mv + 15) & ~15;
-    *total = *tile_bytes + *score_bytes + *lm_bytes + 2 * mv + 16;
+    *surv_bytes = (2 * mv + 15) & ~15;
+    *total = *tile_bytes + *score_bytes + *surv_bytes + 4 * mf + 16;
 }
 cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch) {
-    int tb, sb, lb, tot;
-    fast_smem(P, &tb, &sb, &lb, &tot);
+    int tb, sb, vb, tot;
+    fast_smem(P, &tb, &sb, &vb, &tot);
     if (tot > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, tot);
         if (e != cudaSuccess) return e;
     }
     dim3 grid(P.total_cells, batch);
-    k_fast_cells<<<grid, FAST_THREADS, tot, s>>>(pyr, cell_cnt, stage, P, tb, sb, lb);
+    k_fast_cells<<<grid, FAST_THREADS, tot, s>>>(pyr, cell_cnt, stage, P, tb, sb, vb);
     return cudaSuccess;
 }
 size_t quadtree_smem(int cap, int* p2_out) {

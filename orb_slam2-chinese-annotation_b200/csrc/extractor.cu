@@ -167,7 +167,7 @@ void free_buffers(orb_extractor* e) {
     cudaFree(e->d_pyr); cudaFree(e->d_blur); cudaFree(e->d_cell_cnt); cudaFree(e->d_cell_prefix); cudaFree(e->d_stage);
     cudaFree(e->d_keys); cudaFree(e->d_lvl_kp); cudaFree(e->d_lvl_cnt); cudaFree(e->d_lvl_ncand); cudaFree(e->d_kps);
     cudaFree(e->d_desc); cudaFree(e->d_counts); cudaFree(e->d_status); cudaFree(e->d_tables); cudaFree(e->d_u_right);
-    cudaFree(e->d_depth); cudaFree(e->d_sad); cudaFree(e->d_row_start); cudaFree(e->d_row_items);
+    cudaFree(e->d_depth); cudaFree(e->d_sad); cudaFree(e->d_in); cudaFree(e->d_row_start); cudaFree(e->d_row_items);
     if (e->ev_done) cudaEventDestroy(e->ev_done);
     for (int i = 0; i < ORB_N_STAGES + 4; ++i) if (e->ev_stage[i]) cudaEventDestroy(e->ev_stage[i]);
     if (e->h_pin) cudaFreeHost(e->h_pin);
@@ -278,6 +278,8 @@ int orb_run_slots(orb_extractor* e, int b0, int n) { return run_pipeline(e, b0, 
 int orb_pipe_streams(orb_extractor* e) {
     if (!e->s_h2d) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_h2d, cudaStreamNonBlocking));
     if (!e->s_d2h) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_d2h, cudaStreamNonBlocking));
+    if (!e->d_in && e->max_batch > 1 && !getenv("ORB_B200_NO_STAGING"))
+        ORB_CUDA(cudaMalloc((void**)&e->d_in, (size_t)e->max_batch * e->max_w * e->max_h));
     return ORB_OK;
 }
 cudaEvent_t orb_pool_event(orb_extractor* e, int i) {
@@ -300,7 +302,13 @@ int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w
     const LevelGeom& G0 = e->plan.lv[0];
     uint8_t* dst = e->d_pyr + G0.off + (size_t)b0 * G0.img_stride;
     const uint8_t* src = imgs + (size_t)b0 * img_stride;
-    if (img_stride == (size_t)stride * h && G0.img_stride == (unsigned long long)G0.pitch * h) {
+    if (img_stride == (size_t)stride * h && stride == w && e->d_in && G0.img_stride == (unsigned long long)G0.pitch * h) {
+        // dense host batch: one linear copy at full PCIe rate into the staging area, then an on-device
+        // strided copy into the pitched level-0 slots (a strided host->device copy of w-byte rows is DMA-descriptor bound)
+        uint8_t* stg = e->d_in + (size_t)b0 * w * h;
+        ORB_CUDA(cudaMemcpyAsync(stg, src, (size_t)n * w * h, cudaMemcpyHostToDevice, st));
+        ORB_CUDA(cudaMemcpy2DAsync(dst, G0.pitch, stg, w, w, (size_t)h * n, cudaMemcpyDeviceToDevice, st));
+    } else if (img_stride == (size_t)stride * h && G0.img_stride == (unsigned long long)G0.pitch * h) {
         ORB_CUDA(cudaMemcpy2DAsync(dst, G0.pitch, src, stride, w, (size_t)h * n, cudaMemcpyHostToDevice, st));
     } else {
         for (int b = 0; b < n; ++b)

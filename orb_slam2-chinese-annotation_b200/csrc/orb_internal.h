@@ -108,6 +108,7 @@ struct orb_extractor {
     // download (s_d2h) of consecutive chunks overlap
     cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
     std::vector<cudaEvent_t> ev_pool;
+    uint8_t* d_in = nullptr;        // dense upload staging [max_batch][max_w * max_h]
     // optional per-stage event timing of the last pipeline run (bench.py roofline numbers)
     bool timing = false;
     cudaEvent_t ev_stage[ORB_N_STAGES + 4] = {nullptr};

@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(256) k_gauss7(const uint8_t* __restrict__ pyr,
 // One CTA per cell.  Phases: (1) stage the cell view in shared memory, (2) cheap necessary test
 // at minTh on every interior pixel, survivors compacted, (3) exact score on dense warps with
 // 3-input min/max, (4) local-maximum map + counts, (5) ordered (row-major) write.
-#define FAST_THREADS 256
+#define FAST_THREADS 128
 #define FAST_WARPS (FAST_THREADS / 32)
 
 __device__ __forceinline__ int min3i(int a, int b, int c) { return min(min(a, b), c); }
@@ -189,17 +189,26 @@ __device__ __forceinline__ int fast_corner_score(const int v, const int (&p)[16]
 }
 
 // Dynamic shared memory: tile (th x tp bytes, rows word-aligned like the level) | scores
-// ((ih+2) x sp bytes, zero frame) | survivors (u16 pixel index) | final list (u32: index << 8 | score)
+// ((ih+2) x sp bytes, zero frame) | list A (u16 pixel index) | list B (u16) | final list (u32: index << 8 | score)
 //
 // The reference runs FAST at iniThFAST and only when the post-NMS list of the cell is empty again
 // at minThFAST.  Same here: pass 0 tests, scores and suppresses at ini_th (few survivors); pass 1
 // runs only for cells that came out empty.  Suppression at threshold t compares against neighbour
 // scores that are themselves >= t, which is what the score map holds during that pass.
+//
+// Per pass: (A) byte-SIMD necessary test on 4 pixels per thread: both ring pixels of the vertical
+// pair (1, 9) and of the horizontal pair (5, 13) within t of the centre => no 9-arc; (B) scalar
+// test with polarity on all four axis/diagonal pairs; (C) exact score; (D) 3x3 suppression.
+// Each stage works on the compacted survivors of the previous one.
+__device__ __forceinline__ unsigned gt_bytes(unsigned ad, unsigned k) {  // bit 7 of byte j set <=> ad.j > 127 - k.j  (k.j <= 127)
+    return ad | ((ad & 0x7f7f7f7fu) + k);
+}
+
 __global__ void __launch_bounds__(FAST_THREADS)
 k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
              const int smem_tile_bytes, const int smem_score_bytes, const int smem_surv_bytes) {
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int s_nsurv, s_nfin;
+    __shared__ int s_na, s_nb, s_nfin;
 
     int l = 0;
     while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].cell_off) ++l;
@@ -207,7 +216,7 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
     const int cell = blockIdx.x - G.cell_off;
     const int ci = cell / G.n_cols, cj = cell - ci * G.n_cols;
     const int b = blockIdx.y;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     int* out_cnt = cell_cnt + (size_t)b * P.total_cells + blockIdx.x;
 
     // cell view [iniX, maxX) x [iniY, maxY) (reference :819-839)
@@ -221,19 +230,19 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
     if (iw <= 0 || ih <= 0) { if (tid == 0) *out_cnt = 0; return; }
 
     uint8_t* sc = smem + smem_tile_bytes;
-    uint16_t* surv = reinterpret_cast<uint16_t*>(sc + smem_score_bytes);
-    uint32_t* fin = reinterpret_cast<uint32_t*>(sc + smem_score_bytes + smem_surv_bytes);
+    uint16_t* list_a = reinterpret_cast<uint16_t*>(sc + smem_score_bytes);
+    uint16_t* list_b = reinterpret_cast<uint16_t*>(sc + smem_score_bytes + smem_surv_bytes);
+    uint32_t* fin = reinterpret_cast<uint32_t*>(sc + smem_score_bytes + 2 * smem_surv_bytes);
     const int tpw = (G.w_cell + 6 + 3 + 3) >> 2, tp = tpw * 4;  // tile pitch in words / bytes
     const int sp = iw + 2;                                     // score pitch
-    const int npix = iw * ih;
     const unsigned magic = (1u << 20) / (unsigned)iw + 1u;  // i / iw == (i * magic) >> 20 for i < 2^20 / iw
 
     // (1) stage with aligned 32-bit loads: the tile keeps the level's word alignment (view starts at byte `shift`)
     const int shift = iniX & 3;
+    uint32_t* tw32 = reinterpret_cast<uint32_t*>(smem);
     {
         const uint8_t* S = pyr + G.off + (size_t)b * G.img_stride + (size_t)iniY * G.pitch + (iniX - shift);
         const int nw = (tw + shift + 3) >> 2;
-        uint32_t* tw32 = reinterpret_cast<uint32_t*>(smem);
         const unsigned wmagic = (1u << 20) / (unsigned)nw + 1u;
         for (int i = tid; i < nw * th; i += FAST_THREADS) {
             const int y = (int)(((unsigned)i * wmagic) >> 20), x = i - y * nw;
@@ -243,66 +252,102 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
         for (int i = tid; i < (((ih + 2) * sp + 3) >> 2); i += FAST_THREADS) sc32[i] = 0u;
     }
     const uint8_t* tile = smem + shift;
+    // interior words of a row: word wx holds interior pixels xi = 4 * wx - shift - 3 + k, k = 0..3
+    const int w0 = (shift + 3) >> 2, nwi = ((shift + 3 + iw - 1) >> 2) - w0 + 1;
+    const unsigned gmagic = (1u << 20) / (unsigned)nwi + 1u;
+    const int ngroups = nwi * ih;
 
     for (int pass = 0; pass < 2; ++pass) {
         const int t = pass == 0 ? P.ini_th : P.min_th;
-        if (tid == 0) { s_nsurv = 0; s_nfin = 0; }
+        if (tid == 0) { s_na = 0; s_nb = 0; s_nfin = 0; }
         __syncthreads();
 
-        // (2) necessary test: a 9-arc contains one pixel of every opposite pair of the ring
-        for (int base = 0; base < npix; base += FAST_THREADS) {
-            const int i = base + tid;
+        // (A) 4 pixels per thread
+        const unsigned kk = (unsigned)(127 - min(t, 126)) * 0x01010101u;
+        for (int base = 0; base < ngroups; base += FAST_THREADS) {
+            const int g = base + tid;
+            unsigned m = 0;
+            int i0 = 0;
+            if (g < ngroups) {
+                const int y = (int)(((unsigned)g * gmagic) >> 20), wx = w0 + (g - y * nwi);
+                const uint32_t* c = tw32 + (y + 3) * tpw + wx;
+                const unsigned C = c[0], N = c[-3 * tpw], S = c[3 * tpw], L = c[-1], R = c[1];
+                const unsigned E = __byte_perm(C, R, 0x6543), Wp = __byte_perm(L, C, 0x4321);  // x + 3, x - 3
+                const unsigned pv = gt_bytes(__vabsdiffu4(N, C), kk) | gt_bytes(__vabsdiffu4(S, C), kk);
+                const unsigned ph = gt_bytes(__vabsdiffu4(E, C), kk) | gt_bytes(__vabsdiffu4(Wp, C), kk);
+                const int xi0 = 4 * wx - shift - 3;
+                unsigned valid = 0x80808080u;
+                if (xi0 < 0) valid &= 0xffffffffu << (8 * -xi0);
+                if (xi0 + 4 > iw) valid &= 0xffffffffu >> (8 * (xi0 + 4 - iw));
+                m = pv & ph & valid;
+                i0 = y * iw + xi0;
+            }
+            const int cnt = __popc(m);
+            const unsigned b1 = __ballot_sync(0xffffffffu, cnt >= 1);
+            if (b1) {
+                const unsigned b2 = __ballot_sync(0xffffffffu, cnt >= 2), b3 = __ballot_sync(0xffffffffu, cnt >= 3),
+                               b4 = __ballot_sync(0xffffffffu, cnt >= 4);
+                int wbase = 0;
+                if (lane == 0) wbase = atomicAdd(&s_na, __popc(b1) + __popc(b2) + __popc(b3) + __popc(b4));
+                wbase = __shfl_sync(0xffffffffu, wbase, 0);
+                const unsigned lt = (1u << lane) - 1;
+                int o = wbase + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt) + __popc(b4 & lt);
+                if (m & 0x80u) list_a[o++] = (uint16_t)i0;
+                if (m & 0x8000u) list_a[o++] = (uint16_t)(i0 + 1);
+                if (m & 0x800000u) list_a[o++] = (uint16_t)(i0 + 2);
+                if (m & 0x80000000u) list_a[o++] = (uint16_t)(i0 + 3);
+            }
+        }
+        __syncthreads();
+        const int na = s_na;
+        if (na == 0) { if (pass == 0) continue; break; }   // uniform: nothing can appear at this threshold
+
+        // (B) necessary test with polarity: a 9-arc contains one pixel of every opposite pair of the ring
+        for (int base = 0; base < na; base += FAST_THREADS) {
+            const int k = base + tid;
             bool pass_t = false;
-            if (i < npix) {
+            int i = 0;
+            if (k < na) {
+                i = list_a[k];
                 const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
                 const uint8_t* c = tile + (y + 3) * tp + x + 3;
                 const int v = c[0], lo = v - t, hi = v + t;
-                const int p0 = c[3 * tp], p8 = c[-3 * tp];
-                bool dark = p0 < lo || p8 < lo, brt = p0 > hi || p8 > hi;
-                if (dark || brt) {
-                    const int p4 = c[3], p12 = c[-3];
-                    dark = dark && (p4 < lo || p12 < lo); brt = brt && (p4 > hi || p12 > hi);
-                    if (dark || brt) {
-                        const int p2 = c[2 * tp + 2], p10 = c[-2 * tp - 2], p6 = c[-2 * tp + 2], p14 = c[2 * tp - 2];
-                        dark = dark && (p2 < lo || p10 < lo) && (p6 < lo || p14 < lo);
-                        brt = brt && (p2 > hi || p10 > hi) && (p6 > hi || p14 > hi);
-                        pass_t = dark || brt;
-                    }
-                }
+                const int p0 = c[3 * tp], p8 = c[-3 * tp], p4 = c[3], p12 = c[-3];
+                const int p2 = c[2 * tp + 2], p10 = c[-2 * tp - 2], p6 = c[-2 * tp + 2], p14 = c[2 * tp - 2];
+                const bool dark = (p0 < lo || p8 < lo) && (p4 < lo || p12 < lo) && (p2 < lo || p10 < lo) && (p6 < lo || p14 < lo);
+                const bool brt = (p0 > hi || p8 > hi) && (p4 > hi || p12 > hi) && (p2 > hi || p10 > hi) && (p6 > hi || p14 > hi);
+                pass_t = dark || brt;
             }
             const unsigned m = __ballot_sync(0xffffffffu, pass_t);
             if (m) {
                 int wbase = 0;
-                if (lane == 0) wbase = atomicAdd(&s_nsurv, __popc(m));
+                if (lane == 0) wbase = atomicAdd(&s_nb, __popc(m));
                 wbase = __shfl_sync(0xffffffffu, wbase, 0);
-                if (pass_t) surv[wbase + __popc(m & ((1u << lane) - 1))] = (uint16_t)i;
+                if (pass_t) list_b[wbase + __popc(m & ((1u << lane) - 1))] = (uint16_t)i;
             }
         }
         __syncthreads();
+        const int nb = s_nb;
+        if (nb == 0) { if (pass == 0) continue; break; }
 
-        // (3) exact score of the survivors (dense warps); kept in a register for (4)
-        const int nsurv = s_nsurv;
-        if (nsurv == 0) { if (pass == 0) continue; break; }   // uniform: nothing can appear at this threshold
-        for (int k0 = 0; k0 < nsurv; k0 += FAST_THREADS) {
-            const int k = k0 + tid;
-            if (k < nsurv) {
-                const int i = surv[k];
-                const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
-                const uint8_t* c = tile + (y + 3) * tp + x + 3;
-                int p[16];
-                p[0] = c[3 * tp];          p[1] = c[3 * tp + 1];   p[2] = c[2 * tp + 2];   p[3] = c[tp + 3];
-                p[4] = c[3];               p[5] = c[-tp + 3];      p[6] = c[-2 * tp + 2];  p[7] = c[-3 * tp + 1];
-                p[8] = c[-3 * tp];         p[9] = c[-3 * tp - 1];  p[10] = c[-2 * tp - 2]; p[11] = c[-tp - 3];
-                p[12] = c[-3];             p[13] = c[tp - 3];      p[14] = c[2 * tp - 2];  p[15] = c[3 * tp - 1];
-                const int s = fast_corner_score(c[0], p);
-                if (s >= t) sc[(y + 1) * sp + x + 1] = (uint8_t)s;
-            }
+        // (C) exact score of the survivors (dense warps)
+        for (int k = tid; k < nb; k += FAST_THREADS) {
+            const int i = list_b[k];
+            const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
+            const uint8_t* c = tile + (y + 3) * tp + x + 3;
+            int p[16];
+            p[0] = c[3 * tp];          p[1] = c[3 * tp + 1];   p[2] = c[2 * tp + 2];   p[3] = c[tp + 3];
+            p[4] = c[3];               p[5] = c[-tp + 3];      p[6] = c[-2 * tp + 2];  p[7] = c[-3 * tp + 1];
+            p[8] = c[-3 * tp];         p[9] = c[-3 * tp - 1];  p[10] = c[-2 * tp - 2]; p[11] = c[-tp - 3];
+            p[12] = c[-3];             p[13] = c[tp - 3];      p[14] = c[2 * tp - 2];  p[15] = c[3 * tp - 1];
+            const int s = fast_corner_score(c[0], p);
+            if (s >= t) sc[(y + 1) * sp + x + 1] = (uint8_t)s;
         }
         __syncthreads();
 
-        // (4) strict local maxima among the survivors -> final list (unordered)
-        for (int k = tid; k < nsurv; k += FAST_THREADS) {
-            const int i = surv[k];
+        // (D) strict local maxima among the survivors -> final list (unordered)
+        for (int k = tid; k < nb; k += FAST_THREADS) {
+            const int i = list_b[k];
             const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
             const uint8_t* q = sc + (y + 1) * sp + x + 1;
             const int s = q[0];
@@ -882,7 +927,7 @@ static void fast_smem(const Plan& P, int* tile_bytes, int* score_bytes, int* sur
     *tile_bytes = (mt + 15) & ~15;
     *score_bytes = (ms + 15) & ~15;
     *surv_bytes = (2 * mv + 15) & ~15;
-    *total = *tile_bytes + *score_bytes + *surv_bytes + 4 * mf + 16;
+    *total = *tile_bytes + *score_bytes + 2 * *surv_bytes + 4 * mf + 16;
 }
 cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch) {
     int tb, sb, vb, tot;

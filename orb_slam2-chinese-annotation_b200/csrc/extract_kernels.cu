@@ -380,7 +380,7 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
 // partitioned between two ping-pong key buffers.  Equal-size ties of the sorted expansion phase
 // (reference :703 sorts pair<int, ExtractorNode*>, i.e. by heap address) use the canonical rule
 // "later-created node first" == higher index in R.
-#define QT_THREADS 512
+#define QT_THREADS 256
 #define QT_WARPS (QT_THREADS / 32)
 #define QT_BIG 1024  // nodes with more keys are partitioned by the whole CTA
 
@@ -471,13 +471,17 @@ __device__ __forceinline__ void warp_partition4(const uint32_t* __restrict__ src
 }
 
 // same, by the whole CTA (all threads must call); counts returned in sh.big_cnt
-__device__ void block_partition4(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, int n, int sx, int sy, QtShared& sh) {
+struct QuadrantOf { int sx, sy; __device__ __forceinline__ int operator()(uint32_t k) const { return key_quadrant(k, sx, sy); } };
+// root index of a key (reference :588): (int)(pt.x / hX), clamped to the 4 bins this partition supports
+struct RootOf { float hx; __device__ __forceinline__ int operator()(uint32_t k) const { return min((int)__fdiv_rn((float)ORB_KEY_X(k), hx), 3); } };
+template <class F>
+__device__ void block_partition4(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, int n, const F quad, QtShared& sh) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lt = (1u << lane) - 1;
     if (tid < 4) sh.big_cnt[tid] = 0;
     __syncthreads();
     int c[4] = {0, 0, 0, 0};
-    for (int i = tid; i < n; i += QT_THREADS) c[key_quadrant(src[i], sx, sy)]++;
+    for (int i = tid; i < n; i += QT_THREADS) c[quad(src[i])]++;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         int v = c[j];
@@ -490,7 +494,7 @@ __device__ void block_partition4(const uint32_t* __restrict__ src, uint32_t* __r
     for (int i0 = 0; i0 < n; i0 += QT_THREADS) {
         const int i = i0 + tid;
         uint32_t k = 0; int q = -1;
-        if (i < n) { k = src[i]; q = key_quadrant(k, sx, sy); }
+        if (i < n) { k = src[i]; q = quad(k); }
         unsigned m[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) { m[j] = __ballot_sync(0xffffffffu, q == j); if (lane == 0) sh.big_wc[warp][j] = __popc(m[j]); }
@@ -585,6 +589,24 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
     {
         const int n_ini = G.n_ini;
         const float hX = G.h_x;
+        if (n_ini <= 4) {
+            // one stable 4-way partition by root index
+            block_partition4(kbuf0, kbuf1, n, RootOf{hX}, sh);
+            if (tid == 0) {
+                int run = 0;
+                for (int r = 0; r < n_ini; ++r) {
+                    QNode nd;
+                    nd.start = run | (int)0x80000000;
+                    nd.count = sh.big_cnt[r];
+                    nd.x0 = (short)(int)(hX * (float)r);
+                    nd.x1 = (short)(int)(hX * (float)(r + 1));
+                    nd.y0 = 0;
+                    nd.y1 = (short)G.win_h;
+                    nxt[r] = nd;  // list order; reversed below
+                    run += nd.count;
+                }
+            }
+        } else {
         int run = 0;
         for (int r = 0; r < n_ini; ++r) {
             int seg_begin = run;
@@ -607,6 +629,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
                 nd.y1 = (short)G.win_h;
                 nxt[r] = nd;  // list order; reversed below
             }
+        }
         }
         __syncthreads();
         // drop empty roots, reverse into cur
@@ -661,7 +684,10 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
         if (np == 0) break;  // every node holds one key: list cannot grow
 
         // b. partition every parent's keys into the other key buffer
-        for (int k = 0; k < np; ++k) {  // big nodes: whole CTA (uniform branch)
+        int big = 0;
+        for (int k = tid; k < np; k += QT_THREADS) big |= cur[par[k]].count > QT_BIG;
+        big = __syncthreads_or(big);
+        for (int k = 0; big && k < np; ++k) {  // big nodes: whole CTA (uniform branch)
             const QNode nd = cur[par[k]];
             if (nd.count <= QT_BIG) continue;
             const int st = nd.start & 0x7fffffff;
@@ -669,7 +695,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
             const uint32_t* src = (in1 ? kbuf1 : kbuf0) + st;
             uint32_t* dst = (in1 ? kbuf0 : kbuf1) + st;
             const int sx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), sy = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
-            block_partition4(src, dst, nd.count, sx, sy, sh);
+            block_partition4(src, dst, nd.count, QuadrantOf{sx, sy}, sh);
             if (tid < 4) cc[4 * k + tid] = sh.big_cnt[tid];
             __syncthreads();
         }

@@ -14,6 +14,32 @@ __constant__ __align__(16) signed char c_pattern[1024] = {
 };
 
 // ------------------------------------------------------------------------------------------
+// Ingest: caller images (any row stride, any alignment) -> the pitched, word-aligned level-0 slots.
+// One thread assembles one aligned 32-bit destination word from the two aligned source words that
+// cover it (funnel shift); reads and writes are coalesced.  The source allocation must extend to
+// the next 4-byte boundary past its last byte (true for cudaMalloc'ed buffers).
+__global__ void __launch_bounds__(256) k_ingest(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, const int w, const int h,
+                                                const int stride, const unsigned long long img_stride, const int dst_pitch,
+                                                const unsigned long long dst_img_stride) {
+    const int j = blockIdx.x * 256 + threadIdx.x;  // destination word within the row
+    const int y = blockIdx.y, b = blockIdx.z;
+    if (4 * j >= w) return;
+    const unsigned long long a = (unsigned long long)src + (unsigned long long)b * img_stride + (unsigned long long)y * stride + 4ull * j;
+    const uint32_t* q = reinterpret_cast<const uint32_t*>(a & ~3ull);
+    const unsigned sh = (unsigned)(a & 3ull) * 8u;
+    const uint32_t lo = __ldg(q);
+    uint32_t v = lo;
+    if (sh) v = __funnelshift_r(lo, __ldg(q + 1), sh);
+    const int rem = w - 4 * j;
+    if (rem < 4) v &= 0xffffffffu >> (8 * (4 - rem));
+    *reinterpret_cast<uint32_t*>(dst + (size_t)b * dst_img_stride + (size_t)y * dst_pitch + 4 * j) = v;
+}
+void launch_ingest(cudaStream_t s, const uint8_t* src, uint8_t* dst, int w, int h, int stride, size_t img_stride, int dst_pitch, size_t dst_img_stride, int batch) {
+    dim3 grid(((w + 3) / 4 + 255) / 256, h, batch);
+    k_ingest<<<grid, 256, 0, s>>>(src, dst, w, h, stride, img_stride, dst_pitch, dst_img_stride);
+}
+
+// ------------------------------------------------------------------------------------------
 // Pyramid: level l <- level l-1, OpenCV 8u INTER_LINEAR (11-bit coefficients).  One thread
 // produces 4 horizontally adjacent pixels of one row and stores them as one 32-bit word.  The
 // two source rows are read as aligned words; a (pixel, right neighbour) byte pair is pulled out

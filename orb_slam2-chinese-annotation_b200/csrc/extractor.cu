@@ -7,6 +7,7 @@
 #include <cstring>
 
 void launch_resize(cudaStream_t s, uint8_t* pyr, const LevelGeom& src, const LevelGeom& dst, int batch);
+void launch_ingest(cudaStream_t s, const uint8_t* src, uint8_t* dst, int w, int h, int stride, size_t img_stride, int dst_pitch, size_t dst_img_stride, int batch);
 void launch_gauss(cudaStream_t s, const uint8_t* pyr, uint8_t* blur, const Plan& P, int batch);
 cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch);
 cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefix, const uint32_t* stage, uint32_t* keys,
@@ -279,7 +280,7 @@ int orb_pipe_streams(orb_extractor* e) {
     if (!e->s_h2d) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_h2d, cudaStreamNonBlocking));
     if (!e->s_d2h) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_d2h, cudaStreamNonBlocking));
     if (!e->d_in && e->max_batch > 1 && !getenv("ORB_B200_NO_STAGING"))
-        ORB_CUDA(cudaMalloc((void**)&e->d_in, (size_t)e->max_batch * e->max_w * e->max_h));
+        ORB_CUDA(cudaMalloc((void**)&e->d_in, (size_t)e->max_batch * e->max_w * e->max_h + 16));
     return ORB_OK;
 }
 cudaEvent_t orb_pool_event(orb_extractor* e, int i) {
@@ -293,6 +294,7 @@ cudaEvent_t orb_pool_event(orb_extractor* e, int i) {
 // Chunks are large enough to fill the GPU several times over and small enough that a batch has
 // ~8 of them in flight between the upload, kernel and download streams.
 int orb_chunk_size(int batch) {
+    if (const char* v = getenv("ORB_B200_CHUNK")) { const int c = atoi(v); if (c > 0) return c < batch ? c : batch; }
     if (batch <= 8) return batch;
     const int c = (batch + 7) / 8;
     return c < 8 ? 8 : c;
@@ -302,12 +304,13 @@ int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w
     const LevelGeom& G0 = e->plan.lv[0];
     uint8_t* dst = e->d_pyr + G0.off + (size_t)b0 * G0.img_stride;
     const uint8_t* src = imgs + (size_t)b0 * img_stride;
-    if (img_stride == (size_t)stride * h && stride == w && e->d_in && G0.img_stride == (unsigned long long)G0.pitch * h) {
-        // dense host batch: one linear copy at full PCIe rate into the staging area, then an on-device
-        // strided copy into the pitched level-0 slots (a strided host->device copy of w-byte rows is DMA-descriptor bound)
+    if (img_stride == (size_t)stride * h && stride == w && e->d_in) {
+        // dense host batch: one linear copy at full PCIe rate into the staging area, then the ingest kernel
+        // re-pitches it on the device (strided copies of w-byte rows are DMA-descriptor bound, host or device)
         uint8_t* stg = e->d_in + (size_t)b0 * w * h;
         ORB_CUDA(cudaMemcpyAsync(stg, src, (size_t)n * w * h, cudaMemcpyHostToDevice, st));
-        ORB_CUDA(cudaMemcpy2DAsync(dst, G0.pitch, stg, w, w, (size_t)h * n, cudaMemcpyDeviceToDevice, st));
+        launch_ingest(st, stg, dst, w, h, w, (size_t)w * h, G0.pitch, G0.img_stride, n);
+        e->launches++;
     } else if (img_stride == (size_t)stride * h && G0.img_stride == (unsigned long long)G0.pitch * h) {
         ORB_CUDA(cudaMemcpy2DAsync(dst, G0.pitch, src, stride, w, (size_t)h * n, cudaMemcpyHostToDevice, st));
     } else {
@@ -465,14 +468,8 @@ int orb_extract_device(orb_extractor* e, const uint8_t* d_imgs, int batch, int w
     int st = ensure_plan(e, w, h, batch);
     if (st != ORB_OK) return st;
     const LevelGeom& G0 = e->plan.lv[0];
-    if (img_stride == (size_t)stride * h || batch == 1) {
-        ORB_CUDA(cudaMemcpy2DAsync(e->d_pyr + G0.off, G0.pitch, d_imgs, stride, w, (size_t)h * (batch == 1 ? 1 : batch),
-                                   cudaMemcpyDeviceToDevice, e->stream));
-    } else {
-        for (int b = 0; b < batch; ++b)
-            ORB_CUDA(cudaMemcpy2DAsync(e->d_pyr + G0.off + (size_t)b * G0.img_stride, G0.pitch, d_imgs + (size_t)b * img_stride, stride,
-                                       w, h, cudaMemcpyDeviceToDevice, e->stream));
-    }
+    launch_ingest(e->stream, d_imgs, e->d_pyr + G0.off, w, h, stride, img_stride, G0.pitch, G0.img_stride, batch);
+    e->launches++;
     return run_pipeline(e, batch);
 }
 

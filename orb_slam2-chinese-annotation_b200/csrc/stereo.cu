@@ -9,6 +9,9 @@
 // The per-row lists are built with atomics (unordered): the reference keeps the first candidate
 // on equal distance, i.e. the lowest right index, which a (distance, index) minimum reproduces.
 #include "orb_internal.h"
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 #define ST_TH_HIGH 100
 #define ST_TH_ORB 75  // (TH_HIGH + TH_LOW) / 2
@@ -315,8 +318,11 @@ int orb_stereo_frames(orb_extractor* l, orb_extractor* r, const uint8_t* imgs_l,
     int st = orb_ensure_plan(l, w, h, batch);
     if (st == ORB_OK) st = orb_ensure_plan(r, w, h, batch);
     if (st == ORB_OK) st = orb_pipe_streams(l);
+    if (st == ORB_OK) st = orb_pipe_streams(r);   // the right handle's upload staging area
     if (st != ORB_OK) return st;
     const int chunk = orb_chunk_size(batch), nch = (batch + chunk - 1) / chunk;
+    const bool dbg = getenv("ORB_B200_DEBUG") != nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
     if (!orb_pool_event(l, 3 * nch + 1)) { orb_set_error("event"); return ORB_ERR_CUDA; }
     // uploads must not overtake work already queued on the two kernel streams
     ORB_CUDA(cudaEventRecord(l->ev_pool[3 * nch], l->stream));
@@ -333,11 +339,12 @@ int orb_stereo_frames(orb_extractor* l, orb_extractor* r, const uint8_t* imgs_l,
         if ((st = orb_upload_slots(r, imgs_r, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) return st;
         ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
         ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
-        if ((st = orb_run_slots(l, b0, n)) != ORB_OK) return st;
+        const bool skip = dbg && getenv("ORB_B200_SKIP_COMPUTE");
+        if (!skip && (st = orb_run_slots(l, b0, n)) != ORB_OK) return st;
         ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
-        if ((st = orb_run_slots(r, b0, n)) != ORB_OK) return st;
+        if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) return st;
         // ... then ComputeStereoMatches (:95)
-        if ((st = stereo_launch(l, r, b0, n, mbf, min_d, max_d, false)) != ORB_OK) return st;
+        if (!skip && (st = stereo_launch(l, r, b0, n, mbf, min_d, max_d, false)) != ORB_OK) return st;
         ORB_CUDA(cudaEventRecord(done, l->stream));
         ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, done, 0));
         if ((st = orb_download_slots(l, b0, n, kps_l, desc_l, cap, l->s_d2h)) != ORB_OK) return st;
@@ -348,6 +355,15 @@ int orb_stereo_frames(orb_extractor* l, orb_extractor* r, const uint8_t* imgs_l,
             ORB_CUDA(cudaMemcpy2DAsync(depth + (size_t)b0 * cap, (size_t)cap * 4, l->d_depth + (size_t)b0 * kc, (size_t)kc * 4, (size_t)m * 4, n,
                                        cudaMemcpyDeviceToHost, l->s_d2h));
         }
+    }
+    const auto t_enq = std::chrono::steady_clock::now();
+    if (dbg) {
+        ORB_CUDA(cudaStreamSynchronize(l->s_h2d)); const auto t1 = std::chrono::steady_clock::now();
+        ORB_CUDA(cudaStreamSynchronize(l->stream)); ORB_CUDA(cudaStreamSynchronize(r->stream)); const auto t2 = std::chrono::steady_clock::now();
+        ORB_CUDA(cudaStreamSynchronize(l->s_d2h)); const auto t3 = std::chrono::steady_clock::now();
+        auto ms = [&](std::chrono::steady_clock::time_point a) { return std::chrono::duration<double, std::milli>(a - t_begin).count(); };
+        fprintf(stderr, "[orb_stereo_frames] batch %d chunk %d: enqueued %.2f ms, uploads done %.2f, kernels done %.2f, downloads done %.2f\n",
+                batch, chunk, ms(t_enq), ms(t1), ms(t2), ms(t3));
     }
     int st_l = 0, st_r = 0;
     ORB_CUDA(cudaMemcpyAsync(&st_l, l->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->s_d2h));

@@ -1,0 +1,181 @@
+// Drives the C++ drop-in classes (include/ORBextractor.h, include/ORBmatcher.h) the way the
+// reference's callers do, on scenarios written by tests/test_gpu_cpp_dropin.py, and writes the
+// results back for comparison with the oracle.  Frame / KeyFrame / MapPoint are small structs with
+// the reference's member names (include/Frame.h, include/KeyFrame.h, include/MapPoint.h).
+//   test_dropin extract <in> <out> | mappoints <in> <out> | lastframe <in> <out> | bow <in> <out> | tri <in> <out>
+#include <cstdio>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "ORBextractor.h"
+#include "ORBmatcher.h"
+#include "blobio.h"
+
+struct MapPoint {
+    bool mbTrackInView; float mTrackProjX, mTrackProjY, mTrackProjXR; int mnTrackScaleLevel; float mTrackViewCos;
+    cv::Mat mDescriptor, mWorldPos; int nObs; bool mbBad; int id;
+    bool isBad() { return mbBad; }
+    cv::Mat GetDescriptor() { return mDescriptor.clone(); }
+    cv::Mat GetWorldPos() { return mWorldPos.clone(); }
+    int Observations() { return nObs; }
+};
+
+struct Frame {  // also stands in for KeyFrame
+    int N;
+    std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
+    std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2;
+    cv::Mat mDescriptors, mTcw;
+    std::vector<MapPoint*> mvpMapPoints;
+    std::vector<bool> mvbOutlier;
+    float mnMinX, mnMinY, mnMaxX, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
+    float fx, fy, cx, cy, mbf, mb;
+    std::map<unsigned, std::vector<unsigned> > mFeatVec;
+    cv::Mat mOw;
+    std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
+    MapPoint* GetMapPoint(int i) { return mvpMapPoints[i]; }
+    cv::Mat GetCameraCenter() { return mOw.clone(); }
+    cv::Mat GetRotation() { cv::Mat R(3, 3, CV_32F); for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) R.at<float>(r, c) = mTcw.at<float>(r, c); return R; }
+    cv::Mat GetTranslation() { cv::Mat t(3, 1, CV_32F); for (int r = 0; r < 3; ++r) t.at<float>(r, 0) = mTcw.at<float>(r, 3); return t; }
+};
+
+static cv::Mat Identity4() { cv::Mat T = cv::Mat::zeros(4, 4, CV_32F); for (int i = 0; i < 4; ++i) T.at<float>(i, i) = 1.f; return T; }
+
+static void LoadFrame(const Blob& b, const std::string& p, Frame& F) {
+    F.N = (int)b.count(p + "x");
+    const float* x = b.get<float>(p + "x"); const float* y = b.get<float>(p + "y"); const float* ang = b.get<float>(p + "angle");
+    const int* oct = b.get<int>(p + "octave"); const float* ur = b.get<float>(p + "u_right");
+    F.mvKeysUn.resize(F.N); F.mvuRight.assign(ur, ur + F.N);
+    for (int i = 0; i < F.N; ++i) F.mvKeysUn[i] = cv::KeyPoint(x[i], y[i], 31.f, ang[i], 0.f, oct[i]);
+    F.mvKeys = F.mvKeysUn;
+    F.mDescriptors.create(F.N, 32, CV_8U);
+    if (F.N) std::memcpy(F.mDescriptors.data, b.get<unsigned char>(p + "desc"), (size_t)F.N * 32);
+    const float* sf = b.get<float>(p + "sf"); const size_t nl = b.count(p + "sf");
+    F.mvScaleFactors.assign(sf, sf + nl);
+    F.mvLevelSigma2.resize(nl); for (size_t l = 0; l < nl; ++l) F.mvLevelSigma2[l] = sf[l] * sf[l];
+    const float* g = b.get<float>(p + "grid");  // min_x, min_y, max_x, max_y, inv_w, inv_h
+    F.mnMinX = g[0]; F.mnMinY = g[1]; F.mnMaxX = g[2]; F.mnMaxY = g[3]; F.mfGridElementWidthInv = g[4]; F.mfGridElementHeightInv = g[5];
+    F.mvpMapPoints.assign(F.N, (MapPoint*)NULL); F.mvbOutlier.assign(F.N, false);
+    F.mTcw = Identity4(); F.mOw = cv::Mat::zeros(3, 1, CV_32F);
+    F.fx = F.fy = 1.f; F.cx = F.cy = 0.f; F.mbf = 0.f; F.mb = 0.f;
+    if (b.has(p + "fv_ids")) {
+        const unsigned* ids = b.get<unsigned>(p + "fv_ids"); const int* st = b.get<int>(p + "fv_start"); const unsigned* it = b.get<unsigned>(p + "fv_items");
+        for (size_t k = 0; k < b.count(p + "fv_ids"); ++k) F.mFeatVec[ids[k]] = std::vector<unsigned>(it + st[k], it + st[k + 1]);
+    }
+}
+
+static cv::Mat Row32(const unsigned char* p) { cv::Mat d(1, 32, CV_8U); std::memcpy(d.data, p, 32); return d; }
+
+int main(int argc, char** argv) {
+    if (argc < 4) { fprintf(stderr, "usage: test_dropin <mode> <in> <out>\n"); return 2; }
+    const std::string mode = argv[1];
+    try {
+        Blob b; b.load(argv[2]);
+        BlobWriter w(argv[3]);
+        if (mode == "extract") {
+            const int* p = b.get<int>("params");  // w, h, nfeatures, nlevels, iniTh, minTh
+            const float sf = b.get<float>("scale")[0];
+            cv::Mat img(p[1], p[0], CV_8UC1, const_cast<unsigned char*>(b.get<unsigned char>("image")));
+            ORB_SLAM2::ORBextractor ext(p[2], sf, p[3], p[4], p[5]);
+            ext.SetKeepPyramidOnHost(true);
+            std::vector<cv::KeyPoint> kps; cv::Mat desc;
+            ext(img, cv::Mat(), kps, desc);
+            // second call on the same instance, as Tracking does frame after frame
+            std::vector<cv::KeyPoint> kps2; cv::Mat desc2;
+            ext(img, cv::Mat(), kps2, desc2);
+            if (kps2.size() != kps.size()) throw std::runtime_error("second call differs");
+            w.put("kps", "u1", kps.data(), kps.size() * sizeof(cv::KeyPoint));
+            w.put("desc", "u1", desc.data, (size_t)desc.rows * 32);
+            std::vector<float> tabs = ext.GetScaleFactors();
+            w.put("sf", "f4", tabs.data(), tabs.size());
+            const cv::Mat& l3 = ext.mvImagePyramid[3];
+            int dims[2] = {l3.cols, l3.rows};
+            w.put("l3_dims", "i4", dims, 2);
+            w.put("l3", "u1", l3.data, (size_t)l3.rows * l3.cols);
+            // batch entry point
+            std::vector<cv::Mat> imgs(3, img); std::vector<std::vector<cv::KeyPoint> > bk; std::vector<cv::Mat> bd;
+            ext.ExtractBatch(imgs, bk, bd);
+            int same = bk.size() == 3 && bk[2].size() == kps.size() && std::memcmp(bd[2].data, desc.data, (size_t)desc.rows * 32) == 0;
+            w.put("batch_same", "i4", &same, 1);
+            // empty image: outputs untouched (:1095)
+            std::vector<cv::KeyPoint> ke(7); cv::Mat de;
+            ext(cv::Mat(), cv::Mat(), ke, de);
+            int untouched = ke.size() == 7;
+            w.put("empty_untouched", "i4", &untouched, 1);
+        } else if (mode == "mappoints") {
+            Frame F; LoadFrame(b, "f_", F);
+            const int M = (int)b.count("mp_valid");
+            std::vector<MapPoint> store(M); std::vector<MapPoint*> mps(M);
+            const unsigned char* valid = b.get<unsigned char>("mp_valid"); const unsigned char* blocks = b.get<unsigned char>("mp_blocks");
+            for (int i = 0; i < M; ++i) {
+                MapPoint& m = store[i];
+                m.mbTrackInView = valid[i] != 0; m.mbBad = false; m.id = i;
+                m.mTrackProjX = b.get<float>("mp_proj_x")[i]; m.mTrackProjY = b.get<float>("mp_proj_y")[i]; m.mTrackProjXR = b.get<float>("mp_proj_xr")[i];
+                m.mnTrackScaleLevel = b.get<int>("mp_level")[i]; m.mTrackViewCos = b.get<float>("mp_view_cos")[i];
+                m.mDescriptor = Row32(b.get<unsigned char>("mp_desc") + (size_t)i * 32); m.nObs = blocks[i] ? 1 : 0;
+                mps[i] = &m;
+            }
+            // keypoints that already hold an observed MapPoint (:90-93)
+            MapPoint holder; holder.nObs = 3; holder.id = -2;
+            const unsigned char* occ = b.get<unsigned char>("occupied");
+            for (int i = 0; i < F.N; ++i) if (occ[i]) F.mvpMapPoints[i] = &holder;
+            ORB_SLAM2::ORBmatcher matcher(b.get<float>("ratio")[0], true);
+            const int n = matcher.SearchByProjection(F, mps, b.get<float>("th")[0]);
+            std::vector<int> match(F.N, -1);
+            for (int i = 0; i < F.N; ++i) if (F.mvpMapPoints[i] && F.mvpMapPoints[i] != &holder) match[i] = F.mvpMapPoints[i]->id;
+            w.put("n", "i4", &n, 1); w.put("match", "i4", match.data(), match.size());
+        } else if (mode == "lastframe") {
+            Frame Cur, Last; LoadFrame(b, "f_", Cur);
+            const int M = (int)b.count("l_valid");
+            Last = Cur; Last.N = M; Last.mvKeys.assign(M, cv::KeyPoint()); Last.mvKeysUn.assign(M, cv::KeyPoint());
+            Last.mvpMapPoints.assign(M, (MapPoint*)NULL); Last.mvbOutlier.assign(M, false);
+            std::vector<MapPoint> store(M);
+            for (int i = 0; i < M; ++i) {
+                MapPoint& m = store[i];
+                m.id = i; m.mbBad = false; m.nObs = b.get<unsigned char>("l_blocks")[i] ? 1 : 0;
+                m.mDescriptor = Row32(b.get<unsigned char>("l_desc") + (size_t)i * 32);
+                m.mWorldPos.create(3, 1, CV_32F);
+                m.mWorldPos.at<float>(0) = b.get<float>("l_xc")[i]; m.mWorldPos.at<float>(1) = b.get<float>("l_yc")[i]; m.mWorldPos.at<float>(2) = b.get<float>("l_zc")[i];
+                Last.mvKeys[i].octave = b.get<int>("l_octave")[i]; Last.mvKeysUn[i].angle = b.get<float>("l_angle")[i];
+                if (b.get<unsigned char>("l_valid")[i]) Last.mvpMapPoints[i] = &m;
+            }
+            const float* cam = b.get<float>("cam");
+            Cur.fx = cam[0]; Cur.fy = cam[1]; Cur.cx = cam[2]; Cur.cy = cam[3]; Cur.mbf = cam[4]; Cur.mb = 1e9f;  // identity poses: neither forward nor backward
+            ORB_SLAM2::ORBmatcher matcher(0.9f, b.get<int>("check_ori")[0] != 0);
+            const int n = matcher.SearchByProjection(Cur, Last, b.get<float>("th")[0], false);
+            std::vector<int> match(Cur.N, -1);
+            for (int i = 0; i < Cur.N; ++i) if (Cur.mvpMapPoints[i]) match[i] = Cur.mvpMapPoints[i]->id;
+            w.put("n", "i4", &n, 1); w.put("match", "i4", match.data(), match.size());
+        } else if (mode == "bow" || mode == "tri") {
+            Frame A, B; LoadFrame(b, "a_", A); LoadFrame(b, "b_", B);
+            std::vector<MapPoint> sa(A.N), sb(B.N);
+            for (int i = 0; i < A.N; ++i) { sa[i].id = i; sa[i].mbBad = false; if (b.get<unsigned char>("has_a")[i]) A.mvpMapPoints[i] = &sa[i]; }
+            for (int i = 0; i < B.N; ++i) { sb[i].id = i; sb[i].mbBad = false; if (b.get<unsigned char>("has_b")[i]) B.mvpMapPoints[i] = &sb[i]; }
+            ORB_SLAM2::ORBmatcher matcher(b.get<float>("ratio")[0], true);
+            if (mode == "bow") {
+                std::vector<MapPoint*> out;
+                const int n = matcher.SearchByBoW(&A, B, out);
+                std::vector<int> match(B.N, -1);
+                for (int j = 0; j < B.N; ++j) if (out[j]) match[j] = out[j]->id;
+                w.put("n", "i4", &n, 1); w.put("match", "i4", match.data(), match.size());
+            } else {
+                // camera centre of KF1 expressed in KF2 = (ex, ey, 1) with unit intrinsics -> epipole (ex, ey)
+                const float* ep = b.get<float>("epipole");
+                A.mOw.at<float>(0) = ep[0]; A.mOw.at<float>(1) = ep[1]; A.mOw.at<float>(2) = 1.f;
+                cv::Mat F12(3, 3, CV_32F); std::memcpy(F12.data, b.get<float>("f12"), 36);
+                std::vector<std::pair<size_t, size_t> > pairs;
+                const int n = matcher.SearchForTriangulation(&A, &B, F12, pairs, b.get<int>("only_stereo")[0] != 0);
+                std::vector<int> flat;
+                for (size_t k = 0; k < pairs.size(); ++k) { flat.push_back((int)pairs[k].first); flat.push_back((int)pairs[k].second); }
+                w.put("n", "i4", &n, 1); w.put("pairs", "i4", flat.data(), flat.size());
+            }
+        } else {
+            fprintf(stderr, "unknown mode %s\n", mode.c_str());
+            return 2;
+        }
+    } catch (const std::exception& e) {
+        fprintf(stderr, "test_dropin: %s\n", e.what());
+        return 1;
+    }
+    return 0;
+}

@@ -1,0 +1,125 @@
+"""The C++ drop-in classes (include/ORBextractor.h, include/ORBmatcher.h: the reference's class
+names and signatures over the C ABI) driven the way the reference's callers drive them, by
+tests/cpp/test_dropin.cpp, and compared with the CPU oracle on the same scenarios."""
+import importlib
+import os
+import subprocess
+import numpy as np
+import pytest
+import cppio
+import orc
+
+synth = importlib.import_module("orb_slam2-chinese-annotation_b200.synth")
+views = importlib.import_module("orb_slam2-chinese-annotation_b200.views")
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+BIN = os.path.join(HERE, "cpp", "build", "test_dropin")
+
+# cv::KeyPoint as laid out by include/orb_b200_cv.h (and by OpenCV): pt.x pt.y size angle response octave class_id
+KP = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+
+
+@pytest.fixture(scope="module")
+def dropin():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(HERE, "cpp")])
+    assert os.path.exists(BIN)
+
+    def run(mode, arrays, tmp_path):
+        fin, fout = str(tmp_path / (mode + ".in")), str(tmp_path / (mode + ".out"))
+        cppio.write(fin, arrays)
+        r = subprocess.run([BIN, mode, fin, fout], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        return cppio.read(fout)
+    return run
+
+
+def _frame_blob(p, d):
+    f = views.Frame(d["x"], d["y"], d["octave"], d["angle"], d["desc"], d["sf"], d["bounds"], d["u_right"])
+    out = {p + "x": f.x, p + "y": f.y, p + "octave": f.octave, p + "angle": f.angle, p + "desc": f.desc.reshape(-1),
+           p + "u_right": f.u_right, p + "sf": f.sf,
+           p + "grid": np.array([f.bounds[0], f.bounds[1], f.bounds[2], f.bounds[3], f.inv_w, f.inv_h], np.float32)}
+    return f, out
+
+
+def _fv_blob(p, mapping):
+    v = views.FeatureVector(mapping)
+    return v, {p + "fv_ids": v.node_ids, p + "fv_start": v.start, p + "fv_items": v.items}
+
+
+def _f32(v):
+    return np.array([v], np.float32)
+
+
+@pytest.mark.parametrize("w,h,nf", [(640, 480, 1000), (1241, 376, 2000)])
+def test_extractor_operator(dropin, tmp_path, w, h, nf):
+    img = synth.make_image(w, h, 11)
+    out = dropin("extract", {"params": np.array([w, h, nf, 8, 20, 7], np.int32), "scale": _f32(1.2), "image": img.reshape(-1)}, tmp_path)
+    o = orc.Extractor(nf, 1.2, 8, 20, 7)
+    okp, odesc = o.extract(img)
+    kps = out["kps"].view(KP)
+    assert len(kps) == len(okp)
+    for f in ("x", "y", "size", "angle", "response", "octave"):
+        assert np.array_equal(kps[f], okp[f]), f
+    assert (kps["class_id"] == -1).all()
+    assert np.array_equal(out["desc"].reshape(-1, 32), odesc)
+    assert np.array_equal(out["sf"], o.tables()["sf"])
+    lw, lh = out["l3_dims"]
+    assert np.array_equal(out["l3"].reshape(lh, lw), o.level(3))      # mvImagePyramid[3] is readable by callers
+    assert out["batch_same"][0] == 1 and out["empty_untouched"][0] == 1
+
+
+@pytest.mark.parametrize("idx,th,coarse", [(0, 1.0, False), (1, 3.0, False), (3, 3.0, True)])
+def test_search_by_projection_mappoints(dropin, tmp_path, idx, th, coarse):
+    f, mps, occ = synth.make_projection_scenario(2000, 2000, idx, coarse_desc=coarse)
+    F, blob = _frame_blob("f_", f)
+    blob.update({"mp_valid": views.u8(mps["valid"]), "mp_blocks": views.u8(mps["blocks"]), "mp_proj_x": mps["proj_x"], "mp_proj_y": mps["proj_y"],
+                 "mp_proj_xr": mps["proj_xr"], "mp_level": mps["level"], "mp_view_cos": mps["view_cos"], "mp_desc": mps["desc"].reshape(-1),
+                 "occupied": views.u8(occ), "ratio": _f32(0.8), "th": _f32(th)})
+    out = dropin("mappoints", blob, tmp_path)
+    n_o, m_o = orc.search_by_projection_mps(F, mps, th, np.float32(0.8), occ)
+    assert out["n"][0] == n_o and np.array_equal(out["match"], m_o)
+    assert n_o > 100
+
+
+@pytest.mark.parametrize("idx,th,check_ori", [(0, 7.0, True), (1, 15.0, True), (2, 7.0, False)])
+def test_search_by_projection_lastframe(dropin, tmp_path, idx, th, check_ori):
+    f, last, cam = synth.make_lastframe_scenario(2000, idx)
+    F, blob = _frame_blob("f_", f)
+    blob.update({"l_valid": views.u8(last["valid"]), "l_blocks": views.u8(last["blocks"]), "l_xc": last["xc"], "l_yc": last["yc"], "l_zc": last["zc"],
+                 "l_octave": last["octave"], "l_angle": last["angle"], "l_desc": last["desc"].reshape(-1),
+                 "cam": np.array(cam, np.float32), "th": _f32(th), "check_ori": np.array([int(check_ori)], np.int32)})
+    out = dropin("lastframe", blob, tmp_path)
+    n_o, m_o = orc.search_by_projection_last(F, last, cam, th, False, False, check_ori)
+    assert out["n"][0] == n_o and np.array_equal(out["match"], m_o)
+    assert n_o > 100
+
+
+@pytest.mark.parametrize("idx,coarse,ratio", [(0, False, 0.7), (2, True, 0.9)])
+def test_search_by_bow(dropin, tmp_path, idx, coarse, ratio):
+    a, fva, b, fvb, has_a, has_b = synth.make_bow_scenario(2000, 1900, idx, coarse_desc=coarse)
+    KF, blob = _frame_blob("a_", a)
+    F, bb = _frame_blob("b_", b); blob.update(bb)
+    va, ba = _fv_blob("a_", fva); vb, bb = _fv_blob("b_", fvb); blob.update(ba); blob.update(bb)
+    blob.update({"has_a": views.u8(has_a), "has_b": views.u8(has_b), "ratio": _f32(ratio)})
+    out = dropin("bow", blob, tmp_path)
+    n_o, m_o = orc.search_by_bow(KF, va, has_a, F, vb, np.float32(ratio), True)
+    assert out["n"][0] == n_o and np.array_equal(out["match"], m_o)
+
+
+@pytest.mark.parametrize("idx,only_stereo", [(0, False), (1, True)])
+def test_search_for_triangulation(dropin, tmp_path, idx, only_stereo):
+    a, fva, b, fvb, has_a, has_b = synth.make_bow_scenario(2000, 2000, 10 + idx)
+    KF1, blob = _frame_blob("a_", a)
+    KF2, bb = _frame_blob("b_", b); blob.update(bb)
+    va, ba = _fv_blob("a_", fva); vb, bb = _fv_blob("b_", fvb); blob.update(ba); blob.update(bb)
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32)
+    blob.update({"has_a": views.u8(has_a), "has_b": views.u8(has_b), "ratio": _f32(0.6), "epipole": np.array([2000.0, 188.0], np.float32),
+                 "f12": F12.reshape(-1), "only_stereo": np.array([int(only_stereo)], np.int32)})
+    out = dropin("tri", blob, tmp_path)
+    sigma2 = (a["sf"] * a["sf"]).astype(np.float32)
+    n_o, m_o = orc.search_for_triangulation(KF1, va, has_a, KF2, vb, has_b, F12, (2000.0, 188.0), sigma2, only_stereo, True)
+    assert out["n"][0] == n_o
+    assert out["pairs"].reshape(-1, 2).tolist() == [[int(i), int(m_o[i])] for i in np.nonzero(m_o >= 0)[0]]
+    assert n_o > 20

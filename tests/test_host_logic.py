@@ -44,6 +44,23 @@ def test_no_cpu_fallback_without_device():
         mt.ORBmatcher()
 
 
+def test_cpp_dropin_headers_compile_and_fail_loudly_without_device(tmp_path):
+    """include/ORBextractor.h / include/ORBmatcher.h (the reference's class names over the C ABI) build into
+    the drop-in driver; without a CUDA device the extractor throws instead of computing on the host."""
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "tests", "cpp")])
+    exe = os.path.join(ROOT, "tests", "cpp", "build", "test_dropin")
+    assert os.path.exists(exe)
+    import torch
+    if torch.cuda.is_available():
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import cppio
+    fin = str(tmp_path / "e.in")
+    cppio.write(fin, {"params": np.array([64, 64, 100, 8, 20, 7], np.int32), "scale": np.array([1.2], np.float32), "image": np.zeros(64 * 64, np.uint8)})
+    r = subprocess.run([exe, "extract", fin, str(tmp_path / "e.out")], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 1 and "no CUDA device" in r.stderr, (r.returncode, r.stderr)
+
+
 def test_product_package_does_not_touch_the_oracle():
     for dirpath, _, files in os.walk(os.path.join(ROOT, PKG)):
         for f in files:

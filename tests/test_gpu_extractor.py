@@ -46,6 +46,23 @@ def _compare(img, g, o, nlevels=8):
     return len(kps)
 
 
+def test_high_resolution_stress_config():
+    """BASELINE.json configs[4]: 3840x2160 monocular, nFeatures=8000 (largest level size a packed key holds)."""
+    w, h, nf = 3840, 2160, 8000
+    g = _gpu_extractor(w, h, nf, batch=2)
+    o = orc.Extractor(nf, 1.2, 8, 20, 7)
+    img = synth.make_image(w, h, 0)
+    n = _compare(img, g, o)
+    assert n >= 8000
+    # a batch of two distinct 4K frames equals two single calls
+    img2 = synth.make_image(w, h, 1)
+    kps, desc, cnt = g.extract_batch(np.stack([img2, img]))
+    okps, odesc = o.extract(img2)
+    assert cnt[0] == len(okps) and np.array_equal(desc[0][:cnt[0]], odesc)
+    assert np.array_equal(kps[0][:cnt[0]]["angle"].view(np.uint32), okps["angle"].view(np.uint32))
+    assert cnt[1] == n
+
+
 @pytest.mark.parametrize("w,h,nf", CONFIGS)
 def test_extractor_matches_oracle(w, h, nf):
     g = _gpu_extractor(w, h, nf)

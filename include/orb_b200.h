@@ -246,6 +246,68 @@ int orb_search_for_triangulation(orb_matcher* m, const orb_frame_view* kf1, cons
                                  float ex, float ey, const float* level_sigma2, int only_stereo,
                                  int check_orientation, int32_t* match12, int32_t* nmatches);
 
+/* SearchByBoW(KeyFrame*, KeyFrame*, matches12) (src/ORBmatcher.cc:581-716).  *_has_mappoint[i] != 0:
+ * feature i holds a good MapPoint.  match12[i] = KF2 feature index matched to KF1 feature i or -1. */
+int orb_search_by_bow_keyframes(orb_matcher* m, const orb_frame_view* kf1, const orb_featvec_view* fv1,
+                                const uint8_t* kf1_has_mappoint, const orb_frame_view* kf2,
+                                const orb_featvec_view* fv2, const uint8_t* kf2_has_mappoint, float nn_ratio,
+                                int check_orientation, int32_t* match12, int32_t* nmatches);
+
+/* MapPoints projected by the caller into a frame / keyframe (the reference does this with cv::Mat
+ * float algebra, MapPoint::PredictScale and the distance / viewing-angle gates before the search:
+ * src/ORBmatcher.cc:326-369, :926-968, :1264-1296, :1643-1672).  Per point: valid (passed every
+ * gate), projection (u, v[, ur]), search radius (th * mvScaleFactors[predicted level]), accepted
+ * keypoint octaves [min_level, max_level] (Frame::GetFeaturesInArea convention: max_level < 0 = open),
+ * descriptor, and (rotation check only) the angle of the source keypoint. */
+typedef struct {
+    int32_t n;
+    const uint8_t* valid;
+    const float* u;
+    const float* v;
+    const float* ur;          /* may be NULL (only read by the Fuse chi-square test) */
+    const float* radius;
+    const int32_t* min_level;
+    const int32_t* max_level;
+    const uint8_t* desc;      /* n x 32 */
+    const float* angle;       /* may be NULL when check_orientation == 0 */
+} orb_projected_view;
+
+/* Projection searches that CLAIM keypoints as they go:
+ *   SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1622-1759):
+ *     occupied[i] = CurrentFrame.mvpMapPoints[i] != NULL, max_dist = ORBdist, rotation check;
+ *   SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) (:311-427):
+ *     occupied[i] = vpMatched[i] != NULL, max_dist = TH_LOW, no rotation check.
+ * Points are visited in order; the best unclaimed candidate (strict <, first wins) within max_dist
+ * is claimed.  match[i] = point index given to keypoint i or -1 (after the rotation cull);
+ * point_best_idx[p] (may be NULL) = keypoint claimed by point p before the cull, or -1. */
+int orb_search_by_projection_claiming(orb_matcher* m, const orb_frame_view* f, const orb_projected_view* pts,
+                                      const uint8_t* occupied, int max_dist, int check_orientation, int32_t* match,
+                                      int32_t* point_best_idx, int32_t* nmatches);
+
+/* Independent best candidate per projected point — the search step of Fuse (src/ORBmatcher.cc:903-1054
+ * with inv_level_sigma2 = pKF->mvInvLevelSigma2: chi-square gate 5.99 / 7.8 on the reprojection error;
+ * :1056-1207 with inv_level_sigma2 = NULL) and of each direction of SearchBySim3 (:1264-1340).
+ * best_idx[p] = keypoint index with the smallest distance (first wins) if it is <= max_dist, else -1;
+ * best_dist[p] (may be NULL) = that smallest distance (256 when no candidate).  The caller replays
+ * the map updates (Replace / AddObservation) in point order, as they touch host-side map state. */
+int orb_search_projected_best(orb_matcher* m, const orb_frame_view* f, const orb_projected_view* pts,
+                              const float* inv_level_sigma2, int max_dist, int32_t* best_idx, int32_t* best_dist,
+                              int32_t* nfound);
+
+/* SearchBySim3 (src/ORBmatcher.cc:1212-1455): pts1_in_kf2[i] = MapPoint of KF1 feature i projected
+ * into KF2 (valid = has a good, not already matched MapPoint that passes the gates), pts2_in_kf1
+ * likewise; match12[i] = KF2 feature j iff i -> j and j -> i agree, else -1. */
+int orb_search_by_sim3(orb_matcher* m, const orb_frame_view* kf1, const orb_projected_view* pts1_in_kf2,
+                       const orb_frame_view* kf2, const orb_projected_view* pts2_in_kf1, int32_t* match12,
+                       int32_t* nfound);
+
+/* SearchForInitialization (src/ORBmatcher.cc:429-578): level-0 keypoints of F1 searched in a
+ * window_size window of F2 around prev_matched; a later, closer match displaces an earlier one.
+ * match12[i] = F2 index or -1.  (The caller refreshes vbPrevMatched from match12, :571-574.) */
+int orb_search_for_initialization(orb_matcher* m, const orb_frame_view* f1, const orb_frame_view* f2,
+                                  const float* prev_matched_x, const float* prev_matched_y, int window_size,
+                                  float nn_ratio, int check_orientation, int32_t* match12, int32_t* nmatches);
+
 #ifdef __cplusplus
 }
 #endif

@@ -10,6 +10,11 @@
 //   orc_search_by_projection_last    <- ORBmatcher::SearchByProjection(C,L)    src/ORBmatcher.cc:1460-1619
 //   orc_search_by_bow                <- ORBmatcher::SearchByBoW(KF,F)          src/ORBmatcher.cc:164-306
 //   orc_search_for_triangulation     <- ORBmatcher::SearchForTriangulation     src/ORBmatcher.cc:718-900, 144-161
+//   orc_search_by_bow_keyframes      <- ORBmatcher::SearchByBoW(KF,KF)         src/ORBmatcher.cc:581-716
+//   orc_search_by_projection_claiming<- SearchByProjection(F,KF,found,th,dist) src/ORBmatcher.cc:1622-1759 and (KF,Scw,..) :311-427
+//   orc_search_projected_best        <- candidate loops of Fuse x2             src/ORBmatcher.cc:903-1207
+//   orc_search_by_sim3               <- ORBmatcher::SearchBySim3               src/ORBmatcher.cc:1212-1455
+//   orc_search_for_initialization    <- ORBmatcher::SearchForInitialization    src/ORBmatcher.cc:429-578
 //   three_maxima                     <- ORBmatcher::ComputeThreeMaxima         src/ORBmatcher.cc:1765-1809
 //
 // Float expressions of the form x*a + y*b are evaluated as fmaf(x, a, y*b): that is the code GCC
@@ -417,4 +422,200 @@ int orc_search_for_triangulation(const orb_frame_view* kf1, const orb_featvec_vi
     return nmatches;
 }
 
+
+// ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)   src/ORBmatcher.cc:581-716
+int orc_search_by_bow_keyframes(const orb_frame_view* kf1, const orb_featvec_view* fv1, const uint8_t* has_mp1, const orb_frame_view* kf2,
+                                const orb_featvec_view* fv2, const uint8_t* has_mp2, float nn_ratio, int check_orientation, int32_t* match12) {
+    for (int i = 0; i < kf1->n; ++i) match12[i] = -1;
+    std::vector<bool> vbMatched2(kf2->n, false);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int nmatches = 0;
+    int a = 0, b = 0;
+    while (a < fv1->n_nodes && b < fv2->n_nodes) {
+        if (fv1->node_ids[a] == fv2->node_ids[b]) {
+            for (int p = fv1->start[a]; p < fv1->start[a + 1]; ++p) {
+                const int idx1 = (int)fv1->items[p];
+                if (!has_mp1[idx1]) continue;                       // !pMP1 || pMP1->isBad()
+                const uint8_t* d1 = kf1->desc + 32 * (size_t)idx1;
+                int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+                for (int q = fv2->start[b]; q < fv2->start[b + 1]; ++q) {
+                    const int idx2 = (int)fv2->items[q];
+                    if (vbMatched2[idx2] || !has_mp2[idx2]) continue;
+                    const int dist = ddist(d1, kf2->desc + 32 * (size_t)idx2);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (bestDist1 < TH_LOW) {
+                    if ((float)bestDist1 < nn_ratio * (float)bestDist2) {
+                        match12[idx1] = bestIdx2;
+                        vbMatched2[bestIdx2] = true;
+                        if (check_orientation) rotHist[rot_bin(kf1->angle[idx1], kf2->angle[bestIdx2])].push_back(idx1);
+                        ++nmatches;
+                    }
+                }
+            }
+            ++a; ++b;
+        } else if (fv1->node_ids[a] < fv2->node_ids[b]) {
+            a = (int)(std::lower_bound(fv1->node_ids, fv1->node_ids + fv1->n_nodes, fv2->node_ids[b]) - fv1->node_ids);
+        } else {
+            b = (int)(std::lower_bound(fv2->node_ids, fv2->node_ids + fv2->n_nodes, fv1->node_ids[a]) - fv2->node_ids);
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx : rotHist[i]) { match12[idx] = -1; --nmatches; }
+        }
+    }
+    return nmatches;
+}
+
+// The search loops of
+//   SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist)   src/ORBmatcher.cc:1622-1759 (loop :1666-1712)
+//   SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th)         src/ORBmatcher.cc:311-427   (loop :371-420)
+// over points the caller has already projected and gated (orb_projected_view).  occupied =
+// CurrentFrame.mvpMapPoints[i2] != NULL / vpMatched[idx] != NULL; an accepted keypoint becomes occupied.
+int orc_search_by_projection_claiming(const orb_frame_view* f, const orb_projected_view* pts, const uint8_t* occupied, int max_dist,
+                                      int check_orientation, int32_t* match, int32_t* point_best_idx) {
+    Grid g; build_grid(*f, g);
+    std::vector<uint8_t> occ(f->n, 0);
+    for (int i = 0; i < f->n; ++i) { match[i] = -1; if (occupied) occ[i] = occupied[i]; }
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int nmatches = 0;
+    std::vector<int> vIndices;
+    for (int i = 0; i < pts->n; ++i) {
+        if (point_best_idx) point_best_idx[i] = -1;
+        if (!pts->valid[i]) continue;
+        features_in_area(*f, g, pts->u[i], pts->v[i], pts->radius[i], pts->min_level[i], pts->max_level[i], vIndices);
+        if (vIndices.empty()) continue;
+        const uint8_t* dMP = pts->desc + 32 * (size_t)i;
+        int bestDist = 256, bestIdx = -1;
+        for (int idx : vIndices) {
+            if (occ[idx]) continue;
+            const int dist = ddist(dMP, f->desc + 32 * (size_t)idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (bestDist <= max_dist && bestIdx >= 0) {
+            match[bestIdx] = i;
+            occ[bestIdx] = 1;
+            if (point_best_idx) point_best_idx[i] = bestIdx;
+            ++nmatches;
+            if (check_orientation) rotHist[rot_bin(pts->angle[i], f->angle[bestIdx])].push_back(bestIdx);
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; ++i)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) { match[idx] = -1; --nmatches; }
+    }
+    return nmatches;
+}
+
+// The candidate loop shared by Fuse(KF, MapPoints, th) src/ORBmatcher.cc:903-1054 (loop :960-1017, chi-square gate
+// when inv_level_sigma2 != NULL), Fuse(KF, Scw, ...) :1056-1207 (loop :1146-1174) and each direction of
+// SearchBySim3 :1212-1455 (loops :1299-1331, :1379-1411).
+int orc_search_projected_best(const orb_frame_view* f, const orb_projected_view* pts, const float* inv_level_sigma2, int max_dist,
+                              int32_t* best_idx, int32_t* best_dist) {
+    Grid g; build_grid(*f, g);
+    int nfound = 0;
+    std::vector<int> vIndices;
+    for (int i = 0; i < pts->n; ++i) {
+        best_idx[i] = -1;
+        if (best_dist) best_dist[i] = 256;
+        if (!pts->valid[i]) continue;
+        const float u = pts->u[i], v = pts->v[i];
+        features_in_area(*f, g, u, v, pts->radius[i], -1, -1, vIndices);     // KeyFrame::GetFeaturesInArea: no level filter
+        if (vIndices.empty()) continue;
+        const uint8_t* dMP = pts->desc + 32 * (size_t)i;
+        int bestDist = 256, bestIdx = -1;
+        for (int idx : vIndices) {
+            const int kpLevel = f->octave[idx];
+            if (kpLevel < pts->min_level[i] || kpLevel > pts->max_level[i]) continue;
+            if (inv_level_sigma2) {
+                const float kpx = f->x[idx], kpy = f->y[idx];
+                const float ex = u - kpx, ey = v - kpy;
+                if (f->u_right && f->u_right[idx] >= 0) {
+                    const float er = pts->ur[i] - f->u_right[idx];
+                    const float e2 = fmaf(er, er, fmaf(ex, ex, ey * ey));
+                    if (e2 * inv_level_sigma2[kpLevel] > 7.8) continue;
+                } else {
+                    const float e2 = fmaf(ex, ex, ey * ey);
+                    if (e2 * inv_level_sigma2[kpLevel] > 5.99) continue;
+                }
+            }
+            const int dist = ddist(dMP, f->desc + 32 * (size_t)idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (best_dist) best_dist[i] = bestDist;
+        if (bestDist <= max_dist && bestIdx >= 0) { best_idx[i] = bestIdx; ++nfound; }
+    }
+    return nfound;
+}
+
+// ORBmatcher::SearchBySim3   src/ORBmatcher.cc:1212-1455 (agreement step :1423-1439)
+int orc_search_by_sim3(const orb_frame_view* kf1, const orb_projected_view* pts1_in_kf2, const orb_frame_view* kf2,
+                       const orb_projected_view* pts2_in_kf1, int32_t* match12) {
+    std::vector<int32_t> vnMatch1(std::max(kf1->n, 1), -1), vnMatch2(std::max(kf2->n, 1), -1);
+    orc_search_projected_best(kf2, pts1_in_kf2, nullptr, TH_HIGH, vnMatch1.data(), nullptr);
+    orc_search_projected_best(kf1, pts2_in_kf1, nullptr, TH_HIGH, vnMatch2.data(), nullptr);
+    int nFound = 0;
+    for (int i1 = 0; i1 < kf1->n; ++i1) {
+        match12[i1] = -1;
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0) {
+            const int idx1 = vnMatch2[idx2];
+            if (idx1 == i1) { match12[i1] = idx2; ++nFound; }
+        }
+    }
+    return nFound;
+}
+
+// ORBmatcher::SearchForInitialization   src/ORBmatcher.cc:429-578
+int orc_search_for_initialization(const orb_frame_view* f1, const orb_frame_view* f2, const float* prev_x, const float* prev_y, int windowSize,
+                                  float nn_ratio, int check_orientation, int32_t* vnMatches12) {
+    Grid g; build_grid(*f2, g);
+    int nmatches = 0;
+    for (int i = 0; i < f1->n; ++i) vnMatches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    std::vector<int> vMatchedDistance(f2->n, INT_MAX), vnMatches21(f2->n, -1);
+    std::vector<int> vIndices2;
+    for (int i1 = 0; i1 < f1->n; ++i1) {
+        const int level1 = f1->octave[i1];
+        if (level1 > 0) continue;
+        features_in_area(*f2, g, prev_x[i1], prev_y[i1], (float)windowSize, level1, level1, vIndices2);
+        if (vIndices2.empty()) continue;
+        const uint8_t* d1 = f1->desc + 32 * (size_t)i1;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            const int dist = ddist(d1, f2->desc + 32 * (size_t)i2);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * nn_ratio) {
+                if (vnMatches21[bestIdx2] >= 0) { vnMatches12[vnMatches21[bestIdx2]] = -1; --nmatches; }
+                vnMatches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                ++nmatches;
+                if (check_orientation) rotHist[rot_bin(f1->angle[i1], f2->angle[bestIdx2])].push_back(i1);
+            }
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i])
+                if (vnMatches12[idx1] >= 0) { vnMatches12[idx1] = -1; --nmatches; }
+        }
+    }
+    return nmatches;
+}
 }  // extern "C"

@@ -24,7 +24,8 @@ EXPORTS = [
     "orb_matcher_create", "orb_matcher_destroy", "orb_matcher_stream", "orb_matcher_launch_count", "orb_matcher_sync",
     "orb_descriptor_distance", "orb_match_bruteforce", "orb_match_bruteforce_device", "orb_assign_features_to_grid",
     "orb_search_by_projection_mappoints", "orb_search_by_projection_lastframe", "orb_search_by_bow",
-    "orb_search_for_triangulation",
+    "orb_search_for_triangulation", "orb_search_by_bow_keyframes", "orb_search_by_projection_claiming",
+    "orb_search_projected_best", "orb_search_by_sim3", "orb_search_for_initialization",
 ]
 
 

@@ -208,13 +208,19 @@ __global__ void k_prep_lastframe(int n, const uint8_t* __restrict__ valid, const
     q[i] = Q;
 }
 
+// static per-candidate filters of k_area_candidates
+#define FILTER_STEREO_WINDOW 0   // |proj_xr - mvuRight| <= r for stereo keypoints (:95-100, :1555-1561)
+#define FILTER_NONE 1
+#define FILTER_FUSE_CHI2 2       // chi-square reprojection test of Fuse (:977-1003)
+
 // Frame::GetFeaturesInArea + the static candidate filters, one warp per query, in the
 // reference's order (ix, then iy, then insertion order).  FILL=false counts, FILL=true writes
 // packed candidates: index (16 bits) | distance << 16 (9 bits) | octave << 25.
 template <bool FILL>
 __global__ void __launch_bounds__(256)
-k_area_candidates(int nq, const Query* __restrict__ q, const uint8_t* __restrict__ qdesc, DFrame F, int* __restrict__ counts,
-                  const int* __restrict__ starts, uint32_t* __restrict__ cands) {
+k_area_candidates(int nq, const Query* __restrict__ q, const uint8_t* __restrict__ qdesc, DFrame F, int filter,
+                  const float* __restrict__ inv_sigma2, int* __restrict__ counts, const int* __restrict__ starts,
+                  uint32_t* __restrict__ cands) {
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (w >= nq) return;
     const Query Q = q[w];
@@ -253,9 +259,22 @@ k_area_candidates(int nq, const Query* __restrict__ q, const uint8_t* __restrict
                             const float dx = __fsub_rn(F.x[idx], x), dy = __fsub_rn(F.y[idx], y);
                             ok = fabsf(dx) < r && fabsf(dy) < r;
                         }
-                        if (ok && F.u_right) {
+                        if (ok && filter == FILTER_STEREO_WINDOW && F.u_right) {
                             const float ur = F.u_right[idx];
                             if (ur > 0 && fabsf(__fsub_rn(Q.xr, ur)) > r) ok = false;
+                        }
+                        if (ok && filter == FILTER_FUSE_CHI2) {
+                            // reprojection test of Fuse(KF, MapPoints) (reference :977-1003), GCC-style contraction
+                            const float ex = __fsub_rn(x, F.x[idx]), ey = __fsub_rn(y, F.y[idx]);
+                            const float kpr = F.u_right ? F.u_right[idx] : -1.f;
+                            if (kpr >= 0) {
+                                const float er = __fsub_rn(Q.xr, kpr);
+                                const float e2 = __fmaf_rn(er, er, __fmaf_rn(ex, ex, __fmul_rn(ey, ey)));
+                                if ((double)__fmul_rn(e2, inv_sigma2[oct]) > 7.8) ok = false;
+                            } else {
+                                const float e2 = __fmaf_rn(ex, ex, __fmul_rn(ey, ey));
+                                if ((double)__fmul_rn(e2, inv_sigma2[oct]) > 5.99) ok = false;
+                            }
                         }
                     }
                     const unsigned m = __ballot_sync(0xffffffffu, ok);
@@ -365,16 +384,21 @@ __device__ void rot_cull_warp(const int* __restrict__ hist_idx, const int* __res
 
 // MODE 0: SearchByProjection(Frame, MapPoints)  -- best + second best with levels, ratio test
 // MODE 1: SearchByProjection(Cur, Last)         -- best only, rotation histogram
+// MODE 2: projected points with claiming (relocalisation :1622-1759, loop :311-427) -- best only, accept
+//         <= max_dist, every accepted keypoint is closed to later points, optional rotation histogram
 __global__ void __launch_bounds__(32)
 k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* __restrict__ starts, const uint32_t* __restrict__ cands,
                      const uint8_t* __restrict__ blocks, const float* __restrict__ q_angle, DFrame F, const uint8_t* __restrict__ occupied,
-                     uint8_t* __restrict__ occ, float nn_ratio, int check_ori, int* __restrict__ match, int* __restrict__ hist_idx,
+                     uint8_t* __restrict__ occ, float nn_ratio, int check_ori, int max_dist, int* __restrict__ match,
+                     int* __restrict__ q_best_idx, int* __restrict__ q_best_dist, int* __restrict__ hist_idx,
                      int* __restrict__ hist_bin, int* __restrict__ nmatches_out) {
     __shared__ int s_cnt[32];
     const int lane = threadIdx.x;
     for (int i = lane; i < F.n; i += 32) { match[i] = -1; occ[i] = occupied ? occupied[i] : 0; }
     __syncwarp();
     int nmatches = 0, n_hist = 0;
+    if (q_best_idx) for (int i = lane; i < nq; i += 32) { q_best_idx[i] = -1; q_best_dist[i] = 256; }
+    __syncwarp();
     for (int w = 0; w < nq; ++w) {
         const int c0 = starts[w], c1 = starts[w + 1];
         if (c0 == c1) continue;
@@ -404,10 +428,19 @@ k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* _
                     ++nmatches;
                 }
             }
-        } else {
+        } else if (mode == 1) {
             if (bestDist <= M_TH_HIGH) {
                 if (lane == 0) {
                     match[bestIdx] = w; occ[bestIdx] = blocks[w];
+                    if (check_ori) { hist_idx[n_hist] = bestIdx; hist_bin[n_hist] = rot_bin(q_angle[w], F.angle[bestIdx]); }
+                }
+                ++nmatches; ++n_hist;
+            }
+        } else {
+            if (bestDist <= max_dist) {
+                if (lane == 0) {
+                    match[bestIdx] = w; occ[bestIdx] = 1;
+                    q_best_idx[w] = bestIdx; q_best_dist[w] = bestDist;
                     if (check_ori) { hist_idx[n_hist] = bestIdx; hist_bin[n_hist] = rot_bin(q_angle[w], F.angle[bestIdx]); }
                 }
                 ++nmatches; ++n_hist;
@@ -417,7 +450,33 @@ k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* _
     }
     if (lane == 0) *nmatches_out = nmatches;
     __syncwarp();
-    if (mode == 1 && check_ori) rot_cull_warp(hist_idx, hist_bin, n_hist, match, nmatches_out, s_cnt);
+    if (mode >= 1 && check_ori) rot_cull_warp(hist_idx, hist_bin, n_hist, match, nmatches_out, s_cnt);
+}
+
+// Projected points WITHOUT claiming (SearchBySim3 :1212-1455 per direction, Fuse :903-1207): every point is
+// independent; one warp per point takes the first minimum-distance candidate (strict <).
+__global__ void __launch_bounds__(256)
+k_best_independent(int nq, const int* __restrict__ starts, const uint32_t* __restrict__ cands, const uint8_t* __restrict__ occupied,
+                   int max_dist, int* __restrict__ q_best_idx, int* __restrict__ q_best_dist, int* __restrict__ nmatches_out) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= nq) return;
+    const int c0 = starts[w], c1 = starts[w + 1];
+    unsigned best = 0xffffffffu;
+    for (int p = c0 + lane; p < c1; p += 32) {
+        const uint32_t c = cands[p];
+        if (occupied && occupied[c & 0xffffu]) continue;
+        best = min(best, (((c >> 16) & 0x1ffu) << 16) | (unsigned)min(p - c0, 0xffff));
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane == 0) {
+        int bi = -1, bd = 256;
+        if (best != 0xffffffffu) {
+            bd = (int)(best >> 16);
+            if (bd <= max_dist) { bi = (int)(cands[c0 + (best & 0xffffu)] & 0xffffu); atomicAdd(nmatches_out, 1); }
+        }
+        q_best_idx[w] = bi; q_best_dist[w] = bd;
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -475,6 +534,122 @@ k_resolve_bow(int n_entries, const BowEntry* __restrict__ e, const uint32_t* __r
     if (lane == 0) *nmatches_out = nmatches;
     __syncwarp();
     if (check_ori) rot_cull_warp(hist_idx, hist_bin, n_hist, match_f, nmatches_out, s_cnt);
+}
+
+// SearchByBoW(KF1, KF2) (reference :581-716): as k_resolve_bow but both features need a MapPoint, KF2
+// features are claimed through vbMatched2 (which the rotation cull does NOT release), the threshold is
+// strict (< TH_LOW) and the result is indexed by the KF1 feature.
+__global__ void __launch_bounds__(32)
+k_resolve_bow_kf(int n_entries, const BowEntry* __restrict__ e, const uint32_t* __restrict__ cands, const float* __restrict__ angle1,
+                 const float* __restrict__ angle2, int n1, int n2, const uint8_t* __restrict__ has2, uint8_t* __restrict__ closed2,
+                 float nn_ratio, int check_ori, int* __restrict__ match12, int* __restrict__ hist_idx, int* __restrict__ hist_bin,
+                 int* __restrict__ nmatches_out) {
+    __shared__ int s_cnt[32];
+    const int lane = threadIdx.x;
+    for (int i = lane; i < n1; i += 32) match12[i] = -1;
+    for (int i = lane; i < n2; i += 32) closed2[i] = has2[i] ? 0 : 1;   // !pMP2 (or bad) -> never a candidate
+    __syncwarp();
+    int nmatches = 0, n_hist = 0;
+    for (int w = 0; w < n_entries; ++w) {
+        const BowEntry E = e[w];
+        const int cnt = E.f1 - E.f0;
+        Best2 v; v.b = 0xffffffffu; v.s = 0xffffffffu;
+        for (int p = lane; p < cnt; p += 32) {
+            const uint32_t c = cands[E.c_start + p];
+            if (closed2[c & 0xffffu]) continue;
+            Best2 t; t.b = (((c >> 16) & 0x1ffu) << 16) | (unsigned)p; t.s = 0xffffffffu;
+            v = merge2(v, t);
+        }
+        v = warp_best2(v);
+        if (v.b == 0xffffffffu) continue;
+        const int d1 = (int)(v.b >> 16), d2 = v.s == 0xffffffffu ? 256 : (int)(v.s >> 16);
+        if (d1 < M_TH_LOW && (float)d1 < __fmul_rn(nn_ratio, (float)d2)) {
+            const int idx2 = (int)(cands[E.c_start + (v.b & 0xffffu)] & 0xffffu);
+            if (lane == 0) {
+                match12[E.q_idx] = idx2; closed2[idx2] = 1;
+                if (check_ori) { hist_idx[n_hist] = E.q_idx; hist_bin[n_hist] = rot_bin(angle1[E.q_idx], angle2[idx2]); }
+            }
+            ++nmatches; ++n_hist;
+        }
+        __syncwarp();
+    }
+    if (lane == 0) *nmatches_out = nmatches;
+    __syncwarp();
+    if (check_ori) rot_cull_warp(hist_idx, hist_bin, n_hist, match12, nmatches_out, s_cnt);
+}
+
+// SearchForInitialization (reference :429-578): sequential over the level-0 keypoints of F1; a candidate i2 is
+// skipped when an earlier match holds it with a distance <= the new one (vMatchedDistance), otherwise the
+// earlier match is displaced.  Displaced entries stay in the rotation histogram (they count towards the bin
+// sizes) and the cull only clears entries that are still matched (:556-562).
+__global__ void __launch_bounds__(32)
+k_resolve_initialization(int nq, const int* __restrict__ starts, const uint32_t* __restrict__ cands, const float* __restrict__ angle1,
+                         const float* __restrict__ angle2, int n2, float nn_ratio, int check_ori, int* __restrict__ match12,
+                         int* __restrict__ match21, int* __restrict__ mdist, int* __restrict__ hist_idx, int* __restrict__ hist_bin,
+                         int* __restrict__ nmatches_out) {
+    __shared__ int s_cnt[32];
+    const int lane = threadIdx.x;
+    for (int i = lane; i < nq; i += 32) match12[i] = -1;
+    for (int i = lane; i < n2; i += 32) { match21[i] = -1; mdist[i] = 0x7fffffff; }
+    __syncwarp();
+    int nmatches = 0, n_hist = 0;
+    for (int w = 0; w < nq; ++w) {
+        const int c0 = starts[w], c1 = starts[w + 1];
+        if (c0 == c1) continue;
+        Best2 v; v.b = 0xffffffffu; v.s = 0xffffffffu;
+        for (int p = c0 + lane; p < c1; p += 32) {
+            const uint32_t c = cands[p];
+            const int d = (int)((c >> 16) & 0x1ffu);
+            if (mdist[c & 0xffffu] <= d) continue;
+            Best2 t; t.b = ((unsigned)d << 16) | (unsigned)(p - c0); t.s = 0xffffffffu;
+            v = merge2(v, t);
+        }
+        v = warp_best2(v);
+        if (v.b == 0xffffffffu) continue;
+        const int bestDist = (int)(v.b >> 16);
+        const float second = v.s == 0xffffffffu ? 2147483648.f : (float)(int)(v.s >> 16);   // (float)INT_MAX
+        if (bestDist <= M_TH_LOW && (float)bestDist < __fmul_rn(second, nn_ratio)) {
+            const int i2 = (int)(cands[c0 + (v.b & 0xffffu)] & 0xffffu);
+            const int old = match21[i2];
+            if (lane == 0) {
+                if (old >= 0) match12[old] = -1;
+                match12[w] = i2; match21[i2] = w; mdist[i2] = bestDist;
+                if (check_ori) { hist_idx[n_hist] = w; hist_bin[n_hist] = rot_bin(angle1[w], angle2[i2]); }
+            }
+            if (old >= 0) --nmatches;
+            ++nmatches; ++n_hist;
+        }
+        __syncwarp();
+    }
+    __syncwarp();
+    if (check_ori) {
+        if (lane < M_HISTO + 2) s_cnt[lane] = 0;
+        __syncwarp();
+        for (int i = lane; i < n_hist; i += 32) atomicAdd(&s_cnt[hist_bin[i]], 1);
+        __syncwarp();
+        int i1, i2, i3;
+        three_maxima(s_cnt, i1, i2, i3);
+        int removed = 0;
+        for (int i = lane; i < n_hist; i += 32) {
+            const int b = hist_bin[i];
+            if (b != i1 && b != i2 && b != i3 && match12[hist_idx[i]] >= 0) { match12[hist_idx[i]] = -1; ++removed; }
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) removed += __shfl_xor_sync(0xffffffffu, removed, o);
+        nmatches -= removed;
+    }
+    if (lane == 0) *nmatches_out = nmatches;
+}
+
+// SearchBySim3 agreement (reference :1423-1439): keep i1 -> i2 only when i2 -> i1
+__global__ void k_mutual_check(int n1, int n2, const int* __restrict__ m1, const int* __restrict__ m2, int* __restrict__ match12,
+                               int* __restrict__ nfound) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n1) return;
+    const int i2 = m1[i];
+    int r = -1;
+    if (i2 >= 0 && i2 < n2 && m2[i2] == i) { r = i2; atomicAdd(nfound, 1); }
+    match12[i] = r;
 }
 
 // SearchForTriangulation: no claiming in the reference (vbMatched2 is never set), so every query
@@ -718,35 +893,59 @@ int orb_assign_features_to_grid(orb_matcher* m, const float* kp_x, const float* 
     return ORB_OK;
 }
 
-// shared tail of the two projection searches: count -> scan -> fill -> sequential resolve
-static int projection_common(orb_matcher* m, int mode, int nq, const Query* dq, const uint8_t* d_qdesc, const uint8_t* d_blocks,
-                             const float* d_qangle, const DFrame& F, const uint8_t* occupied, float nn_ratio, int check_ori,
-                             int32_t* match, int32_t* nmatches) {
+// shared tail of the projection searches: count -> scan -> fill -> resolve
+struct ProjOpts {
+    int mode = 0;                 // k_resolve_projection mode, or -1: independent points (k_best_independent)
+    int filter = FILTER_STEREO_WINDOW;
+    const float* d_inv_sigma2 = nullptr;
+    float nn_ratio = 0.f;
+    int check_ori = 0;
+    int max_dist = M_TH_HIGH;
+    int32_t* q_best_idx = nullptr;   // host outputs per query (modes 2 and -1)
+    int32_t* q_best_dist = nullptr;
+};
+
+static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Query* dq, const uint8_t* d_qdesc, const uint8_t* d_blocks,
+                             const float* d_qangle, const DFrame& F, const uint8_t* occupied, int32_t* match, int32_t* nmatches) {
     int st;
-    int *counts, *starts, *dmatch, *hidx, *hbin;
+    int *counts, *starts, *dmatch, *hidx, *hbin, *qbi = nullptr, *qbd = nullptr;
     uint8_t* occ; const uint8_t* d_occupied = nullptr;
     if ((st = ws_alloc(m, &counts, std::max(nq, 1))) != ORB_OK || (st = ws_alloc(m, &starts, nq + 1)) != ORB_OK) return st;
     if ((st = ws_alloc(m, &dmatch, std::max(F.n, 1))) != ORB_OK || (st = ws_alloc(m, &occ, std::max(F.n, 1))) != ORB_OK) return st;
     if ((st = ws_alloc(m, &hidx, std::max(nq, 1))) != ORB_OK || (st = ws_alloc(m, &hbin, std::max(nq, 1))) != ORB_OK) return st;
+    if (o.mode == 2 || o.mode == -1) {
+        if ((st = ws_alloc(m, &qbi, std::max(nq, 1))) != ORB_OK || (st = ws_alloc(m, &qbd, std::max(nq, 1))) != ORB_OK) return st;
+    }
     if (occupied) { if ((st = ws_upload(m, &d_occupied, occupied, F.n)) != ORB_OK) return st; }
+    const int filter = o.filter; const float* d_inv_sigma2 = o.d_inv_sigma2;
     if (nq > 0) {
         const int blocks = (nq * 32 + 255) / 256;
-        k_area_candidates<false><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, counts, nullptr, nullptr);
+        k_area_candidates<false><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, counts, nullptr, nullptr);
         k_scan<<<1, 1024, 0, m->stream>>>(counts, nq, starts);
         int total = 0;
         ORB_CUDA(cudaMemcpyAsync(&total, starts + nq, 4, cudaMemcpyDeviceToHost, m->stream));
         ORB_CUDA(cudaStreamSynchronize(m->stream));
         if ((size_t)total > m->cands_cap) { orb_set_error("candidate workspace too small"); return ORB_ERR_CAPACITY; }
-        k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, nullptr, starts, m->d_cands);
+        k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, nullptr, starts, m->d_cands);
         m->launches += 3;
     } else {
         ORB_CUDA(cudaMemsetAsync(starts, 0, 4, m->stream));
     }
-    k_resolve_projection<<<1, 32, 0, m->stream>>>(mode, nq, dq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied, occ, nn_ratio, check_ori,
-                                                  dmatch, hidx, hbin, m->d_scal);
-    m->launches++;
+    if (o.mode == -1) {
+        ORB_CUDA(cudaMemsetAsync(m->d_scal, 0, 4, m->stream));
+        if (nq > 0) {
+            k_best_independent<<<(nq * 32 + 255) / 256, 256, 0, m->stream>>>(nq, starts, m->d_cands, d_occupied, o.max_dist, qbi, qbd, m->d_scal);
+            m->launches++;
+        }
+    } else {
+        k_resolve_projection<<<1, 32, 0, m->stream>>>(o.mode, nq, dq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied, occ, o.nn_ratio,
+                                                      o.check_ori, o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal);
+        m->launches++;
+    }
     ORB_CUDA(cudaGetLastError());
-    if (F.n > 0) ORB_CUDA(cudaMemcpyAsync(match, dmatch, (size_t)F.n * 4, cudaMemcpyDeviceToHost, m->stream));
+    if (match && o.mode != -1 && F.n > 0) ORB_CUDA(cudaMemcpyAsync(match, dmatch, (size_t)F.n * 4, cudaMemcpyDeviceToHost, m->stream));
+    if (o.q_best_idx && nq > 0) ORB_CUDA(cudaMemcpyAsync(o.q_best_idx, qbi, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
+    if (o.q_best_dist && nq > 0) ORB_CUDA(cudaMemcpyAsync(o.q_best_dist, qbd, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
     ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
     ORB_CUDA(cudaStreamSynchronize(m->stream));
     return ORB_OK;
@@ -768,7 +967,8 @@ int orb_search_by_projection_mappoints(orb_matcher* m, const orb_frame_view* f, 
         (st = ws_upload(m, &db, mps->blocks, nq)) != ORB_OK || (st = ws_alloc(m, &dq, std::max(nq, 1))) != ORB_OK) return st;
     if (mps->proj_xr) { if ((st = ws_upload(m, &dxr, mps->proj_xr, nq)) != ORB_OK) return st; }
     if (nq > 0) { k_prep_mappoints<<<(nq + 255) / 256, 256, 0, m->stream>>>(nq, dv, dx, dy, dxr, dl, dvc, th, F, dq); m->launches++; }
-    return projection_common(m, 0, nq, dq, dd, db, nullptr, F, occupied, nn_ratio, 0, match, nmatches);
+    ProjOpts o; o.mode = 0; o.nn_ratio = nn_ratio;
+    return projection_common(m, o, nq, dq, dd, db, nullptr, F, occupied, match, nmatches);
 }
 
 int orb_search_by_projection_lastframe(orb_matcher* m, const orb_frame_view* cur, const orb_lastframe_view* last, const orb_camera* cam,
@@ -788,7 +988,8 @@ int orb_search_by_projection_lastframe(orb_matcher* m, const orb_frame_view* cur
         (st = ws_upload(m, &dd, last->desc, (size_t)nq * 32)) != ORB_OK || (st = ws_upload(m, &db, last->blocks, nq)) != ORB_OK ||
         (st = ws_alloc(m, &dq, std::max(nq, 1))) != ORB_OK) return st;
     if (nq > 0) { k_prep_lastframe<<<(nq + 255) / 256, 256, 0, m->stream>>>(nq, dv, dx, dy, dz, doct, *cam, th, forward, backward, F, dq); m->launches++; }
-    return projection_common(m, 1, nq, dq, dd, db, da, F, occupied, 0.f, check_orientation, match, nmatches);
+    ProjOpts o; o.mode = 1; o.check_ori = check_orientation;
+    return projection_common(m, o, nq, dq, dd, db, da, F, occupied, match, nmatches);
 }
 
 static int check_fv(const orb_featvec_view* v) {
@@ -884,4 +1085,176 @@ int orb_search_for_triangulation(orb_matcher* m, const orb_frame_view* kf1, cons
     return ORB_OK;
 }
 
+
+// ---- searches over caller-projected points (reference :311-427, :903-1207, :1212-1455, :1622-1759) ----
+static int check_points(const orb_projected_view* p, int need_angle) {
+    return p && p->n >= 0 && (p->n == 0 || (p->valid && p->u && p->v && p->radius && p->min_level && p->max_level && p->desc &&
+                                            (!need_angle || p->angle)));
+}
+
+static int upload_points(orb_matcher* m, const orb_projected_view* p, const Query** dq, const uint8_t** dd, const float** da) {
+    std::vector<Query> q((size_t)std::max(p->n, 1));
+    for (int i = 0; i < p->n; ++i) {
+        Query& Q = q[i];
+        Q.valid = p->valid[i]; Q.x = p->u[i]; Q.y = p->v[i]; Q.r = p->radius[i]; Q.xr = p->ur ? p->ur[i] : 0.f;
+        Q.min_level = p->min_level[i]; Q.max_level = p->max_level[i]; Q.pad = 0;
+    }
+    int st;
+    *da = nullptr;
+    if ((st = ws_upload(m, dq, q.data(), (size_t)p->n)) != ORB_OK || (st = ws_upload(m, dd, p->desc, (size_t)p->n * 32)) != ORB_OK) return st;
+    if (p->angle) { if ((st = ws_upload(m, da, p->angle, (size_t)p->n)) != ORB_OK) return st; }
+    return ORB_OK;
+}
+
+int orb_search_by_projection_claiming(orb_matcher* m, const orb_frame_view* f, const orb_projected_view* pts, const uint8_t* occupied,
+                                      int max_dist, int check_orientation, int32_t* match, int32_t* point_best_idx, int32_t* nmatches) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!f || !check_points(pts, check_orientation) || !match || !nmatches || max_dist < 0 || max_dist > 255 ||
+        (check_orientation && f->n > 0 && !f->angle)) return ORB_ERR_BAD_ARG;
+    DFrame F;
+    if ((st = upload_frame(m, f, &F, true)) != ORB_OK) return st;
+    const Query* dq; const uint8_t* dd; const float* da;
+    if ((st = upload_points(m, pts, &dq, &dd, &da)) != ORB_OK) return st;
+    ProjOpts o; o.mode = 2; o.filter = FILTER_NONE; o.check_ori = check_orientation; o.max_dist = max_dist; o.q_best_idx = point_best_idx;
+    return projection_common(m, o, pts->n, dq, dd, nullptr, da, F, occupied, match, nmatches);
+}
+
+int orb_search_projected_best(orb_matcher* m, const orb_frame_view* f, const orb_projected_view* pts, const float* inv_level_sigma2,
+                              int max_dist, int32_t* best_idx, int32_t* best_dist, int32_t* nfound) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!f || !check_points(pts, 0) || !best_idx || !nfound || max_dist < 0 || max_dist > 255) return ORB_ERR_BAD_ARG;
+    DFrame F;
+    if ((st = upload_frame(m, f, &F, true)) != ORB_OK) return st;
+    const Query* dq; const uint8_t* dd; const float* da;
+    if ((st = upload_points(m, pts, &dq, &dd, &da)) != ORB_OK) return st;
+    ProjOpts o; o.mode = -1; o.filter = FILTER_NONE; o.max_dist = max_dist; o.q_best_idx = best_idx; o.q_best_dist = best_dist;
+    if (inv_level_sigma2) {
+        float s[ORB_MAX_LEVELS];
+        for (int i = 0; i < ORB_MAX_LEVELS; ++i) s[i] = i < f->n_levels ? inv_level_sigma2[i] : 1.f;
+        if ((st = ws_upload(m, &o.d_inv_sigma2, s, (size_t)ORB_MAX_LEVELS)) != ORB_OK) return st;
+        o.filter = FILTER_FUSE_CHI2;
+    }
+    return projection_common(m, o, pts->n, dq, dd, nullptr, nullptr, F, nullptr, nullptr, nfound);
+}
+
+int orb_search_by_sim3(orb_matcher* m, const orb_frame_view* kf1, const orb_projected_view* pts1_in_kf2, const orb_frame_view* kf2,
+                       const orb_projected_view* pts2_in_kf1, int32_t* match12, int32_t* nfound) {
+    if (!m || !kf1 || !kf2 || !check_points(pts1_in_kf2, 0) || !check_points(pts2_in_kf1, 0) || !match12 || !nfound ||
+        pts1_in_kf2->n != kf1->n || pts2_in_kf1->n != kf2->n) return ORB_ERR_BAD_ARG;
+    // vnMatch1 / vnMatch2 (reference :1290-1340, :1343-1420): two independent best-candidate searches
+    std::vector<int32_t> m1((size_t)std::max(kf1->n, 1)), m2((size_t)std::max(kf2->n, 1));
+    int32_t n1 = 0, n2 = 0;
+    int st = orb_search_projected_best(m, kf2, pts1_in_kf2, nullptr, M_TH_HIGH, m1.data(), nullptr, &n1);
+    if (st != ORB_OK) return st;
+    if ((st = orb_search_projected_best(m, kf1, pts2_in_kf1, nullptr, M_TH_HIGH, m2.data(), nullptr, &n2)) != ORB_OK) return st;
+    // mutual agreement (:1423-1439)
+    if ((st = begin_call(m)) != ORB_OK) return st;
+    const int32_t *d1, *d2; int* d12;
+    if ((st = ws_upload(m, &d1, m1.data(), (size_t)kf1->n)) != ORB_OK || (st = ws_upload(m, &d2, m2.data(), (size_t)kf2->n)) != ORB_OK ||
+        (st = ws_alloc(m, &d12, std::max(kf1->n, 1))) != ORB_OK) return st;
+    ORB_CUDA(cudaMemsetAsync(m->d_scal, 0, 4, m->stream));
+    if (kf1->n > 0) {
+        k_mutual_check<<<(kf1->n + 255) / 256, 256, 0, m->stream>>>(kf1->n, kf2->n, d1, d2, d12, m->d_scal);
+        m->launches++;
+        ORB_CUDA(cudaGetLastError());
+        ORB_CUDA(cudaMemcpyAsync(match12, d12, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, m->stream));
+    }
+    ORB_CUDA(cudaMemcpyAsync(nfound, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+
+int orb_search_for_initialization(orb_matcher* m, const orb_frame_view* f1, const orb_frame_view* f2, const float* prev_matched_x,
+                                  const float* prev_matched_y, int window_size, float nn_ratio, int check_orientation, int32_t* match12,
+                                  int32_t* nmatches) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!f1 || !f2 || !match12 || !nmatches || (f1->n > 0 && (!prev_matched_x || !prev_matched_y || !f1->octave)) ||
+        (check_orientation && ((f1->n > 0 && !f1->angle) || (f2->n > 0 && !f2->angle)))) return ORB_ERR_BAD_ARG;
+    DFrame F2;
+    if ((st = upload_frame(m, f2, &F2, true)) != ORB_OK) return st;
+    const int nq = f1->n;
+    std::vector<Query> q((size_t)std::max(nq, 1));
+    for (int i = 0; i < nq; ++i) {
+        Query& Q = q[i];
+        Q.valid = f1->octave[i] > 0 ? 0 : 1;          // level1 > 0 -> continue (:449-451)
+        Q.x = prev_matched_x[i]; Q.y = prev_matched_y[i]; Q.r = (float)window_size; Q.xr = 0.f;
+        Q.min_level = 0; Q.max_level = 0; Q.pad = 0;  // GetFeaturesInArea(..., level1, level1) with level1 == 0
+    }
+    const Query* dq; const uint8_t* dd; const float* da1 = nullptr;
+    int *counts, *starts, *d12, *d21, *dmd, *hidx, *hbin;
+    if ((st = ws_upload(m, &dq, q.data(), (size_t)nq)) != ORB_OK || (st = ws_upload(m, &dd, f1->desc, (size_t)nq * 32)) != ORB_OK ||
+        (st = ws_alloc(m, &counts, std::max(nq, 1))) != ORB_OK || (st = ws_alloc(m, &starts, nq + 1)) != ORB_OK ||
+        (st = ws_alloc(m, &d12, std::max(nq, 1))) != ORB_OK || (st = ws_alloc(m, &d21, std::max(f2->n, 1))) != ORB_OK ||
+        (st = ws_alloc(m, &dmd, std::max(f2->n, 1))) != ORB_OK || (st = ws_alloc(m, &hidx, std::max(nq, 1))) != ORB_OK ||
+        (st = ws_alloc(m, &hbin, std::max(nq, 1))) != ORB_OK) return st;
+    if (f1->angle) { if ((st = ws_upload(m, &da1, f1->angle, (size_t)nq)) != ORB_OK) return st; }
+    if (nq > 0) {
+        const int blocks = (nq * 32 + 255) / 256;
+        k_area_candidates<false><<<blocks, 256, 0, m->stream>>>(nq, dq, dd, F2, FILTER_NONE, nullptr, counts, nullptr, nullptr);
+        k_scan<<<1, 1024, 0, m->stream>>>(counts, nq, starts);
+        int total = 0;
+        ORB_CUDA(cudaMemcpyAsync(&total, starts + nq, 4, cudaMemcpyDeviceToHost, m->stream));
+        ORB_CUDA(cudaStreamSynchronize(m->stream));
+        if ((size_t)total > m->cands_cap) { orb_set_error("candidate workspace too small"); return ORB_ERR_CAPACITY; }
+        k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, dd, F2, FILTER_NONE, nullptr, nullptr, starts, m->d_cands);
+        m->launches += 3;
+    } else {
+        ORB_CUDA(cudaMemsetAsync(starts, 0, 4, m->stream));
+    }
+    k_resolve_initialization<<<1, 32, 0, m->stream>>>(nq, starts, m->d_cands, da1, F2.angle, f2->n, nn_ratio, check_orientation, d12, d21, dmd,
+                                                      hidx, hbin, m->d_scal);
+    m->launches++;
+    ORB_CUDA(cudaGetLastError());
+    if (nq > 0) ORB_CUDA(cudaMemcpyAsync(match12, d12, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+
+int orb_search_by_bow_keyframes(orb_matcher* m, const orb_frame_view* kf1, const orb_featvec_view* fv1, const uint8_t* kf1_has_mappoint,
+                                const orb_frame_view* kf2, const orb_featvec_view* fv2, const uint8_t* kf2_has_mappoint, float nn_ratio,
+                                int check_orientation, int32_t* match12, int32_t* nmatches) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!kf1 || !kf2 || !check_fv(fv1) || !check_fv(fv2) || !kf1_has_mappoint || !kf2_has_mappoint || !match12 || !nmatches ||
+        (check_orientation && (!kf1->angle || !kf2->angle))) return ORB_ERR_BAD_ARG;
+    DFrame K1, K2;
+    if ((st = upload_frame(m, kf1, &K1, false)) != ORB_OK || (st = upload_frame(m, kf2, &K2, false)) != ORB_OK) return st;
+    std::vector<std::pair<int, int>> nodes;
+    merge_join(fv1, fv2, nodes);
+    std::vector<BowEntry> entries;
+    size_t total = 0;
+    for (auto& ab : nodes) {
+        const int f0 = fv2->start[ab.second], f1 = fv2->start[ab.second + 1];
+        for (int p = fv1->start[ab.first]; p < fv1->start[ab.first + 1]; ++p) {
+            const int qi = (int)fv1->items[p];
+            if (qi < 0 || qi >= kf1->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
+            if (!kf1_has_mappoint[qi] || f1 == f0) continue;
+            BowEntry e; e.q_idx = qi; e.f0 = f0; e.f1 = f1; e.c_start = (int)total;
+            entries.push_back(e);
+            total += (size_t)(f1 - f0);
+        }
+    }
+    if (total > m->cands_cap) { orb_set_error("candidate workspace too small"); return ORB_ERR_CAPACITY; }
+    const int ne = (int)entries.size();
+    const int n_items2 = fv2->n_nodes ? fv2->start[fv2->n_nodes] : 0;
+    for (int i = 0; i < n_items2; ++i) if (fv2->items[i] >= (uint32_t)kf2->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
+    const BowEntry* de; const uint32_t* ditems; const uint8_t* dhas2; uint8_t* dclosed; int *dmatch, *hidx, *hbin;
+    if ((st = ws_upload(m, &de, entries.data(), ne)) != ORB_OK || (st = ws_upload(m, &ditems, fv2->items, n_items2)) != ORB_OK ||
+        (st = ws_upload(m, &dhas2, kf2_has_mappoint, kf2->n)) != ORB_OK || (st = ws_alloc(m, &dclosed, std::max(kf2->n, 1))) != ORB_OK ||
+        (st = ws_alloc(m, &dmatch, std::max(kf1->n, 1))) != ORB_OK || (st = ws_alloc(m, &hidx, std::max(ne, 1))) != ORB_OK ||
+        (st = ws_alloc(m, &hbin, std::max(ne, 1))) != ORB_OK) return st;
+    if (ne > 0) { k_bow_distances<<<(ne * 32 + 255) / 256, 256, 0, m->stream>>>(ne, de, K1.desc, K2.desc, ditems, m->d_cands); m->launches++; }
+    k_resolve_bow_kf<<<1, 32, 0, m->stream>>>(ne, de, m->d_cands, K1.angle, K2.angle, kf1->n, kf2->n, dhas2, dclosed, nn_ratio,
+                                              check_orientation, dmatch, hidx, hbin, m->d_scal);
+    m->launches++;
+    ORB_CUDA(cudaGetLastError());
+    if (kf1->n > 0) ORB_CUDA(cudaMemcpyAsync(match12, dmatch, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
 }  // extern "C"

@@ -5,7 +5,7 @@ indices where the reference stores MapPoint pointers."""
 import ctypes as C
 import numpy as np
 from .capi import check, lib, ptr
-from .views import Camera, Frame, FeatureVector, LastFrameView, MapPointView, GridParams, u8, _addr
+from .views import Camera, Frame, FeatureVector, LastFrameView, MapPointView, ProjectedView, GridParams, u8, _addr
 
 
 class ORBmatcher:
@@ -100,6 +100,59 @@ class ORBmatcher:
         return n.value, pairs
 
 
+    # int SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, std::vector<MapPoint*> &vpMatches12)
+    def SearchByBoWKeyFrames(self, KF1, fv1, has_mp1, KF2, fv2, has_mp2):
+        match = np.empty(max(KF1.N, 1), np.int32); n = C.c_int32()
+        h1 = u8(has_mp1); h2 = u8(has_mp2)
+        k1 = KF1.view(); k2 = KF2.view(); a = fv1.view(); b = fv2.view()
+        check(lib().orb_search_by_bow_keyframes(self._h, C.byref(k1), C.byref(a), ptr(h1), C.byref(k2), C.byref(b), ptr(h2),
+                                                C.c_float(self.mfNNratio), int(self.mbCheckOrientation), ptr(match), C.byref(n)))
+        return n.value, match[:KF1.N]
+
+    # int SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint*> &sAlreadyFound, th, ORBdist)
+    # int SearchByProjection(KeyFrame *pKF, cv::Mat Scw, const vector<MapPoint*> &vpPoints, vector<MapPoint*> &vpMatched, int th)
+    def SearchByProjectionClaiming(self, F, points, occupied, max_dist, check_ori=None):
+        """points: dict valid, u, v, ur, radius, min_level, max_level, desc, angle (see orb_projected_view)."""
+        pv = _proj_view(points)
+        match = np.empty(max(F.N, 1), np.int32); pbest = np.empty(max(pv[0].n, 1), np.int32); n = C.c_int32()
+        occ = None if occupied is None else u8(occupied)
+        fv = F.view()
+        co = self.mbCheckOrientation if check_ori is None else check_ori
+        check(lib().orb_search_by_projection_claiming(self._h, C.byref(fv), C.byref(pv[0]), ptr(occ), int(max_dist), int(co), ptr(match),
+                                                      ptr(pbest), C.byref(n)))
+        return n.value, match[:F.N], pbest[:pv[0].n]
+
+    # search step of int Fuse(KeyFrame *pKF, const vector<MapPoint*> &vpMapPoints, th) and Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)
+    def FuseCandidates(self, KF, points, inv_level_sigma2=None, max_dist=None):
+        pv = _proj_view(points)
+        bi = np.empty(max(pv[0].n, 1), np.int32); bd = np.empty(max(pv[0].n, 1), np.int32); n = C.c_int32()
+        s2 = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+        kv = KF.view()
+        check(lib().orb_search_projected_best(self._h, C.byref(kv), C.byref(pv[0]), ptr(s2), int(self.TH_LOW if max_dist is None else max_dist),
+                                              ptr(bi), ptr(bd), C.byref(n)))
+        return n.value, bi[:pv[0].n], bd[:pv[0].n]
+
+    # int SearchBySim3(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint*> &vpMatches12, s12, R12, t12, th)
+    def SearchBySim3(self, KF1, pts1_in_kf2, KF2, pts2_in_kf1):
+        p1 = _proj_view(pts1_in_kf2); p2 = _proj_view(pts2_in_kf1)
+        match = np.empty(max(KF1.N, 1), np.int32); n = C.c_int32()
+        k1 = KF1.view(); k2 = KF2.view()
+        check(lib().orb_search_by_sim3(self._h, C.byref(k1), C.byref(p1[0]), C.byref(k2), C.byref(p2[0]), ptr(match), C.byref(n)))
+        return n.value, match[:KF1.N]
+
+    # int SearchForInitialization(Frame &F1, Frame &F2, vector<cv::Point2f> &vbPrevMatched, vector<int> &vnMatches12, int windowSize=10)
+    def SearchForInitialization(self, F1, F2, prev_x, prev_y, windowSize=10):
+        """Returns (nmatches, vnMatches12); prev_x / prev_y (float32 arrays) are updated in place (:571-574)."""
+        match = np.empty(max(F1.N, 1), np.int32); n = C.c_int32()
+        f1 = F1.view(); f2 = F2.view()
+        check(lib().orb_search_for_initialization(self._h, C.byref(f1), C.byref(f2), ptr(prev_x), ptr(prev_y), int(windowSize),
+                                                  C.c_float(self.mfNNratio), int(self.mbCheckOrientation), ptr(match), C.byref(n)))
+        m = match[:F1.N]
+        ok = m >= 0
+        prev_x[ok] = F2.x[m[ok]]; prev_y[ok] = F2.y[m[ok]]
+        return n.value, m
+
+
 def _mp_view(d):
     keep = dict(valid=u8(d["valid"]), proj_x=np.ascontiguousarray(d["proj_x"], np.float32), proj_y=np.ascontiguousarray(d["proj_y"], np.float32),
                 proj_xr=np.ascontiguousarray(d["proj_xr"], np.float32), level=np.ascontiguousarray(d["level"], np.int32),
@@ -113,4 +166,13 @@ def _last_view(d):
                 zc=np.ascontiguousarray(d["zc"], np.float32), octave=np.ascontiguousarray(d["octave"], np.int32),
                 angle=np.ascontiguousarray(d["angle"], np.float32), desc=np.ascontiguousarray(d["desc"], np.uint8), blocks=u8(d["blocks"]))
     v = LastFrameView(len(keep["valid"]), *[_addr(keep[k]) for k in ("valid", "xc", "yc", "zc", "octave", "angle", "desc", "blocks")])
+    return v, keep
+
+
+def _proj_view(d):
+    f32 = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+    keep = dict(valid=u8(d["valid"]), u=f32(d["u"]), v=f32(d["v"]), ur=f32(d.get("ur")), radius=f32(d["radius"]),
+                min_level=np.ascontiguousarray(d["min_level"], np.int32), max_level=np.ascontiguousarray(d["max_level"], np.int32),
+                desc=np.ascontiguousarray(d["desc"], np.uint8), angle=f32(d.get("angle")))
+    v = ProjectedView(len(keep["valid"]), *[_addr(keep[k]) for k in ("valid", "u", "v", "ur", "radius", "min_level", "max_level", "desc", "angle")])
     return v, keep

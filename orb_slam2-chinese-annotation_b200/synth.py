@@ -173,3 +173,72 @@ def make_bow_scenario(n1=2000, n2=2000, idx=0, n_nodes=120, coarse_desc=False, *
     for i in range(n2):
         fvb.setdefault(int(node_b[i]), []).append(i)
     return a, fva, b, fvb, (rng.random(n1) < 0.6), (rng.random(n2) < 0.3)
+
+
+def make_projected_points_scenario(n_kp=2000, n_pts=2000, idx=0, th=10.0, level_span=(1, 1), match_frac=0.7, coarse_desc=False, **kw):
+    """Frame / KeyFrame + MapPoints already projected into it by the caller (the shared input of the
+    relocalisation / loop SearchByProjection variants, Fuse and SearchBySim3): projection, radius
+    th * sf[predicted level], accepted octaves [pred - level_span[0], pred + level_span[1]]."""
+    rng = np.random.default_rng(SEED_BASE + 0x700000 + int(idx))
+    f = make_frame_arrays(n_kp, 100 + idx, coarse_desc=coarse_desc, **kw)
+    src = rng.integers(0, n_kp, n_pts)
+    matched = rng.random(n_pts) < match_frac
+    u = np.where(matched, f["x"][src] + rng.normal(0, 2, n_pts), rng.uniform(0, f["bounds"][2], n_pts)).astype(np.float32)
+    v = np.where(matched, f["y"][src] + rng.normal(0, 2, n_pts), rng.uniform(0, f["bounds"][3], n_pts)).astype(np.float32)
+    desc = np.where(matched[:, None], perturb_descriptors(rng, f["desc"][src]), rng.integers(0, 256, (n_pts, 32), dtype=np.uint8)).astype(np.uint8)
+    if coarse_desc:
+        desc = f["desc"][src]
+    pred = np.clip(f["octave"][src] + rng.integers(0, 2, n_pts), 0, len(f["sf"]) - 1).astype(np.int32)
+    urs = f["u_right"][src] if f["u_right"] is not None else np.full(n_pts, -1.0)
+    dangle = np.where(rng.random(n_pts) < 0.8, rng.normal(30, 5, n_pts), rng.uniform(0, 360, n_pts))
+    pts = dict(valid=(rng.random(n_pts) < 0.9), u=u, v=v,
+               ur=np.where(urs >= 0, urs + rng.normal(0, 1.5, n_pts), u - 10).astype(np.float32),
+               radius=(np.float32(th) * f["sf"][pred]).astype(np.float32),
+               min_level=(pred - level_span[0]).astype(np.int32), max_level=(pred + level_span[1]).astype(np.int32),
+               desc=desc, angle=np.mod(f["angle"][src] + dangle, 360).astype(np.float32))
+    occupied = rng.random(n_kp) < 0.15
+    return f, pts, occupied
+
+
+def make_sim3_scenario(n1=2000, n2=2000, idx=0, th=7.5):
+    """Two KeyFrames with mutually projected MapPoints (SearchBySim3): for ~70 % of the features the
+    MapPoint of KF1 feature i lands on its KF2 partner j and vice versa."""
+    rng = np.random.default_rng(SEED_BASE + 0x800000 + int(idx))
+    a = make_frame_arrays(n1, 300 + 2 * idx); b = make_frame_arrays(n2, 301 + 2 * idx)
+    nm = min(n1, n2) * 7 // 10
+    ia = rng.permutation(n1)[:nm]; ib = rng.permutation(n2)[:nm]
+    part_a = rng.integers(0, n2, n1); part_a[ia] = ib      # partner of each KF1 feature in KF2 (random for the rest)
+    part_b = rng.integers(0, n1, n2); part_b[ib] = ia
+
+    def project(dst, partner, n_src):
+        pred = np.clip(dst["octave"][partner] + rng.integers(0, 2, n_src), 0, 7).astype(np.int32)
+        return dict(valid=(rng.random(n_src) < 0.85), u=(dst["x"][partner] + rng.normal(0, 2, n_src)).astype(np.float32),
+                    v=(dst["y"][partner] + rng.normal(0, 2, n_src)).astype(np.float32), ur=None,
+                    radius=(np.float32(th) * dst["sf"][pred]).astype(np.float32), min_level=(pred - 1).astype(np.int32),
+                    max_level=pred, desc=perturb_descriptors(rng, dst["desc"][partner], 0.05), angle=None)
+    return a, project(b, part_a, n1), b, project(a, part_b, n2)
+
+
+def make_initialization_scenario(n1=2000, n2=2000, idx=0, coarse_desc=False):
+    """Two monocular frames for SearchForInitialization: F2 keypoints are F1 keypoints moved by a small
+    flow; vbPrevMatched starts as the F1 positions (reference src/Tracking.cc:650-652)."""
+    rng = np.random.default_rng(SEED_BASE + 0x900000 + int(idx))
+    a = make_frame_arrays(n1, 200 + 2 * idx, stereo=False, coarse_desc=coarse_desc)
+    b = make_frame_arrays(n2, 201 + 2 * idx, stereo=False, coarse_desc=coarse_desc)
+    nm = min(n1, n2) * 8 // 10
+    ia = rng.permutation(n1)[:nm]; ib = rng.permutation(n2)[:nm]
+    if not coarse_desc:
+        b["desc"][ib] = perturb_descriptors(rng, a["desc"][ia], 0.04)
+    b["x"][ib] = np.clip(a["x"][ia] + rng.normal(8, 20, nm), 20, 1220).astype(np.float32)
+    b["y"][ib] = np.clip(a["y"][ia] + rng.normal(0, 20, nm), 20, 355).astype(np.float32)
+    b["octave"][ib] = a["octave"][ia]
+    b["angle"][ib] = np.mod(a["angle"][ia] + np.where(rng.random(nm) < 0.8, rng.normal(5, 4, nm), rng.uniform(0, 360, nm)), 360).astype(np.float32)
+    # several F1 keypoints share one F2 partner (duplicates in F1) -> the displacement rule (:509-513)
+    dup = rng.permutation(n1)[: n1 // 10]
+    srcs = rng.choice(ia, len(dup))
+    a["x"][dup] = a["x"][srcs] + rng.normal(0, 1, len(dup)).astype(np.float32)
+    a["y"][dup] = a["y"][srcs] + rng.normal(0, 1, len(dup)).astype(np.float32)
+    a["octave"][dup] = a["octave"][srcs]
+    if not coarse_desc:
+        a["desc"][dup] = perturb_descriptors(rng, a["desc"][srcs], 0.02)
+    return a, b, a["x"].copy(), a["y"].copy()

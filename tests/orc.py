@@ -242,6 +242,57 @@ def search_for_triangulation(KF1, fv1, has1, KF2, fv2, has2, F12, epipole, sigma
     return n, match[:KF1.N]
 
 
+def _opt(a):
+    return None if a is None else a.ctypes.data
+
+
+def search_by_bow_keyframes(KF1, fv1, has1, KF2, fv2, has2, nn_ratio, check_ori):
+    match = np.empty(max(KF1.N, 1), np.int32)
+    h1 = _views.u8(has1); h2 = _views.u8(has2)
+    k1 = KF1.view(); k2 = KF2.view(); a = fv1.view(); b = fv2.view()
+    lib.orc_search_by_bow_keyframes.argtypes = [C.c_void_p] * 6 + [C.c_float, C.c_int, C.c_void_p]
+    n = lib.orc_search_by_bow_keyframes(C.byref(k1), C.byref(a), _p(h1), C.byref(k2), C.byref(b), _p(h2), nn_ratio, int(check_ori), _p(match))
+    return n, match[:KF1.N]
+
+
+def search_by_projection_claiming(F, points, occupied, max_dist, check_ori):
+    pv, keep = _mt._proj_view(points)
+    match = np.empty(max(F.N, 1), np.int32); pbest = np.empty(max(pv.n, 1), np.int32)
+    occ = None if occupied is None else _views.u8(occupied)
+    fv = F.view()
+    lib.orc_search_by_projection_claiming.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    n = lib.orc_search_by_projection_claiming(C.byref(fv), C.byref(pv), _opt(occ), int(max_dist), int(check_ori), _p(match), _p(pbest))
+    return n, match[:F.N], pbest[:pv.n]
+
+
+def search_projected_best(KF, points, inv_level_sigma2, max_dist):
+    pv, keep = _mt._proj_view(points)
+    bi = np.empty(max(pv.n, 1), np.int32); bd = np.empty(max(pv.n, 1), np.int32)
+    s2 = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+    kv = KF.view()
+    lib.orc_search_projected_best.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    n = lib.orc_search_projected_best(C.byref(kv), C.byref(pv), _opt(s2), int(max_dist), _p(bi), _p(bd))
+    return n, bi[:pv.n], bd[:pv.n]
+
+
+def search_by_sim3(KF1, pts1, KF2, pts2):
+    p1, k1_ = _mt._proj_view(pts1); p2, k2_ = _mt._proj_view(pts2)
+    match = np.empty(max(KF1.N, 1), np.int32)
+    k1 = KF1.view(); k2 = KF2.view()
+    lib.orc_search_by_sim3.argtypes = [C.c_void_p] * 5
+    n = lib.orc_search_by_sim3(C.byref(k1), C.byref(p1), C.byref(k2), C.byref(p2), _p(match))
+    return n, match[:KF1.N]
+
+
+def search_for_initialization(F1, F2, prev_x, prev_y, window, nn_ratio, check_ori):
+    match = np.empty(max(F1.N, 1), np.int32)
+    f1 = F1.view(); f2 = F2.view()
+    px = np.ascontiguousarray(prev_x, np.float32); py = np.ascontiguousarray(prev_y, np.float32)
+    lib.orc_search_for_initialization.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_float, C.c_int, C.c_void_p]
+    n = lib.orc_search_for_initialization(C.byref(f1), C.byref(f2), _p(px), _p(py), int(window), nn_ratio, int(check_ori), _p(match))
+    return n, match[:F1.N]
+
+
 # ---- the reference's own ORBextractor.cc compiled verbatim (oracle/_ref; built only where /root/reference exists)
 _REF_SO = os.path.join(ROOT, "oracle", "_ref", "libref_orbextractor.so")
 

@@ -109,3 +109,76 @@ def test_search_for_triangulation(gm, idx, only_stereo, coarse):
     assert pairs == [(int(i), int(m_o[i])) for i in np.nonzero(m_o >= 0)[0]]
     if not coarse:
         assert n_o > 20
+
+
+@pytest.mark.parametrize("idx,ratio,coarse", [(0, 0.75, False), (1, 0.6, False), (2, 0.9, True)])
+def test_search_by_bow_keyframes(gm, idx, ratio, coarse):
+    """SearchByBoW(KF, KF) (reference src/ORBmatcher.cc:581-716, LoopClosing.cc:287)."""
+    a, fva, b, fvb, _, _ = synth.make_bow_scenario(2000, 1950, 20 + idx, coarse_desc=coarse)
+    rng = np.random.default_rng(idx)
+    has_a = rng.random(2000) < 0.7; has_b = rng.random(1950) < 0.7
+    KF1, KF2 = _frame(a), _frame(b)
+    va, vb = views.FeatureVector(fva), views.FeatureVector(fvb)
+    for check_ori in (True, False):
+        gm.mfNNratio = ratio; gm.mbCheckOrientation = check_ori
+        n_g, m_g = gm.SearchByBoWKeyFrames(KF1, va, has_a, KF2, vb, has_b)
+        n_o, m_o = orc.search_by_bow_keyframes(KF1, va, has_a, KF2, vb, has_b, ratio, check_ori)
+        assert n_g == n_o and np.array_equal(m_g, m_o), (idx, n_g, n_o)
+    gm.mfNNratio = 0.8; gm.mbCheckOrientation = True
+    if not coarse:
+        assert n_o > 50
+
+
+@pytest.mark.parametrize("idx,th,span,max_dist,ori,coarse", [
+    (0, 10.0, (1, 1), 100, True, False),    # relocalisation: SearchByProjection(F, KF, found, 10, 100), levels pred-1..pred+1
+    (1, 3.0, (1, 1), 64, True, False),      # relocalisation refinement (3, 64)
+    (2, 10.0, (1, 0), 50, False, False),    # loop closing: SearchByProjection(KF, Scw, points, matched, 10), levels pred-1..pred
+    (3, 10.0, (1, 1), 100, True, True),     # tie-heavy descriptors
+])
+def test_search_by_projection_claiming(gm, idx, th, span, max_dist, ori, coarse):
+    f, pts, occ = synth.make_projected_points_scenario(2000, 2000, idx, th=th, level_span=span, coarse_desc=coarse)
+    F = _frame(f)
+    for use_occ in (True, False):
+        n_g, m_g, b_g = gm.SearchByProjectionClaiming(F, pts, occ if use_occ else None, max_dist, check_ori=ori)
+        n_o, m_o, b_o = orc.search_by_projection_claiming(F, pts, occ if use_occ else None, max_dist, ori)
+        assert n_g == n_o and np.array_equal(m_g, m_o) and np.array_equal(b_g, b_o), (idx, n_g, n_o, int((m_g != m_o).sum()))
+    assert n_o > 100
+
+
+@pytest.mark.parametrize("idx,th,chi2,coarse", [(0, 3.0, True, False), (1, 4.0, False, False), (2, 3.0, True, True), (3, 20.0, True, False)])
+def test_fuse_candidates(gm, idx, th, chi2, coarse):
+    """Search step of Fuse(KF, MapPoints, th) (chi-square gate) and Fuse(KF, Scw, ...) (reference :903-1207)."""
+    f, pts, _ = synth.make_projected_points_scenario(2000, 2500, 10 + idx, th=th, level_span=(1, 0), coarse_desc=coarse)
+    KF = _frame(f)
+    inv_s2 = (1.0 / (f["sf"] * f["sf"])).astype(np.float32) if chi2 else None
+    n_g, i_g, d_g = gm.FuseCandidates(KF, pts, inv_s2)
+    n_o, i_o, d_o = orc.search_projected_best(KF, pts, inv_s2, 50)
+    assert n_g == n_o and np.array_equal(i_g, i_o) and np.array_equal(d_g, d_o), (idx, n_g, n_o, int((i_g != i_o).sum()))
+    assert n_o > 100
+
+
+@pytest.mark.parametrize("idx", [0, 1])
+def test_search_by_sim3(gm, idx):
+    a, p12, b, p21 = synth.make_sim3_scenario(1500, 1400, idx)
+    KF1, KF2 = _frame(a), _frame(b)
+    n_g, m_g = gm.SearchBySim3(KF1, p12, KF2, p21)
+    n_o, m_o = orc.search_by_sim3(KF1, p12, KF2, p21)
+    assert n_g == n_o and np.array_equal(m_g, m_o), (n_g, n_o)
+    assert n_o > 300
+
+
+@pytest.mark.parametrize("idx,window,ratio,coarse", [(0, 100, 0.9, False), (1, 30, 0.9, False), (2, 100, 0.9, True), (3, 100, 0.6, False)])
+def test_search_for_initialization(gm, idx, window, ratio, coarse):
+    a, b, px, py = synth.make_initialization_scenario(2000, 1900, idx, coarse_desc=coarse)
+    F1, F2 = _frame(a), _frame(b)
+    for check_ori in (True, False):
+        gm.mfNNratio = ratio; gm.mbCheckOrientation = check_ori
+        gx, gy = px.copy(), py.copy()
+        n_g, m_g = gm.SearchForInitialization(F1, F2, gx, gy, window)
+        n_o, m_o = orc.search_for_initialization(F1, F2, px, py, window, ratio, check_ori)
+        assert n_g == n_o and np.array_equal(m_g, m_o), (idx, n_g, n_o, int((m_g != m_o).sum()))
+        ok = m_o >= 0
+        assert np.array_equal(gx[ok], F2.x[m_o[ok]]) and np.array_equal(gx[~ok], px[~ok])
+    gm.mfNNratio = 0.8; gm.mbCheckOrientation = True
+    if not coarse:
+        assert n_o > 100

@@ -107,6 +107,12 @@ int orb_get_level(orb_extractor* e, int image, int level, int blurred, int borde
 int orb_get_level_candidates(orb_extractor* e, int image, int level, int32_t* xys, int cap, int32_t* n);
 int orb_get_level_keypoints(orb_extractor* e, int image, int level, int32_t* xys, int cap, int32_t* n);
 
+/* Self-check of the device sincosf used by the rBRIEF kernel (the reference's cos(float)/sin(float),
+ * src/ORBextractor.cc:124-125, are one glibc sincosf call).  Evaluates every float whose bit pattern
+ * lies in [first_bits, last_bits] on CUDA device `device` and returns the 64-bit checksum that
+ * tests/cpp/sincosf_sweep.c computes with the host libm. */
+int orb_sincosf_sweep_device(uint32_t first_bits, uint32_t last_bits, int device, uint64_t* checksum);
+
 /* ------------------------------------------------------------------ stereo */
 /* Frame::ComputeStereoMatches for image `image` of the last batches of the two extractor handles
  * (left and right pyramids stay device-resident).  Keypoints/descriptors are the extractors' own

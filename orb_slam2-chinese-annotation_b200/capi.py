@@ -25,7 +25,7 @@ EXPORTS = [
     "orb_descriptor_distance", "orb_match_bruteforce", "orb_match_bruteforce_device", "orb_assign_features_to_grid",
     "orb_search_by_projection_mappoints", "orb_search_by_projection_lastframe", "orb_search_by_bow",
     "orb_search_for_triangulation", "orb_search_by_bow_keyframes", "orb_search_by_projection_claiming",
-    "orb_search_projected_best", "orb_search_by_sim3", "orb_search_for_initialization",
+    "orb_search_projected_best", "orb_search_by_sim3", "orb_search_for_initialization", "orb_sincosf_sweep_device",
 ]
 
 

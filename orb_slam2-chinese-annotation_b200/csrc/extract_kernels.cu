@@ -858,101 +858,137 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 #define OD_WARPS 8
-#define OD_PP 40  // pitch of the staged 37 x 37 descriptor patch
+#define OD_KP_PER_CTA 32   // keypoint slots per CTA: each warp walks OD_KP_PER_CTA / OD_WARPS of them
+#define OD_DW 11           // words per staged row of the 37 x 37 blurred patch (37 + 3 bytes of alignment slack)
+#define OD_RW 9            // words per staged row of the 31 x 31 raw patch
+// pattern copy in global memory: the CTA prologue reads it coalesced (constant memory would
+// serialise the per-thread indices)
+__device__ __align__(16) signed char g_pattern[1024] = {
+#include "../../include/orb_pattern_31.inc"
+};
+
+// Both patches are fetched with aligned 32-bit loads (all of them in flight together) and keep
+// the level's word alignment in shared memory; the rBRIEF gathers and the moment columns then
+// read bytes from shared memory only.
 __global__ void __launch_bounds__(OD_WARPS * 32)
 k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur, const uint32_t* __restrict__ lvl_kp,
                   const int* __restrict__ lvl_cnt, orb_keypoint* __restrict__ kps, uint8_t* __restrict__ desc,
                   int* __restrict__ counts, const Plan P) {
     __shared__ float2 s_pat[512];
-    __shared__ uint8_t s_patch[OD_WARPS][37 * OD_PP];
-    for (int i = threadIdx.x; i < 512; i += OD_WARPS * 32)  // point i = byte (i / 16), sample (i % 16); stored [sample][byte]: conflict-free
-        s_pat[(i & 15) * 32 + (i >> 4)] = make_float2((float)c_pattern[2 * i], (float)c_pattern[2 * i + 1]);
-    __syncthreads();
+    __shared__ uint32_t s_desc[OD_WARPS][37 * OD_DW];
+    __shared__ uint32_t s_raw[OD_WARPS][31 * OD_RW];
+    __shared__ int s_cnt[ORB_MAX_LEVELS], s_pre[ORB_MAX_LEVELS];
     const int b = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int slot = blockIdx.x * OD_WARPS + warp;
     const int* cnt = lvl_cnt + b * ORB_MAX_LEVELS;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
+    for (int i = threadIdx.x; i < 512; i += OD_WARPS * 32) {  // point i = byte (i / 16), sample (i % 16); stored [sample][byte]: conflict-free
+        const char2 p = reinterpret_cast<const char2*>(g_pattern)[i];
+        s_pat[(i & 15) * 32 + (i >> 4)] = make_float2((float)p.x, (float)p.y);
+    }
+    if (threadIdx.x == 0) {
         int t = 0;
-        for (int l = 0; l < P.nlevels; ++l) t += cnt[l];
-        counts[b] = t;
+        for (int l = 0; l < P.nlevels; ++l) { const int c = cnt[l]; s_cnt[l] = c; s_pre[l] = t; t += c; }
+        if (blockIdx.x == 0) counts[b] = t;
     }
-    if (slot >= P.kp_cap) return;
-    int l = 0;
-    while (l + 1 < P.nlevels && slot >= P.lv[l + 1].kp_off) ++l;
-    const LevelGeom& G = P.lv[l];
-    const int idx = slot - G.kp_off;
-    if (idx >= cnt[l]) return;
-    int out_idx = idx;
-    for (int j = 0; j < l; ++j) out_idx += cnt[j];
+    __syncthreads();
 
-    const uint32_t key = lvl_kp[(size_t)b * P.kp_cap + slot];
-    const int px = ORB_KEY_X(key) + ORB_WIN, py = ORB_KEY_Y(key) + ORB_WIN;
-    const int pitch = G.pitch;
-    const uint8_t* img = pyr + G.off + (size_t)b * G.img_stride + (size_t)py * pitch + px;
-    const uint8_t* c = blur + G.off + (size_t)b * G.img_stride + (size_t)py * pitch + px;
+    uint32_t* sd = s_desc[warp];
+    uint32_t* sr = s_raw[warp];
+#pragma unroll 1
+    for (int it = 0; it < OD_KP_PER_CTA / OD_WARPS; ++it) {
+        const int slot = blockIdx.x * OD_KP_PER_CTA + it * OD_WARPS + warp;
+        if (slot >= P.kp_cap) break;
+        int l = 0;
+        while (l + 1 < P.nlevels && slot >= P.lv[l + 1].kp_off) ++l;
+        const LevelGeom& G = P.lv[l];
+        const int idx = slot - G.kp_off;
+        if (idx >= s_cnt[l]) continue;
+        const int out_idx = idx + s_pre[l];
 
-    // stage the 37 x 37 blurred patch (max |rotated offset| is 18): two row segments per row
-    uint8_t* sp = s_patch[warp];
-    {
-        const int c0 = lane - 18, c1 = lane + 14;
-#pragma unroll 4
-        for (int r = -18; r <= 18; ++r) {
-            const uint8_t* row = c + r * pitch;
-            sp[(r + 18) * OD_PP + lane] = row[c0];
-            if (lane < 5) sp[(r + 18) * OD_PP + 32 + lane] = row[c1];
+        const uint32_t key = lvl_kp[(size_t)b * P.kp_cap + slot];
+        const int px = ORB_KEY_X(key) + ORB_WIN, py = ORB_KEY_Y(key) + ORB_WIN;
+        const int pitch = G.pitch;
+        const size_t img_off = G.off + (size_t)b * G.img_stride;
+        // rows are 64-byte aligned, so the alignment of a patch row is that of its first column
+        const int dsh = (px - 18) & 3, rsh = (px - 15) & 3;
+        const uint8_t* dbase = blur + img_off + (size_t)(py - 18) * pitch + (px - 18 - dsh);
+        const uint8_t* rbase = pyr + img_off + (size_t)(py - 15) * pitch + (px - 15 - rsh);
+        __syncwarp();  // the previous keypoint's readers are done with sd / sr
+        uint32_t vr[9], vd[13];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            const int i = k * 32 + lane;
+            const int r = (i * 57) >> 9, c = i - r * OD_RW;   // i / 9 for i < 288
+            vr[k] = i < 31 * OD_RW ? __ldg(reinterpret_cast<const uint32_t*>(rbase + r * pitch) + c) : 0u;
         }
-    }
-
-    // IC_Angle (reference :77-113): integer moments over the radius-15 disc; lane = column u
-    int m10 = 0, m01 = 0;
-    {
-        const int u = lane - ORB_HALF_PATCH;
-        const int au = u < 0 ? -u : u;
 #pragma unroll
-        for (int v = -ORB_HALF_PATCH; v <= ORB_HALF_PATCH; ++v) {
-            const int d = P.umax[v < 0 ? -v : v];
-            int val = 0;
-            if (lane < 31 && au <= d) val = img[v * pitch + u];
-            m10 += u * val;
-            m01 += v * val;
+        for (int k = 0; k < 13; ++k) {
+            const int i = k * 32 + lane;
+            const int r = (i * 745) >> 13, c = i - r * OD_DW;  // i / 11 for i < 416
+            vd[k] = i < 37 * OD_DW ? __ldg(reinterpret_cast<const uint32_t*>(dbase + r * pitch) + c) : 0u;
         }
-    }
 #pragma unroll
-    for (int o = 16; o; o >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-    }
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
+        for (int k = 0; k < 9; ++k) { const int i = k * 32 + lane; if (i < 31 * OD_RW) sr[i] = vr[k]; }
+#pragma unroll
+        for (int k = 0; k < 13; ++k) { const int i = k * 32 + lane; if (i < 37 * OD_DW) sd[i] = vd[k]; }
+        __syncwarp();
 
-    // rBRIEF (reference :119-164): lane = descriptor byte, 8 comparisons on the staged patch
-    const float rad = __fmul_rn(angle, 0.017453292519943295f);  // factorPI = (float)(CV_PI/180.f)
-    float a, bsin;
-    orb_sincosf(rad, &bsin, &a);
-    __syncwarp();
-    const uint8_t* spc = sp + 18 * OD_PP + 18;
-    int val = 0;
+        // IC_Angle (reference :77-113): integer moments over the radius-15 disc; lane = column u
+        int m10 = 0, m01 = 0;
+        {
+            const int u = lane - ORB_HALF_PATCH;
+            const int au = u < 0 ? -u : u;
+            const uint8_t* col = reinterpret_cast<const uint8_t*>(sr) + rsh + (lane < 31 ? lane : 0);
+            int colsum = 0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const float2 p0 = s_pat[(2 * k) * 32 + lane], p1 = s_pat[(2 * k + 1) * 32 + lane];
-        const int r0 = __float2int_rn(__fmaf_rn(p0.x, bsin, __fmul_rn(p0.y, a)));
-        const int q0 = __float2int_rn(__fmaf_rn(p0.x, a, -__fmul_rn(p0.y, bsin)));
-        const int r1 = __float2int_rn(__fmaf_rn(p1.x, bsin, __fmul_rn(p1.y, a)));
-        const int q1 = __float2int_rn(__fmaf_rn(p1.x, a, -__fmul_rn(p1.y, bsin)));
-        const int t0 = spc[r0 * OD_PP + q0], t1 = spc[r1 * OD_PP + q1];
-        val |= (t0 < t1) << k;
-    }
-    desc[((size_t)b * P.kp_cap + out_idx) * 32 + lane] = (uint8_t)val;
-    if (lane == 0) {
-        orb_keypoint kp;
-        kp.x = (float)px; kp.y = (float)py;
-        if (l != 0) { kp.x = __fmul_rn(kp.x, G.sf); kp.y = __fmul_rn(kp.y, G.sf); }
-        kp.size = G.patch_size;
-        kp.angle = angle;
-        kp.response = (float)ORB_KEY_S(key);
-        kp.octave = l;
-        kp.class_id = -1;
-        kps[(size_t)b * P.kp_cap + out_idx] = kp;
+            for (int v = -ORB_HALF_PATCH; v <= ORB_HALF_PATCH; ++v) {
+                const int d = P.umax[v < 0 ? -v : v];
+                int val = col[(v + ORB_HALF_PATCH) * (OD_RW * 4)];
+                if (lane >= 31 || au > d) val = 0;
+                colsum += val;
+                m01 += v * val;
+            }
+            m10 = u * colsum;
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+            m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+        }
+        const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+        // rBRIEF (reference :119-164): lane = descriptor byte, 8 comparisons on the staged patch
+        const float rad = __fmul_rn(angle, 0.017453292519943295f);  // factorPI = (float)(CV_PI/180.f)
+        float a, bsin;
+        orb_sincosf(rad, &bsin, &a);
+        const uint8_t* spc = reinterpret_cast<const uint8_t*>(sd) + 18 * (OD_DW * 4) + 18 + dsh;
+        int val = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float2 p0 = s_pat[(2 * k) * 32 + lane], p1 = s_pat[(2 * k + 1) * 32 + lane];
+            const int r0 = __float2int_rn(__fmaf_rn(p0.x, bsin, __fmul_rn(p0.y, a)));
+            const int q0 = __float2int_rn(__fmaf_rn(p0.x, a, -__fmul_rn(p0.y, bsin)));
+            const int r1 = __float2int_rn(__fmaf_rn(p1.x, bsin, __fmul_rn(p1.y, a)));
+            const int q1 = __float2int_rn(__fmaf_rn(p1.x, a, -__fmul_rn(p1.y, bsin)));
+            const int t0 = spc[r0 * (OD_DW * 4) + q0], t1 = spc[r1 * (OD_DW * 4) + q1];
+            val |= (t0 < t1) << k;
+        }
+        desc[((size_t)b * P.kp_cap + out_idx) * 32 + lane] = (uint8_t)val;
+        if (lane < 7) {  // one 4-byte field of the 28-byte record per lane
+            float fx = (float)px, fy = (float)py;
+            if (l != 0) { fx = __fmul_rn(fx, G.sf); fy = __fmul_rn(fy, G.sf); }
+            uint32_t f;
+            switch (lane) {
+                case 0: f = __float_as_uint(fx); break;
+                case 1: f = __float_as_uint(fy); break;
+                case 2: f = __float_as_uint(G.patch_size); break;
+                case 3: f = __float_as_uint(angle); break;
+                case 4: f = __float_as_uint((float)ORB_KEY_S(key)); break;
+                case 5: f = (uint32_t)l; break;
+                default: f = 0xffffffffu; break;  // class_id = -1
+            }
+            reinterpret_cast<uint32_t*>(kps + (size_t)b * P.kp_cap + out_idx)[lane] = f;
+        }
     }
 }
 
@@ -1015,6 +1051,42 @@ cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefi
 }
 void launch_orient_describe(cudaStream_t s, const uint8_t* pyr, const uint8_t* blur, const uint32_t* lvl_kp, const int* lvl_cnt,
                             orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int batch) {
-    dim3 grid((P.kp_cap + OD_WARPS - 1) / OD_WARPS, batch);
+    dim3 grid((P.kp_cap + OD_KP_PER_CTA - 1) / OD_KP_PER_CTA, batch);
     k_orient_describe<<<grid, OD_WARPS * 32, 0, s>>>(pyr, blur, lvl_kp, lvl_cnt, kps, desc, counts, P);
+}
+
+// ------------------------------------------------------------------------------------------
+// Exhaustive self-check of orb_sincosf on the device (include/orb_b200.h: orb_sincosf_sweep_device).
+__global__ void __launch_bounds__(256) k_sincosf_sweep(const uint32_t first, const unsigned long long count, unsigned long long* __restrict__ sum) {
+    unsigned long long acc = 0ull;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x; i < count; i += (unsigned long long)gridDim.x * 256) {
+        const uint32_t u = first + (uint32_t)i;
+        float s, c;
+        orb_sincosf(__uint_as_float(u), &s, &c);
+        unsigned long long v = ((unsigned long long)__float_as_uint(s) << 32) | __float_as_uint(c);
+        v ^= (unsigned long long)u * 0x9E3779B97F4A7C15ull;
+        v *= 0xD6E8FEB86659FD93ull;
+        v ^= v >> 32;
+        acc += v;
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(sum, acc);
+}
+extern "C" int orb_sincosf_sweep_device(uint32_t first_bits, uint32_t last_bits, int device, uint64_t* checksum) {
+    if (!checksum || last_bits < first_bits) return ORB_ERR_BAD_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); orb_set_error("no CUDA device: this library has no CPU fallback"); return ORB_ERR_CUDA; }
+    if (device < 0 || device >= ndev) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(device));
+    unsigned long long* d = nullptr;
+    ORB_CUDA(cudaMalloc((void**)&d, 8));
+    ORB_CUDA(cudaMemset(d, 0, 8));
+    k_sincosf_sweep<<<148 * 16, 256>>>(first_bits, (unsigned long long)last_bits - first_bits + 1ull, d);
+    unsigned long long h = 0;
+    cudaError_t e = cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (e != cudaSuccess) { orb_set_error(cudaGetErrorString(e)); return ORB_ERR_CUDA; }
+    *checksum = h;
+    return ORB_OK;
 }

@@ -128,14 +128,26 @@ __global__ void __launch_bounds__(256) k_gauss7(const uint8_t* __restrict__ pyr,
     uint8_t* D = blur + G.off + (size_t)blockIdx.y * G.img_stride;
     const int tid = threadIdx.x;
     const int W = G.w, H = G.h;
+    // levels of at least 4 x 4 pixels need one reflection at most (halo of 3); tiny levels take the loop
+    const bool one_step = W >= 4 && H >= 4;
     for (int i = tid; i < (BLUR_TH + 6) * BLUR_RW; i += 256) {
-        const int ry = i / BLUR_RW, j = i - ry * BLUR_RW;
-        const int gy = reflect101(min(ty + ry - 3, H + 2), H);
+        const int ry = (i * 241) >> 13, j = i - ry * BLUR_RW;   // i / 34 for i < 2380
+        int gy = ty + ry - 3;
+        if (one_step) { gy = gy < 0 ? -gy : gy; gy = gy >= H ? 2 * (H - 1) - gy : gy; gy = max(gy, 0); }
+        else gy = reflect101(min(gy, H + 2), H);
         const int gx = tx - 4 + 4 * j;
         const uint8_t* row = S + (size_t)gy * G.pitch;
         uint32_t v;
         if (gx >= 0 && gx + 3 < W) v = *reinterpret_cast<const uint32_t*>(row + gx);
-        else {
+        else if (one_step) {
+            v = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                int x = gx + k;
+                x = x < 0 ? -x : x; x = x >= W ? 2 * (W - 1) - x : x; x = max(x, 0);
+                v |= (uint32_t)row[x] << (8 * k);
+            }
+        } else {
             v = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) v |= (uint32_t)row[reflect101(min(gx + k, W + 2), W)] << (8 * k);
@@ -182,220 +194,266 @@ __global__ void __launch_bounds__(256) k_gauss7(const uint8_t* __restrict__ pyr,
 // s = max(bright, dark) - 1 per interior pixel; corner at th <=> s >= th; a corner survives NMS
 // iff s is strictly greater than the raw scores of its 8 neighbours inside the cell interior
 // (outside counts as 0).  The set of strict local maxima does not depend on th, so the
-// iniTh -> minTh retry only re-filters the same list.
+// iniTh -> minTh retry (reference :843-850) only re-filters the same list: a cell keeps its maxima
+// with s >= iniTh, or, when it has none, those with s >= minTh.
 //
-// One CTA per cell.  Phases: (1) stage the cell view in shared memory, (2) cheap necessary test
-// at minTh on every interior pixel, survivors compacted, (3) exact score on dense warps with
-// 3-input min/max, (4) local-maximum map + counts, (5) ordered (row-major) write.
-#define FAST_THREADS 128
-#define FAST_WARPS (FAST_THREADS / 32)
+// One CTA per group of ORB_FAST_G consecutive cells of a cell row (their interiors tile a
+// contiguous strip).  The strip's 4-pixel words are split into 8 contiguous row-major chunks, one
+// per warp, and every list below is a per-warp segment that stays in row-major order, so the
+// final write needs no sort and no atomics:
+//   (1) stage the strip in shared memory with 16-byte loads;
+//   (2) byte-SIMD necessary test at minTh on 4 pixels per thread, survivors appended in order;
+//   (3) exact score of the survivors, two pixels per thread on packed 16-bit lanes (VIADD.16x2 /
+//       VIMNMX3.S16x2), into a shared score map; corners compacted in place, in order;
+//   (4) strict local maxima inside the own cell, compacted in place; per-warp per-cell counts;
+//   (5) per-cell threshold choice, prefix over warps, ordered (row-major) write.
+// The tile pitch TP and score pitch TP - 32 are compile-time so that every ring / neighbour
+// offset is an immediate.
+#define FAST_THREADS 256
+#define FAST_WARPS 8
 
-__device__ __forceinline__ int min3i(int a, int b, int c) { return min(min(a, b), c); }
-__device__ __forceinline__ int max3i(int a, int b, int c) { return max(max(a, b), c); }
-
-// max over the 16 arcs of 9 contiguous ring pixels of min(d) and of min(-d):  returns
-// max(bright, dark) - 1, the largest threshold at which the pixel is a FAST-9 corner.
-__device__ __forceinline__ int fast_corner_score(const int v, const int (&p)[16]) {
-    int d[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) d[k] = v - p[k];
-    int lo3[16], hi3[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        lo3[k] = min3i(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-        hi3[k] = max3i(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-    }
-    int bright = -512, dark = 512;
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        bright = max(bright, min3i(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]));
-        dark = min(dark, max3i(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]));
-    }
-    return max(bright, -dark) - 1;
-}
-
-// Dynamic shared memory: tile (th x tp bytes, rows word-aligned like the level) | scores
-// ((ih+2) x sp bytes, zero frame) | list A (u16 pixel index) | list B (u16) | final list (u32: index << 8 | score)
-//
-// The reference runs FAST at iniThFAST and only when the post-NMS list of the cell is empty again
-// at minThFAST.  Same here: pass 0 tests, scores and suppresses at ini_th (few survivors); pass 1
-// runs only for cells that came out empty.  Suppression at threshold t compares against neighbour
-// scores that are themselves >= t, which is what the score map holds during that pass.
-//
-// Per pass: (A) byte-SIMD necessary test on 4 pixels per thread: both ring pixels of the vertical
-// pair (1, 9) and of the horizontal pair (5, 13) within t of the centre => no 9-arc; (B) scalar
-// test with polarity on all four axis/diagonal pairs; (C) exact score; (D) 3x3 suppression.
-// Each stage works on the compacted survivors of the previous one.
 __device__ __forceinline__ unsigned gt_bytes(unsigned ad, unsigned k) {  // bit 7 of byte j set <=> ad.j > 127 - k.j  (k.j <= 127)
     return ad | ((ad & 0x7f7f7f7fu) + k);
 }
 
+// FAST score of two pixels at once.  e[k] = ring[k] - centre on packed signed 16-bit lanes.
+// dark = max over the 16 arcs of min over 9 contiguous e; bright = -(min over arcs of max over 9).
+__device__ __forceinline__ unsigned fast_score_x2(const unsigned (&e)[16]) {
+    unsigned lo3[16], hi3[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        lo3[k] = __vimin3_s16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+        hi3[k] = __vimax3_s16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+    }
+    unsigned a9[16], z9[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        a9[k] = __vimin3_s16x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
+        z9[k] = __vimax3_s16x2(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
+    }
+    unsigned dk = __vimax3_s16x2(a9[0], a9[1], a9[2]), br = __vimin3_s16x2(z9[0], z9[1], z9[2]);
+#pragma unroll
+    for (int k = 3; k < 15; k += 2) {
+        dk = __vimax3_s16x2(dk, a9[k], a9[k + 1]);
+        br = __vimin3_s16x2(br, z9[k], z9[k + 1]);
+    }
+    // max(dark, -bright) - 1 on both lanes; -min(br, z9[15]) = max(-br, -z9[15])
+    return __vsub2(__vimax3_s16x2(__vmaxs2(dk, a9[15]), __vneg2(br), __vneg2(z9[15])), 0x00010001u);
+}
+
+// Dynamic shared memory: tile (rows x TP bytes, 16-byte aligned like the level) | score map
+// ((ih + 2) x SP bytes, zero frame) | lists (u16: y << 8 | x)
+template <int TP>
 __global__ void __launch_bounds__(FAST_THREADS)
 k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
-             const int smem_tile_bytes, const int smem_score_bytes, const int smem_surv_bytes) {
+             const int smem_tile_bytes, const int smem_score_bytes) {
+    constexpr int SP = TP - 32, TPW = TP / 4;
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int s_na, s_nb, s_nfin;
+    __shared__ int s_wc[FAST_WARPS][ORB_FAST_G];   // per warp, per cell: maxima | maxima with s >= iniTh << 16
 
     int l = 0;
-    while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].cell_off) ++l;
+    while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].grp_off) ++l;
     const LevelGeom& G = P.lv[l];
-    const int cell = blockIdx.x - G.cell_off;
-    const int ci = cell / G.n_cols, cj = cell - ci * G.n_cols;
+    const int g = blockIdx.x - G.grp_off;
+    const int ci = (int)(((unsigned)g * G.grp_magic) >> 20), cj0 = (g - ci * G.n_grp_x) * ORB_FAST_G;
+    const int nc = min(ORB_FAST_G, G.n_cols - cj0);
     const int b = blockIdx.y;
-    const int tid = threadIdx.x, lane = tid & 31;
-    int* out_cnt = cell_cnt + (size_t)b * P.total_cells + blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt = (1u << lane) - 1;
+    const int cell0 = ci * G.n_cols + cj0;
+    int* out_cnt = cell_cnt + (size_t)b * P.total_cells + G.cell_off + cell0;
+    const int w_cell = G.w_cell;
 
-    // cell view [iniX, maxX) x [iniY, maxY) (reference :819-839)
-    const int iniY = ORB_WIN + ci * G.h_cell, iniX = ORB_WIN + cj * G.w_cell;
-    int maxY = iniY + G.h_cell + 6, maxX = iniX + G.w_cell + 6;
-    if (iniY >= G.max_by - 3 || iniX >= G.max_bx - 6) { if (tid == 0) *out_cnt = 0; return; }
-    maxY = min(maxY, G.max_by);
-    maxX = min(maxX, G.max_bx);
+    // strip view [iniX, maxX) x [iniY, maxY) (reference :819-839).  A cell is skipped when
+    // iniX >= maxBorderX - 6; only the last processed cell of a row can be clipped.
+    const int iniY = ORB_WIN + ci * G.h_cell, iniX = ORB_WIN + cj0 * w_cell;
+    int nv = 0;
+    if (iniY < G.max_by - 3)
+        for (int j = 0; j < nc; ++j) nv += (iniX + j * w_cell < G.max_bx - 6);
+    const int maxY = min(iniY + G.h_cell + 6, G.max_by), maxX = min(iniX + nv * w_cell + 6, G.max_bx);
     const int tw = maxX - iniX, th = maxY - iniY;
     const int iw = tw - 6, ih = th - 6;  // interior = tested pixels
-    if (iw <= 0 || ih <= 0) { if (tid == 0) *out_cnt = 0; return; }
+    if (nv == 0 || iw <= 0 || ih <= 0) { if (tid < nc) out_cnt[tid] = 0; return; }
+    if (tid >= nv && tid < nc) out_cnt[tid] = 0;
 
     uint8_t* sc = smem + smem_tile_bytes;
-    uint16_t* list_a = reinterpret_cast<uint16_t*>(sc + smem_score_bytes);
-    uint16_t* list_b = reinterpret_cast<uint16_t*>(sc + smem_score_bytes + smem_surv_bytes);
-    uint32_t* fin = reinterpret_cast<uint32_t*>(sc + smem_score_bytes + 2 * smem_surv_bytes);
-    const int tpw = (G.w_cell + 6 + 3 + 3) >> 2, tp = tpw * 4;  // tile pitch in words / bytes
-    const int sp = iw + 2;                                     // score pitch
-    const unsigned magic = (1u << 20) / (unsigned)iw + 1u;  // i / iw == (i * magic) >> 20 for i < 2^20 / iw
+    uint16_t* list = reinterpret_cast<uint16_t*>(sc + smem_score_bytes);
 
-    // (1) stage with aligned 32-bit loads: the tile keeps the level's word alignment (view starts at byte `shift`)
-    const int shift = iniX & 3;
-    uint32_t* tw32 = reinterpret_cast<uint32_t*>(smem);
+    // (1) stage with aligned 16-byte loads (view starts at byte `shift` of the tile rows)
+    const int shift = iniX & 15;
     {
         const uint8_t* S = pyr + G.off + (size_t)b * G.img_stride + (size_t)iniY * G.pitch + (iniX - shift);
-        const int nw = (tw + shift + 3) >> 2;
-        const unsigned wmagic = (1u << 20) / (unsigned)nw + 1u;
-        for (int i = tid; i < nw * th; i += FAST_THREADS) {
-            const int y = (int)(((unsigned)i * wmagic) >> 20), x = i - y * nw;
-            tw32[y * tpw + x] = __ldg(reinterpret_cast<const uint32_t*>(S + (size_t)y * G.pitch) + x);
+        const int nq = (tw + shift + 15) >> 4;
+        const unsigned qmagic = (1u << 16) / (unsigned)nq + 1u;   // i / nq for i < 2^16 / nq
+        uint4* t4 = reinterpret_cast<uint4*>(smem);
+        for (int i = tid; i < nq * th; i += FAST_THREADS) {
+            const int y = (int)(((unsigned)i * qmagic) >> 16), x = i - y * nq;
+            t4[y * (TP / 16) + x] = __ldg(reinterpret_cast<const uint4*>(S + (size_t)y * G.pitch) + x);
         }
         uint32_t* sc32 = reinterpret_cast<uint32_t*>(sc);
-        for (int i = tid; i < (((ih + 2) * sp + 3) >> 2); i += FAST_THREADS) sc32[i] = 0u;
+        for (int i = tid; i < (ih + 2) * (SP / 4); i += FAST_THREADS) sc32[i] = 0u;
     }
+    __syncthreads();
+    const uint32_t* tw32 = reinterpret_cast<const uint32_t*>(smem);
     const uint8_t* tile = smem + shift;
     // interior words of a row: word wx holds interior pixels xi = 4 * wx - shift - 3 + k, k = 0..3
     const int w0 = (shift + 3) >> 2, nwi = ((shift + 3 + iw - 1) >> 2) - w0 + 1;
     const unsigned gmagic = (1u << 20) / (unsigned)nwi + 1u;
     const int ngroups = nwi * ih;
+    const int chunk = (ngroups + FAST_WARPS - 1) / FAST_WARPS;
+    uint16_t* seg = list + warp * chunk * 4;
+    const int t = P.min_th, ini_th = P.ini_th;
 
-    for (int pass = 0; pass < 2; ++pass) {
-        const int t = pass == 0 ? P.ini_th : P.min_th;
-        if (tid == 0) { s_na = 0; s_nb = 0; s_nfin = 0; }
-        __syncthreads();
-
-        // (A) 4 pixels per thread
+    // (2) necessary test: both ring pixels of the vertical pair (1, 9) and of the horizontal pair
+    // (5, 13) within t of the centre => no 9-arc
+    int n_a = 0;
+    {
         const unsigned kk = (unsigned)(127 - min(t, 126)) * 0x01010101u;
-        for (int base = 0; base < ngroups; base += FAST_THREADS) {
-            const int g = base + tid;
-            unsigned m = 0;
-            int i0 = 0;
-            if (g < ngroups) {
-                const int y = (int)(((unsigned)g * gmagic) >> 20), wx = w0 + (g - y * nwi);
-                const uint32_t* c = tw32 + (y + 3) * tpw + wx;
-                const unsigned C = c[0], N = c[-3 * tpw], S = c[3 * tpw], L = c[-1], R = c[1];
+        const int xfirst = 4 * w0 - shift - 3;                       // <= 0: interior x of byte 0 of the first word
+        const unsigned mfirst = 0x80808080u << (8 * -xfirst);
+        const int over = xfirst + 4 * nwi - iw;                      // bytes of the last word beyond the interior (0..3)
+        const unsigned mlast = 0x80808080u >> (8 * over);
+        const int gend = min(ngroups, (warp + 1) * chunk);
+        for (int gi = warp * chunk + lane; gi - lane < gend; gi += 32) {
+            unsigned m = 0, i0 = 0;
+            if (gi < gend) {
+                const int y = (int)(((unsigned)gi * gmagic) >> 20), wxi = gi - y * nwi;
+                const uint32_t* c = tw32 + (y + 3) * TPW + w0 + wxi;
+                const unsigned C = c[0], N = c[-3 * TPW], S = c[3 * TPW], L = c[-1], R = c[1];
                 const unsigned E = __byte_perm(C, R, 0x6543), Wp = __byte_perm(L, C, 0x4321);  // x + 3, x - 3
                 const unsigned pv = gt_bytes(__vabsdiffu4(N, C), kk) | gt_bytes(__vabsdiffu4(S, C), kk);
                 const unsigned ph = gt_bytes(__vabsdiffu4(E, C), kk) | gt_bytes(__vabsdiffu4(Wp, C), kk);
-                const int xi0 = 4 * wx - shift - 3;
-                unsigned valid = 0x80808080u;
-                if (xi0 < 0) valid &= 0xffffffffu << (8 * -xi0);
-                if (xi0 + 4 > iw) valid &= 0xffffffffu >> (8 * (xi0 + 4 - iw));
-                m = pv & ph & valid;
-                i0 = y * iw + xi0;
+                m = pv & ph & 0x80808080u;
+                if (wxi == 0) m &= mfirst;
+                if (wxi == nwi - 1) m &= mlast;
+                i0 = (unsigned)((y << 8) + xfirst + 4 * wxi);
             }
             const int cnt = __popc(m);
             const unsigned b1 = __ballot_sync(0xffffffffu, cnt >= 1);
             if (b1) {
                 const unsigned b2 = __ballot_sync(0xffffffffu, cnt >= 2), b3 = __ballot_sync(0xffffffffu, cnt >= 3),
                                b4 = __ballot_sync(0xffffffffu, cnt >= 4);
-                int wbase = 0;
-                if (lane == 0) wbase = atomicAdd(&s_na, __popc(b1) + __popc(b2) + __popc(b3) + __popc(b4));
-                wbase = __shfl_sync(0xffffffffu, wbase, 0);
-                const unsigned lt = (1u << lane) - 1;
-                int o = wbase + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt) + __popc(b4 & lt);
-                if (m & 0x80u) list_a[o++] = (uint16_t)i0;
-                if (m & 0x8000u) list_a[o++] = (uint16_t)(i0 + 1);
-                if (m & 0x800000u) list_a[o++] = (uint16_t)(i0 + 2);
-                if (m & 0x80000000u) list_a[o++] = (uint16_t)(i0 + 3);
+                int o = n_a + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt) + __popc(b4 & lt);
+                if (m & 0x80u) seg[o++] = (uint16_t)i0;
+                if (m & 0x8000u) seg[o++] = (uint16_t)(i0 + 1);
+                if (m & 0x800000u) seg[o++] = (uint16_t)(i0 + 2);
+                if (m & 0x80000000u) seg[o++] = (uint16_t)(i0 + 3);
+                n_a += __popc(b1) + __popc(b2) + __popc(b3) + __popc(b4);
             }
         }
-        __syncthreads();
-        const int na = s_na;
-        if (na == 0) { if (pass == 0) continue; break; }   // uniform: nothing can appear at this threshold
-
-        // (B) necessary test with polarity: a 9-arc contains one pixel of every opposite pair of the ring
-        for (int base = 0; base < na; base += FAST_THREADS) {
-            const int k = base + tid;
-            bool pass_t = false;
-            int i = 0;
-            if (k < na) {
-                i = list_a[k];
-                const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
-                const uint8_t* c = tile + (y + 3) * tp + x + 3;
-                const int v = c[0], lo = v - t, hi = v + t;
-                const int p0 = c[3 * tp], p8 = c[-3 * tp], p4 = c[3], p12 = c[-3];
-                const int p2 = c[2 * tp + 2], p10 = c[-2 * tp - 2], p6 = c[-2 * tp + 2], p14 = c[2 * tp - 2];
-                const bool dark = (p0 < lo || p8 < lo) && (p4 < lo || p12 < lo) && (p2 < lo || p10 < lo) && (p6 < lo || p14 < lo);
-                const bool brt = (p0 > hi || p8 > hi) && (p4 > hi || p12 > hi) && (p2 > hi || p10 > hi) && (p6 > hi || p14 > hi);
-                pass_t = dark || brt;
-            }
-            const unsigned m = __ballot_sync(0xffffffffu, pass_t);
-            if (m) {
-                int wbase = 0;
-                if (lane == 0) wbase = atomicAdd(&s_nb, __popc(m));
-                wbase = __shfl_sync(0xffffffffu, wbase, 0);
-                if (pass_t) list_b[wbase + __popc(m & ((1u << lane) - 1))] = (uint16_t)i;
-            }
-        }
-        __syncthreads();
-        const int nb = s_nb;
-        if (nb == 0) { if (pass == 0) continue; break; }
-
-        // (C) exact score of the survivors (dense warps)
-        for (int k = tid; k < nb; k += FAST_THREADS) {
-            const int i = list_b[k];
-            const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
-            const uint8_t* c = tile + (y + 3) * tp + x + 3;
-            int p[16];
-            p[0] = c[3 * tp];          p[1] = c[3 * tp + 1];   p[2] = c[2 * tp + 2];   p[3] = c[tp + 3];
-            p[4] = c[3];               p[5] = c[-tp + 3];      p[6] = c[-2 * tp + 2];  p[7] = c[-3 * tp + 1];
-            p[8] = c[-3 * tp];         p[9] = c[-3 * tp - 1];  p[10] = c[-2 * tp - 2]; p[11] = c[-tp - 3];
-            p[12] = c[-3];             p[13] = c[tp - 3];      p[14] = c[2 * tp - 2];  p[15] = c[3 * tp - 1];
-            const int s = fast_corner_score(c[0], p);
-            if (s >= t) sc[(y + 1) * sp + x + 1] = (uint8_t)s;
-        }
-        __syncthreads();
-
-        // (D) strict local maxima among the survivors -> final list (unordered)
-        for (int k = tid; k < nb; k += FAST_THREADS) {
-            const int i = list_b[k];
-            const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
-            const uint8_t* q = sc + (y + 1) * sp + x + 1;
-            const int s = q[0];
-            if (s >= t && s > q[-1] && s > q[1] && s > q[-sp - 1] && s > q[-sp] && s > q[-sp + 1] && s > q[sp - 1] && s > q[sp] && s > q[sp + 1])
-                fin[atomicAdd(&s_nfin, 1)] = ((uint32_t)i << 8) | (uint32_t)s;
-        }
-        __syncthreads();
-        if (s_nfin > 0) break;   // uniform.  Empty at iniThFAST -> retry with minThFAST (:843-850)
     }
+    __syncwarp();
 
-    // (5) ordered write: rank of a keypoint = number of keypoints at a smaller row-major index
-    const int nfin = s_nfin;
-    if (tid == 0) *out_cnt = nfin;
-    uint32_t* out = stage + (size_t)b * P.stage_per_image + G.stage_off + (size_t)cell * G.cell_cap;
-    const int kx0 = 3 + cj * G.w_cell, ky0 = 3 + ci * G.h_cell;  // window-relative coords of interior (0, 0)
-    for (int k = tid; k < nfin; k += FAST_THREADS) {
-        const uint32_t e = fin[k];
-        int rank = 0;
-        for (int j = 0; j < nfin; ++j) rank += fin[j] < e;
-        const int i = (int)(e >> 8), s = (int)(e & 0xffu);
-        const int y = (int)(((unsigned)i * magic) >> 20), x = i - y * iw;
-        out[rank] = ((uint32_t)s << 24) | ((uint32_t)(y + ky0) << 12) | (uint32_t)(x + kx0);
+    // (3) exact score, two survivors per thread; corners (s >= minTh) compacted in place
+    int n_c = 0;
+    for (int k0 = 0; k0 < n_a; k0 += 64) {
+        const int k = k0 + 2 * lane;
+        const bool va = k < n_a, vb = k + 1 < n_a;
+        const unsigned pr = va ? reinterpret_cast<const uint32_t*>(seg)[k >> 1] : 0u;  // segments start 8-byte aligned
+        const int ia = (int)(pr & 0xffffu), ib = vb ? (int)(pr >> 16) : ia;
+        const int ya = ia >> 8, xa = ia & 0xff, yb = ib >> 8, xb = ib & 0xff;
+        const uint8_t* ca = tile + (ya + 3) * TP + xa + 3;
+        const uint8_t* cb = tile + (yb + 3) * TP + xb + 3;
+        const unsigned negv = __vneg2((unsigned)ca[0] | ((unsigned)cb[0] << 16));
+        unsigned e[16];
+#define RING(k_, off_) e[k_] = __vadd2((unsigned)ca[off_] | ((unsigned)cb[off_] << 16), negv)
+        RING(0, 3 * TP);       RING(1, 3 * TP + 1);   RING(2, 2 * TP + 2);    RING(3, TP + 3);
+        RING(4, 3);            RING(5, -TP + 3);      RING(6, -2 * TP + 2);   RING(7, -3 * TP + 1);
+        RING(8, -3 * TP);      RING(9, -3 * TP - 1);  RING(10, -2 * TP - 2);  RING(11, -TP - 3);
+        RING(12, -3);          RING(13, TP - 3);      RING(14, 2 * TP - 2);   RING(15, 3 * TP - 1);
+#undef RING
+        const unsigned s2 = fast_score_x2(e);
+        const int sa = (int)(short)(s2 & 0xffffu), sb = (int)(short)(s2 >> 16);
+        const bool fa = va && sa >= t, fb = vb && sb >= t;
+        if (fa) sc[(ya + 1) * SP + xa + 1] = (uint8_t)sa;
+        if (fb) sc[(yb + 1) * SP + xb + 1] = (uint8_t)sb;
+        const unsigned ba = __ballot_sync(0xffffffffu, fa), bb = __ballot_sync(0xffffffffu, fb);  // also orders the reads above before the writes below
+        int o = n_c + __popc(ba & lt) + __popc(bb & lt);
+        if (fa) seg[o++] = (uint16_t)ia;
+        if (fb) seg[o] = (uint16_t)ib;
+        n_c += __popc(ba) + __popc(bb);
+        __syncwarp();
+    }
+    __syncthreads();   // score map complete
+
+    // (4) strict local maxima inside the own cell's interior, compacted in place (in order); per-lane
+    // counts per cell in 16-bit fields (cells 0,1 | cells 2,3), reduced once per warp
+    unsigned ca01 = 0, ca23 = 0, cs01 = 0, cs23 = 0;
+    int n_m = 0;
+    for (int k0 = 0; k0 < n_c; k0 += 32) {
+        const int k = k0 + lane;
+        bool mx = false;
+        int i = 0;
+        if (k < n_c) {
+            i = seg[k];
+            const int y = i >> 8, x = i & 0xff;
+            const uint8_t* q = sc + (y + 1) * SP + x + 1;
+            const int s = q[0];
+            const int c = (int)(((unsigned)x * G.wcell_magic) >> 20);
+            const int lx = x - c * w_cell;
+            const int cw = (c == nv - 1) ? iw - c * w_cell : w_cell;
+            const int nb0 = max(q[-SP], q[SP]);
+            const int nbl = max(max(q[-1], q[-SP - 1]), q[SP - 1]);
+            const int nbr = max(max(q[1], q[-SP + 1]), q[SP + 1]);
+            mx = s > nb0 && (lx == 0 || s > nbl) && (lx == cw - 1 || s > nbr);
+            if (mx) {
+                const unsigned inc = 1u << ((c & 1) << 4), incs = s >= ini_th ? inc : 0u;
+                if (c < 2) { ca01 += inc; cs01 += incs; } else { ca23 += inc; cs23 += incs; }
+            }
+        }
+        const unsigned bm = __ballot_sync(0xffffffffu, mx);   // also orders this iteration's reads before the writes
+        if (mx) seg[n_m + __popc(bm & lt)] = (uint16_t)i;
+        n_m += __popc(bm);
+        __syncwarp();
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        ca01 += __shfl_xor_sync(0xffffffffu, ca01, o); ca23 += __shfl_xor_sync(0xffffffffu, ca23, o);
+        cs01 += __shfl_xor_sync(0xffffffffu, cs01, o); cs23 += __shfl_xor_sync(0xffffffffu, cs23, o);
+    }
+    if (lane < ORB_FAST_G) {
+        const unsigned a = lane < 2 ? ca01 : ca23, st = lane < 2 ? cs01 : cs23;
+        const int sh = (lane & 1) << 4;
+        s_wc[warp][lane] = (int)(((a >> sh) & 0xffffu) | (((st >> sh) & 0xffffu) << 16));
+    }
+    __syncthreads();
+
+    // (5) threshold per cell (reference :843-850), offsets of this warp's segment, ordered write.
+    // lane = 4 * w' + c holds the counts of warp w' for cell c (FAST_WARPS * ORB_FAST_G == 32)
+    int tot = s_wc[lane >> 2][lane & 3];
+    int before = (lane >> 2) < warp ? tot : 0;
+#pragma unroll
+    for (int o = 4; o < 32; o <<= 1) {
+        tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        before += __shfl_xor_sync(0xffffffffu, before, o);
+    }
+    const bool use_ini = (tot >> 16) > 0;
+    if (warp == 0 && lane < nv) out_cnt[lane] = use_ini ? (tot >> 16) : (tot & 0xffff);
+    const int my_base = use_ini ? (before >> 16) : (before & 0xffff), my_th = use_ini ? ini_th : 0;
+    int base_c[ORB_FAST_G], th_c[ORB_FAST_G];
+#pragma unroll
+    for (int c = 0; c < ORB_FAST_G; ++c) {
+        base_c[c] = __shfl_sync(0xffffffffu, my_base, c);
+        th_c[c] = __shfl_sync(0xffffffffu, my_th, c);
+    }
+    const int ky0 = 3 + ci * G.h_cell, kx00 = 3 + cj0 * w_cell;
+    uint32_t* out0 = stage + (size_t)b * P.stage_per_image + G.stage_off + (size_t)cell0 * G.cell_cap;
+    for (int k0 = 0; k0 < n_m; k0 += 32) {
+        const int k = k0 + lane;
+        int c = -1, s = 0, y = 0, x = 0;
+        if (k < n_m) {
+            const int i = seg[k];
+            y = i >> 8; x = i & 0xff;
+            s = sc[(y + 1) * SP + x + 1];
+            c = (int)(((unsigned)x * G.wcell_magic) >> 20);
+        }
+#pragma unroll
+        for (int cc = 0; cc < ORB_FAST_G; ++cc) {
+            const bool mine = c == cc && s >= th_c[cc];
+            const unsigned bm = __ballot_sync(0xffffffffu, mine);
+            if (mine) out0[cc * G.cell_cap + base_c[cc] + __popc(bm & lt)] = ((uint32_t)s << 24) | ((uint32_t)(y + ky0) << 12) | (uint32_t)(x + kx00);
+            base_c[cc] += __popc(bm);
+        }
     }
 }
 
@@ -1002,30 +1060,37 @@ void launch_gauss(cudaStream_t s, const uint8_t* pyr, uint8_t* blur, const Plan&
     dim3 grid(P.total_tiles, batch);
     k_gauss7<<<grid, 256, 0, s>>>(pyr, blur, P);
 }
-static void fast_smem(const Plan& P, int* tile_bytes, int* score_bytes, int* surv_bytes, int* total) {
-    int mt = 0, ms = 0, mv = 0, mf = 0;
+// Tile pitch variant: 192 bytes covers w_cell <= 39 (every level with >= 4 cell columns), 272 the rest (w_cell <= 59).
+static int fast_tile_pitch(const Plan& P) {
+    int wc = 0;
+    for (int l = 0; l < P.nlevels; ++l) if (P.lv[l].n_cols > 0) wc = max(wc, P.lv[l].w_cell);
+    return (ORB_FAST_G * wc + 6 + 15 + 15 <= 192 + 15) && (ORB_FAST_G * wc + 2 + 3 <= 160 + 3) ? 192 : 272;
+}
+static void fast_smem(const Plan& P, int tp, int* tile_bytes, int* score_bytes, int* total) {
+    int mh = 0, mv = 0;
     for (int l = 0; l < P.nlevels; ++l) {
         const LevelGeom& G = P.lv[l];
-        const int tp = ((G.w_cell + 6 + 3 + 3) >> 2) * 4, th = G.h_cell + 6;
-        mt = max(mt, tp * th);
-        ms = max(ms, (G.w_cell + 2) * (G.h_cell + 2));
-        mv = max(mv, G.w_cell * G.h_cell);
-        mf = max(mf, G.cell_cap);
+        if (G.n_cols == 0) continue;
+        mh = max(mh, G.h_cell);
+        // 4-pixel words per strip row (+2 for alignment) x rows, rounded up per warp, 4 entries each
+        mv = max(mv, 4 * ((ORB_FAST_G * G.w_cell / 4 + 2) * G.h_cell + FAST_WARPS));
     }
-    *tile_bytes = (mt + 15) & ~15;
-    *score_bytes = (ms + 15) & ~15;
-    *surv_bytes = (2 * mv + 15) & ~15;
-    *total = *tile_bytes + *score_bytes + 2 * *surv_bytes + 4 * mf + 16;
+    *tile_bytes = tp * (mh + 6);
+    *score_bytes = (tp - 32) * (mh + 2);
+    *total = *tile_bytes + *score_bytes + 2 * mv + 16;
 }
 cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch) {
-    int tb, sb, vb, tot;
-    fast_smem(P, &tb, &sb, &vb, &tot);
+    const int tp = fast_tile_pitch(P);
+    int tb, sb, tot;
+    fast_smem(P, tp, &tb, &sb, &tot);
+    if (tot > 200 * 1024) return cudaErrorInvalidConfiguration;
+    auto kern = tp == 192 ? k_fast_cells<192> : k_fast_cells<272>;
     if (tot > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, tot);
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tot);
         if (e != cudaSuccess) return e;
     }
-    dim3 grid(P.total_cells, batch);
-    k_fast_cells<<<grid, FAST_THREADS, tot, s>>>(pyr, cell_cnt, stage, P, tb, sb, vb);
+    dim3 grid(P.total_groups, batch);
+    kern<<<grid, FAST_THREADS, tot, s>>>(pyr, cell_cnt, stage, P, tb, sb);
     return cudaSuccess;
 }
 size_t quadtree_smem(int cap, int* p2_out) {

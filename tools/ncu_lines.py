@@ -17,7 +17,11 @@ for r in data:
     if r[iln] in seen and False: pass
     first.append(r)
 agg = {}
+def _int(v):
+    try: return int(v)
+    except ValueError: return None
 for r in first:
+    if _int(r[isamp]) is None or _int(r[iinst]) is None: continue
     a = agg.setdefault(int(r[iln]), [0, 0, r[isrc]]); a[0] += int(r[isamp]); a[1] += int(r[iinst])
 ts = sum(a[0] for a in agg.values()); ti = sum(a[1] for a in agg.values())
 print("samples", ts, "warp instr", ti)

@@ -9,6 +9,15 @@
 #include "orb_internal.h"
 #include "sincosf_glibc.h"
 
+// LDGSTS: global -> shared copies that bypass the register file (4- or 16-byte, both sides aligned)
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 __constant__ __align__(16) signed char c_pattern[1024] = {
 #include "../../include/orb_pattern_31.inc"
 };
@@ -52,53 +61,70 @@ __device__ __forceinline__ unsigned pick_pair(unsigned w0, unsigned w1, unsigned
     return __byte_perm(lo, hi, j | ((j + 1) << 4));
 }
 
+#define RESIZE_ROWS 4   // destination rows per thread: the horizontal tables and byte selectors are per column
 __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr, const LevelGeom src, const LevelGeom dst) {
     const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4;
-    const int y = blockIdx.y * 4 + threadIdx.y;
-    if (x4 >= dst.w || y >= dst.h) return;
+    const int y0 = (blockIdx.y * 4 + threadIdx.y) * RESIZE_ROWS;
+    if (x4 >= dst.w || y0 >= dst.h) return;
     const uint8_t* S = pyr + src.off + (size_t)blockIdx.z * src.img_stride;
     uint8_t* D = pyr + dst.off + (size_t)blockIdx.z * dst.img_stride;
-    int sy0 = dst.yofs[y], sy1 = sy0 + 1;
-    sy0 = min(max(sy0, 0), src.h - 1);
-    sy1 = min(max(sy1, 0), src.h - 1);
-    const unsigned bw = reinterpret_cast<const unsigned*>(dst.beta)[y];
-    const int b0 = (int)(bw & 0xffffu), b1 = (int)(bw >> 16);
-    const uint8_t* r0 = S + (size_t)sy0 * src.pitch;
-    const uint8_t* r1 = S + (size_t)sy1 * src.pitch;
     // tables are padded to a multiple of 4 entries and 16-byte aligned
     const int4 xo = reinterpret_cast<const int4*>(dst.xofs)[x4 >> 2];
     const uint4 al = reinterpret_cast<const uint4*>(dst.alpha)[x4 >> 2];
     const int base = xo.x & ~3;
     const int sxs[4] = {xo.x, xo.y, xo.z, xo.w};
     const unsigned als[4] = {al.x, al.y, al.z, al.w};
-    uint32_t out = 0;
-    if (xo.w - base <= 7) {
-        const unsigned* p0 = reinterpret_cast<const unsigned*>(r0 + base);
-        const unsigned* p1 = reinterpret_cast<const unsigned*>(r1 + base);
-        const unsigned u0 = p0[0], u1 = p0[1], u2 = p0[2], v0 = p1[0], v1 = p1[1], v2 = p1[2];
+    const bool window = xo.w - base <= 7;
+    unsigned sel[4];
+    bool hi4[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int idx = sxs[i] - base;
-            const int h0 = (int)__dp2a_lo(als[i], pick_pair(u0, u1, u2, idx), 0u);
-            const int h1 = (int)__dp2a_lo(als[i], pick_pair(v0, v1, v2, idx), 0u);
-            int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-            v = min(max(v, 0), 255);
-            out |= (uint32_t)v << (8 * i);
-        }
-    } else {  // generic path (scale factors whose 4-pixel footprint exceeds the 12-byte window)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int sx = sxs[i], sx1 = min(sx + 1, src.w - 1);
-            const int a0 = (int)(als[i] & 0xffffu), a1 = (int)(als[i] >> 16);
-            const int h0 = r0[sx] * a0 + r0[sx1] * a1;
-            const int h1 = r1[sx] * a0 + r1[sx1] * a1;
-            int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-            v = min(max(v, 0), 255);
-            out |= (uint32_t)v << (8 * i);
-        }
+    for (int i = 0; i < 4; ++i) {
+        const int idx = sxs[i] - base;
+        const unsigned j = idx & 3;
+        sel[i] = j | ((j + 1) << 4);
+        hi4[i] = idx >= 4;
     }
-    // rows are pitch-padded to a multiple of 64 bytes, so the full word is always in bounds
-    *reinterpret_cast<uint32_t*>(D + (size_t)y * dst.pitch + x4) = out;
+#pragma unroll
+    for (int r = 0; r < RESIZE_ROWS; ++r) {
+        const int y = y0 + r;
+        if (y >= dst.h) break;
+        int sy0 = dst.yofs[y], sy1 = sy0 + 1;
+        sy0 = min(max(sy0, 0), src.h - 1);
+        sy1 = min(max(sy1, 0), src.h - 1);
+        const unsigned bw = reinterpret_cast<const unsigned*>(dst.beta)[y];
+        const int b0 = (int)(bw & 0xffffu), b1 = (int)(bw >> 16);
+        const uint8_t* r0 = S + (size_t)sy0 * src.pitch;
+        const uint8_t* r1 = S + (size_t)sy1 * src.pitch;
+        uint32_t out = 0;
+        if (window) {
+            const unsigned* p0 = reinterpret_cast<const unsigned*>(r0 + base);
+            const unsigned* p1 = reinterpret_cast<const unsigned*>(r1 + base);
+            const unsigned u0 = p0[0], u1 = p0[1], u2 = p0[2], v0 = p1[0], v1 = p1[1], v2 = p1[2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const unsigned pu = __byte_perm(hi4[i] ? u1 : u0, hi4[i] ? u2 : u1, sel[i]);
+                const unsigned pv = __byte_perm(hi4[i] ? v1 : v0, hi4[i] ? v2 : v1, sel[i]);
+                const int h0 = (int)__dp2a_lo(als[i], pu, 0u);
+                const int h1 = (int)__dp2a_lo(als[i], pv, 0u);
+                // weights sum to 2048 * 2048: the result is a convex combination of bytes, no clamp needed
+                const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+                out |= (uint32_t)v << (8 * i);
+            }
+        } else {  // generic path (scale factors whose 4-pixel footprint exceeds the 12-byte window)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int sx = sxs[i], sx1 = min(sx + 1, src.w - 1);
+                const int a0 = (int)(als[i] & 0xffffu), a1 = (int)(als[i] >> 16);
+                const int h0 = r0[sx] * a0 + r0[sx1] * a1;
+                const int h1 = r1[sx] * a0 + r1[sx1] * a1;
+                int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+                v = min(max(v, 0), 255);
+                out |= (uint32_t)v << (8 * i);
+            }
+        }
+        // rows are pitch-padded to a multiple of 64 bytes, so the full word is always in bounds
+        *reinterpret_cast<uint32_t*>(D + (size_t)y * dst.pitch + x4) = out;
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -138,8 +164,8 @@ __global__ void __launch_bounds__(256) k_gauss7(const uint8_t* __restrict__ pyr,
         const int gx = tx - 4 + 4 * j;
         const uint8_t* row = S + (size_t)gy * G.pitch;
         uint32_t v;
-        if (gx >= 0 && gx + 3 < W) v = *reinterpret_cast<const uint32_t*>(row + gx);
-        else if (one_step) {
+        if (gx >= 0 && gx + 3 < W) { cp_async4(&raw[ry][j], row + gx); continue; }   // asynchronous: no register staging, all loads in flight
+        if (one_step) {
             v = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -154,6 +180,7 @@ __global__ void __launch_bounds__(256) k_gauss7(const uint8_t* __restrict__ pyr,
         }
         raw[ry][j] = v;
     }
+    cp_async_wait_all();
     __syncthreads();
     const int cx = tid & 31, r0 = (tid >> 5) * 8;
     const int ox = tx + 4 * cx;
@@ -288,10 +315,11 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
         uint4* t4 = reinterpret_cast<uint4*>(smem);
         for (int i = tid; i < nq * th; i += FAST_THREADS) {
             const int y = (int)(((unsigned)i * qmagic) >> 16), x = i - y * nq;
-            t4[y * (TP / 16) + x] = __ldg(reinterpret_cast<const uint4*>(S + (size_t)y * G.pitch) + x);
+            cp_async16(&t4[y * (TP / 16) + x], reinterpret_cast<const uint4*>(S + (size_t)y * G.pitch) + x);
         }
         uint32_t* sc32 = reinterpret_cast<uint32_t*>(sc);
         for (int i = tid; i < (ih + 2) * (SP / 4); i += FAST_THREADS) sc32[i] = 0u;
+        cp_async_wait_all();
     }
     __syncthreads();
     const uint32_t* tw32 = reinterpret_cast<const uint32_t*>(smem);
@@ -658,10 +686,12 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
     }
     const int n = carry;
     __syncthreads();
-    for (int c = warp; c < n_cells; c += QT_WARPS) {
+    // one thread per cell (lists are short; a warp per cell would serialise n_cells / 8 dependent round trips)
+    for (int c = tid; c < n_cells; c += QT_THREADS) {
         const int cnt = ccnt[c], o = cpre[c];
         const uint32_t* s = stg + (size_t)c * G.cell_cap;
-        for (int i = lane; i < cnt; i += 32) kbuf0[o + i] = s[i];
+#pragma unroll 4
+        for (int i = 0; i < cnt; ++i) kbuf0[o + i] = s[i];
     }
     if (tid == 0) lvl_ncand[b * ORB_MAX_LEVELS + l] = n;
     __syncthreads();
@@ -872,9 +902,23 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
         size = new_size;
     }
 
-    // ---- 3. best response per node (first maximum wins), emitted in list order
+    // ---- 3. best response per node (first maximum wins), emitted in list order.  Small nodes: one
+    // thread each; nodes with many keys: one warp each.
+    for (int i = tid; i < size; i += QT_THREADS) {
+        const QNode nd = cur[i];
+        if (nd.count > 64) continue;
+        const uint32_t* src = ((nd.start < 0) ? kbuf1 : kbuf0) + (nd.start & 0x7fffffff);
+        uint32_t bk = src[0];
+#pragma unroll 4
+        for (int j = 1; j < nd.count; ++j) {
+            const uint32_t k = src[j];
+            if ((k >> 24) > (bk >> 24)) bk = k;
+        }
+        out[size - 1 - i] = bk;
+    }
     for (int i = warp; i < size; i += QT_WARPS) {
         const QNode nd = cur[i];
+        if (nd.count <= 64) continue;
         const uint32_t* src = ((nd.start < 0) ? kbuf1 : kbuf0) + (nd.start & 0x7fffffff);
         unsigned long long best = 0ull;
         for (int j = lane; j < nd.count; j += 32) {
@@ -1053,7 +1097,7 @@ k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ b
 // ------------------------------------------------------------------------------------------
 // host-callable launchers (used by extractor.cu)
 void launch_resize(cudaStream_t s, uint8_t* pyr, const LevelGeom& src, const LevelGeom& dst, int batch) {
-    dim3 block(64, 4), grid((dst.w + 255) / 256, (dst.h + 3) / 4, batch);
+    dim3 block(64, 4), grid((dst.w + 255) / 256, (dst.h + 4 * RESIZE_ROWS - 1) / (4 * RESIZE_ROWS), batch);
     k_resize_level<<<grid, block, 0, s>>>(pyr, src, dst);
 }
 void launch_gauss(cudaStream_t s, const uint8_t* pyr, uint8_t* blur, const Plan& P, int batch) {

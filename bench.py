@@ -38,6 +38,11 @@ CPU_DESC = {
 }
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per image of the ncu --set full capture named below (batch 32)
+NCU_TRAFFIC_SOURCE = "profiles/r1_v3_full_batch32.txt"
+NCU_TRAFFIC_BYTES_PER_IMAGE = {"fast_cells": 1327000}
+
+
 def algorithmic_bytes_per_image(n_kp):
     """sum(levels) read + levels 1..7 written + blurred levels written + per-keypoint patches."""
     sizes = [(1241, 376), (1034, 313), (862, 261), (718, 218), (598, 181), (499, 151), (416, 126), (346, 105)]
@@ -139,7 +144,7 @@ def run_reference(args):
         return
     left, right = synth_pool()
     cores = os.cpu_count() or 1
-    per_step = max(16, 2 * cores)
+    per_step = 12 * cores   # ~0.1 core-seconds per pair: a step is about 1.5 s of wall clock on all cores
     cpu_pairs_per_s(min(per_step, cores), cores, left, right)  # page in
     for _ in range(args.warmup):
         cpu_pairs_per_s(per_step, cores, left, right)
@@ -306,8 +311,13 @@ def run_ours(args):
         dom_ms_launch = ext_stages[dom] / (1 if dom.startswith("stereo") else 2)
         achieved = dom_bytes / (dom_ms_launch * 1e-3) / 1e9
         pipe_ms = sum(v for k, v in stages.items())
+        # the same launch against the INT issue rate: SURVEY 8(d) counts 80 simple integer ops per pyramid pixel for FAST
+        sm_mhz = clocks.get("sm_mhz") or 1965.0
+        alu_peak = 148 * 128 * sm_mhz * 1e6 / 1e12
+        alu_ach = 1444097 * 80 * B / (stages["fast_cells"] / 2 * 1e-3) / 1e12
+        traffic = NCU_TRAFFIC_BYTES_PER_IMAGE.get(dom)
         cores = os.cpu_count() or 1
-        cpu_n = max(16, 2 * cores)
+        cpu_n = 12 * cores   # ~0.1 core-seconds per pair: about 20 s of CPU work
         cpu_val, cpu_dt, cpu_kind = cpu_pairs_per_s(cpu_n, cores, left, right)
         line = {
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -320,7 +330,10 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src,
+                         "traffic": (traffic * B if traffic else None), "traffic_source": NCU_TRAFFIC_SOURCE,
+                         "peak_source": peak_src,
+                         "alu": {"kernel": "fast_cells", "achieved": alu_ach, "peak": alu_peak, "unit": "Top/s (int, algorithmic: 80 per pixel)",
+                                 "frac": alu_ach / alu_peak},
                          "pipeline_achieved": 2 * B * alg_img / (pipe_ms * 1e-3) / 1e9,
                          "stage_ms_per_step": stages},
             "cpu_baseline": {"value": cpu_val, "unit": "frames/s", "cores": cores, "kind": cpu_kind,

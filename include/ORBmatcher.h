@@ -10,8 +10,11 @@
  * ORB_SLAM2::Frame, ORB_SLAM2::KeyFrame and ORB_SLAM2::MapPoint (unchanged call sites:
  * matcher.SearchByProjection(mCurrentFrame, mLastFrame, th, bMono) ...), in tests/cpp with small
  * structs carrying the same member names.  No CPU fallback: without a CUDA device the constructor
- * throws.  Not covered yet (SURVEY 8f "next"): SearchForInitialization, SearchBySim3, Fuse,
- * the relocalisation / loop SearchByProjection variants and SearchByBoW(KF, KF).
+ * throws.  Every public method of the reference class is covered.  The projection searches of
+ * relocalisation, loop closing, Fuse and SearchBySim3 keep the reference's host-side gates
+ * (cv::Mat float algebra, MapPoint::PredictScale, IsInImage) in this header, written with the
+ * reference's expressions, and replay the map updates (Replace / AddObservation / AddMapPoint) in
+ * point order on the host; the candidate search, Hamming distances and claims run on the device.
  */
 #ifndef ORBMATCHER_H
 #define ORBMATCHER_H
@@ -167,6 +170,263 @@ public:
         return nmatches;
     }
 
+    // Matching for the Map Initialization (only used in the monocular case)   (src/ORBmatcher.cc:429-578)
+    template <class FrameT>
+    int SearchForInitialization(FrameT& F1, FrameT& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10) {
+        FrameArrays a1, a2; GatherFrame(F1, a1); GatherFrame(F2, a2);
+        std::vector<float> px(a1.n > 0 ? a1.n : 1), py(a1.n > 0 ? a1.n : 1);
+        for (int i = 0; i < a1.n; ++i) { px[i] = vbPrevMatched[i].x; py[i] = vbPrevMatched[i].y; }
+        std::vector<int32_t> match(a1.n > 0 ? a1.n : 1, -1);
+        int32_t nmatches = 0;
+        Check(orb_search_for_initialization(Handle(), &a1.view, &a2.view, px.data(), py.data(), windowSize, mfNNratio, mbCheckOrientation,
+                                            match.data(), &nmatches));
+        vnMatches12.assign(match.begin(), match.begin() + a1.n);
+        for (int i = 0; i < a1.n; ++i) if (vnMatches12[i] >= 0) vbPrevMatched[i] = F2.mvKeysUn[vnMatches12[i]].pt;  // :571-574
+        return nmatches;
+    }
+
+    // Loop detection: brute force within vocabulary nodes between two KeyFrames   (src/ORBmatcher.cc:581-716)
+    template <class KeyFrameT, class MapPointT>
+    int SearchByBoW(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12) {
+        const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+        vpMatches12 = std::vector<MapPointT*>(vpMapPoints1.size(), static_cast<MapPointT*>(NULL));
+        FrameArrays a1, a2; GatherFrame(*pKF1, a1); GatherFrame(*pKF2, a2);
+        std::vector<unsigned char> has1(a1.n > 0 ? a1.n : 1, 0), has2(a2.n > 0 ? a2.n : 1, 0);
+        for (int i = 0; i < a1.n; ++i) has1[i] = vpMapPoints1[i] && !vpMapPoints1[i]->isBad();  // :620-624
+        for (int i = 0; i < a2.n; ++i) has2[i] = vpMapPoints2[i] && !vpMapPoints2[i]->isBad();  // :639-645
+        FeatVec v1, v2; Flatten(pKF1->mFeatVec, v1); Flatten(pKF2->mFeatVec, v2);
+        std::vector<int32_t> match(a1.n > 0 ? a1.n : 1, -1);
+        int32_t nmatches = 0;
+        Check(orb_search_by_bow_keyframes(Handle(), &a1.view, &v1.view, has1.data(), &a2.view, &v2.view, has2.data(), mfNNratio,
+                                          mbCheckOrientation, match.data(), &nmatches));
+        for (int i = 0; i < a1.n; ++i) if (match[i] >= 0) vpMatches12[i] = vpMapPoints2[match[i]];  // :665
+        return nmatches;
+    }
+
+    // Project MapPoints seen in KeyFrame into the Frame and search matches.
+    // Used in relocalisation (Tracking)                                  (src/ORBmatcher.cc:1622-1759)
+    template <class FrameT, class KeyFrameT, class MapPointT>
+    int SearchByProjection(FrameT& CurrentFrame, KeyFrameT* pKF, const std::set<MapPointT*>& sAlreadyFound, const float th, const int ORBdist) {
+        FrameArrays fa; GatherFrame(CurrentFrame, fa);
+        float Rcw[9], tcw[3], Ow[3];
+        SplitPose(CurrentFrame.mTcw, Rcw, tcw);
+        CameraCentre(Rcw, tcw, Ow);                                              // :1626-1628
+        const std::vector<MapPointT*> vpMPs = pKF->GetMapPointMatches();
+        const int M = (int)vpMPs.size();
+        Projected pv(M);
+        for (int i = 0; i < M; ++i) {
+            MapPointT* pMP = vpMPs[i];
+            if (!pMP || pMP->isBad() || sAlreadyFound.count(pMP)) continue;      // :1639-1643
+            const cv::Mat x3Dw = pMP->GetWorldPos();
+            const float xw[3] = {x3Dw.template at<float>(0), x3Dw.template at<float>(1), x3Dw.template at<float>(2)};
+            const float xc = MulRowAdd(Rcw + 0, xw, tcw[0]), yc = MulRowAdd(Rcw + 3, xw, tcw[1]), zc = MulRowAdd(Rcw + 6, xw, tcw[2]);
+            const float invzc = (float)(1.0 / zc);                               // :1650
+            const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx, v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+            if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+            if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+            const float dist3D = Norm3(xw[0] - Ow[0], xw[1] - Ow[1], xw[2] - Ow[2]);   // :1661-1662
+            if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+            const int lvl = pMP->PredictScale(dist3D, &CurrentFrame);
+            pv.Set(i, u, v, 0.f, th * CurrentFrame.mvScaleFactors[lvl], lvl - 1, lvl + 1, pMP->GetDescriptor(), pKF->mvKeysUn[i].angle);
+        }
+        std::vector<unsigned char> occ(fa.n > 0 ? fa.n : 1, 0);
+        for (int i = 0; i < fa.n; ++i) occ[i] = CurrentFrame.mvpMapPoints[i] != NULL;    // :1690
+        std::vector<int32_t> match(fa.n > 0 ? fa.n : 1, -1);
+        int32_t nmatches = 0;
+        Check(orb_search_by_projection_claiming(Handle(), &fa.view, pv.View(true), occ.data(), ORBdist, mbCheckOrientation, match.data(), NULL, &nmatches));
+        for (int i = 0; i < fa.n; ++i) if (match[i] >= 0) CurrentFrame.mvpMapPoints[i] = vpMPs[match[i]];
+        return nmatches;
+    }
+
+    // Project MapPoints using a Similarity Transformation and search matches.
+    // Used in loop detection (Loop Closing)                              (src/ORBmatcher.cc:311-427)
+    template <class KeyFrameT, class MapPointT>
+    int SearchByProjection(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, std::vector<MapPointT*>& vpMatched, int th) {
+        FrameArrays fa; GatherFrame(*pKF, fa);
+        const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy;
+        float Rcw[9], tcw[3], Ow[3];
+        DecomposeSim3(Scw, Rcw, tcw);                                            // :320-325
+        CameraCentre(Rcw, tcw, Ow);
+        std::set<MapPointT*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+        spAlreadyFound.erase(static_cast<MapPointT*>(NULL));
+        const int M = (int)vpPoints.size();
+        Projected pv(M);
+        for (int i = 0; i < M; ++i) {
+            MapPointT* pMP = vpPoints[i];
+            if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;             // :340
+            const cv::Mat p3Dw = pMP->GetWorldPos();
+            const float xw[3] = {p3Dw.template at<float>(0), p3Dw.template at<float>(1), p3Dw.template at<float>(2)};
+            const float p3Dc[3] = {MulRowAdd(Rcw + 0, xw, tcw[0]), MulRowAdd(Rcw + 3, xw, tcw[1]), MulRowAdd(Rcw + 6, xw, tcw[2])};
+            if (p3Dc[2] < 0.0) continue;                                         // :350
+            const float invz = 1 / p3Dc[2];
+            const float x = p3Dc[0] * invz, y = p3Dc[1] * invz;
+            const float u = fx * x + cx, v = fy * y + cy;
+            if (!pKF->IsInImage(u, v)) continue;
+            const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+            const float PO[3] = {xw[0] - Ow[0], xw[1] - Ow[1], xw[2] - Ow[2]};
+            const float dist = Norm3(PO[0], PO[1], PO[2]);
+            if (dist < minDistance || dist > maxDistance) continue;
+            const cv::Mat Pn = pMP->GetNormal();                                 // viewing angle below 60 degrees (:374-377)
+            if (Dot3(PO, Pn) < 0.5 * dist) continue;
+            const int lvl = pMP->PredictScale(dist, pKF);
+            // GetFeaturesInArea(u, v, radius) has no level filter; the level window [lvl-1, lvl] is applied to the candidates (:393-395)
+            pv.Set(i, u, v, 0.f, th * pKF->mvScaleFactors[lvl], lvl - 1, lvl, pMP->GetDescriptor(), 0.f);
+        }
+        std::vector<unsigned char> occ(fa.n > 0 ? fa.n : 1, 0);
+        for (int i = 0; i < fa.n; ++i) occ[i] = vpMatched[i] != NULL;            // :391
+        std::vector<int32_t> match(fa.n > 0 ? fa.n : 1, -1);
+        int32_t nmatches = 0;
+        Check(orb_search_by_projection_claiming(Handle(), &fa.view, pv.View(false), occ.data(), TH_LOW, 0, match.data(), NULL, &nmatches));
+        for (int i = 0; i < fa.n; ++i) if (match[i] >= 0) vpMatched[i] = vpPoints[match[i]];   // :412
+        return nmatches;
+    }
+
+    // Project MapPoints into KeyFrame and search for duplicated MapPoints.    (src/ORBmatcher.cc:903-1054)
+    template <class KeyFrameT, class MapPointT>
+    int Fuse(KeyFrameT* pKF, const std::vector<MapPointT*>& vpMapPoints, const float th = 3.0) {
+        FrameArrays fa; GatherFrame(*pKF, fa);
+        const cv::Mat mR = pKF->GetRotation(), mt = pKF->GetTranslation(), mO = pKF->GetCameraCenter();
+        float Rcw[9], tcw[3], Ow[3];
+        for (int r = 0; r < 3; ++r) { for (int k = 0; k < 3; ++k) Rcw[3 * r + k] = mR.template at<float>(r, k); tcw[r] = mt.template at<float>(r); Ow[r] = mO.template at<float>(r); }
+        const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy, bf = pKF->mbf;
+        const int M = (int)vpMapPoints.size();
+        Projected pv(M);
+        for (int i = 0; i < M; ++i) {
+            MapPointT* pMP = vpMapPoints[i];
+            if (!pMP) continue;
+            if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;                // :927
+            float u, v, invz, dist3D;
+            if (!ProjectAndGate(pKF, pMP, Rcw, tcw, Ow, fx, fy, cx, cy, u, v, invz, dist3D)) continue;
+            const float ur = u - bf * invz;
+            const int lvl = pMP->PredictScale(dist3D, pKF);
+            pv.Set(i, u, v, ur, th * pKF->mvScaleFactors[lvl], lvl - 1, lvl, pMP->GetDescriptor(), 0.f);
+        }
+        std::vector<int32_t> best(M > 0 ? M : 1, -1);
+        int32_t nfound = 0;
+        Check(orb_search_projected_best(Handle(), &fa.view, pv.View(false), pKF->mvInvLevelSigma2.data(), TH_LOW, best.data(), NULL, &nfound));
+        // the map updates touch host-side state: replayed in point order (:1042-1070).  A point that an earlier
+        // update made bad or put into the keyframe is skipped, as the reference's gate at :927 would.
+        int nFused = 0;
+        for (int i = 0; i < M; ++i) {
+            if (best[i] < 0) continue;
+            MapPointT* pMP = vpMapPoints[i];
+            if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+            MapPointT* pMPinKF = pKF->GetMapPoint(best[i]);
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) {
+                    if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+                    else pMPinKF->Replace(pMP);
+                }
+            } else {
+                pMP->AddObservation(pKF, best[i]);
+                pKF->AddMapPoint(pMP, best[i]);
+            }
+            nFused++;
+        }
+        return nFused;
+    }
+
+    // Project MapPoints into KeyFrame using a given Sim3 and search for duplicated MapPoints.   (src/ORBmatcher.cc:1056-1207)
+    template <class KeyFrameT, class MapPointT>
+    int Fuse(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, float th, std::vector<MapPointT*>& vpReplacePoint) {
+        FrameArrays fa; GatherFrame(*pKF, fa);
+        const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy;
+        float Rcw[9], tcw[3], Ow[3];
+        DecomposeSim3(Scw, Rcw, tcw);
+        CameraCentre(Rcw, tcw, Ow);
+        const std::set<MapPointT*> spAlreadyFound = pKF->GetMapPoints();
+        const int M = (int)vpPoints.size();
+        Projected pv(M);
+        for (int i = 0; i < M; ++i) {
+            MapPointT* pMP = vpPoints[i];
+            if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;             // :1087
+            float u, v, invz, dist3D;
+            if (!ProjectAndGate(pKF, pMP, Rcw, tcw, Ow, fx, fy, cx, cy, u, v, invz, dist3D)) continue;
+            const int lvl = pMP->PredictScale(dist3D, pKF);
+            pv.Set(i, u, v, 0.f, th * pKF->mvScaleFactors[lvl], lvl - 1, lvl, pMP->GetDescriptor(), 0.f);
+        }
+        std::vector<int32_t> best(M > 0 ? M : 1, -1);
+        int32_t nfound = 0;
+        Check(orb_search_projected_best(Handle(), &fa.view, pv.View(false), NULL, TH_LOW, best.data(), NULL, &nfound));
+        int nFused = 0;
+        for (int i = 0; i < M; ++i) {   // :1184-1202
+            if (best[i] < 0) continue;
+            MapPointT* pMP = vpPoints[i];
+            MapPointT* pMPinKF = pKF->GetMapPoint(best[i]);
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) vpReplacePoint[i] = pMPinKF;
+            } else {
+                pMP->AddObservation(pKF, best[i]);
+                pKF->AddMapPoint(pMP, best[i]);
+            }
+            nFused++;
+        }
+        return nFused;
+    }
+
+    // Search matches between MapPoints seen in KF1 and KF2 transforming by a Sim3 [s12*R12|t12].
+    // In the stereo and RGB-D case, s12 = 1                                (src/ORBmatcher.cc:1212-1455)
+    template <class KeyFrameT, class MapPointT>
+    int SearchBySim3(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12, const float& s12, const cv::Mat& R12,
+                     const cv::Mat& t12, const float th) {
+        const float fx = pKF1->fx, fy = pKF1->fy, cx = pKF1->cx, cy = pKF1->cy;    // :1216-1219 (KF1's intrinsics for both directions)
+        float R1w[9], t1w[3], R2w[9], t2w[3], sR12[9], sR21[9], t12f[3], t21[3];
+        { const cv::Mat R = pKF1->GetRotation(), t = pKF1->GetTranslation(); for (int r = 0; r < 3; ++r) { for (int k = 0; k < 3; ++k) R1w[3 * r + k] = R.template at<float>(r, k); t1w[r] = t.template at<float>(r); } }
+        { const cv::Mat R = pKF2->GetRotation(), t = pKF2->GetTranslation(); for (int r = 0; r < 3; ++r) { for (int k = 0; k < 3; ++k) R2w[3 * r + k] = R.template at<float>(r, k); t2w[r] = t.template at<float>(r); } }
+        const float inv_s = (float)(1.0 / s12);
+        for (int r = 0; r < 3; ++r) {
+            for (int k = 0; k < 3; ++k) { sR12[3 * r + k] = s12 * R12.at<float>(r, k); sR21[3 * r + k] = inv_s * R12.at<float>(k, r); }   // :1229-1230
+            t12f[r] = t12.at<float>(r);
+        }
+        for (int r = 0; r < 3; ++r) t21[r] = (float)(-((double)sR21[3 * r] * t12f[0] + (double)sR21[3 * r + 1] * t12f[1] + (double)sR21[3 * r + 2] * t12f[2]));   // :1231
+
+        const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+        const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
+        std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+        for (int i = 0; i < N1; ++i) {                                           // :1242-1253
+            MapPointT* pMP = vpMatches12[i];
+            if (pMP) {
+                vbAlreadyMatched1[i] = true;
+                const int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+                if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+            }
+        }
+        FrameArrays a1, a2; GatherFrame(*pKF1, a1); GatherFrame(*pKF2, a2);
+        Projected p1(N1), p2(N2);
+        for (int dir = 0; dir < 2; ++dir) {
+            // dir 0: MapPoints of KF1 into KF2 (:1259-1334); dir 1: MapPoints of KF2 into KF1 (:1337-1410)
+            const std::vector<MapPointT*>& src = dir == 0 ? vpMapPoints1 : vpMapPoints2;
+            const std::vector<bool>& done = dir == 0 ? vbAlreadyMatched1 : vbAlreadyMatched2;
+            const float* Rw = dir == 0 ? R1w : R2w; const float* tw = dir == 0 ? t1w : t2w;
+            const float* sR = dir == 0 ? sR21 : sR12; const float* tt = dir == 0 ? t21 : t12f;
+            KeyFrameT* dst = dir == 0 ? pKF2 : pKF1;
+            Projected& pv = dir == 0 ? p1 : p2;
+            for (int i = 0; i < (int)src.size(); ++i) {
+                MapPointT* pMP = src[i];
+                if (!pMP || done[i]) continue;
+                if (pMP->isBad()) continue;
+                const cv::Mat p3Dw = pMP->GetWorldPos();
+                const float xw[3] = {p3Dw.template at<float>(0), p3Dw.template at<float>(1), p3Dw.template at<float>(2)};
+                const float pa[3] = {MulRowAdd(Rw + 0, xw, tw[0]), MulRowAdd(Rw + 3, xw, tw[1]), MulRowAdd(Rw + 6, xw, tw[2])};
+                const float pb[3] = {MulRowAdd(sR + 0, pa, tt[0]), MulRowAdd(sR + 3, pa, tt[1]), MulRowAdd(sR + 6, pa, tt[2])};
+                if (pb[2] < 0.0) continue;
+                const float invz = (float)(1.0 / pb[2]);
+                const float x = pb[0] * invz, y = pb[1] * invz;
+                const float u = fx * x + cx, v = fy * y + cy;
+                if (!dst->IsInImage(u, v)) continue;
+                const float dist3D = Norm3(pb[0], pb[1], pb[2]);
+                if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+                const int lvl = pMP->PredictScale(dist3D, dst);
+                pv.Set(i, u, v, 0.f, th * dst->mvScaleFactors[lvl], lvl - 1, lvl, pMP->GetDescriptor(), 0.f);
+            }
+        }
+        std::vector<int32_t> match(N1 > 0 ? N1 : 1, -1);
+        int32_t nFound = 0;
+        Check(orb_search_by_sim3(Handle(), &a1.view, p1.View(false), &a2.view, p2.View(false), match.data(), &nFound));
+        for (int i1 = 0; i1 < N1; ++i1) if (match[i1] >= 0) vpMatches12[i1] = vpMapPoints2[match[i1]];   // :1441-1446
+        return nFound;
+    }
+
 public:
     static const int TH_LOW = 50;
     static const int TH_HIGH = 100;
@@ -244,6 +504,65 @@ protected:
         out.view.n_nodes = (int32_t)out.ids.size(); out.view.node_ids = out.ids.data(); out.view.start = out.start.data();
         out.view.items = out.items.data();
     }
+    // flat arrays behind an orb_projected_view
+    struct Projected {
+        std::vector<unsigned char> valid, desc;
+        std::vector<float> u, v, ur, radius, angle;
+        std::vector<int32_t> lo, hi;
+        orb_projected_view view;
+        explicit Projected(int n) : valid(n > 0 ? n : 1, 0), desc((size_t)(n > 0 ? n : 1) * 32, 0), u(valid.size(), 0.f), v(valid.size(), 0.f), ur(valid.size(), 0.f),
+                                    radius(valid.size(), 0.f), angle(valid.size(), 0.f), lo(valid.size(), 0), hi(valid.size(), -1) { view.n = n; }
+        void Set(int i, float pu, float pv, float pur, float r, int lmin, int lmax, const cv::Mat& d, float ang) {
+            valid[i] = 1; u[i] = pu; v[i] = pv; ur[i] = pur; radius[i] = r; lo[i] = lmin; hi[i] = lmax; angle[i] = ang;
+            std::memcpy(&desc[(size_t)i * 32], d.ptr<unsigned char>(0), 32);
+        }
+        const orb_projected_view* View(bool with_angle) {
+            view.valid = valid.data(); view.u = u.data(); view.v = v.data(); view.ur = ur.data(); view.radius = radius.data();
+            view.min_level = lo.data(); view.max_level = hi.data(); view.desc = desc.data(); view.angle = with_angle ? angle.data() : NULL;
+            return &view;
+        }
+    };
+    // Ow = -Rcw.t() * tcw on CV_32F data (gemm accumulates in double)
+    static void CameraCentre(const float* R, const float* t, float* Ow) {
+        for (int r = 0; r < 3; ++r) Ow[r] = (float)(-((double)R[0 * 3 + r] * t[0] + (double)R[1 * 3 + r] * t[1] + (double)R[2 * 3 + r] * t[2]));
+    }
+    // Shared gate of Fuse / Fuse(Scw) (:932-972, :1091-1127): positive depth, inside the image, distance inside the
+    // scale-invariance region, viewing angle below 60 degrees.
+    template <class KeyFrameT, class MapPointT>
+    static bool ProjectAndGate(KeyFrameT* pKF, MapPointT* pMP, const float* Rcw, const float* tcw, const float* Ow, float fx, float fy, float cx,
+                               float cy, float& u, float& v, float& invz, float& dist3D) {
+        const cv::Mat p3Dw = pMP->GetWorldPos();
+        const float xw[3] = {p3Dw.template at<float>(0), p3Dw.template at<float>(1), p3Dw.template at<float>(2)};
+        const float p3Dc[3] = {MulRowAdd(Rcw + 0, xw, tcw[0]), MulRowAdd(Rcw + 3, xw, tcw[1]), MulRowAdd(Rcw + 6, xw, tcw[2])};
+        if (p3Dc[2] < 0.0f) return false;
+        invz = 1 / p3Dc[2];
+        const float x = p3Dc[0] * invz, y = p3Dc[1] * invz;
+        u = fx * x + cx; v = fy * y + cy;
+        if (!pKF->IsInImage(u, v)) return false;
+        const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+        const float PO[3] = {xw[0] - Ow[0], xw[1] - Ow[1], xw[2] - Ow[2]};
+        dist3D = Norm3(PO[0], PO[1], PO[2]);
+        if (dist3D < minDistance || dist3D > maxDistance) return false;
+        const cv::Mat Pn = pMP->GetNormal();
+        if (Dot3(PO, Pn) < 0.5 * dist3D) return false;
+        return true;
+    }
+    // Scw -> rotation and translation without the scale (:320-324).  Mat / float is Mat * (1.0 / s) with float elements.
+    static void DecomposeSim3(const cv::Mat& Scw, float* R, float* t, float* scale = NULL) {
+        float sR[9], st[3];
+        SplitPose(Scw, sR, st);
+        const float scw = (float)std::sqrt((double)sR[0] * sR[0] + (double)sR[1] * sR[1] + (double)sR[2] * sR[2]);
+        const float inv = (float)(1.0 / (double)scw);
+        for (int k = 0; k < 9; ++k) R[k] = sR[k] * inv;
+        for (int k = 0; k < 3; ++k) t[k] = st[k] * inv;
+        if (scale) *scale = scw;
+    }
+    // a.dot(b) on 3 x 1 CV_32F: accumulated in double
+    static double Dot3(const float* a, const cv::Mat& b) {
+        return (double)a[0] * b.at<float>(0) + (double)a[1] * b.at<float>(1) + (double)a[2] * b.at<float>(2);
+    }
+    // (float)cv::norm(3 x 1 CV_32F): sum of squares in double, sqrt in double
+    static float Norm3(float a, float b, float c) { return (float)std::sqrt((double)a * a + (double)b * b + (double)c * c); }
     static void SplitPose(const cv::Mat& Tcw, float* R, float* t) {
         for (int r = 0; r < 3; ++r) { for (int k = 0; k < 3; ++k) R[3 * r + k] = Tcw.at<float>(r, k); t[r] = Tcw.at<float>(r, 3); }
     }

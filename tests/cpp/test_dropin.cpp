@@ -4,7 +4,9 @@
 // the reference's member names (include/Frame.h, include/KeyFrame.h, include/MapPoint.h).
 //   test_dropin extract <in> <out> | mappoints <in> <out> | lastframe <in> <out> | bow <in> <out> | tri <in> <out>
 #include <cstdio>
+#include <cmath>
 #include <map>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -12,32 +14,58 @@
 #include "ORBmatcher.h"
 #include "blobio.h"
 
+struct Frame;
 struct MapPoint {
     bool mbTrackInView; float mTrackProjX, mTrackProjY, mTrackProjXR; int mnTrackScaleLevel; float mTrackViewCos;
-    cv::Mat mDescriptor, mWorldPos; int nObs; bool mbBad; int id;
+    cv::Mat mDescriptor, mWorldPos, mNormal; int nObs; bool mbBad; int id;
+    float mfMaxDistance, mfMinDistance;
+    std::map<Frame*, size_t> mObservations;
+    MapPoint* mpReplaced;
+    MapPoint() : mbTrackInView(false), nObs(0), mbBad(false), id(-1), mfMaxDistance(0.f), mfMinDistance(0.f), mpReplaced(NULL) {}
     bool isBad() { return mbBad; }
     cv::Mat GetDescriptor() { return mDescriptor.clone(); }
     cv::Mat GetWorldPos() { return mWorldPos.clone(); }
+    cv::Mat GetNormal() { return mNormal.clone(); }
     int Observations() { return nObs; }
+    float GetMinDistanceInvariance() { return 0.8f * mfMinDistance; }   // src/MapPoint.cc:404-414
+    float GetMaxDistanceInvariance() { return 1.2f * mfMaxDistance; }
+    inline int PredictScale(const float& currentDist, Frame* pF);        // src/MapPoint.cc:417-450
+    bool IsInKeyFrame(Frame* pKF) { return mObservations.count(pKF) != 0; }
+    int GetIndexInKeyFrame(Frame* pKF) { return mObservations.count(pKF) ? (int)mObservations[pKF] : -1; }
+    void AddObservation(Frame* pKF, size_t idx) { if (!mObservations.count(pKF)) { mObservations[pKF] = idx; nObs++; } }
+    // src/MapPoint.cc:158-211 reduced to what Fuse observes afterwards: the replaced point goes bad
+    void Replace(MapPoint* pMP) { if (pMP == this) return; mbBad = true; mpReplaced = pMP; }
 };
 
 struct Frame {  // also stands in for KeyFrame
     int N;
     std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
-    std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2;
+    std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
     cv::Mat mDescriptors, mTcw;
     std::vector<MapPoint*> mvpMapPoints;
     std::vector<bool> mvbOutlier;
     float mnMinX, mnMinY, mnMaxX, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
     float fx, fy, cx, cy, mbf, mb;
+    float mfLogScaleFactor; int mnScaleLevels;
     std::map<unsigned, std::vector<unsigned> > mFeatVec;
     cv::Mat mOw;
     std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
+    std::set<MapPoint*> GetMapPoints() { std::set<MapPoint*> s; for (size_t i = 0; i < mvpMapPoints.size(); ++i) if (mvpMapPoints[i] && !mvpMapPoints[i]->isBad()) s.insert(mvpMapPoints[i]); return s; }
     MapPoint* GetMapPoint(int i) { return mvpMapPoints[i]; }
+    void AddMapPoint(MapPoint* pMP, size_t idx) { mvpMapPoints[idx] = pMP; }
+    bool IsInImage(const float& x, const float& y) const { return (x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY); }
     cv::Mat GetCameraCenter() { return mOw.clone(); }
     cv::Mat GetRotation() { cv::Mat R(3, 3, CV_32F); for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) R.at<float>(r, c) = mTcw.at<float>(r, c); return R; }
     cv::Mat GetTranslation() { cv::Mat t(3, 1, CV_32F); for (int r = 0; r < 3; ++r) t.at<float>(r, 0) = mTcw.at<float>(r, 3); return t; }
 };
+
+inline int MapPoint::PredictScale(const float& currentDist, Frame* pF) {
+    const float ratio = mfMaxDistance / currentDist;
+    int nScale = (int)std::ceil(std::log(ratio) / pF->mfLogScaleFactor);
+    if (nScale < 0) nScale = 0;
+    else if (nScale >= pF->mnScaleLevels) nScale = pF->mnScaleLevels - 1;
+    return nScale;
+}
 
 static cv::Mat Identity4() { cv::Mat T = cv::Mat::zeros(4, 4, CV_32F); for (int i = 0; i < 4; ++i) T.at<float>(i, i) = 1.f; return T; }
 
@@ -53,6 +81,8 @@ static void LoadFrame(const Blob& b, const std::string& p, Frame& F) {
     const float* sf = b.get<float>(p + "sf"); const size_t nl = b.count(p + "sf");
     F.mvScaleFactors.assign(sf, sf + nl);
     F.mvLevelSigma2.resize(nl); for (size_t l = 0; l < nl; ++l) F.mvLevelSigma2[l] = sf[l] * sf[l];
+    F.mvInvLevelSigma2.resize(nl); for (size_t l = 0; l < nl; ++l) F.mvInvLevelSigma2[l] = 1.0f / F.mvLevelSigma2[l];
+    F.mnScaleLevels = (int)nl; F.mfLogScaleFactor = std::log(nl > 1 ? sf[1] : 1.2f);
     const float* g = b.get<float>(p + "grid");  // min_x, min_y, max_x, max_y, inv_w, inv_h
     F.mnMinX = g[0]; F.mnMinY = g[1]; F.mnMaxX = g[2]; F.mnMaxY = g[3]; F.mfGridElementWidthInv = g[4]; F.mfGridElementHeightInv = g[5];
     F.mvpMapPoints.assign(F.N, (MapPoint*)NULL); F.mvbOutlier.assign(F.N, false);
@@ -62,6 +92,32 @@ static void LoadFrame(const Blob& b, const std::string& p, Frame& F) {
         const unsigned* ids = b.get<unsigned>(p + "fv_ids"); const int* st = b.get<int>(p + "fv_start"); const unsigned* it = b.get<unsigned>(p + "fv_items");
         for (size_t k = 0; k < b.count(p + "fv_ids"); ++k) F.mFeatVec[ids[k]] = std::vector<unsigned>(it + st[k], it + st[k + 1]);
     }
+}
+
+static cv::Mat Row32(const unsigned char* p);
+// MapPoints of a world scenario: position, normal, distance range, descriptor, flags
+static void LoadPoints(const Blob& b, const std::string& p, std::vector<MapPoint>& store, std::vector<MapPoint*>& ptrs) {
+    const int M = (int)b.count(p + "maxd");
+    store.assign(M, MapPoint()); ptrs.assign(M, (MapPoint*)NULL);
+    for (int i = 0; i < M; ++i) {
+        MapPoint& m = store[i];
+        m.id = i;
+        m.mWorldPos.create(3, 1, CV_32F); m.mNormal.create(3, 1, CV_32F);
+        for (int k = 0; k < 3; ++k) { m.mWorldPos.at<float>(k) = b.get<float>(p + "xw")[3 * i + k]; m.mNormal.at<float>(k) = b.get<float>(p + "normal")[3 * i + k]; }
+        m.mfMaxDistance = b.get<float>(p + "maxd")[i]; m.mfMinDistance = b.get<float>(p + "mind")[i];
+        m.mDescriptor = Row32(b.get<unsigned char>(p + "desc") + (size_t)i * 32);
+        m.mbBad = b.get<unsigned char>(p + "bad")[i] != 0;
+        m.nObs = b.get<int>(p + "nobs")[i];
+        if (!b.get<unsigned char>(p + "null")[i]) ptrs[i] = &m;
+    }
+}
+static void SetPose(Frame& F, const float* T, const float* cam) {
+    F.mTcw.create(4, 4, CV_32F); std::memcpy(F.mTcw.data, T, 64);
+    F.fx = cam[0]; F.fy = cam[1]; F.cx = cam[2]; F.cy = cam[3]; F.mbf = cam[4];
+    // Ow = -R^T t like KeyFrame::SetPose (src/KeyFrame.cc:67-84), float products accumulated in double
+    F.mOw.create(3, 1, CV_32F);
+    for (int r = 0; r < 3; ++r)
+        F.mOw.at<float>(r) = (float)(-((double)T[0 * 4 + r] * T[3] + (double)T[1 * 4 + r] * T[7] + (double)T[2 * 4 + r] * T[11]));
 }
 
 static cv::Mat Row32(const unsigned char* p) { cv::Mat d(1, 32, CV_8U); std::memcpy(d.data, p, 32); return d; }
@@ -169,6 +225,57 @@ int main(int argc, char** argv) {
                 for (size_t k = 0; k < pairs.size(); ++k) { flat.push_back((int)pairs[k].first); flat.push_back((int)pairs[k].second); }
                 w.put("n", "i4", &n, 1); w.put("pairs", "i4", flat.data(), flat.size());
             }
+        } else if (mode == "reloc" || mode == "loop") {
+            Frame F; LoadFrame(b, "f_", F);
+            SetPose(F, b.get<float>("pose"), b.get<float>("cam"));
+            std::vector<MapPoint> store; std::vector<MapPoint*> pts; LoadPoints(b, "p_", store, pts);
+            const int M = (int)pts.size();
+            MapPoint holder; holder.id = -2; holder.nObs = 3;
+            const unsigned char* occ = b.get<unsigned char>("occupied"); const unsigned char* found = b.get<unsigned char>("p_found");
+            ORB_SLAM2::ORBmatcher matcher(0.75f, b.get<int>("check_ori")[0] != 0);
+            int n;
+            std::vector<int> match(F.N, -1);
+            if (mode == "reloc") {   // Tracking::Relocalization: matcher.SearchByProjection(mCurrentFrame, vpCandidateKFs[i], sFound, 10, 100)
+                for (int i = 0; i < F.N; ++i) if (occ[i]) F.mvpMapPoints[i] = &holder;
+                Frame K; K.N = M; K.mvpMapPoints = pts; K.mvKeysUn.assign(M, cv::KeyPoint());
+                for (int i = 0; i < M; ++i) K.mvKeysUn[i].angle = b.get<float>("p_angle")[i];
+                std::set<MapPoint*> sFound;
+                for (int i = 0; i < M; ++i) if (found[i] && pts[i]) sFound.insert(pts[i]);
+                n = matcher.SearchByProjection(F, &K, sFound, b.get<float>("th")[0], b.get<int>("max_dist")[0]);
+                for (int i = 0; i < F.N; ++i) if (F.mvpMapPoints[i] && F.mvpMapPoints[i] != &holder) match[i] = F.mvpMapPoints[i]->id;
+            } else {                 // LoopClosing::ComputeSim3: matcher.SearchByProjection(mpCurrentKF, mScw, mvpLoopMapPoints, mvpCurrentMatchedPoints, 10)
+                std::vector<MapPoint*> vpMatched(F.N, (MapPoint*)NULL);
+                int nf = 0;
+                std::vector<int> foundIdx; for (int i = 0; i < M; ++i) if (found[i]) foundIdx.push_back(i);
+                for (int i = 0; i < F.N; ++i) if (occ[i]) vpMatched[i] = (nf < (int)foundIdx.size()) ? pts[foundIdx[nf++]] : &holder;
+                std::vector<MapPoint*> before = vpMatched;
+                cv::Mat Scw(4, 4, CV_32F); std::memcpy(Scw.data, b.get<float>("pose"), 64);
+                n = matcher.SearchByProjection(&F, Scw, pts, vpMatched, (int)b.get<float>("th")[0]);
+                for (int i = 0; i < F.N; ++i) if (vpMatched[i] && !before[i]) match[i] = vpMatched[i]->id;
+            }
+            w.put("n", "i4", &n, 1); w.put("match", "i4", match.data(), match.size());
+        } else if (mode == "init") {
+            Frame A, B; LoadFrame(b, "a_", A); LoadFrame(b, "b_", B);
+            std::vector<cv::Point2f> prev(A.N);
+            for (int i = 0; i < A.N; ++i) prev[i] = cv::Point2f(b.get<float>("prev_x")[i], b.get<float>("prev_y")[i]);
+            ORB_SLAM2::ORBmatcher matcher(b.get<float>("ratio")[0], b.get<int>("check_ori")[0] != 0);
+            std::vector<int> m12;
+            const int n = matcher.SearchForInitialization(A, B, prev, m12, b.get<int>("window")[0]);
+            std::vector<float> px(A.N), py(A.N);
+            for (int i = 0; i < A.N; ++i) { px[i] = prev[i].x; py[i] = prev[i].y; }
+            w.put("n", "i4", &n, 1); w.put("match", "i4", m12.data(), m12.size());
+            w.put("prev_x", "f4", px.data(), px.size()); w.put("prev_y", "f4", py.data(), py.size());
+        } else if (mode == "bowkf") {
+            Frame A, B; LoadFrame(b, "a_", A); LoadFrame(b, "b_", B);
+            std::vector<MapPoint> sa(A.N), sb(B.N);
+            for (int i = 0; i < A.N; ++i) { sa[i].id = i; if (b.get<unsigned char>("has_a")[i]) A.mvpMapPoints[i] = &sa[i]; }
+            for (int i = 0; i < B.N; ++i) { sb[i].id = i; if (b.get<unsigned char>("has_b")[i]) B.mvpMapPoints[i] = &sb[i]; }
+            ORB_SLAM2::ORBmatcher matcher(b.get<float>("ratio")[0], b.get<int>("check_ori")[0] != 0);
+            std::vector<MapPoint*> out;
+            const int n = matcher.SearchByBoW(&A, &B, out);
+            std::vector<int> match(A.N, -1);
+            for (int i = 0; i < A.N; ++i) if (out[i]) match[i] = out[i]->id;
+            w.put("n", "i4", &n, 1); w.put("match", "i4", match.data(), match.size());
         } else {
             fprintf(stderr, "unknown mode %s\n", mode.c_str());
             return 2;

@@ -38,7 +38,7 @@ def dropin():
 def _frame_blob(p, d):
     f = views.Frame(d["x"], d["y"], d["octave"], d["angle"], d["desc"], d["sf"], d["bounds"], d["u_right"])
     out = {p + "x": f.x, p + "y": f.y, p + "octave": f.octave, p + "angle": f.angle, p + "desc": f.desc.reshape(-1),
-           p + "u_right": f.u_right, p + "sf": f.sf,
+           p + "u_right": f.u_right if f.u_right is not None else np.full(len(f.x), -1.0, np.float32), p + "sf": f.sf,
            p + "grid": np.array([f.bounds[0], f.bounds[1], f.bounds[2], f.bounds[3], f.inv_w, f.inv_h], np.float32)}
     return f, out
 
@@ -123,3 +123,72 @@ def test_search_for_triangulation(dropin, tmp_path, idx, only_stereo):
     assert out["n"][0] == n_o
     assert out["pairs"].reshape(-1, 2).tolist() == [[int(i), int(m_o[i])] for i in np.nonzero(m_o >= 0)[0]]
     assert n_o > 20
+
+
+@pytest.mark.parametrize("idx,window,ratio,check_ori", [(0, 100, 0.9, True), (1, 30, 0.9, False)])
+def test_search_for_initialization(dropin, tmp_path, idx, window, ratio, check_ori):
+    a, b, px, py = synth.make_initialization_scenario(2000, 1900, idx)
+    F1, blob = _frame_blob("a_", a)
+    F2, bb = _frame_blob("b_", b); blob.update(bb)
+    blob.update({"prev_x": px, "prev_y": py, "ratio": _f32(ratio), "check_ori": np.array([int(check_ori)], np.int32),
+                 "window": np.array([window], np.int32)})
+    out = dropin("init", blob, tmp_path)
+    n_o, m_o = orc.search_for_initialization(F1, F2, px, py, window, np.float32(ratio), check_ori)
+    assert out["n"][0] == n_o and np.array_equal(out["match"], m_o)
+    ok = m_o >= 0      # vbPrevMatched refreshed from the matches (reference :571-574)
+    assert np.array_equal(out["prev_x"][ok], F2.x[m_o[ok]]) and np.array_equal(out["prev_x"][~ok], px[~ok])
+    assert np.array_equal(out["prev_y"][ok], F2.y[m_o[ok]]) and np.array_equal(out["prev_y"][~ok], py[~ok])
+    assert n_o > 100
+
+
+@pytest.mark.parametrize("idx,ratio,check_ori", [(0, 0.75, True), (1, 0.6, False)])
+def test_search_by_bow_keyframes(dropin, tmp_path, idx, ratio, check_ori):
+    a, fva, b, fvb, has_a, has_b = synth.make_bow_scenario(2000, 1900, 20 + idx)
+    KF1, blob = _frame_blob("a_", a)
+    KF2, bb = _frame_blob("b_", b); blob.update(bb)
+    va, ba = _fv_blob("a_", fva); vb, bb = _fv_blob("b_", fvb); blob.update(ba); blob.update(bb)
+    blob.update({"has_a": views.u8(has_a), "has_b": views.u8(has_b), "ratio": _f32(ratio), "check_ori": np.array([int(check_ori)], np.int32)})
+    out = dropin("bowkf", blob, tmp_path)
+    n_o, m_o = orc.search_by_bow_keyframes(KF1, va, has_a, KF2, vb, has_b, np.float32(ratio), check_ori)
+    assert out["n"][0] == n_o and np.array_equal(out["match"], m_o)
+    assert n_o > 50
+
+
+import worldsim
+
+
+def _world_blob(f, wd, occ, th, check_ori, max_dist=100):
+    F, blob = _frame_blob("f_", f)
+    blob.update(worldsim.blob(wd))
+    blob.update({"pose": wd["pose"].reshape(-1), "cam": np.array(worldsim.CAM, np.float32), "occupied": views.u8(occ), "th": _f32(th),
+                 "check_ori": np.array([int(check_ori)], np.int32), "max_dist": np.array([max_dist], np.int32)})
+    return F, blob
+
+
+@pytest.mark.parametrize("idx,th,max_dist,check_ori", [(0, 10.0, 100, True), (1, 3.0, 64, True), (2, 10.0, 100, False)])
+def test_relocalisation_search_by_projection(dropin, tmp_path, idx, th, max_dist, check_ori):
+    """Tracking::Relocalization's SearchByProjection(F, KF, sFound, th, ORBdist): host gates in the header + claiming search."""
+    f = synth.make_frame_arrays(2000, 500 + idx)
+    wd = worldsim.make_world(f, idx, 2000, with_null=True, perturb=synth.perturb_descriptors)
+    occ = np.random.default_rng(idx).random(2000) < 0.15
+    F, blob = _world_blob(f, wd, occ, th, check_ori, max_dist)
+    out = dropin("reloc", blob, tmp_path)
+    pts = worldsim.gate_relocalisation(f, wd, th)
+    n_o, m_o, _ = orc.search_by_projection_claiming(F, pts, occ, max_dist, check_ori)
+    assert out["n"][0] == n_o and np.array_equal(out["match"], m_o)
+    assert n_o > 100 and 0.5 < pts["valid"].mean() < 0.95
+
+
+@pytest.mark.parametrize("idx,th", [(0, 10), (1, 5)])
+def test_loop_search_by_projection(dropin, tmp_path, idx, th):
+    """LoopClosing::ComputeSim3's SearchByProjection(KF, Scw, points, matched, th)."""
+    f = synth.make_frame_arrays(2000, 510 + idx)
+    wd = worldsim.make_world(f, 10 + idx, 2000, scale=1.0 + 0.3 * idx, perturb=synth.perturb_descriptors)
+    occ = np.random.default_rng(idx).random(2000) < 0.15
+    assert wd["found"].sum() <= occ.sum()
+    F, blob = _world_blob(f, wd, occ, float(th), False)
+    out = dropin("loop", blob, tmp_path)
+    pts = worldsim.gate_keyframe(f, wd, th, sim3=True, skip=wd["bad"] | wd["found"])
+    n_o, m_o, _ = orc.search_by_projection_claiming(F, pts, occ, 50, False)
+    assert out["n"][0] == n_o and np.array_equal(out["match"], m_o)
+    assert n_o > 100

@@ -254,6 +254,59 @@ int main(int argc, char** argv) {
                 for (int i = 0; i < F.N; ++i) if (vpMatched[i] && !before[i]) match[i] = vpMatched[i]->id;
             }
             w.put("n", "i4", &n, 1); w.put("match", "i4", match.data(), match.size());
+        } else if (mode == "fuse" || mode == "fuse_scw") {
+            // LocalMapping::SearchInNeighbors: matcher.Fuse(pKFi, vpMapPointMatches) (src/LocalMapping.cc:584,613);
+            // LoopClosing::SearchAndFuse: matcher.Fuse(pKF, cvScw, mvpLoopMapPoints, 4, vpReplacePoints) (src/LoopClosing.cc:652)
+            Frame K; LoadFrame(b, "f_", K);
+            SetPose(K, b.get<float>("pose"), b.get<float>("cam"));
+            std::vector<MapPoint> store; std::vector<MapPoint*> pts; LoadPoints(b, "p_", store, pts);
+            const int M = (int)pts.size();
+            // MapPoints the keyframe already holds (e_kp[j] = keypoint index of existing point j)
+            const int E = (int)b.count("e_kp");
+            std::vector<MapPoint> existing(E);
+            for (int j = 0; j < E; ++j) {
+                existing[j].id = 100000 + j; existing[j].nObs = b.get<int>("e_nobs")[j]; existing[j].mbBad = b.get<unsigned char>("e_bad")[j] != 0;
+                K.mvpMapPoints[b.get<int>("e_kp")[j]] = &existing[j];
+            }
+            // candidate points that are already observed in the keyframe (:927 IsInKeyFrame / :1087 spAlreadyFound)
+            const int* inkf = b.get<int>("p_in_kf");
+            for (int i = 0; i < M; ++i) if (inkf[i] >= 0 && pts[i]) { pts[i]->mObservations[&K] = (size_t)inkf[i]; K.mvpMapPoints[inkf[i]] = pts[i]; }
+            ORB_SLAM2::ORBmatcher matcher;
+            int n;
+            std::vector<int> replace(M, -1);
+            if (mode == "fuse") n = matcher.Fuse(&K, pts, b.get<float>("th")[0]);
+            else {
+                cv::Mat Scw(4, 4, CV_32F); std::memcpy(Scw.data, b.get<float>("pose"), 64);
+                std::vector<MapPoint*> vpReplace(M, (MapPoint*)NULL);
+                n = matcher.Fuse(&K, Scw, pts, b.get<float>("th")[0], vpReplace);
+                for (int i = 0; i < M; ++i) if (vpReplace[i]) replace[i] = vpReplace[i]->id;
+            }
+            std::vector<int> kf_mp(K.N, -1), p_bad(M, 0), p_repl(M, -1), p_idx(M, -1), e_bad(E, 0), e_repl(E, -1);
+            for (int i = 0; i < K.N; ++i) if (K.mvpMapPoints[i]) kf_mp[i] = K.mvpMapPoints[i]->id;
+            for (int i = 0; i < M; ++i) { p_bad[i] = store[i].mbBad; if (store[i].mpReplaced) p_repl[i] = store[i].mpReplaced->id; p_idx[i] = store[i].GetIndexInKeyFrame(&K); }
+            for (int j = 0; j < E; ++j) { e_bad[j] = existing[j].mbBad; if (existing[j].mpReplaced) e_repl[j] = existing[j].mpReplaced->id; }
+            w.put("n", "i4", &n, 1); w.put("kf_mp", "i4", kf_mp.data(), kf_mp.size()); w.put("replace", "i4", replace.data(), replace.size());
+            w.put("p_bad", "i4", p_bad.data(), p_bad.size()); w.put("p_repl", "i4", p_repl.data(), p_repl.size()); w.put("p_idx", "i4", p_idx.data(), p_idx.size());
+            w.put("e_bad", "i4", e_bad.data(), e_bad.size()); w.put("e_repl", "i4", e_repl.data(), e_repl.size());
+        } else if (mode == "sim3") {
+            // LoopClosing::ComputeSim3: matcher.SearchBySim3(mpCurrentKF, pKF, vpMapPointMatches, s, R, t, 7.5) (src/LoopClosing.cc:348)
+            Frame A, B; LoadFrame(b, "a_", A); LoadFrame(b, "b_", B);
+            SetPose(A, b.get<float>("pose_a"), b.get<float>("cam")); SetPose(B, b.get<float>("pose_b"), b.get<float>("cam"));
+            std::vector<MapPoint> sa, sb; std::vector<MapPoint*> pa, pb;
+            LoadPoints(b, "pa_", sa, pa); LoadPoints(b, "pb_", sb, pb);
+            A.mvpMapPoints = pa; B.mvpMapPoints = pb;
+            for (int j = 0; j < B.N; ++j) if (pb[j]) pb[j]->mObservations[&B] = (size_t)j;
+            std::vector<MapPoint*> m12(A.N, (MapPoint*)NULL);
+            const int* pre = b.get<int>("pre");
+            for (int i = 0; i < A.N; ++i) if (pre[i] >= 0) m12[i] = &sb[pre[i]];
+            cv::Mat R12(3, 3, CV_32F), t12(3, 1, CV_32F);
+            std::memcpy(R12.data, b.get<float>("r12"), 36); std::memcpy(t12.data, b.get<float>("t12"), 12);
+            const float s12 = b.get<float>("s12")[0];
+            ORB_SLAM2::ORBmatcher matcher(0.75f, true);
+            const int n = matcher.SearchBySim3(&A, &B, m12, s12, R12, t12, b.get<float>("th")[0]);
+            std::vector<int> match(A.N, -1);
+            for (int i = 0; i < A.N; ++i) if (m12[i]) match[i] = m12[i]->id;
+            w.put("n", "i4", &n, 1); w.put("match", "i4", match.data(), match.size());
         } else if (mode == "init") {
             Frame A, B; LoadFrame(b, "a_", A); LoadFrame(b, "b_", B);
             std::vector<cv::Point2f> prev(A.N);

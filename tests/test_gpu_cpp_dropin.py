@@ -192,3 +192,118 @@ def test_loop_search_by_projection(dropin, tmp_path, idx, th):
     n_o, m_o, _ = orc.search_by_projection_claiming(F, pts, occ, 50, False)
     assert out["n"][0] == n_o and np.array_equal(out["match"], m_o)
     assert n_o > 100
+
+
+def _fuse_scenario(idx, scale):
+    f = synth.make_frame_arrays(2000, 520 + idx)
+    wd = worldsim.make_world(f, 20 + idx, 2500, scale=scale, with_null=(scale == 1.0), perturb=synth.perturb_descriptors)
+    rng = np.random.default_rng(77 + idx)
+    perm = rng.permutation(2000)
+    e_kp = perm[:600].astype(np.int32)                       # keypoints that already hold a MapPoint
+    e_nobs = rng.integers(1, 6, 600).astype(np.int32); e_bad = rng.random(600) < 0.1
+    in_kf = np.full(2500, -1, np.int32)                      # candidates already observed in the keyframe
+    sel = np.nonzero(rng.random(2500) < 0.05)[0]
+    in_kf[sel] = perm[600:600 + len(sel)]
+    in_kf[wd["null"]] = -1
+    return f, wd, e_kp, e_nobs, e_bad, in_kf
+
+
+@pytest.mark.parametrize("idx,th", [(0, 3.0), (1, 5.0)])
+def test_fuse(dropin, tmp_path, idx, th):
+    """Fuse(KF, MapPoints, th): gates + chi-square candidate search on the device, map updates replayed in point order."""
+    f, wd, e_kp, e_nobs, e_bad, in_kf = _fuse_scenario(idx, 1.0)
+    KF, blob = _world_blob(f, wd, np.zeros(2000, bool), th, False)
+    blob.update({"e_kp": e_kp, "e_nobs": e_nobs, "e_bad": views.u8(e_bad), "p_in_kf": in_kf})
+    out = dropin("fuse", blob, tmp_path)
+    pts = worldsim.gate_keyframe(f, wd, th, sim3=False, skip=wd["null"] | wd["bad"] | (in_kf >= 0), bf=worldsim.CAM[4])
+    inv_s2 = (np.float32(1.0) / (f["sf"] * f["sf"]).astype(np.float32)).astype(np.float32)
+    _, best, _ = orc.search_projected_best(KF, pts, inv_s2, 50)
+    M, E = 2500, 600
+    kf_mp = np.full(2000, -1, np.int64); kf_mp[e_kp] = 100000 + np.arange(E); kf_mp[in_kf[in_kf >= 0]] = np.nonzero(in_kf >= 0)[0]
+    p_bad = wd["bad"].copy(); p_idx = in_kf.copy(); p_nobs = wd["nobs"].copy(); p_repl = np.full(M, -1); eb = e_bad.copy(); e_repl = np.full(E, -1)
+    n = 0
+    for i in range(M):
+        if best[i] < 0 or p_bad[i] or p_idx[i] >= 0:
+            continue
+        cur = kf_mp[best[i]]
+        if cur >= 0:
+            cur_bad = eb[cur - 100000] if cur >= 100000 else p_bad[cur]
+            cur_nobs = e_nobs[cur - 100000] if cur >= 100000 else p_nobs[cur]
+            if not cur_bad:
+                if cur_nobs > p_nobs[i]:
+                    p_bad[i] = True; p_repl[i] = cur
+                elif cur >= 100000:
+                    eb[cur - 100000] = True; e_repl[cur - 100000] = i
+                else:
+                    p_bad[cur] = True; p_repl[cur] = i
+        else:
+            p_idx[i] = best[i]; p_nobs[i] += 1; kf_mp[best[i]] = i
+        n += 1
+    assert out["n"][0] == n and n > 100
+    assert np.array_equal(out["kf_mp"], kf_mp) and np.array_equal(out["p_idx"], p_idx)
+    assert np.array_equal(out["p_bad"] != 0, p_bad) and np.array_equal(out["p_repl"], p_repl)
+    assert np.array_equal(out["e_bad"] != 0, eb) and np.array_equal(out["e_repl"], e_repl)
+    assert (p_repl >= 0).sum() > 5 and (e_repl >= 0).sum() > 5 and (p_idx >= 0).sum() > (in_kf >= 0).sum() + 50
+
+
+@pytest.mark.parametrize("idx,th", [(0, 4.0), (1, 4.0)])
+def test_fuse_sim3(dropin, tmp_path, idx, th):
+    """Fuse(KF, Scw, points, th, vpReplacePoint) of LoopClosing::SearchAndFuse."""
+    f, wd, e_kp, e_nobs, e_bad, in_kf = _fuse_scenario(2 + idx, 1.0 + 0.25 * (idx + 1))
+    KF, blob = _world_blob(f, wd, np.zeros(2000, bool), th, False)
+    blob.update({"e_kp": e_kp, "e_nobs": e_nobs, "e_bad": views.u8(e_bad), "p_in_kf": in_kf})
+    out = dropin("fuse_scw", blob, tmp_path)
+    pts = worldsim.gate_keyframe(f, wd, th, sim3=True, skip=wd["bad"] | (in_kf >= 0))
+    _, best, _ = orc.search_projected_best(KF, pts, None, 50)
+    M, E = 2500, 600
+    kf_mp = np.full(2000, -1, np.int64); kf_mp[e_kp] = 100000 + np.arange(E); kf_mp[in_kf[in_kf >= 0]] = np.nonzero(in_kf >= 0)[0]
+    p_idx = in_kf.copy(); replace = np.full(M, -1); n = 0
+    for i in range(M):
+        if best[i] < 0:
+            continue
+        cur = kf_mp[best[i]]
+        if cur >= 0:
+            cur_bad = e_bad[cur - 100000] if cur >= 100000 else wd["bad"][cur]
+            if not cur_bad:
+                replace[i] = cur
+        else:
+            p_idx[i] = best[i]; kf_mp[best[i]] = i
+        n += 1
+    assert out["n"][0] == n and n > 100
+    assert np.array_equal(out["kf_mp"], kf_mp) and np.array_equal(out["p_idx"], p_idx) and np.array_equal(out["replace"], replace)
+    assert (replace >= 0).sum() > 20
+
+
+@pytest.mark.parametrize("idx,s12", [(0, 1.0), (1, 1.1)])
+def test_search_by_sim3(dropin, tmp_path, idx, s12):
+    """SearchBySim3(KF1, KF2, matches12, s12, R12, t12, th): both projections gated on the host, mutual agreement on the device."""
+    n1, n2, th = 1500, 1400, 7.5
+    a = synth.make_frame_arrays(n1, 540 + 2 * idx); b = synth.make_frame_arrays(n2, 541 + 2 * idx)
+    rng = np.random.default_rng(900 + idx)
+    nm = min(n1, n2) * 7 // 10
+    ia = rng.permutation(n1)[:nm]; ib = rng.permutation(n2)[:nm]
+    part_a = rng.integers(0, n2, n1); part_a[ia] = ib      # partner of each KF1 feature in KF2
+    part_b = rng.integers(0, n1, n2); part_b[ib] = ia
+    # MapPoints of KF1's features land on their KF2 partners under T2w; those of KF2 on KF1 partners under T1w
+    wd1 = worldsim.make_world(b, 30 + 2 * idx, n1, match_frac=0.9, with_null=True, perturb=synth.perturb_descriptors, src=part_a)
+    wd2 = worldsim.make_world(a, 31 + 2 * idx, n2, scale=s12, match_frac=0.9, with_null=True, perturb=synth.perturb_descriptors, src=part_b)
+    wd2["maxd"] = (wd2["maxd"] * np.float32(s12)).astype(np.float32); wd2["mind"] = (wd2["mind"] * np.float32(s12)).astype(np.float32)
+    R12 = wd2["R"] @ wd1["R"].T
+    t12 = s12 * wd2["t"] - s12 * R12 @ wd1["t"]
+    R12, t12 = R12.astype(np.float32), t12.astype(np.float32)
+    pre = np.where(rng.random(n1) < 0.05, rng.integers(0, n2, n1), -1).astype(np.int32)
+    A, blob = _frame_blob("a_", a)
+    B, bb = _frame_blob("b_", b); blob.update(bb)
+    blob.update(worldsim.blob(wd1, "pa_")); blob.update(worldsim.blob(wd2, "pb_"))
+    blob.update({"pose_a": wd2["pose"].reshape(-1), "pose_b": wd1["pose"].reshape(-1), "cam": np.array(worldsim.CAM, np.float32), "pre": pre,
+                 "r12": R12.reshape(-1), "t12": t12, "s12": _f32(s12), "th": _f32(th)})
+    out = dropin("sim3", blob, tmp_path)
+    sR12, sR21, t21 = worldsim.sim3_matrices(s12, R12, t12)
+    done1 = pre >= 0
+    done2 = np.zeros(n2, bool); done2[pre[done1]] = True
+    p1 = worldsim.gate_sim3(b, wd1, wd2["pose"][:3, :3], wd2["pose"][:3, 3], sR21, t21, th, wd1["null"] | done1 | wd1["bad"])
+    p2 = worldsim.gate_sim3(a, wd2, wd1["pose"][:3, :3], wd1["pose"][:3, 3], sR12, t12, th, wd2["null"] | done2 | wd2["bad"])
+    n_o, m_o = orc.search_by_sim3(A, p1, B, p2)
+    assert out["n"][0] == n_o
+    assert np.array_equal(out["match"], np.where(m_o >= 0, m_o, pre))
+    assert n_o > 200

@@ -51,7 +51,7 @@ def predict_scale(maxd, dist, sf):
     return np.clip(n, 0, len(sf) - 1)
 
 
-def make_world(f, idx, n_pts, scale=1.0, match_frac=0.7, with_null=False, desc_src=None, perturb=None):
+def make_world(f, idx, n_pts, scale=1.0, match_frac=0.7, with_null=False, desc_src=None, perturb=None, src=None):
     """MapPoints in world coordinates that project (under the returned pose) onto / near keypoints of
     the frame arrays `f`; a few percent fail each of the reference's gates."""
     rng = np.random.default_rng(0x5EED0000 + 0x900000 + int(idx))
@@ -60,7 +60,8 @@ def make_world(f, idx, n_pts, scale=1.0, match_frac=0.7, with_null=False, desc_s
     R = _rodrigues(rng.normal(0, 0.05, 3)); t = rng.normal(0, 0.5, 3)
     T = np.eye(4); T[:3, :3] = scale * R; T[:3, 3] = scale * t
     T = T.astype(F32)
-    src = rng.integers(0, n_kp, n_pts)
+    rnd_src = rng.integers(0, n_kp, n_pts)
+    src = rnd_src if src is None else np.asarray(src)
     matched = rng.random(n_pts) < match_frac
     u0 = np.where(matched, f["x"][src] + rng.normal(0, 2, n_pts), rng.uniform(-40, f["bounds"][2] + 40, n_pts))
     v0 = np.where(matched, f["y"][src] + rng.normal(0, 2, n_pts), rng.uniform(-40, f["bounds"][3] + 40, n_pts))
@@ -82,7 +83,7 @@ def make_world(f, idx, n_pts, scale=1.0, match_frac=0.7, with_null=False, desc_s
     return dict(pose=T, xw=Xw, maxd=maxd.astype(F32), mind=mind.astype(F32), normal=normal.astype(F32), desc=desc,
                 bad=rng.random(n_pts) < 0.04, null=(rng.random(n_pts) < 0.03) if with_null else np.zeros(n_pts, bool),
                 nobs=rng.integers(1, 6, n_pts).astype(np.int32), found=rng.random(n_pts) < 0.04,
-                angle=np.mod(f["angle"][src] + dangle, 360).astype(F32), src=src)
+                angle=np.mod(f["angle"][src] + dangle, 360).astype(F32), src=src, R=R, t=t)
 
 
 def blob(wd, prefix="p_"):
@@ -143,3 +144,32 @@ def gate_keyframe(f, wd, th, sim3, skip, bf=None):
         lvl = predict_scale(wd["maxd"], dist, f["sf"])
         ur = None if bf is None else u - F32(bf) * invz
     return _pts(valid, u, v, ur, F32(th) * f["sf"][lvl], lvl - 1, lvl, wd, False)
+
+
+def gate_sim3(dst, wd, Rw, tw, sR, tt, th, skip):
+    """One direction of SearchBySim3 (reference :1259-1305 / :1337-1383): MapPoints seen in one keyframe
+    (pose Rw, tw) moved by the similarity (sR, tt) into the other one (frame arrays `dst`)."""
+    fx, fy, cx, cy = (F32(c) for c in CAM[:4])
+    with np.errstate(all="ignore"):
+        pa = mul_row_add(Rw, wd["xw"], tw)
+        pb = mul_row_add(sR, pa, tt)
+        valid = ~skip & ~(pb[:, 2] < 0)
+        invz = (1.0 / pb[:, 2].astype(F64)).astype(F32)
+        x = pb[:, 0] * invz; y = pb[:, 1] * invz
+        u = fx * x + cx; v = fy * y + cy
+        b = dst["bounds"]
+        valid &= (u >= F32(b[0])) & (u < F32(b[2])) & (v >= F32(b[1])) & (v < F32(b[3]))
+        dist = norm3(pb)
+        valid &= ~((dist < F32(0.8) * wd["mind"]) | (dist > F32(1.2) * wd["maxd"]))
+        lvl = predict_scale(wd["maxd"], dist, dst["sf"])
+    return _pts(valid, u, v, None, F32(th) * dst["sf"][lvl], lvl - 1, lvl, wd, False)
+
+
+def sim3_matrices(s12, R12, t12):
+    """sR12, sR21, t21 of reference :1229-1231."""
+    s12 = F32(s12); R12 = R12.astype(F32); t12 = t12.astype(F32)
+    sR12 = (s12 * R12).astype(F32)
+    sR21 = (F32(1.0 / F64(s12)) * R12.T).astype(F32)
+    a, t = sR21.astype(F64), t12.astype(F64)
+    t21 = np.array([-((a[r, 0] * t[0] + a[r, 1] * t[1]) + a[r, 2] * t[2]) for r in range(3)]).astype(F32)
+    return sR12, sR21, t21

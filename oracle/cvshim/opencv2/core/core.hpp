@@ -14,6 +14,11 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <climits>
+#include <cfloat>
+#include <iostream>
+#include <sstream>
+#include <string>
 #include <vector>
 #include "../../../prim.hpp"
 
@@ -21,6 +26,8 @@ typedef unsigned char uchar;
 #define CV_8U 0
 #define CV_8UC1 0
 #define CV_32F 5
+#define CV_32FC1 5
+#define CV_64F 6
 #define CV_PI 3.1415926535897932384626433832795
 
 static inline int cvRound(double v) { return (int)lrint(v); }
@@ -61,64 +68,94 @@ struct KeyPoint {
 };
 
 struct ZerosExpr { int rows, cols, type; };
+class Mat;
+struct MatT;   // lazy transpose (keeps cv::gemm's GEMM_1_T flag: that path accumulates in double)
+
+static inline size_t cvshim_esz(int type) { return type == CV_8U ? 1 : type == CV_32F ? 4 : 8; }
 
 class Mat {
     struct Buf { int refs; };  // header of a malloc'd block: [Buf][pixels]; bypasses operator new on purpose
     Buf* buf_;
+    int type_;
     void retain() { if (buf_) ++buf_->refs; }
     void drop() { if (buf_ && --buf_->refs == 0) std::free(buf_); buf_ = nullptr; }
 public:
     int rows, cols;
     size_t step;
     uchar* data;
-    Mat() : buf_(nullptr), rows(0), cols(0), step(0), data(nullptr) {}
-    Mat(int r, int c, int type) : buf_(nullptr), rows(0), cols(0), step(0), data(nullptr) { create(r, c, type); }
-    Mat(Size s, int type) : buf_(nullptr), rows(0), cols(0), step(0), data(nullptr) { create(s.height, s.width, type); }
-    Mat(const Mat& o) : buf_(o.buf_), rows(o.rows), cols(o.cols), step(o.step), data(o.data) { retain(); }
+    Mat() : buf_(nullptr), type_(CV_8U), rows(0), cols(0), step(0), data(nullptr) {}
+    Mat(int r, int c, int type) : buf_(nullptr), type_(CV_8U), rows(0), cols(0), step(0), data(nullptr) { create(r, c, type); }
+    Mat(Size s, int type) : buf_(nullptr), type_(CV_8U), rows(0), cols(0), step(0), data(nullptr) { create(s.height, s.width, type); }
+    Mat(const Mat& o) : buf_(o.buf_), type_(o.type_), rows(o.rows), cols(o.cols), step(o.step), data(o.data) { retain(); }
+    Mat(const ZerosExpr& z) : buf_(nullptr), type_(CV_8U), rows(0), cols(0), step(0), data(nullptr) { *this = z; }
+    inline Mat(const MatT& t);
     // external (caller-owned) pixels, no ownership
-    Mat(int r, int c, int type, void* ext, size_t ext_step) : buf_(nullptr), rows(r), cols(c), step(ext_step), data((uchar*)ext) { assert(type == CV_8UC1); }
+    Mat(int r, int c, int type, void* ext, size_t ext_step = 0) : buf_(nullptr), type_(type), rows(r), cols(c), step(ext_step ? ext_step : (size_t)c * cvshim_esz(type)), data((uchar*)ext) {}
     ~Mat() { drop(); }
     Mat& operator=(const Mat& o) {
-        if (this != &o) { Buf* nb = o.buf_; if (nb) ++nb->refs; drop(); buf_ = nb; rows = o.rows; cols = o.cols; step = o.step; data = o.data; }
+        if (this != &o) { Buf* nb = o.buf_; if (nb) ++nb->refs; drop(); buf_ = nb; type_ = o.type_; rows = o.rows; cols = o.cols; step = o.step; data = o.data; }
         return *this;
     }
     Mat& operator=(const ZerosExpr& z) {
         create(z.rows, z.cols, z.type);
-        for (int y = 0; y < rows; ++y) std::memset(data + (size_t)y * step, 0, (size_t)cols);
+        for (int y = 0; y < rows; ++y) std::memset(data + (size_t)y * step, 0, (size_t)cols * elemSize());
         return *this;
     }
     void create(int r, int c, int type) {
-        assert(type == CV_8UC1);
-        if (data && rows == r && cols == c) return;  // cv::Mat::create keeps a matching buffer
+        if (data && rows == r && cols == c && type_ == type) return;  // cv::Mat::create keeps a matching buffer
         drop();
-        rows = r; cols = c; step = (size_t)c;
-        buf_ = (Buf*)std::malloc(sizeof(Buf) + 16 + (size_t)r * c + 64);
+        type_ = type;
+        rows = r; cols = c; step = (size_t)c * cvshim_esz(type);
+        buf_ = (Buf*)std::malloc(sizeof(Buf) + 16 + (size_t)r * step + 64);
         buf_->refs = 1;
         data = (uchar*)buf_ + sizeof(Buf) + 16 - sizeof(Buf) % 16;
     }
     void release() { drop(); rows = cols = 0; step = 0; data = nullptr; }
     static ZerosExpr zeros(int r, int c, int type) { ZerosExpr z = {r, c, type}; return z; }
+    static Mat ones(int r, int c, int type) { assert(type == CV_32F); Mat m(r, c, type); for (int y = 0; y < r; ++y) for (int x = 0; x < c; ++x) m.at<float>(y, x) = 1.f; return m; }
+    static Mat eye(int r, int c, int type) { assert(type == CV_32F); Mat m = zeros(r, c, type); for (int i = 0; i < std::min(r, c); ++i) m.at<float>(i, i) = 1.f; return m; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
-    int type() const { return CV_8UC1; }
-    size_t step1() const { return step; }
+    int type() const { return type_; }
+    int depth() const { return type_; }
+    int channels() const { return 1; }
+    size_t elemSize() const { return cvshim_esz(type_); }
+    size_t step1() const { return step / elemSize(); }
+    size_t total() const { return (size_t)rows * cols; }
+    bool isContinuous() const { return rows <= 1 || step == (size_t)cols * elemSize(); }
+    Size size() const { return Size(cols, rows); }
     Mat operator()(const Rect& r) const {
         assert(r.x >= 0 && r.y >= 0 && r.x + r.width <= cols && r.y + r.height <= rows);
-        Mat m(*this); m.data = data + (size_t)r.y * step + r.x; m.rows = r.height; m.cols = r.width; return m;
+        Mat m(*this); m.data = data + (size_t)r.y * step + r.x * elemSize(); m.rows = r.height; m.cols = r.width; return m;
     }
     Mat rowRange(int a, int b) const { assert(0 <= a && a <= b && b <= rows); Mat m(*this); m.data = data + (size_t)a * step; m.rows = b - a; return m; }
-    Mat colRange(int a, int b) const { assert(0 <= a && a <= b && b <= cols); Mat m(*this); m.data = data + a; m.cols = b - a; return m; }
+    Mat colRange(int a, int b) const { assert(0 <= a && a <= b && b <= cols); Mat m(*this); m.data = data + a * elemSize(); m.cols = b - a; return m; }
+    Mat row(int y) const { return rowRange(y, y + 1); }
+    Mat col(int x) const { return colRange(x, x + 1); }
     Mat clone() const {
         Mat m; if (empty()) return m;
-        m.create(rows, cols, CV_8UC1);
-        for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step, data + (size_t)y * step, (size_t)cols);
+        m.create(rows, cols, type_);
+        for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step, data + (size_t)y * step, (size_t)cols * elemSize());
         return m;
     }
+    inline void copyTo(const class _OutputArray& dst) const;
+    void convertTo(Mat& dst, int type) const {
+        assert(type_ == CV_8U && type == CV_32F);
+        Mat out(rows, cols, CV_32F);
+        for (int y = 0; y < rows; ++y) for (int x = 0; x < cols; ++x) out.at<float>(y, x) = (float)data[(size_t)y * step + x];
+        dst = out;
+    }
+    Mat reshape(int, int = 0) const { std::abort(); }   // only behind the reference's distortion path (src/Frame.cc:468)
+    inline MatT t() const;
     template <typename T> T& at(int y, int x) { return *(T*)(data + (size_t)y * step + x * sizeof(T)); }
     template <typename T> const T& at(int y, int x) const { return *(const T*)(data + (size_t)y * step + x * sizeof(T)); }
+    // cv::Mat::at(i0): element i0 of a row or column vector (column vectors may be strided views)
+    template <typename T> T& at(int i) { return cols == 1 ? at<T>(i, 0) : rows == 1 ? at<T>(0, i) : at<T>(i / cols, i % cols); }
+    template <typename T> const T& at(int i) const { return cols == 1 ? at<T>(i, 0) : rows == 1 ? at<T>(0, i) : at<T>(i / cols, i % cols); }
     uchar* ptr(int y = 0) { return data + (size_t)y * step; }
     const uchar* ptr(int y = 0) const { return data + (size_t)y * step; }
     template <typename T> T* ptr(int y = 0) { return (T*)(data + (size_t)y * step); }
     template <typename T> const T* ptr(int y = 0) const { return (const T*)(data + (size_t)y * step); }
+    inline double dot(const Mat& o) const;
 };
 
 class _InputArray {
@@ -132,6 +169,7 @@ class _OutputArray {
     Mat* m_;
 public:
     _OutputArray(Mat& m) : m_(&m) {}
+    _OutputArray(const Mat& m) : m_(const_cast<Mat*>(&m)) {}   // temporaries (ROI headers) as copyTo targets
     void create(int r, int c, int type) const { m_->create(r, c, type); }
     void release() const { m_->release(); }
     Mat getMat() const { return *m_; }
@@ -184,3 +222,4 @@ struct KeyPointsFilter {
 };
 
 }  // namespace cv
+#include "matalg.hpp"

@@ -223,6 +223,23 @@ void orc_assign_features_to_grid(const float* x, const float* y, int n, const or
     *n_items = m;
 }
 
+/* Frame::GetFeaturesInArea (src/Frame.cc:368-424) / KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:594-633, min = max = -1)
+ * for nq query windows; q_start[nq + 1], q_items[cap]; returns the total or -1 when cap is too small. */
+int orc_features_in_area(const orb_frame_view* f, int nq, const float* qx, const float* qy, const float* qr, const int32_t* qmin,
+                         const int32_t* qmax, int32_t* q_start, int32_t* q_items, int cap) {
+    Grid g; build_grid(*f, g);
+    std::vector<int> v;
+    int m = 0;
+    for (int q = 0; q < nq; ++q) {
+        q_start[q] = m;
+        features_in_area(*f, g, qx[q], qy[q], qr[q], qmin[q], qmax[q], v);
+        if (m + (int)v.size() > cap) return -1;
+        for (int i : v) q_items[m++] = i;
+    }
+    q_start[nq] = m;
+    return m;
+}
+
 int orc_search_by_projection_mps(const orb_frame_view* f, const orb_mappoint_view* mps, float th, float nn_ratio, const uint8_t* occupied,
                                  int32_t* match) {
     Grid g; build_grid(*f, g);

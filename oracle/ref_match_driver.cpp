@@ -1,0 +1,390 @@
+// TEST INFRASTRUCTURE — drives the REFERENCE'S OWN matcher / stereo code on the scenario files of
+// tests/test_gpu_cpp_dropin.py (same modes and blob layout as tests/cpp/test_dropin.cpp), so that
+// the oracle's expectations for those scenarios are pinned against the reference itself.
+//
+// Compiled verbatim, where they lie under /root/reference (oracle/Makefile target `refmatch`):
+//   src/ORBmatcher.cc  src/Frame.cc  src/KeyFrame.cc  src/MapPoint.cc  src/Map.cc
+//   src/KeyFrameDatabase.cc  src/ORBextractor.cc  Thirdparty/DBoW2/DBoW2/*.cpp  Thirdparty/DBoW2/DUtils/*.cpp
+// against oracle/cvshim (container types + cv::Mat algebra with OpenCV 4.13's arithmetic) and the
+// reference's own headers.  Objects are real ORB_SLAM2::Frame / KeyFrame / MapPoint / Map instances;
+// this file only fills their members from the scenario and reads the results back.  Protected
+// members (MapPoint::mDescriptor, Frame::AssignFeaturesToGrid ...) are reached by compiling THIS
+// translation unit with the access keywords opened; the reference's translation units are untouched.
+//   ref_match_driver <mode> <in> <out>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <list>
+#include <map>
+#include <mutex>
+#include <set>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <vector>
+#include <unistd.h>
+#include <opencv2/core/core.hpp>
+
+#define private public
+#define protected public
+#include "ORBmatcher.h"
+#include "Map.h"
+#include "KeyFrameDatabase.h"
+#undef private
+#undef protected
+#include "../tests/cpp/blobio.h"
+
+using namespace ORB_SLAM2;
+
+// oracle/ref_wrap.cpp: the reference extractor under the monotonic heap (canonical quadtree tie-break)
+struct ref_keypoint { float x, y, size, angle, response; int32_t octave; };
+extern "C" void* ref_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th);
+extern "C" int ref_extract(void* e, const uint8_t* img, int w, int h, int stride, ref_keypoint* kps, uint8_t* desc, int cap);
+
+static Map g_map;
+static ORBVocabulary g_voc;
+static KeyFrameDatabase* g_db = NULL;
+
+static cv::Mat Identity4() { return cv::Mat::eye(4, 4, CV_32F); }
+static cv::Mat Row32(const unsigned char* p) { cv::Mat d(1, 32, CV_8U); std::memcpy(d.data, p, 32); return d; }
+static cv::Mat Mat44(const float* T) { cv::Mat m(4, 4, CV_32F); std::memcpy(m.data, T, 64); return m; }
+
+// Frame members from a scenario (prefix p): undistorted keypoints, descriptors, scale tables, grid.
+// fx.. and the image bounds are static in the reference (include/Frame.h:80-85,173-179): every frame
+// of one scenario shares them, as in the reference.
+static void LoadFrame(const Blob& b, const std::string& p, Frame& F) {
+    F.N = (int)b.count(p + "x");
+    const float* x = b.get<float>(p + "x"); const float* y = b.get<float>(p + "y"); const float* ang = b.get<float>(p + "angle");
+    const int* oct = b.get<int>(p + "octave"); const float* ur = b.get<float>(p + "u_right");
+    F.mvKeysUn.resize(F.N); F.mvuRight.assign(ur, ur + F.N); F.mvDepth.assign(F.N, -1.f);
+    for (int i = 0; i < F.N; ++i) F.mvKeysUn[i] = cv::KeyPoint(x[i], y[i], 31.f, ang[i], 0.f, oct[i]);
+    F.mvKeys = F.mvKeysUn;
+    F.mDescriptors.create(F.N, 32, CV_8U);
+    if (F.N) std::memcpy(F.mDescriptors.data, b.get<unsigned char>(p + "desc"), (size_t)F.N * 32);
+    const float* sf = b.get<float>(p + "sf"); const size_t nl = b.count(p + "sf");
+    F.mvScaleFactors.assign(sf, sf + nl);
+    F.mvInvScaleFactors.resize(nl); F.mvLevelSigma2.resize(nl); F.mvInvLevelSigma2.resize(nl);
+    for (size_t l = 0; l < nl; ++l) { F.mvInvScaleFactors[l] = 1.0f / sf[l]; F.mvLevelSigma2[l] = sf[l] * sf[l]; F.mvInvLevelSigma2[l] = 1.0f / F.mvLevelSigma2[l]; }
+    F.mnScaleLevels = (int)nl; F.mfScaleFactor = nl > 1 ? sf[1] : 1.2f; F.mfLogScaleFactor = std::log(F.mfScaleFactor);
+    const float* g = b.get<float>(p + "grid");  // min_x, min_y, max_x, max_y, inv_w, inv_h
+    Frame::mnMinX = g[0]; Frame::mnMinY = g[1]; Frame::mnMaxX = g[2]; Frame::mnMaxY = g[3];
+    Frame::mfGridElementWidthInv = g[4]; Frame::mfGridElementHeightInv = g[5];
+    Frame::mbInitialComputations = false;
+    F.mvpMapPoints.assign(F.N, (MapPoint*)NULL); F.mvbOutlier.assign(F.N, false);
+    F.mpORBvocabulary = &g_voc; F.mpORBextractorLeft = F.mpORBextractorRight = NULL; F.mpReferenceKF = NULL;
+    F.mTimeStamp = 0; F.mnId = Frame::nNextId++;
+    F.mK = cv::Mat::eye(3, 3, CV_32F); F.mDistCoef = cv::Mat::zeros(4, 1, CV_32F);
+    Frame::fx = Frame::fy = 1.f; Frame::cx = Frame::cy = 0.f; Frame::invfx = Frame::invfy = 1.f;
+    F.mbf = 0.f; F.mb = 0.f; F.mThDepth = 0.f;
+    for (int i = 0; i < FRAME_GRID_COLS; ++i) for (int j = 0; j < FRAME_GRID_ROWS; ++j) F.mGrid[i][j].clear();
+    F.AssignFeaturesToGrid();                  // src/Frame.cc:261-276
+    F.SetPose(Identity4());                    // src/Frame.cc:287-300
+    if (b.has(p + "fv_ids")) {
+        const unsigned* ids = b.get<unsigned>(p + "fv_ids"); const int* st = b.get<int>(p + "fv_start"); const unsigned* it = b.get<unsigned>(p + "fv_items");
+        for (size_t k = 0; k < b.count(p + "fv_ids"); ++k) for (int q = st[k]; q < st[k + 1]; ++q) F.mFeatVec.addFeature(ids[k], it[q]);
+    }
+}
+static void SetCamera(Frame& F, const float* cam) {
+    Frame::fx = cam[0]; Frame::fy = cam[1]; Frame::cx = cam[2]; Frame::cy = cam[3];
+    Frame::invfx = 1.0f / cam[0]; Frame::invfy = 1.0f / cam[1];
+    F.mbf = cam[4]; F.mb = F.mbf / Frame::fx;
+}
+
+// MapPoints of a world scenario: position, normal, distance range, descriptor, flags.  ids[MapPoint*] = index.
+static std::map<MapPoint*, int> g_id;
+static MapPoint* NewPoint(const float* xw, KeyFrame* pRef) {
+    cv::Mat pos(3, 1, CV_32F);
+    for (int k = 0; k < 3; ++k) pos.at<float>(k) = xw ? xw[k] : 0.f;
+    return new MapPoint(pos, pRef, &g_map);    // src/MapPoint.cc:32-44
+}
+static void LoadPoints(const Blob& b, const std::string& p, KeyFrame* pRef, std::vector<MapPoint*>& all, std::vector<MapPoint*>& ptrs, int idBase = 0) {
+    const int M = (int)b.count(p + "maxd");
+    all.assign(M, (MapPoint*)NULL); ptrs.assign(M, (MapPoint*)NULL);
+    for (int i = 0; i < M; ++i) {
+        MapPoint* m = NewPoint(b.get<float>(p + "xw") + 3 * i, pRef);
+        for (int k = 0; k < 3; ++k) m->mNormalVector.at<float>(k) = b.get<float>(p + "normal")[3 * i + k];
+        m->mfMaxDistance = b.get<float>(p + "maxd")[i]; m->mfMinDistance = b.get<float>(p + "mind")[i];
+        m->mDescriptor = Row32(b.get<unsigned char>(p + "desc") + (size_t)i * 32);
+        m->mbBad = b.get<unsigned char>(p + "bad")[i] != 0;
+        m->nObs = b.get<int>(p + "nobs")[i];
+        g_id[m] = idBase + i; all[i] = m;
+        if (!b.get<unsigned char>(p + "null")[i]) ptrs[i] = m;
+    }
+}
+static int IdOf(MapPoint* m) { return m && g_id.count(m) ? g_id[m] : -1; }
+
+// A KeyFrame whose features are M placeholders carrying only an angle (the KeyFrame side of the
+// relocalisation search reads pKF->mvKeysUn[i].angle and GetMapPointMatches(), nothing else).
+static KeyFrame* MakeAngleKeyFrame(const Frame& like, int M, const float* angle) {
+    Frame S(like);
+    S.N = M; S.mvKeys.assign(M, cv::KeyPoint()); S.mvKeysUn.assign(M, cv::KeyPoint());
+    for (int i = 0; i < M; ++i) S.mvKeysUn[i].angle = angle[i];
+    S.mvuRight.assign(M, -1.f); S.mvDepth.assign(M, -1.f);
+    S.mDescriptors = cv::Mat::zeros(M > 0 ? M : 1, 32, CV_8U);
+    S.mvpMapPoints.assign(M, (MapPoint*)NULL); S.mvbOutlier.assign(M, false);
+    for (int i = 0; i < FRAME_GRID_COLS; ++i) for (int j = 0; j < FRAME_GRID_ROWS; ++j) S.mGrid[i][j].clear();
+    return new KeyFrame(S, &g_map, g_db);
+}
+
+static void PutMatch(BlobWriter& w, int n, const std::vector<int>& match) { w.put("n", "i4", &n, 1); w.put("match", "i4", match.data(), match.size()); }
+
+static int RunStereo(const Blob& b, BlobWriter& w);
+static int RunGrid(const Blob& b, BlobWriter& w);
+
+int main(int argc, char** argv) {
+    if (argc < 4) { fprintf(stderr, "usage: ref_match_driver <mode> <in> <out>\n"); return 2; }
+    const std::string mode = argv[1];
+    try {
+        Blob b; b.load(argv[2]);
+        BlobWriter w(argv[3]);
+        g_db = new KeyFrameDatabase(g_voc);
+        if (mode == "stereo") return RunStereo(b, w);
+        if (mode == "grid") return RunGrid(b, w);
+        if (mode == "mappoints") {
+            Frame F; LoadFrame(b, "f_", F);
+            KeyFrame* ref = new KeyFrame(F, &g_map, g_db);
+            const int M = (int)b.count("mp_valid");
+            std::vector<MapPoint*> mps(M);
+            const unsigned char* valid = b.get<unsigned char>("mp_valid"); const unsigned char* blocks = b.get<unsigned char>("mp_blocks");
+            for (int i = 0; i < M; ++i) {
+                MapPoint* m = NewPoint(NULL, ref); g_id[m] = i;
+                m->mbTrackInView = valid[i] != 0;
+                m->mTrackProjX = b.get<float>("mp_proj_x")[i]; m->mTrackProjY = b.get<float>("mp_proj_y")[i]; m->mTrackProjXR = b.get<float>("mp_proj_xr")[i];
+                m->mnTrackScaleLevel = b.get<int>("mp_level")[i]; m->mTrackViewCos = b.get<float>("mp_view_cos")[i];
+                m->mDescriptor = Row32(b.get<unsigned char>("mp_desc") + (size_t)i * 32); m->nObs = blocks[i] ? 1 : 0;
+                mps[i] = m;
+            }
+            MapPoint* holder = NewPoint(NULL, ref); holder->nObs = 3;   // keypoints that already hold an observed MapPoint (:90-93)
+            const unsigned char* occ = b.get<unsigned char>("occupied");
+            for (int i = 0; i < F.N; ++i) if (occ[i]) F.mvpMapPoints[i] = holder;
+            ORBmatcher matcher(b.get<float>("ratio")[0], true);
+            const int n = matcher.SearchByProjection(F, mps, b.get<float>("th")[0]);
+            std::vector<int> match(F.N, -1);
+            for (int i = 0; i < F.N; ++i) if (F.mvpMapPoints[i] && F.mvpMapPoints[i] != holder) match[i] = IdOf(F.mvpMapPoints[i]);
+            PutMatch(w, n, match);
+        } else if (mode == "lastframe") {
+            Frame Cur; LoadFrame(b, "f_", Cur);
+            KeyFrame* ref = new KeyFrame(Cur, &g_map, g_db);
+            const int M = (int)b.count("l_valid");
+            Frame Last(Cur);
+            Last.N = M; Last.mvKeys.assign(M, cv::KeyPoint()); Last.mvKeysUn.assign(M, cv::KeyPoint());
+            Last.mvpMapPoints.assign(M, (MapPoint*)NULL); Last.mvbOutlier.assign(M, false);
+            for (int i = 0; i < M; ++i) {
+                const float xw[3] = {b.get<float>("l_xc")[i], b.get<float>("l_yc")[i], b.get<float>("l_zc")[i]};
+                MapPoint* m = NewPoint(xw, ref); g_id[m] = i;
+                m->nObs = b.get<unsigned char>("l_blocks")[i] ? 1 : 0;
+                m->mDescriptor = Row32(b.get<unsigned char>("l_desc") + (size_t)i * 32);
+                Last.mvKeys[i].octave = b.get<int>("l_octave")[i]; Last.mvKeysUn[i].angle = b.get<float>("l_angle")[i];
+                if (b.get<unsigned char>("l_valid")[i]) Last.mvpMapPoints[i] = m;
+            }
+            SetCamera(Cur, b.get<float>("cam")); Cur.mb = 1e9f;  // identity poses: neither forward nor backward
+            ORBmatcher matcher(0.9f, b.get<int>("check_ori")[0] != 0);
+            const int n = matcher.SearchByProjection(Cur, Last, b.get<float>("th")[0], false);
+            std::vector<int> match(Cur.N, -1);
+            for (int i = 0; i < Cur.N; ++i) if (Cur.mvpMapPoints[i]) match[i] = IdOf(Cur.mvpMapPoints[i]);
+            PutMatch(w, n, match);
+        } else if (mode == "bow" || mode == "tri" || mode == "bowkf") {
+            Frame A, B; LoadFrame(b, "a_", A); LoadFrame(b, "b_", B);
+            if (mode == "tri") {   // camera centre of KF1 = (ex, ey, 1), KF2 at the origin with unit intrinsics -> epipole (ex, ey)
+                const float* ep = b.get<float>("epipole");
+                cv::Mat T = Identity4(); T.at<float>(0, 3) = -ep[0]; T.at<float>(1, 3) = -ep[1]; T.at<float>(2, 3) = -1.f;
+                A.SetPose(T);
+            }
+            KeyFrame* KA = new KeyFrame(A, &g_map, g_db); KeyFrame* KB = new KeyFrame(B, &g_map, g_db);
+            std::vector<MapPoint*> sb(B.N, (MapPoint*)NULL);
+            for (int i = 0; i < A.N; ++i) if (b.get<unsigned char>("has_a")[i]) { MapPoint* m = NewPoint(NULL, KA); g_id[m] = i; KA->AddMapPoint(m, i); }
+            for (int i = 0; i < B.N; ++i) if (b.get<unsigned char>("has_b")[i]) { MapPoint* m = NewPoint(NULL, KB); g_id[m] = i; KB->AddMapPoint(m, i); B.mvpMapPoints[i] = m; }
+            const bool ori = b.has("check_ori") ? b.get<int>("check_ori")[0] != 0 : true;
+            ORBmatcher matcher(b.get<float>("ratio")[0], ori);
+            if (mode == "bow") {
+                std::vector<MapPoint*> out;
+                const int n = matcher.SearchByBoW(KA, B, out);
+                std::vector<int> match(B.N, -1);
+                for (int j = 0; j < B.N; ++j) if (out[j]) match[j] = IdOf(out[j]);
+                PutMatch(w, n, match);
+            } else if (mode == "bowkf") {
+                std::vector<MapPoint*> out;
+                const int n = matcher.SearchByBoW(KA, KB, out);
+                std::vector<int> match(A.N, -1);
+                for (int i = 0; i < A.N; ++i) if (out[i]) match[i] = IdOf(out[i]);
+                PutMatch(w, n, match);
+            } else {
+                cv::Mat F12(3, 3, CV_32F); std::memcpy(F12.data, b.get<float>("f12"), 36);
+                std::vector<std::pair<size_t, size_t> > pairs;
+                const int n = matcher.SearchForTriangulation(KA, KB, F12, pairs, b.get<int>("only_stereo")[0] != 0);
+                std::vector<int> flat;
+                for (size_t k = 0; k < pairs.size(); ++k) { flat.push_back((int)pairs[k].first); flat.push_back((int)pairs[k].second); }
+                w.put("n", "i4", &n, 1); w.put("pairs", "i4", flat.data(), flat.size());
+            }
+        } else if (mode == "reloc" || mode == "loop") {
+            Frame F; LoadFrame(b, "f_", F);
+            SetCamera(F, b.get<float>("cam"));
+            F.SetPose(Mat44(b.get<float>("pose")));
+            const int M = (int)b.count("p_maxd");
+            const unsigned char* occ = b.get<unsigned char>("occupied"); const unsigned char* found = b.get<unsigned char>("p_found");
+            ORBmatcher matcher(0.75f, b.get<int>("check_ori")[0] != 0);
+            std::vector<MapPoint*> all, pts;
+            std::vector<int> match(F.N, -1);
+            int n;
+            if (mode == "reloc") {   // Tracking::Relocalization: matcher.SearchByProjection(mCurrentFrame, vpCandidateKFs[i], sFound, 10, 100)
+                KeyFrame* K = MakeAngleKeyFrame(F, M, b.get<float>("p_angle"));
+                LoadPoints(b, "p_", K, all, pts);
+                MapPoint* holder = NewPoint(NULL, K); holder->nObs = 3;
+                for (int i = 0; i < F.N; ++i) if (occ[i]) F.mvpMapPoints[i] = holder;
+                for (int i = 0; i < M; ++i) if (pts[i]) K->AddMapPoint(pts[i], i);
+                std::set<MapPoint*> sFound;
+                for (int i = 0; i < M; ++i) if (found[i] && pts[i]) sFound.insert(pts[i]);
+                n = matcher.SearchByProjection(F, K, sFound, b.get<float>("th")[0], b.get<int>("max_dist")[0]);
+                for (int i = 0; i < F.N; ++i) if (F.mvpMapPoints[i] && F.mvpMapPoints[i] != holder) match[i] = IdOf(F.mvpMapPoints[i]);
+            } else {                 // LoopClosing::ComputeSim3: matcher.SearchByProjection(mpCurrentKF, mScw, mvpLoopMapPoints, mvpCurrentMatchedPoints, 10)
+                KeyFrame* K = new KeyFrame(F, &g_map, g_db);
+                LoadPoints(b, "p_", K, all, pts);
+                MapPoint* holder = NewPoint(NULL, K); holder->nObs = 3;
+                std::vector<MapPoint*> vpMatched(F.N, (MapPoint*)NULL);
+                int nf = 0;
+                std::vector<int> foundIdx; for (int i = 0; i < M; ++i) if (found[i]) foundIdx.push_back(i);
+                for (int i = 0; i < F.N; ++i) if (occ[i]) vpMatched[i] = (nf < (int)foundIdx.size()) ? pts[foundIdx[nf++]] : holder;
+                std::vector<MapPoint*> before = vpMatched;
+                n = matcher.SearchByProjection(K, Mat44(b.get<float>("pose")), pts, vpMatched, (int)b.get<float>("th")[0]);
+                for (int i = 0; i < F.N; ++i) if (vpMatched[i] && !before[i]) match[i] = IdOf(vpMatched[i]);
+            }
+            PutMatch(w, n, match);
+        } else if (mode == "fuse" || mode == "fuse_scw") {
+            // LocalMapping::SearchInNeighbors: matcher.Fuse(pKFi, vpMapPointMatches) (src/LocalMapping.cc:584,613);
+            // LoopClosing::SearchAndFuse: matcher.Fuse(pKF, cvScw, mvpLoopMapPoints, 4, vpReplacePoints) (src/LoopClosing.cc:652)
+            Frame F; LoadFrame(b, "f_", F);
+            SetCamera(F, b.get<float>("cam"));
+            F.SetPose(Mat44(b.get<float>("pose")));
+            KeyFrame* K = new KeyFrame(F, &g_map, g_db);
+            std::vector<MapPoint*> all, pts; LoadPoints(b, "p_", K, all, pts);
+            const int M = (int)pts.size();
+            const int E = (int)b.count("e_kp");    // MapPoints the keyframe already holds
+            std::vector<MapPoint*> existing(E);
+            for (int j = 0; j < E; ++j) {
+                MapPoint* m = NewPoint(NULL, K); g_id[m] = 100000 + j;
+                m->nObs = b.get<int>("e_nobs")[j]; m->mbBad = b.get<unsigned char>("e_bad")[j] != 0;
+                existing[j] = m; K->AddMapPoint(m, b.get<int>("e_kp")[j]);
+            }
+            const int* inkf = b.get<int>("p_in_kf");   // candidates already observed in the keyframe (:927 / :1087)
+            for (int i = 0; i < M; ++i) if (inkf[i] >= 0 && pts[i]) { pts[i]->mObservations[K] = (size_t)inkf[i]; K->AddMapPoint(pts[i], inkf[i]); }
+            ORBmatcher matcher;
+            int n;
+            std::vector<int> replace(M, -1);
+            if (mode == "fuse") n = matcher.Fuse(K, pts, b.get<float>("th")[0]);
+            else {
+                std::vector<MapPoint*> vpReplace(M, (MapPoint*)NULL);
+                n = matcher.Fuse(K, Mat44(b.get<float>("pose")), pts, b.get<float>("th")[0], vpReplace);
+                for (int i = 0; i < M; ++i) if (vpReplace[i]) replace[i] = IdOf(vpReplace[i]);
+            }
+            std::vector<int> kf_mp(F.N, -1), p_bad(M, 0), p_repl(M, -1), p_idx(M, -1), p_nobs(M, 0), e_bad(E, 0), e_repl(E, -1);
+            for (int i = 0; i < F.N; ++i) kf_mp[i] = IdOf(K->GetMapPoint(i));
+            for (int i = 0; i < M; ++i) { p_bad[i] = all[i]->mbBad; p_repl[i] = IdOf(all[i]->mpReplaced); p_idx[i] = all[i]->GetIndexInKeyFrame(K); p_nobs[i] = all[i]->nObs; }
+            for (int j = 0; j < E; ++j) { e_bad[j] = existing[j]->mbBad; e_repl[j] = IdOf(existing[j]->mpReplaced); }
+            w.put("n", "i4", &n, 1); w.put("kf_mp", "i4", kf_mp.data(), kf_mp.size()); w.put("replace", "i4", replace.data(), replace.size());
+            w.put("p_bad", "i4", p_bad.data(), p_bad.size()); w.put("p_repl", "i4", p_repl.data(), p_repl.size()); w.put("p_idx", "i4", p_idx.data(), p_idx.size());
+            w.put("p_nobs", "i4", p_nobs.data(), p_nobs.size());
+            w.put("e_bad", "i4", e_bad.data(), e_bad.size()); w.put("e_repl", "i4", e_repl.data(), e_repl.size());
+        } else if (mode == "sim3") {
+            // LoopClosing::ComputeSim3: matcher.SearchBySim3(mpCurrentKF, pKF, vpMapPointMatches, s, R, t, 7.5) (src/LoopClosing.cc:348)
+            Frame A, B; LoadFrame(b, "a_", A); LoadFrame(b, "b_", B);
+            SetCamera(A, b.get<float>("cam")); SetCamera(B, b.get<float>("cam"));
+            A.SetPose(Mat44(b.get<float>("pose_a"))); B.SetPose(Mat44(b.get<float>("pose_b")));
+            KeyFrame* KA = new KeyFrame(A, &g_map, g_db); KeyFrame* KB = new KeyFrame(B, &g_map, g_db);
+            std::vector<MapPoint*> sa, sb, pa, pb;
+            LoadPoints(b, "pa_", KA, sa, pa); LoadPoints(b, "pb_", KB, sb, pb);
+            for (int i = 0; i < A.N; ++i) if (pa[i]) KA->AddMapPoint(pa[i], i);
+            for (int j = 0; j < B.N; ++j) if (pb[j]) { KB->AddMapPoint(pb[j], j); pb[j]->mObservations[KB] = (size_t)j; }
+            std::vector<MapPoint*> m12(A.N, (MapPoint*)NULL);
+            const int* pre = b.get<int>("pre");
+            for (int i = 0; i < A.N; ++i) if (pre[i] >= 0) m12[i] = sb[pre[i]];
+            cv::Mat R12(3, 3, CV_32F), t12(3, 1, CV_32F);
+            std::memcpy(R12.data, b.get<float>("r12"), 36); std::memcpy(t12.data, b.get<float>("t12"), 12);
+            ORBmatcher matcher(0.75f, true);
+            const int n = matcher.SearchBySim3(KA, KB, m12, b.get<float>("s12")[0], R12, t12, b.get<float>("th")[0]);
+            std::vector<int> match(A.N, -1);
+            for (int i = 0; i < A.N; ++i) if (m12[i]) match[i] = IdOf(m12[i]);
+            PutMatch(w, n, match);
+        } else if (mode == "init") {
+            Frame A, B; LoadFrame(b, "a_", A); LoadFrame(b, "b_", B);
+            std::vector<cv::Point2f> prev(A.N);
+            for (int i = 0; i < A.N; ++i) prev[i] = cv::Point2f(b.get<float>("prev_x")[i], b.get<float>("prev_y")[i]);
+            ORBmatcher matcher(b.get<float>("ratio")[0], b.get<int>("check_ori")[0] != 0);
+            std::vector<int> m12;
+            const int n = matcher.SearchForInitialization(A, B, prev, m12, b.get<int>("window")[0]);
+            std::vector<float> px(A.N), py(A.N);
+            for (int i = 0; i < A.N; ++i) { px[i] = prev[i].x; py[i] = prev[i].y; }
+            PutMatch(w, n, m12);
+            w.put("prev_x", "f4", px.data(), px.size()); w.put("prev_y", "f4", py.data(), py.size());
+        } else {
+            fprintf(stderr, "unknown mode %s\n", mode.c_str());
+            return 2;
+        }
+    } catch (const std::exception& e) {
+        fprintf(stderr, "ref_match_driver: %s\n", e.what());
+        return 1;
+    }
+    return 0;
+}
+
+// Frame::ComputeStereoMatches (src/Frame.cc:516-704) on a stereo pair: both images go through the
+// reference extractor, the Frame is filled the way its stereo constructor does (:64-126), then the
+// reference's own ComputeStereoMatches runs.  (The fork's debugging dump "xiewenzhang.txt", :556,
+// lands in the current directory: the test runs this binary inside its tmp_path.)
+static int RunStereo(const Blob& b, BlobWriter& w) {
+    const int* p = b.get<int>("params");  // w, h, nfeatures, nlevels, iniTh, minTh
+    const float sf = b.get<float>("scale")[0];
+    const float mbf = b.get<float>("stereo")[0], fx = b.get<float>("stereo")[1];
+    ORBextractor* eL = (ORBextractor*)ref_extractor_create(p[2], sf, p[3], p[4], p[5]);
+    ORBextractor* eR = (ORBextractor*)ref_extractor_create(p[2], sf, p[3], p[4], p[5]);
+    const int cap = p[2] * 4 + 1024;
+    std::vector<ref_keypoint> kl(cap), kr(cap); std::vector<uint8_t> dl((size_t)cap * 32), dr((size_t)cap * 32);
+    const int nl = ref_extract(eL, b.get<unsigned char>("left"), p[0], p[1], p[0], kl.data(), dl.data(), cap);
+    const int nr = ref_extract(eR, b.get<unsigned char>("right"), p[0], p[1], p[0], kr.data(), dr.data(), cap);
+    if (nl < 0 || nr < 0) throw std::runtime_error("keypoint capacity");
+    Frame F;
+    F.mpORBextractorLeft = eL; F.mpORBextractorRight = eR;
+    F.mnScaleLevels = eL->GetLevels(); F.mfScaleFactor = eL->GetScaleFactor(); F.mfLogScaleFactor = std::log(F.mfScaleFactor);
+    F.mvScaleFactors = eL->GetScaleFactors(); F.mvInvScaleFactors = eL->GetInverseScaleFactors();
+    F.mvLevelSigma2 = eL->GetScaleSigmaSquares(); F.mvInvLevelSigma2 = eL->GetInverseScaleSigmaSquares();
+    F.mvKeys.resize(nl); F.mvKeysRight.resize(nr);
+    for (int i = 0; i < nl; ++i) F.mvKeys[i] = cv::KeyPoint(kl[i].x, kl[i].y, kl[i].size, kl[i].angle, kl[i].response, kl[i].octave);
+    for (int i = 0; i < nr; ++i) F.mvKeysRight[i] = cv::KeyPoint(kr[i].x, kr[i].y, kr[i].size, kr[i].angle, kr[i].response, kr[i].octave);
+    F.mDescriptors.create(nl, 32, CV_8U); F.mDescriptorsRight.create(nr, 32, CV_8U);
+    if (nl) std::memcpy(F.mDescriptors.data, dl.data(), (size_t)nl * 32);
+    if (nr) std::memcpy(F.mDescriptorsRight.data, dr.data(), (size_t)nr * 32);
+    F.N = nl;
+    F.mvKeysUn = F.mvKeys;                       // no distortion (src/Frame.cc:454-458)
+    Frame::fx = fx; F.mbf = mbf; F.mb = mbf / fx; // :117
+    F.ComputeStereoMatches();
+    const float maxd = F.mbf / F.mb;              // :529-531 (minZ = mb)
+    w.put("kl", "u1", kl.data(), (size_t)nl * sizeof(ref_keypoint)); w.put("dl", "u1", dl.data(), (size_t)nl * 32);
+    w.put("kr", "u1", kr.data(), (size_t)nr * sizeof(ref_keypoint)); w.put("dr", "u1", dr.data(), (size_t)nr * 32);
+    w.put("u_right", "f4", F.mvuRight.data(), F.mvuRight.size()); w.put("depth", "f4", F.mvDepth.data(), F.mvDepth.size());
+    w.put("max_d", "f4", &maxd, 1);
+    return 0;
+}
+
+// Frame::AssignFeaturesToGrid / GetFeaturesInArea and KeyFrame::GetFeaturesInArea on query windows
+static int RunGrid(const Blob& b, BlobWriter& w) {
+    Frame F; LoadFrame(b, "f_", F);
+    KeyFrame* K = new KeyFrame(F, &g_map, g_db);
+    std::vector<int> start(1, 0), items;
+    for (int ix = 0; ix < FRAME_GRID_COLS; ++ix)
+        for (int iy = 0; iy < FRAME_GRID_ROWS; ++iy) { for (size_t k = 0; k < F.mGrid[ix][iy].size(); ++k) items.push_back((int)F.mGrid[ix][iy][k]); start.push_back((int)items.size()); }
+    w.put("cell_start", "i4", start.data(), start.size()); w.put("cell_items", "i4", items.data(), items.size());
+    const int Q = (int)b.count("qx");
+    std::vector<int> qs(1, 0), qi, ks(1, 0), ki;
+    for (int q = 0; q < Q; ++q) {
+        const std::vector<size_t> v = F.GetFeaturesInArea(b.get<float>("qx")[q], b.get<float>("qy")[q], b.get<float>("qr")[q], b.get<int>("qmin")[q], b.get<int>("qmax")[q]);
+        for (size_t k = 0; k < v.size(); ++k) qi.push_back((int)v[k]);
+        qs.push_back((int)qi.size());
+        const std::vector<size_t> u = K->GetFeaturesInArea(b.get<float>("qx")[q], b.get<float>("qy")[q], b.get<float>("qr")[q]);
+        for (size_t k = 0; k < u.size(); ++k) ki.push_back((int)u[k]);
+        ks.push_back((int)ki.size());
+    }
+    w.put("q_start", "i4", qs.data(), qs.size()); w.put("q_items", "i4", qi.data(), qi.size());
+    w.put("k_start", "i4", ks.data(), ks.size()); w.put("k_items", "i4", ki.data(), ki.size());
+    return 0;
+}

@@ -201,6 +201,19 @@ def assign_features_to_grid(frame):
     return cs, ci[:n.value].copy()
 
 
+def features_in_area_batch(frame, qx, qy, qr, qmin, qmax):
+    """GetFeaturesInArea for a batch of windows: (start[nq + 1], items)."""
+    qx = np.ascontiguousarray(qx, np.float32); qy = np.ascontiguousarray(qy, np.float32); qr = np.ascontiguousarray(qr, np.float32)
+    qmin = np.ascontiguousarray(qmin, np.int32); qmax = np.ascontiguousarray(qmax, np.int32)
+    nq = len(qx); cap = max(frame.N, 1) * nq
+    st = np.empty(nq + 1, np.int32); it = np.empty(cap, np.int32)
+    fv = frame.view()
+    lib.orc_features_in_area.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 7 + [C.c_int]
+    n = lib.orc_features_in_area(C.byref(fv), nq, _p(qx), _p(qy), _p(qr), _p(qmin), _p(qmax), _p(st), _p(it), cap)
+    assert n >= 0
+    return st, it[:n].copy()
+
+
 def search_by_projection_mps(F, mappoints, th, nn_ratio, occupied=None):
     mp, keep = _mt._mp_view(mappoints)
     match = np.empty(max(F.N, 1), np.int32)

@@ -85,7 +85,7 @@ public:
     template <class FrameT>
     int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono) {
         FrameArrays fa; GatherFrame(CurrentFrame, fa);
-        // :1472-1487 (float matrices; products accumulate in double like cv::gemm on CV_32F)
+        // :1472-1487 (float matrices; -Rcw.t() * tcw carries a transpose flag: cv::gemm accumulates it in double)
         float Rcw[9], tcw[3], Rlw[9], tlw[3], twc[3], tlc[3];
         SplitPose(CurrentFrame.mTcw, Rcw, tcw); SplitPose(LastFrame.mTcw, Rlw, tlw);
         for (int r = 0; r < 3; ++r) twc[r] = (float)(-((double)Rcw[0 * 3 + r] * tcw[0] + (double)Rcw[1 * 3 + r] * tcw[1] + (double)Rcw[2 * 3 + r] * tcw[2]));
@@ -378,7 +378,7 @@ public:
             for (int k = 0; k < 3; ++k) { sR12[3 * r + k] = s12 * R12.at<float>(r, k); sR21[3 * r + k] = inv_s * R12.at<float>(k, r); }   // :1229-1230
             t12f[r] = t12.at<float>(r);
         }
-        for (int r = 0; r < 3; ++r) t21[r] = (float)(-((double)sR21[3 * r] * t12f[0] + (double)sR21[3 * r + 1] * t12f[1] + (double)sR21[3 * r + 2] * t12f[2]));   // :1231
+        for (int r = 0; r < 3; ++r) t21[r] = -MulRow(sR21 + 3 * r, t12f);   // :1231 (-sR21 * t12: plain 3x3 * 3x1 product, float)
 
         const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
         const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
@@ -566,10 +566,15 @@ protected:
     static void SplitPose(const cv::Mat& Tcw, float* R, float* t) {
         for (int r = 0; r < 3; ++r) { for (int k = 0; k < 3; ++k) R[3 * r + k] = Tcw.at<float>(r, k); t[r] = Tcw.at<float>(r, 3); }
     }
-    // one row of R * x + t on CV_32F data: cv::gemm accumulates float products in double
-    static float MulRowAdd(const float* row, const float* x, float t) {
-        return (float)((double)row[0] * x[0] + (double)row[1] * x[1] + (double)row[2] * x[2] + (double)t);
+    // one row of R * x + t on CV_32F data.  cv::gemm without transpose flags and inner length 2..4 (3x3 * 3x1)
+    // takes its unrolled path: float products summed left to right in float, then "+ t" (probed against
+    // OpenCV 4.13; products that carry a transpose flag, e.g. -R.t() * t, accumulate in double instead).
+    // Each product goes through double (exact) and back, so no compiler can contract it into an FMA.
+    static float MulRow(const float* row, const float* x) {
+        const float p0 = (float)((double)row[0] * x[0]), p1 = (float)((double)row[1] * x[1]), p2 = (float)((double)row[2] * x[2]);
+        return (p0 + p1) + p2;
     }
+    static float MulRowAdd(const float* row, const float* x, float t) { return MulRow(row, x) + t; }
 
     float mfNNratio;
     bool mbCheckOrientation;

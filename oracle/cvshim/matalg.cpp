@@ -52,7 +52,7 @@ Mat scale(const Mat& a, double alpha) {
     assert(a.type() == CV_32F);
     Mat d(a.rows, a.cols, CV_32F);
     for (int r = 0; r < a.rows; ++r)
-        for (int c = 0; c < a.cols; ++c) d.at<float>(r, c) = (float)((double)F(a, r, c) * alpha);
+        for (int c = 0; c < a.cols; ++c) d.at<float>(r, c) = F(a, r, c) * (float)alpha;   // cvtScale 32f -> 32f works in float
     return d;
 }
 
@@ -60,7 +60,7 @@ Mat transpose_scaled(const Mat& a, double alpha) {
     assert(a.type() == CV_32F);
     Mat d(a.cols, a.rows, CV_32F);
     for (int r = 0; r < a.rows; ++r)
-        for (int c = 0; c < a.cols; ++c) d.at<float>(c, r) = alpha == 1.0 ? F(a, r, c) : (float)((double)F(a, r, c) * alpha);
+        for (int c = 0; c < a.cols; ++c) d.at<float>(c, r) = alpha == 1.0 ? F(a, r, c) : F(a, r, c) * (float)alpha;
     return d;
 }
 

@@ -7,7 +7,7 @@
 //     float products summed left to right in float, unfused; "+C" is one more float add;
 //   * every other product (A.t()*B, longer inner lengths): products accumulated in double,
 //     result = (float)(alpha * sum);
-//   * alpha*A, A/alpha, A.t()*alpha: (float)(a * (double)alpha), division = times (1.0 / alpha);
+//   * alpha*A, A/alpha, A.t()*alpha: a * (float)alpha in float (cvtScale 32f -> 32f), division = times (float)(1.0 / alpha);
 //   * norm (L2) and dot: accumulated in double.
 // The numeric kernels live in oracle/cvshim/matalg.cpp, compiled with -ffp-contract=off.
 #pragma once

@@ -132,6 +132,7 @@ static void PutMatch(BlobWriter& w, int n, const std::vector<int>& match) { w.pu
 
 static int RunStereo(const Blob& b, BlobWriter& w);
 static int RunGrid(const Blob& b, BlobWriter& w);
+static int RunAlgebra(const Blob& b, BlobWriter& w);
 
 int main(int argc, char** argv) {
     if (argc < 4) { fprintf(stderr, "usage: ref_match_driver <mode> <in> <out>\n"); return 2; }
@@ -142,6 +143,7 @@ int main(int argc, char** argv) {
         g_db = new KeyFrameDatabase(g_voc);
         if (mode == "stereo") return RunStereo(b, w);
         if (mode == "grid") return RunGrid(b, w);
+        if (mode == "algebra") return RunAlgebra(b, w);
         if (mode == "mappoints") {
             Frame F; LoadFrame(b, "f_", F);
             KeyFrame* ref = new KeyFrame(F, &g_map, g_db);
@@ -386,5 +388,23 @@ static int RunGrid(const Blob& b, BlobWriter& w) {
     }
     w.put("q_start", "i4", qs.data(), qs.size()); w.put("q_items", "i4", qi.data(), qi.size());
     w.put("k_start", "i4", ks.data(), ks.size()); w.put("k_items", "i4", ki.data(), ki.size());
+    return 0;
+}
+
+// The shim's cv::Mat algebra on batches of random matrices, for comparison with the real cv2.gemm / cv2.norm
+// (tests/test_oracle_refmatch.py::test_shim_algebra_matches_cv2).
+static int RunAlgebra(const Blob& b, BlobWriter& w) {
+    const int n = (int)b.count("x") / 3;
+    const float* R = b.get<float>("R"); const float* x = b.get<float>("x"); const float* t = b.get<float>("t"); const float* T4 = b.get<float>("T4");
+    std::vector<float> rxt(3 * n), ow(3 * n), nrm(n), rr(9 * n), tt(16 * n), dt(n);
+    for (int i = 0; i < n; ++i) {
+        cv::Mat Rm(3, 3, CV_32F, (void*)(R + 9 * i)), xm(3, 1, CV_32F, (void*)(x + 3 * i)), tm(3, 1, CV_32F, (void*)(t + 3 * i)), Tm(4, 4, CV_32F, (void*)(T4 + 16 * i));
+        cv::Mat a = Rm * xm + tm, o = -Rm.t() * tm, r2 = Rm * Rm, t2 = Tm * Tm;
+        for (int k = 0; k < 3; ++k) { rxt[3 * i + k] = a.at<float>(k); ow[3 * i + k] = o.at<float>(k); }
+        nrm[i] = (float)cv::norm(xm); dt[i] = (float)xm.dot(tm);
+        std::memcpy(&rr[9 * i], r2.data, 36); std::memcpy(&tt[16 * i], t2.data, 64);
+    }
+    w.put("rxt", "f4", rxt.data(), rxt.size()); w.put("ow", "f4", ow.data(), ow.size()); w.put("norm", "f4", nrm.data(), nrm.size());
+    w.put("rr", "f4", rr.data(), rr.size()); w.put("tt", "f4", tt.data(), tt.size()); w.put("dot", "f4", dt.data(), dt.size());
     return 0;
 }

@@ -105,3 +105,70 @@ def test_grid_and_features_in_area(dropin, tmp_path, seed):
     st, it = orc.features_in_area_batch(F, qx, qy, qr, np.full(Q, -1), np.full(Q, -1))
     assert np.array_equal(out["k_start"], st) and np.array_equal(out["k_items"], it)
     assert out["q_start"][-1] > 1000
+
+
+@pytest.mark.parametrize("idx,th", [(0, 3.0), (1, 3.0)])
+def test_fuse(dropin, tmp_path, idx, th):
+    """Fuse(KF, MapPoints, th) (src/ORBmatcher.cc:903-1054) with the reference's real MapPoint::Replace /
+    AddObservation / KeyFrame::ReplaceMapPointMatch (src/MapPoint.cc:97-211) applied by the reference itself:
+    the oracle's candidate search + a replay of those map updates gives the same map."""
+    f, wd, e_kp, e_nobs, e_bad, in_kf = D._fuse_scenario(idx, 1.0)
+    KF, blob = D._world_blob(f, wd, np.zeros(2000, bool), th, False)
+    blob.update({"e_kp": e_kp, "e_nobs": e_nobs, "e_bad": views.u8(e_bad), "p_in_kf": in_kf})
+    out = dropin("fuse", blob, tmp_path)
+    pts = worldsim.gate_keyframe(f, wd, th, sim3=False, skip=wd["null"] | wd["bad"] | (in_kf >= 0), bf=worldsim.CAM[4])
+    inv_s2 = (np.float32(1.0) / (f["sf"] * f["sf"]).astype(np.float32)).astype(np.float32)
+    _, best, _ = orc.search_projected_best(KF, pts, inv_s2, 50)
+    M, E = 2500, 600
+    stereo_kp = KF.u_right >= 0 if KF.u_right is not None else np.zeros(2000, bool)
+    kf_mp = np.full(2000, -1, np.int64); kf_mp[e_kp] = 100000 + np.arange(E); kf_mp[in_kf[in_kf >= 0]] = np.nonzero(in_kf >= 0)[0]
+    p_bad = wd["bad"].copy(); p_idx = in_kf.copy(); p_nobs = wd["nobs"].copy(); p_repl = np.full(M, -1); eb = e_bad.copy(); e_repl = np.full(E, -1)
+    n = 0
+    for i in range(M):
+        if best[i] < 0 or p_bad[i] or p_idx[i] >= 0:
+            continue
+        slot = best[i]
+        cur = kf_mp[slot]
+        if cur >= 0:
+            cur_bad = eb[cur - 100000] if cur >= 100000 else p_bad[cur]
+            cur_nobs = e_nobs[cur - 100000] if cur >= 100000 else p_nobs[cur]
+            if not cur_bad:
+                if cur_nobs > p_nobs[i]:           # pMP->Replace(pMPinKF): pMP observes nothing yet
+                    p_bad[i] = True; p_repl[i] = cur
+                elif cur >= 100000:                # pMPinKF->Replace(pMP): scenario 'existing' points carry no observation map
+                    eb[cur - 100000] = True; e_repl[cur - 100000] = i
+                else:                              # a scenario point sitting in the keyframe hands its slot over
+                    p_bad[cur] = True; p_repl[cur] = i
+                    s = p_idx[cur]; p_idx[cur] = -1
+                    if s >= 0:
+                        kf_mp[s] = i; p_idx[i] = s; p_nobs[i] += 2 if stereo_kp[s] else 1
+        else:
+            p_idx[i] = slot; p_nobs[i] += 2 if stereo_kp[slot] else 1; kf_mp[slot] = i
+        n += 1
+    assert out["n"][0] == n and n > 100
+    assert np.array_equal(out["p_bad"] != 0, p_bad) and np.array_equal(out["p_repl"], p_repl)
+    assert np.array_equal(out["e_bad"] != 0, eb) and np.array_equal(out["e_repl"], e_repl)
+    assert np.array_equal(out["kf_mp"], kf_mp) and np.array_equal(out["p_idx"], p_idx) and np.array_equal(out["p_nobs"], p_nobs)
+
+
+def test_shim_algebra_matches_cv2(dropin, tmp_path):
+    """oracle/cvshim's cv::Mat products / norms (what the verbatim reference build computes its poses and
+    projections with) == the real OpenCV 4.13 (cv2.gemm, cv2.norm) bit for bit, and == the numpy restatement
+    tests/worldsim.py uses for the host-side gates."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(5)
+    n = 4000
+    R = rng.standard_normal((n, 3, 3)).astype(np.float32); x = (rng.standard_normal((n, 3)) * 9).astype(np.float32)
+    t = rng.standard_normal((n, 3)).astype(np.float32); T4 = rng.standard_normal((n, 4, 4)).astype(np.float32)
+    out = dropin("algebra", {"R": R.reshape(-1), "x": x.reshape(-1), "t": t.reshape(-1), "T4": T4.reshape(-1)}, tmp_path)
+    rxt = np.stack([cv2.gemm(R[i], x[i].reshape(3, 1), 1.0, t[i].reshape(3, 1), 1.0)[:, 0] for i in range(n)])
+    ow = np.stack([cv2.gemm(R[i], t[i].reshape(3, 1), -1.0, None, 0.0, flags=cv2.GEMM_1_T)[:, 0] for i in range(n)])
+    rr = np.stack([cv2.gemm(R[i], R[i], 1.0, None, 0.0) for i in range(n)]); tt = np.stack([cv2.gemm(T4[i], T4[i], 1.0, None, 0.0) for i in range(n)])
+    nrm = np.array([cv2.norm(x[i].reshape(3, 1)) for i in range(n)]).astype(np.float32)
+    assert np.array_equal(out["rxt"].reshape(n, 3), rxt) and np.array_equal(out["ow"].reshape(n, 3), ow)
+    assert np.array_equal(out["rr"].reshape(n, 3, 3), rr) and np.array_equal(out["tt"].reshape(n, 4, 4), tt)
+    assert np.array_equal(out["norm"], nrm)
+    for i in range(0, n, 40):   # the numpy restatement of the gates
+        assert np.array_equal(worldsim.mul_row_add(R[i], x[i:i + 1], t[i])[0], rxt[i])
+        assert np.array_equal(worldsim.camera_centre(R[i], t[i]), ow[i])
+    assert np.array_equal(worldsim.norm3(x), nrm)

@@ -1,7 +1,7 @@
 """TEST INFRASTRUCTURE.  World-frame scenarios for the ORBmatcher methods whose host side projects
 MapPoints itself (reference src/ORBmatcher.cc:311-427, 903-1207, 1212-1455, 1622-1759), and a numpy
 float32 restatement of those host-side gates.  The restatement follows the reference expression by
-expression (cv::Mat products of CV_32F data accumulate in double, everything else is float), so
+expression (plain 3x3 * 3x1 cv::Mat products in float, transposed products and norms in double), so
 that the projected view it produces can be handed to the oracle and compared with what the C++
 drop-in class (include/ORBmatcher.h) computes from the same MapPoints."""
 import numpy as np
@@ -19,11 +19,17 @@ def _rodrigues(w):
     return np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * (K @ K)
 
 
-def mul_row_add(R, x, t):
-    """R * x + t on CV_32F data: cv::gemm accumulates the float products in double."""
-    R = R.astype(F64); x64 = x.astype(F64); t = t.astype(F64)
-    cols = [(((R[r, 0] * x64[:, 0] + R[r, 1] * x64[:, 1]) + R[r, 2] * x64[:, 2]) + t[r]).astype(F32) for r in range(3)]
+def mul_row(R, x):
+    """R * x on CV_32F data, 3x3 * 3x1 without transpose flags: cv::gemm's unrolled path, float products
+    summed left to right in float (probed against cv2 4.13, tests/test_oracle_primitives.py)."""
+    R = R.astype(F32); x = x.astype(F32)
+    cols = [((R[r, 0] * x[:, 0] + R[r, 1] * x[:, 1]).astype(F32) + R[r, 2] * x[:, 2]).astype(F32) for r in range(3)]
     return np.stack(cols, 1)
+
+
+def mul_row_add(R, x, t):
+    """R * x + t: the product above, then one float add."""
+    return (mul_row(R, x) + t.astype(F32)[None, :]).astype(F32)
 
 
 def camera_centre(R, t):
@@ -170,6 +176,5 @@ def sim3_matrices(s12, R12, t12):
     s12 = F32(s12); R12 = R12.astype(F32); t12 = t12.astype(F32)
     sR12 = (s12 * R12).astype(F32)
     sR21 = (F32(1.0 / F64(s12)) * R12.T).astype(F32)
-    a, t = sR21.astype(F64), t12.astype(F64)
-    t21 = np.array([-((a[r, 0] * t[0] + a[r, 1] * t[1]) + a[r, 2] * t[2]) for r in range(3)]).astype(F32)
+    t21 = (-mul_row(sR21, t12[None, :])[0]).astype(F32)      # -sR21 * t12: plain product, float
     return sR12, sR21, t21

@@ -314,6 +314,31 @@ int orb_search_for_initialization(orb_matcher* m, const orb_frame_view* f1, cons
                                   const float* prev_matched_x, const float* prev_matched_y, int window_size,
                                   float nn_ratio, int check_orientation, int32_t* match12, int32_t* nmatches);
 
+/* ---- Bag of words: Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:439-449, src/KeyFrame.cc:60-71) ----
+ * mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4) is, per descriptor, the tree descent of
+ * DBoW2::TemplatedVocabulary<FORB>::transform(feature, word_id, weight, nid, levelsup)
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1239-1283): at every node go to the child with the smallest
+ * Hamming distance (strict <: the first child wins ties) until a leaf; word_id = the leaf's word, node_id = the
+ * node passed at level L - levelsup (0 = root when that level is <= 0).  The std::map assembly of BowVector /
+ * FeatureVector from (word_id, node_id) and the word weights is host work (include/ORBVocabulary.h).
+ *
+ * A vocabulary is handed over as loadFromTextFile reads it (:1362-1450): node i (1 <= i < n_nodes, node 0 = root)
+ * has parent[i] < i, is_leaf[i] and a 32-byte descriptor desc[i*32 ..]; children keep file order; words are
+ * numbered in file order of the leaves.  max_features bounds n of the host entry point. */
+typedef struct orb_vocabulary orb_vocabulary;
+int orb_vocabulary_create(int levels, int n_nodes, const int32_t* parent, const uint8_t* is_leaf, const uint8_t* desc,
+                          int max_features, int device, orb_vocabulary** out);
+void orb_vocabulary_destroy(orb_vocabulary* v);
+int orb_vocabulary_info(const orb_vocabulary* v, int32_t* n_nodes, int32_t* n_words, int32_t* max_children);
+void* orb_vocabulary_stream(const orb_vocabulary* v);
+long long orb_vocabulary_launch_count(const orb_vocabulary* v);
+int orb_vocabulary_sync(orb_vocabulary* v);
+/* host buffers: desc n x 32 -> word_id[n], node_id[n] (synchronous) */
+int orb_bow_transform(orb_vocabulary* v, const uint8_t* desc, int n, int levelsup, int32_t* word_id, int32_t* node_id);
+/* device buffers (16-byte aligned descriptors, e.g. an extractor's d_desc), asynchronous on the vocabulary's stream */
+int orb_bow_transform_device(orb_vocabulary* v, const uint8_t* d_desc, int n, int levelsup, int32_t* d_word_id,
+                             int32_t* d_node_id);
+
 #ifdef __cplusplus
 }
 #endif

@@ -34,6 +34,7 @@
 #include "KeyFrameDatabase.h"
 #undef private
 #undef protected
+#include "Converter.h"
 #include "../tests/cpp/blobio.h"
 
 using namespace ORB_SLAM2;
@@ -133,6 +134,7 @@ static void PutMatch(BlobWriter& w, int n, const std::vector<int>& match) { w.pu
 static int RunStereo(const Blob& b, BlobWriter& w);
 static int RunGrid(const Blob& b, BlobWriter& w);
 static int RunAlgebra(const Blob& b, BlobWriter& w);
+static int RunBowTransform(const Blob& b, BlobWriter& w, const char* vocfile);
 
 int main(int argc, char** argv) {
     if (argc < 4) { fprintf(stderr, "usage: ref_match_driver <mode> <in> <out>\n"); return 2; }
@@ -144,6 +146,7 @@ int main(int argc, char** argv) {
         if (mode == "stereo") return RunStereo(b, w);
         if (mode == "grid") return RunGrid(b, w);
         if (mode == "algebra") return RunAlgebra(b, w);
+        if (mode == "bowtransform") return RunBowTransform(b, w, argc > 4 ? argv[4] : "");
         if (mode == "mappoints") {
             Frame F; LoadFrame(b, "f_", F);
             KeyFrame* ref = new KeyFrame(F, &g_map, g_db);
@@ -406,5 +409,40 @@ static int RunAlgebra(const Blob& b, BlobWriter& w) {
     }
     w.put("rxt", "f4", rxt.data(), rxt.size()); w.put("ow", "f4", ow.data(), ow.size()); w.put("norm", "f4", nrm.data(), nrm.size());
     w.put("rr", "f4", rr.data(), rr.size()); w.put("tt", "f4", tt.data(), tt.size()); w.put("dot", "f4", dt.data(), dt.size());
+    return 0;
+}
+
+// Frame::ComputeBoW (src/Frame.cc:439-449): ORBVocabulary::loadFromTextFile + transform(vCurrentDesc, mBowVec, mFeatVec, levelsup),
+// all the reference's own DBoW2.  Doubles are written as raw bytes ("u1").
+static int RunBowTransform(const Blob& b, BlobWriter& w, const char* vocfile) {
+    ORBVocabulary voc;
+    if (!voc.loadFromTextFile(vocfile)) throw std::runtime_error("vocabulary load failed");
+    Frame F;
+    F.mpORBvocabulary = &voc;
+    F.N = (int)b.count("desc") / 32;
+    F.mDescriptors.create(F.N, 32, CV_8U);
+    std::memcpy(F.mDescriptors.data, b.get<unsigned char>("desc"), (size_t)F.N * 32);
+    const int levelsup = b.get<int>("levelsup")[0];
+    if (levelsup == 4) F.ComputeBoW();            // the reference's call, levelsup hard-wired to 4 (:448)
+    else voc.transform(Converter::toDescriptorVector(F.mDescriptors), F.mBowVec, F.mFeatVec, levelsup);
+    std::vector<unsigned> bw_ids, fv_ids, fv_items; std::vector<double> bw_vals; std::vector<int> fv_start(1, 0);
+    for (DBoW2::BowVector::const_iterator it = F.mBowVec.begin(); it != F.mBowVec.end(); ++it) { bw_ids.push_back(it->first); bw_vals.push_back(it->second); }
+    for (DBoW2::FeatureVector::const_iterator it = F.mFeatVec.begin(); it != F.mFeatVec.end(); ++it) {
+        fv_ids.push_back(it->first);
+        for (size_t k = 0; k < it->second.size(); ++k) fv_items.push_back(it->second[k]);
+        fv_start.push_back((int)fv_items.size());
+    }
+    w.put("bow_ids", "u4", bw_ids.data(), bw_ids.size()); w.put("bow_vals", "u1", bw_vals.data(), bw_vals.size() * 8);
+    w.put("fv_ids", "u4", fv_ids.data(), fv_ids.size()); w.put("fv_start", "i4", fv_start.data(), fv_start.size()); w.put("fv_items", "u4", fv_items.data(), fv_items.size());
+    // per-feature descent
+    std::vector<int> word(F.N), node(F.N); std::vector<double> weight(F.N);
+    for (int i = 0; i < F.N; ++i) {
+        DBoW2::WordId id; DBoW2::NodeId nid = 0; DBoW2::WordValue wv;
+        voc.transform(F.mDescriptors.row(i), id, wv, &nid, levelsup);
+        word[i] = (int)id; node[i] = (int)nid; weight[i] = wv;
+    }
+    w.put("word", "i4", word.data(), word.size()); w.put("node", "i4", node.data(), node.size()); w.put("weight", "u1", weight.data(), weight.size() * 8);
+    const int info[2] = {(int)voc.size(), (int)voc.getDepthLevels()};
+    w.put("info", "i4", info, 2);
     return 0;
 }

@@ -242,3 +242,54 @@ def make_initialization_scenario(n1=2000, n2=2000, idx=0, coarse_desc=False):
     if not coarse_desc:
         a["desc"][dup] = perturb_descriptors(rng, a["desc"][srcs], 0.02)
     return a, b, a["x"].copy(), a["y"].copy()
+
+
+def make_vocabulary(k=10, L=3, seed=0, ragged=True, stop_frac=0.02):
+    """A synthetic DBoW2 vocabulary tree in loadFromTextFile's node order (depth-first, as createTree /
+    saveToTextFile emit it): each node's descriptor is its parent's with ~1/8 of the bits re-drawn, so
+    descents are decisive near the root and tie-prone near the leaves; `ragged` drops children of some
+    nodes (k-means clusters can come out empty); a few words get weight 0 (stopped words)."""
+    rng = np.random.default_rng(0x5EED0000 + 0xB0000 + seed)
+    parent, leaf, desc, weight = [0], [0], [np.zeros(32, np.uint8)], [0.0]
+
+    def grow(pid, pdesc, level):
+        nk = k if not ragged or level == 1 else int(rng.integers(max(2, k - 4), k + 1))
+        for _ in range(nk):
+            mask = np.packbits(rng.random(256) < (0.5 if level == 1 else 0.125))
+            d = (pdesc & ~mask) | (rng.integers(0, 256, 32).astype(np.uint8) & mask)
+            nid = len(parent)
+            is_leaf = level == L
+            parent.append(pid); leaf.append(int(is_leaf)); desc.append(d)
+            weight.append(0.0 if not is_leaf else (0.0 if rng.random() < stop_frac else float(rng.uniform(0.5, 12.0))))
+            if not is_leaf:
+                grow(nid, d, level + 1)
+
+    grow(0, np.zeros(32, np.uint8), 1)
+    return dict(k=k, L=L, scoring=0, weighting=0, parent=np.array(parent, np.int32), is_leaf=np.array(leaf, np.uint8),
+                desc=np.stack(desc), weight=np.array(weight, np.float64))
+
+
+def write_text_vocabulary(path, voc):
+    """ORBvoc.txt layout (TemplatedVocabulary.h:1452-1480 saveToTextFile).  No newline after the last node:
+    loadFromTextFile's `while(!f.eof())` loop (:1402) would read one more, empty, line and append a node
+    with unspecified fields under the root."""
+    lines = ["%d %d %d %d" % (voc["k"], voc["L"], voc["scoring"], voc["weighting"])]
+    for i in range(1, len(voc["parent"])):
+        lines.append("%d %d %s %.17g" % (voc["parent"][i], voc["is_leaf"][i], " ".join(str(int(b)) for b in voc["desc"][i]), voc["weight"][i]))
+    with open(path, "w") as f:
+        f.write("\n".join(lines))
+
+
+def vocabulary_queries(voc, n, seed=0, tie_frac=0.1):
+    """Descriptors to transform: noisy copies of random leaves, plus some exact copies of INNER nodes' parents
+    (equidistant children: exercises the first-child-wins tie rule)."""
+    rng = np.random.default_rng(0x5EED0000 + 0xB1000 + seed)
+    leaves = np.nonzero(voc["is_leaf"])[0]
+    src = voc["desc"][rng.choice(leaves, n)]
+    q = perturb_descriptors(rng, src)
+    inner = np.nonzero(voc["is_leaf"] == 0)[0][1:]
+    nt = int(n * tie_frac)
+    if len(inner) and nt:
+        q[:nt] = voc["desc"][rng.choice(inner, nt)]
+    q[nt:nt + max(1, n // 50)] = rng.integers(0, 2, (max(1, n // 50), 1)).astype(np.uint8) * 255   # all-zero / all-one rows
+    return q

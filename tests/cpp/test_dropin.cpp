@@ -12,6 +12,7 @@
 
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
+#include "ORBVocabulary.h"
 #include "blobio.h"
 
 struct Frame;
@@ -329,6 +330,28 @@ int main(int argc, char** argv) {
             std::vector<int> match(A.N, -1);
             for (int i = 0; i < A.N; ++i) if (out[i]) match[i] = out[i]->id;
             w.put("n", "i4", &n, 1); w.put("match", "i4", match.data(), match.size());
+        } else if (mode == "bowtransform") {
+            // Frame::ComputeBoW (src/Frame.cc:439-449): mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4)
+            ORB_SLAM2::ORBVocabulary voc;
+            if (argc < 5 || !voc.loadFromTextFile(argv[4])) throw std::runtime_error("vocabulary load failed");
+            const int N = (int)b.count("desc") / 32;
+            cv::Mat descriptors(N, 32, CV_8U);
+            std::memcpy(descriptors.data, b.get<unsigned char>("desc"), (size_t)N * 32);
+            std::vector<cv::Mat> vCurrentDesc;                       // Converter::toDescriptorVector (src/Converter.cc:27-35)
+            for (int j = 0; j < N; ++j) vCurrentDesc.push_back(descriptors.row(j));
+            DBoW2::BowVector bv; DBoW2::FeatureVector fv;
+            voc.transform(vCurrentDesc, bv, fv, b.get<int>("levelsup")[0]);
+            std::vector<unsigned> bw_ids, fv_ids, fv_items; std::vector<double> bw_vals; std::vector<int> fv_start(1, 0);
+            for (DBoW2::BowVector::const_iterator it = bv.begin(); it != bv.end(); ++it) { bw_ids.push_back(it->first); bw_vals.push_back(it->second); }
+            for (DBoW2::FeatureVector::const_iterator it = fv.begin(); it != fv.end(); ++it) {
+                fv_ids.push_back(it->first);
+                for (size_t k = 0; k < it->second.size(); ++k) fv_items.push_back(it->second[k]);
+                fv_start.push_back((int)fv_items.size());
+            }
+            w.put("bow_ids", "u4", bw_ids.data(), bw_ids.size()); w.put("bow_vals", "u1", bw_vals.data(), bw_vals.size() * 8);
+            w.put("fv_ids", "u4", fv_ids.data(), fv_ids.size()); w.put("fv_start", "i4", fv_start.data(), fv_start.size()); w.put("fv_items", "u4", fv_items.data(), fv_items.size());
+            const int info[2] = {(int)voc.size(), voc.getDepthLevels()};
+            w.put("info", "i4", info, 2);
         } else {
             fprintf(stderr, "unknown mode %s\n", mode.c_str());
             return 2;

@@ -372,3 +372,14 @@ def stereo_match_ref(rL, rR, kpL, dL, kpR, dR, sf, inv_sf, mbf, min_d, max_d):
     kept = lib.orc_stereo_match_levels(n, pl, lw, lh, ls, pr, rw, rh, rs, _p(kpL), _p(dL), nL, _p(kpR), _p(dR), nR, _p(sf), _p(inv_sf),
                                        mbf, min_d, max_d, _p(ur), _p(dp), _p(sad))
     return ur[:nL], dp[:nL], sad[:nL], kept
+
+
+def bow_transform(voc, desc, levelsup=4):
+    """Vocabulary-tree descent of DBoW2 transform (oracle/bow_oracle.cpp): (word ids, node ids)."""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); n = len(desc)
+    parent = np.ascontiguousarray(voc["parent"], np.int32); leaf = np.ascontiguousarray(voc["is_leaf"], np.uint8); nd = np.ascontiguousarray(voc["desc"], np.uint8)
+    word = np.empty(max(n, 1), np.int32); node = np.empty(max(n, 1), np.int32)
+    lib.orc_bow_transform.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    lib.orc_bow_transform.restype = None
+    lib.orc_bow_transform(int(voc["L"]), len(parent), _p(parent), _p(leaf), _p(nd), _p(desc), n, int(levelsup), _p(word), _p(node))
+    return word[:n], node[:n]

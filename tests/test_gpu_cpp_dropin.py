@@ -26,10 +26,10 @@ def dropin():
     subprocess.check_call(["make", "-s", "-C", os.path.join(HERE, "cpp")])
     assert os.path.exists(BIN)
 
-    def run(mode, arrays, tmp_path):
+    def run(mode, arrays, tmp_path, *extra):
         fin, fout = str(tmp_path / (mode + ".in")), str(tmp_path / (mode + ".out"))
         cppio.write(fin, arrays)
-        r = subprocess.run([BIN, mode, fin, fout], capture_output=True, text=True, timeout=300)
+        r = subprocess.run([BIN, mode, fin, fout] + list(extra), capture_output=True, text=True, timeout=300)
         assert r.returncode == 0, r.stderr
         return cppio.read(fout)
     return run
@@ -307,3 +307,21 @@ def test_search_by_sim3(dropin, tmp_path, idx, s12):
     assert out["n"][0] == n_o
     assert np.array_equal(out["match"], np.where(m_o >= 0, m_o, pre))
     assert n_o > 200
+
+
+@pytest.mark.parametrize("k,L,levelsup,seed", [(10, 3, 1, 0), (10, 4, 4, 1), (6, 5, 4, 2)])
+def test_orbvocabulary_transform(dropin, tmp_path, k, L, levelsup, seed):
+    """include/ORBVocabulary.h: loadFromTextFile + transform(features, BowVector, FeatureVector, levelsup) as Frame::ComputeBoW calls it."""
+    bow = importlib.import_module("orb_slam2-chinese-annotation_b200.bow")
+    voc = synth.make_vocabulary(k, L, seed)
+    vf = str(tmp_path / "voc.txt")
+    synth.write_text_vocabulary(vf, voc)
+    q = synth.vocabulary_queries(voc, 2000, seed)
+    out = dropin("bowtransform", {"desc": q.reshape(-1), "levelsup": np.array([levelsup], np.int32)}, tmp_path, vf)
+    word, node = orc.bow_transform(voc, q, levelsup)
+    leaves = np.nonzero(voc["is_leaf"])[0]
+    ids, vals, fv = bow.assemble(word, node, voc["weight"][leaves], voc["weighting"], voc["scoring"])
+    assert out["info"][0] == len(leaves) and out["info"][1] == L
+    assert np.array_equal(out["bow_ids"], ids) and np.array_equal(out["bow_vals"].view(np.float64), vals)
+    assert np.array_equal(out["fv_ids"], fv.node_ids) and np.array_equal(out["fv_start"], fv.start) and np.array_equal(out["fv_items"], fv.items)
+    assert len(ids) > 100

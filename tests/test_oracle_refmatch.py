@@ -32,10 +32,10 @@ def dropin():
     if not os.path.exists(BIN):
         pytest.skip("oracle/_ref/ref_match_driver not built (needs /root/reference)")
 
-    def run(mode, arrays, tmp_path):
+    def run(mode, arrays, tmp_path, *extra):
         fin, fout = str(tmp_path / (mode + ".in")), str(tmp_path / (mode + ".out"))
         cppio.write(fin, arrays)
-        r = subprocess.run([BIN, mode, fin, fout], capture_output=True, text=True, timeout=600, cwd=str(tmp_path))
+        r = subprocess.run([BIN, mode, fin, fout] + list(extra), capture_output=True, text=True, timeout=600, cwd=str(tmp_path))
         assert r.returncode == 0, r.stderr
         return cppio.read(fout)
     return run
@@ -52,6 +52,7 @@ test_relocalisation_search_by_projection = D.test_relocalisation_search_by_proje
 test_loop_search_by_projection = D.test_loop_search_by_projection
 test_fuse_sim3 = D.test_fuse_sim3
 test_search_by_sim3 = D.test_search_by_sim3
+test_orbvocabulary_transform = D.test_orbvocabulary_transform     # ORBVocabulary::loadFromTextFile + transform: the reference's DBoW2
 
 
 REFKP = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4")])
@@ -172,3 +173,37 @@ def test_shim_algebra_matches_cv2(dropin, tmp_path):
         assert np.array_equal(worldsim.mul_row_add(R[i], x[i:i + 1], t[i])[0], rxt[i])
         assert np.array_equal(worldsim.camera_centre(R[i], t[i]), ow[i])
     assert np.array_equal(worldsim.norm3(x), nrm)
+
+
+bow = importlib.import_module("orb_slam2-chinese-annotation_b200.bow")
+
+
+@pytest.mark.parametrize("k,L,levelsup,seed,ragged", [(10, 3, 1, 0, True), (10, 4, 2, 1, False), (6, 5, 4, 2, True), (10, 3, 4, 3, True)])
+def test_bow_transform_vs_reference_dbow2(dropin, tmp_path, k, L, levelsup, seed, ragged):
+    """Frame::ComputeBoW through the reference's own DBoW2 (loadFromTextFile + transform, verbatim) == the oracle's
+    tree descent + the host assembly of BowVector / FeatureVector (orb_slam2-chinese-annotation_b200/bow.py), doubles bit-equal."""
+    voc = synth.make_vocabulary(k, L, seed, ragged=ragged)
+    vf = str(tmp_path / "voc.txt")
+    synth.write_text_vocabulary(vf, voc)
+    parsed = bow.parse_text_vocabulary(vf)
+    for key in ("parent", "is_leaf", "desc", "weight"):
+        assert np.array_equal(parsed[key], voc[key]), key
+    q = synth.vocabulary_queries(voc, 2000, seed)
+    fin, fout = str(tmp_path / "bt.in"), str(tmp_path / "bt.out")
+    cppio.write(fin, {"desc": q.reshape(-1), "levelsup": np.array([levelsup], np.int32)})
+    r = subprocess.run([BIN, "bowtransform", fin, fout, vf], capture_output=True, text=True, timeout=600, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stderr
+    out = cppio.read(fout)
+    word, node = orc.bow_transform(voc, q, levelsup)
+    assert out["info"][0] == voc["is_leaf"].sum() and out["info"][1] == L
+    assert np.array_equal(out["word"], word) and np.array_equal(out["node"], node)
+    leaves = np.nonzero(voc["is_leaf"])[0]
+    assert np.array_equal(out["weight"].view(np.float64), voc["weight"][leaves][word])
+    ids, vals, fv = bow.assemble(word, node, voc["weight"][leaves], voc["weighting"], voc["scoring"])
+    assert np.array_equal(out["bow_ids"], ids) and np.array_equal(out["bow_vals"].view(np.float64), vals)
+    assert np.array_equal(out["fv_ids"], fv.node_ids) and np.array_equal(out["fv_start"], fv.start) and np.array_equal(out["fv_items"], fv.items)
+    assert len(ids) > 100 and abs(vals.sum() - 1.0) < 1e-9
+    if levelsup < L:
+        assert len(fv.node_ids) > 5
+    else:
+        assert list(fv.node_ids) == [0]          # L - levelsup <= 0: every feature files under the root

@@ -314,6 +314,24 @@ int orb_search_for_initialization(orb_matcher* m, const orb_frame_view* f1, cons
                                   const float* prev_matched_x, const float* prev_matched_y, int window_size,
                                   float nn_ratio, int check_orientation, int32_t* match12, int32_t* nmatches);
 
+/* Frame::isInFrustum (src/Frame.cc:303-366) for n MapPoints at once, as Tracking::SearchLocalPoints calls it per
+ * point (src/Tracking.cc:1012-1036) before SearchByProjection(Frame, MapPoints).  rcw / tcw / ow = the Frame's
+ * mRcw (row-major 3x3), mtcw, mOw; bounds = mnMinX..mnMaxY (the inverse cell sizes are not read).  Per point:
+ * world position, normal, mfMinDistance / mfMaxDistance (the 0.8 / 1.2 invariance factors are applied here).
+ * Outputs: in_view = mbTrackInView, u / v / ur = mTrackProjX / mTrackProjY / mTrackProjXR, view_cos = mTrackViewCos,
+ * dist = |P - Ow| for MapPoint::PredictScale (a logf the caller evaluates: mnTrackScaleLevel).  For points that
+ * fail a gate the values computed up to that gate are returned and in_view = 0. */
+int orb_is_in_frustum(orb_matcher* m, const float* rcw, const float* tcw, const float* ow, const orb_camera* cam,
+                      const orb_grid_params* bounds, float viewing_cos_limit, int n, const float* xw, const float* normal,
+                      const float* min_distance, const float* max_distance, uint8_t* in_view, float* u, float* v, float* ur,
+                      float* view_cos, float* dist);
+
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:250-326) for n_points MapPoints: point p owns the
+ * descriptors desc[start[p] .. start[p+1]) of its observations, in the order the reference gathers them (:262-268);
+ * best_idx[p] = the observation whose median distance to the others is smallest (median = element
+ * int(0.5*(N-1)) of the sorted row, first row wins ties), -1 for a point without observations. */
+int orb_distinctive_descriptors(orb_matcher* m, int n_points, const int32_t* start, const uint8_t* desc, int32_t* best_idx);
+
 /* ---- Bag of words: Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:439-449, src/KeyFrame.cc:60-71) ----
  * mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4) is, per descriptor, the tree descent of
  * DBoW2::TemplatedVocabulary<FORB>::transform(feature, word_id, weight, nid, levelsup)

@@ -636,3 +636,54 @@ int orc_search_for_initialization(const orb_frame_view* f1, const orb_frame_view
     return nmatches;
 }
 }  // extern "C"
+
+/* Frame::isInFrustum (src/Frame.cc:303-366) without the PredictScale step (dist is returned for it).  cv::Mat algebra as
+ * OpenCV 4.13 evaluates it (R*P+t: float, left to right; norm / dot: double); scalar float expressions with the fused
+ * operations GCC emits for the reference's -O3 -march=native build, written out (this file is built with -ffp-contract=off).
+ * Pinned against the verbatim reference build: tests/test_oracle_refmatch.py::test_is_in_frustum. */
+extern "C" void orc_is_in_frustum(const float* R, const float* t, const float* Ow, const orb_camera* cam, const orb_grid_params* b, float cos_limit, int n,
+                                  const float* xw, const float* nrm, const float* mind, const float* maxd, uint8_t* in_view, float* u_out, float* v_out,
+                                  float* ur_out, float* cos_out, float* dist_out) {
+    for (int i = 0; i < n; ++i) {
+        const float X = xw[3 * i], Y = xw[3 * i + 1], Z = xw[3 * i + 2];
+        float u = 0.f, v = 0.f, ur = 0.f, vc = 0.f, dist = 0.f; uint8_t ok = 0;
+        const float pcx = ((R[0] * X + R[1] * Y) + R[2] * Z) + t[0];
+        const float pcy = ((R[3] * X + R[4] * Y) + R[5] * Z) + t[1];
+        const float pcz = ((R[6] * X + R[7] * Y) + R[8] * Z) + t[2];
+        do {
+            if (pcz < 0.0f) break;
+            const float invz = 1.0f / pcz;
+            u = fmaf(cam->fx * pcx, invz, cam->cx);
+            v = fmaf(cam->fy * pcy, invz, cam->cy);
+            if (u < b->min_x || u > b->max_x) break;
+            if (v < b->min_y || v > b->max_y) break;
+            const float px = X - Ow[0], py = Y - Ow[1], pz = Z - Ow[2];
+            dist = (float)std::sqrt(((double)px * px + (double)py * py) + (double)pz * pz);
+            if (dist < 0.8f * mind[i] || dist > 1.2f * maxd[i]) break;
+            const double dot = ((double)px * nrm[3 * i] + (double)py * nrm[3 * i + 1]) + (double)pz * nrm[3 * i + 2];
+            vc = (float)(dot / (double)dist);
+            if (vc < cos_limit) break;
+            ok = 1;
+            ur = fmaf(-cam->mbf, invz, u);
+        } while (0);
+        in_view[i] = ok; u_out[i] = u; v_out[i] = v; ur_out[i] = ur; cos_out[i] = vc; dist_out[i] = dist;
+    }
+}
+
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:270-320) on gathered descriptor rows. */
+extern "C" void orc_distinctive_descriptors(int n_points, const int32_t* start, const uint8_t* desc, int32_t* best_idx) {
+    for (int p = 0; p < n_points; ++p) {
+        const int s = start[p], N = start[p + 1] - s;
+        int BestMedian = INT_MAX, BestIdx = -1;
+        std::vector<std::vector<int>> D(N, std::vector<int>(N, 0));
+        for (int i = 0; i < N; ++i)
+            for (int j = i + 1; j < N; ++j) D[i][j] = D[j][i] = ddist(desc + (size_t)(s + i) * 32, desc + (size_t)(s + j) * 32);
+        for (int i = 0; i < N; ++i) {
+            std::vector<int> vDists(D[i]);
+            std::sort(vDists.begin(), vDists.end());
+            const int median = vDists[0.5 * (N - 1)];
+            if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+        }
+        best_idx[p] = BestIdx;
+    }
+}

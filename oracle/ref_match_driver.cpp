@@ -134,6 +134,8 @@ static void PutMatch(BlobWriter& w, int n, const std::vector<int>& match) { w.pu
 static int RunStereo(const Blob& b, BlobWriter& w);
 static int RunGrid(const Blob& b, BlobWriter& w);
 static int RunAlgebra(const Blob& b, BlobWriter& w);
+static int RunFrustum(const Blob& b, BlobWriter& w);
+static int RunDistinctive(const Blob& b, BlobWriter& w);
 static int RunBowTransform(const Blob& b, BlobWriter& w, const char* vocfile);
 
 int main(int argc, char** argv) {
@@ -146,6 +148,8 @@ int main(int argc, char** argv) {
         if (mode == "stereo") return RunStereo(b, w);
         if (mode == "grid") return RunGrid(b, w);
         if (mode == "algebra") return RunAlgebra(b, w);
+        if (mode == "frustum") return RunFrustum(b, w);
+        if (mode == "distinctive") return RunDistinctive(b, w);
         if (mode == "bowtransform") return RunBowTransform(b, w, argc > 4 ? argv[4] : "");
         if (mode == "mappoints") {
             Frame F; LoadFrame(b, "f_", F);
@@ -444,5 +448,64 @@ static int RunBowTransform(const Blob& b, BlobWriter& w, const char* vocfile) {
     w.put("word", "i4", word.data(), word.size()); w.put("node", "i4", node.data(), node.size()); w.put("weight", "u1", weight.data(), weight.size() * 8);
     const int info[2] = {(int)voc.size(), (int)voc.getDepthLevels()};
     w.put("info", "i4", info, 2);
+    return 0;
+}
+
+// Frame::isInFrustum (src/Frame.cc:303-366) per MapPoint of a world scenario, as Tracking::SearchLocalPoints drives it.
+static int RunFrustum(const Blob& b, BlobWriter& w) {
+    Frame F; LoadFrame(b, "f_", F);
+    SetCamera(F, b.get<float>("cam"));
+    F.SetPose(Mat44(b.get<float>("pose")));
+    KeyFrame* K = new KeyFrame(F, &g_map, g_db);
+    std::vector<MapPoint*> all, pts; LoadPoints(b, "p_", K, all, pts);
+    const int M = (int)all.size();
+    const float lim = b.get<float>("cos_limit")[0];
+    std::vector<unsigned char> ok(M); std::vector<float> u(M), v(M), ur(M), vc(M); std::vector<int> lvl(M);
+    for (int i = 0; i < M; ++i) {
+        MapPoint* m = all[i];
+        m->mTrackProjX = m->mTrackProjY = m->mTrackProjXR = m->mTrackViewCos = 0.f; m->mnTrackScaleLevel = -1;
+        ok[i] = F.isInFrustum(m, lim) ? 1 : 0;
+        if (ok[i] != (m->mbTrackInView ? 1 : 0)) throw std::runtime_error("mbTrackInView differs from the return value");
+        u[i] = m->mTrackProjX; v[i] = m->mTrackProjY; ur[i] = m->mTrackProjXR; vc[i] = m->mTrackViewCos; lvl[i] = m->mnTrackScaleLevel;
+    }
+    cv::Mat Ow = F.GetCameraCenter();
+    float pose[15];
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) pose[3 * r + c] = F.mRcw.at<float>(r, c); pose[9 + r] = F.mtcw.at<float>(r); pose[12 + r] = Ow.at<float>(r); }
+    w.put("in_view", "u1", ok.data(), M); w.put("u", "f4", u.data(), M); w.put("v", "f4", v.data(), M); w.put("ur", "f4", ur.data(), M);
+    w.put("view_cos", "f4", vc.data(), M); w.put("level", "i4", lvl.data(), M); w.put("rt_ow", "f4", pose, 15);
+    return 0;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:250-326): KeyFrames holding descriptor rows, MapPoints observing
+// (keyframe, row) pairs.  The reference gathers the rows in std::map<KeyFrame*, size_t> order, i.e. by KeyFrame ADDRESS; the rows
+// are written back in the order the reference saw them, with the descriptor it chose.
+static int RunDistinctive(const Blob& b, BlobWriter& w) {
+    const int nkf = b.get<int>("dims")[0], rows = b.get<int>("dims")[1], P = (int)b.count("start") - 1;
+    Frame F; LoadFrame(b, "f_", F);
+    std::vector<KeyFrame*> kfs(nkf);
+    for (int k = 0; k < nkf; ++k) {
+        Frame S(F);
+        S.N = rows; S.mvKeys.assign(rows, cv::KeyPoint()); S.mvKeysUn.assign(rows, cv::KeyPoint()); S.mvuRight.assign(rows, -1.f); S.mvDepth.assign(rows, -1.f);
+        S.mDescriptors.create(rows, 32, CV_8U); std::memcpy(S.mDescriptors.data, b.get<unsigned char>("kf_desc") + (size_t)k * rows * 32, (size_t)rows * 32);
+        S.mvpMapPoints.assign(rows, (MapPoint*)NULL); S.mvbOutlier.assign(rows, false);
+        for (int i = 0; i < FRAME_GRID_COLS; ++i) for (int j = 0; j < FRAME_GRID_ROWS; ++j) S.mGrid[i][j].clear();
+        kfs[k] = new KeyFrame(S, &g_map, g_db);
+    }
+    const int* start = b.get<int>("start"); const int* okf = b.get<int>("obs_kf"); const int* orow = b.get<int>("obs_row");
+    std::vector<unsigned char> gathered, chosen((size_t)P * 32, 0); std::vector<int> gstart(1, 0);
+    for (int p = 0; p < P; ++p) {
+        MapPoint* m = NewPoint(NULL, kfs[0]);
+        for (int q = start[p]; q < start[p + 1]; ++q) m->AddObservation(kfs[okf[q]], (size_t)orow[q]);
+        m->ComputeDistinctiveDescriptors();
+        const std::map<KeyFrame*, size_t> obs = m->GetObservations();
+        for (std::map<KeyFrame*, size_t>::const_iterator it = obs.begin(); it != obs.end(); ++it) {
+            const unsigned char* r = it->first->mDescriptors.ptr(it->second);
+            gathered.insert(gathered.end(), r, r + 32);
+        }
+        gstart.push_back((int)gathered.size() / 32);
+        cv::Mat d = m->GetDescriptor();
+        if (!d.empty()) std::memcpy(&chosen[(size_t)p * 32], d.data, 32);
+    }
+    w.put("g_start", "i4", gstart.data(), gstart.size()); w.put("g_desc", "u1", gathered.data(), gathered.size()); w.put("chosen", "u1", chosen.data(), chosen.size());
     return 0;
 }

@@ -27,7 +27,7 @@ EXPORTS = [
     "orb_search_for_triangulation", "orb_search_by_bow_keyframes", "orb_search_by_projection_claiming",
     "orb_search_projected_best", "orb_search_by_sim3", "orb_search_for_initialization", "orb_sincosf_sweep_device",
     "orb_vocabulary_create", "orb_vocabulary_destroy", "orb_vocabulary_info", "orb_vocabulary_stream", "orb_vocabulary_launch_count",
-    "orb_vocabulary_sync", "orb_bow_transform", "orb_bow_transform_device",
+    "orb_vocabulary_sync", "orb_bow_transform", "orb_bow_transform_device", "orb_is_in_frustum", "orb_distinctive_descriptors",
 ]
 
 

@@ -1258,3 +1258,147 @@ int orb_search_by_bow_keyframes(orb_matcher* m, const orb_frame_view* kf1, const
     return ORB_OK;
 }
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// Feeding SearchByProjection: Frame::isInFrustum over the local map (reference src/Frame.cc:303-366,
+// called per MapPoint from Tracking::SearchLocalPoints, src/Tracking.cc:1012-1036) and
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:250-326).
+namespace {
+
+// One thread per MapPoint.  Float sequence of the reference (cv::Mat algebra as OpenCV 4.13 evaluates
+// it: R*P+t in float left to right, norm and dot in double; scalar expressions as GCC contracts them
+// for the reference's -O3 -march=native build: fx*PcX*invz+cx -> fma(fx*PcX, invz, cx), u-mbf*invz ->
+// fma(-mbf, invz, u)).  PredictScale (a logf) stays with the caller; dist is returned for it.
+__global__ void k_is_in_frustum(int n, const float* __restrict__ xw, const float* __restrict__ nrm, const float* __restrict__ mind,
+                                const float* __restrict__ maxd, float r00, float r01, float r02, float r10, float r11, float r12, float r20,
+                                float r21, float r22, float t0, float t1, float t2, float o0, float o1, float o2, orb_camera cam,
+                                float min_x, float min_y, float max_x, float max_y, float cos_limit, uint8_t* __restrict__ in_view,
+                                float* __restrict__ u_out, float* __restrict__ v_out, float* __restrict__ ur_out, float* __restrict__ cos_out,
+                                float* __restrict__ dist_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float X = xw[3 * i], Y = xw[3 * i + 1], Z = xw[3 * i + 2];
+    uint8_t ok = 0;
+    float u = 0.f, v = 0.f, ur = 0.f, vc = 0.f, dist = 0.f;
+    const float pcx = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r00, X), __fmul_rn(r01, Y)), __fmul_rn(r02, Z)), t0);
+    const float pcy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r10, X), __fmul_rn(r11, Y)), __fmul_rn(r12, Z)), t1);
+    const float pcz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r20, X), __fmul_rn(r21, Y)), __fmul_rn(r22, Z)), t2);
+    if (!(pcz < 0.0f)) {
+        const float invz = __fdiv_rn(1.0f, pcz);
+        u = __fmaf_rn(__fmul_rn(cam.fx, pcx), invz, cam.cx);
+        v = __fmaf_rn(__fmul_rn(cam.fy, pcy), invz, cam.cy);
+        if (!(u < min_x || u > max_x) && !(v < min_y || v > max_y)) {
+            const float px = __fsub_rn(X, o0), py = __fsub_rn(Y, o1), pz = __fsub_rn(Z, o2);
+            dist = (float)sqrt(__dadd_rn(__dadd_rn(__dmul_rn((double)px, (double)px), __dmul_rn((double)py, (double)py)), __dmul_rn((double)pz, (double)pz)));
+            if (!(dist < __fmul_rn(0.8f, mind[i]) || dist > __fmul_rn(1.2f, maxd[i]))) {
+                const double dot = __dadd_rn(__dadd_rn(__dmul_rn((double)px, (double)nrm[3 * i]), __dmul_rn((double)py, (double)nrm[3 * i + 1])),
+                                             __dmul_rn((double)pz, (double)nrm[3 * i + 2]));
+                vc = (float)__ddiv_rn(dot, (double)dist);
+                if (!(vc < cos_limit)) {
+                    ok = 1;
+                    ur = __fmaf_rn(-cam.mbf, invz, u);
+                }
+            }
+        }
+    }
+    in_view[i] = ok; u_out[i] = u; v_out[i] = v; ur_out[i] = ur; cos_out[i] = vc; dist_out[i] = dist;
+}
+
+// One CTA per MapPoint: N x N Hamming distances of its observations' descriptors, the median of every row
+// (element int(0.5 * (N - 1)) of the sorted row, found from a 257-bin histogram), the row with the
+// smallest median (first wins).  One warp per row at a time.
+#define DD_THREADS 128
+__global__ void __launch_bounds__(DD_THREADS) k_distinctive(const int* __restrict__ start, const uint8_t* __restrict__ desc, int* __restrict__ best_idx) {
+    __shared__ int hist[DD_THREADS / 32][264];
+    __shared__ unsigned best[DD_THREADS / 32];
+    const int p = blockIdx.x, s = start[p], N = start[p + 1] - s;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned my_best = 0xffffffffu;                  // (median << 16) | row
+    const int kth = (int)(0.5 * (N - 1));
+    for (int i = warp; i < N; i += DD_THREADS / 32) {
+        for (int b = lane; b < 264; b += 32) hist[warp][b] = 0;
+        __syncwarp();
+        const uint4* pi = reinterpret_cast<const uint4*>(desc + (size_t)(s + i) * 32);
+        const uint4 a0 = __ldg(pi), a1 = __ldg(pi + 1);
+        for (int j = lane; j < N; j += 32) {
+            const uint4* pj = reinterpret_cast<const uint4*>(desc + (size_t)(s + j) * 32);
+            atomicAdd(&hist[warp][orb_hamming256(a0, a1, __ldg(pj), __ldg(pj + 1))], 1);
+        }
+        __syncwarp();
+        // lane l owns bins [8l, 8l + 8) (+ bin 256 on lane 31 via the 9th slot)
+        int c[9], tot = 0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) { c[b] = hist[warp][lane * 8 + b]; tot += c[b]; }
+        c[8] = lane == 31 ? hist[warp][256] : 0; tot += c[8];
+        int incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        int before = incl - tot, med = -1;
+#pragma unroll
+        for (int b = 0; b < 9; ++b) { if (med < 0 && kth < before + c[b]) med = (b == 8 ? 256 : lane * 8 + b); before += c[b]; }
+        const unsigned found = __ballot_sync(0xffffffffu, med >= 0);
+        const int m = __shfl_sync(0xffffffffu, med, __ffs(found) - 1);
+        my_best = min(my_best, ((unsigned)m << 16) | (unsigned)i);
+        __syncwarp();
+    }
+    if (lane == 0) best[warp] = my_best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned b = best[0];
+        for (int w = 1; w < DD_THREADS / 32; ++w) b = min(b, best[w]);
+        best_idx[p] = N > 0 ? (int)(b & 0xffffu) : -1;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int orb_is_in_frustum(orb_matcher* m, const float* rcw, const float* tcw, const float* ow, const orb_camera* cam, const orb_grid_params* bounds,
+                      float viewing_cos_limit, int n, const float* xw, const float* normal, const float* min_distance, const float* max_distance,
+                      uint8_t* in_view, float* u, float* v, float* ur, float* view_cos, float* dist) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!rcw || !tcw || !ow || !cam || !bounds || n < 0 || (n > 0 && (!xw || !normal || !min_distance || !max_distance || !in_view || !u || !v || !ur || !view_cos || !dist)))
+        return ORB_ERR_BAD_ARG;
+    if (n == 0) return ORB_OK;
+    const float *dx, *dn, *dmin, *dmax; float *du, *dv, *dur, *dc, *dd; uint8_t* dok;
+    if ((st = ws_upload(m, &dx, xw, (size_t)n * 3)) != ORB_OK || (st = ws_upload(m, &dn, normal, (size_t)n * 3)) != ORB_OK ||
+        (st = ws_upload(m, &dmin, min_distance, n)) != ORB_OK || (st = ws_upload(m, &dmax, max_distance, n)) != ORB_OK ||
+        (st = ws_alloc(m, &du, n)) != ORB_OK || (st = ws_alloc(m, &dv, n)) != ORB_OK || (st = ws_alloc(m, &dur, n)) != ORB_OK ||
+        (st = ws_alloc(m, &dc, n)) != ORB_OK || (st = ws_alloc(m, &dd, n)) != ORB_OK || (st = ws_alloc(m, &dok, n)) != ORB_OK) return st;
+    k_is_in_frustum<<<(n + 255) / 256, 256, 0, m->stream>>>(n, dx, dn, dmin, dmax, rcw[0], rcw[1], rcw[2], rcw[3], rcw[4], rcw[5], rcw[6], rcw[7], rcw[8],
+                                                            tcw[0], tcw[1], tcw[2], ow[0], ow[1], ow[2], *cam, bounds->min_x, bounds->min_y, bounds->max_x,
+                                                            bounds->max_y, viewing_cos_limit, dok, du, dv, dur, dc, dd);
+    m->launches++;
+    ORB_CUDA(cudaGetLastError());
+    ORB_CUDA(cudaMemcpyAsync(in_view, dok, n, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(u, du, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(v, dv, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(ur, dur, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(view_cos, dc, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(dist, dd, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+
+int orb_distinctive_descriptors(orb_matcher* m, int n_points, const int32_t* start, const uint8_t* desc, int32_t* best_idx) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (n_points < 0 || (n_points > 0 && (!start || !desc || !best_idx))) return ORB_ERR_BAD_ARG;
+    if (n_points == 0) return ORB_OK;
+    for (int p = 0; p < n_points; ++p)
+        if (start[p + 1] < start[p] || start[p + 1] - start[p] > 65535) { orb_set_error("bad observation ranges"); return ORB_ERR_BAD_ARG; }
+    const int total = start[n_points];
+    const int* ds; const uint8_t* dd; int* db;
+    if ((st = ws_upload(m, &ds, start, (size_t)n_points + 1)) != ORB_OK || (st = ws_upload(m, &dd, desc, (size_t)total * 32)) != ORB_OK ||
+        (st = ws_alloc(m, &db, n_points)) != ORB_OK) return st;
+    k_distinctive<<<n_points, DD_THREADS, 0, m->stream>>>(ds, dd, db);
+    m->launches++;
+    ORB_CUDA(cudaGetLastError());
+    ORB_CUDA(cudaMemcpyAsync(best_idx, db, (size_t)n_points * 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+
+}  // extern "C"

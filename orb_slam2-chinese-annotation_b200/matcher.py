@@ -152,6 +152,28 @@ class ORBmatcher:
         prev_x[ok] = F2.x[m[ok]]; prev_y[ok] = F2.y[m[ok]]
         return n.value, m
 
+    # bool Frame::isInFrustum(MapPoint *pMP, float viewingCosLimit), batched over the local map (src/Frame.cc:303-366)
+    def isInFrustum(self, Rcw, tcw, Ow, cam, bounds, viewingCosLimit, xw, normal, min_distance, max_distance):
+        """-> dict(in_view, u, v, ur, view_cos, dist); mnTrackScaleLevel = PredictScale(dist) stays with the caller."""
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        Rcw, tcw, Ow, xw, normal = f32(Rcw).reshape(9), f32(tcw).reshape(3), f32(Ow).reshape(3), f32(xw).reshape(-1, 3), f32(normal).reshape(-1, 3)
+        mind, maxd = f32(min_distance), f32(max_distance)
+        n = len(xw)
+        c = Camera(*[float(v) for v in cam]); g = GridParams(float(bounds[0]), float(bounds[1]), float(bounds[2]), float(bounds[3]), 0.0, 0.0)
+        ok = np.zeros(max(n, 1), np.uint8); outs = [np.zeros(max(n, 1), np.float32) for _ in range(5)]
+        check(lib().orb_is_in_frustum(self._h, ptr(Rcw), ptr(tcw), ptr(Ow), C.byref(c), C.byref(g), C.c_float(viewingCosLimit), n, ptr(xw), ptr(normal),
+                                      ptr(mind), ptr(maxd), ptr(ok), *[ptr(o) for o in outs]))
+        return dict(in_view=ok[:n], u=outs[0][:n], v=outs[1][:n], ur=outs[2][:n], view_cos=outs[3][:n], dist=outs[4][:n])
+
+    # void MapPoint::ComputeDistinctiveDescriptors(), batched over MapPoints (src/MapPoint.cc:250-326)
+    def ComputeDistinctiveDescriptors(self, start, desc):
+        """start[P + 1] offsets into desc (rows of each point's observations, reference gather order) -> best row per point."""
+        start = np.ascontiguousarray(start, np.int32); desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        P = len(start) - 1
+        best = np.empty(max(P, 1), np.int32)
+        check(lib().orb_distinctive_descriptors(self._h, P, ptr(start), ptr(desc), ptr(best)))
+        return best[:P]
+
 
 def _mp_view(d):
     keep = dict(valid=u8(d["valid"]), proj_x=np.ascontiguousarray(d["proj_x"], np.float32), proj_y=np.ascontiguousarray(d["proj_y"], np.float32),

@@ -383,3 +383,25 @@ def bow_transform(voc, desc, levelsup=4):
     lib.orc_bow_transform.restype = None
     lib.orc_bow_transform(int(voc["L"]), len(parent), _p(parent), _p(leaf), _p(nd), _p(desc), n, int(levelsup), _p(word), _p(node))
     return word[:n], node[:n]
+
+
+def is_in_frustum(Rcw, tcw, Ow, cam, bounds, cos_limit, xw, normal, mind, maxd):
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    Rcw, tcw, Ow, xw, normal, mind, maxd = f32(Rcw).reshape(9), f32(tcw).reshape(3), f32(Ow).reshape(3), f32(xw).reshape(-1, 3), f32(normal).reshape(-1, 3), f32(mind), f32(maxd)
+    n = len(xw)
+    c = _views.Camera(*[float(v) for v in cam]); g = _views.GridParams(float(bounds[0]), float(bounds[1]), float(bounds[2]), float(bounds[3]), 0.0, 0.0)
+    ok = np.zeros(max(n, 1), np.uint8); outs = [np.zeros(max(n, 1), np.float32) for _ in range(5)]
+    lib.orc_is_in_frustum.argtypes = [C.c_void_p] * 5 + [C.c_float, C.c_int] + [C.c_void_p] * 10
+    lib.orc_is_in_frustum.restype = None
+    lib.orc_is_in_frustum(_p(Rcw), _p(tcw), _p(Ow), C.byref(c), C.byref(g), cos_limit, n, _p(xw), _p(normal), _p(mind), _p(maxd), _p(ok), *[_p(o) for o in outs])
+    return dict(in_view=ok[:n], u=outs[0][:n], v=outs[1][:n], ur=outs[2][:n], view_cos=outs[3][:n], dist=outs[4][:n])
+
+
+def distinctive_descriptors(start, desc):
+    start = np.ascontiguousarray(start, np.int32); desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    P = len(start) - 1
+    best = np.empty(max(P, 1), np.int32)
+    lib.orc_distinctive_descriptors.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.orc_distinctive_descriptors.restype = None
+    lib.orc_distinctive_descriptors(P, _p(start), _p(desc), _p(best))
+    return best[:P]

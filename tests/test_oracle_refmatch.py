@@ -207,3 +207,42 @@ def test_bow_transform_vs_reference_dbow2(dropin, tmp_path, k, L, levelsup, seed
         assert len(fv.node_ids) > 5
     else:
         assert list(fv.node_ids) == [0]          # L - levelsup <= 0: every feature files under the root
+
+
+@pytest.mark.parametrize("idx,cos_limit", [(0, 0.5), (1, 0.5), (2, 0.8)])
+def test_is_in_frustum(dropin, tmp_path, idx, cos_limit):
+    """Frame::isInFrustum (src/Frame.cc:303-366, verbatim, built with the reference's -O3 + FMA flags) == the oracle's
+    restatement, every float bit-equal (mTrackProjX/Y/XR, mTrackViewCos), and mnTrackScaleLevel == PredictScale(dist)."""
+    f, wd = worldsim.frustum_scenario(idx)
+    F, blob = D._world_blob(f, wd, np.zeros(2000, bool), 1.0, False)
+    blob["cos_limit"] = D._f32(cos_limit)
+    out = dropin("frustum", blob, tmp_path)
+    R, t, Ow = out["rt_ow"][:9], out["rt_ow"][9:12], out["rt_ow"][12:15]
+    assert np.array_equal(Ow, worldsim.camera_centre(wd["pose"][:3, :3], wd["pose"][:3, 3]))
+    o = orc.is_in_frustum(R, t, Ow, worldsim.CAM, f["bounds"], cos_limit, wd["xw"], wd["normal"], wd["mind"], wd["maxd"])
+    ok = o["in_view"] != 0
+    assert np.array_equal(out["in_view"] != 0, ok)
+    for k in ("u", "v", "ur", "view_cos"):
+        assert np.array_equal(out[k][ok], o[k][ok]), k
+    assert np.array_equal(out["level"][ok], worldsim.predict_scale(wd["maxd"][ok], o["dist"][ok], f["sf"]))
+    assert 0.3 < ok.mean() < 0.97
+
+
+@pytest.mark.parametrize("idx", [0, 1])
+def test_compute_distinctive_descriptors(dropin, tmp_path, idx):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:250-326, verbatim) == the oracle on the rows in the
+    order the reference gathered them (std::map<KeyFrame*, size_t>: KeyFrame address order)."""
+    kf_desc, start, okf, orow = worldsim.distinctive_scenario(idx)
+    f = synth.make_frame_arrays(50, 990)
+    F, blob = D._frame_blob("f_", f)
+    blob.update({"dims": np.array(kf_desc.shape[:2], np.int32), "kf_desc": kf_desc.reshape(-1), "start": start, "obs_kf": okf, "obs_row": orow})
+    out = dropin("distinctive", blob, tmp_path)
+    gs, gd = out["g_start"], out["g_desc"].reshape(-1, 32)
+    assert np.array_equal(np.diff(gs), np.diff(start))
+    best = orc.distinctive_descriptors(gs, gd)
+    chosen = out["chosen"].reshape(-1, 32)
+    n_obs = np.diff(gs)
+    assert np.all(best[n_obs == 0] == -1) and np.all(chosen[n_obs == 0] == 0)
+    has = n_obs > 0
+    assert np.array_equal(chosen[has], gd[gs[:-1][has] + best[has]])
+    assert (best[has] > 0).sum() > 50

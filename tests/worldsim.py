@@ -178,3 +178,37 @@ def sim3_matrices(s12, R12, t12):
     sR21 = (F32(1.0 / F64(s12)) * R12.T).astype(F32)
     t21 = (-mul_row(sR21, t12[None, :])[0]).astype(F32)      # -sR21 * t12: plain product, float
     return sR12, sR21, t21
+
+
+def frustum_scenario(idx, n_pts=3000):
+    """Frame + world MapPoints for Frame::isInFrustum: the make_world points (a few percent fail each gate)."""
+    import importlib
+    synth = importlib.import_module("orb_slam2-chinese-annotation_b200.synth")
+    f = synth.make_frame_arrays(2000, 560 + idx)
+    wd = make_world(f, 40 + idx, n_pts, perturb=synth.perturb_descriptors)
+    return f, wd
+
+
+def distinctive_scenario(idx, n_kf=24, rows=300, n_points=400):
+    """KeyFrames with descriptor rows and MapPoints observing 0..n_kf of them: each point's rows are noisy copies of
+    one base descriptor (some points get coarse descriptors, so medians tie)."""
+    rng = np.random.default_rng(0x5EED0000 + 0xD0000 + idx)
+    kf_desc = rng.integers(0, 256, (n_kf, rows, 32), dtype=np.uint8)
+    start = [0]; okf = []; orow = []
+    free = [list(rng.permutation(rows)) for _ in range(n_kf)]
+    for p in range(n_points):
+        n_obs = int(rng.choice([0, 1, 2, 3, 5, 8, 13, n_kf], p=[0.02, 0.05, 0.1, 0.2, 0.25, 0.2, 0.13, 0.05]))
+        kfs = rng.permutation(n_kf)[:n_obs]
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        coarse = rng.random() < 0.3
+        for k in kfs:
+            if not free[k]:
+                continue
+            r = free[k].pop()
+            flips = np.packbits(rng.random(256) < 0.1)
+            if coarse:
+                flips = flips & 0x11
+            kf_desc[k, r] = base ^ flips
+            okf.append(int(k)); orow.append(int(r))
+        start.append(len(okf))
+    return kf_desc, np.array(start, np.int32), np.array(okf, np.int32), np.array(orow, np.int32)

@@ -357,6 +357,29 @@ int orb_bow_transform(orb_vocabulary* v, const uint8_t* desc, int n, int levelsu
 int orb_bow_transform_device(orb_vocabulary* v, const uint8_t* d_desc, int n, int levelsup, int32_t* d_word_id,
                              int32_t* d_node_id);
 
+/* ---- In front of the extractor: stereo rectification and gray conversion ----
+ * cv::remap(imLeft, imLeftRect, M1l, M2l, cv::INTER_LINEAR) with the CV_32F maps of initUndistortRectifyMap
+ * (Examples/Stereo/stereo_euroc.cc:97-98,136-137; BORDER_CONSTANT 0) and cv::cvtColor(im, im, CV_RGB2GRAY | CV_BGR2GRAY |
+ * CV_RGBA2GRAY | CV_BGRA2GRAY) (src/Tracking.cc:174-199), OpenCV 4.13's 8-bit fixed point bit for bit.  A rectifier
+ * holds one camera's maps (dst_w x dst_h floats each, row-major; both NULL = gray conversion only), converted once to
+ * the fixed-point form cv::remap derives per call.  max_batch bounds the host entry points. */
+typedef struct orb_rectifier orb_rectifier;
+int orb_rectifier_create(const float* map_x, const float* map_y, int dst_w, int dst_h, int src_w, int src_h, int max_batch,
+                         int device, orb_rectifier** out);
+void orb_rectifier_destroy(orb_rectifier* r);
+void* orb_rectifier_stream(const orb_rectifier* r);
+long long orb_rectifier_launch_count(const orb_rectifier* r);
+int orb_rectifier_sync(orb_rectifier* r);
+/* host buffers: batch images stacked vertically (image b starts at row b * src_h / b * dst_h), synchronous */
+int orb_remap(orb_rectifier* r, const uint8_t* src, int src_stride, int batch, uint8_t* dst, int dst_stride);
+int orb_gray(orb_rectifier* r, const uint8_t* src, int w, int h, int channels, int rgb_order, int src_stride, uint8_t* dst,
+             int dst_stride);
+/* device buffers, asynchronous on the rectifier's stream (dst may be the input of orb_extract_device) */
+int orb_remap_device(orb_rectifier* r, const uint8_t* d_src, int src_stride, size_t src_img_stride, int batch, uint8_t* d_dst,
+                     int dst_stride, size_t dst_img_stride);
+int orb_gray_device(orb_rectifier* r, const uint8_t* d_src, int w, int h, int channels, int rgb_order, int src_stride,
+                    size_t src_img_stride, int batch, uint8_t* d_dst, int dst_stride, size_t dst_img_stride);
+
 #ifdef __cplusplus
 }
 #endif

@@ -285,6 +285,10 @@ void orc_resize_linear_u8(const uint8_t* s, int sw, int sh, int ss, uint8_t* d, 
     orc::resize_linear_u8(s, sw, sh, ss, d, dw, dh, ds);
 }
 void orc_gauss7_u8(const uint8_t* s, int w, int h, int ss, uint8_t* d, int ds) { orc::gauss7_u8(s, w, h, ss, d, ds); }
+void orc_remap_linear_u8(const uint8_t* s, int sw, int sh, int ss, const float* mx, const float* my, uint8_t* d, int dw, int dh, int ds) {
+    orc::remap_linear_u8(s, sw, sh, ss, mx, my, d, dw, dh, ds);
+}
+void orc_gray_u8(const uint8_t* s, int w, int h, int ss, int channels, int rgb_order, uint8_t* d, int ds) { orc::gray_u8(s, w, h, ss, channels, rgb_order, d, ds); }
 void orc_border101(const uint8_t* s, int w, int h, int ss, uint8_t* d, int ds, int b) { orc::border101(s, w, h, ss, d, ds, b); }
 int orc_fast9_16(const uint8_t* img, int w, int h, int stride, int th, int32_t* xys, int cap) {
     std::vector<FastPt> v;

@@ -21,6 +21,10 @@ typedef struct orc_extractor orc_extractor;
 /* ---- primitives (for KATs against cv2) ---- */
 void orc_resize_linear_u8(const uint8_t* src, int sw, int sh, int sstride, uint8_t* dst, int dw, int dh, int dstride);
 void orc_gauss7_u8(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride);
+/* cv::remap INTER_LINEAR with CV_32FC1 x / y maps, BORDER_CONSTANT 0 (stereo rectification, Examples/Stereo/stereo_euroc.cc:136-137) */
+void orc_remap_linear_u8(const uint8_t* src, int sw, int sh, int sstride, const float* mapx, const float* mapy, uint8_t* dst, int dw, int dh, int dstride);
+/* cv::cvtColor 8U RGB/BGR/RGBA/BGRA -> GRAY (src/Tracking.cc:174-199) */
+void orc_gray_u8(const uint8_t* src, int w, int h, int sstride, int channels, int rgb_order, uint8_t* dst, int dstride);
 void orc_border101(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride, int b);
 /* cv::FAST(view, th, nms=true); returns count, writes up to cap (x,y,score) int triples */
 int orc_fast9_16(const uint8_t* img, int w, int h, int stride, int threshold, int32_t* xys, int cap);

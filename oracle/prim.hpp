@@ -16,6 +16,7 @@
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 // use anything under oracle/.
 #pragma once
+#include <climits>
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
@@ -231,4 +232,36 @@ static inline float fast_atan2(float y, float x) {
     return a;
 }
 
+
+// cv::remap(src, dst, map1 = x (CV_32FC1), map2 = y (CV_32FC1), INTER_LINEAR, BORDER_CONSTANT 0) on 8UC1, as the EuRoC
+// stereo example rectifies its images (reference Examples/Stereo/stereo_euroc.cc:97-98,136-137).  OpenCV >= 3 fixed point:
+// coordinates to 1/32 px (cvRound(x * 32), half to even), integer part saturated to short, bilinear weights
+// (32-fy)(32-fx)*32 ... summing to 2^15, result (sum + 2^14) >> 15; pixels outside the source read 0.
+static inline void remap_linear_u8(const uint8_t* src, int sw, int sh, int sstride, const float* mapx, const float* mapy, uint8_t* dst, int dw,
+                                   int dh, int dstride) {
+    for (int y = 0; y < dh; ++y)
+        for (int x = 0; x < dw; ++x) {
+            const float fxs = mapx[(size_t)y * dw + x] * 32.f, fys = mapy[(size_t)y * dw + x] * 32.f;
+            // cvRound saturates through cvtss2si: out-of-range and NaN give INT_MIN
+            const int sx = (fxs >= -2147483648.f && fxs < 2147483648.f) ? (int)lrintf(fxs) : INT_MIN;
+            const int sy = (fys >= -2147483648.f && fys < 2147483648.f) ? (int)lrintf(fys) : INT_MIN;
+            const int fx = sx & 31, fy = sy & 31;
+            const int ix = std::max(-32768, std::min(32767, sx >> 5)), iy = std::max(-32768, std::min(32767, sy >> 5));
+            const int w00 = (32 - fy) * (32 - fx) * 32, w01 = (32 - fy) * fx * 32, w10 = fy * (32 - fx) * 32, w11 = fy * fx * 32;
+            auto px = [&](int yy, int xx) -> int { return (xx >= 0 && xx < sw && yy >= 0 && yy < sh) ? src[(size_t)yy * sstride + xx] : 0; };
+            const int v = px(iy, ix) * w00 + px(iy, ix + 1) * w01 + px(iy + 1, ix) * w10 + px(iy + 1, ix + 1) * w11;
+            dst[(size_t)y * dstride + x] = (uint8_t)((v + (1 << 14)) >> 15);
+        }
+}
+
+// cv::cvtColor(src, dst, CV_RGB2GRAY / CV_BGR2GRAY / CV_RGBA2GRAY / CV_BGRA2GRAY) on 8U (reference src/Tracking.cc:174-199):
+// OpenCV 4 fixed point, 15 bits: (R*9798 + G*19235 + B*3735 + 2^14) >> 15.  rgb_order != 0: channel 0 is R.
+static inline void gray_u8(const uint8_t* src, int w, int h, int sstride, int channels, int rgb_order, uint8_t* dst, int dstride) {
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            const uint8_t* p = src + (size_t)y * sstride + (size_t)x * channels;
+            const int r = rgb_order ? p[0] : p[2], g = p[1], b = rgb_order ? p[2] : p[0];
+            dst[(size_t)y * dstride + x] = (uint8_t)((r * 9798 + g * 19235 + b * 3735 + (1 << 14)) >> 15);
+        }
+}
 }  // namespace orc

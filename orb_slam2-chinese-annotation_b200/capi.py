@@ -28,6 +28,8 @@ EXPORTS = [
     "orb_search_projected_best", "orb_search_by_sim3", "orb_search_for_initialization", "orb_sincosf_sweep_device",
     "orb_vocabulary_create", "orb_vocabulary_destroy", "orb_vocabulary_info", "orb_vocabulary_stream", "orb_vocabulary_launch_count",
     "orb_vocabulary_sync", "orb_bow_transform", "orb_bow_transform_device", "orb_is_in_frustum", "orb_distinctive_descriptors",
+    "orb_rectifier_create", "orb_rectifier_destroy", "orb_rectifier_stream", "orb_rectifier_launch_count", "orb_rectifier_sync",
+    "orb_remap", "orb_gray", "orb_remap_device", "orb_gray_device",
 ]
 
 
@@ -59,11 +61,14 @@ def lib():
         L.orb_extractor_launch_count.restype = C.c_longlong
         L.orb_matcher_launch_count.restype = C.c_longlong
         L.orb_vocabulary_stream.restype = C.c_void_p
+        L.orb_rectifier_stream.restype = C.c_void_p
+        L.orb_rectifier_launch_count.restype = C.c_longlong
         L.orb_vocabulary_launch_count.restype = C.c_longlong
         for name in ("orb_extractor_stream", "orb_extractor_launch_count", "orb_extractor_max_keypoints",
                      "orb_extractor_destroy", "orb_extractor_sync", "orb_matcher_stream", "orb_matcher_launch_count",
                      "orb_matcher_destroy", "orb_matcher_sync", "orb_vocabulary_stream", "orb_vocabulary_launch_count",
-                     "orb_vocabulary_destroy", "orb_vocabulary_sync"):
+                     "orb_vocabulary_destroy", "orb_vocabulary_sync", "orb_rectifier_stream", "orb_rectifier_launch_count",
+                     "orb_rectifier_destroy", "orb_rectifier_sync"):
             getattr(L, name).argtypes = [C.c_void_p]
         _lib = L
     return _lib

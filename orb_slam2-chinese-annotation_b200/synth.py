@@ -293,3 +293,22 @@ def vocabulary_queries(voc, n, seed=0, tie_frac=0.1):
         q[:nt] = voc["desc"][rng.choice(inner, nt)]
     q[nt:nt + max(1, n // 50)] = rng.integers(0, 2, (max(1, n // 50), 1)).astype(np.uint8) * 255   # all-zero / all-one rows
     return q
+
+
+def make_rectify_maps(w, h, seed=0, src_w=None, src_h=None):
+    """Float x / y maps shaped like cv::initUndistortRectifyMap(..., CV_32F, M1, M2) output: a small rotation plus
+    radial distortion around the principal point, so a band along the borders maps outside the source image."""
+    rng = np.random.default_rng(SEED_BASE + 0xEC7000 + seed)
+    src_w = w if src_w is None else src_w; src_h = h if src_h is None else src_h
+    fx = 0.61 * w; fy = fx; cx = 0.49 * w; cy = 0.52 * h
+    k1, k2 = -0.28 + 0.02 * rng.standard_normal(), 0.07 + 0.01 * rng.standard_normal()
+    th = 0.01 * rng.standard_normal(3)
+    R = np.array([[1, -th[2], th[1]], [th[2], 1, -th[0]], [-th[1], th[0], 1]])
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float64)
+    X = (xx - cx) / fx; Y = (yy - cy) / fy
+    P = np.stack([X, Y, np.ones_like(X)], -1) @ R.T
+    x = P[..., 0] / P[..., 2]; y = P[..., 1] / P[..., 2]
+    r2 = x * x + y * y
+    d = 1 + k1 * r2 + k2 * r2 * r2
+    mx = (fx * x * d + 0.5 * src_w + 1.3).astype(np.float32); my = (fy * y * d + 0.5 * src_h - 0.8).astype(np.float32)
+    return mx, my

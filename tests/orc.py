@@ -405,3 +405,23 @@ def distinctive_descriptors(start, desc):
     lib.orc_distinctive_descriptors.restype = None
     lib.orc_distinctive_descriptors(P, _p(start), _p(desc), _p(best))
     return best[:P]
+
+
+def remap_linear_u8(src, mapx, mapy):
+    src = np.ascontiguousarray(src, np.uint8); mapx = np.ascontiguousarray(mapx, np.float32); mapy = np.ascontiguousarray(mapy, np.float32)
+    dh, dw = mapx.shape
+    dst = np.empty((dh, dw), np.uint8)
+    lib.orc_remap_linear_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
+    lib.orc_remap_linear_u8.restype = None
+    lib.orc_remap_linear_u8(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(mapx), _p(mapy), _p(dst), dw, dh, dw)
+    return dst
+
+
+def gray_u8(src, rgb_order):
+    src = np.ascontiguousarray(src, np.uint8)
+    h, w, ch = src.shape
+    dst = np.empty((h, w), np.uint8)
+    lib.orc_gray_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+    lib.orc_gray_u8.restype = None
+    lib.orc_gray_u8(_p(src), w, h, src.strides[0], ch, int(bool(rgb_order)), _p(dst), w)
+    return dst

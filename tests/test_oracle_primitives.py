@@ -140,3 +140,23 @@ def test_primitives_match_committed_golden():
         assert np.array_equal(orc.fast9_16(img, th), g["fast%d" % th])
     at = np.array([orc.fast_atan2(y, x) for y, x in g["atan_in"]], np.float32)
     assert np.array_equal(at, g["atan_out"])
+
+
+def test_remap_and_gray_match_cv2_golden():
+    """cv::remap(INTER_LINEAR, float maps, BORDER_CONSTANT) and cv::cvtColor(*2GRAY) restatements vs vectors made by the real
+    cv2 4.13 (tests/golden/make_golden_rectify.py), incl. half-step rounding, border, far-outside and NaN coordinates."""
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "rectify.npz"))
+    assert np.array_equal(orc.remap_linear_u8(g["img"], g["mx"], g["my"]), g["remapped"])
+    assert np.array_equal(orc.gray_u8(g["bgr"], False), g["bgr2gray"]) and np.array_equal(orc.gray_u8(g["bgr"], True), g["rgb2gray"])
+    assert np.array_equal(orc.gray_u8(g["bgra"], False), g["bgra2gray"]) and np.array_equal(orc.gray_u8(g["bgra"], True), g["rgba2gray"])
+    assert (g["remapped"] == 0).mean() < 0.5
+
+
+def test_remap_matches_live_cv2():
+    cv2 = pytest.importorskip("cv2")
+    import importlib
+    synth = importlib.import_module("orb_slam2-chinese-annotation_b200.synth")
+    for (w, h, seed) in [(752, 480, 0), (640, 480, 1)]:
+        img = synth.make_image(w, h, seed)
+        mx, my = synth.make_rectify_maps(w, h, seed)
+        assert np.array_equal(orc.remap_linear_u8(img, mx, my), cv2.remap(img, mx, my, cv2.INTER_LINEAR))

@@ -1,7 +1,10 @@
 // TEST INFRASTRUCTURE — CPU oracle for stereo matching and the ORBmatcher searches (not product
-// code; see orb_oracle.h).  "parity unpinned by the reference's own tests": the reference's
-// Frame.cc / ORBmatcher.cc need OpenCV C++, DBoW2, Eigen and g2o and cannot be compiled here, so
-// these are line-by-line restatements over plain arrays:
+// code; see orb_oracle.h).  Line-by-line restatements over plain arrays.  PINNED against the reference itself:
+// src/ORBmatcher.cc, Frame.cc, KeyFrame.cc, MapPoint.cc, Map.cc, KeyFrameDatabase.cc and the vendored DBoW2 are
+// compiled verbatim (oracle/Makefile `refmatch`, against oracle/cvshim) into oracle/_ref/ref_match_driver and
+// run on real Frame / KeyFrame / MapPoint objects; tests/test_oracle_refmatch.py compares every function below
+// with it, bit for bit, on the scenarios the GPU tests use (the reference has no tests or golden vectors of
+// its own for this path):
 //
 //   orc_stereo_match                 <- Frame::ComputeStereoMatches            src/Frame.cc:516-704
 //   grid / area query                <- Frame::AssignFeaturesToGrid, PosInGrid,

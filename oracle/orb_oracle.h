@@ -1,8 +1,9 @@
 /* TEST INFRASTRUCTURE — C API of the CPU oracle (restatement of the reference's ORB front-end).
  * Parity pinning: primitives vs cv2 4.13.0 (tests/golden), extractor control flow vs the
  * reference's own src/ORBextractor.cc compiled verbatim (oracle/_ref, see oracle/Makefile).
- * Matchers and stereo are restatements only ("port"): the reference's ORBmatcher.cc / Frame.cc
- * cannot be compiled here (need OpenCV C++, DBoW2, Eigen, g2o).
+ * Matchers, grid, stereo, isInFrustum, ComputeDistinctiveDescriptors and the DBoW2 transform are pinned against the
+ * reference's own ORBmatcher.cc / Frame.cc / KeyFrame.cc / MapPoint.cc / DBoW2 compiled verbatim
+ * (oracle/_ref/ref_match_driver, tests/test_oracle_refmatch.py); remap / cvtColor against cv2 4.13 goldens.
  * Only tests/, __graft_entry__.smoke() and bench.py (cpu_baseline / --impl reference) may use it. */
 #ifndef ORB_ORACLE_H
 #define ORB_ORACLE_H

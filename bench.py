@@ -296,6 +296,9 @@ def run_ours(args):
     # slot rows are downloaded whole (cap == the handle's kp_cap here): keypoints + descriptors of both sides, uRight, depth, counts
     d2h = int(B * cap * (2 * (kp_dt.itemsize + 32) + 8) + 2 * B * 4 + 8)
 
+    matching = None
+    if rank == 0:
+        matching = bench_matching(local)
     if rank == 0:
         peaks = {}
         try:
@@ -345,6 +348,7 @@ def run_ours(args):
                                  "frac": alu_ach / alu_peak},
                          "pipeline_achieved": 2 * B * alg_img / (pipe_ms * 1e-3) / 1e9,
                          "stage_ms_per_step": stages},
+            "matching": matching,
             "cpu_baseline": {"value": cpu_val, "unit": "frames/s", "cores": cores, "kind": cpu_kind,
                              "sample": "%d stereo pairs on %d host threads in %.1f s; %s" % (cpu_n, cores, cpu_dt, CPU_DESC[cpu_kind])},
         }
@@ -352,6 +356,58 @@ def run_ours(args):
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def bench_matching(local):
+    """BASELINE.json configs[3] beside the headline step (rank 0, outside its timed region): ORBmatcher Hamming matching on
+    2000 x 2000 descriptor sets, 1024 frame pairs: brute force (best / second best per row, device-resident, CUDA events on the
+    matcher's stream) and grid-guided SearchByProjection(Frame, MapPoints) through the host API (one call per frame)."""
+    synth = importlib.import_module(PKG + ".synth")
+    mt = importlib.import_module(PKG + ".matcher")
+    views = importlib.import_module(PKG + ".views")
+    capi = importlib.import_module(PKG + ".capi")
+    import torch
+    P, N = 1024, 2000
+    rng = np.random.default_rng(7)
+    U = 32   # unique pairs, tiled to P (the kernel's time does not depend on the content; 131 MB of descriptors > L2)
+    a = rng.integers(0, 256, (U, N, 32), dtype=np.uint8)
+    b = a[:, rng.permutation(N)] ^ np.packbits(rng.random((U, N, 256)) < 0.08, axis=2)
+    a = np.tile(a, (P // U, 1, 1)); b = np.tile(b, (P // U, 1, 1))
+    m = mt.ORBmatcher(0.6, True, max_n=8192, max_pairs=1, device=local)
+    L = capi.lib()
+    st = torch.cuda.ExternalStream(L.orb_matcher_stream(m._h), device=local)
+    da = torch.from_numpy(a).cuda(); db = torch.from_numpy(b).cuda()
+    bi = torch.empty((P, N), dtype=torch.int32, device="cuda"); bd = torch.empty_like(bi); sd = torch.empty_like(bi)
+    torch.cuda.synchronize()
+
+    def run():
+        capi.check(L.orb_match_bruteforce_device(m._h, C.c_void_p(da.data_ptr()), C.c_void_p(db.data_ptr()), P, N, N, C.c_void_p(bi.data_ptr()),
+                                                 C.c_void_p(bd.data_ptr()), C.c_void_p(sd.data_ptr())))
+    for _ in range(2):
+        run()
+    capi.check(L.orb_matcher_sync(m._h))
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    K = 5
+    e0.record(st)
+    for _ in range(K):
+        run()
+    e1.record(st)
+    capi.check(L.orb_matcher_sync(m._h))
+    bf_ms = e0.elapsed_time(e1) / K
+    # grid-guided projection search, host API, one frame per call
+    f, mps, occ = synth.make_projection_scenario(N, N, 0)
+    F = views.Frame(f["x"], f["y"], f["octave"], f["angle"], f["desc"], f["sf"], f["bounds"], f["u_right"])
+    for _ in range(3):
+        m.SearchByProjection(F, mps, 3.0, occ)
+    t0 = time.perf_counter(); reps = 50
+    for _ in range(reps):
+        n_sp, _ = m.SearchByProjection(F, mps, 3.0, occ)
+    sp_ms = (time.perf_counter() - t0) / reps * 1e3
+    popc = P * N * N * 8 / (bf_ms * 1e-3)
+    return {"workload": "2000x2000 descriptors per frame pair, 1024 pairs (BASELINE.json configs[3])",
+            "bruteforce": {"ms_per_1024_pairs": bf_ms, "pairs_per_s": P / (bf_ms * 1e-3), "popc_Tops": popc / 1e12,
+                           "int_peak_Tops": 148 * 128 * 1965e6 / 1e12 / 4, "note": "POPC issues at 1/4 rate: peak = 148 SM x 32 popc/clk x 1.965 GHz"},
+            "search_by_projection_host_api": {"ms_per_frame": sp_ms, "frames_per_s": 1e3 / sp_ms, "matches": int(n_sp), "th": 3.0}}
 
 
 def main():

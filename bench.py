@@ -406,7 +406,8 @@ def bench_matching(local):
     popc = P * N * N * 8 / (bf_ms * 1e-3)
     return {"workload": "2000x2000 descriptors per frame pair, 1024 pairs (BASELINE.json configs[3])",
             "bruteforce": {"ms_per_1024_pairs": bf_ms, "pairs_per_s": P / (bf_ms * 1e-3), "popc_Tops": popc / 1e12,
-                           "int_peak_Tops": 148 * 128 * 1965e6 / 1e12 / 4, "note": "POPC issues at 1/4 rate: peak = 148 SM x 32 popc/clk x 1.965 GHz"},
+                           "popc_peak_Tops": 148 * 16 * 1965e6 / 1e12, "frac": popc / (148 * 16 * 1965e6),
+                           "note": "peak = 148 SM x 16 POPC/clk/SM (CUDA C Programming Guide arithmetic-throughput table; not re-measured here) x 1.965 GHz"},
             "search_by_projection_host_api": {"ms_per_frame": sp_ms, "frames_per_s": 1e3 / sp_ms, "matches": int(n_sp), "th": 3.0}}
 
 

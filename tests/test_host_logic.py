@@ -42,6 +42,52 @@ def test_no_cpu_fallback_without_device():
     mt = importlib.import_module(PKG + ".matcher")
     with pytest.raises(capi.OrbError):
         mt.ORBmatcher()
+    bow = importlib.import_module(PKG + ".bow")
+    with pytest.raises(capi.OrbError) as e:
+        bow.ORBVocabulary().load_arrays(**synth.make_vocabulary(4, 2, 0))
+    assert e.value.status == capi.ORB_ERR_CUDA
+    rect = importlib.import_module(PKG + ".rectify")
+    with pytest.raises(capi.OrbError) as e:
+        rect.Rectifier(*synth.make_rectify_maps(64, 48, 0))
+    assert e.value.status == capi.ORB_ERR_CUDA
+
+
+def test_bow_assembly_matches_the_map_semantics():
+    """Host assembly of BowVector / FeatureVector (bow.assemble) against a literal std::map-style restatement of
+    TemplatedVocabulary::transform (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1146-1207) for all weighting / scoring kinds."""
+    bow = importlib.import_module(PKG + ".bow")
+    rng = np.random.default_rng(3)
+    n, W = 500, 60
+    word = rng.integers(0, W, n).astype(np.int32); node = (word // 7).astype(np.int32)
+    ww = rng.uniform(0.1, 9.0, W); ww[rng.integers(0, W, 5)] = 0.0
+    for weighting in range(4):
+        for scoring in range(6):
+            v, fv = {}, {}
+            for i in range(n):
+                w = ww[word[i]]
+                if w > 0:
+                    if weighting in (bow.TF_IDF, bow.TF):
+                        v[int(word[i])] = v.get(int(word[i]), 0.0) + w
+                    else:
+                        v.setdefault(int(word[i]), w)
+                    fv.setdefault(int(node[i]), []).append(i)
+            keys = sorted(v)
+            must = scoring != bow.DOT_PRODUCT
+            if weighting in (bow.TF_IDF, bow.TF) and v and not must:
+                for k in keys:
+                    v[k] /= float(len(v))
+            if must:
+                norm = 0.0
+                for k in keys:
+                    norm += v[k] * v[k] if scoring == bow.L2_NORM else abs(v[k])
+                if scoring == bow.L2_NORM:
+                    norm = np.sqrt(norm)
+                if norm > 0:
+                    for k in keys:
+                        v[k] /= norm
+            ids, vals, f = bow.assemble(word, node, ww, weighting, scoring)
+            assert list(ids) == keys and np.array_equal(vals, np.array([v[k] for k in keys])), (weighting, scoring)
+            assert list(f.node_ids) == sorted(fv) and list(f.items) == [i for k in sorted(fv) for i in fv[k]]
 
 
 def test_cpp_dropin_headers_compile_and_fail_loudly_without_device(tmp_path):

@@ -307,6 +307,15 @@ int orb_chunk_size(int batch) {
     const int c = (batch + 3) / 4;
     return c < 8 ? 8 : c;
 }
+// Chunks of the upload / kernels / download pipeline: uniform.  (A ramp that starts with a quarter-size chunk and grows
+// 1.5x per chunk, to shorten the unhidden first upload, measured 29.2-29.4 k frames/s against 29.7-29.8 k for four equal
+// chunks at batch 256 on B200: the small chunks cost more in kernel efficiency than the shorter fill gains.)
+std::vector<int> orb_chunk_bounds(int batch) {
+    std::vector<int> b(1, 0);
+    const int c = orb_chunk_size(batch);
+    while (b.back() < batch) b.push_back(std::min(batch, b.back() + c));
+    return b;
+}
 // Host images [b0, b0 + n) of a batch -> level 0 of the same slots.
 int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, int stride, size_t img_stride, cudaStream_t st) {
     const LevelGeom& G0 = e->plan.lv[0];
@@ -526,13 +535,14 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, i
     if (st != ORB_OK) return st;
     st = orb_pipe_streams(e);
     if (st != ORB_OK) return st;
-    const int chunk = orb_chunk_size(batch), nch = (batch + chunk - 1) / chunk;
+    const std::vector<int> cb = orb_chunk_bounds(batch);
+    const int nch = (int)cb.size() - 1;
     if (!orb_pool_event(e, 2 * nch)) { orb_set_error("event"); return ORB_ERR_CUDA; }
     // uploads must not overtake work already queued on the kernel stream
     ORB_CUDA(cudaEventRecord(e->ev_pool[2 * nch], e->stream));
     ORB_CUDA(cudaStreamWaitEvent(e->s_h2d, e->ev_pool[2 * nch], 0));
     for (int c = 0; c < nch; ++c) {
-        const int b0 = c * chunk, n = batch - b0 < chunk ? batch - b0 : chunk;
+        const int b0 = cb[c], n = cb[c + 1] - cb[c];
         st = orb_upload_slots(e, imgs, b0, n, w, h, stride, img_stride, e->s_h2d);
         if (st != ORB_OK) return st;
         ORB_CUDA(cudaEventRecord(e->ev_pool[2 * c], e->s_h2d));

@@ -129,6 +129,8 @@ int orb_run_slots(orb_extractor* e, int b0, int n);
 int orb_pipe_streams(orb_extractor* e);
 cudaEvent_t orb_pool_event(orb_extractor* e, int i);
 int orb_chunk_size(int batch);
+// chunk boundaries of a host batch: bounds[0] = 0 < ... < bounds[n] = batch (ramped sizes, see extractor.cu)
+std::vector<int> orb_chunk_bounds(int batch);
 int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, int stride, size_t img_stride, cudaStream_t st);
 int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st);
 #define ORB_CUDA(call)                                                                      \

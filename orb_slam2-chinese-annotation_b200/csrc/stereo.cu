@@ -320,7 +320,8 @@ int orb_stereo_frames(orb_extractor* l, orb_extractor* r, const uint8_t* imgs_l,
     if (st == ORB_OK) st = orb_pipe_streams(l);
     if (st == ORB_OK) st = orb_pipe_streams(r);   // the right handle's upload staging area
     if (st != ORB_OK) return st;
-    const int chunk = orb_chunk_size(batch), nch = (batch + chunk - 1) / chunk;
+    const std::vector<int> cb = orb_chunk_bounds(batch);
+    const int nch = (int)cb.size() - 1, chunk = cb[1];
     const bool dbg = getenv("ORB_B200_DEBUG") != nullptr;
     const auto t_begin = std::chrono::steady_clock::now();
     if (!orb_pool_event(l, 3 * nch + 1)) { orb_set_error("event"); return ORB_ERR_CUDA; }
@@ -331,7 +332,7 @@ int orb_stereo_frames(orb_extractor* l, orb_extractor* r, const uint8_t* imgs_l,
     ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, l->ev_pool[3 * nch + 1], 0));
     const int kc = l->plan.kp_cap, m = cap < kc ? cap : kc;
     for (int c = 0; c < nch; ++c) {
-        const int b0 = c * chunk, n = batch - b0 < chunk ? batch - b0 : chunk;
+        const int b0 = cb[c], n = cb[c + 1] - cb[c];
         cudaEvent_t up_l = l->ev_pool[3 * c], up_r = l->ev_pool[3 * c + 1], done = l->ev_pool[3 * c + 2];
         // Frame::Frame: ExtractORB(0, left) and ExtractORB(1, right) run side by side (src/Frame.cc:81-84) ...
         if ((st = orb_upload_slots(l, imgs_l, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) return st;

@@ -325,3 +325,19 @@ def test_orbvocabulary_transform(dropin, tmp_path, k, L, levelsup, seed):
     assert np.array_equal(out["bow_ids"], ids) and np.array_equal(out["bow_vals"].view(np.float64), vals)
     assert np.array_equal(out["fv_ids"], fv.node_ids) and np.array_equal(out["fv_start"], fv.start) and np.array_equal(out["fv_items"], fv.items)
     assert len(ids) > 100
+
+
+def test_soak_dropin_vs_oracle_over_seeds(dropin, tmp_path):
+    """Every matcher scenario on 4 further seeds (40 scenarios) through the CUDA drop-in; tests/test_oracle_refmatch.py runs
+    the same seeds (and more) through the reference itself."""
+    for idx in range(4, 8):
+        test_search_by_projection_mappoints(dropin, tmp_path, idx, 3.0, idx % 3 == 0)
+        test_search_by_projection_lastframe(dropin, tmp_path, idx, 7.0 + idx % 9, idx % 2 == 0)
+        test_search_by_bow(dropin, tmp_path, idx, idx % 2 == 1, 0.7 + 0.01 * (idx % 20))
+        test_search_for_triangulation(dropin, tmp_path, idx, idx % 2 == 0)
+        test_search_for_initialization(dropin, tmp_path, idx, 30 + 5 * idx, 0.9, idx % 2 == 0)
+        test_search_by_bow_keyframes(dropin, tmp_path, idx, 0.6 + 0.01 * idx, idx % 2 == 0)
+        test_relocalisation_search_by_projection(dropin, tmp_path, idx, 3.0 + idx % 8, 64 + idx, idx % 2 == 0)
+        test_loop_search_by_projection(dropin, tmp_path, idx, 5 + idx % 6)
+        test_fuse_sim3(dropin, tmp_path, idx, 4.0)
+        test_search_by_sim3(dropin, tmp_path, idx, 1.0 + 0.02 * idx)

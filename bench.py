@@ -39,8 +39,8 @@ CPU_DESC = {
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per image of the ncu --set full capture named below (batch 32)
-NCU_TRAFFIC_SOURCE = "profiles/r1_v3_full_batch32.txt"
-NCU_TRAFFIC_BYTES_PER_IMAGE = {"fast_cells": 1327000}
+NCU_TRAFFIC_SOURCE = "profiles/r1_v6_full_fast_cells.txt"
+NCU_TRAFFIC_BYTES_PER_IMAGE = {"fast_cells": 1328000}   # (42.34 MB read + 0.13 MB written) / 32 images; algorithmic: 1.51 MB
 
 
 def algorithmic_bytes_per_image(n_kp):

@@ -382,6 +382,23 @@ __device__ void rot_cull_warp(const int* __restrict__ hist_idx, const int* __res
     if (lane == 0) *nmatches_io -= removed;
 }
 
+#define RP_G 8
+// offsets and first 32 candidates (one per lane) of points [base, base + RP_G); points past nq come out empty
+__device__ __forceinline__ void rp_load_group(int base, int nq, int lane, const int* __restrict__ starts, const uint32_t* __restrict__ cands,
+                                              uint32_t (&c)[RP_G], int (&c0)[RP_G], int (&c1)[RP_G]) {
+    const int sv = __ldg(starts + min(base + min(lane, RP_G), nq));
+#pragma unroll
+    for (int k = 0; k < RP_G; ++k) {
+        const int a = __shfl_sync(0xffffffffu, sv, k), b = __shfl_sync(0xffffffffu, sv, k + 1);
+        c0[k] = a; c1[k] = base + k < nq ? b : a;
+        c[k] = (a + lane < c1[k]) ? __ldg(cands + a + lane) : 0xffffffffu;
+    }
+}
+// candidate at position pos of a point's list: the first 32 sit in the lanes' registers (warp-uniform pos)
+__device__ __forceinline__ uint32_t rp_cand(const uint32_t* __restrict__ cands, int c0, unsigned pos, uint32_t myc) {
+    return pos < 32u ? __shfl_sync(0xffffffffu, myc, (int)pos) : cands[c0 + pos];
+}
+
 // MODE 0: SearchByProjection(Frame, MapPoints)  -- best + second best with levels, ratio test
 // MODE 1: SearchByProjection(Cur, Last)         -- best only, rotation histogram
 // MODE 2: projected points with claiming (relocalisation :1622-1759, loop :311-427) -- best only, accept
@@ -389,21 +406,36 @@ __device__ void rot_cull_warp(const int* __restrict__ hist_idx, const int* __res
 __global__ void __launch_bounds__(32)
 k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* __restrict__ starts, const uint32_t* __restrict__ cands,
                      const uint8_t* __restrict__ blocks, const float* __restrict__ q_angle, DFrame F, const uint8_t* __restrict__ occupied,
-                     uint8_t* __restrict__ occ, float nn_ratio, int check_ori, int max_dist, int* __restrict__ match,
+                     uint8_t* occ, float nn_ratio, int check_ori, int max_dist, int* __restrict__ match,
                      int* __restrict__ q_best_idx, int* __restrict__ q_best_dist, int* __restrict__ hist_idx,
-                     int* __restrict__ hist_bin, int* __restrict__ nmatches_out) {
+                     int* __restrict__ hist_bin, int* __restrict__ nmatches_out, int occ_shared) {
     __shared__ int s_cnt[32];
+    extern __shared__ uint8_t s_occ[];   // the claimed-keypoint flags live in shared memory when they fit (occ_shared): they are
+    if (occ_shared) occ = s_occ;         // read and written on the serial chain, one L2 round trip per point otherwise
     const int lane = threadIdx.x;
     for (int i = lane; i < F.n; i += 32) { match[i] = -1; occ[i] = occupied ? occupied[i] : 0; }
     __syncwarp();
     int nmatches = 0, n_hist = 0;
     if (q_best_idx) for (int i = lane; i < nq; i += 32) { q_best_idx[i] = -1; q_best_dist[i] = 256; }
     __syncwarp();
-    for (int w = 0; w < nq; ++w) {
-        const int c0 = starts[w], c1 = starts[w + 1];
+    // The points are resolved one after the other (a keypoint claimed by an earlier point is closed to later ones), but their
+    // candidate lists do not depend on that order: the lists of the next RP_G points (offsets, then the first 32 candidates of
+    // each, one per lane) are loaded while the current RP_G points are resolved, which takes the two dependent global loads
+    // per point out of the serial chain.
+    uint32_t pre[RP_G], nxt[RP_G];
+    int p0[RP_G], p1[RP_G], n0[RP_G], n1[RP_G];
+    rp_load_group(0, nq, lane, starts, cands, pre, p0, p1);
+    for (int base = 0; base < nq; base += RP_G) {
+        rp_load_group(base + RP_G, nq, lane, starts, cands, nxt, n0, n1);
+#pragma unroll
+        for (int k = 0; k < RP_G; ++k) {
+        const int w = base + k;
+        const int c0 = p0[k], c1 = p1[k];
+        const uint32_t myc = pre[k];
         if (c0 == c1) continue;
         Best2 v; v.b = 0xffffffffu; v.s = 0xffffffffu;
-        for (int p = c0 + lane; p < c1; p += 32) {
+        if (c0 + lane < c1 && !occ[myc & 0xffffu]) { v.b = (((myc >> 16) & 0x1ffu) << 16) | (unsigned)lane; }
+        for (int p = c0 + 32 + lane; p < c1; p += 32) {
             const uint32_t c = cands[p];
             if (occ[c & 0xffffu]) continue;
             Best2 t; t.b = (((c >> 16) & 0x1ffu) << 16) | (unsigned)(p - c0); t.s = 0xffffffffu;
@@ -412,13 +444,13 @@ k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* _
         v = warp_best2(v);
         if (v.b == 0xffffffffu) continue;
         const int bestDist = (int)(v.b >> 16);
-        const uint32_t cb = cands[c0 + (v.b & 0xffffu)];
+        const uint32_t cb = rp_cand(cands, c0, v.b & 0xffffu, myc);
         const int bestIdx = (int)(cb & 0xffffu);
         if (mode == 0) {
             if (bestDist <= M_TH_HIGH) {
                 bool reject = false;
                 if (v.s != 0xffffffffu) {
-                    const uint32_t cs = cands[c0 + (v.s & 0xffffu)];
+                    const uint32_t cs = rp_cand(cands, c0, v.s & 0xffffu, myc);
                     const int bestDist2 = (int)(v.s >> 16);
                     if ((cb >> 25) == (cs >> 25) && (float)bestDist > __fmul_rn(nn_ratio, (float)bestDist2)) reject = true;
                 }
@@ -447,6 +479,9 @@ k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* _
             }
         }
         __syncwarp();
+        }
+#pragma unroll
+        for (int k = 0; k < RP_G; ++k) { pre[k] = nxt[k]; p0[k] = n0[k]; p1[k] = n1[k]; }
     }
     if (lane == 0) *nmatches_out = nmatches;
     __syncwarp();
@@ -938,8 +973,9 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
             m->launches++;
         }
     } else {
-        k_resolve_projection<<<1, 32, 0, m->stream>>>(o.mode, nq, dq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied, occ, o.nn_ratio,
-                                                      o.check_ori, o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal);
+        const int occ_shared = F.n <= 40 * 1024;
+        k_resolve_projection<<<1, 32, occ_shared ? (size_t)((F.n + 15) & ~15) : 0, m->stream>>>(o.mode, nq, dq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied,
+                                                      occ, o.nn_ratio, o.check_ori, o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal, occ_shared);
         m->launches++;
     }
     ORB_CUDA(cudaGetLastError());

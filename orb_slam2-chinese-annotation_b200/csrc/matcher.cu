@@ -427,12 +427,8 @@ k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* _
     rp_load_group(0, nq, lane, starts, cands, pre, p0, p1);
     for (int base = 0; base < nq; base += RP_G) {
         rp_load_group(base + RP_G, nq, lane, starts, cands, nxt, n0, n1);
-#pragma unroll
-        for (int k = 0; k < RP_G; ++k) {
-        const int w = base + k;
-        const int c0 = p0[k], c1 = p1[k];
-        const uint32_t myc = pre[k];
-        if (c0 == c1) continue;
+        auto serial_one = [&](const int w, const int c0, const int c1, const uint32_t myc) {
+        if (c0 == c1) return;
         Best2 v; v.b = 0xffffffffu; v.s = 0xffffffffu;
         if (c0 + lane < c1 && !occ[myc & 0xffffu]) { v.b = (((myc >> 16) & 0x1ffu) << 16) | (unsigned)lane; }
         for (int p = c0 + 32 + lane; p < c1; p += 32) {
@@ -442,7 +438,7 @@ k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* _
             v = merge2(v, t);
         }
         v = warp_best2(v);
-        if (v.b == 0xffffffffu) continue;
+        if (v.b == 0xffffffffu) return;
         const int bestDist = (int)(v.b >> 16);
         const uint32_t cb = rp_cand(cands, c0, v.b & 0xffffu, myc);
         const int bestIdx = (int)(cb & 0xffffu);
@@ -479,6 +475,66 @@ k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* _
             }
         }
         __syncwarp();
+        };
+        // Four points at a time, 8 lanes each, resolved against the claim state at the start of the group; the result stands
+        // unless a later point of the group still had, among its free candidates, a keypoint that an earlier point of the group
+        // closes (rare: then, or when a list is longer than 8, the four are resolved one after the other as before).
+#pragma unroll
+        for (int h = 0; h < RP_G / 4; ++h) {
+            const int j = lane >> 3, t = lane & 7;
+            int cnt[4];
+            bool small = true;
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) { cnt[jj] = p1[4 * h + jj] - p0[4 * h + jj]; small = small && cnt[jj] <= 8; }
+            bool done = false;
+            if (small) {
+                uint32_t c = 0xffffffffu; int n = 0;
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) { const uint32_t vv = __shfl_sync(0xffffffffu, pre[4 * h + jj], t); if (j == jj) { c = vv; n = cnt[jj]; } }
+                const int w = base + 4 * h + j;
+                const bool fr = t < n && !occ[c & 0xffffu];
+                Best2 v; v.b = fr ? ((((c >> 16) & 0x1ffu) << 16) | (unsigned)t) : 0xffffffffu; v.s = 0xffffffffu;
+#pragma unroll
+                for (int o = 4; o; o >>= 1) { Best2 x; x.b = __shfl_xor_sync(0xffffffffu, v.b, o); x.s = __shfl_xor_sync(0xffffffffu, v.s, o); v = merge2(v, x); }
+                const bool any = v.b != 0xffffffffu;
+                const int bestDist = (int)(v.b >> 16);
+                const uint32_t cb = __shfl_sync(0xffffffffu, c, (lane & 24) + (int)(v.b & 7u));
+                const uint32_t cs = __shfl_sync(0xffffffffu, c, (lane & 24) + (int)(v.s & 7u));
+                const int bestIdx = (int)(cb & 0xffffu);
+                bool accept = false;
+                if (any) {
+                    if (mode == 0) {
+                        accept = bestDist <= M_TH_HIGH;
+                        if (accept && v.s != 0xffffffffu && (cb >> 25) == (cs >> 25) && (float)bestDist > __fmul_rn(nn_ratio, (float)(int)(v.s >> 16))) accept = false;
+                    } else if (mode == 1) accept = bestDist <= M_TH_HIGH;
+                    else accept = bestDist <= max_dist;
+                }
+                const int blk = accept ? (mode == 2 ? 1 : (int)blocks[w]) : 0;
+                const int claim = (accept && blk) ? bestIdx : -1;
+                bool conflict = false;
+#pragma unroll
+                for (int i = 0; i < 3; ++i) { const int ci = __shfl_sync(0xffffffffu, claim, 8 * i); if (j > i && fr && ci >= 0 && (int)(c & 0xffffu) == ci) conflict = true; }
+                if (!__any_sync(0xffffffffu, conflict)) {
+                    done = true;
+                    const unsigned acc = __ballot_sync(0xffffffffu, accept && t == 0);
+                    const int slot = n_hist + __popc(acc & ((1u << lane) - 1u));
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {     // in point order: a later point overwrites an earlier, non-closing one on the same keypoint
+                        if (j == i && t == 0 && accept) {
+                            match[bestIdx] = w; occ[bestIdx] = (uint8_t)blk;
+                            if (mode == 2) { q_best_idx[w] = bestIdx; q_best_dist[w] = bestDist; }
+                            if (mode >= 1 && check_ori) { hist_idx[slot] = bestIdx; hist_bin[slot] = rot_bin(q_angle[w], F.angle[bestIdx]); }
+                        }
+                        __syncwarp();
+                    }
+                    nmatches += __popc(acc);
+                    if (mode >= 1) n_hist += __popc(acc);
+                }
+            }
+            if (!done) {
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) serial_one(base + 4 * h + jj, p0[4 * h + jj], p1[4 * h + jj], pre[4 * h + jj]);
+            }
         }
 #pragma unroll
         for (int k = 0; k < RP_G; ++k) { pre[k] = nxt[k]; p0[k] = n0[k]; p1[k] = n1[k]; }

@@ -182,3 +182,37 @@ def test_search_for_initialization(gm, idx, window, ratio, coarse):
     gm.mfNNratio = 0.8; gm.mbCheckOrientation = True
     if not coarse:
         assert n_o > 100
+
+
+def _repeat_points(d, k, n_keep):
+    """Every point k times in a row: neighbours in the visiting order compete for exactly the same keypoints, which is the case
+    the group-optimistic resolve kernel has to replay serially."""
+    out = {}
+    for key, v in d.items():
+        out[key] = np.repeat(v[:n_keep], k, axis=0) if isinstance(v, np.ndarray) and len(v) >= n_keep else v
+    return out
+
+
+@pytest.mark.parametrize("idx,k", [(0, 2), (1, 3), (3, 4)])
+def test_projection_searches_with_competing_neighbours(gm, idx, k):
+    """SearchByProjection(F, MapPoints), (Cur, Last) and the claiming variant when consecutive points want the same keypoint."""
+    f, mps, occ = synth.make_projection_scenario(2000, 2000, idx, coarse_desc=(idx == 3))
+    F = _frame(f)
+    mpk = _repeat_points(mps, k, 2000 // k)
+    mpk["blocks"] = (np.arange(len(mpk["blocks"])) % 3 != 0)          # mix of closing and non-closing points
+    n_g, m_g = gm.SearchByProjection(F, mpk, 3.0, occupied=occ)
+    n_o, m_o = orc.search_by_projection_mps(F, mpk, 3.0, gm.mfNNratio, occ)
+    assert n_g == n_o and np.array_equal(m_g, m_o), (idx, k, n_g, n_o, int((m_g != m_o).sum()))
+    assert n_o > 100
+    f2, last, cam = synth.make_lastframe_scenario(2000, idx)
+    F2 = _frame(f2)
+    lk = _repeat_points(last, k, 2000 // k)
+    n_g, m_g = gm.SearchByProjectionLastFrame(F2, lk, cam, 15.0, False, False)
+    n_o, m_o = orc.search_by_projection_last(F2, lk, cam, 15.0, False, False, gm.mbCheckOrientation)
+    assert n_g == n_o and np.array_equal(m_g, m_o), (idx, k, n_g, n_o)
+    f3, pts, occ3 = synth.make_projected_points_scenario(2000, 2000, idx, th=10.0, level_span=(1, 1), coarse_desc=(idx == 3))
+    F3 = _frame(f3)
+    pk = _repeat_points(pts, k, 2000 // k)
+    n_g, m_g, b_g = gm.SearchByProjectionClaiming(F3, pk, occ3, 100, check_ori=True)
+    n_o, m_o, b_o = orc.search_by_projection_claiming(F3, pk, occ3, 100, True)
+    assert n_g == n_o and np.array_equal(m_g, m_o) and np.array_equal(b_g, b_o), (idx, k, n_g, n_o)

@@ -1,8 +1,7 @@
 // sm_100a kernels of the ORB extractor (reference src/ORBextractor.cc).  Integer/byte work,
 // HBM- and ALU-bound; no tensor cores by design.
 //
-//   k_resize_level     ComputePyramid's cv::resize(INTER_LINEAR) 8u fixed point      :1172-1207
-//   k_gauss7           GaussianBlur(7x7, sigma 2, REFLECT_101) 8u fixed point         :1143-1145
+//   k_resize_level     cv::resize(INTER_LINEAR) 8u, untiled fallback for scale factors beyond the TMA box (pyramid_kernels.cu)
 //   k_fast_cells       per-cell FAST-9/16 + NMS + iniTh->minTh retry                  :785-865
 //   k_quadtree         DistributeOctTree / DivideNode as array-backed list emulation  :500-782
 //   k_orient_describe  IC_Angle + fastAtan2 + rBRIEF + final keypoint assembly        :77-164, 1141-1167
@@ -49,7 +48,8 @@ void launch_ingest(cudaStream_t s, const uint8_t* src, uint8_t* dst, int w, int 
 }
 
 // ------------------------------------------------------------------------------------------
-// Pyramid: level l <- level l-1, OpenCV 8u INTER_LINEAR (11-bit coefficients).  One thread
+// Pyramid, untiled fallback (scale factors whose source footprint exceeds the TMA box of k_resize_tma):
+// level l <- level l-1, OpenCV 8u INTER_LINEAR (11-bit coefficients).  One thread
 // produces 4 horizontally adjacent pixels of one row and stores them as one 32-bit word.  The
 // two source rows are read as aligned words; a (pixel, right neighbour) byte pair is pulled out
 // with one PRMT and weighted with one DP2A (the two 16-bit horizontal coefficients of a pixel are
@@ -124,95 +124,6 @@ __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr,
         }
         // rows are pitch-padded to a multiple of 64 bytes, so the full word is always in bounds
         *reinterpret_cast<uint32_t*>(D + (size_t)y * dst.pitch + x4) = out;
-    }
-}
-
-// ------------------------------------------------------------------------------------------
-// 7x7 Gaussian, sigma 2, BORDER_REFLECT_101 at the level's own edge, OpenCV >= 4 fixed point:
-// Q0.8 taps {18,34,48,56,48,34,18}; horizontal Q8.8 (u16), vertical Q16.16, (v + 2^15) >> 16.
-// CTA tile 128 x 64; a thread owns a 4-pixel-wide strip of 8 rows and slides a 7-row window of
-// horizontal sums held in registers down its strip.  Horizontal sums are two DP4A per pixel on
-// byte windows assembled with PRMT from three aligned shared-memory words.
-#define BLUR_TW 128
-#define BLUR_TH 64
-#define BLUR_RW ((BLUR_TW + 8) / 4)  // words per staged row: 4 bytes of halo (3 used) on each side
-__device__ __forceinline__ int reflect101(int p, int len) {
-    if (len == 1) return 0;
-    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
-    return p;
-}
-
-__global__ void __launch_bounds__(256) k_gauss7(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, const Plan P) {
-    __shared__ uint32_t raw[BLUR_TH + 6][BLUR_RW];
-    int l = 0;
-    while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].tile_off) ++l;
-    const LevelGeom& G = P.lv[l];
-    const int t = blockIdx.x - G.tile_off;
-    const int tyi = t / G.tiles_x;
-    const int tx = (t - tyi * G.tiles_x) * BLUR_TW, ty = tyi * BLUR_TH;
-    const uint8_t* S = pyr + G.off + (size_t)blockIdx.y * G.img_stride;
-    uint8_t* D = blur + G.off + (size_t)blockIdx.y * G.img_stride;
-    const int tid = threadIdx.x;
-    const int W = G.w, H = G.h;
-    // levels of at least 4 x 4 pixels need one reflection at most (halo of 3); tiny levels take the loop
-    const bool one_step = W >= 4 && H >= 4;
-    for (int i = tid; i < (BLUR_TH + 6) * BLUR_RW; i += 256) {
-        const int ry = (i * 241) >> 13, j = i - ry * BLUR_RW;   // i / 34 for i < 2380
-        int gy = ty + ry - 3;
-        if (one_step) { gy = gy < 0 ? -gy : gy; gy = gy >= H ? 2 * (H - 1) - gy : gy; gy = max(gy, 0); }
-        else gy = reflect101(min(gy, H + 2), H);
-        const int gx = tx - 4 + 4 * j;
-        const uint8_t* row = S + (size_t)gy * G.pitch;
-        uint32_t v;
-        if (gx >= 0 && gx + 3 < W) { cp_async4(&raw[ry][j], row + gx); continue; }   // asynchronous: no register staging, all loads in flight
-        if (one_step) {
-            v = 0;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                int x = gx + k;
-                x = x < 0 ? -x : x; x = x >= W ? 2 * (W - 1) - x : x; x = max(x, 0);
-                v |= (uint32_t)row[x] << (8 * k);
-            }
-        } else {
-            v = 0;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) v |= (uint32_t)row[reflect101(min(gx + k, W + 2), W)] << (8 * k);
-        }
-        raw[ry][j] = v;
-    }
-    cp_async_wait_all();
-    __syncthreads();
-    const int cx = tid & 31, r0 = (tid >> 5) * 8;
-    const int ox = tx + 4 * cx;
-    if (ox >= W || ty + r0 >= H) return;
-    const unsigned wA = 18u | (34u << 8) | (48u << 16) | (56u << 24), wB = 48u | (34u << 8) | (18u << 16);
-    uint32_t hs[7][4];
-#pragma unroll
-    for (int i = 0; i < 14; ++i) {
-        const uint32_t w0 = raw[r0 + i][cx], w1 = raw[r0 + i][cx + 1], w2 = raw[r0 + i][cx + 2];
-        uint32_t hn[4];
-        hn[0] = __dp4a(__byte_perm(w0, w1, 0x4321), wA, __dp4a(__byte_perm(w1, 0u, 0x4321), wB, 0u));
-        hn[1] = __dp4a(__byte_perm(w0, w1, 0x5432), wA, __dp4a(__byte_perm(w1, w2, 0x4432), wB, 0u));
-        hn[2] = __dp4a(__byte_perm(w0, w1, 0x6543), wA, __dp4a(__byte_perm(w1, w2, 0x5543), wB, 0u));
-        hn[3] = __dp4a(w1, wA, __dp4a(w2, wB, 0u));
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-#pragma unroll
-            for (int j = 0; j < 6; ++j) hs[j][k] = hs[j + 1][k];
-            hs[6][k] = hn[k];
-        }
-        if (i >= 6) {
-            const int oy = ty + r0 + i - 6;
-            if (oy < H) {
-                uint32_t out = 0;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint32_t v = 18u * (hs[0][k] + hs[6][k]) + 34u * (hs[1][k] + hs[5][k]) + 48u * (hs[2][k] + hs[4][k]) + 56u * hs[3][k];
-                    out |= ((v + 32768u) >> 16) << (8 * k);
-                }
-                *reinterpret_cast<uint32_t*>(D + (size_t)oy * G.pitch + ox) = out;
-            }
-        }
     }
 }
 
@@ -1096,13 +1007,9 @@ k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ b
 
 // ------------------------------------------------------------------------------------------
 // host-callable launchers (used by extractor.cu)
-void launch_resize(cudaStream_t s, uint8_t* pyr, const LevelGeom& src, const LevelGeom& dst, int batch) {
+void launch_resize_untiled(cudaStream_t s, uint8_t* pyr, const LevelGeom& src, const LevelGeom& dst, int batch) {
     dim3 block(64, 4), grid((dst.w + 255) / 256, (dst.h + 4 * RESIZE_ROWS - 1) / (4 * RESIZE_ROWS), batch);
     k_resize_level<<<grid, block, 0, s>>>(pyr, src, dst);
-}
-void launch_gauss(cudaStream_t s, const uint8_t* pyr, uint8_t* blur, const Plan& P, int batch) {
-    dim3 grid(P.total_tiles, batch);
-    k_gauss7<<<grid, 256, 0, s>>>(pyr, blur, P);
 }
 // Tile pitch variant: 192 bytes covers w_cell <= 39 (every level with >= 4 cell columns), 272 the rest (w_cell <= 59).
 static int fast_tile_pitch(const Plan& P) {

@@ -6,9 +6,9 @@
 #include <cstdio>
 #include <cstring>
 
-void launch_resize(cudaStream_t s, uint8_t* pyr, const LevelGeom& src, const LevelGeom& dst, int batch);
+void launch_resize(cudaStream_t s, uint8_t* pyr, const CUtensorMap* src_map, bool tma, const LevelGeom& src, const LevelGeom& dst, int b0, int batch);
 void launch_ingest(cudaStream_t s, const uint8_t* src, uint8_t* dst, int w, int h, int stride, size_t img_stride, int dst_pitch, size_t dst_img_stride, int batch);
-void launch_gauss(cudaStream_t s, const uint8_t* pyr, uint8_t* blur, const Plan& P, int batch);
+void launch_gauss(cudaStream_t s, const TmaMaps& maps, const uint8_t* pyr, uint8_t* blur, const Plan& P, int b0, int batch);
 cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch);
 cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefix, const uint32_t* stage, uint32_t* keys,
                             uint32_t* lvl_kp, int* lvl_cnt, int* lvl_ncand, int* status, const Plan& P, int batch);
@@ -170,6 +170,46 @@ void layout_for_batch(Plan& P, int batch) {
     }
 }
 
+// TMA descriptors over the level buffers of the current batch layout (orb_internal.h: TmaMaps).  The encoder is a
+// driver entry point; it is looked up through the runtime so that the library does not link libcuda.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn tma_encoder() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+int build_tma_maps(orb_extractor* e, int batch) {
+    EncodeTiledFn enc = tma_encoder();
+    if (!enc) { orb_set_error("cuTensorMapEncodeTiled not available from this driver"); return ORB_ERR_CUDA; }
+    const Plan& P = e->plan;
+    for (int l = 0; l < P.nlevels; ++l) {
+        const LevelGeom& G = P.lv[l];
+        const cuuint64_t dims[3] = {(cuuint64_t)G.w, (cuuint64_t)G.h, (cuuint64_t)batch};
+        const cuuint64_t strides[2] = {(cuuint64_t)G.pitch, (cuuint64_t)G.img_stride};
+        const cuuint32_t estr[3] = {1, 1, 1};
+        const cuuint32_t box_blur[3] = {ORB_BLUR_BOXW, ORB_BLUR_BOXH, 1}, box_rz[3] = {ORB_RZ_BOXW, ORB_RZ_BOXH, 1};
+        void* base = e->d_pyr + G.off;
+        CUresult r = enc(&e->tm_blur.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box_blur, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r == CUDA_SUCCESS)
+            r = enc(&e->tm_resize.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box_rz, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { orb_set_error("cuTensorMapEncodeTiled failed (code " + std::to_string((int)r) + ")"); return ORB_ERR_CUDA; }
+        // the staged source box of k_resize_tma covers scales up to 1.35 (x) and 1.33 (y); anything else takes the untiled kernel
+        e->rz_tma[l] = false;
+        if (l > 0) {
+            const LevelGeom& S = P.lv[l - 1];
+            e->rz_tma[l] = S.w >= G.w && S.h >= G.h && (double)S.w <= 1.35 * G.w && (double)S.h <= 1.33 * G.h;
+        }
+    }
+    return ORB_OK;
+}
+
 void free_buffers(orb_extractor* e) {
     cudaFree(e->d_pyr); cudaFree(e->d_blur); cudaFree(e->d_cell_cnt); cudaFree(e->d_cell_prefix); cudaFree(e->d_stage);
     cudaFree(e->d_keys); cudaFree(e->d_lvl_kp); cudaFree(e->d_lvl_cnt); cudaFree(e->d_lvl_ncand); cudaFree(e->d_kps);
@@ -191,7 +231,11 @@ int ensure_plan(orb_extractor* e, int w, int h, int batch) {
         return ORB_ERR_CAPACITY;
     }
     if (e->plan_w == w && e->plan_h == h) {
-        if (e->last_batch != batch) layout_for_batch(e->plan, batch);
+        if (e->last_batch != batch) {
+            layout_for_batch(e->plan, batch);
+            const int st = build_tma_maps(e, batch);
+            if (st != ORB_OK) { e->plan_w = e->plan_h = -1; return st; }
+        }
         e->last_batch = batch;
         return ORB_OK;
     }
@@ -221,6 +265,8 @@ int ensure_plan(orb_extractor* e, int w, int h, int batch) {
     ORB_CUDA(cudaStreamSynchronize(e->stream));
     layout_for_batch(P, batch);
     e->plan = P; e->plan_w = w; e->plan_h = h; e->last_batch = batch;
+    const int tst = build_tma_maps(e, batch);
+    if (tst != ORB_OK) { e->plan_w = e->plan_h = -1; return tst; }
     return ORB_OK;
 }
 
@@ -245,7 +291,7 @@ int run_pipeline(orb_extractor* e, int b0, int batch) {
     const bool T = e->timing;
     // event i is recorded BEFORE stage i; event 5 after the last extractor stage
     if (T) cudaEventRecord(e->ev_stage[0], s);
-    for (int l = 1; l < P.nlevels; ++l) { launch_resize(s, e->d_pyr, P.lv[l - 1], P.lv[l], batch); e->launches++; }
+    for (int l = 1; l < P.nlevels; ++l) { launch_resize(s, e->d_pyr, &e->tm_resize.lv[l - 1], e->rz_tma[l], Q.lv[l - 1], Q.lv[l], b0, batch); e->launches++; }
     if (T) cudaEventRecord(e->ev_stage[1], s);
     if (P.total_cells > 0) {
         ORB_CUDA(launch_fast(s, e->d_pyr, cell_cnt, stage, P, batch)); e->launches++;
@@ -254,7 +300,7 @@ int run_pipeline(orb_extractor* e, int b0, int batch) {
     ORB_CUDA(launch_quadtree(s, cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, e->d_status, P, batch));
     e->launches++;
     if (T) cudaEventRecord(e->ev_stage[3], s);
-    launch_gauss(s, e->d_pyr, e->d_blur, P, batch); e->launches++;
+    launch_gauss(s, e->tm_blur, e->d_pyr, e->d_blur, Q, b0, batch); e->launches++;
     if (T) cudaEventRecord(e->ev_stage[4], s);
     launch_orient_describe(s, e->d_pyr, e->d_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, batch);
     e->launches++;

@@ -1,6 +1,7 @@
 // Internal definitions shared by the extractor, stereo and matcher translation units.
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda.h>   // CUtensorMap only; the encoder is fetched with cudaGetDriverEntryPoint (no libcuda link)
 #include <stdint.h>
 #include <stddef.h>
 #include <string>
@@ -64,6 +65,19 @@ struct Plan {
     LevelGeom lv[ORB_MAX_LEVELS];
 };
 
+// TMA descriptors (cp.async.bulk.tensor): one 3-D map (x, y, image) per pyramid level over the pitched level
+// buffers; the box is the staged tile of the kernel that uses the map.  Out-of-image box elements are zero-filled by
+// the hardware; the kernels turn the zeros into BORDER_REFLECT_101 on edge tiles only.
+#define ORB_BLUR_TW 128                     // blur: output tile width / height, staged box = tile + halo
+#define ORB_BLUR_TH 64
+#define ORB_BLUR_BOXW (ORB_BLUR_TW + 32)    // x from tile_x - 16: the innermost box coordinate must be a multiple of 16 bytes (measured: illegal instruction otherwise)
+#define ORB_BLUR_BOXH (ORB_BLUR_TH + 6)
+#define ORB_RZ_DW 128                       // resize: destination tile, staged source box (scale <= 1.35 / 1.33, else the untiled kernel)
+#define ORB_RZ_DH 64
+#define ORB_RZ_BOXW 192
+#define ORB_RZ_BOXH 88
+struct TmaMaps { CUtensorMap lv[ORB_MAX_LEVELS]; };
+
 struct orb_extractor {
     int nfeatures = 0, nlevels = 0, ini_th = 0, min_th = 0;
     double scale_factor = 0;
@@ -78,6 +92,8 @@ struct orb_extractor {
     Plan plan;
     int plan_w = -1, plan_h = -1;
     int last_batch = 0;
+    TmaMaps tm_blur, tm_resize;     // rebuilt with the plan / batch layout
+    bool rz_tma[ORB_MAX_LEVELS] = {false};   // level l is resampled from l-1 by the TMA-staged kernel
 
     // device buffers (sized for max geometry x max_batch)
     uint8_t* d_pyr = nullptr;

@@ -3,7 +3,7 @@
 //
 //   k_resize_level     cv::resize(INTER_LINEAR) 8u, untiled fallback for scale factors beyond the TMA box (pyramid_kernels.cu)
 //   k_fast_cells       per-cell FAST-9/16 + NMS + iniTh->minTh retry                  :785-865
-//   k_quadtree         DistributeOctTree / DivideNode as array-backed list emulation  :500-782
+//   (k_quadtree: DistributeOctTree / DivideNode, quadtree_kernel.cu)
 //   k_orient_describe  IC_Angle + fastAtan2 + rBRIEF + final keypoint assembly        :77-164, 1141-1167
 #include "orb_internal.h"
 #include "sincosf_glibc.h"
@@ -397,457 +397,6 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
 }
 
 // ------------------------------------------------------------------------------------------
-// Quadtree.  One CTA per (level, image).  The reference's std::list<ExtractorNode> is emulated
-// with an array R holding the list in REVERSE order (push_front == append), compacted after
-// every pass; a node's keys are a contiguous run of packed candidates that is stably 4-way
-// partitioned between two ping-pong key buffers.  Equal-size ties of the sorted expansion phase
-// (reference :703 sorts pair<int, ExtractorNode*>, i.e. by heap address) use the canonical rule
-// "later-created node first" == higher index in R.
-#define QT_THREADS 256
-#define QT_WARPS (QT_THREADS / 32)
-#define QT_BIG 1024  // nodes with more keys are partitioned by the whole CTA
-
-struct QNode {
-    int start;             // first key (bit 31: which key buffer holds the keys)
-    int count;
-    short x0, x1, y0, y1;  // UL.x, UR.x, UL.y, BL.y
-};
-
-struct QtShared {
-    int warp_sums[QT_WARPS + 1];
-    int scal[8];
-    int big_cnt[4];
-    int big_wc[QT_WARPS][4];
-};
-
-// exclusive scan over the CTA of one value per thread; returns the exclusive prefix, total in *total
-__device__ __forceinline__ int block_excl_scan(int v, int* total, int* warp_sums) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int n = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += n;
-    }
-    if (lane == 31) warp_sums[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-        int w = lane < QT_WARPS ? warp_sums[lane] : 0;
-        int winc = w;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int n = __shfl_up_sync(0xffffffffu, winc, o);
-            if (lane >= o) winc += n;
-        }
-        if (lane < QT_WARPS) warp_sums[lane] = winc - w;
-        if (lane == 31) warp_sums[QT_WARPS] = winc;
-    }
-    __syncthreads();
-    const int res = inc - v + warp_sums[warp];
-    *total = warp_sums[QT_WARPS];
-    __syncthreads();
-    return res;
-}
-
-__device__ __forceinline__ int key_quadrant(uint32_t k, int sx, int sy) {
-    return (ORB_KEY_X(k) < sx ? 0 : 1) + (ORB_KEY_Y(k) < sy ? 0 : 2);
-}
-
-// stable 4-way partition of src[0..n) into dst by quadrant, done by one warp; returns counts in c[4]
-__device__ __forceinline__ void warp_partition4(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, int n, int sx, int sy, int (&c)[4]) {
-    const int lane = threadIdx.x & 31;
-    const unsigned lt = (1u << lane) - 1;
-    c[0] = c[1] = c[2] = c[3] = 0;
-    if (n <= 32) {
-        uint32_t k = 0; int q = -1;
-        if (lane < n) { k = src[lane]; q = key_quadrant(k, sx, sy); }
-        unsigned m[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { m[j] = __ballot_sync(0xffffffffu, q == j); c[j] = __popc(m[j]); }
-        if (q >= 0) {
-            int pos = 0;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) if (j < q) pos += c[j];
-            unsigned mq = q == 0 ? m[0] : q == 1 ? m[1] : q == 2 ? m[2] : m[3];
-            dst[pos + __popc(mq & lt)] = k;
-        }
-        return;
-    }
-    for (int i0 = 0; i0 < n; i0 += 32) {
-        const int i = i0 + lane;
-        const int q = i < n ? key_quadrant(src[i], sx, sy) : -1;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) c[j] += __popc(__ballot_sync(0xffffffffu, q == j));
-    }
-    int o[4] = {0, c[0], c[0] + c[1], c[0] + c[1] + c[2]};
-    for (int i0 = 0; i0 < n; i0 += 32) {
-        const int i = i0 + lane;
-        uint32_t k = 0; int q = -1;
-        if (i < n) { k = src[i]; q = key_quadrant(k, sx, sy); }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const unsigned m = __ballot_sync(0xffffffffu, q == j);
-            if (q == j) dst[o[j] + __popc(m & lt)] = k;
-            o[j] += __popc(m);
-        }
-    }
-}
-
-// same, by the whole CTA (all threads must call); counts returned in sh.big_cnt
-struct QuadrantOf { int sx, sy; __device__ __forceinline__ int operator()(uint32_t k) const { return key_quadrant(k, sx, sy); } };
-// root index of a key (reference :588): (int)(pt.x / hX), clamped to the 4 bins this partition supports
-struct RootOf { float hx; __device__ __forceinline__ int operator()(uint32_t k) const { return min((int)__fdiv_rn((float)ORB_KEY_X(k), hx), 3); } };
-template <class F>
-__device__ void block_partition4(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, int n, const F quad, QtShared& sh) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const unsigned lt = (1u << lane) - 1;
-    if (tid < 4) sh.big_cnt[tid] = 0;
-    __syncthreads();
-    int c[4] = {0, 0, 0, 0};
-    for (int i = tid; i < n; i += QT_THREADS) c[quad(src[i])]++;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        int v = c[j];
-#pragma unroll
-        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0 && v) atomicAdd(&sh.big_cnt[j], v);
-    }
-    __syncthreads();
-    int base[4] = {0, sh.big_cnt[0], sh.big_cnt[0] + sh.big_cnt[1], sh.big_cnt[0] + sh.big_cnt[1] + sh.big_cnt[2]};
-    for (int i0 = 0; i0 < n; i0 += QT_THREADS) {
-        const int i = i0 + tid;
-        uint32_t k = 0; int q = -1;
-        if (i < n) { k = src[i]; q = quad(k); }
-        unsigned m[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { m[j] = __ballot_sync(0xffffffffu, q == j); if (lane == 0) sh.big_wc[warp][j] = __popc(m[j]); }
-        __syncthreads();
-        if (q >= 0) {
-            int pos = base[q];
-            for (int w = 0; w < warp; ++w) pos += sh.big_wc[w][q];
-            const unsigned mq = q == 0 ? m[0] : q == 1 ? m[1] : q == 2 ? m[2] : m[3];
-            dst[pos + __popc(mq & lt)] = k;
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            int s = 0;
-            for (int w = 0; w < QT_WARPS; ++w) s += sh.big_wc[w][j];
-            base[j] += s;
-        }
-        __syncthreads();
-    }
-}
-
-// bitonic sort, descending, of n (power of two) 64-bit keys in shared memory
-__device__ void block_sort_desc(unsigned long long* a, int n) {
-    for (int k = 2; k <= n; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = threadIdx.x; i < n; i += QT_THREADS) {
-                const int ixj = i ^ j;
-                if (ixj > i) {
-                    const unsigned long long x = a[i], y = a[ixj];
-                    const bool up = (i & k) == 0;  // descending overall: "up" blocks keep larger first
-                    if (up ? (x < y) : (x > y)) { a[i] = y; a[ixj] = x; }
-                }
-            }
-            __syncthreads();
-        }
-    }
-}
-
-// Dynamic shared memory layout (cap = node_cap_max, p2 = next pow2 >= cap):
-//   QNode nodeA[cap] | QNode nodeB[cap] | int par[cap] | int cc[cap*4] | int pre_ne[cap+1] | int pre_g[cap] |
-//   int flag[cap] | u64 sortk[p2]
-__global__ void __launch_bounds__(QT_THREADS)
-k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, const uint32_t* __restrict__ stage,
-           uint32_t* __restrict__ keys, uint32_t* __restrict__ lvl_kp, int* __restrict__ lvl_cnt, int* __restrict__ lvl_ncand,
-           int* __restrict__ status, const Plan P, const int cap, const int p2) {
-    extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ QtShared sh;
-    const int l = blockIdx.x, b = blockIdx.y;
-    const LevelGeom& G = P.lv[l];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-
-    QNode* cur = reinterpret_cast<QNode*>(smem);
-    QNode* nxt = cur + cap;
-    int* par = reinterpret_cast<int*>(nxt + cap);
-    int* cc = par + cap;
-    int* pre_ne = cc + 4 * cap;
-    int* pre_g = pre_ne + cap + 1;
-    int* flag = pre_g + cap;
-    unsigned long long* sortk = reinterpret_cast<unsigned long long*>(smem + (((size_t)((uint8_t*)(flag + cap) - smem) + 7) & ~(size_t)7));
-
-    const int n_cells = G.n_cols * G.n_rows;
-    const int* ccnt = cell_cnt + (size_t)b * P.total_cells + G.cell_off;
-    int* cpre = cell_prefix + (size_t)b * P.total_cells + G.cell_off;
-    const uint32_t* stg = stage + (size_t)b * P.stage_per_image + G.stage_off;
-    uint32_t* kbuf0 = keys + (size_t)b * 2 * P.stage_per_image + G.stage_off;
-    uint32_t* kbuf1 = kbuf0 + P.stage_per_image;
-    uint32_t* out = lvl_kp + (size_t)b * P.kp_cap + G.kp_off;
-
-    // ---- 0. ordered gather of the per-cell FAST lists (cells row-major) into key buffer 0
-    int carry = 0;
-    for (int c0 = 0; c0 < n_cells; c0 += QT_THREADS) {
-        const int c = c0 + tid;
-        const int v = c < n_cells ? ccnt[c] : 0;
-        int tot;
-        const int ex = block_excl_scan(v, &tot, sh.warp_sums);
-        if (c < n_cells) cpre[c] = carry + ex;
-        carry += tot;
-    }
-    const int n = carry;
-    __syncthreads();
-    // one thread per cell (lists are short; a warp per cell would serialise n_cells / 8 dependent round trips)
-    for (int c = tid; c < n_cells; c += QT_THREADS) {
-        const int cnt = ccnt[c], o = cpre[c];
-        const uint32_t* s = stg + (size_t)c * G.cell_cap;
-#pragma unroll 4
-        for (int i = 0; i < cnt; ++i) kbuf0[o + i] = s[i];
-    }
-    if (tid == 0) lvl_ncand[b * ORB_MAX_LEVELS + l] = n;
-    __syncthreads();
-    if (n == 0) { if (tid == 0) lvl_cnt[b * ORB_MAX_LEVELS + l] = 0; return; }
-
-    // ---- 1. root nodes (reference :562-607): key -> root (int)(x / hX), stable
-    const int N = G.n_feat;
-    int size = 0;
-    {
-        const int n_ini = G.n_ini;
-        const float hX = G.h_x;
-        if (n_ini <= 4) {
-            // one stable 4-way partition by root index
-            block_partition4(kbuf0, kbuf1, n, RootOf{hX}, sh);
-            if (tid == 0) {
-                int run = 0;
-                for (int r = 0; r < n_ini; ++r) {
-                    QNode nd;
-                    nd.start = run | (int)0x80000000;
-                    nd.count = sh.big_cnt[r];
-                    nd.x0 = (short)(int)(hX * (float)r);
-                    nd.x1 = (short)(int)(hX * (float)(r + 1));
-                    nd.y0 = 0;
-                    nd.y1 = (short)G.win_h;
-                    nxt[r] = nd;  // list order; reversed below
-                    run += nd.count;
-                }
-            }
-        } else {
-        int run = 0;
-        for (int r = 0; r < n_ini; ++r) {
-            int seg_begin = run;
-            for (int i0 = 0; i0 < n; i0 += QT_THREADS) {
-                const int i = i0 + tid;
-                uint32_t k = 0; int f = 0;
-                if (i < n) { k = kbuf0[i]; f = ((int)((float)ORB_KEY_X(k) / hX) == r); }
-                int tot;
-                const int ex = block_excl_scan(f, &tot, sh.warp_sums);
-                if (f) kbuf1[run + ex] = k;
-                run += tot;
-            }
-            if (tid == 0) {
-                QNode nd;
-                nd.start = seg_begin | (int)0x80000000;
-                nd.count = run - seg_begin;
-                nd.x0 = (short)(int)(hX * (float)r);
-                nd.x1 = (short)(int)(hX * (float)(r + 1));
-                nd.y0 = 0;
-                nd.y1 = (short)G.win_h;
-                nxt[r] = nd;  // list order; reversed below
-            }
-        }
-        }
-        __syncthreads();
-        // drop empty roots, reverse into cur
-        if (tid == 0) {
-            int m = 0;
-            for (int r = n_ini - 1; r >= 0; --r) if (nxt[r].count > 0) cur[m++] = nxt[r];
-            sh.scal[0] = m;
-        }
-        __syncthreads();
-        size = sh.scal[0];
-    }
-
-    // ---- 2. expansion passes
-    bool sorted_phase = false;
-    bool finish = false;
-    while (!finish) {
-        // a. parents in processing order
-        int np = 0;
-        if (!sorted_phase) {
-            int carry2 = 0;
-            for (int i0 = 0; i0 < size; i0 += QT_THREADS) {
-                const int i = i0 + tid;
-                const int f = (i < size && cur[i].count > 1) ? 1 : 0;
-                int tot;
-                const int ex = block_excl_scan(f, &tot, sh.warp_sums);
-                if (f) flag[i] = carry2 + ex;  // ascending rank, flipped below
-                carry2 += tot;
-            }
-            np = carry2;
-            __syncthreads();
-            for (int i = tid; i < size; i += QT_THREADS)
-                if (cur[i].count > 1) par[np - 1 - flag[i]] = i;
-        } else {
-            int carry2 = 0;
-            for (int i0 = 0; i0 < size; i0 += QT_THREADS) {
-                const int i = i0 + tid;
-                const int f = (i < size && cur[i].count > 1) ? 1 : 0;
-                int tot;
-                const int ex = block_excl_scan(f, &tot, sh.warp_sums);
-                if (f) sortk[carry2 + ex] = ((unsigned long long)(unsigned)cur[i].count << 32) | (unsigned)i;
-                carry2 += tot;
-            }
-            np = carry2;
-            int np2 = 1;
-            while (np2 < np) np2 <<= 1;
-            for (int i = np + tid; i < np2; i += QT_THREADS) sortk[i] = 0ull;
-            __syncthreads();
-            block_sort_desc(sortk, np2);
-            for (int i = tid; i < np; i += QT_THREADS) par[i] = (int)(sortk[i] & 0xffffffffu);
-        }
-        __syncthreads();
-        if (np == 0) break;  // every node holds one key: list cannot grow
-
-        // b. partition every parent's keys into the other key buffer
-        int big = 0;
-        for (int k = tid; k < np; k += QT_THREADS) big |= cur[par[k]].count > QT_BIG;
-        big = __syncthreads_or(big);
-        for (int k = 0; big && k < np; ++k) {  // big nodes: whole CTA (uniform branch)
-            const QNode nd = cur[par[k]];
-            if (nd.count <= QT_BIG) continue;
-            const int st = nd.start & 0x7fffffff;
-            const bool in1 = nd.start < 0;
-            const uint32_t* src = (in1 ? kbuf1 : kbuf0) + st;
-            uint32_t* dst = (in1 ? kbuf0 : kbuf1) + st;
-            const int sx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), sy = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
-            block_partition4(src, dst, nd.count, QuadrantOf{sx, sy}, sh);
-            if (tid < 4) cc[4 * k + tid] = sh.big_cnt[tid];
-            __syncthreads();
-        }
-        for (int k = warp; k < np; k += QT_WARPS) {
-            const QNode nd = cur[par[k]];
-            if (nd.count > QT_BIG) continue;
-            const int st = nd.start & 0x7fffffff;
-            const bool in1 = nd.start < 0;
-            const uint32_t* src = (in1 ? kbuf1 : kbuf0) + st;
-            uint32_t* dst = (in1 ? kbuf0 : kbuf1) + st;
-            const int sx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), sy = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
-            int c[4];
-            warp_partition4(src, dst, nd.count, sx, sy, c);
-            if (lane < 4) cc[4 * k + lane] = lane == 0 ? c[0] : lane == 1 ? c[1] : lane == 2 ? c[2] : c[3];
-        }
-        __syncthreads();
-
-        // c. prefix of non-empty children and of list growth, in processing order
-        int carry_ne = 0;
-        for (int k0 = 0; k0 < np; k0 += QT_THREADS) {
-            const int k = k0 + tid;
-            int ne = 0;
-            if (k < np) ne = (cc[4 * k] > 0) + (cc[4 * k + 1] > 0) + (cc[4 * k + 2] > 0) + (cc[4 * k + 3] > 0);
-            int tot;
-            const int ex = block_excl_scan(ne, &tot, sh.warp_sums);
-            if (k < np) { pre_ne[k] = carry_ne + ex; pre_g[k] = carry_ne + ex + ne - (k + 1); }
-            carry_ne += tot;
-        }
-        if (tid == 0) { pre_ne[np] = carry_ne; sh.scal[1] = np; }
-        __syncthreads();
-        // pre_g[k] = size growth after dividing parents 0..k (inclusive)
-        int ncom = np;
-        if (sorted_phase) {
-            for (int k = tid; k < np; k += QT_THREADS)
-                if (size + pre_g[k] >= N && (k == 0 || size + pre_g[k - 1] < N)) atomicMin(&sh.scal[1], k + 1);
-            __syncthreads();
-            ncom = sh.scal[1];
-        }
-
-        // d. next list = surviving nodes (same relative order) ++ children in creation order
-        for (int i = tid; i < size; i += QT_THREADS) flag[i] = 1;
-        __syncthreads();
-        for (int k = tid; k < ncom; k += QT_THREADS) flag[par[k]] = 0;
-        __syncthreads();
-        int n_surv = 0;
-        for (int i0 = 0; i0 < size; i0 += QT_THREADS) {
-            const int i = i0 + tid;
-            const int f = i < size ? flag[i] : 0;
-            int tot;
-            const int ex = block_excl_scan(f, &tot, sh.warp_sums);
-            if (f) nxt[n_surv + ex] = cur[i];
-            n_surv += tot;
-        }
-        const int n_children = pre_ne[ncom];
-        int my_expand = 0;
-        for (int k = tid; k < ncom; k += QT_THREADS) {
-            const QNode nd = cur[par[k]];
-            const int hx = (nd.x1 - nd.x0 + 1) >> 1, hy = (nd.y1 - nd.y0 + 1) >> 1;
-            const int sx = nd.x0 + hx, sy = nd.y0 + hy;
-            const int flip = (nd.start & 0x80000000) ^ 0x80000000;
-            int st = nd.start & 0x7fffffff;
-            int pos = n_surv + pre_ne[k];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int c = cc[4 * k + q];
-                if (c > 0) {
-                    QNode ch;
-                    ch.start = st | flip;
-                    ch.count = c;
-                    ch.x0 = (short)((q & 1) ? sx : nd.x0);
-                    ch.x1 = (short)((q & 1) ? nd.x1 : sx);
-                    ch.y0 = (short)((q & 2) ? sy : nd.y0);
-                    ch.y1 = (short)((q & 2) ? nd.y1 : sy);
-                    nxt[pos++] = ch;
-                    my_expand += c > 1;
-                }
-                st += c;
-            }
-        }
-        int n_expand;
-        block_excl_scan(my_expand, &n_expand, sh.warp_sums);
-        const int new_size = n_surv + n_children;
-        if (new_size > cap) { if (tid == 0) atomicExch(status, ORB_ERR_INTERNAL); break; }
-        { QNode* t = cur; cur = nxt; nxt = t; }
-        __syncthreads();
-
-        // e. termination (reference :688-757)
-        if (new_size >= N || new_size == size) finish = true;
-        else if (!sorted_phase && new_size + 3 * n_expand > N) sorted_phase = true;
-        size = new_size;
-    }
-
-    // ---- 3. best response per node (first maximum wins), emitted in list order.  Small nodes: one
-    // thread each; nodes with many keys: one warp each.
-    for (int i = tid; i < size; i += QT_THREADS) {
-        const QNode nd = cur[i];
-        if (nd.count > 64) continue;
-        const uint32_t* src = ((nd.start < 0) ? kbuf1 : kbuf0) + (nd.start & 0x7fffffff);
-        uint32_t bk = src[0];
-#pragma unroll 4
-        for (int j = 1; j < nd.count; ++j) {
-            const uint32_t k = src[j];
-            if ((k >> 24) > (bk >> 24)) bk = k;
-        }
-        out[size - 1 - i] = bk;
-    }
-    for (int i = warp; i < size; i += QT_WARPS) {
-        const QNode nd = cur[i];
-        if (nd.count <= 64) continue;
-        const uint32_t* src = ((nd.start < 0) ? kbuf1 : kbuf0) + (nd.start & 0x7fffffff);
-        unsigned long long best = 0ull;
-        for (int j = lane; j < nd.count; j += 32) {
-            const uint32_t k = src[j];
-            const unsigned long long v = ((unsigned long long)(k >> 24) << 32) | (unsigned)(0x7fffffff - j);
-            best = v > best ? v : best;
-        }
-#pragma unroll
-        for (int o = 16; o; o >>= 1) {
-            const unsigned long long v = __shfl_xor_sync(0xffffffffu, best, o);
-            best = v > best ? v : best;
-        }
-        if (lane == 0) out[size - 1 - i] = src[0x7fffffff - (int)(best & 0xffffffffu)];
-    }
-    if (tid == 0) lvl_cnt[b * ORB_MAX_LEVELS + l] = size;
-}
-
-// ------------------------------------------------------------------------------------------
 // Orientation + descriptor + final keypoint record.  One warp per keypoint slot.
 __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     // cv::fastAtan2, float32, every operation individually rounded
@@ -1042,27 +591,6 @@ cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint3
     }
     dim3 grid(P.total_groups, batch);
     kern<<<grid, FAST_THREADS, tot, s>>>(pyr, cell_cnt, stage, P, tb, sb);
-    return cudaSuccess;
-}
-size_t quadtree_smem(int cap, int* p2_out) {
-    int p2 = 1;
-    while (p2 < cap) p2 <<= 1;
-    *p2_out = p2;
-    size_t bytes = (size_t)cap * (2 * sizeof(QNode) + 4 + 16 + 4 + 4 + 4) + 4 + 8;
-    bytes = (bytes + 7) & ~(size_t)7;
-    return bytes + (size_t)p2 * 8;
-}
-cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefix, const uint32_t* stage, uint32_t* keys,
-                            uint32_t* lvl_kp, int* lvl_cnt, int* lvl_ncand, int* status, const Plan& P, int batch) {
-    int cap = 0;
-    for (int l = 0; l < P.nlevels; ++l) cap = max(cap, P.lv[l].node_cap);
-    int p2;
-    const size_t bytes = quadtree_smem(cap, &p2);
-    if (bytes > 200 * 1024) return cudaErrorInvalidConfiguration;
-    cudaError_t e = cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-    if (e != cudaSuccess) return e;
-    dim3 grid(P.nlevels, batch);
-    k_quadtree<<<grid, QT_THREADS, bytes, s>>>(cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, status, P, cap, p2);
     return cudaSuccess;
 }
 void launch_orient_describe(cudaStream_t s, const uint8_t* pyr, const uint8_t* blur, const uint32_t* lvl_kp, const int* lvl_cnt,

@@ -146,6 +146,8 @@ int build_plan(const orb_extractor& e, int w, int h, Plan& P, Needs& need, std::
         off += G.img_stride;  // scaled by batch when laid out (levels are batch-major, see layout())
         ncap_max = std::max(ncap_max, G.node_cap);
         if (l > 0) {
+            G.rz_qx = (unsigned)(((unsigned long long)P.lv[l - 1].w << 16) / (unsigned)G.w);
+            G.rz_qy = (unsigned)(((unsigned long long)P.lv[l - 1].h << 16) / (unsigned)G.h);
             tbytes += 4 * 64 + (((size_t)G.w + 3) & ~(size_t)3) * 8 + (size_t)G.h * 8 + 64;
             if (tabs) {
                 HostTables& T = (*tabs)[l];

@@ -51,6 +51,7 @@ struct LevelGeom {
     const short* alpha;
     const int* yofs;
     const short* beta;
+    unsigned rz_qx, rz_qy;      // floor(2^16 * w[l-1] / w[l]), same for h: tile origin of the TMA-staged resize without a division
     float sf;                   // mvScaleFactor[level]
     float patch_size;           // (float)(int)(PATCH_SIZE * sf)
 };

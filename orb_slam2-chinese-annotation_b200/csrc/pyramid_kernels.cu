@@ -40,21 +40,22 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 
 // ------------------------------------------------------------------------------------------
 // Pyramid: level l <- level l-1, OpenCV 8u INTER_LINEAR (11-bit coefficients).
-// One CTA produces a 128 x 64 destination tile from one TMA-staged source box.  The box origin is
-// (floor(dx0 * sw / dw) rounded down to 16 bytes, floor(dy0 * sh / dh)), a lower bound of xofs[dx0] / yofs[dy0] for
-// scales >= 1, so the box load does not wait for a table lookup (the innermost TMA coordinate must be a multiple of
-// 16 bytes).  Scales up to 1.35 (x) / 1.33 (y) fit the 192 x 88 box (host-checked; larger scales take
-// k_resize_level in extract_kernels.cu).  A lane owns 4 adjacent destination columns and walks down 8 rows; the
+// One CTA (4 warps) produces a 128 x 64 destination tile from one TMA-staged source box.  The box origin is a lower
+// bound of (xofs[dx0], yofs[dy0]) computed from the tile index alone ((dx0 * floor(2^16 sw / dw)) >> 16, rounded down
+// to 16 bytes: the innermost TMA coordinate must be a multiple of 16 bytes), so thread 0 issues the load before any
+// table lookup.  Scales up to 1.35 (x) / 1.33 (y) fit the 192 x 88 box (host-checked; larger scales take
+// k_resize_level in extract_kernels.cu).  A lane owns 4 adjacent destination columns and walks down 16 rows; the
 // horizontal pass of a source row ((pixel, right neighbour) byte pair cut out of two aligned shared-memory words with
 // one PRMT, weighted with one IDP.2A) is kept and reused by the next destination row, which shares that source row
 // in 5 of 6 cases at scale 1.2.  The vertical blend is two IMAD.HI.
-#define RZ_ROWS 8   // destination rows per warp
+#define RZ_WARPS 4
+#define RZ_ROWS (ORB_RZ_DH / RZ_WARPS)   // destination rows per warp
 __device__ __forceinline__ unsigned mad_u32(unsigned a, unsigned b, unsigned c) {   // stays on the FMA pipe (the ALU pipe is the busy one here)
     unsigned r;
     asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
     return r;
 }
-struct RzCols {   // per-lane column state: word offsets of the two 8-byte windows, PRMT selectors, packed weights
+struct RzCols {   // per-lane column state: byte offsets of the two 8-byte windows, PRMT selectors, packed weights
     int wa, wb;
     unsigned sel[4], al[4];
 };
@@ -68,27 +69,31 @@ __device__ __forceinline__ void rz_row(const uint8_t* __restrict__ row, const Rz
     h[3] = __dp2a_lo(c.al[3], __byte_perm(b0, b1, c.sel[3]), 0u) >> 4;
 }
 
-__global__ void __launch_bounds__(256) k_resize_tma(const __grid_constant__ CUtensorMap src_map, uint8_t* __restrict__ pyr,
-                                                    const LevelGeom src, const LevelGeom dst, const int b0) {
+__global__ void __launch_bounds__(RZ_WARPS * 32) k_resize_tma(const __grid_constant__ CUtensorMap src_map, uint8_t* __restrict__ pyr,
+                                                              const LevelGeom src, const LevelGeom dst, const int b0) {
     __shared__ __align__(128) uint8_t tile[ORB_RZ_BOXH * ORB_RZ_BOXW + 16];   // +16: the last lane's 8-byte window may overhang
+    __shared__ uint2 rows[ORB_RZ_DH];   // per destination row: byte offsets of its two source rows in the tile | packed vertical weights
     __shared__ uint64_t bar;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int dx0 = blockIdx.x * ORB_RZ_DW, dy0 = blockIdx.y * ORB_RZ_DH;
-    const int sx0 = (int)(((long long)dx0 * src.w) / dst.w) & ~15, sy0 = (int)(((long long)dy0 * src.h) / dst.h);
-    if (tid == 0) mbar_init(&bar, 1);
-    __syncthreads();
+    const int sx0 = (int)(((unsigned)dx0 * dst.rz_qx) >> 16) & ~15, sy0 = (int)(((unsigned)dy0 * dst.rz_qy) >> 16);
     if (tid == 0) {
+        mbar_init(&bar, 1);
         mbar_expect_tx(&bar, ORB_RZ_BOXH * ORB_RZ_BOXW);
         tma_load_3d(tile, &src_map, &bar, sx0, sy0, b0 + (int)blockIdx.z);
     }
-    // coefficient tables (padded to 4 entries, 16-byte aligned) while the box is in flight
+    // coefficient tables while the box is in flight
+    if (tid < ORB_RZ_DH) {
+        const int y = min(dy0 + tid, dst.h - 1);
+        const int r0 = dst.yofs[y] - sy0;                   // 0 <= yofs <= src.h - 1 for scales >= 1
+        const int r1 = min(r0 + 1, src.h - 1 - sy0);
+        rows[tid] = make_uint2((unsigned)(r0 * ORB_RZ_BOXW) | ((unsigned)(r1 * ORB_RZ_BOXW) << 16), reinterpret_cast<const unsigned*>(dst.beta)[y]);
+    }
     const int x4 = dx0 + 4 * lane;
     const int y0 = dy0 + RZ_ROWS * warp;
     const bool live = x4 < dst.w && y0 < dst.h;
     RzCols c;
-    int yo[RZ_ROWS];
-    unsigned bw[RZ_ROWS];
-    if (live) {
+    if (live) {   // tables are padded to 4 entries and 16-byte aligned
         const int4 xo = reinterpret_cast<const int4*>(dst.xofs)[x4 >> 2];
         const uint4 al = reinterpret_cast<const uint4*>(dst.alpha)[x4 >> 2];
         // source columns step by 1 or 2 per destination column (scale <= 1.35): pixels 0,1 and pixels 2,3 each fit an 8-byte window
@@ -97,41 +102,39 @@ __global__ void __launch_bounds__(256) k_resize_tma(const __grid_constant__ CUte
         const unsigned j0 = sa & 3, j1 = (xo.y - sx0) - c.wa, j2 = sb & 3, j3 = (xo.w - sx0) - c.wb;
         c.sel[0] = j0 | ((j0 + 1) << 4); c.sel[1] = j1 | ((j1 + 1) << 4); c.sel[2] = j2 | ((j2 + 1) << 4); c.sel[3] = j3 | ((j3 + 1) << 4);
         c.al[0] = al.x; c.al[1] = al.y; c.al[2] = al.z; c.al[3] = al.w;
-#pragma unroll
-        for (int r = 0; r < RZ_ROWS; ++r) {
-            const int y = min(y0 + r, dst.h - 1);
-            yo[r] = dst.yofs[y];
-            bw[r] = reinterpret_cast<const unsigned*>(dst.beta)[y];
-        }
     }
+    __syncthreads();   // row table and barrier initialisation visible to everyone
     mbar_wait(&bar, 0);
     if (!live) return;
     uint8_t* D = pyr + dst.off + (size_t)(b0 + blockIdx.z) * dst.img_stride + (size_t)y0 * dst.pitch + x4;
-    int cur = -1;            // source row whose horizontal pass is in hc
+    const int nrows = min(RZ_ROWS, dst.h - y0);
+    unsigned cur = 0xffffffffu;   // tile offset of the source row whose horizontal pass is in hc
     unsigned hc[4];
 #pragma unroll
     for (int r = 0; r < RZ_ROWS; ++r) {
-        if (y0 + r >= dst.h) break;
-        const int r0 = min(max(yo[r], 0), src.h - 1) - sy0, r1 = min(max(yo[r] + 1, 0), src.h - 1) - sy0;
+        if (r >= nrows) break;
+        const uint2 rw = rows[RZ_ROWS * warp + r];
+        const unsigned o0 = rw.x & 0xffffu, o1 = rw.x >> 16;
         unsigned ha[4];
-        if (r0 == cur) {   // warp-uniform
+        if (o0 == cur) {   // warp-uniform
 #pragma unroll
             for (int i = 0; i < 4; ++i) ha[i] = hc[i];
         } else {
-            rz_row(tile + r0 * ORB_RZ_BOXW, c, ha);
+            rz_row(tile + o0, c, ha);
         }
-        if (r1 != r0) rz_row(tile + r1 * ORB_RZ_BOXW, c, hc);
+        if (o1 != o0) rz_row(tile + o1, c, hc);
         else {
 #pragma unroll
             for (int i = 0; i < 4; ++i) hc[i] = ha[i];
         }
-        cur = r1;
-        const unsigned B0 = (bw[r] & 0xffffu) << 16, B1 = bw[r] & 0xffff0000u;   // weights pre-shifted: umulhi(v, b << 16) == (b * v) >> 16
+        cur = o1;
+        const unsigned B0 = rw.y << 16, B1 = rw.y & 0xffff0000u;   // weights pre-shifted: umulhi(v, b << 16) == (b * v) >> 16
         unsigned v[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) v[i] = (__umulhi(ha[i], B0) + __umulhi(hc[i], B1) + 2u) >> 2;   // convex combination of bytes: no clamp
         // rows are pitch-padded to a multiple of 64 bytes, so the full word is always in bounds
-        *reinterpret_cast<uint32_t*>(D + (size_t)r * dst.pitch) = mad_u32(mad_u32(v[3], 256u, v[2]), 65536u, mad_u32(v[1], 256u, v[0]));
+        *reinterpret_cast<uint32_t*>(D) = mad_u32(mad_u32(v[3], 256u, v[2]), 65536u, mad_u32(v[1], 256u, v[0]));
+        D += dst.pitch;
     }
 }
 
@@ -250,7 +253,7 @@ void launch_resize(cudaStream_t s, uint8_t* pyr, const CUtensorMap* src_map, boo
         return;
     }
     dim3 grid((dst.w + ORB_RZ_DW - 1) / ORB_RZ_DW, (dst.h + ORB_RZ_DH - 1) / ORB_RZ_DH, batch);
-    k_resize_tma<<<grid, 256, 0, s>>>(*src_map, pyr, src, dst, b0);
+    k_resize_tma<<<grid, RZ_WARPS * 32, 0, s>>>(*src_map, pyr, src, dst, b0);
 }
 void launch_gauss(cudaStream_t s, const TmaMaps& maps, const uint8_t* pyr, uint8_t* blur, const Plan& P, int b0, int batch) {
     dim3 grid(P.total_tiles, batch);

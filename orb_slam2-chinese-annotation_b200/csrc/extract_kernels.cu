@@ -154,9 +154,10 @@ __device__ __forceinline__ unsigned gt_bytes(unsigned ad, unsigned k) {  // bit 
     return ad | ((ad & 0x7f7f7f7fu) + k);
 }
 
-// FAST score of two pixels at once.  e[k] = ring[k] - centre on packed signed 16-bit lanes.
-// dark = max over the 16 arcs of min over 9 contiguous e; bright = -(min over arcs of max over 9).
-__device__ __forceinline__ unsigned fast_score_x2(const unsigned (&e)[16]) {
+// FAST score of two pixels at once.  e[k] = ring[k] (raw bytes) on packed 16-bit lanes, c = the two centres.
+// min / max commute with the subtraction of the centre, so the arc network runs on the raw ring:
+// dark = (max over the 16 arcs of min over 9 contiguous e) - c; bright = c - (min over arcs of max over 9).
+__device__ __forceinline__ unsigned fast_score_x2(const unsigned (&e)[16], const unsigned c) {
     unsigned lo3[16], hi3[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
@@ -175,8 +176,8 @@ __device__ __forceinline__ unsigned fast_score_x2(const unsigned (&e)[16]) {
         dk = __vimax3_s16x2(dk, a9[k], a9[k + 1]);
         br = __vimin3_s16x2(br, z9[k], z9[k + 1]);
     }
-    // max(dark, -bright) - 1 on both lanes; -min(br, z9[15]) = max(-br, -z9[15])
-    return __vsub2(__vimax3_s16x2(__vmaxs2(dk, a9[15]), __vneg2(br), __vneg2(z9[15])), 0x00010001u);
+    // max(dark, bright) - 1 on both lanes
+    return __vsub2(__vmaxs2(__vsub2(__vmaxs2(dk, a9[15]), c), __vsub2(c, __vmins2(br, z9[15]))), 0x00010001u);
 }
 
 // Dynamic shared memory: tile (rows x TP bytes, 16-byte aligned like the level) | score map
@@ -293,15 +294,15 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
         const int ya = ia >> 8, xa = ia & 0xff, yb = ib >> 8, xb = ib & 0xff;
         const uint8_t* ca = tile + (ya + 3) * TP + xa + 3;
         const uint8_t* cb = tile + (yb + 3) * TP + xb + 3;
-        const unsigned negv = __vneg2((unsigned)ca[0] | ((unsigned)cb[0] << 16));
+        const unsigned cen = (unsigned)ca[0] | ((unsigned)cb[0] << 16);
         unsigned e[16];
-#define RING(k_, off_) e[k_] = __vadd2((unsigned)ca[off_] | ((unsigned)cb[off_] << 16), negv)
+#define RING(k_, off_) e[k_] = (unsigned)ca[off_] | ((unsigned)cb[off_] << 16)
         RING(0, 3 * TP);       RING(1, 3 * TP + 1);   RING(2, 2 * TP + 2);    RING(3, TP + 3);
         RING(4, 3);            RING(5, -TP + 3);      RING(6, -2 * TP + 2);   RING(7, -3 * TP + 1);
         RING(8, -3 * TP);      RING(9, -3 * TP - 1);  RING(10, -2 * TP - 2);  RING(11, -TP - 3);
         RING(12, -3);          RING(13, TP - 3);      RING(14, 2 * TP - 2);   RING(15, 3 * TP - 1);
 #undef RING
-        const unsigned s2 = fast_score_x2(e);
+        const unsigned s2 = fast_score_x2(e, cen);
         const int sa = (int)(short)(s2 & 0xffffu), sb = (int)(short)(s2 >> 16);
         const bool fa = va && sa >= t, fb = vb && sb >= t;
         if (fa) sc[(ya + 1) * SP + xa + 1] = (uint8_t)sa;

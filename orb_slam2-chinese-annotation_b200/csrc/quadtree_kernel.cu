@@ -357,13 +357,14 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
     __syncthreads();
     for (int i = tid; i < n; i += QT_THREADS) atomicMax(&best_s[leaf[i]], ORB_KEY_S(kbuf[i]));
     __syncthreads();
+    const unsigned mw = 0xffffffffu / (unsigned)G.w_cell + 1u, mh = 0xffffffffu / (unsigned)G.h_cell + 1u;   // exact quotients for x < 4096, d < 64
     for (int i = tid; i < n; i += QT_THREADS) {
         const uint32_t k = kbuf[i];
         const int nl = (int)leaf[i];
         if (ORB_KEY_S(k) != best_s[nl]) continue;
         // original order = (cell row, cell column, row in cell, column in cell); cell interiors start 3 pixels into the window
         const int xr = ORB_KEY_X(k) - 3, yr = ORB_KEY_Y(k) - 3;
-        const int cj = xr / G.w_cell, ci = yr / G.h_cell;
+        const int cj = (int)__umulhi((unsigned)xr, mw), ci = (int)__umulhi((unsigned)yr, mh);
         const unsigned ord = ((unsigned)ci << 20) | ((unsigned)cj << 12) | ((unsigned)(yr - ci * G.h_cell) << 6) | (unsigned)(xr - cj * G.w_cell);
         atomicMin(&best_k[nl], ((unsigned long long)ord << 32) | k);
     }

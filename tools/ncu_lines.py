@@ -1,29 +1,25 @@
 #!/usr/bin/env python
-"""Per-source-line stall-sample shares from an ncu report (source page, cuda view).
-  tools/ncu_lines.py <prof.ncu-rep> <kernel-regex> [top]"""
-import csv, subprocess, sys
-rep, kern = sys.argv[1:3]
-top = int(sys.argv[3]) if len(sys.argv) > 3 else 30
-txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", "regex:" + kern, "--print-source", "sass,cuda"],
-                     capture_output=True, text=True).stdout
+"""Per-source-line hot spots of an .ncu-rep captured with --import-source on (kernels compiled -lineinfo).
+   tools/ncu_lines.py <file.ncu-rep> [top_n]   -> lines sorted by line number, with their share of executed
+   warp instructions and of stall samples (first captured launch of each kernel)."""
+import csv, subprocess, sys, collections
+rep = sys.argv[1]; top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
 rows = list(csv.reader(txt.splitlines()))
-hi = [i for i, r in enumerate(rows) if r and r[0] == "Line No"][0]
-h = rows[hi]
-isamp, iinst, isrc, iln = h.index("# Samples"), h.index("Instructions Executed"), h.index("Source"), h.index("Line No")
-data = [r for r in rows[hi + 1:] if len(r) > isamp and r[iln].isdigit()]
-# only the first captured launch of the kernel
-seen = set(); first = []
-for r in data:
-    if r[iln] in seen and False: pass
-    first.append(r)
-agg = {}
-def _int(v):
-    try: return int(v)
-    except ValueError: return None
-for r in first:
-    if _int(r[isamp]) is None or _int(r[iinst]) is None: continue
-    a = agg.setdefault(int(r[iln]), [0, 0, r[isrc]]); a[0] += int(r[isamp]); a[1] += int(r[iinst])
-ts = sum(a[0] for a in agg.values()); ti = sum(a[1] for a in agg.values())
-print("samples", ts, "warp instr", ti)
-for ln, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
-    print("%5d  samp %.3f  instr %.3f  %s" % (ln, a[0] / ts, a[1] / max(ti, 1), a[2].strip()[:100]))
+hdr = None; agg = collections.OrderedDict(); src = {}; fn = None; done = set()
+for r in rows:
+    if r and r[0] == "Function Name":
+        if agg: break
+        fn = r[1]; continue
+    if r and r[0] == "Line No": hdr = r; continue
+    if not hdr or len(r) < len(hdr): continue
+    ln = r[0]
+    if not ln.isdigit(): continue
+    ie = hdr.index("Instructions Executed"); ss = hdr.index("# Samples")
+    a = agg.setdefault(int(ln), [0, 0]); a[0] += int(r[ie]) if r[ie].isdigit() else 0; a[1] += int(r[ss]) if r[ss].isdigit() else 0
+    src[int(ln)] = r[1]
+ti = sum(v[0] for v in agg.values()) or 1; ts = sum(v[1] for v in agg.values()) or 1
+print("#", fn); print("# total warp instructions %d, samples %d" % (ti, ts))
+keep = sorted(agg, key=lambda k: -agg[k][1])[:top]
+for k in sorted(keep):
+    print("%5d inst %5.1f%% smp %5.1f%%  %s" % (k, 100.0 * agg[k][0] / ti, 100.0 * agg[k][1] / ts, src[k].strip()[:120]))

@@ -1,18 +1,29 @@
 #!/usr/bin/env python
-"""Benchmark of the ORB front-end hot path (BASELINE.json: "ORB extract+match frames/s @1241x376
-2000kp").  One step = one batch of KITTI-shape stereo frames through: extract(left), extract(right),
-ComputeStereoMatches.  A frame is one stereo pair.
+"""Benchmark of the ORB front-end hot path (BASELINE.json: "ORB extract+match frames/s @1241x376 2000kp").
+One step = one batch of KITTI-shape stereo frames through: extract(left), extract(right), ComputeStereoMatches.
+A frame is one stereo pair.
 
   python bench.py --gpus N --steps K --warmup W              our CUDA path (N>1: under torchrun)
   python bench.py --impl reference ...                        the reference's CPU path on host cores
 
-Prints ONE JSON line (see the keys below).  `value` is measured with inputs resident in HBM,
-`e2e` through the C ABI with host buffers (pinned H2D and D2H inside the timed region).
+Prints ONE JSON line.  `value` is measured with inputs resident in HBM, `e2e` through the C ABI with host buffers
+(pinned H2D and D2H inside the timed region).  Beside the headline the same line carries (untimed for `value`):
+  roofline      every kernel against ITS measured roof: HBM copy bandwidth (MEASURED_PEAKS.json) for the pyramid and the
+                blur, the measured ALU-pipe issue rate (profiles/MEASURED_INT_PEAKS.json, tools/peaks_int.cu) for FAST,
+                quadtree, rBRIEF and stereo; numerators of the INT kernels are instruction counts read by ncu at this
+                batch size (profiles/r2_ncu_counts.json, tools/ncu_counts.py)
+  sustained     the same step repeated for >= 2 s
+  parity_checked  pairs of the timed batch compared bit for bit with the CPU oracle after the timing
+  latency       BASELINE configs[1] at batch 1 and configs[0] (one 640x480 frame) through the C++ drop-in classes,
+                timed per frame like Examples/Stereo/stereo_kitti.cc:80-122, beside the reference's own CPU latency
+  configs       configs[2] (EuRoC 752x480 / 1200, 256 pairs) and configs[4] (3840x2160 / 8000, 128 frames per GPU)
+  matching      configs[3] (2000 x 2000 descriptors per pair, 1024 pairs)
 """
 import argparse
 import ctypes as C
 import importlib
 import json
+import math
 import os
 import subprocess
 import sys
@@ -25,35 +36,67 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 PKG = "orb_slam2-chinese-annotation_b200"
 
-W, H, NFEAT = 1241, 376, 2000            # Examples/Stereo/KITTI00-02.yaml
-MBF, FX = 386.1448, 718.856
 N_LEVELS, SCALE, INI_TH, MIN_TH = 8, 1.2, 20, 7
-WORKLOAD = "kitti_stereo_1241x376_2000kp (BASELINE.json configs[1])"
 METRIC = "ORB extract+match frames/s @1241x376 2000kp"
-POOL = 16                                # distinct synthetic stereo pairs, tiled to the batch
+CFG = {
+    # Examples/Stereo/KITTI00-02.yaml:8,25,38-51
+    "kitti": dict(w=1241, h=376, nfeat=2000, mbf=386.1448, fx=718.856, stereo=True, pool=16,
+                  workload="kitti_stereo_1241x376_2000kp (BASELINE.json configs[1])"),
+    # Examples/Stereo/EuRoC.yaml:18-19,25,88-101
+    "euroc": dict(w=752, h=480, nfeat=1200, mbf=47.906, fx=435.205, stereo=True, pool=16,
+                  workload="euroc_stereo_752x480_1200kp, 256 pairs per GPU (BASELINE.json configs[2])"),
+    "uhd": dict(w=3840, h=2160, nfeat=8000, mbf=0.0, fx=2000.0, stereo=False, pool=2,
+                workload="uhd_mono_3840x2160_8000kp, 128 frames per GPU = 1024 over 8 GPUs (BASELINE.json configs[4])"),
+    # Examples/Monocular/TUM1.yaml:30-43
+    "tum": dict(w=640, h=480, nfeat=1000, mbf=40.0, fx=517.3, stereo=False, pool=8,
+                workload="tum_mono_640x480_1000kp, one frame (BASELINE.json configs[0])"),
+}
+CONFIG_KEYS = {"workload": CFG["kitti"]["workload"], "frame": "stereo pair (2 images)", "image": "1241x376 8u", "nfeatures": 2000,
+               "levels": N_LEVELS, "scale_factor": SCALE, "fast_thresholds": [INI_TH, MIN_TH]}
 CPU_DESC = {
-    "reference": "extraction = the reference's own src/ORBextractor.cc compiled verbatim (oracle/_ref, OpenCV primitives = scalar "
-                 "restatements pinned to cv2 4.13), stereo = line-by-line port of Frame::ComputeStereoMatches",
+    "reference": "extraction = the reference's own src/ORBextractor.cc compiled verbatim (oracle/_ref), its OpenCV primitives being SCALAR "
+                 "restatements pinned to cv2 4.13 (a SIMD OpenCV build is roughly 2x faster: BASELINE.md section 4), stereo = line-by-line "
+                 "port of Frame::ComputeStereoMatches",
     "port": "CPU oracle: restatement of the reference ORBextractor + ComputeStereoMatches (oracle/_ref not built on this box)",
 }
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per image of the ncu --set full capture named below (batch 32)
-NCU_TRAFFIC_SOURCE = "profiles/r1_v6_full_fast_cells.txt"
-NCU_TRAFFIC_BYTES_PER_IMAGE = {"fast_cells": 1328000}   # (42.34 MB read + 0.13 MB written) / 32 images; algorithmic: 1.51 MB
+def level_sizes(w, h):
+    sf = [np.float32(1.0)]
+    for _ in range(1, N_LEVELS):
+        sf.append(np.float32(np.float64(sf[-1]) * np.float64(np.float32(SCALE))))
+    out = []
+    for s in sf:
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+    return out
 
 
-def algorithmic_bytes_per_image(n_kp):
-    """sum(levels) read + levels 1..7 written + blurred levels written + per-keypoint patches."""
-    sizes = [(1241, 376), (1034, 313), (862, 261), (718, 218), (598, 181), (499, 151), (416, 126), (346, 105)]
-    s = sum(w * h for w, h in sizes)
-    return s + (s - W * H) + s + n_kp * (749 + 961 + 32 + 28)
+def algorithmic_bytes(cfg, n_kp):
+    """SURVEY.md 8(d), per image: every level read once + levels 1..7 written + blurred levels written + per-keypoint patches;
+    and the same split per kernel."""
+    sz = level_sizes(cfg["w"], cfg["h"])
+    s = sum(a * b for a, b in sz)
+    s1 = s - cfg["w"] * cfg["h"]
+    per_kernel = {
+        "pyramid": (s - sz[-1][0] * sz[-1][1]) + s1,      # read levels 0..6 once, write levels 1..7
+        "fast_cells": s + 4 * 8 * n_kp,                    # read every level once, write candidate keys (about 8 per kept keypoint)
+        "quadtree": 3 * 4 * 8 * n_kp,                      # candidate keys: gather + leaf ids (lower bound)
+        "blur": 2 * s,                                     # read + write every level
+        "orient_describe": n_kp * (749 + 961 + 32 + 28),
+    }
+    return s + s1 + s + n_kp * (749 + 961 + 32 + 28), per_kernel, s
 
 
-def synth_pool():
+def synth_pool(cfg):
     synth = importlib.import_module(PKG + ".synth")
-    pairs = [synth.make_stereo_pair(W, H, i, fx=FX) for i in range(POOL)]
+    pairs = [synth.make_stereo_pair(cfg["w"], cfg["h"], i, fx=cfg["fx"]) for i in range(cfg["pool"])]
     return np.stack([p[0] for p in pairs]), np.stack([p[1] for p in pairs])
+
+
+def tile_pool(pool, B, rank):
+    reps = (B + len(pool) - 1) // len(pool)
+    return np.roll(np.tile(pool, (reps, 1, 1))[:B], rank, axis=0)   # every rank works on its own frames (weak scaling)
 
 
 class ClockSampler:
@@ -136,62 +179,102 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
-# ------------------------------------------------------------------------------------------ CPU
-def cpu_pairs_per_s(n_pairs, threads, left, right):
-    """Times the CPU oracle (restatement of the reference's ORBextractor + ComputeStereoMatches) on
-    n_pairs stereo frames using `threads` host threads (ctypes releases the GIL)."""
+# ------------------------------------------------------------------------------------------ CPU (oracle = checker / baseline only)
+def _orc():
     sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import orc  # TEST INFRASTRUCTURE used here only as the timed CPU baseline
+    import orc  # TEST INFRASTRUCTURE: used here only as the timed CPU baseline and the post-timing checker
+    return orc
 
+
+def cpu_units_per_s(cfg, n_units, threads, left, right):
+    """Times the reference's CPU path (oracle/_ref when built, else the oracle port) on n_units frames (stereo pairs, or
+    single images for a mono config) using `threads` host threads (ctypes releases the GIL)."""
+    orc = _orc()
     use_ref = orc.ref_available()   # the reference's own ORBextractor.cc compiled verbatim (oracle/_ref)
-    tabs = orc.Extractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH).tables()
+    nf = cfg["nfeat"]
+    tabs = orc.Extractor(nf, SCALE, N_LEVELS, INI_TH, MIN_TH).tables()
+    pool = len(left)
 
-    def work(tid, out):
-        if use_ref:
-            ol = orc.RefExtractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH); orr = orc.RefExtractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH)
-        else:
-            ol = orc.Extractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH); orr = orc.Extractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH)
+    def work(tid, out, lat):
+        mk = orc.RefExtractor if use_ref else orc.Extractor
+        ol = mk(nf, SCALE, N_LEVELS, INI_TH, MIN_TH); orr = mk(nf, SCALE, N_LEVELS, INI_TH, MIN_TH)
         n = 0
-        for i in range(tid, n_pairs, threads):
-            kl, dl = ol.extract(left[i % POOL]); kr, dr = orr.extract(right[i % POOL])
-            if use_ref:
-                orc.stereo_match_ref(ol, orr, kl, dl, kr, dr, tabs["sf"], tabs["inv_sf"], MBF, 0.0, FX)
-            else:
-                orc.stereo_match(ol, orr, kl, dl, kr, dr, MBF, 0.0, FX)
+        for i in range(tid, n_units, threads):
+            t0 = time.perf_counter()
+            kl, dl = ol.extract(left[i % pool])
+            if cfg["stereo"]:
+                kr, dr = orr.extract(right[i % pool])
+                if use_ref:
+                    orc.stereo_match_ref(ol, orr, kl, dl, kr, dr, tabs["sf"], tabs["inv_sf"], cfg["mbf"], 0.0, cfg["fx"])
+                else:
+                    orc.stereo_match(ol, orr, kl, dl, kr, dr, cfg["mbf"], 0.0, cfg["fx"])
+            lat.append(time.perf_counter() - t0)
             n += 1
         out[tid] = n
 
     out = [0] * threads
-    ts = [threading.Thread(target=work, args=(t, out)) for t in range(threads)]
+    lats = [[] for _ in range(threads)]
+    ts = [threading.Thread(target=work, args=(t, out, lats[t])) for t in range(threads)]
     t0 = time.perf_counter()
     for t in ts:
         t.start()
     for t in ts:
         t.join()
     dt = time.perf_counter() - t0
-    return sum(out) / dt, dt, ("reference" if use_ref else "port")
+    return sum(out) / dt, dt, ("reference" if use_ref else "port"), [x for l in lats for x in l]
+
+
+def cpu_stereo_latency(cfg, n_pairs, left, right):
+    """The reference's own per-frame shape: left and right extraction on two threads (src/Frame.cc:81-84), then
+    ComputeStereoMatches; steady clock per frame, median / mean like Examples/Stereo/stereo_kitti.cc:113-122."""
+    orc = _orc()
+    use_ref = orc.ref_available()
+    nf = cfg["nfeat"]
+    mk = orc.RefExtractor if use_ref else orc.Extractor
+    ol = mk(nf, SCALE, N_LEVELS, INI_TH, MIN_TH); orr = mk(nf, SCALE, N_LEVELS, INI_TH, MIN_TH)
+    tabs = orc.Extractor(nf, SCALE, N_LEVELS, INI_TH, MIN_TH).tables()
+    ms = []
+    for i in range(n_pairs + 2):
+        res = {}
+        t0 = time.perf_counter()
+        if cfg["stereo"]:
+            tl = threading.Thread(target=lambda: res.__setitem__("l", ol.extract(left[i % len(left)])))
+            tr = threading.Thread(target=lambda: res.__setitem__("r", orr.extract(right[i % len(left)])))
+            tl.start(); tr.start(); tl.join(); tr.join()
+            kl, dl = res["l"]; kr, dr = res["r"]
+            if use_ref:
+                orc.stereo_match_ref(ol, orr, kl, dl, kr, dr, tabs["sf"], tabs["inv_sf"], cfg["mbf"], 0.0, cfg["fx"])
+            else:
+                orc.stereo_match(ol, orr, kl, dl, kr, dr, cfg["mbf"], 0.0, cfg["fx"])
+        else:
+            ol.extract(left[i % len(left)])
+        if i >= 2:
+            ms.append((time.perf_counter() - t0) * 1e3)
+    return {"median_ms": float(np.median(ms)), "mean_ms": float(np.mean(ms)), "frames": n_pairs, "threads": 2 if cfg["stereo"] else 1,
+            "kind": "reference" if use_ref else "port"}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    left, right = synth_pool()
+    cfg = CFG["kitti"]
+    left, right = synth_pool(cfg)
     cores = os.cpu_count() or 1
     per_step = 12 * cores   # ~0.1 core-seconds per pair: a step is about 1.5 s of wall clock on all cores
-    cpu_pairs_per_s(min(per_step, cores), cores, left, right)  # page in
+    cpu_units_per_s(cfg, min(per_step, cores), cores, left, right)  # page in
     for _ in range(args.warmup):
-        cpu_pairs_per_s(per_step, cores, left, right)
+        cpu_units_per_s(cfg, per_step, cores, left, right)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        kind = cpu_pairs_per_s(per_step, cores, left, right)[2]
+        kind = cpu_units_per_s(cfg, per_step, cores, left, right)[2]
     dt = time.perf_counter() - t0
     val = per_step * args.steps / dt
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frame": "stereo pair", "pairs_per_step": per_step},
+        "config": CONFIG_KEYS, "pairs_per_step": per_step,
         "cpu_baseline": {"value": val, "unit": "frames/s", "cores": cores, "kind": kind,
                          "sample": "%d stereo pairs per step x %d steps, %d host threads; %s"
                                    % (per_step, args.steps, cores, CPU_DESC[kind])},
@@ -201,6 +284,295 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------ GPU
+class Job:
+    """One workload (a CFG entry) on this rank's GPU: handles, device-resident inputs, timing helpers."""
+
+    def __init__(self, cfg, B, local, rank, dist):
+        import torch
+        self.torch = torch
+        ext = importlib.import_module(PKG + ".extractor")
+        self.stereo_mod = importlib.import_module(PKG + ".stereo")
+        self.capi = importlib.import_module(PKG + ".capi")
+        self.cfg, self.B, self.local, self.rank, self.dist = cfg, B, local, rank, dist
+        self.left_pool, self.right_pool = synth_pool(cfg)
+        self.hl = tile_pool(self.left_pool, B, rank)
+        self.hr = tile_pool(self.right_pool, B, rank) if cfg["stereo"] else None
+        mk = lambda: ext.ORBextractor(cfg["nfeat"], SCALE, N_LEVELS, INI_TH, MIN_TH, max_width=cfg["w"], max_height=cfg["h"],
+                                      max_batch=B, device=local)
+        self.gl = mk()
+        self.gr = mk() if cfg["stereo"] else None
+        self.cap = self.gl.kp_cap
+        self.dl = torch.from_numpy(self.hl).cuda()
+        self.dr = torch.from_numpy(self.hr).cuda() if cfg["stereo"] else None
+        torch.cuda.synchronize()
+        self.sl = torch.cuda.ExternalStream(self.gl.stream, device=local)
+
+    def close(self):
+        self.gl.close()
+        if self.gr:
+            self.gr.close()
+        self.dl = self.dr = None
+        self.torch.cuda.empty_cache()
+
+    def step_device(self):
+        c = self.cfg
+        self.gl.extract_device(self.dl.data_ptr(), self.B, c["w"], c["h"])
+        if c["stereo"]:
+            self.gr.extract_device(self.dr.data_ptr(), self.B, c["w"], c["h"])
+            self.stereo_mod.compute_stereo_matches_device(self.gl, self.gr, c["mbf"], c["fx"], 0.0, batch=self.B)
+
+    def sync_all(self):
+        self.gl.sync()
+        if self.gr:
+            self.gr.sync()
+        self.torch.cuda.synchronize()
+        if self.dist is not None:
+            self.dist.barrier()
+
+    def launches(self):
+        return self.gl.launch_count + (self.gr.launch_count if self.gr else 0)
+
+    def max_over_ranks(self, ms):
+        t = self.torch.tensor([ms], dtype=self.torch.float64, device="cuda")
+        if self.dist is not None:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def time_device(self, steps, warmup):
+        """CUDA events on the left handle's stream (the stereo stage makes the left stream wait for the right one, and the next
+        step's right extraction waits for the left stream: the left stream covers the whole step chain); max over ranks."""
+        torch = self.torch
+        for _ in range(warmup):
+            self.step_device()
+        self.sync_all()
+        l0 = self.launches()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record(self.sl)
+        for _ in range(steps):
+            self.step_device()
+        e1.record(self.sl)
+        self.sync_all()
+        return self.max_over_ranks(e0.elapsed_time(e1)), self.launches() - l0
+
+    def stage_times(self, n_prof=3):
+        """Per-stage event times, one handle at a time so that the other stream's kernels do not share the SMs."""
+        c = self.cfg
+        self.gl.set_timing(True)
+        if self.gr:
+            self.gr.set_timing(True)
+        acc = {}
+        for _ in range(n_prof):
+            self.gl.extract_device(self.dl.data_ptr(), self.B, c["w"], c["h"]); self.gl.sync()
+            sr = {}
+            if self.gr:
+                self.gr.extract_device(self.dr.data_ptr(), self.B, c["w"], c["h"]); self.gr.sync()
+                self.stereo_mod.compute_stereo_matches_device(self.gl, self.gr, c["mbf"], c["fx"], 0.0, batch=self.B); self.gl.sync()
+                sr = self.gr.stage_ms()
+            sl = self.gl.stage_ms()
+            for k in sl:
+                acc[k] = acc.get(k, 0.0) + sl[k] + (sr.get(k, 0.0) if not k.startswith("stereo") else 0.0)
+        self.gl.set_timing(False)
+        if self.gr:
+            self.gr.set_timing(False)
+        return {k: v / n_prof for k, v in acc.items() if c["stereo"] or not k.startswith("stereo")}
+
+    def e2e(self, steps):
+        """The call a user of the reference makes, batched, HOST buffers in and out: Frame::Frame(left, right) = ExtractORB x2 +
+        ComputeStereoMatches (src/Frame.cc:60-115) -> orb_stereo_frames; a mono config -> orb_extract_batch."""
+        torch, capi, c, B, cap = self.torch, self.capi, self.cfg, self.B, self.cap
+        L = capi.lib()
+        kp_sz = capi.KP_DTYPE.itemsize
+        pl = torch.from_numpy(self.hl).pin_memory()
+        sides = 2 if c["stereo"] else 1
+        o_k = [torch.empty((B, cap, kp_sz), dtype=torch.uint8).pin_memory() for _ in range(sides)]
+        o_d = [torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory() for _ in range(sides)]
+        o_n = [np.zeros(B, np.int32) for _ in range(3)]
+        if c["stereo"]:
+            pr = torch.from_numpy(self.hr).pin_memory()
+            o_u = torch.empty((B, cap), dtype=torch.float32).pin_memory(); o_z = torch.empty((B, cap), dtype=torch.float32).pin_memory()
+
+            def step_host():
+                capi.check(L.orb_stereo_frames(self.gl.handle, self.gr.handle, C.c_void_p(pl.data_ptr()), C.c_void_p(pr.data_ptr()), B, c["w"], c["h"],
+                                               c["w"], C.c_size_t(c["w"] * c["h"]), C.c_float(c["mbf"]), C.c_float(0.0), C.c_float(c["fx"]),
+                                               C.c_void_p(o_k[0].data_ptr()), C.c_void_p(o_d[0].data_ptr()), capi.ptr(o_n[0]),
+                                               C.c_void_p(o_k[1].data_ptr()), C.c_void_p(o_d[1].data_ptr()), capi.ptr(o_n[1]),
+                                               C.c_void_p(o_u.data_ptr()), C.c_void_p(o_z.data_ptr()), cap))
+        else:
+            def step_host():
+                capi.check(L.orb_extract_batch(self.gl.handle, C.c_void_p(pl.data_ptr()), B, c["w"], c["h"], c["w"], C.c_size_t(c["w"] * c["h"]),
+                                               C.c_void_p(o_k[0].data_ptr()), C.c_void_p(o_d[0].data_ptr()), cap, capi.ptr(o_n[0])))
+        for _ in range(3):
+            step_host()
+        self.sync_all()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            step_host()
+        self.sync_all()
+        ms = self.max_over_ranks((time.perf_counter() - t0) * 1e3)
+        h2d = sides * B * c["w"] * c["h"]
+        # slot rows are downloaded whole (cap == the handle's kp_cap): keypoints + descriptors per side, uRight, depth, counts
+        d2h = int(B * cap * (sides * (kp_sz + 32) + (8 if c["stereo"] else 0)) + sides * B * 4 + 8)
+        self.host_out = (o_k, o_d, o_n, (o_u, o_z) if c["stereo"] else None)
+        return ms, h2d, d2h
+
+
+def check_parity(job, picks):
+    """Bit-equality of `picks` frames of the batch just timed (outputs of the last host-buffer step) against the CPU oracle."""
+    orc = _orc()
+    c = job.cfg
+    o_k, o_d, o_n, st = job.host_out
+    kp_dt = job.capi.KP_DTYPE
+    ol = orc.Extractor(c["nfeat"], SCALE, N_LEVELS, INI_TH, MIN_TH); orr = orc.Extractor(c["nfeat"], SCALE, N_LEVELS, INI_TH, MIN_TH)
+    ok = 0
+    for b in picks:
+        okl, odl = ol.extract(job.hl[b])
+        n = int(o_n[0][b])
+        gk = o_k[0].numpy()[b].view(kp_dt).reshape(-1)[:n]
+        good = n == len(okl) and all(np.array_equal(gk[f], okl[f]) for f in ("x", "y", "angle", "response", "octave", "size"))
+        good = good and np.array_equal(o_d[0].numpy()[b][:n], odl)
+        if c["stereo"]:
+            okr, odr = orr.extract(job.hr[b])
+            m = int(o_n[1][b])
+            good = good and m == len(okr) and np.array_equal(o_d[1].numpy()[b][:m], odr)
+            our, odp, _, _ = orc.stereo_match(ol, orr, okl, odl, okr, odr, c["mbf"], 0.0, c["fx"])
+            good = good and np.array_equal(st[0].numpy()[b][:n], our) and np.array_equal(st[1].numpy()[b][:n], odp)
+        if not good:
+            raise SystemExit("bench.py: parity check FAILED on frame %d of the timed batch" % b)
+        ok += 1
+    return ok
+
+
+def load_json(path, default):
+    try:
+        return json.load(open(os.path.join(ROOT, path)))
+    except Exception:
+        return default
+
+
+def roofline_block(cfg, B, stages, n_kp, clocks):
+    """Every stage against its own measured roof.  HBM: algorithmic bytes / event time / measured copy bandwidth.  INT: ALU-pipe
+    lane-operations counted by ncu at this batch size / event time / (measured ALU-pipe lanes per clock per SM x SMs x clock)."""
+    peaks = load_json("MEASURED_PEAKS.json", {})
+    ipk = load_json("profiles/MEASURED_INT_PEAKS.json", {})
+    counts = load_json("profiles/r2_ncu_counts.json", {})
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    hbm_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    sms = int(ipk.get("sms", 148))
+    lanes = float(ipk.get("tests", {}).get("lop3", {}).get("lanes_per_clk_per_sm", 64.0))
+    sm_mhz = clocks.get("sm_mhz") or 1965.0
+    alu_peak = lanes * sms * sm_mhz * 1e6 / 1e9      # G lane-ops/s
+    issue_peak = 128.0 * sms * sm_mhz * 1e6 / 1e9    # 4 schedulers x 32 lanes per clock per SM
+    _, bytes_k, _ = algorithmic_bytes(cfg, n_kp)
+    kernel_of = {"pyramid": "k_resize_tma", "fast_cells": "k_fast_cells", "quadtree": "k_quadtree", "blur": "k_gauss7_tma",
+                 "orient_describe": "k_orient_describe", "stereo_match": "k_stereo_match", "stereo_rows": "k_stereo_rows",
+                 "stereo_median": "k_stereo_median"}
+    bound_of = {"pyramid": "hbm", "blur": "hbm"}
+    per = {}
+    sides = 2 if cfg["stereo"] else 1
+    for k, ms in stages.items():
+        if ms <= 0:
+            continue
+        images = B * (1 if k.startswith("stereo") else sides)     # image (or pair) units behind this stage time
+        ent = {"ms_per_step": ms, "bound": bound_of.get(k, "int")}
+        if k in bytes_k:
+            a = bytes_k[k] * images / (ms * 1e-3) / 1e9
+            ent["hbm"] = {"alg_bytes_per_image": int(bytes_k[k]), "achieved_GBs": a, "frac": a / hbm}
+        cn = counts.get("kernels", {}).get(kernel_of.get(k, ""), None)
+        if cn and counts.get("workload") == cfg["workload"]:
+            a = cn["alu_lane_ops_per_unit"] * images / (ms * 1e-3) / 1e9
+            t = cn["thread_inst_per_unit"] * images / (ms * 1e-3) / 1e9
+            ent["int"] = {"alu_lane_ops_per_unit": cn["alu_lane_ops_per_unit"], "achieved_Gops": a, "frac": a / alu_peak,
+                          "issue_frac": t / issue_peak, "dram_bytes_per_unit_ncu": cn.get("dram_bytes_per_unit")}
+        per[k] = ent
+    dom = max(per, key=lambda k: per[k]["ms_per_step"])
+    d = per[dom]
+    if d["bound"] == "hbm":
+        top = {"bound": "hbm", "kernel": dom, "achieved": d["hbm"]["achieved_GBs"], "peak": hbm, "unit": "GB/s", "frac": d["hbm"]["frac"]}
+    elif "int" in d:
+        top = {"bound": "int", "kernel": dom, "achieved": d["int"]["achieved_Gops"], "peak": alu_peak,
+               "unit": "G lane-ops/s on the ALU pipe (ncu sm__inst_executed_pipe_alu x 32)", "frac": d["int"]["frac"]}
+    else:
+        top = {"bound": "int", "kernel": dom, "achieved": None, "peak": alu_peak, "unit": "G lane-ops/s on the ALU pipe", "frac": None,
+               "note": "profiles/r2_ncu_counts.json has no counts for this workload"}
+    cn = counts.get("kernels", {}).get(kernel_of.get(dom, ""), {}) if counts.get("workload") == cfg["workload"] else {}
+    units = B * (1 if dom.startswith("stereo") else 1)   # per launch: one handle, B images
+    top["traffic"] = (cn.get("dram_bytes_per_unit") * units) if cn.get("dram_bytes_per_unit") else None
+    top["traffic_source"] = counts.get("source")
+    top["peak_source"] = {"hbm": hbm_src, "int": "measured: profiles/MEASURED_INT_PEAKS.json (%g lanes/clk/SM x %d SMs) x sampled SM clock %.0f MHz"
+                          % (lanes, sms, sm_mhz)}
+    top["per_kernel"] = per
+    tot, _, _ = algorithmic_bytes(cfg, n_kp)
+    top["pipeline_hbm_frac"] = sides * B * tot / (sum(stages.values()) * 1e-3) / 1e9 / hbm
+    return top
+
+
+def run_latency(cfg_name, local):
+    """Batch 1 through the C++ drop-in classes (tools/latency_bench.cpp), beside the reference's CPU latency."""
+    cfg = CFG[cfg_name]
+    exe = os.path.join(ROOT, "tools", "build", "latency_bench")
+    if not os.path.exists(exe):
+        return {"unavailable": "tools/build/latency_bench not built"}
+    left, right = synth_pool(dict(cfg, pool=8))
+    path = "/tmp/orb_b200_latency_%s_%d.bin" % (cfg_name, os.getpid())
+    (np.concatenate([left.ravel(), right.ravel()]) if cfg["stereo"] else left.ravel()).tofile(path)
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES=vis.split(",")[local] if vis else str(local))
+    out = {}
+    try:
+        base = [exe, "stereo" if cfg["stereo"] else "mono", path, str(cfg["w"]), str(cfg["h"]), "8", str(cfg["nfeat"]), str(cfg["mbf"]), str(cfg["fx"]),
+                "200", "20"]
+        out["ours"] = json.loads(subprocess.run(base + ["0", "1"], capture_output=True, text=True, env=env, timeout=120).stdout)
+        out["ours_with_host_pyramid"] = json.loads(subprocess.run(base + ["1", "1"], capture_output=True, text=True, env=env, timeout=120).stdout)
+    except Exception as e:   # noqa
+        out["error"] = repr(e)
+    finally:
+        try:
+            os.remove(path)
+        except OSError:
+            pass
+    out["reference_cpu"] = cpu_stereo_latency(cfg, 12, left, right)
+    out["workload"] = cfg["workload"]
+    out["how"] = ("per frame, steady clock, 200 frames after 20 warm-ups (Examples/Stereo/stereo_kitti.cc:80-122); ours = ORB_SLAM2::ORBextractor::operator() "
+                  "on two threads + orb_stereo_match, host cv::Mat in, std::vector<cv::KeyPoint> / cv::Mat out; reference = two extraction threads + "
+                  "ComputeStereoMatches on the host CPU")
+    return out
+
+
+def run_extra(name, B, steps, local, rank, world, dist, cores):
+    """A further BASELINE.json config: device-resident and host-buffer throughput, HBM fraction, CPU sample."""
+    cfg = CFG[name]
+    job = Job(cfg, B, local, rank, dist)
+    ms, _ = job.time_device(steps, 3)
+    val = world * B * steps / (ms * 1e-3)
+    stages = job.stage_times(2)
+    _, _, counts = job.gl.download(min(B, 8))
+    n_kp = float(np.mean(counts))
+    e_steps = max(2, steps // 2)
+    e_ms, h2d, d2h = job.e2e(e_steps)
+    e_val = world * B * e_steps / (e_ms * 1e-3)
+    out = None
+    if rank == 0:
+        parity = check_parity(job, [0, B - 1] if cfg["w"] < 2000 else [0])
+        peaks = load_json("MEASURED_PEAKS.json", {})
+        hbm = float(peaks.get("hbm_gbs", 6650.0))
+        tot, bytes_k, _ = algorithmic_bytes(cfg, n_kp)
+        sides = 2 if cfg["stereo"] else 1
+        per = {k: {"ms_per_step": v, **({"hbm_frac": bytes_k[k] * sides * B / (v * 1e-3) / 1e9 / hbm} if k in bytes_k and v > 0 else {})}
+               for k, v in stages.items()}
+        n_cpu = cores * (2 if cfg["w"] < 2000 else 1)
+        cpu_val, cpu_dt, cpu_kind, _ = cpu_units_per_s(cfg, n_cpu, cores, job.left_pool, job.right_pool)
+        out = {"workload": cfg["workload"], "unit": "frames/s", "frame": "stereo pair" if cfg["stereo"] else "image",
+               "frames_per_step_per_gpu": B, "value": val, "ms_per_step": ms / steps, "steps": steps,
+               "e2e": {"value": e_val, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e_steps},
+               "avg_keypoints": n_kp, "stage_ms_per_step": per,
+               "pipeline_hbm_frac": sides * B * tot / (sum(stages.values()) * 1e-3) / 1e9 / hbm,
+               "alg_bytes_per_image": int(tot), "parity_checked": parity,
+               "cpu_baseline": {"value": cpu_val, "unit": "frames/s", "cores": cores, "kind": cpu_kind,
+                                "sample": "%d frames on %d host threads in %.1f s" % (n_cpu, cores, cpu_dt)}}
+    job.close()
+    return out
+
+
 def run_ours(args):
     import torch
     rank = int(os.environ.get("RANK", "0"))
@@ -223,168 +595,67 @@ def run_ours(args):
         finally:
             os.dup2(saved, 1); os.close(saved); os.close(devnull)
 
-    ext = importlib.import_module(PKG + ".extractor")
-    stereo = importlib.import_module(PKG + ".stereo")
-    capi = importlib.import_module(PKG + ".capi")
+    cfg = CFG["kitti"]
     B = args.batch
-    left, right = synth_pool()
-    reps = (B + POOL - 1) // POOL
-    # every rank works on its own frames (weak scaling); rotate the pool so ranks differ
-    hl = np.roll(np.tile(left, (reps, 1, 1))[:B], rank, axis=0)
-    hr = np.roll(np.tile(right, (reps, 1, 1))[:B], rank, axis=0)
+    warmup = max(args.warmup, 3)
+    cores = os.cpu_count() or 1
+    job = Job(cfg, B, local, rank, dist)
+    if args.profile_run:   # exactly two device-resident steps and nothing else (tools/ncu_counts.py captures these launches)
+        job.step_device(); job.step_device(); job.sync_all()
+        print(json.dumps({"profile_run": True, "steps": 2, "pairs_per_step": B, "workload": cfg["workload"]}), flush=True)
+        return
 
-    gl = ext.ORBextractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH, max_width=W, max_height=H, max_batch=B, device=local)
-    gr = ext.ORBextractor(NFEAT, SCALE, N_LEVELS, INI_TH, MIN_TH, max_width=W, max_height=H, max_batch=B, device=local)
-    cap = gl.kp_cap
-
-    # ---- device-resident inputs for `value`
-    dl = torch.from_numpy(hl).cuda(); dr = torch.from_numpy(hr).cuda()
-    torch.cuda.synchronize()
-
-    def step_device():
-        gl.extract_device(dl.data_ptr(), B, W, H)
-        gr.extract_device(dr.data_ptr(), B, W, H)
-        stereo.compute_stereo_matches_device(gl, gr, MBF, FX, 0.0, batch=B)
-
-    def sync_all():
-        gl.sync(); gr.sync(); torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-
-    sl = torch.cuda.ExternalStream(gl.stream, device=local)
-
-    for _ in range(max(args.warmup, 3)):
-        step_device()
-    sync_all()
-    l0 = gl.launch_count + gr.launch_count
+    # ---- headline: EXACTLY args.steps steps, device-resident inputs, CUDA events, max over ranks
+    job.time_device(0, warmup)
     sampler = ClockSampler(local)
-    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    sync_all()
-    # the stereo stage makes the left stream wait for the right stream, and the next step's right
-    # extraction waits for the left stream: timing on the left stream covers the whole step chain
-    e0.record(sl)
-    for _ in range(args.steps):
-        step_device()
-    e1.record(sl)
-    gr.sync()
-    sync_all()
-    ms_total = e0.elapsed_time(e1)
+    ms_total, launches = job.time_device(args.steps, 0)
     clocks = sampler.stop()
-    launches = (gl.launch_count + gr.launch_count - l0)
-    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
     value = world * B * args.steps / (ms_total * 1e-3)
 
-    # ---- per-stage event timing (separate, untimed-for-value pass) for the roofline object
-    gl.set_timing(True); gr.set_timing(True)
-    acc = {}
-    n_prof = 3
-    for _ in range(n_prof):
-        # serialised (one handle at a time) so that the per-stage event times are not inflated by
-        # the other stream's kernels sharing the SMs
-        gl.extract_device(dl.data_ptr(), B, W, H); gl.sync()
-        gr.extract_device(dr.data_ptr(), B, W, H); gr.sync()
-        stereo.compute_stereo_matches_device(gl, gr, MBF, FX, 0.0, batch=B); gl.sync()
-        sl_ms = gl.stage_ms(); sr_ms = gr.stage_ms()
-        for k in sl_ms:
-            acc[k] = acc.get(k, 0.0) + sl_ms[k] + (sr_ms[k] if not k.startswith("stereo") else 0.0)
-    gl.set_timing(False); gr.set_timing(False)
-    stages = {k: v / n_prof for k, v in acc.items()}   # ms per step, both images of the pairs
-    _, _, counts = gl.download(B)
+    # ---- the same step for >= 2 s (clocks settle, more clock samples)
+    s_steps = max(args.steps, int(math.ceil(2000.0 / (ms_total / args.steps))))
+    sampler = ClockSampler(local)
+    s_ms, _ = job.time_device(s_steps, 0)
+    s_clocks = sampler.stop()
+    sustained = {"value": world * B * s_steps / (s_ms * 1e-3), "unit": "frames/s", "steps": s_steps, "seconds": s_ms * 1e-3, "clocks": s_clocks}
+
+    stages = job.stage_times(3)
+    _, _, counts = job.gl.download(B)
     n_kp = float(np.mean(counts))
 
     # ---- e2e through the C ABI with pinned host buffers
-    pl = torch.from_numpy(hl).pin_memory(); pr = torch.from_numpy(hr).pin_memory()
-    kp_dt = capi.KP_DTYPE
-    o_k = [torch.empty((B, cap, kp_dt.itemsize), dtype=torch.uint8).pin_memory() for _ in range(2)]
-    o_d = [torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory() for _ in range(2)]
-    o_n = [np.zeros(B, np.int32) for _ in range(3)]
-    o_u = torch.empty((B, cap), dtype=torch.float32).pin_memory(); o_z = torch.empty((B, cap), dtype=torch.float32).pin_memory()
-    L = capi.lib()
-
-    def step_host():
-        # the call a user of the reference makes for a stereo frame: Frame::Frame(left, right, ...) =
-        # ExtractORB x2 + ComputeStereoMatches (src/Frame.cc:60-115), batched, host buffers in and out
-        capi.check(L.orb_stereo_frames(gl.handle, gr.handle, C.c_void_p(pl.data_ptr()), C.c_void_p(pr.data_ptr()), B, W, H, W,
-                                       C.c_size_t(W * H), C.c_float(MBF), C.c_float(0.0), C.c_float(FX),
-                                       C.c_void_p(o_k[0].data_ptr()), C.c_void_p(o_d[0].data_ptr()), capi.ptr(o_n[0]),
-                                       C.c_void_p(o_k[1].data_ptr()), C.c_void_p(o_d[1].data_ptr()), capi.ptr(o_n[1]),
-                                       C.c_void_p(o_u.data_ptr()), C.c_void_p(o_z.data_ptr()), cap))
-
-    for _ in range(3):
-        step_host()
-    sync_all()
     e_steps = max(3, args.steps // 2)
-    t0 = time.perf_counter()
-    for _ in range(e_steps):
-        step_host()
-    sync_all()
-    e_ms = (time.perf_counter() - t0) * 1e3
-    t = torch.tensor([e_ms], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e_val = world * B * e_steps / (float(t.item()) * 1e-3)
-    h2d = 2 * B * W * H
-    # slot rows are downloaded whole (cap == the handle's kp_cap here): keypoints + descriptors of both sides, uRight, depth, counts
-    d2h = int(B * cap * (2 * (kp_dt.itemsize + 32) + 8) + 2 * B * 4 + 8)
+    e_ms, h2d, d2h = job.e2e(e_steps)
+    e_val = world * B * e_steps / (e_ms * 1e-3)
+    parity = check_parity(job, [0, 1, B // 2, B - 1]) if rank == 0 else 0
+    left_pool, right_pool = job.left_pool, job.right_pool
+    job.close()
 
-    matching = None
+    # ---- the other BASELINE.json configs (every rank: they are sharded like the headline)
+    extras = {}
+    if not args.headline_only:
+        extras["euroc_752x480_1200"] = run_extra("euroc", 256, 6, local, rank, world, dist, cores)
+        extras["uhd_3840x2160_8000"] = run_extra("uhd", 128, 2, local, rank, world, dist, cores)
+
     if rank == 0:
-        matching = bench_matching(local)
-    if rank == 0:
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
-        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-        ext_stages = {k: v for k, v in stages.items()}
-        dom = max(ext_stages, key=lambda k: ext_stages[k])
-        # algorithmic bytes of the whole extraction of one image x images per launch,
-        # attributed to the pipeline; the dominant kernel's own share is reported next to it
-        alg_img = algorithmic_bytes_per_image(n_kp)
-        per_kernel_bytes = {
-            "pyramid": lambda: (1444097 - W * H) * 2 + W * H,       # read levels 0..6 once, write levels 1..7
-            "fast_cells": lambda: 1444097 + 4 * 16000,               # read every level once, write candidate keys
-            "quadtree": lambda: 3 * 4 * 16000,                        # gather + partition passes over candidate keys (lower bound)
-            "blur": lambda: 2 * 1444097,                              # read + write every level
-            "orient_describe": lambda: n_kp * (749 + 961 + 32 + 28),
-        }
-        dom_bytes = per_kernel_bytes.get(dom, lambda: alg_img)() * B  # per launch (one image side)
-        dom_ms_launch = ext_stages[dom] / (1 if dom.startswith("stereo") else 2)
-        achieved = dom_bytes / (dom_ms_launch * 1e-3) / 1e9
-        pipe_ms = sum(v for k, v in stages.items())
-        # the same launch against the INT issue rate: SURVEY 8(d) counts 80 simple integer ops per pyramid pixel for FAST
-        sm_mhz = clocks.get("sm_mhz") or 1965.0
-        alu_peak = 148 * 128 * sm_mhz * 1e6 / 1e12
-        alu_ach = 1444097 * 80 * B / (stages["fast_cells"] / 2 * 1e-3) / 1e12
-        traffic = NCU_TRAFFIC_BYTES_PER_IMAGE.get(dom)
-        cores = os.cpu_count() or 1
+        matching = None if args.headline_only else bench_matching(local)
+        latency = None
+        if not args.headline_only:
+            latency = {"kitti_stereo_batch1": run_latency("kitti", local), "tum_mono_640x480": run_latency("tum", local)}
         cpu_n = 12 * cores   # ~0.1 core-seconds per pair: about 20 s of CPU work
-        cpu_val, cpu_dt, cpu_kind = cpu_pairs_per_s(cpu_n, cores, left, right)
+        cpu_val, cpu_dt, cpu_kind, _ = cpu_units_per_s(cfg, cpu_n, cores, left_pool, right_pool)
         line = {
-            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-            "data": "synthetic",
-            "config": {"workload": WORKLOAD, "frame": "stereo pair (2 images)", "pairs_per_step_per_gpu": B, "nfeatures": NFEAT,
-                       "levels": N_LEVELS, "l2": "inputs larger than L2: %d MB of images + %d MB of intermediates per step"
-                       % (2 * B * W * H >> 20, int(2 * B * 9.5)), "avg_keypoints": n_kp},
+            "data": "synthetic", "config": CONFIG_KEYS,
+            "batch": {"pairs_per_step_per_gpu": B, "avg_keypoints": n_kp,
+                      "l2": "inputs larger than L2: %d MB of images + %d MB of intermediates per step" % (2 * B * cfg["w"] * cfg["h"] >> 20, int(2 * B * 9.5))},
             "e2e": {"value": e_val, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e_steps},
-            "gpu_launches": int(launches),
-            "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": (traffic * B if traffic else None), "traffic_source": NCU_TRAFFIC_SOURCE,
-                         "peak_source": peak_src,
-                         "alu": {"kernel": "fast_cells", "achieved": alu_ach, "peak": alu_peak, "unit": "Top/s (int, algorithmic: 80 per pixel)",
-                                 "frac": alu_ach / alu_peak},
-                         "pipeline_achieved": 2 * B * alg_img / (pipe_ms * 1e-3) / 1e9,
-                         "stage_ms_per_step": stages},
-            "matching": matching,
+            "gpu_launches": int(launches), "clocks": clocks, "sustained": sustained, "parity_checked": parity,
+            "roofline": roofline_block(cfg, B, stages, n_kp, clocks),
             "cpu_baseline": {"value": cpu_val, "unit": "frames/s", "cores": cores, "kind": cpu_kind,
                              "sample": "%d stereo pairs on %d host threads in %.1f s; %s" % (cpu_n, cores, cpu_dt, CPU_DESC[cpu_kind])},
+            "latency": latency, "configs": extras, "matching": matching,
         }
         print(json.dumps(line), flush=True)
     if dist is not None:
@@ -441,6 +712,7 @@ def bench_matching(local):
     # Tracking, LocalMapping and LoopClosing threads concurrently (threading)
     T = 8
     ms_ = [mt.ORBmatcher(0.6, True, max_n=8192, max_pairs=1, device=local) for _ in range(T)]
+
     def worker(mm, out, k):
         for _ in range(3):
             mm.SearchByProjection(F, mps, 3.0, occ)
@@ -450,17 +722,19 @@ def bench_matching(local):
         out[k] = time.perf_counter() - t
     outs = [0.0] * T
     ths = [threading.Thread(target=worker, args=(ms_[k], outs, k)) for k in range(T)]
-    t0 = time.perf_counter()
     for t in ths:
         t.start()
     for t in ths:
         t.join()
     mt_fps = T * reps / max(outs)
     popc = P * N * N * 8 / (bf_ms * 1e-3)
+    ipk = load_json("profiles/MEASURED_INT_PEAKS.json", {})
+    popc_lanes = float(ipk.get("tests", {}).get("popc", {}).get("lanes_per_clk_per_sm", 16.0))
+    popc_peak = popc_lanes * int(ipk.get("sms", 148)) * 1965e6
     return {"workload": "2000x2000 descriptors per frame pair, 1024 pairs (BASELINE.json configs[3])",
             "bruteforce": {"ms_per_1024_pairs": bf_ms, "pairs_per_s": P / (bf_ms * 1e-3), "popc_Tops": popc / 1e12,
-                           "popc_peak_Tops": 148 * 16 * 1965e6 / 1e12, "frac": popc / (148 * 16 * 1965e6),
-                           "note": "peak = 148 SM x 16 POPC/clk/SM (CUDA C Programming Guide arithmetic-throughput table; not re-measured here) x 1.965 GHz"},
+                           "popc_peak_Tops": popc_peak / 1e12, "frac": popc / popc_peak,
+                           "peak_source": "measured: profiles/MEASURED_INT_PEAKS.json popc %.2f lanes/clk/SM x SMs x 1965 MHz" % popc_lanes},
             "search_by_projection_host_api": {"ms_per_frame": sp_ms, "frames_per_s": 1e3 / sp_ms, "matches": int(n_sp), "th": 3.0,
                                               "frames_per_s_8_host_threads": mt_fps}}
 
@@ -468,10 +742,12 @@ def bench_matching(local):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=256, help="stereo pairs per step per GPU")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--profile-run", action="store_true", help="two device-resident steps only, for ncu")
+    ap.add_argument("--headline-only", action="store_true", help="skip the extra configs / latency / matching sections (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

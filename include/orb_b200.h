@@ -227,6 +227,57 @@ int orb_search_by_projection_lastframe(orb_matcher* m, const orb_frame_view* cur
                                        int check_orientation, const uint8_t* occupied, int32_t* match,
                                        int32_t* nmatches);
 
+/* Batched forms of the two tracking searches (BASELINE.json configs[3]: "batch of 1024 pairs"): `pairs` independent
+ * frame pairs per call.  Every array holds `pairs` consecutive blocks of `stride` elements (descriptors: stride * 32
+ * bytes), n[p] of them valid; pointers may be host (pinned for full copy speed) or device memory.  The grid constants,
+ * scale factors and camera are shared by the batch (one camera).  occupied / match: [pairs][f->stride]; nmatches:
+ * [pairs]; forward / backward (src/ORBmatcher.cc:1486-1487): one flag per pair.  The handle must have been created with
+ * max_pairs >= pairs.  Results are those of `pairs` single calls. */
+typedef struct {
+    int32_t pairs, stride;
+    const int32_t* n;
+    const float* x;
+    const float* y;
+    const int32_t* octave;
+    const float* angle;
+    const float* u_right;      /* may be NULL */
+    const uint8_t* desc;
+    orb_grid_params grid;
+    const float* scale_factors;
+    int32_t n_levels;
+} orb_frame_batch_view;
+typedef struct {
+    int32_t pairs, stride;
+    const int32_t* n;
+    const uint8_t* valid;
+    const float* proj_x;
+    const float* proj_y;
+    const float* proj_xr;      /* may be NULL */
+    const int32_t* level;
+    const float* view_cos;
+    const uint8_t* desc;
+    const uint8_t* blocks;
+} orb_mappoint_batch_view;
+typedef struct {
+    int32_t pairs, stride;
+    const int32_t* n;
+    const uint8_t* valid;
+    const float* xc;
+    const float* yc;
+    const float* zc;
+    const int32_t* octave;
+    const float* angle;
+    const uint8_t* desc;
+    const uint8_t* blocks;
+} orb_lastframe_batch_view;
+int orb_search_by_projection_mappoints_batch(orb_matcher* m, const orb_frame_batch_view* f, const orb_mappoint_batch_view* mps,
+                                             float th, float nn_ratio, const uint8_t* occupied, int32_t* match,
+                                             int32_t* nmatches);
+int orb_search_by_projection_lastframe_batch(orb_matcher* m, const orb_frame_batch_view* cur,
+                                             const orb_lastframe_batch_view* last, const orb_camera* cam, float th,
+                                             const uint8_t* forward, const uint8_t* backward, int check_orientation,
+                                             const uint8_t* occupied, int32_t* match, int32_t* nmatches);
+
 /* FeatureVector (DBoW2::FeatureVector = std::map<NodeId, vector<unsigned>>) flattened as CSR in
  * ascending node id: node_ids[n_nodes], start[n_nodes+1], items[start[n_nodes]]. */
 typedef struct {

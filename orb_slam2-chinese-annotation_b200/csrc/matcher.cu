@@ -41,7 +41,31 @@ struct DFrame {
     float sf[ORB_MAX_LEVELS];
     const int* cell_start;
     const int* cell_items;
+    // batched calls: frame p of the batch starts p * stride elements further in every array (0: a single frame)
+    int stride;
+    const int* n_arr;
 };
+
+// Query-side layout of a batched call (one frame pair per CTA / grid row): pair p reads its points at p * qstride, its
+// candidate offsets at p * (qstride + 1), its candidates at cand_base[p].  qstride == 0: a single pair.
+struct Batch {
+    int qstride;
+    const int* nq_arr;
+    const int* cand_base;
+};
+__device__ __forceinline__ DFrame frame_at(const DFrame& F, int p) {
+    DFrame G = F;
+    if (F.stride) {
+        const size_t o = (size_t)p * F.stride;
+        G.n = F.n_arr[p];
+        G.x += o; G.y += o; G.octave += o; G.desc += o * 32;
+        if (G.angle) G.angle += o;
+        if (G.u_right) G.u_right += o;
+        G.cell_start += (size_t)p * (GRID_CELLS + 1);
+        G.cell_items += o;
+    }
+    return G;
+}
 
 struct Query {
     float x, y, r, xr;
@@ -117,10 +141,15 @@ k_bruteforce(const uint8_t* __restrict__ A, const uint8_t* __restrict__ Bm, int 
 // ascending keypoint index (insertion order).  One CTA: bitonic sort of (cell << 16 | index).
 __global__ void __launch_bounds__(1024)
 k_grid_build(const float* __restrict__ x, const float* __restrict__ y, int n, int p2, orb_grid_params g, int* __restrict__ cell_start,
-             int* __restrict__ cell_items, int* __restrict__ n_items) {
+             int* __restrict__ cell_items, int* __restrict__ n_items, int stride = 0, const int* __restrict__ n_arr = nullptr) {
     extern __shared__ uint32_t keys[];
     __shared__ int cnt[GRID_CELLS + 1];
     const int tid = threadIdx.x;
+    if (stride) {   // one CTA per frame of a batch
+        const size_t o = (size_t)blockIdx.x * stride;
+        x += o; y += o; cell_items += o; cell_start += (size_t)blockIdx.x * (GRID_CELLS + 1); n_items += blockIdx.x;
+        n = n_arr[blockIdx.x];
+    }
     for (int i = tid; i <= GRID_CELLS; i += 1024) cnt[i] = 0;
     __syncthreads();
     for (int i = tid; i < p2; i += 1024) {
@@ -165,8 +194,14 @@ k_grid_build(const float* __restrict__ x, const float* __restrict__ y, int n, in
 // Query records.
 __global__ void k_prep_mappoints(int n, const uint8_t* __restrict__ valid, const float* __restrict__ px, const float* __restrict__ py,
                                  const float* __restrict__ pxr, const int* __restrict__ level, const float* __restrict__ view_cos,
-                                 float th, DFrame F, Query* __restrict__ q) {
+                                 float th, DFrame F, Query* __restrict__ q, Batch B) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (B.qstride) {
+        const size_t o = (size_t)blockIdx.y * B.qstride;
+        n = B.nq_arr[blockIdx.y];
+        valid += o; px += o; py += o; level += o; view_cos += o; q += o;
+        if (pxr) pxr += o;
+    }
     if (i >= n) return;
     Query Q;
     Q.valid = valid[i];
@@ -181,8 +216,15 @@ __global__ void k_prep_mappoints(int n, const uint8_t* __restrict__ valid, const
 
 __global__ void k_prep_lastframe(int n, const uint8_t* __restrict__ valid, const float* __restrict__ xc, const float* __restrict__ yc,
                                  const float* __restrict__ zc, const int* __restrict__ octave, orb_camera cam, float th, int forward,
-                                 int backward, DFrame F, Query* __restrict__ q) {
+                                 int backward, DFrame F, Query* __restrict__ q, Batch B, const uint8_t* __restrict__ fwd_arr,
+                                 const uint8_t* __restrict__ bwd_arr) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (B.qstride) {
+        const size_t o = (size_t)blockIdx.y * B.qstride;
+        n = B.nq_arr[blockIdx.y];
+        valid += o; xc += o; yc += o; zc += o; octave += o; q += o;
+        forward = fwd_arr[blockIdx.y]; backward = bwd_arr[blockIdx.y];
+    }
     if (i >= n) return;
     Query Q;
     Q.valid = valid[i]; Q.pad = 0; Q.x = Q.y = Q.r = Q.xr = 0.f; Q.min_level = Q.max_level = 0;
@@ -218,11 +260,18 @@ __global__ void k_prep_lastframe(int n, const uint8_t* __restrict__ valid, const
 // packed candidates: index (16 bits) | distance << 16 (9 bits) | octave << 25.
 template <bool FILL>
 __global__ void __launch_bounds__(256)
-k_area_candidates(int nq, const Query* __restrict__ q, const uint8_t* __restrict__ qdesc, DFrame F, int filter,
+k_area_candidates(int nq, const Query* __restrict__ q, const uint8_t* __restrict__ qdesc, DFrame F0, int filter,
                   const float* __restrict__ inv_sigma2, int* __restrict__ counts, const int* __restrict__ starts,
-                  uint32_t* __restrict__ cands) {
+                  uint32_t* __restrict__ cands, Batch B) {
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (B.qstride) {
+        const size_t o = (size_t)blockIdx.y * B.qstride;
+        nq = B.nq_arr[blockIdx.y];
+        q += o; counts += o;
+        if (FILL) { qdesc += o * 32; starts += (size_t)blockIdx.y * (B.qstride + 1); cands += B.cand_base[blockIdx.y]; }
+    }
     if (w >= nq) return;
+    const DFrame F = frame_at(F0, blockIdx.y);
     const Query Q = q[w];
     int total = 0;
     if (Q.valid) {
@@ -292,9 +341,10 @@ k_area_candidates(int nq, const Query* __restrict__ q, const uint8_t* __restrict
 }
 
 // single-CTA exclusive scan: starts[0..n] from counts[0..n)
-__global__ void __launch_bounds__(1024) k_scan(const int* __restrict__ counts, int n, int* __restrict__ starts) {
+__global__ void __launch_bounds__(1024) k_scan(const int* __restrict__ counts, int n, int* __restrict__ starts, Batch B, int* __restrict__ totals) {
     __shared__ int ws[33];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (B.qstride) { n = B.nq_arr[blockIdx.x]; counts += (size_t)blockIdx.x * B.qstride; starts += (size_t)blockIdx.x * (B.qstride + 1); }
     int carry = 0;
     for (int i0 = 0; i0 < n; i0 += 1024) {
         const int i = i0 + tid;
@@ -316,7 +366,14 @@ __global__ void __launch_bounds__(1024) k_scan(const int* __restrict__ counts, i
         carry += ws[32];
         __syncthreads();
     }
-    if (tid == 0) starts[n] = carry;
+    if (tid == 0) { starts[n] = carry; if (totals) totals[blockIdx.x] = carry; }
+}
+// candidate base of every pair: exclusive scan of the per-pair totals (one thread: a few thousand pairs at most)
+__global__ void k_pair_bases(const int* __restrict__ totals, int pairs, int* __restrict__ base) {
+    if (threadIdx.x || blockIdx.x) return;
+    long long run = 0;
+    for (int p = 0; p < pairs; ++p) { base[p] = (int)run; run += totals[p]; }
+    base[pairs] = run > 0x7fffffffLL ? -1 : (int)run;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -405,12 +462,23 @@ __device__ __forceinline__ uint32_t rp_cand(const uint32_t* __restrict__ cands, 
 //         <= max_dist, every accepted keypoint is closed to later points, optional rotation histogram
 __global__ void __launch_bounds__(32)
 k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* __restrict__ starts, const uint32_t* __restrict__ cands,
-                     const uint8_t* __restrict__ blocks, const float* __restrict__ q_angle, DFrame F, const uint8_t* __restrict__ occupied,
+                     const uint8_t* __restrict__ blocks, const float* __restrict__ q_angle, DFrame F0, const uint8_t* __restrict__ occupied,
                      uint8_t* occ, float nn_ratio, int check_ori, int max_dist, int* __restrict__ match,
                      int* __restrict__ q_best_idx, int* __restrict__ q_best_dist, int* __restrict__ hist_idx,
-                     int* __restrict__ hist_bin, int* __restrict__ nmatches_out, int occ_shared) {
+                     int* __restrict__ hist_bin, int* __restrict__ nmatches_out, int occ_shared, Batch B) {
     __shared__ int s_cnt[32];
     extern __shared__ uint8_t s_occ[];   // the claimed-keypoint flags live in shared memory when they fit (occ_shared): they are
+    const DFrame F = frame_at(F0, blockIdx.x);
+    if (B.qstride) {   // one warp (CTA) per frame pair of a batch
+        const int p = blockIdx.x;
+        const size_t o = (size_t)p * B.qstride, fo = (size_t)p * F0.stride;
+        nq = B.nq_arr[p];
+        q += o; starts += (size_t)p * (B.qstride + 1); cands += B.cand_base[p]; blocks += o;
+        if (q_angle) q_angle += o;
+        if (occupied) occupied += fo;
+        occ += fo; match += fo; hist_idx += o; hist_bin += o; nmatches_out += p;
+        if (q_best_idx) { q_best_idx += o; q_best_dist += o; }
+    }
     if (occ_shared) occ = s_occ;         // read and written on the serial chain, one L2 round trip per point otherwise
     const int lane = threadIdx.x;
     for (int i = lane; i < F.n; i += 32) { match[i] = -1; occ[i] = occupied ? occupied[i] : 0; }
@@ -858,6 +926,17 @@ void merge_join(const orb_featvec_view* a, const orb_featvec_view* b, std::vecto
     }
 }
 
+// The candidate list buffer grows to the size the counting pass found (the caller has synchronised the stream).
+int ensure_cands(orb_matcher* m, size_t total) {
+    if (total <= m->cands_cap) return ORB_OK;
+    const size_t want = total + total / 4 + 4096;
+    uint32_t* p = nullptr;
+    if (cudaMalloc((void**)&p, want * 4) != cudaSuccess) { cudaGetLastError(); orb_set_error("candidate workspace: out of device memory"); return ORB_ERR_CAPACITY; }
+    cudaFree(m->d_cands);
+    m->d_cands = p; m->cands_cap = want;
+    return ORB_OK;
+}
+
 int begin_call(orb_matcher* m) {
     if (!m) return ORB_ERR_BAD_ARG;
     ORB_CUDA(cudaSetDevice(m->device));
@@ -883,9 +962,10 @@ int orb_matcher_create(int max_pairs, int max_n, int device, orb_matcher** out) 
     ORB_CUDA(cudaSetDevice(device));
     orb_matcher* m = new orb_matcher();
     m->device = device; m->max_pairs = max_pairs; m->max_n = max_n;
-    m->ws_cap = (size_t)max_pairs * max_n * (2 * 32 + 3 * 4) + (size_t)max_n * 512 + (8u << 20);
-    m->cands_cap = std::min<size_t>((size_t)max_n * max_n, (size_t)128 << 20);
-    m->cands_cap = std::max<size_t>(m->cands_cap, 1 << 16);
+    // per pair and feature: frame SoA (52 B) + grid items, point SoA (54 B), query records, offsets, matches, histogram slots;
+    // brute force: 2 x 32 B + 3 ints.  Candidate lists start at 64 per feature and grow on demand (ensure_cands).
+    m->ws_cap = (size_t)max_pairs * max_n * 256 + (size_t)max_pairs * 16 * 1024 + (size_t)max_n * 512 + (8u << 20);
+    m->cands_cap = std::max<size_t>((size_t)max_pairs * max_n * 64, 1 << 16);
     if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc((void**)&m->d_ws, m->ws_cap) != cudaSuccess ||
         cudaMalloc((void**)&m->d_cands, m->cands_cap * 4) != cudaSuccess || cudaMalloc((void**)&m->d_scal, 64) != cudaSuccess) {
         orb_set_error(std::string("matcher allocation: ") + cudaGetErrorString(cudaGetLastError()));
@@ -1011,13 +1091,13 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
     const int filter = o.filter; const float* d_inv_sigma2 = o.d_inv_sigma2;
     if (nq > 0) {
         const int blocks = (nq * 32 + 255) / 256;
-        k_area_candidates<false><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, counts, nullptr, nullptr);
-        k_scan<<<1, 1024, 0, m->stream>>>(counts, nq, starts);
+        k_area_candidates<false><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, counts, nullptr, nullptr, Batch{0, nullptr, nullptr});
+        k_scan<<<1, 1024, 0, m->stream>>>(counts, nq, starts, Batch{0, nullptr, nullptr}, nullptr);
         int total = 0;
         ORB_CUDA(cudaMemcpyAsync(&total, starts + nq, 4, cudaMemcpyDeviceToHost, m->stream));
         ORB_CUDA(cudaStreamSynchronize(m->stream));
-        if ((size_t)total > m->cands_cap) { orb_set_error("candidate workspace too small"); return ORB_ERR_CAPACITY; }
-        k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, nullptr, starts, m->d_cands);
+        if ((st = ensure_cands(m, (size_t)total)) != ORB_OK) return st;
+        k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, nullptr, starts, m->d_cands, Batch{0, nullptr, nullptr});
         m->launches += 3;
     } else {
         ORB_CUDA(cudaMemsetAsync(starts, 0, 4, m->stream));
@@ -1031,7 +1111,7 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
     } else {
         const int occ_shared = F.n <= 40 * 1024;
         k_resolve_projection<<<1, 32, occ_shared ? (size_t)((F.n + 15) & ~15) : 0, m->stream>>>(o.mode, nq, dq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied,
-                                                      occ, o.nn_ratio, o.check_ori, o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal, occ_shared);
+                                                      occ, o.nn_ratio, o.check_ori, o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal, occ_shared, Batch{0, nullptr, nullptr});
         m->launches++;
     }
     ORB_CUDA(cudaGetLastError());
@@ -1058,7 +1138,7 @@ int orb_search_by_projection_mappoints(orb_matcher* m, const orb_frame_view* f, 
         (st = ws_upload(m, &dvc, mps->view_cos, nq)) != ORB_OK || (st = ws_upload(m, &dd, mps->desc, (size_t)nq * 32)) != ORB_OK ||
         (st = ws_upload(m, &db, mps->blocks, nq)) != ORB_OK || (st = ws_alloc(m, &dq, std::max(nq, 1))) != ORB_OK) return st;
     if (mps->proj_xr) { if ((st = ws_upload(m, &dxr, mps->proj_xr, nq)) != ORB_OK) return st; }
-    if (nq > 0) { k_prep_mappoints<<<(nq + 255) / 256, 256, 0, m->stream>>>(nq, dv, dx, dy, dxr, dl, dvc, th, F, dq); m->launches++; }
+    if (nq > 0) { k_prep_mappoints<<<(nq + 255) / 256, 256, 0, m->stream>>>(nq, dv, dx, dy, dxr, dl, dvc, th, F, dq, Batch{0, nullptr, nullptr}); m->launches++; }
     ProjOpts o; o.mode = 0; o.nn_ratio = nn_ratio;
     return projection_common(m, o, nq, dq, dd, db, nullptr, F, occupied, match, nmatches);
 }
@@ -1079,9 +1159,152 @@ int orb_search_by_projection_lastframe(orb_matcher* m, const orb_frame_view* cur
         (st = ws_upload(m, &doct, last->octave, nq)) != ORB_OK || (st = ws_upload(m, &da, last->angle, nq)) != ORB_OK ||
         (st = ws_upload(m, &dd, last->desc, (size_t)nq * 32)) != ORB_OK || (st = ws_upload(m, &db, last->blocks, nq)) != ORB_OK ||
         (st = ws_alloc(m, &dq, std::max(nq, 1))) != ORB_OK) return st;
-    if (nq > 0) { k_prep_lastframe<<<(nq + 255) / 256, 256, 0, m->stream>>>(nq, dv, dx, dy, dz, doct, *cam, th, forward, backward, F, dq); m->launches++; }
+    if (nq > 0) { k_prep_lastframe<<<(nq + 255) / 256, 256, 0, m->stream>>>(nq, dv, dx, dy, dz, doct, *cam, th, forward, backward, F, dq, Batch{0, nullptr, nullptr}, nullptr, nullptr); m->launches++; }
     ProjOpts o; o.mode = 1; o.check_ori = check_orientation;
     return projection_common(m, o, nq, dq, dd, db, da, F, occupied, match, nmatches);
+}
+
+
+// ------------------------------------------------------------------------------------------ batched projection searches
+// (BASELINE configs[3]: many frame pairs per call).  Every array of the views holds `pairs` consecutive blocks of `stride`
+// elements; each field goes up with ONE copy (cudaMemcpyDefault: host or device pointers alike), the kernels get a pair
+// dimension (one resolve warp per pair), and the matches come back with one copy.
+}  // extern "C"
+namespace {
+template <typename T>
+int ws_upload_any(orb_matcher* m, const T** dp, const T* src, size_t count) {
+    T* p = nullptr;
+    int st = ws_alloc(m, &p, std::max<size_t>(count, 1));
+    if (st != ORB_OK) return st;
+    if (count) ORB_CUDA(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyDefault, m->stream));
+    *dp = p;
+    return ORB_OK;
+}
+
+int upload_frame_batch(orb_matcher* m, const orb_frame_batch_view* f, DFrame* D, std::vector<int>& n_host) {
+    if (!f || f->pairs < 1 || f->pairs > m->max_pairs || f->stride < 1 || f->stride > m->max_n || f->stride > 65535 || !f->n || !f->x || !f->y ||
+        !f->octave || !f->desc) {
+        orb_set_error("bad frame batch view (pairs <= max_pairs, stride <= min(max_n, 65535))");
+        return ORB_ERR_BAD_ARG;
+    }
+    std::memset(D, 0, sizeof(*D));
+    D->grid = f->grid; D->stride = f->stride;
+    for (int i = 0; i < ORB_MAX_LEVELS; ++i) D->sf[i] = (f->scale_factors && i < f->n_levels) ? f->scale_factors[i] : 1.f;
+    const size_t tot = (size_t)f->pairs * f->stride;
+    int st;
+    if ((st = ws_upload_any(m, &D->n_arr, f->n, f->pairs)) != ORB_OK || (st = ws_upload_any(m, &D->x, f->x, tot)) != ORB_OK ||
+        (st = ws_upload_any(m, &D->y, f->y, tot)) != ORB_OK || (st = ws_upload_any(m, &D->octave, f->octave, tot)) != ORB_OK ||
+        (st = ws_upload_any(m, &D->desc, f->desc, tot * 32)) != ORB_OK) return st;
+    if (f->angle) { if ((st = ws_upload_any(m, &D->angle, f->angle, tot)) != ORB_OK) return st; }
+    if (f->u_right) { if ((st = ws_upload_any(m, &D->u_right, f->u_right, tot)) != ORB_OK) return st; }
+    // the counts are needed on the host too (bounds), wherever the caller keeps them
+    n_host.resize(f->pairs);
+    ORB_CUDA(cudaMemcpyAsync(n_host.data(), f->n, (size_t)f->pairs * 4, cudaMemcpyDefault, m->stream));
+    int *cs, *ci, *ni;
+    if ((st = ws_alloc(m, &cs, (size_t)f->pairs * (GRID_CELLS + 1))) != ORB_OK || (st = ws_alloc(m, &ci, tot)) != ORB_OK ||
+        (st = ws_alloc(m, &ni, f->pairs)) != ORB_OK) return st;
+    int p2 = 1;
+    while (p2 < f->stride) p2 <<= 1;
+    const size_t smem = (size_t)p2 * 4;
+    if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_grid_build<<<f->pairs, 1024, smem, m->stream>>>(D->x, D->y, 0, p2, f->grid, cs, ci, ni, f->stride, D->n_arr);
+    m->launches++;
+    D->cell_start = cs; D->cell_items = ci;
+    return ORB_OK;
+}
+
+int projection_batch(orb_matcher* m, int mode, int pairs, int qstride, const int* d_nq, const Query* dq, const uint8_t* d_qdesc, const uint8_t* d_blocks,
+                     const float* d_qangle, const DFrame& F, const uint8_t* occupied, float nn_ratio, int check_ori, int32_t* match,
+                     int32_t* nmatches) {
+    int st;
+    const size_t qtot = (size_t)pairs * qstride, ftot = (size_t)pairs * F.stride;
+    int *counts, *starts, *totals, *bases, *dmatch, *hidx, *hbin, *dn;
+    uint8_t* occ; const uint8_t* d_occupied = nullptr;
+    if ((st = ws_alloc(m, &counts, qtot)) != ORB_OK || (st = ws_alloc(m, &starts, (size_t)pairs * (qstride + 1))) != ORB_OK ||
+        (st = ws_alloc(m, &totals, pairs)) != ORB_OK || (st = ws_alloc(m, &bases, pairs + 1)) != ORB_OK ||
+        (st = ws_alloc(m, &dmatch, ftot)) != ORB_OK || (st = ws_alloc(m, &occ, ftot)) != ORB_OK ||
+        (st = ws_alloc(m, &hidx, qtot)) != ORB_OK || (st = ws_alloc(m, &hbin, qtot)) != ORB_OK || (st = ws_alloc(m, &dn, pairs)) != ORB_OK) return st;
+    if (occupied) { if ((st = ws_upload_any(m, &d_occupied, occupied, ftot)) != ORB_OK) return st; }
+    Batch B{qstride, d_nq, nullptr};
+    const dim3 grid((unsigned)((qstride * 32 + 255) / 256), (unsigned)pairs);
+    k_area_candidates<false><<<grid, 256, 0, m->stream>>>(0, dq, d_qdesc, F, FILTER_STEREO_WINDOW, nullptr, counts, nullptr, nullptr, B);
+    k_scan<<<pairs, 1024, 0, m->stream>>>(counts, 0, starts, B, totals);
+    k_pair_bases<<<1, 32, 0, m->stream>>>(totals, pairs, bases);
+    int total = 0;
+    ORB_CUDA(cudaMemcpyAsync(&total, bases + pairs, 4, cudaMemcpyDeviceToHost, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    if (total < 0) { orb_set_error("more than 2^31 candidates in one batch: split the call"); return ORB_ERR_CAPACITY; }
+    if ((st = ensure_cands(m, (size_t)total)) != ORB_OK) return st;
+    B.cand_base = bases;
+    k_area_candidates<true><<<grid, 256, 0, m->stream>>>(0, dq, d_qdesc, F, FILTER_STEREO_WINDOW, nullptr, nullptr, starts, m->d_cands, B);
+    const int occ_shared = F.stride <= 40 * 1024;
+    k_resolve_projection<<<pairs, 32, occ_shared ? (size_t)((F.stride + 15) & ~15) : 0, m->stream>>>(mode, 0, dq, starts, m->d_cands, d_blocks, d_qangle, F,
+                                                  d_occupied, occ, nn_ratio, check_ori, M_TH_HIGH, dmatch, nullptr, nullptr, hidx, hbin, dn, occ_shared, B);
+    m->launches += 5;
+    ORB_CUDA(cudaGetLastError());
+    ORB_CUDA(cudaMemcpyAsync(match, dmatch, ftot * 4, cudaMemcpyDefault, m->stream));
+    ORB_CUDA(cudaMemcpyAsync(nmatches, dn, (size_t)pairs * 4, cudaMemcpyDefault, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    return ORB_OK;
+}
+}  // namespace
+extern "C" {
+
+int orb_search_by_projection_mappoints_batch(orb_matcher* m, const orb_frame_batch_view* f, const orb_mappoint_batch_view* mps, float th, float nn_ratio,
+                                             const uint8_t* occupied, int32_t* match, int32_t* nmatches) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!f || !mps || !match || !nmatches || mps->pairs != f->pairs || mps->stride < 1 || mps->stride > m->max_n || !mps->n || !mps->valid ||
+        !mps->proj_x || !mps->proj_y || !mps->level || !mps->view_cos || !mps->desc || !mps->blocks) return ORB_ERR_BAD_ARG;
+    DFrame F; std::vector<int> nf;
+    if ((st = upload_frame_batch(m, f, &F, nf)) != ORB_OK) return st;
+    const int pairs = f->pairs, qs = mps->stride;
+    const size_t qtot = (size_t)pairs * qs;
+    const uint8_t *dv, *dd, *db; const float *dx, *dy, *dxr = nullptr, *dvc; const int *dl, *dnq; Query* dq;
+    if ((st = ws_upload_any(m, &dnq, mps->n, pairs)) != ORB_OK || (st = ws_upload_any(m, &dv, mps->valid, qtot)) != ORB_OK ||
+        (st = ws_upload_any(m, &dx, mps->proj_x, qtot)) != ORB_OK || (st = ws_upload_any(m, &dy, mps->proj_y, qtot)) != ORB_OK ||
+        (st = ws_upload_any(m, &dl, mps->level, qtot)) != ORB_OK || (st = ws_upload_any(m, &dvc, mps->view_cos, qtot)) != ORB_OK ||
+        (st = ws_upload_any(m, &dd, mps->desc, qtot * 32)) != ORB_OK || (st = ws_upload_any(m, &db, mps->blocks, qtot)) != ORB_OK ||
+        (st = ws_alloc(m, &dq, qtot)) != ORB_OK) return st;
+    if (mps->proj_xr) { if ((st = ws_upload_any(m, &dxr, mps->proj_xr, qtot)) != ORB_OK) return st; }
+    std::vector<int> nq(pairs);
+    ORB_CUDA(cudaMemcpyAsync(nq.data(), mps->n, (size_t)pairs * 4, cudaMemcpyDefault, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    for (int p = 0; p < pairs; ++p)
+        if (nf[p] < 0 || nf[p] > f->stride || nq[p] < 0 || nq[p] > qs) { orb_set_error("batch view: n[p] outside [0, stride]"); return ORB_ERR_BAD_ARG; }
+    k_prep_mappoints<<<dim3((unsigned)((qs + 255) / 256), (unsigned)pairs), 256, 0, m->stream>>>(0, dv, dx, dy, dxr, dl, dvc, th, F, dq, Batch{qs, dnq, nullptr});
+    m->launches++;
+    return projection_batch(m, 0, pairs, qs, dnq, dq, dd, db, nullptr, F, occupied, nn_ratio, 0, match, nmatches);
+}
+
+int orb_search_by_projection_lastframe_batch(orb_matcher* m, const orb_frame_batch_view* cur, const orb_lastframe_batch_view* last, const orb_camera* cam,
+                                             float th, const uint8_t* forward, const uint8_t* backward, int check_orientation, const uint8_t* occupied,
+                                             int32_t* match, int32_t* nmatches) {
+    int st = begin_call(m);
+    if (st != ORB_OK) return st;
+    if (!cur || !last || !cam || !match || !nmatches || !forward || !backward || last->pairs != cur->pairs || last->stride < 1 || last->stride > m->max_n ||
+        !last->n || !last->valid || !last->xc || !last->yc || !last->zc || !last->octave || !last->angle || !last->desc || !last->blocks ||
+        (check_orientation && !cur->angle)) return ORB_ERR_BAD_ARG;
+    DFrame F; std::vector<int> nf;
+    if ((st = upload_frame_batch(m, cur, &F, nf)) != ORB_OK) return st;
+    const int pairs = cur->pairs, qs = last->stride;
+    const size_t qtot = (size_t)pairs * qs;
+    const uint8_t *dv, *dd, *db, *dfw, *dbw; const float *dx, *dy, *dz, *da; const int *doct, *dnq; Query* dq;
+    if ((st = ws_upload_any(m, &dnq, last->n, pairs)) != ORB_OK || (st = ws_upload_any(m, &dv, last->valid, qtot)) != ORB_OK ||
+        (st = ws_upload_any(m, &dx, last->xc, qtot)) != ORB_OK || (st = ws_upload_any(m, &dy, last->yc, qtot)) != ORB_OK ||
+        (st = ws_upload_any(m, &dz, last->zc, qtot)) != ORB_OK || (st = ws_upload_any(m, &doct, last->octave, qtot)) != ORB_OK ||
+        (st = ws_upload_any(m, &da, last->angle, qtot)) != ORB_OK || (st = ws_upload_any(m, &dd, last->desc, qtot * 32)) != ORB_OK ||
+        (st = ws_upload_any(m, &db, last->blocks, qtot)) != ORB_OK || (st = ws_upload_any(m, &dfw, forward, pairs)) != ORB_OK ||
+        (st = ws_upload_any(m, &dbw, backward, pairs)) != ORB_OK || (st = ws_alloc(m, &dq, qtot)) != ORB_OK) return st;
+    std::vector<int> nq(pairs);
+    ORB_CUDA(cudaMemcpyAsync(nq.data(), last->n, (size_t)pairs * 4, cudaMemcpyDefault, m->stream));
+    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    for (int p = 0; p < pairs; ++p)
+        if (nf[p] < 0 || nf[p] > cur->stride || nq[p] < 0 || nq[p] > qs) { orb_set_error("batch view: n[p] outside [0, stride]"); return ORB_ERR_BAD_ARG; }
+    k_prep_lastframe<<<dim3((unsigned)((qs + 255) / 256), (unsigned)pairs), 256, 0, m->stream>>>(0, dv, dx, dy, dz, doct, *cam, th, 0, 0, F, dq, Batch{qs, dnq, nullptr},
+                                                                                              dfw, dbw);
+    m->launches++;
+    return projection_batch(m, 1, pairs, qs, dnq, dq, dd, db, da, F, occupied, 0.f, check_orientation, match, nmatches);
 }
 
 static int check_fv(const orb_featvec_view* v) {
@@ -1112,7 +1335,7 @@ int orb_search_by_bow(orb_matcher* m, const orb_frame_view* kf, const orb_featve
             total += (size_t)(f1 - f0);
         }
     }
-    if (total > m->cands_cap) { orb_set_error("candidate workspace too small"); return ORB_ERR_CAPACITY; }
+    if ((st = ensure_cands(m, total)) != ORB_OK) return st;
     const int ne = (int)entries.size();
     const int n_items2 = f_fv->n_nodes ? f_fv->start[f_fv->n_nodes] : 0;
     for (int i = 0; i < n_items2; ++i) if (f_fv->items[i] >= (uint32_t)f->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
@@ -1285,13 +1508,13 @@ int orb_search_for_initialization(orb_matcher* m, const orb_frame_view* f1, cons
     if (f1->angle) { if ((st = ws_upload(m, &da1, f1->angle, (size_t)nq)) != ORB_OK) return st; }
     if (nq > 0) {
         const int blocks = (nq * 32 + 255) / 256;
-        k_area_candidates<false><<<blocks, 256, 0, m->stream>>>(nq, dq, dd, F2, FILTER_NONE, nullptr, counts, nullptr, nullptr);
-        k_scan<<<1, 1024, 0, m->stream>>>(counts, nq, starts);
+        k_area_candidates<false><<<blocks, 256, 0, m->stream>>>(nq, dq, dd, F2, FILTER_NONE, nullptr, counts, nullptr, nullptr, Batch{0, nullptr, nullptr});
+        k_scan<<<1, 1024, 0, m->stream>>>(counts, nq, starts, Batch{0, nullptr, nullptr}, nullptr);
         int total = 0;
         ORB_CUDA(cudaMemcpyAsync(&total, starts + nq, 4, cudaMemcpyDeviceToHost, m->stream));
         ORB_CUDA(cudaStreamSynchronize(m->stream));
-        if ((size_t)total > m->cands_cap) { orb_set_error("candidate workspace too small"); return ORB_ERR_CAPACITY; }
-        k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, dd, F2, FILTER_NONE, nullptr, nullptr, starts, m->d_cands);
+        if ((st = ensure_cands(m, (size_t)total)) != ORB_OK) return st;
+        k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, dd, F2, FILTER_NONE, nullptr, nullptr, starts, m->d_cands, Batch{0, nullptr, nullptr});
         m->launches += 3;
     } else {
         ORB_CUDA(cudaMemsetAsync(starts, 0, 4, m->stream));
@@ -1330,7 +1553,7 @@ int orb_search_by_bow_keyframes(orb_matcher* m, const orb_frame_view* kf1, const
             total += (size_t)(f1 - f0);
         }
     }
-    if (total > m->cands_cap) { orb_set_error("candidate workspace too small"); return ORB_ERR_CAPACITY; }
+    if ((st = ensure_cands(m, total)) != ORB_OK) return st;
     const int ne = (int)entries.size();
     const int n_items2 = fv2->n_nodes ? fv2->start[fv2->n_nodes] : 0;
     for (int i = 0; i < n_items2; ++i) if (fv2->items[i] >= (uint32_t)kf2->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }

@@ -5,7 +5,8 @@ indices where the reference stores MapPoint pointers."""
 import ctypes as C
 import numpy as np
 from .capi import check, lib, ptr
-from .views import Camera, Frame, FeatureVector, LastFrameView, MapPointView, ProjectedView, GridParams, u8, _addr
+from .views import (Camera, Frame, FeatureVector, LastFrameView, MapPointView, ProjectedView, GridParams, FrameBatchView,
+                    MapPointBatchView, LastFrameBatchView, u8, _addr)
 
 
 class ORBmatcher:
@@ -76,6 +77,46 @@ class ORBmatcher:
         check(lib().orb_search_by_projection_lastframe(self._h, C.byref(cv), C.byref(lv[0]), C.byref(c), C.c_float(th), int(forward),
                                                        int(backward), int(self.mbCheckOrientation), ptr(occ), ptr(match), C.byref(n)))
         return n.value, match[:Cur.N]
+
+    # ---- batched forms of the two tracking searches: one call for many frame pairs (BASELINE.json configs[3])
+    def SearchByProjectionBatch(self, frames, mappoints, th=3.0, occupied=None):
+        """frames: list of Frame (same camera), mappoints: list of dicts as SearchByProjection takes, occupied: list of arrays or None.
+        -> list of (nmatches, match) like the single call, from ONE library call."""
+        fb = pack_frames(frames)
+        qb = pack_points(mappoints, MP_FIELDS)
+        occ = None if occupied is None else _pad_stack([u8(o) for o in occupied], fb["stride"], np.uint8)
+        match, nm = self.search_mappoints_batch_packed(fb, qb, th, occ)
+        return [(int(nm[p]), match[p, :frames[p].N].copy()) for p in range(len(frames))]
+
+    def search_mappoints_batch_packed(self, fb, qb, th, occ=None, match=None, nm=None):
+        """Packed (pairs, stride) arrays in, (pairs, stride) matches out; bench.py calls this with pinned buffers."""
+        P, S = fb["pairs"], fb["stride"]
+        match = np.empty((P, S), np.int32) if match is None else match
+        nm = np.empty(P, np.int32) if nm is None else nm
+        fv = frame_batch_view(fb)
+        mv = MapPointBatchView(P, qb["stride"], _addr(qb["n"]), *[_addr(qb[k]) for k in MP_FIELDS])
+        check(lib().orb_search_by_projection_mappoints_batch(self._h, C.byref(fv), C.byref(mv), C.c_float(th), C.c_float(self.mfNNratio),
+                                                             ptr(occ), ptr(match), ptr(nm)))
+        return match, nm
+
+    def SearchByProjectionLastFrameBatch(self, curs, lasts, cam, th, forward, backward, occupied=None):
+        """curs: list of Frame, lasts: list of dicts as SearchByProjectionLastFrame takes, forward / backward: one flag per pair."""
+        fb = pack_frames(curs)
+        qb = pack_points(lasts, LAST_FIELDS)
+        occ = None if occupied is None else _pad_stack([u8(o) for o in occupied], fb["stride"], np.uint8)
+        match, nm = self.search_lastframe_batch_packed(fb, qb, cam, th, u8(forward), u8(backward), occ)
+        return [(int(nm[p]), match[p, :curs[p].N].copy()) for p in range(len(curs))]
+
+    def search_lastframe_batch_packed(self, fb, qb, cam, th, forward, backward, occ=None, match=None, nm=None):
+        P, S = fb["pairs"], fb["stride"]
+        match = np.empty((P, S), np.int32) if match is None else match
+        nm = np.empty(P, np.int32) if nm is None else nm
+        fv = frame_batch_view(fb)
+        lv = LastFrameBatchView(P, qb["stride"], _addr(qb["n"]), *[_addr(qb[k]) for k in LAST_FIELDS])
+        c = Camera(*[float(v) for v in cam])
+        check(lib().orb_search_by_projection_lastframe_batch(self._h, C.byref(fv), C.byref(lv), C.byref(c), C.c_float(th), ptr(forward), ptr(backward),
+                                                             int(self.mbCheckOrientation), ptr(occ), ptr(match), ptr(nm)))
+        return match, nm
 
     # int SearchByBoW(KeyFrame *pKF, Frame &F, std::vector<MapPoint*> &vpMapPointMatches)
     def SearchByBoW(self, KF, kf_featvec, kf_has_mappoint, F, f_featvec):
@@ -173,6 +214,46 @@ class ORBmatcher:
         best = np.empty(max(P, 1), np.int32)
         check(lib().orb_distinctive_descriptors(self._h, P, ptr(start), ptr(desc), ptr(best)))
         return best[:P]
+
+
+MP_FIELDS = ("valid", "proj_x", "proj_y", "proj_xr", "level", "view_cos", "desc", "blocks")
+LAST_FIELDS = ("valid", "xc", "yc", "zc", "octave", "angle", "desc", "blocks")
+_DT = dict(valid=np.uint8, blocks=np.uint8, level=np.int32, octave=np.int32, desc=np.uint8)
+
+
+def _pad_stack(arrays, stride, dtype, width=None):
+    out = np.zeros((len(arrays), stride) + (() if width is None else (width,)), dtype)
+    for p, a in enumerate(arrays):
+        out[p, :len(a)] = a
+    return out
+
+
+def pack_frames(frames):
+    """list of Frame -> dict of (pairs, stride[, 32]) arrays for the batched entry points (one camera: grid and scale factors of frames[0])."""
+    S = max(max(f.N for f in frames), 1)
+    fb = dict(pairs=len(frames), stride=S, n=np.array([f.N for f in frames], np.int32), frame0=frames[0])
+    fb["x"] = _pad_stack([f.x for f in frames], S, np.float32); fb["y"] = _pad_stack([f.y for f in frames], S, np.float32)
+    fb["octave"] = _pad_stack([f.octave for f in frames], S, np.int32); fb["angle"] = _pad_stack([f.angle for f in frames], S, np.float32)
+    fb["u_right"] = None if frames[0].u_right is None else _pad_stack([f.u_right for f in frames], S, np.float32)
+    fb["desc"] = _pad_stack([f.desc for f in frames], S, np.uint8, 32)
+    return fb
+
+
+def frame_batch_view(fb):
+    f0 = fb["frame0"]
+    g = GridParams(f0.bounds[0], f0.bounds[1], f0.bounds[2], f0.bounds[3], f0.inv_w, f0.inv_h)
+    return FrameBatchView(fb["pairs"], fb["stride"], _addr(fb["n"]), _addr(fb["x"]), _addr(fb["y"]), _addr(fb["octave"]), _addr(fb["angle"]),
+                          _addr(fb["u_right"]), _addr(fb["desc"]), g, _addr(f0.sf), len(f0.sf))
+
+
+def pack_points(dicts, fields):
+    S = max(max(len(d["valid"]) for d in dicts), 1)
+    qb = dict(pairs=len(dicts), stride=S, n=np.array([len(d["valid"]) for d in dicts], np.int32))
+    for k in fields:
+        dt = _DT.get(k, np.float32)
+        arrs = [np.asarray(d[k]).astype(dt).reshape((-1, 32) if k == "desc" else (-1,)) for d in dicts]
+        qb[k] = _pad_stack(arrs, S, dt, 32 if k == "desc" else None)
+    return qb
 
 
 def _mp_view(d):

@@ -28,6 +28,23 @@ class LastFrameView(C.Structure):
                 ("octave", C.c_void_p), ("angle", C.c_void_p), ("desc", C.c_void_p), ("blocks", C.c_void_p)]
 
 
+class FrameBatchView(C.Structure):
+    _fields_ = [("pairs", C.c_int32), ("stride", C.c_int32), ("n", C.c_void_p), ("x", C.c_void_p), ("y", C.c_void_p), ("octave", C.c_void_p),
+                ("angle", C.c_void_p), ("u_right", C.c_void_p), ("desc", C.c_void_p), ("grid", GridParams), ("scale_factors", C.c_void_p),
+                ("n_levels", C.c_int32)]
+
+
+class MapPointBatchView(C.Structure):
+    _fields_ = [("pairs", C.c_int32), ("stride", C.c_int32), ("n", C.c_void_p), ("valid", C.c_void_p), ("proj_x", C.c_void_p),
+                ("proj_y", C.c_void_p), ("proj_xr", C.c_void_p), ("level", C.c_void_p), ("view_cos", C.c_void_p), ("desc", C.c_void_p),
+                ("blocks", C.c_void_p)]
+
+
+class LastFrameBatchView(C.Structure):
+    _fields_ = [("pairs", C.c_int32), ("stride", C.c_int32), ("n", C.c_void_p), ("valid", C.c_void_p), ("xc", C.c_void_p), ("yc", C.c_void_p),
+                ("zc", C.c_void_p), ("octave", C.c_void_p), ("angle", C.c_void_p), ("desc", C.c_void_p), ("blocks", C.c_void_p)]
+
+
 class Camera(C.Structure):
     _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("mbf", C.c_float)]
 

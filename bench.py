@@ -663,10 +663,22 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+class _Dev:
+    """A device tensor where the packed-view helpers expect a numpy array (they only read .ctypes.data)."""
+    def __init__(self, t):
+        import types
+        self.t = t
+        self.ctypes = types.SimpleNamespace(data=t.data_ptr())
+
+
 def bench_matching(local):
     """BASELINE.json configs[3] beside the headline step (rank 0, outside its timed region): ORBmatcher Hamming matching on
-    2000 x 2000 descriptor sets, 1024 frame pairs: brute force (best / second best per row, device-resident, CUDA events on the
-    matcher's stream) and grid-guided SearchByProjection(Frame, MapPoints) through the host API (one call per frame)."""
+    2000 x 2000 descriptor sets, 1024 frame pairs per call:
+      bruteforce   best / second best per row, device-resident, CUDA events on the matcher's stream, against the MEASURED POPC rate
+      M4           SearchByProjection(Frame, MapPoints) (src/ORBmatcher.cc:47-133; ratio test), th 1 / 3 / 5, ONE batched call
+      M5           SearchByProjection(Cur, Last) (:1460-1619; rotation histogram), th 7 / 15, ONE batched call
+    M4 / M5 are timed twice: pinned HOST buffers in and out (what a caller of the C ABI sees) and device-resident buffers; the CPU
+    figure beside them is the oracle port of the same functions (pinned bit-exact to the reference's ORBmatcher.cc) on all host cores."""
     synth = importlib.import_module(PKG + ".synth")
     mt = importlib.import_module(PKG + ".matcher")
     views = importlib.import_module(PKG + ".views")
@@ -678,7 +690,7 @@ def bench_matching(local):
     a = rng.integers(0, 256, (U, N, 32), dtype=np.uint8)
     b = a[:, rng.permutation(N)] ^ np.packbits(rng.random((U, N, 256)) < 0.08, axis=2)
     a = np.tile(a, (P // U, 1, 1)); b = np.tile(b, (P // U, 1, 1))
-    m = mt.ORBmatcher(0.6, True, max_n=8192, max_pairs=1, device=local)
+    m = mt.ORBmatcher(0.6, True, max_n=2048, max_pairs=P, device=local)
     L = capi.lib()
     st = torch.cuda.ExternalStream(L.orb_matcher_stream(m._h), device=local)
     da = torch.from_numpy(a).cuda(); db = torch.from_numpy(b).cuda()
@@ -699,44 +711,133 @@ def bench_matching(local):
     e1.record(st)
     capi.check(L.orb_matcher_sync(m._h))
     bf_ms = e0.elapsed_time(e1) / K
-    # grid-guided projection search, host API, one frame per call
-    f, mps, occ = synth.make_projection_scenario(N, N, 0)
-    F = views.Frame(f["x"], f["y"], f["octave"], f["angle"], f["desc"], f["sf"], f["bounds"], f["u_right"])
-    for _ in range(3):
-        m.SearchByProjection(F, mps, 3.0, occ)
-    t0 = time.perf_counter(); reps = 50
-    for _ in range(reps):
-        n_sp, _ = m.SearchByProjection(F, mps, 3.0, occ)
-    sp_ms = (time.perf_counter() - t0) / reps * 1e3
-    # the same call from T host threads, one matcher handle (own stream) each: ORB-SLAM2 itself runs its matchers from the
-    # Tracking, LocalMapping and LoopClosing threads concurrently (threading)
-    T = 8
-    ms_ = [mt.ORBmatcher(0.6, True, max_n=8192, max_pairs=1, device=local) for _ in range(T)]
-
-    def worker(mm, out, k):
-        for _ in range(3):
-            mm.SearchByProjection(F, mps, 3.0, occ)
-        t = time.perf_counter()
-        for _ in range(reps):
-            mm.SearchByProjection(F, mps, 3.0, occ)
-        out[k] = time.perf_counter() - t
-    outs = [0.0] * T
-    ths = [threading.Thread(target=worker, args=(ms_[k], outs, k)) for k in range(T)]
-    for t in ths:
-        t.start()
-    for t in ths:
-        t.join()
-    mt_fps = T * reps / max(outs)
+    del da, db, bi, bd, sd
     popc = P * N * N * 8 / (bf_ms * 1e-3)
     ipk = load_json("profiles/MEASURED_INT_PEAKS.json", {})
     popc_lanes = float(ipk.get("tests", {}).get("popc", {}).get("lanes_per_clk_per_sm", 16.0))
     popc_peak = popc_lanes * int(ipk.get("sms", 148)) * 1965e6
-    return {"workload": "2000x2000 descriptors per frame pair, 1024 pairs (BASELINE.json configs[3])",
-            "bruteforce": {"ms_per_1024_pairs": bf_ms, "pairs_per_s": P / (bf_ms * 1e-3), "popc_Tops": popc / 1e12,
-                           "popc_peak_Tops": popc_peak / 1e12, "frac": popc / popc_peak,
-                           "peak_source": "measured: profiles/MEASURED_INT_PEAKS.json popc %.2f lanes/clk/SM x SMs x 1965 MHz" % popc_lanes},
-            "search_by_projection_host_api": {"ms_per_frame": sp_ms, "frames_per_s": 1e3 / sp_ms, "matches": int(n_sp), "th": 3.0,
-                                              "frames_per_s_8_host_threads": mt_fps}}
+    out = {"workload": "2000x2000 descriptors per frame pair, 1024 pairs per call (BASELINE.json configs[3])",
+           "bruteforce": {"ms_per_1024_pairs": bf_ms, "pairs_per_s": P / (bf_ms * 1e-3), "popc_Tops": popc / 1e12,
+                          "popc_peak_Tops": popc_peak / 1e12, "frac": popc / popc_peak,
+                          "peak_source": "measured: profiles/MEASURED_INT_PEAKS.json popc %.2f lanes/clk/SM x SMs x 1965 MHz" % popc_lanes}}
+
+    # ---- grid-guided searches, 1024 pairs per call
+    UQ = 16
+    cores = os.cpu_count() or 1
+    orc = _orc()
+
+    def pin(x):
+        t = torch.from_numpy(np.ascontiguousarray(x)).pin_memory()
+        return t.numpy(), t
+
+    def tiled(qb, fields):
+        o = dict(pairs=P, stride=qb["stride"]); keep = []
+        for k in ("n",) + tuple(fields):
+            if qb.get(k) is None:
+                o[k] = None
+                continue
+            o[k], t = pin(np.tile(qb[k], (P // UQ,) + (1,) * (qb[k].ndim - 1)))
+            keep.append(t)
+        return o, keep
+
+    def dev(o, fields):
+        d = dict(pairs=o["pairs"], stride=o["stride"])
+        for k in ("n",) + tuple(fields):
+            d[k] = None if o.get(k) is None else _Dev(torch.from_numpy(o[k]).cuda())
+        return d
+
+    def timed(call, reps=3):
+        call(); capi.check(L.orb_matcher_sync(m._h))
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            call()
+        capi.check(L.orb_matcher_sync(m._h))
+        return (time.perf_counter() - t0) / reps * 1e3
+
+    FR = ("x", "y", "octave", "angle", "u_right", "desc")
+    res = {}
+    # M4
+    scen = [synth.make_projection_scenario(N, N, i) for i in range(UQ)]
+    frames = [views.Frame(f["x"], f["y"], f["octave"], f["angle"], f["desc"], f["sf"], f["bounds"], f["u_right"]) for f, _, _ in scen]
+    fb0 = mt.pack_frames(frames); qb0 = mt.pack_points([s[1] for s in scen], mt.MP_FIELDS)
+    fb, k1 = tiled(fb0, FR); fb["frame0"] = frames[0]
+    qb, k2 = tiled(qb0, mt.MP_FIELDS)
+    occ, k3 = pin(np.tile(mt._pad_stack([mt.u8(s[2]) for s in scen], fb["stride"], np.uint8), (P // UQ, 1)))
+    match, k4 = pin(np.empty((P, fb["stride"]), np.int32)); nm, k5 = pin(np.empty(P, np.int32))
+    dfb = dev(fb, FR); dfb["frame0"] = frames[0]; dqb = dev(qb, mt.MP_FIELDS)
+    docc = torch.from_numpy(occ).cuda(); dmatch = torch.empty((P, fb["stride"]), dtype=torch.int32, device="cuda"); dnm = torch.empty(P, dtype=torch.int32, device="cuda")
+    m4 = {}
+    for th in (1.0, 3.0, 5.0):
+        ms_h = timed(lambda: m.search_mappoints_batch_packed(fb, qb, th, occ, match, nm))
+        cands = L.orb_matcher_last_candidates(m._h)
+        ms_d = timed(lambda: m.search_mappoints_batch_packed(dfb, dqb, th, docc.data_ptr(), dmatch.data_ptr(), dnm.data_ptr()))
+        # post-check of a few pairs of the timed batch against the oracle
+        for p in (0, 5, P - 1):
+            n_o, m_o = orc.search_by_projection_mps(frames[p % UQ], scen[p % UQ][1], th, m.mfNNratio, scen[p % UQ][2])
+            if int(nm[p]) != n_o or not np.array_equal(match[p, :frames[p % UQ].N], m_o):
+                raise SystemExit("bench.py: batched SearchByProjection differs from the oracle (pair %d, th %g)" % (p, th))
+        m4["th_%g" % th] = {"ms_per_1024_pairs_host_buffers": ms_h, "pairs_per_s_host_buffers": P / (ms_h * 1e-3),
+                            "ms_per_1024_pairs_device_resident": ms_d, "pairs_per_s_device_resident": P / (ms_d * 1e-3),
+                            "candidates_per_pair": cands / P, "popc_Gops_device_resident": cands * 8 / (ms_d * 1e-3) / 1e9,
+                            "matches_pair0": int(nm[0]), "parity_checked": 3}
+    # CPU: the same function on all cores (th 3)
+    def cpu_rate(fn, n_calls):
+        def work(tid, cnt):
+            for i in range(tid, n_calls, cores):
+                fn(i)
+                cnt[tid] += 1
+        cnt = [0] * cores
+        ts = [threading.Thread(target=work, args=(t, cnt)) for t in range(cores)]
+        t0 = time.perf_counter()
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        return sum(cnt) / (time.perf_counter() - t0)
+    cpu4 = cpu_rate(lambda i: orc.search_by_projection_mps(frames[i % UQ], scen[i % UQ][1], 3.0, 0.6, scen[i % UQ][2]), 16 * cores)
+    res["SearchByProjection_Frame_MapPoints"] = dict(m4, cpu_baseline={"value": cpu4, "unit": "frame pairs/s", "cores": cores, "kind": "port", "th": 3.0,
+                                                                       "sample": "%d calls of the oracle port on %d host threads (grid build included)" % (16 * cores, cores)})
+    del dfb, dqb, docc, dmatch, dnm, k1, k2, k3
+    # M5
+    scen5 = [synth.make_lastframe_scenario(N, i) for i in range(UQ)]
+    cam = scen5[0][2]
+    curs = [views.Frame(f["x"], f["y"], f["octave"], f["angle"], f["desc"], f["sf"], f["bounds"], f["u_right"]) for f, _, _ in scen5]
+    fb0 = mt.pack_frames(curs); qb0 = mt.pack_points([s[1] for s in scen5], mt.LAST_FIELDS)
+    fb, k1 = tiled(fb0, FR); fb["frame0"] = curs[0]
+    qb, k2 = tiled(qb0, mt.LAST_FIELDS)
+    fwd, k6 = pin(np.zeros(P, np.uint8)); bwd, k7 = pin(np.zeros(P, np.uint8))
+    match, k4 = pin(np.empty((P, fb["stride"]), np.int32))
+    dfb = dev(fb, FR); dfb["frame0"] = curs[0]; dqb = dev(qb, mt.LAST_FIELDS)
+    dfw = torch.zeros(P, dtype=torch.uint8, device="cuda"); dbw = torch.zeros(P, dtype=torch.uint8, device="cuda")
+    dmatch = torch.empty((P, fb["stride"]), dtype=torch.int32, device="cuda"); dnm = torch.empty(P, dtype=torch.int32, device="cuda")
+    m5 = {}
+    for th in (7.0, 15.0):
+        ms_h = timed(lambda: m.search_lastframe_batch_packed(fb, qb, cam, th, fwd, bwd, None, match, nm))
+        cands = L.orb_matcher_last_candidates(m._h)
+        ms_d = timed(lambda: m.search_lastframe_batch_packed(dfb, dqb, cam, th, dfw.data_ptr(), dbw.data_ptr(), None, dmatch.data_ptr(), dnm.data_ptr()))
+        for p in (0, 7, P - 1):
+            n_o, m_o = orc.search_by_projection_last(curs[p % UQ], scen5[p % UQ][1], cam, th, False, False, True)
+            if int(nm[p]) != n_o or not np.array_equal(match[p, :curs[p % UQ].N], m_o):
+                raise SystemExit("bench.py: batched SearchByProjection(Cur, Last) differs from the oracle (pair %d, th %g)" % (p, th))
+        m5["th_%g" % th] = {"ms_per_1024_pairs_host_buffers": ms_h, "pairs_per_s_host_buffers": P / (ms_h * 1e-3),
+                            "ms_per_1024_pairs_device_resident": ms_d, "pairs_per_s_device_resident": P / (ms_d * 1e-3),
+                            "candidates_per_pair": cands / P, "popc_Gops_device_resident": cands * 8 / (ms_d * 1e-3) / 1e9,
+                            "matches_pair0": int(nm[0]), "parity_checked": 3}
+    cpu5 = cpu_rate(lambda i: orc.search_by_projection_last(curs[i % UQ], scen5[i % UQ][1], cam, 15.0, False, False, True), 16 * cores)
+    res["SearchByProjection_Cur_Last"] = dict(m5, cpu_baseline={"value": cpu5, "unit": "frame pairs/s", "cores": cores, "kind": "port", "th": 15.0,
+                                                                "sample": "%d calls of the oracle port on %d host threads (grid build included)" % (16 * cores, cores)})
+    out["grid_guided"] = res
+    # the single-frame call for comparison (one frame per call: launch- and copy-latency bound)
+    f, mps, occ1 = scen[0]
+    one = mt.ORBmatcher(0.6, True, max_n=8192, max_pairs=1, device=local)
+    for _ in range(3):
+        one.SearchByProjection(frames[0], mps, 3.0, occ1)
+    t0 = time.perf_counter(); reps = 50
+    for _ in range(reps):
+        n_sp, _ = one.SearchByProjection(frames[0], mps, 3.0, occ1)
+    sp_ms = (time.perf_counter() - t0) / reps * 1e3
+    out["search_by_projection_single_call"] = {"ms_per_frame": sp_ms, "frames_per_s": 1e3 / sp_ms, "matches": int(n_sp), "th": 3.0}
+    return out
 
 
 def main():

@@ -145,6 +145,8 @@ int orb_matcher_create(int max_pairs, int max_n, int device, orb_matcher** out);
 void orb_matcher_destroy(orb_matcher* m);
 void* orb_matcher_stream(const orb_matcher* m);
 long long orb_matcher_launch_count(const orb_matcher* m);
+/* Candidates (keypoints inside the search windows, each one 256-bit Hamming distance) examined by the last projection search. */
+long long orb_matcher_last_candidates(const orb_matcher* m);
 int orb_matcher_sync(orb_matcher* m);
 
 /* DescriptorDistance for n descriptor pairs (a[i], b[i]); 32 bytes each. */

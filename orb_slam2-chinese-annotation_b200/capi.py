@@ -24,6 +24,7 @@ EXPORTS = [
     "orb_matcher_create", "orb_matcher_destroy", "orb_matcher_stream", "orb_matcher_launch_count", "orb_matcher_sync",
     "orb_descriptor_distance", "orb_match_bruteforce", "orb_match_bruteforce_device", "orb_assign_features_to_grid",
     "orb_search_by_projection_mappoints", "orb_search_by_projection_lastframe", "orb_search_by_bow",
+    "orb_search_by_projection_mappoints_batch", "orb_search_by_projection_lastframe_batch", "orb_matcher_last_candidates",
     "orb_search_for_triangulation", "orb_search_by_bow_keyframes", "orb_search_by_projection_claiming",
     "orb_search_projected_best", "orb_search_by_sim3", "orb_search_for_initialization", "orb_sincosf_sweep_device",
     "orb_vocabulary_create", "orb_vocabulary_destroy", "orb_vocabulary_info", "orb_vocabulary_stream", "orb_vocabulary_launch_count",
@@ -60,13 +61,14 @@ def lib():
         L.orb_matcher_stream.restype = C.c_void_p
         L.orb_extractor_launch_count.restype = C.c_longlong
         L.orb_matcher_launch_count.restype = C.c_longlong
+        L.orb_matcher_last_candidates.restype = C.c_longlong
         L.orb_vocabulary_stream.restype = C.c_void_p
         L.orb_rectifier_stream.restype = C.c_void_p
         L.orb_rectifier_launch_count.restype = C.c_longlong
         L.orb_vocabulary_launch_count.restype = C.c_longlong
         for name in ("orb_extractor_stream", "orb_extractor_launch_count", "orb_extractor_max_keypoints",
                      "orb_extractor_destroy", "orb_extractor_sync", "orb_matcher_stream", "orb_matcher_launch_count",
-                     "orb_matcher_destroy", "orb_matcher_sync", "orb_vocabulary_stream", "orb_vocabulary_launch_count",
+                     "orb_matcher_last_candidates", "orb_matcher_destroy", "orb_matcher_sync", "orb_vocabulary_stream", "orb_vocabulary_launch_count",
                      "orb_vocabulary_destroy", "orb_vocabulary_sync", "orb_rectifier_stream", "orb_rectifier_launch_count",
                      "orb_rectifier_destroy", "orb_rectifier_sync"):
             getattr(L, name).argtypes = [C.c_void_p]

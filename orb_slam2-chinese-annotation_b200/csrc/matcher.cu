@@ -28,6 +28,7 @@ struct orb_matcher {
     uint32_t* d_cands = nullptr;
     size_t cands_cap = 0;
     int* d_scal = nullptr;     // small device scalars
+    long long last_cands = 0;  // candidates examined by the last projection search (bench: popc work)
 };
 
 namespace {
@@ -987,6 +988,7 @@ void orb_matcher_destroy(orb_matcher* m) {
 
 void* orb_matcher_stream(const orb_matcher* m) { return m ? (void*)m->stream : nullptr; }
 long long orb_matcher_launch_count(const orb_matcher* m) { return m ? m->launches : 0; }
+long long orb_matcher_last_candidates(const orb_matcher* m) { return m ? m->last_cands : 0; }
 int orb_matcher_sync(orb_matcher* m) {
     if (!m) return ORB_ERR_BAD_ARG;
     ORB_CUDA(cudaSetDevice(m->device));
@@ -1097,6 +1099,7 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
         ORB_CUDA(cudaMemcpyAsync(&total, starts + nq, 4, cudaMemcpyDeviceToHost, m->stream));
         ORB_CUDA(cudaStreamSynchronize(m->stream));
         if ((st = ensure_cands(m, (size_t)total)) != ORB_OK) return st;
+        m->last_cands = total;
         k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, nullptr, starts, m->d_cands, Batch{0, nullptr, nullptr});
         m->launches += 3;
     } else {
@@ -1235,6 +1238,7 @@ int projection_batch(orb_matcher* m, int mode, int pairs, int qstride, const int
     ORB_CUDA(cudaStreamSynchronize(m->stream));
     if (total < 0) { orb_set_error("more than 2^31 candidates in one batch: split the call"); return ORB_ERR_CAPACITY; }
     if ((st = ensure_cands(m, (size_t)total)) != ORB_OK) return st;
+    m->last_cands = total;
     B.cand_base = bases;
     k_area_candidates<true><<<grid, 256, 0, m->stream>>>(0, dq, d_qdesc, F, FILTER_STEREO_WINDOW, nullptr, nullptr, starts, m->d_cands, B);
     const int occ_shared = F.stride <= 40 * 1024;

@@ -376,43 +376,65 @@ class Job:
             self.gr.set_timing(False)
         return {k: v / n_prof for k, v in acc.items() if c["stereo"] or not k.startswith("stereo")}
 
-    def e2e(self, steps):
+    def e2e(self, steps, copy_only=False):
         """The call a user of the reference makes, batched, HOST buffers in and out: Frame::Frame(left, right) = ExtractORB x2 +
-        ComputeStereoMatches (src/Frame.cc:60-115) -> orb_stereo_frames; a mono config -> orb_extract_batch."""
+        ComputeStereoMatches (src/Frame.cc:60-115) -> orb_stereo_frames_enqueue / _wait, two batches in flight on alternating pinned
+        buffer sets (the next batch is queued before the previous one is waited for, as a streaming caller does); a mono config ->
+        orb_extract_batch.  Every step uploads its images from pinned host memory and downloads all of its results."""
         torch, capi, c, B, cap = self.torch, self.capi, self.cfg, self.B, self.cap
         L = capi.lib()
         kp_sz = capi.KP_DTYPE.itemsize
         pl = torch.from_numpy(self.hl).pin_memory()
         sides = 2 if c["stereo"] else 1
-        o_k = [torch.empty((B, cap, kp_sz), dtype=torch.uint8).pin_memory() for _ in range(sides)]
-        o_d = [torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory() for _ in range(sides)]
-        o_n = [np.zeros(B, np.int32) for _ in range(3)]
+        capi.check(L.orb_extractor_set_copy_only(self.gl.handle, int(copy_only)))
+        nset = 2 if c["stereo"] else 1
+        sets = []
+        for _ in range(nset):
+            o_k = [torch.empty((B, cap, kp_sz), dtype=torch.uint8).pin_memory() for _ in range(sides)]
+            o_d = [torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory() for _ in range(sides)]
+            o_n = [np.zeros(B, np.int32) for _ in range(2)]
+            o_s = (torch.empty((B, cap), dtype=torch.float32).pin_memory(), torch.empty((B, cap), dtype=torch.float32).pin_memory()) if c["stereo"] else None
+            sets.append((o_k, o_d, o_n, o_s))
         if c["stereo"]:
             pr = torch.from_numpy(self.hr).pin_memory()
-            o_u = torch.empty((B, cap), dtype=torch.float32).pin_memory(); o_z = torch.empty((B, cap), dtype=torch.float32).pin_memory()
+            tick = C.c_int(0)
 
-            def step_host():
-                capi.check(L.orb_stereo_frames(self.gl.handle, self.gr.handle, C.c_void_p(pl.data_ptr()), C.c_void_p(pr.data_ptr()), B, c["w"], c["h"],
-                                               c["w"], C.c_size_t(c["w"] * c["h"]), C.c_float(c["mbf"]), C.c_float(0.0), C.c_float(c["fx"]),
-                                               C.c_void_p(o_k[0].data_ptr()), C.c_void_p(o_d[0].data_ptr()), capi.ptr(o_n[0]),
-                                               C.c_void_p(o_k[1].data_ptr()), C.c_void_p(o_d[1].data_ptr()), capi.ptr(o_n[1]),
-                                               C.c_void_p(o_u.data_ptr()), C.c_void_p(o_z.data_ptr()), cap))
+            def enqueue(i):
+                o_k, o_d, o_n, o_s = sets[i & 1]
+                capi.check(L.orb_stereo_frames_enqueue(self.gl.handle, self.gr.handle, C.c_void_p(pl.data_ptr()), C.c_void_p(pr.data_ptr()), B, c["w"], c["h"],
+                                                       c["w"], C.c_size_t(c["w"] * c["h"]), C.c_float(c["mbf"]), C.c_float(0.0), C.c_float(c["fx"]),
+                                                       C.c_void_p(o_k[0].data_ptr()), C.c_void_p(o_d[0].data_ptr()), C.c_void_p(o_k[1].data_ptr()),
+                                                       C.c_void_p(o_d[1].data_ptr()), C.c_void_p(o_s[0].data_ptr()), C.c_void_p(o_s[1].data_ptr()), cap, C.byref(tick)))
+                return tick.value
+
+            def wait(i, t):
+                o_n = sets[i & 1][2]
+                capi.check(L.orb_stereo_frames_wait(self.gl.handle, self.gr.handle, t, capi.ptr(o_n[0]), capi.ptr(o_n[1])))
+
+            def run(n):
+                t_prev = enqueue(0)
+                for i in range(1, n):
+                    t = enqueue(i)
+                    wait(i - 1, t_prev)
+                    t_prev = t
+                wait(n - 1, t_prev)
         else:
-            def step_host():
-                capi.check(L.orb_extract_batch(self.gl.handle, C.c_void_p(pl.data_ptr()), B, c["w"], c["h"], c["w"], C.c_size_t(c["w"] * c["h"]),
-                                               C.c_void_p(o_k[0].data_ptr()), C.c_void_p(o_d[0].data_ptr()), cap, capi.ptr(o_n[0])))
-        for _ in range(3):
-            step_host()
+            def run(n):
+                o_k, o_d, o_n, _ = sets[0]
+                for _ in range(n):
+                    capi.check(L.orb_extract_batch(self.gl.handle, C.c_void_p(pl.data_ptr()), B, c["w"], c["h"], c["w"], C.c_size_t(c["w"] * c["h"]),
+                                                   C.c_void_p(o_k[0].data_ptr()), C.c_void_p(o_d[0].data_ptr()), cap, capi.ptr(o_n[0])))
+        run(3)
         self.sync_all()
         t0 = time.perf_counter()
-        for _ in range(steps):
-            step_host()
+        run(steps)
         self.sync_all()
         ms = self.max_over_ranks((time.perf_counter() - t0) * 1e3)
+        capi.check(L.orb_extractor_set_copy_only(self.gl.handle, 0))
         h2d = sides * B * c["w"] * c["h"]
         # slot rows are downloaded whole (cap == the handle's kp_cap): keypoints + descriptors per side, uRight, depth, counts
         d2h = int(B * cap * (sides * (kp_sz + 32) + (8 if c["stereo"] else 0)) + sides * B * 4 + 8)
-        self.host_out = (o_k, o_d, o_n, (o_u, o_z) if c["stereo"] else None)
+        self.host_out = sets[(steps - 1) & 1] if c["stereo"] else sets[0]
         return ms, h2d, d2h
 
 
@@ -600,6 +622,16 @@ def run_ours(args):
     warmup = max(args.warmup, 3)
     cores = os.cpu_count() or 1
     job = Job(cfg, B, local, rank, dist)
+    if args.copy_only:   # the host-buffer pipeline with the kernels skipped: the copy ceiling of e2e at this GPU count
+        e_steps = max(6, args.steps)
+        e_ms, h2d, d2h = job.e2e(e_steps, copy_only=True)
+        if rank == 0:
+            print(json.dumps({"copy_only": True, "n_gpus": world, "unit": "frames/s", "value": world * B * e_steps / (e_ms * 1e-3), "steps": e_steps,
+                              "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "pairs_per_step_per_gpu": B,
+                              "per_gpu_GBs": (h2d + d2h) * e_steps / (e_ms * 1e-3) / 1e9, "workload": cfg["workload"]}), flush=True)
+        if dist is not None:
+            dist.barrier(); dist.destroy_process_group()
+        return
     if args.profile_run:   # exactly two device-resident steps and nothing else (tools/ncu_counts.py captures these launches)
         job.step_device(); job.step_device(); job.sync_all()
         print(json.dumps({"profile_run": True, "steps": 2, "pairs_per_step": B, "workload": cfg["workload"]}), flush=True)
@@ -847,6 +879,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=256, help="stereo pairs per step per GPU")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--copy-only", action="store_true", help="e2e pipeline with the kernels skipped (copy ceiling), one JSON line")
     ap.add_argument("--profile-run", action="store_true", help="two device-resident steps only, for ncu")
     ap.add_argument("--headline-only", action="store_true", help="skip the extra configs / latency / matching sections (profiling runs)")
     args = ap.parse_args()

@@ -135,6 +135,18 @@ int orb_stereo_frames(orb_extractor* left, orb_extractor* right, const uint8_t* 
                       int w, int h, int stride, size_t img_stride, float mbf, float min_d, float max_d,
                       orb_keypoint* kps_l, uint8_t* desc_l, int32_t* n_l, orb_keypoint* kps_r, uint8_t* desc_r, int32_t* n_r,
                       float* u_right, float* depth, int cap);
+/* Asynchronous form: enqueue() returns as soon as the batch is queued, wait() when its outputs are in the caller's buffers.  Two
+ * batches may be in flight on one handle pair (same geometry and batch size); chunk c of the second only waits for chunk c of the
+ * first, so consecutive batches hide each other's first upload and last download.  Tickets are waited for in issue order; the
+ * buffers of an enqueued batch stay alive and untouched until its wait() returns.  orb_stereo_frames == enqueue + wait. */
+int orb_stereo_frames_enqueue(orb_extractor* left, orb_extractor* right, const uint8_t* imgs_l, const uint8_t* imgs_r, int batch,
+                              int w, int h, int stride, size_t img_stride, float mbf, float min_d, float max_d,
+                              orb_keypoint* kps_l, uint8_t* desc_l, orb_keypoint* kps_r, uint8_t* desc_r, float* u_right,
+                              float* depth, int cap, int* ticket);
+int orb_stereo_frames_wait(orb_extractor* left, orb_extractor* right, int ticket, int32_t* n_l, int32_t* n_r);
+/* Diagnostic: the host-buffer entry points of this handle (orb_extract_batch, orb_stereo_frames*; set it on the LEFT handle for
+ * the stereo ones) skip the kernels and only move the bytes: the copy ceiling of the pipeline (bench.py --copy-only). */
+int orb_extractor_set_copy_only(orb_extractor* e, int on);
 int orb_stereo_match_device(orb_extractor* left, orb_extractor* right, int batch, float mbf, float min_d, float max_d);
 int orb_stereo_device_results(const orb_extractor* left, const float** d_u_right, const float** d_depth);
 

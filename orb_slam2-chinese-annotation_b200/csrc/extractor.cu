@@ -221,6 +221,8 @@ void free_buffers(orb_extractor* e) {
     for (int i = 0; i < ORB_N_STAGES + 4; ++i) if (e->ev_stage[i]) cudaEventDestroy(e->ev_stage[i]);
     if (e->h_pin) cudaFreeHost(e->h_pin);
     if (e->h_counts) cudaFreeHost(e->h_counts);
+    if (e->h_status) cudaFreeHost(e->h_status);
+    for (int i = 0; i < 2; ++i) if (e->ev_call[i]) cudaEventDestroy(e->ev_call[i]);
     for (cudaEvent_t ev : e->ev_pool) cudaEventDestroy(ev);
     if (e->s_h2d) cudaStreamDestroy(e->s_h2d);
     if (e->s_d2h) cudaStreamDestroy(e->s_d2h);
@@ -386,10 +388,11 @@ int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w
 }
 // Results of slots [b0, b0 + n) -> the caller's [batch][cap] arrays; counts land in e->h_counts.
 // Whole slot rows are copied (one strided copy per array): the tail beyond counts[b] is unspecified.
-int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st) {
+int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st, int* h_counts) {
     const int kc = e->plan.kp_cap;
     const int m = cap < kc ? cap : kc;
-    ORB_CUDA(cudaMemcpyAsync(e->h_counts + b0, e->d_counts + b0, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (!h_counts) h_counts = e->h_counts;
+    ORB_CUDA(cudaMemcpyAsync(h_counts + b0, e->d_counts + b0, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, st));
     if (m > 0) {
         ORB_CUDA(cudaMemcpy2DAsync(kps + (size_t)b0 * cap, (size_t)cap * sizeof(orb_keypoint), e->d_kps + (size_t)b0 * kc, (size_t)kc * sizeof(orb_keypoint),
                                    (size_t)m * sizeof(orb_keypoint), n, cudaMemcpyDeviceToHost, st));
@@ -466,7 +469,10 @@ int orb_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini
     cudaMemset(e->d_counts, 0, B * sizeof(int));
     cudaMemset(e->d_pyr, 0, e->pyr_cap * B);
     cudaMemset(e->d_blur, 0, e->pyr_cap * B);
-    if (cudaMallocHost((void**)&e->h_counts, B * 2 * sizeof(int)) != cudaSuccess) { free_buffers(e); delete e; orb_set_error("pinned alloc"); return ORB_ERR_CUDA; }
+    if (cudaMallocHost((void**)&e->h_counts, B * 2 * sizeof(int)) != cudaSuccess || cudaMallocHost((void**)&e->h_status, 4 * sizeof(int)) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ev_call[0], cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&e->ev_call[1], cudaEventDisableTiming) != cudaSuccess) {
+        free_buffers(e); delete e; orb_set_error("pinned alloc"); return ORB_ERR_CUDA;
+    }
     *out = e;
     return ORB_OK;
 }
@@ -589,18 +595,18 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, i
     // uploads must not overtake work already queued on the kernel stream
     ORB_CUDA(cudaEventRecord(e->ev_pool[2 * nch], e->stream));
     ORB_CUDA(cudaStreamWaitEvent(e->s_h2d, e->ev_pool[2 * nch], 0));
+    // on an error after the first enqueue nothing may stay in flight: the caller is free to release its buffers
+    auto fail = [&](int code) { cudaStreamSynchronize(e->s_h2d); cudaStreamSynchronize(e->stream); cudaStreamSynchronize(e->s_d2h); return code; };
     for (int c = 0; c < nch; ++c) {
         const int b0 = cb[c], n = cb[c + 1] - cb[c];
         st = orb_upload_slots(e, imgs, b0, n, w, h, stride, img_stride, e->s_h2d);
-        if (st != ORB_OK) return st;
-        ORB_CUDA(cudaEventRecord(e->ev_pool[2 * c], e->s_h2d));
-        ORB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_pool[2 * c], 0));
-        st = run_pipeline(e, b0, n);
-        if (st != ORB_OK) return st;
-        ORB_CUDA(cudaEventRecord(e->ev_pool[2 * c + 1], e->stream));
-        ORB_CUDA(cudaStreamWaitEvent(e->s_d2h, e->ev_pool[2 * c + 1], 0));
+        if (st != ORB_OK) return fail(st);
+        if (cudaEventRecord(e->ev_pool[2 * c], e->s_h2d) != cudaSuccess || cudaStreamWaitEvent(e->stream, e->ev_pool[2 * c], 0) != cudaSuccess) return fail(ORB_ERR_CUDA);
+        st = e->copy_only ? ORB_OK : run_pipeline(e, b0, n);
+        if (st != ORB_OK) return fail(st);
+        if (cudaEventRecord(e->ev_pool[2 * c + 1], e->stream) != cudaSuccess || cudaStreamWaitEvent(e->s_d2h, e->ev_pool[2 * c + 1], 0) != cudaSuccess) return fail(ORB_ERR_CUDA);
         st = orb_download_slots(e, b0, n, kps, desc, cap, e->s_d2h);
-        if (st != ORB_OK) return st;
+        if (st != ORB_OK) return fail(st);
     }
     int dst = 0;
     ORB_CUDA(cudaMemcpyAsync(&dst, e->d_status, sizeof(int), cudaMemcpyDeviceToHost, e->s_d2h));

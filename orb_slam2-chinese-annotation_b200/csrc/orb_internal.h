@@ -136,7 +136,13 @@ struct orb_extractor {
     // pinned host staging
     uint8_t* h_pin = nullptr;
     size_t h_pin_cap = 0;
-    int* h_counts = nullptr;        // pinned [max_batch * 2]
+    int* h_counts = nullptr;        // pinned [2][max_batch]: one half per in-flight stereo batch (ticket parity)
+    int* h_status = nullptr;        // pinned [4]: device status words (left, right) per ticket parity
+    // asynchronous stereo batches (orb_stereo_frames_enqueue / _wait); state lives in the LEFT handle
+    int inflight = 0, next_ticket = 0, pipe_chunks = 0;
+    int pipe_batch[2] = {0, 0}, pipe_cap[2] = {0, 0};
+    cudaEvent_t ev_call[2] = {nullptr, nullptr};
+    bool copy_only = false;         // diagnostic: host-buffer entry points skip the kernels (copy ceiling of the pipeline)
 };
 
 void orb_set_error(const std::string& s);
@@ -149,7 +155,7 @@ int orb_chunk_size(int batch);
 // chunk boundaries of a host batch: bounds[0] = 0 < ... < bounds[n] = batch (ramped sizes, see extractor.cu)
 std::vector<int> orb_chunk_bounds(int batch);
 int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, int stride, size_t img_stride, cudaStream_t st);
-int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st);
+int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st, int* h_counts = nullptr);
 #define ORB_CUDA(call)                                                                      \
     do {                                                                                    \
         cudaError_t err__ = (call);                                                         \

@@ -303,6 +303,132 @@ int orb_stereo_match_batch(orb_extractor* l, orb_extractor* r, int batch, float 
     return rc;
 }
 
+// Asynchronous form of the stereo Frame constructor: enqueue() queues uploads, kernels and downloads of the whole batch on the
+// handle pair's three streams and returns; wait() blocks until that call's outputs are in the caller's buffers.  Two calls may be in
+// flight on one handle pair (tickets alternate): chunk c of the next call only waits for chunk c of the previous one (its kernels
+// before the slot is uploaded again, its downloads before the slot's results are overwritten), so the first upload and the last
+// download of consecutive calls overlap with kernels instead of being exposed.  The caller keeps the input and output buffers of
+// an enqueued call alive and untouched until its wait() returns.
+int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t* imgs_l, const uint8_t* imgs_r, int batch, int w, int h, int stride,
+                              size_t img_stride, float mbf, float min_d, float max_d, orb_keypoint* kps_l, uint8_t* desc_l, orb_keypoint* kps_r,
+                              uint8_t* desc_r, float* u_right, float* depth, int cap, int* ticket) {
+    if (!l || !r || l == r || batch < 1 || !ticket) return ORB_ERR_BAD_ARG;
+    if (!imgs_l || !imgs_r || !kps_l || !desc_l || !kps_r || !desc_r || !u_right || !depth || w < 1 || h < 1 || stride < w) return ORB_ERR_BAD_ARG;
+    if (l->device != r->device) { orb_set_error("left and right extractor must share a device"); return ORB_ERR_BAD_ARG; }
+    if (l->inflight >= 2) { orb_set_error("two stereo batches are already in flight on this handle pair: wait for one"); return ORB_ERR_CAPACITY; }
+    ORB_CUDA(cudaSetDevice(l->device));
+    // a different batch size or geometry re-lays the level buffers out: only with nothing in flight
+    if (l->inflight > 0 && (l->plan_w != w || l->plan_h != h || l->last_batch != batch)) {
+        orb_set_error("geometry / batch size must not change while a stereo batch is in flight");
+        return ORB_ERR_BAD_ARG;
+    }
+    int st = orb_ensure_plan(l, w, h, batch);
+    if (st == ORB_OK) st = orb_ensure_plan(r, w, h, batch);
+    if (st == ORB_OK) st = orb_pipe_streams(l);
+    if (st == ORB_OK) st = orb_pipe_streams(r);   // the right handle's upload staging area
+    if (st != ORB_OK) return st;
+    const std::vector<int> cb = orb_chunk_bounds(batch);
+    const int nch = (int)cb.size() - 1;
+    // events per chunk: upload left / right done, kernels done, downloads done; + 2 for the call
+    if (!orb_pool_event(l, 4 * nch + 4)) { orb_set_error("event"); return ORB_ERR_CUDA; }
+    const int tk = l->next_ticket & 1;
+    // uploads must not overtake work already queued on the two kernel streams by other entry points
+    if (l->inflight == 0) {
+        ORB_CUDA(cudaEventRecord(l->ev_pool[4 * nch], l->stream));
+        ORB_CUDA(cudaEventRecord(l->ev_pool[4 * nch + 1], r->stream));
+        ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, l->ev_pool[4 * nch], 0));
+        ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, l->ev_pool[4 * nch + 1], 0));
+    }
+    const bool chained = l->inflight > 0 && l->pipe_chunks == nch;   // the previous call used the same chunking: chunk-granular hand-over
+    if (l->inflight > 0 && !chained) {
+        ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, l->ev_call[tk ^ 1], 0));
+        ORB_CUDA(cudaStreamWaitEvent(l->stream, l->ev_call[tk ^ 1], 0));
+        ORB_CUDA(cudaStreamWaitEvent(r->stream, l->ev_call[tk ^ 1], 0));
+    }
+    const int kc = l->plan.kp_cap, m = cap < kc ? cap : kc;
+    int* hc_l = l->h_counts + (size_t)tk * l->max_batch;
+    int* hc_r = r->h_counts + (size_t)tk * r->max_batch;
+    for (int c = 0; c < nch; ++c) {
+        const int b0 = cb[c], n = cb[c + 1] - cb[c];
+        cudaEvent_t up_l = l->ev_pool[4 * c], up_r = l->ev_pool[4 * c + 1], done = l->ev_pool[4 * c + 2], dl = l->ev_pool[4 * c + 3];
+        if (chained) {   // events still hold the previous call's records for this chunk
+            ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, done, 0));     // its kernels have read the slot's images
+            ORB_CUDA(cudaStreamWaitEvent(l->stream, dl, 0));      // its results have left the slot
+            ORB_CUDA(cudaStreamWaitEvent(r->stream, dl, 0));
+        }
+        // Frame::Frame: ExtractORB(0, left) and ExtractORB(1, right) run side by side (src/Frame.cc:81-84) ...
+        if ((st = orb_upload_slots(l, imgs_l, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
+        ORB_CUDA(cudaEventRecord(up_l, l->s_h2d));
+        if ((st = orb_upload_slots(r, imgs_r, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
+        ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
+        ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
+        const bool skip = l->copy_only;
+        if (!skip && (st = orb_run_slots(l, b0, n)) != ORB_OK) break;
+        ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
+        if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
+        // ... then ComputeStereoMatches (:95)
+        if (!skip && (st = stereo_launch(l, r, b0, n, mbf, min_d, max_d, false)) != ORB_OK) break;
+        if (skip) {   // copy-only diagnostic: keep the stream dependencies of the real pipeline
+            ORB_CUDA(cudaEventRecord(l->ev_done, r->stream));
+            ORB_CUDA(cudaStreamWaitEvent(l->stream, l->ev_done, 0));
+        }
+        ORB_CUDA(cudaEventRecord(done, l->stream));
+        ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, done, 0));
+        if ((st = orb_download_slots(l, b0, n, kps_l, desc_l, cap, l->s_d2h, hc_l)) != ORB_OK) break;
+        if ((st = orb_download_slots(r, b0, n, kps_r, desc_r, cap, l->s_d2h, hc_r)) != ORB_OK) break;
+        if (m > 0) {
+            ORB_CUDA(cudaMemcpy2DAsync(u_right + (size_t)b0 * cap, (size_t)cap * 4, l->d_u_right + (size_t)b0 * kc, (size_t)kc * 4, (size_t)m * 4, n,
+                                       cudaMemcpyDeviceToHost, l->s_d2h));
+            ORB_CUDA(cudaMemcpy2DAsync(depth + (size_t)b0 * cap, (size_t)cap * 4, l->d_depth + (size_t)b0 * kc, (size_t)kc * 4, (size_t)m * 4, n,
+                                       cudaMemcpyDeviceToHost, l->s_d2h));
+        }
+        ORB_CUDA(cudaEventRecord(dl, l->s_d2h));
+    }
+    if (st != ORB_OK) {   // nothing of this call may stay in flight once the caller is told it failed (its buffers may go away)
+        cudaStreamSynchronize(l->s_h2d); cudaStreamSynchronize(l->stream); cudaStreamSynchronize(r->stream); cudaStreamSynchronize(l->s_d2h);
+        l->inflight = 0; l->pipe_chunks = 0;
+        return st;
+    }
+    ORB_CUDA(cudaMemcpyAsync(&l->h_status[2 * tk], l->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->s_d2h));
+    ORB_CUDA(cudaMemcpyAsync(&l->h_status[2 * tk + 1], r->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->s_d2h));
+    ORB_CUDA(cudaEventRecord(l->ev_call[tk], l->s_d2h));
+    l->pipe_chunks = nch;
+    l->pipe_batch[tk] = batch; l->pipe_cap[tk] = cap;
+    *ticket = l->next_ticket++;
+    l->inflight++;
+    return ORB_OK;
+}
+
+int orb_stereo_frames_wait(orb_extractor* l, orb_extractor* r, int ticket, int32_t* n_l, int32_t* n_r) {
+    if (!l || !r || !n_l || !n_r) return ORB_ERR_BAD_ARG;
+    if (l->inflight < 1 || ticket != l->next_ticket - l->inflight) { orb_set_error("tickets are waited for in the order they were issued"); return ORB_ERR_BAD_ARG; }
+    ORB_CUDA(cudaSetDevice(l->device));
+    const int tk = ticket & 1;
+    ORB_CUDA(cudaEventSynchronize(l->ev_call[tk]));
+    l->inflight--;
+    if (l->inflight == 0) {
+        // the right stream has nothing queued beyond what the downloads waited for, but later calls on the right handle alone
+        // must see it idle
+        ORB_CUDA(cudaStreamSynchronize(r->stream));
+    }
+    const int st_l = l->h_status[2 * tk], st_r = l->h_status[2 * tk + 1];
+    if (st_l != 0 || st_r != 0) {
+        cudaMemsetAsync(l->d_status, 0, sizeof(int), l->stream); cudaMemsetAsync(r->d_status, 0, sizeof(int), r->stream);
+        orb_set_error("device-side bound exceeded");
+        return st_l ? st_l : st_r;
+    }
+    const int batch = l->pipe_batch[tk], cap = l->pipe_cap[tk];
+    const int* hc_l = l->h_counts + (size_t)tk * l->max_batch;
+    const int* hc_r = r->h_counts + (size_t)tk * r->max_batch;
+    int rc = ORB_OK;
+    for (int b = 0; b < batch; ++b) {
+        n_l[b] = hc_l[b]; n_r[b] = hc_r[b];
+        if (n_l[b] > cap || n_r[b] > cap) rc = ORB_ERR_CAPACITY;
+    }
+    if (rc != ORB_OK) orb_set_error("keypoint capacity too small");
+    return rc;
+}
+
 int orb_stereo_frames(orb_extractor* l, orb_extractor* r, const uint8_t* imgs_l, const uint8_t* imgs_r, int batch, int w, int h, int stride,
                       size_t img_stride, float mbf, float min_d, float max_d, orb_keypoint* kps_l, uint8_t* desc_l, int32_t* n_l,
                       orb_keypoint* kps_r, uint8_t* desc_r, int32_t* n_r, float* u_right, float* depth, int cap) {
@@ -312,79 +438,18 @@ int orb_stereo_frames(orb_extractor* l, orb_extractor* r, const uint8_t* imgs_l,
         for (int b = 0; b < batch; ++b) n_l[b] = n_r[b] = 0;
         return ORB_OK;
     }
-    if (!imgs_l || !imgs_r || !kps_l || !desc_l || !kps_r || !desc_r || !u_right || !depth || w < 0 || h < 0 || stride < w) return ORB_ERR_BAD_ARG;
-    if (l->device != r->device) { orb_set_error("left and right extractor must share a device"); return ORB_ERR_BAD_ARG; }
-    ORB_CUDA(cudaSetDevice(l->device));
-    int st = orb_ensure_plan(l, w, h, batch);
-    if (st == ORB_OK) st = orb_ensure_plan(r, w, h, batch);
-    if (st == ORB_OK) st = orb_pipe_streams(l);
-    if (st == ORB_OK) st = orb_pipe_streams(r);   // the right handle's upload staging area
+    if (l->inflight > 0) { orb_set_error("an enqueued stereo batch is still in flight on this handle pair"); return ORB_ERR_BAD_ARG; }
+    int ticket = 0;
+    int st = orb_stereo_frames_enqueue(l, r, imgs_l, imgs_r, batch, w, h, stride, img_stride, mbf, min_d, max_d, kps_l, desc_l, kps_r, desc_r,
+                                       u_right, depth, cap, &ticket);
     if (st != ORB_OK) return st;
-    const std::vector<int> cb = orb_chunk_bounds(batch);
-    const int nch = (int)cb.size() - 1, chunk = cb[1];
-    const bool dbg = getenv("ORB_B200_DEBUG") != nullptr;
-    const auto t_begin = std::chrono::steady_clock::now();
-    if (!orb_pool_event(l, 3 * nch + 1)) { orb_set_error("event"); return ORB_ERR_CUDA; }
-    // uploads must not overtake work already queued on the two kernel streams
-    ORB_CUDA(cudaEventRecord(l->ev_pool[3 * nch], l->stream));
-    ORB_CUDA(cudaEventRecord(l->ev_pool[3 * nch + 1], r->stream));
-    ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, l->ev_pool[3 * nch], 0));
-    ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, l->ev_pool[3 * nch + 1], 0));
-    const int kc = l->plan.kp_cap, m = cap < kc ? cap : kc;
-    for (int c = 0; c < nch; ++c) {
-        const int b0 = cb[c], n = cb[c + 1] - cb[c];
-        cudaEvent_t up_l = l->ev_pool[3 * c], up_r = l->ev_pool[3 * c + 1], done = l->ev_pool[3 * c + 2];
-        // Frame::Frame: ExtractORB(0, left) and ExtractORB(1, right) run side by side (src/Frame.cc:81-84) ...
-        if ((st = orb_upload_slots(l, imgs_l, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) return st;
-        ORB_CUDA(cudaEventRecord(up_l, l->s_h2d));
-        if ((st = orb_upload_slots(r, imgs_r, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) return st;
-        ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
-        ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
-        const bool skip = dbg && getenv("ORB_B200_SKIP_COMPUTE");
-        if (!skip && (st = orb_run_slots(l, b0, n)) != ORB_OK) return st;
-        ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
-        if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) return st;
-        // ... then ComputeStereoMatches (:95)
-        if (!skip && (st = stereo_launch(l, r, b0, n, mbf, min_d, max_d, false)) != ORB_OK) return st;
-        ORB_CUDA(cudaEventRecord(done, l->stream));
-        ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, done, 0));
-        if ((st = orb_download_slots(l, b0, n, kps_l, desc_l, cap, l->s_d2h)) != ORB_OK) return st;
-        if ((st = orb_download_slots(r, b0, n, kps_r, desc_r, cap, l->s_d2h)) != ORB_OK) return st;
-        if (m > 0) {
-            ORB_CUDA(cudaMemcpy2DAsync(u_right + (size_t)b0 * cap, (size_t)cap * 4, l->d_u_right + (size_t)b0 * kc, (size_t)kc * 4, (size_t)m * 4, n,
-                                       cudaMemcpyDeviceToHost, l->s_d2h));
-            ORB_CUDA(cudaMemcpy2DAsync(depth + (size_t)b0 * cap, (size_t)cap * 4, l->d_depth + (size_t)b0 * kc, (size_t)kc * 4, (size_t)m * 4, n,
-                                       cudaMemcpyDeviceToHost, l->s_d2h));
-        }
-    }
-    const auto t_enq = std::chrono::steady_clock::now();
-    if (dbg) {
-        ORB_CUDA(cudaStreamSynchronize(l->s_h2d)); const auto t1 = std::chrono::steady_clock::now();
-        ORB_CUDA(cudaStreamSynchronize(l->stream)); ORB_CUDA(cudaStreamSynchronize(r->stream)); const auto t2 = std::chrono::steady_clock::now();
-        ORB_CUDA(cudaStreamSynchronize(l->s_d2h)); const auto t3 = std::chrono::steady_clock::now();
-        auto ms = [&](std::chrono::steady_clock::time_point a) { return std::chrono::duration<double, std::milli>(a - t_begin).count(); };
-        fprintf(stderr, "[orb_stereo_frames] batch %d chunk %d: enqueued %.2f ms, uploads done %.2f, kernels done %.2f, downloads done %.2f\n",
-                batch, chunk, ms(t_enq), ms(t1), ms(t2), ms(t3));
-    }
-    int st_l = 0, st_r = 0;
-    ORB_CUDA(cudaMemcpyAsync(&st_l, l->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->s_d2h));
-    ORB_CUDA(cudaMemcpyAsync(&st_r, r->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->s_d2h));
-    ORB_CUDA(cudaStreamSynchronize(l->s_d2h));
-    // the right stream has nothing queued beyond what the downloads waited for, but later calls on
-    // the right handle alone must see it idle
-    ORB_CUDA(cudaStreamSynchronize(r->stream));
-    if (st_l != 0 || st_r != 0) {
-        cudaMemsetAsync(l->d_status, 0, sizeof(int), l->stream); cudaMemsetAsync(r->d_status, 0, sizeof(int), r->stream);
-        orb_set_error("device-side bound exceeded");
-        return st_l ? st_l : st_r;
-    }
-    int rc = ORB_OK;
-    for (int b = 0; b < batch; ++b) {
-        n_l[b] = l->h_counts[b]; n_r[b] = r->h_counts[b];
-        if (n_l[b] > cap || n_r[b] > cap) rc = ORB_ERR_CAPACITY;
-    }
-    if (rc != ORB_OK) orb_set_error("keypoint capacity too small");
-    return rc;
+    return orb_stereo_frames_wait(l, r, ticket, n_l, n_r);
+}
+
+int orb_extractor_set_copy_only(orb_extractor* e, int on) {
+    if (!e) return ORB_ERR_BAD_ARG;
+    e->copy_only = on != 0;
+    return ORB_OK;
 }
 
 int orb_stereo_match(orb_extractor* l, orb_extractor* r, int image, float mbf, float min_d, float max_d, float* u_right, float* depth, int cap,

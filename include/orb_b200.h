@@ -445,6 +445,23 @@ int orb_remap_device(orb_rectifier* r, const uint8_t* d_src, int src_stride, siz
 int orb_gray_device(orb_rectifier* r, const uint8_t* d_src, int w, int h, int channels, int rgb_order, int src_stride,
                     size_t src_img_stride, int batch, uint8_t* d_dst, int dst_stride, size_t dst_img_stride);
 
+/* ------------------------------------------------------------------ multi-GPU front end */
+/* Frames / stereo pairs of a batch are independent: one handle pair and one host thread per GPU inside the library, GPU g takes the
+ * contiguous block orb_multi_slice(batch, n, g) of a HOST batch (pinned buffers for full copy speed) and writes its rows of the
+ * caller's [batch][cap] outputs; no collective on the data path (north_star).  n_devices == 0: every visible GPU. */
+typedef struct orb_multi orb_multi;
+int orb_multi_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th, int max_w, int max_h,
+                     int max_batch_per_gpu, int n_devices, orb_multi** out);
+void orb_multi_destroy(orb_multi* m);
+int orb_multi_device_count(const orb_multi* m);
+int orb_multi_max_keypoints(const orb_multi* m);
+void orb_multi_slice(int batch, int n_parts, int part, int* first, int* count);
+int orb_multi_stereo_frames(orb_multi* m, const uint8_t* imgs_l, const uint8_t* imgs_r, int batch, int w, int h, int stride,
+                            size_t img_stride, float mbf, float min_d, float max_d, orb_keypoint* kps_l, uint8_t* desc_l, int32_t* n_l,
+                            orb_keypoint* kps_r, uint8_t* desc_r, int32_t* n_r, float* u_right, float* depth, int cap);
+int orb_multi_extract_batch(orb_multi* m, const uint8_t* imgs, int batch, int w, int h, int stride, size_t img_stride,
+                            orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts);
+
 #ifdef __cplusplus
 }
 #endif

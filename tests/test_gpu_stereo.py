@@ -65,3 +65,69 @@ def test_stereo_frames_chunked_equals_stepwise():
     okl, odl = ol.extract(il[18]); okr, odr = orr.extract(ir[18])
     our, odp, _, _ = orc.stereo_match(ol, orr, okl, odl, okr, odr, mbf, 0.0, fx)
     assert np.array_equal(o["u_right"][18][:nl[18]], our) and np.array_equal(o["desc_l"][18][:nl[18]], odl)
+
+
+def test_async_enqueue_wait_two_batches_in_flight():
+    """orb_stereo_frames_enqueue / _wait: two different batches in flight on one handle pair, waited for in order, each equal to
+    the synchronous call on the same images (chunk-granular hand-over between consecutive batches)."""
+    w, h, nf, mbf, fx = 752, 480, 1200, 47.90639384423901, 435.2046959714599
+    B = 19
+    gl = ext.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B)
+    gr = ext.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B)
+    pool = [synth.make_stereo_pair(w, h, i, fx=fx) for i in range(5)]
+    batches = []
+    for k in range(3):
+        il = np.stack([pool[(i * 3 + k) % 5][0] for i in range(B)]); ir = np.stack([pool[(i * 3 + k) % 5][1] for i in range(B)])
+        batches.append((np.ascontiguousarray(il), np.ascontiguousarray(ir)))   # (synth's right images are views: the stack is not C-ordered)
+    with pytest.raises(ValueError):
+        stereo.stereo_frames_enqueue(gl, gr, il, ir[:, :, ::-1], mbf, fx, {})
+    want = [{kk: v.copy() for kk, v in stereo.stereo_frames(gl, gr, il, ir, mbf, fx).items()} for il, ir in batches]
+    cap = gl.kp_cap
+    KP = importlib.import_module("orb_slam2-chinese-annotation_b200.capi").KP_DTYPE
+    def bufs():
+        return dict(kps_l=np.zeros((B, cap), KP), desc_l=np.zeros((B, cap, 32), np.uint8), n_l=np.zeros(B, np.int32),
+                    kps_r=np.zeros((B, cap), KP), desc_r=np.zeros((B, cap, 32), np.uint8), n_r=np.zeros(B, np.int32),
+                    u_right=np.zeros((B, cap), np.float32), depth=np.zeros((B, cap), np.float32))
+    outs = [bufs() for _ in range(3)]
+    t0 = stereo.stereo_frames_enqueue(gl, gr, batches[0][0], batches[0][1], mbf, fx, outs[0])
+    t1 = stereo.stereo_frames_enqueue(gl, gr, batches[1][0], batches[1][1], mbf, fx, outs[1])
+    capi = importlib.import_module("orb_slam2-chinese-annotation_b200.capi")
+    with pytest.raises(capi.OrbError):   # a third batch in flight is refused
+        stereo.stereo_frames_enqueue(gl, gr, batches[2][0], batches[2][1], mbf, fx, outs[2])
+    with pytest.raises(capi.OrbError):   # tickets are waited for in order
+        stereo.stereo_frames_wait(gl, gr, t1, outs[1])
+    stereo.stereo_frames_wait(gl, gr, t0, outs[0])
+    t2 = stereo.stereo_frames_enqueue(gl, gr, batches[2][0], batches[2][1], mbf, fx, outs[2])
+    stereo.stereo_frames_wait(gl, gr, t1, outs[1])
+    stereo.stereo_frames_wait(gl, gr, t2, outs[2])
+    for k in range(3):
+        assert np.array_equal(outs[k]["n_l"], want[k]["n_l"]) and np.array_equal(outs[k]["n_r"], want[k]["n_r"])
+        for b in range(B):
+            nl, nr = want[k]["n_l"][b], want[k]["n_r"][b]
+            for f in ("kps_l", "desc_l", "u_right", "depth"):
+                assert np.array_equal(outs[k][f][b][:nl], want[k][f][b][:nl]), (k, b, f)
+            for f in ("kps_r", "desc_r"):
+                assert np.array_equal(outs[k][f][b][:nr], want[k][f][b][:nr]), (k, b, f)
+    # the synchronous entry point still works afterwards
+    o = stereo.stereo_frames(gl, gr, batches[0][0], batches[0][1], mbf, fx)
+    assert np.array_equal(o["n_l"], want[0]["n_l"])
+
+
+def test_multi_gpu_front_end_equals_single_handle():
+    """orb_multi_stereo_frames: every visible GPU takes a contiguous block of the host batch, in sub-batches of max_batch_per_gpu;
+    the gathered outputs equal one handle pair's."""
+    w, h, nf, mbf, fx = 640, 480, 1000, 40.0, 517.3
+    B = 7
+    pool = [synth.make_stereo_pair(w, h, i, fx=fx) for i in range(3)]
+    il = np.stack([pool[i % 3][0] for i in range(B)]); ir = np.stack([pool[i % 3][1] for i in range(B)])
+    gl = ext.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B)
+    gr = ext.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B)
+    want = stereo.stereo_frames(gl, gr, il, ir, mbf, fx)
+    m = stereo.MultiGpuFrontEnd(nf, 1.2, 8, 20, 7, w, h, max_batch_per_gpu=2)
+    assert m.n_devices >= 1 and m.kp_cap == gl.kp_cap
+    got = m.stereo_frames(il, ir, mbf, fx)
+    assert np.array_equal(got["n_l"], want["n_l"]) and np.array_equal(got["n_r"], want["n_r"])
+    for b in range(B):
+        nl = want["n_l"][b]
+        for f in ("kps_l", "desc_l", "u_right", "depth"):
+            assert np.array_equal(got[f][b][:nl], want[f][b][:nl]), (b, f)

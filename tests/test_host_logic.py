@@ -249,3 +249,23 @@ def test_sharding_world_size_2_gloo(tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "GATHER_OK 5" in r.stdout
+
+
+def test_multi_gpu_slices_cover_the_batch_and_fail_loudly_without_a_gpu():
+    """orb_multi_slice (the library's frame sharding): contiguous blocks that tile [0, batch); orb_multi_create needs a device."""
+    import importlib
+    stereo = importlib.import_module("orb_slam2-chinese-annotation_b200.stereo")
+    capi = importlib.import_module("orb_slam2-chinese-annotation_b200.capi")
+    for batch in (0, 1, 7, 256, 1024, 1023):
+        for parts in (1, 2, 3, 8):
+            nxt = 0
+            sizes = []
+            for p in range(parts):
+                f, c = stereo.multi_slice(batch, parts, p)
+                assert f == nxt and c >= 0
+                nxt += c; sizes.append(c)
+            assert nxt == batch and max(sizes) - min(sizes) <= 1
+    if capi.lib().orb_device_count() == 0:
+        import pytest
+        with pytest.raises(capi.OrbError):
+            stereo.MultiGpuFrontEnd(1000, 1.2, 8, 20, 7, 640, 480, 4)

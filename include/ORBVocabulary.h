@@ -9,12 +9,15 @@
  * reference's order of double operations, so the weights are bit-equal.  No CPU fallback: without a
  * CUDA device loadFromTextFile throws.
  *
- * When the reference's DBoW2 headers (BowVector.h / FeatureVector.h) are included first, their types
- * are used; otherwise the minimal equivalents below stand in.
+ * score(a, b) (src/KeyFrameDatabase.cc:137,267, src/LoopClosing.cc:145) is the host-side merge of ScoringObject.cpp, chosen by
+ * the file's scoring type.  BowVector / FeatureVector are the reference's own DBoW2 containers, included by the path the
+ * reference uses (tests/cpp carries stand-ins under the same relative path for builds outside the reference tree).
+ * One object may be used from several threads (the library serialises the staged transform per handle).
  */
-#ifndef ORB_B200_ORBVOCABULARY_H
-#define ORB_B200_ORBVOCABULARY_H
+#ifndef ORBVOCABULARY_H   /* the guard of the file this one replaces */
+#define ORBVOCABULARY_H
 
+#include <cfloat>
 #include <cmath>
 #include <fstream>
 #include <map>
@@ -25,50 +28,14 @@
 #include "orb_b200.h"
 #include "orb_b200_cv.h"
 
-#ifndef __D_T_BOW_VECTOR__
-#define __D_T_BOW_VECTOR__
-namespace DBoW2 {
-typedef unsigned int WordId;
-typedef double WordValue;
-typedef unsigned int NodeId;
-enum LNorm { L1, L2 };
-enum WeightingType { TF_IDF, TF, IDF, BINARY };
-enum ScoringType { L1_NORM, L2_NORM, CHI_SQUARE, KL, BHATTACHARYYA, DOT_PRODUCT };
-// Thirdparty/DBoW2/DBoW2/BowVector.h:56-104, BowVector.cpp:26-84
-class BowVector : public std::map<WordId, WordValue> {
-public:
-    void addWeight(WordId id, WordValue v) {
-        iterator vit = this->lower_bound(id);
-        if (vit != this->end() && !(this->key_comp()(id, vit->first))) vit->second += v;
-        else this->insert(vit, value_type(id, v));
-    }
-    void addIfNotExist(WordId id, WordValue v) {
-        iterator vit = this->lower_bound(id);
-        if (vit == this->end() || (this->key_comp()(id, vit->first))) this->insert(vit, value_type(id, v));
-    }
-    void normalize(LNorm norm_type) {
-        double norm = 0.0;
-        if (norm_type == L1) { for (iterator it = begin(); it != end(); ++it) norm += std::fabs(it->second); }
-        else { for (iterator it = begin(); it != end(); ++it) norm += it->second * it->second; norm = std::sqrt(norm); }
-        if (norm > 0.0) for (iterator it = begin(); it != end(); ++it) it->second /= norm;
-    }
-};
-}  // namespace DBoW2
-#endif
+#include "Thirdparty/DBoW2/DBoW2/BowVector.h"
+#include "Thirdparty/DBoW2/DBoW2/FeatureVector.h"
 
-#ifndef __D_T_FEATURE_VECTOR__
-#define __D_T_FEATURE_VECTOR__
-namespace DBoW2 {
-// Thirdparty/DBoW2/DBoW2/FeatureVector.h:22-49, FeatureVector.cpp:31-47
-class FeatureVector : public std::map<NodeId, std::vector<unsigned int> > {
-public:
-    void addFeature(NodeId id, unsigned int i_feature) {
-        iterator vit = this->lower_bound(id);
-        if (vit != this->end() && vit->first == id) vit->second.push_back(i_feature);
-        else { vit = this->insert(vit, value_type(id, std::vector<unsigned int>())); vit->second.push_back(i_feature); }
-    }
-};
-}  // namespace DBoW2
+#ifdef ORB_B200_WITH_OPENCV
+// Inside the reference tree: the header this file replaces pulled in DBoW2's TemplatedVocabulary.h, whose file-scope
+// `using namespace std;` (TemplatedVocabulary.h:36) the reference's own headers rely on (Frame.h, Map.h, KeyFrameDatabase.h name
+// vector / list / set unqualified).  Kept for source compatibility there, and only there.
+using namespace std;
 #endif
 
 namespace ORB_SLAM2 {
@@ -143,6 +110,58 @@ public:
             for (DBoW2::BowVector::iterator vit = v.begin(); vit != v.end(); ++vit) vit->second /= nd;
         }
         if (must) v.normalize(norm);
+    }
+
+    // One feature: word id, weight and the node passed at level L - levelsup (TemplatedVocabulary.h:1239-1283)
+    void transform(const cv::Mat& feature, DBoW2::WordId& id, DBoW2::WordValue& weight, DBoW2::NodeId* nid = NULL, int levelsup = 0) const {
+        int32_t word = 0, node = 0;
+        const int st = orb_bow_transform(h_, feature.data, 1, levelsup, &word, &node);
+        if (st != ORB_OK) throw std::runtime_error(std::string("ORBVocabulary::transform (B200): ") + orb_last_error());
+        id = (DBoW2::WordId)word; weight = word_weight_[word];
+        if (nid) *nid = (DBoW2::NodeId)node;
+    }
+    DBoW2::WordId transform(const cv::Mat& feature) const {
+        if (empty()) return 0;
+        DBoW2::WordId id; DBoW2::WordValue w;
+        transform(feature, id, w);
+        return id;
+    }
+
+    // Similarity of two bag-of-words vectors under the vocabulary's scoring type (TemplatedVocabulary.h:1213-1218 ->
+    // ScoringObject.cpp:21-313).  Terms are accumulated over the ids both vectors hold, in ascending id order, like the reference's
+    // merge (which skips ahead with lower_bound: the visited pairs and their order are the same as a plain two-pointer walk).
+    double score(const DBoW2::BowVector& a, const DBoW2::BowVector& b) const {
+        DBoW2::BowVector::const_iterator ia = a.begin(), ib = b.begin();
+        double acc = 0;
+        const bool kl = m_scoring == DBoW2::KL;
+        static const double kLogEps = std::log(DBL_EPSILON);   // GeneralScoring::LOG_EPS = log(DBL_EPSILON)
+        while (ia != a.end() && ib != b.end()) {
+            if (ia->first == ib->first) {
+                const double vi = ia->second, wi = ib->second;
+                switch (m_scoring) {
+                    case DBoW2::L1_NORM: acc += std::fabs(vi - wi) - std::fabs(vi) - std::fabs(wi); break;
+                    case DBoW2::L2_NORM: case DBoW2::DOT_PRODUCT: acc += vi * wi; break;
+                    case DBoW2::CHI_SQUARE: if (vi + wi != 0.0) acc += vi * wi / (vi + wi); break;
+                    case DBoW2::KL: if (vi != 0 && wi != 0) acc += vi * std::log(vi / wi); break;
+                    case DBoW2::BHATTACHARYYA: acc += std::sqrt(vi * wi); break;
+                }
+                ++ia; ++ib;
+            } else if (ia->first < ib->first) {
+                if (kl) acc += ia->second * (std::log(ia->second) - kLogEps);   // a word only the first vector holds (:170-174)
+                ++ia;
+            } else {
+                ++ib;
+            }
+        }
+        switch (m_scoring) {
+            case DBoW2::L1_NORM: return -acc / 2.0;
+            case DBoW2::L2_NORM: return acc >= 1 ? 1.0 : 1.0 - std::sqrt(1.0 - acc);
+            case DBoW2::CHI_SQUARE: return 2. * acc;
+            case DBoW2::KL:
+                for (; ia != a.end(); ++ia) if (ia->second != 0) acc += ia->second * (std::log(ia->second) - kLogEps);
+                return acc;
+            default: return acc;
+        }
     }
 
     orb_vocabulary* handle() const { return h_; }

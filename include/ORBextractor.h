@@ -6,9 +6,10 @@
  *
  * Differences a maintainer should know:
  *   - the handle is sized for images up to (maxWidth x maxHeight), default 4096 x 4096 lazily grown;
- *   - mvImagePyramid is filled only when SetKeepPyramidOnHost(true) (Frame::ComputeStereoMatches is
- *     replaced by orb_stereo_match, which reads the device-resident pyramids, so nothing on the
- *     hot path needs the host copy);
+ *   - mvImagePyramid is always valid but lazy: the levels of the last operator() call are brought to the host on the
+ *     first read after that call (one staged copy, orb_get_pyramid), and not at all when nobody reads them
+ *     (Frame::ComputeStereoMatches, its only reader in the reference, is replaced by orb_stereo_match on the
+ *     device-resident pyramids).  SetKeepPyramidOnHost(true) downloads eagerly inside operator() instead;
  *   - ExtractBatch() is an additional entry point for many images per call.
  */
 #ifndef ORBEXTRACTOR_H
@@ -39,7 +40,7 @@ public:
         mnFeaturesPerLevel.resize(nlevels); umax.resize(16);
         Check(orb_extractor_tables(mHandle, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(), mvInvLevelSigma2.data(),
                                    mnFeaturesPerLevel.data(), umax.data()));
-        mvImagePyramid.resize(nlevels);
+        mvImagePyramid.Bind(this);
     }
     ~ORBextractor() { if (mHandle) orb_extractor_destroy(mHandle); }
     ORBextractor(const ORBextractor&) = delete;
@@ -65,6 +66,7 @@ public:
             cv::Mat d = _descriptors.getMat();
             for (int i = 0; i < n; ++i) std::memcpy(d.ptr<unsigned char>(i), &mDesc[(size_t)i * 32], 32);
         }
+        mvImagePyramid.Invalidate();
         if (mKeepPyramid) DownloadPyramid(0);
     }
 
@@ -101,8 +103,30 @@ public:
     std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
 
     // Levels of the last operator() call, without the 19-pixel border the reference keeps around them
-    // (src/ORBextractor.cc:1181-1203: mvImagePyramid[l] is the ROI inside the bordered buffer).
-    std::vector<cv::Mat> mvImagePyramid;
+    // (src/ORBextractor.cc:1181-1203: mvImagePyramid[l] is the ROI inside the bordered buffer).  Reads like the reference's
+    // std::vector<cv::Mat> (operator[], size(), iteration, conversion); the host copy is made on the first read after a call.
+    class Pyramid {
+    public:
+        Pyramid() : mOwner(nullptr), mStale(false) {}
+        cv::Mat& operator[](size_t l) { Fetch(); return mLevels[l]; }
+        cv::Mat& at(size_t l) { Fetch(); return mLevels.at(l); }
+        size_t size() const { return mLevels.size(); }
+        bool empty() const { return mLevels.empty(); }
+        std::vector<cv::Mat>::iterator begin() { Fetch(); return mLevels.begin(); }
+        std::vector<cv::Mat>::iterator end() { Fetch(); return mLevels.end(); }
+        operator const std::vector<cv::Mat>&() { Fetch(); return mLevels; }
+        void resize(size_t n) { mLevels.resize(n); }
+        bool OnHost() const { return !mStale; }
+    private:
+        friend class ORBextractor;
+        void Bind(ORBextractor* owner) { mOwner = owner; mLevels.resize(owner->nlevels); }
+        void Invalidate() { mStale = true; }
+        void Fetch() { if (mStale && mOwner) { mStale = false; mOwner->DownloadPyramid(0); } }
+        ORBextractor* mOwner;
+        bool mStale;
+        std::vector<cv::Mat> mLevels;
+    };
+    Pyramid mvImagePyramid;
 
     // ---- additions
     void SetKeepPyramidOnHost(bool on) { mKeepPyramid = on; }
@@ -116,16 +140,18 @@ public:
         Recreate();
     }
     void DownloadPyramid(int image) {
-        mvImagePyramid.resize(nlevels);
+        std::vector<cv::Mat>& lv = mvImagePyramid.mLevels;
+        lv.resize(nlevels);
+        std::vector<unsigned char*> dst(nlevels);
+        std::vector<int32_t> stride(nlevels);
         for (int l = 0; l < nlevels; ++l) {
-            cv::Mat& m = mvImagePyramid[l];
-            m.create(mMaxH, mMaxW, CV_8U);
-            int w = 0, h = 0;
-            Check(orb_get_level(mHandle, image, l, 0, 0, m.data, (int)m.step, (int)(m.step * m.rows), &w, &h));
-            cv::Mat t(h, w, CV_8U);
-            for (int y = 0; y < h; ++y) std::memcpy(t.ptr<unsigned char>(y), m.ptr<unsigned char>(y), w);
-            m = t;
+            int32_t w = 0, h = 0;
+            Check(orb_level_size(mHandle, l, &w, &h));
+            lv[l].create(h, w, CV_8U);
+            dst[l] = lv[l].data; stride[l] = (int32_t)lv[l].step;
         }
+        Check(orb_get_pyramid(mHandle, image, dst.data(), stride.data()));
+        mvImagePyramid.mStale = false;
     }
     orb_extractor* Handle() { return mHandle; }  // for orb_stereo_match / orb_stereo_frames
 

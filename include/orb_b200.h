@@ -101,6 +101,11 @@ int orb_extractor_stage_ms(orb_extractor* e, float* ms);
  * descriptors were sampled from instead.  *w, *h receive the unbordered level size. */
 int orb_get_level(orb_extractor* e, int image, int level, int blurred, int border, uint8_t* dst, int dst_stride,
                   int dst_cap_bytes, int* w, int* h);
+/* All levels of image `image` of the last call in one call (the whole mvImagePyramid, unbordered): level l lands in dst[l] with
+ * row stride dst_stride[l] >= its width.  One staged device-to-host pass and one synchronisation instead of one per level. */
+int orb_get_pyramid(orb_extractor* e, int image, uint8_t* const* dst, const int32_t* dst_stride);
+/* Size of pyramid level `level` for the geometry of the last call. */
+int orb_level_size(const orb_extractor* e, int level, int32_t* w, int32_t* h);
 /* Stage outputs of the last call, for stage-level parity tests: FAST candidates fed to the
  * quadtree (x, y, score triples, window-relative, reference order) and the per-level keypoints
  * chosen by the quadtree, level coordinates (x, y, score). */

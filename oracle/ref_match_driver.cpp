@@ -11,6 +11,13 @@
 // members (MapPoint::mDescriptor, Frame::AssignFeaturesToGrid ...) are reached by compiling THIS
 // translation unit with the access keywords opened; the reference's translation units are untouched.
 //   ref_match_driver <mode> <in> <out>
+//
+// -DORB_B200_DROPIN (oracle/Makefile target `dropin`, binary _ref/dropin_real_driver): the SAME driver over the SAME real
+// Frame / KeyFrame / MapPoint / Map / KeyFrameDatabase translation units, but with this repo's include/ORBextractor.h,
+// include/ORBmatcher.h and include/ORBVocabulary.h in place of the reference's headers and liborb_b200.so in place of
+// ORBextractor.cc / ORBmatcher.cc / DBoW2's vocabulary (Frame.cc / MapPoint.cc with patches/*.patch).  Needs a GPU; its output files
+// must equal this driver's byte for byte (tests/test_gpu_dropin_real.py).
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -39,10 +46,12 @@
 
 using namespace ORB_SLAM2;
 
-// oracle/ref_wrap.cpp: the reference extractor under the monotonic heap (canonical quadtree tie-break)
 struct ref_keypoint { float x, y, size, angle, response; int32_t octave; };
+#ifndef ORB_B200_DROPIN
+// oracle/ref_wrap.cpp: the reference extractor under the monotonic heap (canonical quadtree tie-break)
 extern "C" void* ref_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th);
 extern "C" int ref_extract(void* e, const uint8_t* img, int w, int h, int stride, ref_keypoint* kps, uint8_t* desc, int cap);
+#endif
 
 static Map g_map;
 static ORBVocabulary g_voc;
@@ -132,11 +141,16 @@ static KeyFrame* MakeAngleKeyFrame(const Frame& like, int M, const float* angle)
 static void PutMatch(BlobWriter& w, int n, const std::vector<int>& match) { w.put("n", "i4", &n, 1); w.put("match", "i4", match.data(), match.size()); }
 
 static int RunStereo(const Blob& b, BlobWriter& w);
+#ifdef ORB_B200_DROPIN
+static int RunStereoCtor(const Blob& b, BlobWriter& w);
+static int RunDistanceCost(const Blob& b, BlobWriter& w);
+#endif
 static int RunGrid(const Blob& b, BlobWriter& w);
 static int RunAlgebra(const Blob& b, BlobWriter& w);
 static int RunFrustum(const Blob& b, BlobWriter& w);
 static int RunDistinctive(const Blob& b, BlobWriter& w);
 static int RunBowTransform(const Blob& b, BlobWriter& w, const char* vocfile);
+static int RunBowScore(const Blob& b, BlobWriter& w, const char* vocfile);
 
 int main(int argc, char** argv) {
     if (argc < 4) { fprintf(stderr, "usage: ref_match_driver <mode> <in> <out>\n"); return 2; }
@@ -146,11 +160,16 @@ int main(int argc, char** argv) {
         BlobWriter w(argv[3]);
         g_db = new KeyFrameDatabase(g_voc);
         if (mode == "stereo") return RunStereo(b, w);
+#ifdef ORB_B200_DROPIN
+        if (mode == "stereo_ctor") return RunStereoCtor(b, w);
+        if (mode == "dd_cost") return RunDistanceCost(b, w);
+#endif
         if (mode == "grid") return RunGrid(b, w);
         if (mode == "algebra") return RunAlgebra(b, w);
         if (mode == "frustum") return RunFrustum(b, w);
         if (mode == "distinctive") return RunDistinctive(b, w);
         if (mode == "bowtransform") return RunBowTransform(b, w, argc > 4 ? argv[4] : "");
+        if (mode == "bowscore") return RunBowScore(b, w, argc > 4 ? argv[4] : "");
         if (mode == "mappoints") {
             Frame F; LoadFrame(b, "f_", F);
             KeyFrame* ref = new KeyFrame(F, &g_map, g_db);
@@ -345,6 +364,7 @@ static int RunStereo(const Blob& b, BlobWriter& w) {
     const int* p = b.get<int>("params");  // w, h, nfeatures, nlevels, iniTh, minTh
     const float sf = b.get<float>("scale")[0];
     const float mbf = b.get<float>("stereo")[0], fx = b.get<float>("stereo")[1];
+#ifndef ORB_B200_DROPIN
     ORBextractor* eL = (ORBextractor*)ref_extractor_create(p[2], sf, p[3], p[4], p[5]);
     ORBextractor* eR = (ORBextractor*)ref_extractor_create(p[2], sf, p[3], p[4], p[5]);
     const int cap = p[2] * 4 + 1024;
@@ -352,6 +372,18 @@ static int RunStereo(const Blob& b, BlobWriter& w) {
     const int nl = ref_extract(eL, b.get<unsigned char>("left"), p[0], p[1], p[0], kl.data(), dl.data(), cap);
     const int nr = ref_extract(eR, b.get<unsigned char>("right"), p[0], p[1], p[0], kr.data(), dr.data(), cap);
     if (nl < 0 || nr < 0) throw std::runtime_error("keypoint capacity");
+#else
+    // the drop-in class, called the way Frame::ExtractORB calls it (src/Frame.cc:249-258): (*mpORBextractorLeft)(im, cv::Mat(), mvKeys, mDescriptors)
+    ORBextractor* eL = new ORBextractor(p[2], sf, p[3], p[4], p[5]);
+    ORBextractor* eR = new ORBextractor(p[2], sf, p[3], p[4], p[5]);
+    cv::Mat imL(p[1], p[0], CV_8U, (void*)b.get<unsigned char>("left")), imR(p[1], p[0], CV_8U, (void*)b.get<unsigned char>("right"));
+    std::vector<cv::KeyPoint> vkl, vkr; cv::Mat mdl, mdr;
+    (*eL)(imL, cv::Mat(), vkl, mdl); (*eR)(imR, cv::Mat(), vkr, mdr);
+    const int nl = (int)vkl.size(), nr = (int)vkr.size();
+    std::vector<ref_keypoint> kl(nl > 0 ? nl : 1), kr(nr > 0 ? nr : 1); std::vector<uint8_t> dl((size_t)(nl > 0 ? nl : 1) * 32), dr((size_t)(nr > 0 ? nr : 1) * 32);
+    for (int i = 0; i < nl; ++i) { const cv::KeyPoint& k = vkl[i]; const ref_keypoint q = {k.pt.x, k.pt.y, k.size, k.angle, k.response, k.octave}; kl[i] = q; std::memcpy(&dl[(size_t)i * 32], mdl.ptr(i), 32); }
+    for (int i = 0; i < nr; ++i) { const cv::KeyPoint& k = vkr[i]; const ref_keypoint q = {k.pt.x, k.pt.y, k.size, k.angle, k.response, k.octave}; kr[i] = q; std::memcpy(&dr[(size_t)i * 32], mdr.ptr(i), 32); }
+#endif
     Frame F;
     F.mpORBextractorLeft = eL; F.mpORBextractorRight = eR;
     F.mnScaleLevels = eL->GetLevels(); F.mfScaleFactor = eL->GetScaleFactor(); F.mfLogScaleFactor = std::log(F.mfScaleFactor);
@@ -374,6 +406,69 @@ static int RunStereo(const Blob& b, BlobWriter& w) {
     w.put("max_d", "f4", &maxd, 1);
     return 0;
 }
+
+
+#ifdef ORB_B200_DROPIN
+// The reference's stereo Frame CONSTRUCTOR itself (src/Frame.cc:60-126) over the drop-in extractors: two ExtractORB threads,
+// UndistortKeyPoints, the patched ComputeStereoMatches, image bounds, grid.  Frame::mb is read by ComputeStereoMatches (:529) before
+// the constructor assigns it (:117), i.e. upstream reads whatever the storage held; the storage is pre-set to mbf / fx here so that
+// the run is defined.  Same output names as the "stereo" mode.
+static int RunStereoCtor(const Blob& b, BlobWriter& w) {
+    const int* p = b.get<int>("params");
+    const float sf = b.get<float>("scale")[0];
+    const float mbf = b.get<float>("stereo")[0], fx = b.get<float>("stereo")[1];
+    ORBextractor eL(p[2], sf, p[3], p[4], p[5]), eR(p[2], sf, p[3], p[4], p[5]);
+    cv::Mat imL(p[1], p[0], CV_8U, (void*)b.get<unsigned char>("left")), imR(p[1], p[0], CV_8U, (void*)b.get<unsigned char>("right"));
+    cv::Mat K = cv::Mat::eye(3, 3, CV_32F);
+    K.at<float>(0, 0) = fx; K.at<float>(1, 1) = fx; K.at<float>(0, 2) = p[0] * 0.5f; K.at<float>(1, 2) = p[1] * 0.5f;
+    cv::Mat dist = cv::Mat::zeros(4, 1, CV_32F);
+    Frame::mbInitialComputations = true;
+    void* raw = ::operator new(sizeof(Frame));
+    std::memset(raw, 0, sizeof(Frame));
+    {   // pre-set the one member the constructor reads before writing
+        const size_t off = (size_t)((char*)&((Frame*)raw)->mb - (char*)raw);
+        const float mb0 = mbf / fx;
+        std::memcpy((char*)raw + off, &mb0, sizeof(float));
+    }
+    Frame* F = new (raw) Frame(imL, imR, 0.0, &eL, &eR, &g_voc, K, dist, mbf, 35.f * mbf / fx);
+    const int nl = F->N, nr = (int)F->mvKeysRight.size();
+    std::vector<ref_keypoint> kl(nl > 0 ? nl : 1), kr(nr > 0 ? nr : 1);
+    for (int i = 0; i < nl; ++i) { const cv::KeyPoint& k = F->mvKeys[i]; const ref_keypoint q = {k.pt.x, k.pt.y, k.size, k.angle, k.response, k.octave}; kl[i] = q; }
+    for (int i = 0; i < nr; ++i) { const cv::KeyPoint& k = F->mvKeysRight[i]; const ref_keypoint q = {k.pt.x, k.pt.y, k.size, k.angle, k.response, k.octave}; kr[i] = q; }
+    const float maxd = F->mbf / F->mb;
+    w.put("kl", "u1", kl.data(), (size_t)nl * sizeof(ref_keypoint)); w.put("dl", "u1", F->mDescriptors.data, (size_t)nl * 32);
+    w.put("kr", "u1", kr.data(), (size_t)nr * sizeof(ref_keypoint)); w.put("dr", "u1", F->mDescriptorsRight.data, (size_t)nr * 32);
+    w.put("u_right", "f4", F->mvuRight.data(), F->mvuRight.size()); w.put("depth", "f4", F->mvDepth.data(), F->mvDepth.size());
+    w.put("max_d", "f4", &maxd, 1);
+    // the lazily fetched host pyramid of the drop-in (mvImagePyramid[l]): level sizes and a checksum per level
+    std::vector<int> lv;
+    for (int l = 0; l < eL.GetLevels(); ++l) {
+        const cv::Mat& m = eL.mvImagePyramid[l];
+        unsigned sum = 0;
+        for (int y = 0; y < m.rows; ++y) for (int x = 0; x < m.cols; ++x) sum = sum * 31u + m.ptr(y)[x];
+        lv.push_back(m.cols); lv.push_back(m.rows); lv.push_back((int)sum);
+    }
+    w.put("pyr", "i4", lv.data(), lv.size());
+    return 0;
+}
+
+// Cost of ORBmatcher::DescriptorDistance called per pair (upload + launch + synchronise each) against one DescriptorDistances call.
+static int RunDistanceCost(const Blob& b, BlobWriter& w) {
+    const int n = (int)b.count("a") / 32;
+    cv::Mat A(n, 32, CV_8U), B(n, 32, CV_8U);
+    std::memcpy(A.data, b.get<unsigned char>("a"), (size_t)n * 32); std::memcpy(B.data, b.get<unsigned char>("b"), (size_t)n * 32);
+    std::vector<int> one(n), batch;
+    ORBmatcher::DescriptorDistance(A.row(0), B.row(0));   // creates the thread's workspace
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < n; ++i) one[i] = ORBmatcher::DescriptorDistance(A.row(i), B.row(i));
+    const auto t1 = std::chrono::steady_clock::now();
+    ORBmatcher::DescriptorDistances(A, B, batch);
+    const auto t2 = std::chrono::steady_clock::now();
+    const float us[2] = {(float)(std::chrono::duration<double, std::micro>(t1 - t0).count() / n), (float)std::chrono::duration<double, std::micro>(t2 - t1).count()};
+    w.put("one", "i4", one.data(), one.size()); w.put("batch", "i4", batch.data(), batch.size()); w.put("us", "f4", us, 2);
+    return 0;
+}
+#endif
 
 // Frame::AssignFeaturesToGrid / GetFeaturesInArea and KeyFrame::GetFeaturesInArea on query windows
 static int RunGrid(const Blob& b, BlobWriter& w) {
@@ -448,6 +543,31 @@ static int RunBowTransform(const Blob& b, BlobWriter& w, const char* vocfile) {
     w.put("word", "i4", word.data(), word.size()); w.put("node", "i4", node.data(), node.size()); w.put("weight", "u1", weight.data(), weight.size() * 8);
     const int info[2] = {(int)voc.size(), (int)voc.getDepthLevels()};
     w.put("info", "i4", info, 2);
+    return 0;
+}
+
+// ORBVocabulary::score(BowVector, BowVector) as KeyFrameDatabase::DetectLoopCandidates / DetectRelocalizationCandidates call it
+// (src/KeyFrameDatabase.cc:137,267): two descriptor sets transformed by the vocabulary, scored both ways and against themselves.
+static int RunBowScore(const Blob& b, BlobWriter& w, const char* vocfile) {
+    ORBVocabulary voc;
+    if (!voc.loadFromTextFile(vocfile)) throw std::runtime_error("vocabulary load failed");
+    DBoW2::BowVector bv[2]; DBoW2::FeatureVector fv[2];
+    const char* names[2] = {"desc_a", "desc_b"};
+    for (int s = 0; s < 2; ++s) {
+        const int n = (int)b.count(names[s]) / 32;
+        cv::Mat d(n, 32, CV_8U);
+        std::memcpy(d.data, b.get<unsigned char>(names[s]), (size_t)n * 32);
+        std::vector<cv::Mat> rows;
+        for (int j = 0; j < n; ++j) rows.push_back(d.row(j));
+        voc.transform(rows, bv[s], fv[s], 4);
+    }
+    const double sc[4] = {voc.score(bv[0], bv[1]), voc.score(bv[1], bv[0]), voc.score(bv[0], bv[0]), voc.score(bv[1], bv[1])};
+    w.put("scores", "u1", sc, sizeof(sc));
+    for (int s = 0; s < 2; ++s) {
+        std::vector<unsigned> ids; std::vector<double> vals;
+        for (DBoW2::BowVector::const_iterator it = bv[s].begin(); it != bv[s].end(); ++it) { ids.push_back(it->first); vals.push_back(it->second); }
+        w.put(s ? "ids_b" : "ids_a", "u4", ids.data(), ids.size()); w.put(s ? "vals_b" : "vals_a", "u1", vals.data(), vals.size() * 8);
+    }
     return 0;
 }
 

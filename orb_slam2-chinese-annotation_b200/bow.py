@@ -77,10 +77,42 @@ class ORBVocabulary:
         capi.check(capi.lib().orb_bow_transform(self.h, capi.ptr(desc), n, int(levelsup), capi.ptr(word), capi.ptr(node)))
         return word[:n], node[:n]
 
+    def score(self, a, b):
+        """score(BowVector, BowVector) under the vocabulary's scoring type; a, b = (ids, values) as transform() returns them."""
+        return score(a[0], a[1], b[0], b[1], self.scoring)
+
     def transform(self, desc, levelsup=4):
         """transform(features, BowVector&, FeatureVector&, levelsup): returns (word ids ascending, values float64, FeatureVector)."""
         word, node = self.descend(desc, levelsup)
         return assemble(word, node, self.word_weight, self.weighting, self.scoring)
+
+
+def score(ids_a, vals_a, ids_b, vals_b, scoring=L1_NORM):
+    """ORBVocabulary::score(BowVector, BowVector) (src/KeyFrameDatabase.cc:137,267, src/LoopClosing.cc:145 ->
+    Thirdparty/DBoW2/DBoW2/ScoringObject.cpp:21-313): host-side merge of two id-sorted sparse vectors, like the C++ drop-in
+    (include/ORBVocabulary.h); terms are summed in ascending id order."""
+    import math
+    log_eps = math.log(np.finfo(np.float64).eps)
+    term = {L1_NORM: lambda v, w: abs(v - w) - abs(v) - abs(w),
+            L2_NORM: lambda v, w: v * w, DOT_PRODUCT: lambda v, w: v * w,
+            CHI_SQUARE: lambda v, w: v * w / (v + w) if v + w != 0.0 else 0.0,
+            KL: lambda v, w: v * math.log(v / w) if v != 0 and w != 0 else 0.0,
+            BHATTACHARYYA: lambda v, w: math.sqrt(v * w)}[scoring]
+    a = list(zip((int(k) for k in ids_a), (float(v) for v in vals_a))); b = list(zip((int(k) for k in ids_b), (float(v) for v in vals_b)))
+    i = j = 0
+    acc = 0.0
+    while i < len(a) and j < len(b):
+        if a[i][0] == b[j][0]:
+            acc += term(a[i][1], b[j][1]); i += 1; j += 1
+        elif a[i][0] < b[j][0]:
+            if scoring == KL: acc += a[i][1] * (math.log(a[i][1]) - log_eps)   # a word only the first vector holds
+            i += 1
+        else:
+            j += 1
+    if scoring == KL:
+        for k, v in a[i:]:
+            if v != 0: acc += v * (math.log(v) - log_eps)
+    return {L1_NORM: -acc / 2.0, L2_NORM: 1.0 if acc >= 1 else 1.0 - math.sqrt(max(1.0 - acc, 0.0)), CHI_SQUARE: 2.0 * acc}.get(scoring, acc)
 
 
 def assemble(word, node, word_weight, weighting=TF_IDF, scoring=L1_NORM):

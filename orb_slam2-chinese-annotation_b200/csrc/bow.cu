@@ -13,6 +13,7 @@
 // node, d_orig maps back to the caller's node ids, d_word holds the word id of leaves (-1 otherwise).
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 #include "orb_internal.h"
 
 struct orb_vocabulary {
@@ -26,6 +27,10 @@ struct orb_vocabulary {
     uint8_t* d_q = nullptr;       // [max_features][32] staging for host descriptors
     int* d_out = nullptr;         // [2][max_features] word id, node id
     long long launches = 0;
+    // orb_bow_transform stages through d_q / d_out on the one stream: calls on one handle are serialised here, because the
+    // reference transforms on one shared vocabulary from two threads (Frame::ComputeBoW on Tracking, KeyFrame::ComputeBoW on
+    // LocalMapping).  The tree itself is read-only; orb_bow_transform_device leaves ordering to the caller's streams.
+    std::mutex host_call;
 };
 
 namespace {
@@ -166,6 +171,7 @@ int orb_bow_transform(orb_vocabulary* v, const uint8_t* desc, int n, int levelsu
     if (!v || n < 0 || (n > 0 && (!desc || !word_id || !node_id))) return ORB_ERR_BAD_ARG;
     if (n > v->max_features) { orb_set_error("more descriptors than the vocabulary handle was created for"); return ORB_ERR_CAPACITY; }
     if (n == 0) return ORB_OK;
+    std::lock_guard<std::mutex> serialise(v->host_call);
     ORB_CUDA(cudaSetDevice(v->device));
     ORB_CUDA(cudaMemcpyAsync(v->d_q, desc, (size_t)n * 32, cudaMemcpyHostToDevice, v->stream));
     const int st = orb_bow_transform_device(v, v->d_q, n, levelsup, v->d_out, v->d_out + v->max_features);

@@ -222,6 +222,7 @@ void free_buffers(orb_extractor* e) {
     if (e->h_pin) cudaFreeHost(e->h_pin);
     if (e->h_counts) cudaFreeHost(e->h_counts);
     if (e->h_status) cudaFreeHost(e->h_status);
+    if (e->h_pyr) cudaFreeHost(e->h_pyr);
     for (int i = 0; i < 2; ++i) if (e->ev_call[i]) cudaEventDestroy(e->ev_call[i]);
     for (cudaEvent_t ev : e->ev_pool) cudaEventDestroy(ev);
     if (e->s_h2d) cudaStreamDestroy(e->s_h2d);
@@ -647,6 +648,42 @@ int orb_get_level(orb_extractor* e, int image, int level, int blurred, int borde
                 D[border + G.w + x] = S[border + refl(G.w + x, G.w)];
             }
         }
+    }
+    return ORB_OK;
+}
+
+int orb_level_size(const orb_extractor* e, int level, int32_t* w, int32_t* h) {
+    if (!e || !w || !h || e->plan_w < 0 || level < 0 || level >= e->nlevels) return ORB_ERR_BAD_ARG;
+    *w = e->plan.lv[level].w; *h = e->plan.lv[level].h;
+    return ORB_OK;
+}
+
+int orb_get_pyramid(orb_extractor* e, int image, uint8_t* const* dst, const int32_t* dst_stride) {
+    if (!e || !dst || !dst_stride || e->plan_w < 0 || image < 0 || image >= e->last_batch) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(e->device));
+    size_t need = 0;
+    for (int l = 0; l < e->nlevels; ++l) {
+        if (!dst[l] || dst_stride[l] < e->plan.lv[l].w) return ORB_ERR_BAD_ARG;
+        need += (size_t)e->plan.lv[l].w * e->plan.lv[l].h;
+    }
+    if (need > e->h_pyr_cap) {
+        if (e->h_pyr) { cudaFreeHost(e->h_pyr); e->h_pyr = nullptr; e->h_pyr_cap = 0; }
+        ORB_CUDA(cudaMallocHost((void**)&e->h_pyr, need));
+        e->h_pyr_cap = need;
+    }
+    size_t off = 0;
+    for (int l = 0; l < e->nlevels; ++l) {   // dense rows into pinned memory: the copies queue back to back
+        const LevelGeom& G = e->plan.lv[l];
+        ORB_CUDA(cudaMemcpy2DAsync(e->h_pyr + off, G.w, e->d_pyr + G.off + (size_t)image * G.img_stride, G.pitch, G.w, G.h, cudaMemcpyDeviceToHost, e->stream));
+        off += (size_t)G.w * G.h;
+    }
+    ORB_CUDA(cudaStreamSynchronize(e->stream));
+    off = 0;
+    for (int l = 0; l < e->nlevels; ++l) {
+        const LevelGeom& G = e->plan.lv[l];
+        if (dst_stride[l] == G.w) std::memcpy(dst[l], e->h_pyr + off, (size_t)G.w * G.h);
+        else for (int y = 0; y < G.h; ++y) std::memcpy(dst[l] + (size_t)y * dst_stride[l], e->h_pyr + off + (size_t)y * G.w, G.w);
+        off += (size_t)G.w * G.h;
     }
     return ORB_OK;
 }

@@ -137,6 +137,8 @@ struct orb_extractor {
     uint8_t* h_pin = nullptr;
     size_t h_pin_cap = 0;
     int* h_counts = nullptr;        // pinned [2][max_batch]: one half per in-flight stereo batch (ticket parity)
+    uint8_t* h_pyr = nullptr;       // pinned staging of one image's levels (orb_get_pyramid), h_pyr_cap bytes
+    size_t h_pyr_cap = 0;
     int* h_status = nullptr;        // pinned [4]: device status words (left, right) per ticket parity
     // asynchronous stereo batches (orb_stereo_frames_enqueue / _wait); state lives in the LEFT handle
     int inflight = 0, next_ticket = 0, pipe_chunks = 0;

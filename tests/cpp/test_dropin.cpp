@@ -8,6 +8,7 @@
 #include <map>
 #include <set>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "ORBextractor.h"
@@ -133,8 +134,7 @@ int main(int argc, char** argv) {
             const int* p = b.get<int>("params");  // w, h, nfeatures, nlevels, iniTh, minTh
             const float sf = b.get<float>("scale")[0];
             cv::Mat img(p[1], p[0], CV_8UC1, const_cast<unsigned char*>(b.get<unsigned char>("image")));
-            ORB_SLAM2::ORBextractor ext(p[2], sf, p[3], p[4], p[5]);
-            ext.SetKeepPyramidOnHost(true);
+            ORB_SLAM2::ORBextractor ext(p[2], sf, p[3], p[4], p[5]);   // mvImagePyramid: lazy by default, fetched by the read below
             std::vector<cv::KeyPoint> kps; cv::Mat desc;
             ext(img, cv::Mat(), kps, desc);
             // second call on the same instance, as Tracking does frame after frame
@@ -159,6 +159,33 @@ int main(int argc, char** argv) {
             ext(cv::Mat(), cv::Mat(), ke, de);
             int untouched = ke.size() == 7;
             w.put("empty_untouched", "i4", &untouched, 1);
+        } else if (mode == "stereo") {
+            // The stereo Frame constructor as the reference runs it (src/Frame.cc:81-95): ExtractORB left / right on two threads, joined,
+            // then ComputeStereoMatches (= orb_stereo_match on the two handles, patches/Frame_ComputeStereoMatches.patch).  Output names
+            // and layout of oracle/ref_match_driver.cpp's "stereo" mode (the reference's own code on the same input).
+            const int* p = b.get<int>("params");
+            const float sf = b.get<float>("scale")[0];
+            const float mbf = b.get<float>("stereo")[0], fx = b.get<float>("stereo")[1];
+            ORB_SLAM2::ORBextractor eL(p[2], sf, p[3], p[4], p[5]), eR(p[2], sf, p[3], p[4], p[5]);
+            cv::Mat imL(p[1], p[0], CV_8UC1, const_cast<unsigned char*>(b.get<unsigned char>("left")));
+            cv::Mat imR(p[1], p[0], CV_8UC1, const_cast<unsigned char*>(b.get<unsigned char>("right")));
+            std::vector<cv::KeyPoint> kl, kr; cv::Mat dl, dr;
+            std::thread tl([&] { eL(imL, cv::Mat(), kl, dl); });
+            std::thread tr([&] { eR(imR, cv::Mat(), kr, dr); });
+            tl.join(); tr.join();
+            const int N = (int)kl.size();
+            std::vector<float> uR(N > 0 ? N : 1, -1.f), depth(N > 0 ? N : 1, -1.f);
+            const float mb = mbf / fx, maxd = mbf / mb;   // :117, :529-531
+            int32_t n = 0;
+            if (N > 0 && orb_stereo_match(eL.Handle(), eR.Handle(), 0, mbf, 0.f, maxd, uR.data(), depth.data(), N, &n) != ORB_OK) throw std::runtime_error(orb_last_error());
+            struct RefKp { float x, y, size, angle, response; int32_t octave; };
+            std::vector<RefKp> ol(kl.size()), orr(kr.size());
+            for (size_t i = 0; i < kl.size(); ++i) { const RefKp q = {kl[i].pt.x, kl[i].pt.y, kl[i].size, kl[i].angle, kl[i].response, kl[i].octave}; ol[i] = q; }
+            for (size_t i = 0; i < kr.size(); ++i) { const RefKp q = {kr[i].pt.x, kr[i].pt.y, kr[i].size, kr[i].angle, kr[i].response, kr[i].octave}; orr[i] = q; }
+            w.put("kl", "u1", ol.data(), ol.size() * sizeof(RefKp)); w.put("dl", "u1", dl.data, (size_t)dl.rows * 32);
+            w.put("kr", "u1", orr.data(), orr.size() * sizeof(RefKp)); w.put("dr", "u1", dr.data, (size_t)dr.rows * 32);
+            w.put("u_right", "f4", uR.data(), (size_t)N); w.put("depth", "f4", depth.data(), (size_t)N);
+            w.put("max_d", "f4", &maxd, 1);
         } else if (mode == "mappoints") {
             Frame F; LoadFrame(b, "f_", F);
             const int M = (int)b.count("mp_valid");
@@ -352,6 +379,30 @@ int main(int argc, char** argv) {
             w.put("fv_ids", "u4", fv_ids.data(), fv_ids.size()); w.put("fv_start", "i4", fv_start.data(), fv_start.size()); w.put("fv_items", "u4", fv_items.data(), fv_items.size());
             const int info[2] = {(int)voc.size(), voc.getDepthLevels()};
             w.put("info", "i4", info, 2);
+        } else if (mode == "bowscore") {
+            // KeyFrameDatabase::DetectLoopCandidates / DetectRelocalizationCandidates: mpVoc->score(pKF->mBowVec, pKFi->mBowVec) (src/KeyFrameDatabase.cc:137,267)
+            ORB_SLAM2::ORBVocabulary voc;
+            if (argc < 5 || !voc.loadFromTextFile(argv[4])) throw std::runtime_error("vocabulary load failed");
+            const ORB_SLAM2::ORBVocabulary* mpVoc = &voc;
+            DBoW2::BowVector bv[2]; DBoW2::FeatureVector fv[2];
+            const char* names[2] = {"desc_a", "desc_b"};
+            for (int s = 0; s < 2; ++s) {
+                const int n = (int)b.count(names[s]) / 32;
+                cv::Mat d(n, 32, CV_8U);
+                std::memcpy(d.data, b.get<unsigned char>(names[s]), (size_t)n * 32);
+                std::vector<cv::Mat> rows;
+                for (int j = 0; j < n; ++j) rows.push_back(d.row(j));
+                mpVoc->transform(rows, bv[s], fv[s], 4);
+            }
+            const float si = mpVoc->score(bv[0], bv[1]);   // the reference narrows to float at the call site
+            (void)si;
+            const double sc[4] = {mpVoc->score(bv[0], bv[1]), mpVoc->score(bv[1], bv[0]), mpVoc->score(bv[0], bv[0]), mpVoc->score(bv[1], bv[1])};
+            w.put("scores", "u1", sc, sizeof(sc));
+            for (int s = 0; s < 2; ++s) {
+                std::vector<unsigned> ids; std::vector<double> vals;
+                for (DBoW2::BowVector::const_iterator it = bv[s].begin(); it != bv[s].end(); ++it) { ids.push_back(it->first); vals.push_back(it->second); }
+                w.put(s ? "ids_b" : "ids_a", "u4", ids.data(), ids.size()); w.put(s ? "vals_b" : "vals_a", "u1", vals.data(), vals.size() * 8);
+            }
         } else {
             fprintf(stderr, "unknown mode %s\n", mode.c_str());
             return 2;

@@ -385,6 +385,41 @@ def bow_transform(voc, desc, levelsup=4):
     return word[:n], node[:n]
 
 
+def bow_score(ids_a, vals_a, ids_b, vals_b, scoring):
+    """ORACLE (pure Python, small inputs): DBoW2 GeneralScoring::score of two BowVectors, the two-iterator merge of
+    Thirdparty/DBoW2/DBoW2/ScoringObject.cpp:21-313 (L1 :21-59, L2 :64-106, chi-square :111-150, KL :155-200,
+    Bhattacharyya :205-241, dot product :246-282).  scoring: DBoW2::ScoringType 0..5."""
+    import math
+    log_eps = math.log(2.0 ** -52)
+    i = j = 0
+    na, nb = len(ids_a), len(ids_b)
+    s = 0.0
+    while i < na and j < nb:
+        vi, wi = float(vals_a[i]), float(vals_b[j])
+        if ids_a[i] == ids_b[j]:
+            if scoring == 0: s += math.fabs(vi - wi) - math.fabs(vi) - math.fabs(wi)
+            elif scoring in (1, 5): s += vi * wi
+            elif scoring == 2:
+                if vi + wi != 0.0: s += vi * wi / (vi + wi)
+            elif scoring == 3:
+                if vi != 0 and wi != 0: s += vi * math.log(vi / wi)
+            elif scoring == 4: s += math.sqrt(vi * wi)
+            i += 1; j += 1
+        elif ids_a[i] < ids_b[j]:
+            if scoring == 3: s += vi * (math.log(vi) - log_eps)
+            i += 1
+        else:
+            j += 1
+    if scoring == 0: return -s / 2.0
+    if scoring == 1: return 1.0 if s >= 1 else 1.0 - math.sqrt(1.0 - s)
+    if scoring == 2: return 2.0 * s
+    if scoring == 3:
+        while i < na:
+            if vals_a[i] != 0: s += float(vals_a[i]) * (math.log(float(vals_a[i])) - log_eps)
+            i += 1
+    return s
+
+
 def is_in_frustum(Rcw, tcw, Ow, cam, bounds, cos_limit, xw, normal, mind, maxd):
     f32 = lambda a: np.ascontiguousarray(a, np.float32)
     Rcw, tcw, Ow, xw, normal, mind, maxd = f32(Rcw).reshape(9), f32(tcw).reshape(3), f32(Ow).reshape(3), f32(xw).reshape(-1, 3), f32(normal).reshape(-1, 3), f32(mind), f32(maxd)

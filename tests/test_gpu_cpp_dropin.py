@@ -327,6 +327,70 @@ def test_orbvocabulary_transform(dropin, tmp_path, k, L, levelsup, seed):
     assert len(ids) > 100
 
 
+@pytest.mark.parametrize("scoring,weighting,seed", [(0, 0, 0), (1, 0, 1), (2, 1, 2), (3, 0, 3), (4, 2, 4), (5, 0, 5), (0, 3, 6)])
+def test_orbvocabulary_score(dropin, tmp_path, scoring, weighting, seed):
+    """include/ORBVocabulary.h: score(BowVector, BowVector) as KeyFrameDatabase.cc:137,267 / LoopClosing.cc:145 call it, for the six
+    DBoW2 scoring types (ScoringObject.cpp): both orders of two overlapping frames and each frame against itself, doubles bit-equal
+    to the oracle's merge; the two BowVectors equal the oracle's assembly."""
+    bow = importlib.import_module("orb_slam2-chinese-annotation_b200.bow")
+    voc = synth.make_vocabulary(9, 4, seed)
+    voc["scoring"], voc["weighting"] = scoring, weighting
+    vf = str(tmp_path / "voc.txt")
+    synth.write_text_vocabulary(vf, voc)
+    qa = synth.vocabulary_queries(voc, 700, seed); qb = synth.vocabulary_queries(voc, 600, seed + 50)
+    qb[:250] = qa[100:350]     # the two frames share words
+    out = dropin("bowscore", {"desc_a": qa.reshape(-1), "desc_b": qb.reshape(-1)}, tmp_path, vf)
+    leaves = np.nonzero(voc["is_leaf"])[0]
+    vec = []
+    for q in (qa, qb):
+        word, node = orc.bow_transform(voc, q, 4)
+        ids, vals, _ = bow.assemble(word, node, voc["weight"][leaves], weighting, scoring)
+        vec.append((ids, vals))
+    # The L1 family (ORBvoc.txt is L1 / TF-IDF) has no a * b + c in it and is bit-equal everywhere.  The L2 norm of a BowVector and the
+    # L2 / KL / dot-product sums are "acc += a * b": the reference's own build (-O3 -march=native, CMakeLists.txt:10-11) contracts them
+    # into FMAs, a build without FMA does not, so those three are compared to 1e-12 relative and the vector to 1 ulp.
+    exact = scoring in (0, 2, 4)
+    got_vec = [(out["ids_a"], out["vals_a"].view(np.float64)), (out["ids_b"], out["vals_b"].view(np.float64))]
+    for g, v in zip(got_vec, vec):
+        assert np.array_equal(g[0], v[0])
+        if scoring != 1: assert np.array_equal(g[1], v[1])
+        else: assert np.allclose(g[1], v[1], rtol=4e-16, atol=0)
+    assert len(np.intersect1d(vec[0][0], vec[1][0])) > 50 and len(np.setdiff1d(vec[0][0], vec[1][0])) > 50
+    pairs = [(0, 1), (1, 0), (0, 0), (1, 1)]
+    want = np.array([orc.bow_score(*got_vec[i], *got_vec[j], scoring) for i, j in pairs], np.float64)
+    got = out["scores"].view(np.float64)
+    mine = np.array([bow.score(*got_vec[i], *got_vec[j], scoring) for i, j in pairs], np.float64)   # the Python host mirror
+    assert np.array_equal(mine.view(np.uint64), want.view(np.uint64))
+    if exact:
+        assert np.array_equal(got.view(np.uint64), want.view(np.uint64)), (got, want)
+    else:
+        assert np.allclose(got, want, rtol=1e-12, atol=1e-15), (got, want)
+    if scoring == 0:
+        assert 0.0 < got[0] < 1.0 and abs(got[2] - 1.0) < 1e-12
+
+
+REFKP = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4")])
+
+
+@pytest.mark.parametrize("w,h,nf,mbf,fx,seed", [(1241, 376, 2000, 386.1448, 718.856, 0), (752, 480, 1200, 47.90639384423901, 435.2046959714599, 1)])
+def test_stereo_frame_on_two_threads(dropin, tmp_path, w, h, nf, mbf, fx, seed):
+    """The stereo Frame constructor's hot path as the reference runs it (src/Frame.cc:81-95): operator() of the left and right
+    drop-in extractor on two threads, joined, then ComputeStereoMatches = orb_stereo_match on the two handles; against the oracle."""
+    left, right = synth.make_stereo_pair(w, h, seed, fx=fx)
+    out = dropin("stereo", {"params": np.array([w, h, nf, 8, 20, 7], np.int32), "scale": _f32(1.2), "left": np.ascontiguousarray(left).reshape(-1),
+                            "right": np.ascontiguousarray(right).reshape(-1), "stereo": np.array([mbf, fx], np.float32)}, tmp_path)
+    ol = orc.Extractor(nf, 1.2, 8, 20, 7); orr = orc.Extractor(nf, 1.2, 8, 20, 7)
+    okl, odl = ol.extract(left); okr, odr = orr.extract(right)
+    rkl = out["kl"].view(REFKP); rkr = out["kr"].view(REFKP)
+    assert len(rkl) == len(okl) and len(rkr) == len(okr)
+    for f in ("x", "y", "angle", "response", "octave", "size"):
+        assert np.array_equal(rkl[f], okl[f]) and np.array_equal(rkr[f], okr[f]), f
+    assert np.array_equal(out["dl"].reshape(-1, 32), odl) and np.array_equal(out["dr"].reshape(-1, 32), odr)
+    our, odp, _, _ = orc.stereo_match(ol, orr, okl, odl, okr, odr, np.float32(mbf), 0.0, float(out["max_d"][0]))
+    assert np.array_equal(out["u_right"], our) and np.array_equal(out["depth"], odp)
+    assert (our >= 0).sum() > 50
+
+
 def test_soak_dropin_vs_oracle_over_seeds(dropin, tmp_path):
     """Every matcher scenario on 4 further seeds (40 scenarios) through the CUDA drop-in; tests/test_oracle_refmatch.py runs
     the same seeds (and more) through the reference itself."""

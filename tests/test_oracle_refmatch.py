@@ -53,6 +53,7 @@ test_loop_search_by_projection = D.test_loop_search_by_projection
 test_fuse_sim3 = D.test_fuse_sim3
 test_search_by_sim3 = D.test_search_by_sim3
 test_orbvocabulary_transform = D.test_orbvocabulary_transform     # ORBVocabulary::loadFromTextFile + transform: the reference's DBoW2
+test_orbvocabulary_score = D.test_orbvocabulary_score             # ORBVocabulary::score: the reference's ScoringObject.cpp pins the oracle's merge
 
 
 REFKP = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4")])
@@ -228,14 +229,19 @@ def test_is_in_frustum(dropin, tmp_path, idx, cos_limit):
     assert 0.3 < ok.mean() < 0.97
 
 
-@pytest.mark.parametrize("idx", [0, 1])
-def test_compute_distinctive_descriptors(dropin, tmp_path, idx):
-    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:250-326, verbatim) == the oracle on the rows in the
-    order the reference gathered them (std::map<KeyFrame*, size_t>: KeyFrame address order)."""
+def _distinctive_blob(idx):
     kf_desc, start, okf, orow = worldsim.distinctive_scenario(idx)
     f = synth.make_frame_arrays(50, 990)
     F, blob = D._frame_blob("f_", f)
     blob.update({"dims": np.array(kf_desc.shape[:2], np.int32), "kf_desc": kf_desc.reshape(-1), "start": start, "obs_kf": okf, "obs_row": orow})
+    return blob, start
+
+
+@pytest.mark.parametrize("idx", [0, 1])
+def test_compute_distinctive_descriptors(dropin, tmp_path, idx):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:250-326, verbatim) == the oracle on the rows in the
+    order the reference gathered them (std::map<KeyFrame*, size_t>: KeyFrame address order)."""
+    blob, start = _distinctive_blob(idx)
     out = dropin("distinctive", blob, tmp_path)
     gs, gd = out["g_start"], out["g_desc"].reshape(-1, 32)
     assert np.array_equal(np.diff(gs), np.diff(start))

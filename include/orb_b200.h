@@ -117,6 +117,9 @@ int orb_get_level_keypoints(orb_extractor* e, int image, int level, int32_t* xys
  * lies in [first_bits, last_bits] on CUDA device `device` and returns the 64-bit checksum that
  * tests/cpp/sincosf_sweep.c computes with the host libm. */
 int orb_sincosf_sweep_device(uint32_t first_bits, uint32_t last_bits, int device, uint64_t* checksum);
+/* Self-check of the device cv::fastAtan2 used by the orientation stage (IC_Angle, src/ORBextractor.cc:112): out[i] =
+ * fastAtan2(y[i], x[i]) in degrees, evaluated by the same device function the kernel calls.  Host pointers. */
+int orb_fast_atan2_device(const float* y, const float* x, int n, int device, float* out);
 
 /* ------------------------------------------------------------------ stereo */
 /* Frame::ComputeStereoMatches for image `image` of the last batches of the two extractor handles
@@ -466,6 +469,12 @@ int orb_multi_stereo_frames(orb_multi* m, const uint8_t* imgs_l, const uint8_t* 
                             orb_keypoint* kps_r, uint8_t* desc_r, int32_t* n_r, float* u_right, float* depth, int cap);
 int orb_multi_extract_batch(orb_multi* m, const uint8_t* imgs, int batch, int w, int h, int stride, size_t img_stride,
                             orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts);
+
+/* Guard mode (environment ORB_B200_GUARD=1 before the first allocation): every device buffer of the library carries a 4 KB canary
+ * on both sides; this call synchronises the device and reads all canaries back.  *n_buffers = live buffers checked, *n_damaged =
+ * buffers whose canary was overwritten (ORB_ERR_CUDA and a description in orb_last_error() if any).  Without the environment
+ * variable it reports 0 buffers.  Stand-in for compute-sanitizer memcheck where that tool is not available. */
+int orb_debug_guard_check(int32_t* n_buffers, int32_t* n_damaged);
 
 #ifdef __cplusplus
 }

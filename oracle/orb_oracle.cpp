@@ -155,7 +155,9 @@ void divide(const QNode& n, const FastPt* pts, QNode out[4]) {
 }
 
 // DistributeOctTree: returns indices of the kept candidates in the reference's output order.
-std::vector<int> distribute(const FastPt* pts, int n, int minX, int maxX, int minY, int maxY, int N) {
+// stats (optional, test witness): [0] rounds of the sorted phase (:692-757), [1] adjacent equal counts in its sorted lists,
+// [2] early breaks (:745) that fell BETWEEN two nodes of equal count, i.e. where the (count, pointer) tie-break decided the result.
+std::vector<int> distribute(const FastPt* pts, int n, int minX, int maxX, int minY, int maxY, int N, int* stats = nullptr) {
     std::vector<int> result;
     const int nIni = (int)std::round((float)(maxX - minX) / (maxY - minY));
     const float hX = (float)(maxX - minX) / nIni;
@@ -216,12 +218,19 @@ std::vector<int> distribute(const FastPt* pts, int n, int minX, int maxX, int mi
                 std::vector<SizedNode> todo = expandable;
                 expandable.clear();
                 std::sort(todo.begin(), todo.end(), by_size_then_age);
+                if (stats) {
+                    stats[0]++;
+                    for (size_t j = 1; j < todo.size(); ++j) stats[1] += todo[j].first == todo[j - 1].first;
+                }
                 for (int j = (int)todo.size() - 1; j >= 0; --j) {
                     QNode ch[4];
                     divide(*todo[j].second, pts, ch);
                     push_children(ch, expandable, nullptr);
                     nodes.erase(todo[j].second->self);
-                    if ((int)nodes.size() >= N) break;
+                    if ((int)nodes.size() >= N) {
+                        if (stats && j > 0 && todo[j - 1].first == todo[j].first) stats[2]++;
+                        break;
+                    }
                 }
                 if ((int)nodes.size() >= N || (int)nodes.size() == prev2) finish = true;
             }
@@ -387,6 +396,15 @@ int orc_level_keypoints(const orc_extractor* e, int l, orc_keypoint* kps, int ca
     const auto& k = e->lv[l].kps;
     for (size_t i = 0; i < k.size() && (int)i < cap; ++i) kps[i] = k[i];
     return (int)k.size();
+}
+int orc_distribute_stats(const int32_t* xys, int n, int minX, int maxX, int minY, int maxY, int N, int32_t* kept_idx, int cap, int32_t* stats) {
+    std::vector<FastPt> pts(n);
+    for (int i = 0; i < n; ++i) pts[i] = {xys[3 * i], xys[3 * i + 1], xys[3 * i + 2]};
+    int st[3] = {0, 0, 0};
+    std::vector<int> kept = distribute(pts.data(), n, minX, maxX, minY, maxY, N, st);
+    for (size_t i = 0; i < kept.size() && (int)i < cap; ++i) kept_idx[i] = kept[i];
+    for (int k = 0; k < 3; ++k) stats[k] = st[k];
+    return (int)kept.size();
 }
 int orc_distribute(const int32_t* xys, int n, int minX, int maxX, int minY, int maxY, int N, int32_t* kept_idx, int cap) {
     std::vector<FastPt> pts(n);

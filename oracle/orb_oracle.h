@@ -54,6 +54,8 @@ int orc_level_keypoints(const orc_extractor*, int level, orc_keypoint* kps, int 
  * reference output order. */
 int orc_distribute(const int32_t* xys, int n, int min_x, int max_x, int min_y, int max_y, int n_features,
                    int32_t* kept_idx, int cap);
+/* same, plus a witness of the sorted phase: stats[0] rounds, [1] adjacent equal counts in the sorted lists, [2] early breaks between equal counts */
+int orc_distribute_stats(const int32_t* xys, int n, int minX, int maxX, int minY, int maxY, int N, int32_t* kept_idx, int cap, int32_t* stats);
 
 /* ---- matcher (reference src/ORBmatcher.cc) and stereo (src/Frame.cc:516-704); match_oracle.cpp ----
  * The view structs (orb_frame_view, ...) are the plain C types of include/orb_b200.h. */

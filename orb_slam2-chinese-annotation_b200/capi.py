@@ -19,7 +19,7 @@ EXPORTS = [
     "orb_last_error", "orb_device_count", "orb_extractor_create", "orb_extractor_destroy", "orb_extractor_tables",
     "orb_extractor_max_keypoints", "orb_extract", "orb_extract_batch", "orb_extract_device",
     "orb_extractor_device_results", "orb_extractor_download", "orb_extractor_sync", "orb_extractor_stream",
-    "orb_extractor_launch_count", "orb_extractor_set_timing", "orb_extractor_stage_ms", "orb_get_level", "orb_get_pyramid", "orb_level_size", "orb_get_level_candidates", "orb_get_level_keypoints",
+    "orb_extractor_launch_count", "orb_extractor_set_timing", "orb_extractor_stage_ms", "orb_get_level", "orb_get_pyramid", "orb_debug_guard_check", "orb_fast_atan2_device", "orb_level_size", "orb_get_level_candidates", "orb_get_level_keypoints",
     "orb_stereo_match", "orb_stereo_match_batch", "orb_stereo_match_device", "orb_stereo_device_results", "orb_stereo_frames",
     "orb_multi_create", "orb_multi_destroy", "orb_multi_device_count", "orb_multi_max_keypoints", "orb_multi_slice",
     "orb_multi_stereo_frames", "orb_multi_extract_batch",

@@ -115,9 +115,9 @@ int orb_vocabulary_create(int levels, int n_nodes, const int32_t* parent, const 
     orb_vocabulary* v = new orb_vocabulary();
     v->device = device; v->n_nodes = n_nodes; v->n_words = n_words; v->levels = levels; v->max_k = max_k; v->max_features = max_features;
     if (cudaStreamCreateWithFlags(&v->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaMalloc((void**)&v->d_desc, slot_desc.size()) != cudaSuccess || cudaMalloc((void**)&v->d_range, sizeof(int2) * n_nodes) != cudaSuccess ||
-        cudaMalloc((void**)&v->d_orig, 4 * (size_t)n_nodes) != cudaSuccess || cudaMalloc((void**)&v->d_word, 4 * (size_t)n_nodes) != cudaSuccess ||
-        cudaMalloc((void**)&v->d_q, (size_t)max_features * 32) != cudaSuccess || cudaMalloc((void**)&v->d_out, (size_t)max_features * 8) != cudaSuccess ||
+        orb_dev_alloc((void**)&v->d_desc, slot_desc.size()) != cudaSuccess || orb_dev_alloc((void**)&v->d_range, sizeof(int2) * n_nodes) != cudaSuccess ||
+        orb_dev_alloc((void**)&v->d_orig, 4 * (size_t)n_nodes) != cudaSuccess || orb_dev_alloc((void**)&v->d_word, 4 * (size_t)n_nodes) != cudaSuccess ||
+        orb_dev_alloc((void**)&v->d_q, (size_t)max_features * 32) != cudaSuccess || orb_dev_alloc((void**)&v->d_out, (size_t)max_features * 8) != cudaSuccess ||
         cudaMemcpy(v->d_desc, slot_desc.data(), slot_desc.size(), cudaMemcpyHostToDevice) != cudaSuccess ||
         cudaMemcpy(v->d_range, range.data(), sizeof(int2) * n_nodes, cudaMemcpyHostToDevice) != cudaSuccess ||
         cudaMemcpy(v->d_orig, order.data(), 4 * (size_t)n_nodes, cudaMemcpyHostToDevice) != cudaSuccess ||
@@ -134,7 +134,7 @@ void orb_vocabulary_destroy(orb_vocabulary* v) {
     if (!v) return;
     cudaSetDevice(v->device);
     if (v->stream) cudaStreamSynchronize(v->stream);
-    cudaFree(v->d_desc); cudaFree(v->d_range); cudaFree(v->d_orig); cudaFree(v->d_word); cudaFree(v->d_q); cudaFree(v->d_out);
+    orb_dev_free(v->d_desc); orb_dev_free(v->d_range); orb_dev_free(v->d_orig); orb_dev_free(v->d_word); orb_dev_free(v->d_q); orb_dev_free(v->d_out);
     if (v->stream) cudaStreamDestroy(v->stream);
     delete v;
 }
@@ -150,6 +150,7 @@ void* orb_vocabulary_stream(const orb_vocabulary* v) { return v ? (void*)v->stre
 long long orb_vocabulary_launch_count(const orb_vocabulary* v) { return v ? v->launches : 0; }
 
 int orb_bow_transform_device(orb_vocabulary* v, const uint8_t* d_desc, int n, int levelsup, int32_t* d_word_id, int32_t* d_node_id) {
+    ORB_NVTX("orb:bow_transform_device");
     if (!v || n < 0 || (n > 0 && (!d_desc || !d_word_id || !d_node_id))) return ORB_ERR_BAD_ARG;
     if (((uintptr_t)d_desc & 15) != 0) { orb_set_error("descriptors must be 16-byte aligned"); return ORB_ERR_BAD_ARG; }
     if (n == 0) return ORB_OK;
@@ -168,6 +169,7 @@ int orb_bow_transform_device(orb_vocabulary* v, const uint8_t* d_desc, int n, in
 }
 
 int orb_bow_transform(orb_vocabulary* v, const uint8_t* desc, int n, int levelsup, int32_t* word_id, int32_t* node_id) {
+    ORB_NVTX("orb:bow_transform");
     if (!v || n < 0 || (n > 0 && (!desc || !word_id || !node_id))) return ORB_ERR_BAD_ARG;
     if (n > v->max_features) { orb_set_error("more descriptors than the vocabulary handle was created for"); return ORB_ERR_CAPACITY; }
     if (n == 0) return ORB_OK;

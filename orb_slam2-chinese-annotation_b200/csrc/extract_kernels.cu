@@ -625,13 +625,35 @@ extern "C" int orb_sincosf_sweep_device(uint32_t first_bits, uint32_t last_bits,
     if (device < 0 || device >= ndev) return ORB_ERR_BAD_ARG;
     ORB_CUDA(cudaSetDevice(device));
     unsigned long long* d = nullptr;
-    ORB_CUDA(cudaMalloc((void**)&d, 8));
+    ORB_CUDA(orb_dev_alloc((void**)&d, 8));
     ORB_CUDA(cudaMemset(d, 0, 8));
     k_sincosf_sweep<<<148 * 16, 256>>>(first_bits, (unsigned long long)last_bits - first_bits + 1ull, d);
     unsigned long long h = 0;
     cudaError_t e = cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
-    cudaFree(d);
+    orb_dev_free(d);
     if (e != cudaSuccess) { orb_set_error(cudaGetErrorString(e)); return ORB_ERR_CUDA; }
     *checksum = h;
+    return ORB_OK;
+}
+
+// Self-check of the device fastAtan2 used by the orientation stage (include/orb_b200.h: orb_fast_atan2_device).
+__global__ void __launch_bounds__(256) k_fast_atan2(const float* __restrict__ y, const float* __restrict__ x, const int n, float* __restrict__ out) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < n) out[i] = fast_atan2_deg(y[i], x[i]);
+}
+extern "C" int orb_fast_atan2_device(const float* y, const float* x, int n, int device, float* out) {
+    if (!y || !x || !out || n < 0) return ORB_ERR_BAD_ARG;
+    if (n == 0) return ORB_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); orb_set_error("no CUDA device: this library has no CPU fallback"); return ORB_ERR_CUDA; }
+    if (device < 0 || device >= ndev) return ORB_ERR_BAD_ARG;
+    ORB_CUDA(cudaSetDevice(device));
+    float* d = nullptr;
+    ORB_CUDA(orb_dev_alloc((void**)&d, (size_t)n * 12));
+    cudaError_t e = cudaMemcpy(d, y, (size_t)n * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d + n, x, (size_t)n * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) { k_fast_atan2<<<(n + 255) / 256, 256>>>(d, d + n, n, d + 2 * (size_t)n); e = cudaMemcpy(out, d + 2 * (size_t)n, (size_t)n * 4, cudaMemcpyDeviceToHost); }
+    orb_dev_free(d);
+    if (e != cudaSuccess) { orb_set_error(cudaGetErrorString(e)); return ORB_ERR_CUDA; }
     return ORB_OK;
 }

@@ -213,10 +213,10 @@ int build_tma_maps(orb_extractor* e, int batch) {
 }
 
 void free_buffers(orb_extractor* e) {
-    cudaFree(e->d_pyr); cudaFree(e->d_blur); cudaFree(e->d_cell_cnt); cudaFree(e->d_cell_prefix); cudaFree(e->d_stage);
-    cudaFree(e->d_keys); cudaFree(e->d_lvl_kp); cudaFree(e->d_lvl_cnt); cudaFree(e->d_lvl_ncand); cudaFree(e->d_kps);
-    cudaFree(e->d_desc); cudaFree(e->d_counts); cudaFree(e->d_status); cudaFree(e->d_tables); cudaFree(e->d_u_right);
-    cudaFree(e->d_depth); cudaFree(e->d_sad); cudaFree(e->d_in); cudaFree(e->d_row_start); cudaFree(e->d_row_items);
+    orb_dev_free(e->d_pyr); orb_dev_free(e->d_blur); orb_dev_free(e->d_cell_cnt); orb_dev_free(e->d_cell_prefix); orb_dev_free(e->d_stage);
+    orb_dev_free(e->d_keys); orb_dev_free(e->d_lvl_kp); orb_dev_free(e->d_lvl_cnt); orb_dev_free(e->d_lvl_ncand); orb_dev_free(e->d_kps);
+    orb_dev_free(e->d_desc); orb_dev_free(e->d_counts); orb_dev_free(e->d_status); orb_dev_free(e->d_tables); orb_dev_free(e->d_u_right);
+    orb_dev_free(e->d_depth); orb_dev_free(e->d_sad); orb_dev_free(e->d_in); orb_dev_free(e->d_row_start); orb_dev_free(e->d_row_items);
     if (e->ev_done) cudaEventDestroy(e->ev_done);
     for (int i = 0; i < ORB_N_STAGES + 4; ++i) if (e->ev_stage[i]) cudaEventDestroy(e->ev_stage[i]);
     if (e->h_pin) cudaFreeHost(e->h_pin);
@@ -296,19 +296,28 @@ int run_pipeline(orb_extractor* e, int b0, int batch) {
     const bool T = e->timing;
     // event i is recorded BEFORE stage i; event 5 after the last extractor stage
     if (T) cudaEventRecord(e->ev_stage[0], s);
+    nvtxRangePushA("orb:pyramid");
     for (int l = 1; l < P.nlevels; ++l) { launch_resize(s, e->d_pyr, &e->tm_resize.lv[l - 1], e->rz_tma[l], Q.lv[l - 1], Q.lv[l], b0, batch); e->launches++; }
+    nvtxRangePop();
     if (T) cudaEventRecord(e->ev_stage[1], s);
     if (P.total_cells > 0) {
+        ORB_NVTX("orb:fast_cells");
         ORB_CUDA(launch_fast(s, e->d_pyr, cell_cnt, stage, P, batch)); e->launches++;
     }
     if (T) cudaEventRecord(e->ev_stage[2], s);
-    ORB_CUDA(launch_quadtree(s, cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, e->d_status, P, batch));
-    e->launches++;
+    {
+        ORB_NVTX("orb:quadtree");
+        ORB_CUDA(launch_quadtree(s, cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, e->d_status, P, batch));
+        e->launches++;
+    }
     if (T) cudaEventRecord(e->ev_stage[3], s);
-    launch_gauss(s, e->tm_blur, e->d_pyr, e->d_blur, Q, b0, batch); e->launches++;
+    { ORB_NVTX("orb:gauss7"); launch_gauss(s, e->tm_blur, e->d_pyr, e->d_blur, Q, b0, batch); e->launches++; }
     if (T) cudaEventRecord(e->ev_stage[4], s);
-    launch_orient_describe(s, e->d_pyr, e->d_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, batch);
-    e->launches++;
+    {
+        ORB_NVTX("orb:orient_describe");
+        launch_orient_describe(s, e->d_pyr, e->d_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, batch);
+        e->launches++;
+    }
     if (T) { cudaEventRecord(e->ev_stage[5], s); for (int i = 0; i < 5; ++i) e->stage_valid[i] = true; }
     ORB_CUDA(cudaGetLastError());
     return ORB_OK;
@@ -337,7 +346,7 @@ int orb_pipe_streams(orb_extractor* e) {
     if (!e->s_h2d) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_h2d, cudaStreamNonBlocking));
     if (!e->s_d2h) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_d2h, cudaStreamNonBlocking));
     if (!e->d_in && e->max_batch > 1 && !getenv("ORB_B200_NO_STAGING"))
-        ORB_CUDA(cudaMalloc((void**)&e->d_in, (size_t)e->max_batch * e->max_w * e->max_h + 16));
+        ORB_CUDA(orb_dev_alloc((void**)&e->d_in, (size_t)e->max_batch * e->max_w * e->max_h + 16));
     return ORB_OK;
 }
 cudaEvent_t orb_pool_event(orb_extractor* e, int i) {
@@ -369,6 +378,7 @@ std::vector<int> orb_chunk_bounds(int batch) {
 }
 // Host images [b0, b0 + n) of a batch -> level 0 of the same slots.
 int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, int stride, size_t img_stride, cudaStream_t st) {
+    ORB_NVTX("orb:upload_ingest");
     const LevelGeom& G0 = e->plan.lv[0];
     uint8_t* dst = e->d_pyr + G0.off + (size_t)b0 * G0.img_stride;
     const uint8_t* src = imgs + (size_t)b0 * img_stride;
@@ -440,7 +450,7 @@ int orb_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini
     e->kp_cap_max = need.kp_cap + 64;
     e->tables_cap = need.tables_bytes + 4096;
     const size_t B = (size_t)max_batch;
-#define ALLOC(ptr, bytes) do { cudaError_t er = cudaMalloc((void**)&(ptr), (bytes)); if (er != cudaSuccess) { \
+#define ALLOC(ptr, bytes) do { cudaError_t er = orb_dev_alloc((void**)&(ptr), (bytes)); if (er != cudaSuccess) { \
         orb_set_error(std::string("cudaMalloc: ") + cudaGetErrorString(er)); free_buffers(e); delete e; return ORB_ERR_CUDA; } } while (0)
     if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) { delete e; orb_set_error("stream"); return ORB_ERR_CUDA; }
     ALLOC(e->d_pyr, e->pyr_cap * B);

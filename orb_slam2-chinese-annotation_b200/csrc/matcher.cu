@@ -932,8 +932,8 @@ int ensure_cands(orb_matcher* m, size_t total) {
     if (total <= m->cands_cap) return ORB_OK;
     const size_t want = total + total / 4 + 4096;
     uint32_t* p = nullptr;
-    if (cudaMalloc((void**)&p, want * 4) != cudaSuccess) { cudaGetLastError(); orb_set_error("candidate workspace: out of device memory"); return ORB_ERR_CAPACITY; }
-    cudaFree(m->d_cands);
+    if (orb_dev_alloc((void**)&p, want * 4) != cudaSuccess) { cudaGetLastError(); orb_set_error("candidate workspace: out of device memory"); return ORB_ERR_CAPACITY; }
+    orb_dev_free(m->d_cands);
     m->d_cands = p; m->cands_cap = want;
     return ORB_OK;
 }
@@ -967,8 +967,8 @@ int orb_matcher_create(int max_pairs, int max_n, int device, orb_matcher** out) 
     // brute force: 2 x 32 B + 3 ints.  Candidate lists start at 64 per feature and grow on demand (ensure_cands).
     m->ws_cap = (size_t)max_pairs * max_n * 256 + (size_t)max_pairs * 16 * 1024 + (size_t)max_n * 512 + (8u << 20);
     m->cands_cap = std::max<size_t>((size_t)max_pairs * max_n * 64, 1 << 16);
-    if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc((void**)&m->d_ws, m->ws_cap) != cudaSuccess ||
-        cudaMalloc((void**)&m->d_cands, m->cands_cap * 4) != cudaSuccess || cudaMalloc((void**)&m->d_scal, 64) != cudaSuccess) {
+    if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess || orb_dev_alloc((void**)&m->d_ws, m->ws_cap) != cudaSuccess ||
+        orb_dev_alloc((void**)&m->d_cands, m->cands_cap * 4) != cudaSuccess || orb_dev_alloc((void**)&m->d_scal, 64) != cudaSuccess) {
         orb_set_error(std::string("matcher allocation: ") + cudaGetErrorString(cudaGetLastError()));
         orb_matcher_destroy(m);
         return ORB_ERR_CUDA;
@@ -981,7 +981,7 @@ void orb_matcher_destroy(orb_matcher* m) {
     if (!m) return;
     cudaSetDevice(m->device);
     if (m->stream) cudaStreamSynchronize(m->stream);
-    cudaFree(m->d_ws); cudaFree(m->d_cands); cudaFree(m->d_scal);
+    orb_dev_free(m->d_ws); orb_dev_free(m->d_cands); orb_dev_free(m->d_scal);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
 }
@@ -997,6 +997,7 @@ int orb_matcher_sync(orb_matcher* m) {
 }
 
 int orb_descriptor_distance(orb_matcher* m, const uint8_t* a, const uint8_t* b, int n, int32_t* dist) {
+    ORB_NVTX("orb:descriptor_distance");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!a || !b || !dist || n < 0) return ORB_ERR_BAD_ARG;
@@ -1014,6 +1015,7 @@ int orb_descriptor_distance(orb_matcher* m, const uint8_t* a, const uint8_t* b, 
 
 int orb_match_bruteforce_device(orb_matcher* m, const uint8_t* d_a, const uint8_t* d_b, int pairs, int n_a, int n_b, int32_t* d_best_idx,
                                 int32_t* d_best_dist, int32_t* d_second_dist) {
+    ORB_NVTX("orb:match_bruteforce_device");
     if (!m || !d_a || !d_b || !d_best_idx || !d_best_dist || !d_second_dist || pairs < 1 || n_a < 1 || n_b < 0) return ORB_ERR_BAD_ARG;
     ORB_CUDA(cudaSetDevice(m->device));
     dim3 grid((n_a + BF_THREADS - 1) / BF_THREADS, pairs);
@@ -1025,6 +1027,7 @@ int orb_match_bruteforce_device(orb_matcher* m, const uint8_t* d_a, const uint8_
 
 int orb_match_bruteforce(orb_matcher* m, const uint8_t* a, const uint8_t* b, int pairs, int n_a, int n_b, int32_t* best_idx,
                          int32_t* best_dist, int32_t* second_dist) {
+    ORB_NVTX("orb:match_bruteforce");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!a || !b || !best_idx || !best_dist || !second_dist || pairs < 1 || n_a < 1 || n_b < 0) return ORB_ERR_BAD_ARG;
@@ -1128,6 +1131,7 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
 
 int orb_search_by_projection_mappoints(orb_matcher* m, const orb_frame_view* f, const orb_mappoint_view* mps, float th, float nn_ratio,
                                        const uint8_t* occupied, int32_t* match, int32_t* nmatches) {
+    ORB_NVTX("orb:search_by_projection_mappoints");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!f || !mps || !match || !nmatches || mps->n < 0 || (mps->n > 0 && (!mps->valid || !mps->proj_x || !mps->proj_y || !mps->level ||
@@ -1149,6 +1153,7 @@ int orb_search_by_projection_mappoints(orb_matcher* m, const orb_frame_view* f, 
 int orb_search_by_projection_lastframe(orb_matcher* m, const orb_frame_view* cur, const orb_lastframe_view* last, const orb_camera* cam,
                                        float th, int forward, int backward, int check_orientation, const uint8_t* occupied, int32_t* match,
                                        int32_t* nmatches) {
+    ORB_NVTX("orb:search_by_projection_lastframe");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!cur || !last || !cam || !match || !nmatches || last->n < 0 || (last->n > 0 && (!last->valid || !last->xc || !last->yc || !last->zc ||
@@ -1256,6 +1261,7 @@ extern "C" {
 
 int orb_search_by_projection_mappoints_batch(orb_matcher* m, const orb_frame_batch_view* f, const orb_mappoint_batch_view* mps, float th, float nn_ratio,
                                              const uint8_t* occupied, int32_t* match, int32_t* nmatches) {
+    ORB_NVTX("orb:search_by_projection_mappoints_batch");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!f || !mps || !match || !nmatches || mps->pairs != f->pairs || mps->stride < 1 || mps->stride > m->max_n || !mps->n || !mps->valid ||
@@ -1284,6 +1290,7 @@ int orb_search_by_projection_mappoints_batch(orb_matcher* m, const orb_frame_bat
 int orb_search_by_projection_lastframe_batch(orb_matcher* m, const orb_frame_batch_view* cur, const orb_lastframe_batch_view* last, const orb_camera* cam,
                                              float th, const uint8_t* forward, const uint8_t* backward, int check_orientation, const uint8_t* occupied,
                                              int32_t* match, int32_t* nmatches) {
+    ORB_NVTX("orb:search_by_projection_lastframe_batch");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!cur || !last || !cam || !match || !nmatches || !forward || !backward || last->pairs != cur->pairs || last->stride < 1 || last->stride > m->max_n ||
@@ -1318,6 +1325,7 @@ static int check_fv(const orb_featvec_view* v) {
 int orb_search_by_bow(orb_matcher* m, const orb_frame_view* kf, const orb_featvec_view* kf_fv, const uint8_t* kf_has_mappoint,
                       const orb_frame_view* f, const orb_featvec_view* f_fv, float nn_ratio, int check_orientation, int32_t* match_f,
                       int32_t* nmatches) {
+    ORB_NVTX("orb:search_by_bow");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!kf || !f || !check_fv(kf_fv) || !check_fv(f_fv) || !kf_has_mappoint || !match_f || !nmatches ||
@@ -1361,6 +1369,7 @@ int orb_search_for_triangulation(orb_matcher* m, const orb_frame_view* kf1, cons
                                  const orb_frame_view* kf2, const orb_featvec_view* fv2, const uint8_t* kf2_has_mappoint, const float* f12,
                                  float ex, float ey, const float* level_sigma2, int only_stereo, int check_orientation, int32_t* match12,
                                  int32_t* nmatches) {
+    ORB_NVTX("orb:search_for_triangulation");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!kf1 || !kf2 || !check_fv(fv1) || !check_fv(fv2) || !kf1_has_mappoint || !kf2_has_mappoint || !f12 || !level_sigma2 || !match12 ||
@@ -1427,6 +1436,7 @@ static int upload_points(orb_matcher* m, const orb_projected_view* p, const Quer
 
 int orb_search_by_projection_claiming(orb_matcher* m, const orb_frame_view* f, const orb_projected_view* pts, const uint8_t* occupied,
                                       int max_dist, int check_orientation, int32_t* match, int32_t* point_best_idx, int32_t* nmatches) {
+    ORB_NVTX("orb:search_by_projection_claiming");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!f || !check_points(pts, check_orientation) || !match || !nmatches || max_dist < 0 || max_dist > 255 ||
@@ -1441,6 +1451,7 @@ int orb_search_by_projection_claiming(orb_matcher* m, const orb_frame_view* f, c
 
 int orb_search_projected_best(orb_matcher* m, const orb_frame_view* f, const orb_projected_view* pts, const float* inv_level_sigma2,
                               int max_dist, int32_t* best_idx, int32_t* best_dist, int32_t* nfound) {
+    ORB_NVTX("orb:search_projected_best");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!f || !check_points(pts, 0) || !best_idx || !nfound || max_dist < 0 || max_dist > 255) return ORB_ERR_BAD_ARG;
@@ -1460,6 +1471,7 @@ int orb_search_projected_best(orb_matcher* m, const orb_frame_view* f, const orb
 
 int orb_search_by_sim3(orb_matcher* m, const orb_frame_view* kf1, const orb_projected_view* pts1_in_kf2, const orb_frame_view* kf2,
                        const orb_projected_view* pts2_in_kf1, int32_t* match12, int32_t* nfound) {
+    ORB_NVTX("orb:search_by_sim3");
     if (!m || !kf1 || !kf2 || !check_points(pts1_in_kf2, 0) || !check_points(pts2_in_kf1, 0) || !match12 || !nfound ||
         pts1_in_kf2->n != kf1->n || pts2_in_kf1->n != kf2->n) return ORB_ERR_BAD_ARG;
     // vnMatch1 / vnMatch2 (reference :1290-1340, :1343-1420): two independent best-candidate searches
@@ -1488,6 +1500,7 @@ int orb_search_by_sim3(orb_matcher* m, const orb_frame_view* kf1, const orb_proj
 int orb_search_for_initialization(orb_matcher* m, const orb_frame_view* f1, const orb_frame_view* f2, const float* prev_matched_x,
                                   const float* prev_matched_y, int window_size, float nn_ratio, int check_orientation, int32_t* match12,
                                   int32_t* nmatches) {
+    ORB_NVTX("orb:search_for_initialization");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!f1 || !f2 || !match12 || !nmatches || (f1->n > 0 && (!prev_matched_x || !prev_matched_y || !f1->octave)) ||
@@ -1536,6 +1549,7 @@ int orb_search_for_initialization(orb_matcher* m, const orb_frame_view* f1, cons
 int orb_search_by_bow_keyframes(orb_matcher* m, const orb_frame_view* kf1, const orb_featvec_view* fv1, const uint8_t* kf1_has_mappoint,
                                 const orb_frame_view* kf2, const orb_featvec_view* fv2, const uint8_t* kf2_has_mappoint, float nn_ratio,
                                 int check_orientation, int32_t* match12, int32_t* nmatches) {
+    ORB_NVTX("orb:search_by_bow_keyframes");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (!kf1 || !kf2 || !check_fv(fv1) || !check_fv(fv2) || !kf1_has_mappoint || !kf2_has_mappoint || !match12 || !nmatches ||
@@ -1702,6 +1716,7 @@ int orb_is_in_frustum(orb_matcher* m, const float* rcw, const float* tcw, const 
 }
 
 int orb_distinctive_descriptors(orb_matcher* m, int n_points, const int32_t* start, const uint8_t* desc, int32_t* best_idx) {
+    ORB_NVTX("orb:distinctive_descriptors");
     int st = begin_call(m);
     if (st != ORB_OK) return st;
     if (n_points < 0 || (n_points > 0 && (!start || !desc || !best_idx))) return ORB_ERR_BAD_ARG;

@@ -158,6 +158,23 @@ int orb_chunk_size(int batch);
 std::vector<int> orb_chunk_bounds(int batch);
 int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, int stride, size_t img_stride, cudaStream_t st);
 int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st, int* h_counts = nullptr);
+// NVTX ranges around the stages (host-side enqueue; profilers project them onto the stream).  Header-only NVTX3: no-ops unless a
+// tool injects itself.
+#include <nvtx3/nvToolsExt.h>
+struct OrbNvtxRange {
+    explicit OrbNvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~OrbNvtxRange() { nvtxRangePop(); }
+    OrbNvtxRange(const OrbNvtxRange&) = delete;
+    OrbNvtxRange& operator=(const OrbNvtxRange&) = delete;
+};
+#define ORB_NVTX_CAT2(a, b) a##b
+#define ORB_NVTX_CAT(a, b) ORB_NVTX_CAT2(a, b)
+#define ORB_NVTX(name) OrbNvtxRange ORB_NVTX_CAT(orb_nvtx_range_, __LINE__)(name)
+
+// device allocations go through guard.cu (ORB_B200_GUARD=1 adds canaries around every buffer; orb_debug_guard_check reads them)
+cudaError_t orb_dev_alloc(void** p, size_t bytes);
+cudaError_t orb_dev_free(void* p);
+
 #define ORB_CUDA(call)                                                                      \
     do {                                                                                    \
         cudaError_t err__ = (call);                                                         \

@@ -91,8 +91,8 @@ int orb_rectifier_create(const float* map_x, const float* map_y, int dst_w, int 
     r->device = device; r->dw = dst_w; r->dh = dst_h; r->sw = src_w; r->sh = src_h; r->max_batch = max_batch;
     const size_t n = (size_t)dst_w * dst_h;
     bool ok = cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaMalloc((void**)&r->d_src, (size_t)max_batch * src_w * src_h * 4) == cudaSuccess &&
-              cudaMalloc((void**)&r->d_dst, (size_t)max_batch * std::max(n, (size_t)src_w * src_h)) == cudaSuccess;
+              orb_dev_alloc((void**)&r->d_src, (size_t)max_batch * src_w * src_h * 4) == cudaSuccess &&
+              orb_dev_alloc((void**)&r->d_dst, (size_t)max_batch * std::max(n, (size_t)src_w * src_h)) == cudaSuccess;
     if (ok && map_x) {
         // what cv::remap derives from CV_32FC1 maps on every call (imgwarp.cpp, RemapInvoker): sx = cvRound(x * 32) ...
         std::vector<short2> xy(n); std::vector<uint16_t> a(n);
@@ -104,7 +104,7 @@ int orb_rectifier_create(const float* map_x, const float* map_y, int dst_w, int 
             xy[i].y = (short)std::max(-32768, std::min(32767, sy >> 5));
             a[i] = (uint16_t)(((sy & 31) << 5) | (sx & 31));
         }
-        ok = cudaMalloc((void**)&r->d_xy, n * sizeof(short2)) == cudaSuccess && cudaMalloc((void**)&r->d_a, n * 2) == cudaSuccess &&
+        ok = orb_dev_alloc((void**)&r->d_xy, n * sizeof(short2)) == cudaSuccess && orb_dev_alloc((void**)&r->d_a, n * 2) == cudaSuccess &&
              cudaMemcpy(r->d_xy, xy.data(), n * sizeof(short2), cudaMemcpyHostToDevice) == cudaSuccess &&
              cudaMemcpy(r->d_a, a.data(), n * 2, cudaMemcpyHostToDevice) == cudaSuccess;
     }
@@ -121,7 +121,7 @@ void orb_rectifier_destroy(orb_rectifier* r) {
     if (!r) return;
     cudaSetDevice(r->device);
     if (r->stream) cudaStreamSynchronize(r->stream);
-    cudaFree(r->d_xy); cudaFree(r->d_a); cudaFree(r->d_src); cudaFree(r->d_dst);
+    orb_dev_free(r->d_xy); orb_dev_free(r->d_a); orb_dev_free(r->d_src); orb_dev_free(r->d_dst);
     if (r->stream) cudaStreamDestroy(r->stream);
     delete r;
 }
@@ -136,6 +136,7 @@ int orb_rectifier_sync(orb_rectifier* r) {
 
 int orb_remap_device(orb_rectifier* r, const uint8_t* d_src, int src_stride, size_t src_img_stride, int batch, uint8_t* d_dst, int dst_stride,
                      size_t dst_img_stride) {
+    ORB_NVTX("orb:remap_device");
     if (!r || !d_src || !d_dst || batch < 1 || src_stride < r->sw || dst_stride < r->dw) return ORB_ERR_BAD_ARG;
     if (!r->d_xy) { orb_set_error("rectifier was created without maps"); return ORB_ERR_BAD_ARG; }
     ORB_CUDA(cudaSetDevice(r->device));
@@ -160,6 +161,7 @@ int orb_gray_device(orb_rectifier* r, const uint8_t* d_src, int w, int h, int ch
 }
 
 int orb_remap(orb_rectifier* r, const uint8_t* src, int src_stride, int batch, uint8_t* dst, int dst_stride) {
+    ORB_NVTX("orb:remap");
     if (!r || !src || !dst || batch < 1 || src_stride < r->sw || dst_stride < r->dw) return ORB_ERR_BAD_ARG;
     if (batch > r->max_batch) { orb_set_error("batch exceeds the rectifier's max_batch"); return ORB_ERR_CAPACITY; }
     ORB_CUDA(cudaSetDevice(r->device));

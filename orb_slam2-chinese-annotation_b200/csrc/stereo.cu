@@ -244,14 +244,20 @@ static int stereo_launch(orb_extractor* l, orb_extractor* r, int b0, int batch, 
     if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_stereo_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const bool T = l->timing;
     if (T) cudaEventRecord(l->ev_stage[6], l->stream);
+    nvtxRangePushA("orb:stereo_rows");
     k_stereo_rows<<<batch, 512, smem, l->stream>>>(r->d_kps + kr, r->d_counts + b0, row_start, row_items, l->d_status, S);
+    nvtxRangePop();
     if (T) cudaEventRecord(l->ev_stage[7], l->stream);
+    nvtxRangePushA("orb:stereo_match");
     dim3 grid((l->plan.kp_cap + SM_WARPS - 1) / SM_WARPS, batch);
     k_stereo_match<<<grid, SM_WARPS * 32, 0, l->stream>>>(l->d_kps + kl, l->d_desc + kl * 32, l->d_counts + b0, r->d_kps + kr, r->d_desc + kr * 32,
                                                          l->d_pyr, r->d_pyr, row_start, row_items, l->d_u_right + kl, l->d_depth + kl,
                                                          l->d_sad + kl, S, mbf, min_d, max_d);
+    nvtxRangePop();
     if (T) cudaEventRecord(l->ev_stage[8], l->stream);
+    nvtxRangePushA("orb:stereo_median");
     k_stereo_median<<<batch, 512, 0, l->stream>>>(l->d_counts + b0, l->d_u_right + kl, l->d_depth + kl, l->d_sad + kl, l->plan.kp_cap);
+    nvtxRangePop();
     if (T) { cudaEventRecord(l->ev_stage[9], l->stream); l->stage_valid[5] = l->stage_valid[6] = l->stage_valid[7] = true; }
     l->launches += 3;
     ORB_CUDA(cudaGetLastError());

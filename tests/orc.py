@@ -104,6 +104,16 @@ def distribute(cands, min_x, max_x, min_y, max_y, n_features):
     return out[:n].copy()
 
 
+def distribute_stats(cands, min_x, max_x, min_y, max_y, n_features):
+    """distribute() plus the witness of the sorted phase: (kept, [rounds, adjacent equal counts, early breaks between equal counts])."""
+    cands = np.ascontiguousarray(cands, np.int32)
+    cap = len(cands) + 8
+    out = np.empty(cap, np.int32); st = np.zeros(3, np.int32)
+    lib.orc_distribute_stats.restype = C.c_int
+    n = lib.orc_distribute_stats(_p(cands), len(cands), int(min_x), int(max_x), int(min_y), int(max_y), int(n_features), _p(out), cap, _p(st))
+    return out[:n].copy(), st
+
+
 def descriptor_distance(a, b):
     a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
     return lib.orc_descriptor_distance(_p(a), _p(b))

@@ -44,3 +44,31 @@ def test_bow_transform_edge_cases():
     w1, n1 = v.descend(q[:1], 1)
     ow, on = orc.bow_transform(voc, q[:1], 1)
     assert np.array_equal(w1, ow) and np.array_equal(n1, on)
+
+
+def test_one_vocabulary_from_four_threads():
+    """The reference transforms on ONE shared vocabulary from two threads at once (Frame::ComputeBoW on Tracking, KeyFrame::ComputeBoW on
+    LocalMapping).  Four threads, different frames each, 40 calls per thread on one handle (ctypes releases the GIL, the library
+    serialises the staged call): every result equals the oracle's for that thread's frame."""
+    import threading
+    voc = synth.make_vocabulary(10, 4, 21)
+    v = bow.ORBVocabulary(max_features=4096)
+    v.load_arrays(**voc)
+    T = 4
+    qs = [synth.vocabulary_queries(voc, 1500 + 100 * t, 30 + t) for t in range(T)]
+    want = [orc.bow_transform(voc, q, 4) for q in qs]
+    bad = []
+
+    def work(t):
+        for _ in range(40):
+            w, n = v.descend(qs[t], 4)
+            if not (np.array_equal(w, want[t][0]) and np.array_equal(n, want[t][1])):
+                bad.append(t)
+                return
+
+    ts = [threading.Thread(target=work, args=(t,)) for t in range(T)]
+    for th in ts:
+        th.start()
+    for th in ts:
+        th.join()
+    assert not bad, bad

@@ -74,9 +74,9 @@ int orb_extract(orb_extractor* e, const uint8_t* img, int w, int h, int stride, 
 int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, int h, int stride, size_t img_stride,
                       orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts);
 /* Same, but the images are already in device memory and the results stay in the handle's device
- * buffers (see orb_extractor_device_results).  Asynchronous on the handle's stream.  The image
- * allocation is read in aligned 32-bit words, i.e. up to 3 bytes past the last pixel (inside any
- * cudaMalloc'ed buffer). */
+ * buffers (see orb_extractor_device_results).  Asynchronous on the handle's stream.  The images are
+ * read in aligned 16-byte blocks that hold at least one pixel, i.e. up to 15 bytes before the first and past the last
+ * pixel of a row (inside any cudaMalloc'ed buffer, whose size and base are multiples of 256 bytes). */
 int orb_extract_device(orb_extractor* e, const uint8_t* d_imgs, int batch, int w, int h, int stride, size_t img_stride);
 /* Device views of the last batch's results: keypoints [batch][kp_cap], descriptors [batch][kp_cap][32],
  * counts [batch].  Valid until the next extract call on this handle. */

@@ -22,29 +22,45 @@ __constant__ __align__(16) signed char c_pattern[1024] = {
 };
 
 // ------------------------------------------------------------------------------------------
-// Ingest: caller images (any row stride, any alignment) -> the pitched, word-aligned level-0 slots.
-// One thread assembles one aligned 32-bit destination word from the two aligned source words that
-// cover it (funnel shift); reads and writes are coalesced.  The source allocation must extend to
-// the next 4-byte boundary past its last byte (true for cudaMalloc'ed buffers).
+// Ingest: caller images (any row stride, any alignment) -> the pitched, 16-byte-aligned level-0 slots.
+// One thread assembles one aligned 16-byte destination chunk from the two aligned 16-byte source blocks that cover it
+// (word select + funnel shift): two LDG.128 and one STG.128 per thread, (row, chunk) flattened over the image so that no
+// thread idles on a row tail.  Source reads stay inside aligned 16-byte blocks that hold at least one pixel of the row
+// (always inside a cudaMalloc'ed allocation); destination bytes past the row's last pixel are written as 0.
 __global__ void __launch_bounds__(256) k_ingest(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, const int w, const int h,
                                                 const int stride, const unsigned long long img_stride, const int dst_pitch,
-                                                const unsigned long long dst_img_stride) {
-    const int j = blockIdx.x * 256 + threadIdx.x;  // destination word within the row
-    const int y = blockIdx.y, b = blockIdx.z;
-    if (4 * j >= w) return;
-    const unsigned long long a = (unsigned long long)src + (unsigned long long)b * img_stride + (unsigned long long)y * stride + 4ull * j;
-    const uint32_t* q = reinterpret_cast<const uint32_t*>(a & ~3ull);
-    const unsigned sh = (unsigned)(a & 3ull) * 8u;
-    const uint32_t lo = __ldg(q);
-    uint32_t v = lo;
-    if (sh) v = __funnelshift_r(lo, __ldg(q + 1), sh);
-    const int rem = w - 4 * j;
-    if (rem < 4) v &= 0xffffffffu >> (8 * (4 - rem));
-    *reinterpret_cast<uint32_t*>(dst + (size_t)b * dst_img_stride + (size_t)y * dst_pitch + 4 * j) = v;
+                                                const unsigned long long dst_img_stride, const int nch, const unsigned magic) {
+    const unsigned idx = blockIdx.x * 256u + threadIdx.x;
+    const int y = nch == 1 ? (int)idx : (int)__umulhi(idx, magic);   // idx / nch (idx < 2^20, nch <= 256)
+    if (y >= h) return;
+    const int j = (int)idx - y * nch, b = blockIdx.y;
+    const int rem = w - 16 * j;                       // pixels of this chunk (>= 1)
+    const unsigned long long a = (unsigned long long)src + (unsigned long long)b * img_stride + (unsigned long long)y * stride + 16ull * j;
+    const uint4* q = reinterpret_cast<const uint4*>(a & ~15ull);
+    const unsigned mis = (unsigned)(a & 15ull);
+    const uint4 A = __ldg(q);
+    uint4 B = make_uint4(0u, 0u, 0u, 0u);
+    if (mis + (unsigned)min(rem, 16) > 16u) B = __ldg(q + 1);
+    // words mis/4 .. mis/4 + 4 of (A, B), then a byte funnel by mis % 4
+    unsigned w0 = A.x, w1 = A.y, w2 = A.z, w3 = A.w, w4 = B.x, w5 = B.y, w6 = B.z, w7 = B.w;
+    if (mis & 8u) { w0 = w2; w1 = w3; w2 = w4; w3 = w5; w4 = w6; w5 = w7; }
+    if (mis & 4u) { w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; }
+    const unsigned sh = (mis & 3u) * 8u;
+    uint4 v = make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh));
+    if (rem < 16) {
+        const unsigned keep = 0xffffffffu >> (8 * (4 - (rem & 3)));   // rem & 3 == 0 is handled by the word tests
+        if (rem < 4) { v.x &= keep; v.y = v.z = v.w = 0u; }
+        else if (rem < 8) { if (rem & 3) v.y &= keep; else v.y = 0u; v.z = v.w = 0u; }
+        else if (rem < 12) { if (rem & 3) v.z &= keep; else v.z = 0u; v.w = 0u; }
+        else { if (rem & 3) v.w &= keep; else v.w = 0u; }
+    }
+    *reinterpret_cast<uint4*>(dst + (size_t)b * dst_img_stride + (size_t)y * dst_pitch + 16 * j) = v;
 }
 void launch_ingest(cudaStream_t s, const uint8_t* src, uint8_t* dst, int w, int h, int stride, size_t img_stride, int dst_pitch, size_t dst_img_stride, int batch) {
-    dim3 grid(((w + 3) / 4 + 255) / 256, h, batch);
-    k_ingest<<<grid, 256, 0, s>>>(src, dst, w, h, stride, img_stride, dst_pitch, dst_img_stride);
+    const int nch = (w + 15) / 16;
+    const unsigned magic = (unsigned)((1ull << 32) / (unsigned)nch) + 1u;
+    dim3 grid((unsigned)(((size_t)nch * h + 255) / 256), batch);
+    k_ingest<<<grid, 256, 0, s>>>(src, dst, w, h, stride, img_stride, dst_pitch, dst_img_stride, nch, magic);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -430,16 +446,43 @@ __device__ __align__(16) signed char g_pattern[1024] = {
 #include "../../include/orb_pattern_31.inc"
 };
 
+// Weights of the intensity-centroid moments for the raw patch as it is fetched: 31 rows x OD_RW aligned words, the patch starting
+// at byte rsh = 0..3 of the first word.  Entry [rsh][row * OD_RW + word] = (x: the four u = column - 15 as signed bytes, 0 outside
+// the radius-15 disc (|u| <= umax[|v|]); y: 1 inside the disc, 0 outside).  m10 += dp4a(pixels, x); m01 += v * dp4a(pixels, y).
+// Filled by orb_upload_moment_table() when an extractor is created (umax comes from the reference's table code, :466-489).
+__device__ uint2 g_moment_w[4 * 32 * OD_RW];
+cudaError_t orb_upload_moment_table(const int* umax) {
+    uint2 h[4 * 32 * OD_RW];   // same contents from every caller (the disc is a constant of the algorithm)
+    for (int rsh = 0; rsh < 4; ++rsh)
+        for (int i = 0; i < 32 * OD_RW; ++i) {
+            const int r = i / OD_RW, c = i % OD_RW, v = r - ORB_HALF_PATCH;
+            uint32_t wu = 0, wm = 0;
+            for (int j = 0; j < 4 && r < 31; ++j) {
+                const int u = 4 * c + j - rsh - ORB_HALF_PATCH;
+                if (u >= -ORB_HALF_PATCH && u <= ORB_HALF_PATCH && (u < 0 ? -u : u) <= umax[v < 0 ? -v : v]) {
+                    wu |= (uint32_t)(uint8_t)(signed char)u << (8 * j);
+                    wm |= 1u << (8 * j);
+                }
+            }
+            h[rsh * 32 * OD_RW + i] = make_uint2(wu, wm);
+        }
+    return cudaMemcpyToSymbol(g_moment_w, h, sizeof(h));
+}
+__device__ __forceinline__ int dp4a_u8_s8(unsigned px, unsigned w, int acc) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(px), "r"(w), "r"(acc));
+    return d;
+}
+
 // Both patches are fetched with aligned 32-bit loads (all of them in flight together) and keep
 // the level's word alignment in shared memory; the rBRIEF gathers and the moment columns then
 // read bytes from shared memory only.
-__global__ void __launch_bounds__(OD_WARPS * 32)
+__global__ void __launch_bounds__(OD_WARPS * 32, 4)
 k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur, const uint32_t* __restrict__ lvl_kp,
                   const int* __restrict__ lvl_cnt, orb_keypoint* __restrict__ kps, uint8_t* __restrict__ desc,
                   int* __restrict__ counts, const Plan P) {
     __shared__ float2 s_pat[512];
     __shared__ uint32_t s_desc[OD_WARPS][37 * OD_DW];
-    __shared__ uint32_t s_raw[OD_WARPS][31 * OD_RW];
     __shared__ int s_cnt[ORB_MAX_LEVELS], s_pre[ORB_MAX_LEVELS];
     const int b = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -456,7 +499,6 @@ k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ b
     __syncthreads();
 
     uint32_t* sd = s_desc[warp];
-    uint32_t* sr = s_raw[warp];
 #pragma unroll 1
     for (int it = 0; it < OD_KP_PER_CTA / OD_WARPS; ++it) {
         const int slot = blockIdx.x * OD_KP_PER_CTA + it * OD_WARPS + warp;
@@ -491,27 +533,21 @@ k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ b
             vd[k] = i < 37 * OD_DW ? __ldg(reinterpret_cast<const uint32_t*>(dbase + r * pitch) + c) : 0u;
         }
 #pragma unroll
-        for (int k = 0; k < 9; ++k) { const int i = k * 32 + lane; if (i < 31 * OD_RW) sr[i] = vr[k]; }
-#pragma unroll
         for (int k = 0; k < 13; ++k) { const int i = k * 32 + lane; if (i < 37 * OD_DW) sd[i] = vd[k]; }
         __syncwarp();
 
-        // IC_Angle (reference :77-113): integer moments over the radius-15 disc; lane = column u
+        // IC_Angle (reference :77-113): integer moments over the radius-15 disc, straight from the fetched words (exact integers,
+        // any summation order): per word one byte dot product with the u weights and one with the disc mask
         int m10 = 0, m01 = 0;
         {
-            const int u = lane - ORB_HALF_PATCH;
-            const int au = u < 0 ? -u : u;
-            const uint8_t* col = reinterpret_cast<const uint8_t*>(sr) + rsh + (lane < 31 ? lane : 0);
-            int colsum = 0;
+            const uint2* wt = g_moment_w + rsh * (32 * OD_RW) + lane;
 #pragma unroll
-            for (int v = -ORB_HALF_PATCH; v <= ORB_HALF_PATCH; ++v) {
-                const int d = P.umax[v < 0 ? -v : v];
-                int val = col[(v + ORB_HALF_PATCH) * (OD_RW * 4)];
-                if (lane >= 31 || au > d) val = 0;
-                colsum += val;
-                m01 += v * val;
+            for (int k = 0; k < 9; ++k) {
+                const uint2 wq = __ldg(wt + k * 32);
+                const int v = (((k * 32 + lane) * 57) >> 9) - ORB_HALF_PATCH;
+                m10 = dp4a_u8_s8(vr[k], wq.x, m10);
+                m01 += v * dp4a_u8_s8(vr[k], wq.y, 0);
             }
-            m10 = u * colsum;
         }
 #pragma unroll
         for (int o = 16; o; o >>= 1) {

@@ -7,6 +7,7 @@
 #include <cstring>
 
 void launch_resize(cudaStream_t s, uint8_t* pyr, const CUtensorMap* src_map, bool tma, const LevelGeom& src, const LevelGeom& dst, int b0, int batch);
+cudaError_t orb_upload_moment_table(const int* umax);
 void launch_ingest(cudaStream_t s, const uint8_t* src, uint8_t* dst, int w, int h, int stride, size_t img_stride, int dst_pitch, size_t dst_img_stride, int batch);
 void launch_gauss(cudaStream_t s, const TmaMaps& maps, const uint8_t* pyr, uint8_t* blur, const Plan& P, int b0, int batch);
 cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch);
@@ -346,7 +347,7 @@ int orb_pipe_streams(orb_extractor* e) {
     if (!e->s_h2d) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_h2d, cudaStreamNonBlocking));
     if (!e->s_d2h) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_d2h, cudaStreamNonBlocking));
     if (!e->d_in && e->max_batch > 1 && !getenv("ORB_B200_NO_STAGING"))
-        ORB_CUDA(orb_dev_alloc((void**)&e->d_in, (size_t)e->max_batch * e->max_w * e->max_h + 16));
+        ORB_CUDA(orb_dev_alloc((void**)&e->d_in, (size_t)e->max_batch * e->max_w * e->max_h + 64));
     return ORB_OK;
 }
 cudaEvent_t orb_pool_event(orb_extractor* e, int i) {
@@ -436,6 +437,7 @@ int orb_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini
     e->nfeatures = nfeatures; e->scale_factor = (double)scale_factor; e->nlevels = nlevels; e->ini_th = ini_th; e->min_th = min_th;
     e->max_w = max_w; e->max_h = max_h; e->max_batch = max_batch; e->device = device;
     make_tables(*e);
+    if (orb_upload_moment_table(e->umax) != cudaSuccess) { delete e; orb_set_error("moment table upload"); return ORB_ERR_CUDA; }
     Plan P; Needs need;
     int st = build_plan(*e, max_w, max_h, P, need, nullptr);
     if (st != ORB_OK) { delete e; orb_set_error("unsupported maximum geometry (level size must be <= 4096, aspect >= 1:2)"); return st; }
@@ -472,7 +474,7 @@ int orb_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini
     ALLOC(e->d_sad, (size_t)e->kp_cap_max * B * sizeof(int));
     e->row_items_cap = e->kp_cap_max * (2 * (int)std::ceil(2.0f * e->sf[nlevels - 1]) + 3);
     ALLOC(e->d_row_start, B * (ORB_MAX_DIM + 1) * sizeof(int));
-    ALLOC(e->d_row_items, B * (size_t)e->row_items_cap * sizeof(int));
+    ALLOC(e->d_row_items, B * (size_t)e->row_items_cap * sizeof(int2));
     if (cudaEventCreateWithFlags(&e->ev_done, cudaEventDisableTiming) != cudaSuccess) { free_buffers(e); delete e; orb_set_error("event"); return ORB_ERR_CUDA; }
 #undef ALLOC
     cudaMemset(e->d_status, 0, sizeof(int));

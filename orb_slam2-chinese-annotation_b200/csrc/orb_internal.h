@@ -121,7 +121,7 @@ struct orb_extractor {
     float* d_depth = nullptr;
     int* d_sad = nullptr;           // [batch][kp_cap] best SAD per left keypoint (-1 none)
     int* d_row_start = nullptr;     // [batch][ORB_MAX_DIM + 1] vRowIndices as CSR
-    int* d_row_items = nullptr;     // [batch][row_items_cap]
+    int2* d_row_items = nullptr;    // [batch][row_items_cap]  (x bits of the right keypoint, index | octave << 24)
     int row_items_cap = 0;
     cudaEvent_t ev_done = nullptr;
     // host-buffer batches are cut into chunks of image slots: upload (s_h2d), kernels (stream) and

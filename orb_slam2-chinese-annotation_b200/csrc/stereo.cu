@@ -27,7 +27,7 @@ struct StereoGeom {
 
 __global__ void __launch_bounds__(512)
 k_stereo_rows(const orb_keypoint* __restrict__ kps_r, const int* __restrict__ counts_r, int* __restrict__ row_start,
-              int* __restrict__ row_items, int* __restrict__ status, const StereoGeom S) {
+              int2* __restrict__ row_items, int* __restrict__ status, const StereoGeom S) {
     extern __shared__ int s_rows[];  // h0 + 1 counters, then h0 + 1 cursors
     __shared__ int s_warp[17];
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -72,19 +72,22 @@ k_stereo_rows(const orb_keypoint* __restrict__ kps_r, const int* __restrict__ co
     for (int i = tid; i <= H; i += 512) rs[i] = cur[i];
     if (carry > S.items_cap) { if (tid == 0) atomicExch(status, ORB_ERR_INTERNAL); return; }
     __syncthreads();
-    int* items = row_items + (size_t)b * S.items_cap;
+    // an item carries what the candidate filter of k_stereo_match reads (x, octave), so that the filter costs one load
+    int2* items = row_items + (size_t)b * S.items_cap;
     for (int i = tid; i < nR; i += 512) {
-        const float y = K[i].y, r = __fmul_rn(2.0f, S.sf[K[i].octave]);
+        const int oct = K[i].octave;
+        const float y = K[i].y, r = __fmul_rn(2.0f, S.sf[oct]);
         const int maxr = min((int)ceilf(__fadd_rn(y, r)), H - 1), minr = max((int)floorf(__fsub_rn(y, r)), 0);
-        for (int yi = minr; yi <= maxr; ++yi) items[atomicAdd(&cur[yi], 1)] = i;
+        const int2 it = make_int2(__float_as_int(K[i].x), i | (oct << 24));
+        for (int yi = minr; yi <= maxr; ++yi) items[atomicAdd(&cur[yi], 1)] = it;
     }
 }
 
 #define SM_WARPS 8
-__global__ void __launch_bounds__(SM_WARPS * 32)
+__global__ void __launch_bounds__(SM_WARPS * 32, 6)   // latency-bound (a chain of dependent loads per keypoint): as many resident warps as fit
 k_stereo_match(const orb_keypoint* __restrict__ kps_l, const uint8_t* __restrict__ desc_l, const int* __restrict__ counts_l,
                const orb_keypoint* __restrict__ kps_r, const uint8_t* __restrict__ desc_r, const uint8_t* __restrict__ pyr_l,
-               const uint8_t* __restrict__ pyr_r, const int* __restrict__ row_start, const int* __restrict__ row_items,
+               const uint8_t* __restrict__ pyr_r, const int* __restrict__ row_start, const int2* __restrict__ row_items,
                float* __restrict__ u_right, float* __restrict__ depth, int* __restrict__ sad, const StereoGeom S, const float mbf,
                const float min_d, const float max_d) {
     __shared__ int s_l[SM_WARPS][11][12];
@@ -106,30 +109,33 @@ k_stereo_match(const orb_keypoint* __restrict__ kps_l, const uint8_t* __restrict
 
     const uint4* dl = reinterpret_cast<const uint4*>(desc_l + oL * 32);
     const uint4 a0 = dl[0], a1 = dl[1];
-    const int* items = row_items + (size_t)b * S.items_cap;
-    const orb_keypoint* KR = kps_r + (size_t)b * S.kp_cap_r;
+    const int2* items = row_items + (size_t)b * S.items_cap;
     const uint8_t* DR = desc_r + (size_t)b * S.kp_cap_r * 32;
     unsigned best = ((unsigned)ST_TH_HIGH << 20);  // (dist << 20) | iR ; strict < against TH_HIGH
+    float best_x = 0.f;                             // x of this lane's best candidate
     for (int c = c0 + lane; c < c1; c += 32) {
-        const int iR = items[c];
-        const orb_keypoint kr = KR[iR];
-        if (kr.octave < kl.octave - 1 || kr.octave > kl.octave + 1) continue;
-        if (kr.x >= minU && kr.x <= maxU) {
+        const int2 it = __ldg(&items[c]);
+        const int iR = it.y & 0xffffff, octR = it.y >> 24;
+        const float xR = __int_as_float(it.x);
+        if (octR < kl.octave - 1 || octR > kl.octave + 1) continue;
+        if (xR >= minU && xR <= maxU) {
             const uint4* dr = reinterpret_cast<const uint4*>(DR + (size_t)iR * 32);
             const unsigned d = (unsigned)orb_hamming256(a0, a1, dr[0], dr[1]);
-            best = min(best, (d << 20) | (unsigned)iR);
+            const unsigned key = (d << 20) | (unsigned)iR;
+            if (key < best) { best = key; best_x = xR; }
         }
     }
+    const unsigned mine = best;
 #pragma unroll
     for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
     const int bestDist = (int)(best >> 20);
     if (bestDist >= ST_TH_ORB) return;
-    const int bestR = (int)(best & 0xfffffu);
+    // the winning lane hands over its candidate's x (keys are unique: they carry the candidate index)
+    const float uR0 = __shfl_sync(0xffffffffu, best_x, __ffs(__ballot_sync(0xffffffffu, mine == best)) - 1);
 
     // sub-pixel refinement by sliding an 11x11 window on the left keypoint's pyramid level
     const int oct = kl.octave;
     const float isf = S.inv_sf[oct];
-    const float uR0 = KR[bestR].x;
     const int su = (int)roundf(__fmul_rn(kl.x, isf)), sv = (int)roundf(__fmul_rn(kl.y, isf)), sr = (int)roundf(__fmul_rn(uR0, isf));
     const LevelGeom& GL = S.lvl_l[oct];
     const LevelGeom& GR = S.lvl_r[oct];
@@ -236,7 +242,7 @@ static int stereo_launch(orb_extractor* l, orb_extractor* r, int b0, int batch, 
     }
     const size_t kl = (size_t)b0 * S.kp_cap_l, kr = (size_t)b0 * S.kp_cap_r;
     int* row_start = l->d_row_start + (size_t)b0 * (ORB_MAX_DIM + 1);
-    int* row_items = l->d_row_items + (size_t)b0 * S.items_cap;
+    int2* row_items = l->d_row_items + (size_t)b0 * S.items_cap;
     // the right handle's stream must have finished producing its outputs
     ORB_CUDA(cudaEventRecord(r->ev_done, r->stream));
     ORB_CUDA(cudaStreamWaitEvent(l->stream, r->ev_done, 0));

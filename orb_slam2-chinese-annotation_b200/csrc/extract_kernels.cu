@@ -151,20 +151,20 @@ __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr,
 // iniTh -> minTh retry (reference :843-850) only re-filters the same list: a cell keeps its maxima
 // with s >= iniTh, or, when it has none, those with s >= minTh.
 //
-// One CTA per group of ORB_FAST_G consecutive cells of a cell row (their interiors tile a
-// contiguous strip).  The strip's 4-pixel words are split into 8 contiguous row-major chunks, one
-// per warp, and every list below is a per-warp segment that stays in row-major order, so the
-// final write needs no sort and no atomics:
-//   (1) stage the strip in shared memory with 16-byte loads;
-//   (2) byte-SIMD necessary test at minTh on 4 pixels per thread, survivors appended in order;
-//   (3) exact score of the survivors, two pixels per thread on packed 16-bit lanes (VIADD.16x2 /
-//       VIMNMX3.S16x2), into a shared score map; corners compacted in place, in order;
-//   (4) strict local maxima inside the own cell, compacted in place; per-warp per-cell counts;
-//   (5) per-cell threshold choice, prefix over warps, ordered (row-major) write.
-// The tile pitch TP and score pitch TP - 32 are compile-time so that every ring / neighbour
-// offset is an immediate.
-#define FAST_THREADS 256
-#define FAST_WARPS 8
+// One WARP per cell, FC_CELLS consecutive cells per warp, no CTA-wide barrier anywhere: every warp owns a private
+// shared-memory region (tile | score map with a zero frame | list) and every list stays in row-major order, so the
+// final write needs no sort, no atomics and no prefix over warps, and the per-cell threshold choice is a warp vote:
+//   (1) stage the cell view (w_cell + 6) x (h_cell + 6) with 16-byte LDGSTS, zero the score map;
+//   (2) byte-SIMD necessary test at minTh on one 4-pixel word per lane, survivors appended in order
+//       (offsets from three bit-sliced ballots of the per-lane count);
+//   (3) exact score of the survivors, two pixels per lane on packed 16-bit lanes (VIMNMX3.S16x2), into the score
+//       map; corners compacted in place;
+//   (4) strict local maxima (VIMNMX3 over the 8 neighbours), compacted in place, counted with and without iniTh;
+//   (5) ordered write of the maxima that pass the cell's threshold.
+// The tile pitch TP and score pitch SP are compile-time so that every ring / neighbour offset is an immediate.
+#define FC_WARPS 4     // warps per CTA (independent of each other)
+#define FC_CELLS 4     // consecutive cells walked by one warp
+#define FC_TP 80       // tile pitch: view width (<= 59 + 6) + alignment shift (<= 15); 20 words: consecutive rows land in different banks
 
 __device__ __forceinline__ unsigned gt_bytes(unsigned ad, unsigned k) {  // bit 7 of byte j set <=> ad.j > 127 - k.j  (k.j <= 127)
     return ad | ((ad & 0x7f7f7f7fu) + k);
@@ -196,219 +196,178 @@ __device__ __forceinline__ unsigned fast_score_x2(const unsigned (&e)[16], const
     return __vsub2(__vmaxs2(__vsub2(__vmaxs2(dk, a9[15]), c), __vsub2(c, __vmins2(br, z9[15]))), 0x00010001u);
 }
 
-// Dynamic shared memory: tile (rows x TP bytes, 16-byte aligned like the level) | score map
-// ((ih + 2) x SP bytes, zero frame) | lists (u16: y << 8 | x)
-template <int TP>
-__global__ void __launch_bounds__(FAST_THREADS)
+// g / n == (g * c_div_magic[n]) >> 20 for g < 2^20 / n (words of a cell view: n <= 17, g < 17 * 59)
+__constant__ unsigned c_div_magic[20] = {0u, (1u << 20) / 1 + 1, (1u << 20) / 2 + 1, (1u << 20) / 3 + 1, (1u << 20) / 4 + 1, (1u << 20) / 5 + 1,
+    (1u << 20) / 6 + 1, (1u << 20) / 7 + 1, (1u << 20) / 8 + 1, (1u << 20) / 9 + 1, (1u << 20) / 10 + 1, (1u << 20) / 11 + 1, (1u << 20) / 12 + 1,
+    (1u << 20) / 13 + 1, (1u << 20) / 14 + 1, (1u << 20) / 15 + 1, (1u << 20) / 16 + 1, (1u << 20) / 17 + 1, (1u << 20) / 18 + 1, (1u << 20) / 19 + 1};
+
+// Dynamic shared memory, per warp (warp_bytes apart): tile (rows x FC_TP bytes, 16-byte aligned like the level) |
+// score map ((ih + 2) x SP bytes, zero frame) at score_off | list (u16: y << 8 | x) at list_off
+template <int SP>
+__global__ void __launch_bounds__(FC_WARPS * 32)
 k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
-             const int smem_tile_bytes, const int smem_score_bytes) {
-    constexpr int SP = TP - 32, TPW = TP / 4;
+             const int warp_bytes, const int score_off, const int list_off) {
+    constexpr int TP = FC_TP, TPW = TP / 4;
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int s_wc[FAST_WARPS][ORB_FAST_G];   // per warp, per cell: maxima | maxima with s >= iniTh << 16
-
-    int l = 0;
-    while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].grp_off) ++l;
-    const LevelGeom& G = P.lv[l];
-    const int g = blockIdx.x - G.grp_off;
-    const int ci = (int)(((unsigned)g * G.grp_magic) >> 20), cj0 = (g - ci * G.n_grp_x) * ORB_FAST_G;
-    const int nc = min(ORB_FAST_G, G.n_cols - cj0);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1, full = 0xffffffffu;
+    uint8_t* const wt = smem + warp * warp_bytes;
+    uint8_t* const sc = wt + score_off;
+    uint16_t* const seg = reinterpret_cast<uint16_t*>(wt + list_off);
+    const uint32_t* const tw32 = reinterpret_cast<const uint32_t*>(wt);
     const int b = blockIdx.y;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const unsigned lt = (1u << lane) - 1;
-    const int cell0 = ci * G.n_cols + cj0;
-    int* out_cnt = cell_cnt + (size_t)b * P.total_cells + G.cell_off + cell0;
-    const int w_cell = G.w_cell;
-
-    // strip view [iniX, maxX) x [iniY, maxY) (reference :819-839).  A cell is skipped when
-    // iniX >= maxBorderX - 6; only the last processed cell of a row can be clipped.
-    const int iniY = ORB_WIN + ci * G.h_cell, iniX = ORB_WIN + cj0 * w_cell;
-    int nv = 0;
-    if (iniY < G.max_by - 3)
-        for (int j = 0; j < nc; ++j) nv += (iniX + j * w_cell < G.max_bx - 6);
-    const int maxY = min(iniY + G.h_cell + 6, G.max_by), maxX = min(iniX + nv * w_cell + 6, G.max_bx);
-    const int tw = maxX - iniX, th = maxY - iniY;
-    const int iw = tw - 6, ih = th - 6;  // interior = tested pixels
-    if (nv == 0 || iw <= 0 || ih <= 0) { if (tid < nc) out_cnt[tid] = 0; return; }
-    if (tid >= nv && tid < nc) out_cnt[tid] = 0;
-
-    uint8_t* sc = smem + smem_tile_bytes;
-    uint16_t* list = reinterpret_cast<uint16_t*>(sc + smem_score_bytes);
-
-    // (1) stage with aligned 16-byte loads (view starts at byte `shift` of the tile rows)
-    const int shift = iniX & 15;
-    {
-        const uint8_t* S = pyr + G.off + (size_t)b * G.img_stride + (size_t)iniY * G.pitch + (iniX - shift);
-        const int nq = (tw + shift + 15) >> 4;
-        const unsigned qmagic = (1u << 16) / (unsigned)nq + 1u;   // i / nq for i < 2^16 / nq
-        uint4* t4 = reinterpret_cast<uint4*>(smem);
-        for (int i = tid; i < nq * th; i += FAST_THREADS) {
-            const int y = (int)(((unsigned)i * qmagic) >> 16), x = i - y * nq;
-            cp_async16(&t4[y * (TP / 16) + x], reinterpret_cast<const uint4*>(S + (size_t)y * G.pitch) + x);
-        }
-        uint32_t* sc32 = reinterpret_cast<uint32_t*>(sc);
-        for (int i = tid; i < (ih + 2) * (SP / 4); i += FAST_THREADS) sc32[i] = 0u;
-        cp_async_wait_all();
-    }
-    __syncthreads();
-    const uint32_t* tw32 = reinterpret_cast<const uint32_t*>(smem);
-    const uint8_t* tile = smem + shift;
-    // interior words of a row: word wx holds interior pixels xi = 4 * wx - shift - 3 + k, k = 0..3
-    const int w0 = (shift + 3) >> 2, nwi = ((shift + 3 + iw - 1) >> 2) - w0 + 1;
-    const unsigned gmagic = (1u << 20) / (unsigned)nwi + 1u;
-    const int ngroups = nwi * ih;
-    const int chunk = (ngroups + FAST_WARPS - 1) / FAST_WARPS;
-    uint16_t* seg = list + warp * chunk * 4;
     const int t = P.min_th, ini_th = P.ini_th;
+    const unsigned kk = (unsigned)(127 - min(t, 126)) * 0x01010101u;
 
-    // (2) necessary test: both ring pixels of the vertical pair (1, 9) and of the horizontal pair
-    // (5, 13) within t of the centre => no 9-arc
-    int n_a = 0;
-    {
-        const unsigned kk = (unsigned)(127 - min(t, 126)) * 0x01010101u;
-        const int xfirst = 4 * w0 - shift - 3;                       // <= 0: interior x of byte 0 of the first word
-        const unsigned mfirst = 0x80808080u << (8 * -xfirst);
-        const int over = xfirst + 4 * nwi - iw;                      // bytes of the last word beyond the interior (0..3)
-        const unsigned mlast = 0x80808080u >> (8 * over);
-        const int gend = min(ngroups, (warp + 1) * chunk);
-        for (int gi = warp * chunk + lane; gi - lane < gend; gi += 32) {
-            unsigned m = 0, i0 = 0;
-            if (gi < gend) {
-                const int y = (int)(((unsigned)gi * gmagic) >> 20), wxi = gi - y * nwi;
-                const uint32_t* c = tw32 + (y + 3) * TPW + w0 + wxi;
-                const unsigned C = c[0], N = c[-3 * TPW], S = c[3 * TPW], L = c[-1], R = c[1];
-                const unsigned E = __byte_perm(C, R, 0x6543), Wp = __byte_perm(L, C, 0x4321);  // x + 3, x - 3
-                const unsigned pv = gt_bytes(__vabsdiffu4(N, C), kk) | gt_bytes(__vabsdiffu4(S, C), kk);
-                const unsigned ph = gt_bytes(__vabsdiffu4(E, C), kk) | gt_bytes(__vabsdiffu4(Wp, C), kk);
-                m = pv & ph & 0x80808080u;
-                if (wxi == 0) m &= mfirst;
-                if (wxi == nwi - 1) m &= mlast;
-                i0 = (unsigned)((y << 8) + xfirst + 4 * wxi);
-            }
-            const int cnt = __popc(m);
-            const unsigned b1 = __ballot_sync(0xffffffffu, cnt >= 1);
-            if (b1) {
-                const unsigned b2 = __ballot_sync(0xffffffffu, cnt >= 2), b3 = __ballot_sync(0xffffffffu, cnt >= 3),
-                               b4 = __ballot_sync(0xffffffffu, cnt >= 4);
-                int o = n_a + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt) + __popc(b4 & lt);
-                if (m & 0x80u) seg[o++] = (uint16_t)i0;
-                if (m & 0x8000u) seg[o++] = (uint16_t)(i0 + 1);
-                if (m & 0x800000u) seg[o++] = (uint16_t)(i0 + 2);
-                if (m & 0x80000000u) seg[o++] = (uint16_t)(i0 + 3);
-                n_a += __popc(b1) + __popc(b2) + __popc(b3) + __popc(b4);
+    int cg = (blockIdx.x * FC_WARPS + warp) * FC_CELLS;
+    const int cg_end = min(cg + FC_CELLS, P.total_cells);
+    int l = 0;
+#pragma unroll 1
+    for (; cg < cg_end; ++cg) {
+        while (l + 1 < P.nlevels && cg >= P.lv[l + 1].cell_off) ++l;
+        const LevelGeom& G = P.lv[l];
+        const int c = cg - G.cell_off;
+        const int ci = (int)__umulhi((unsigned)c, G.ncols_magic), cj = c - ci * G.n_cols;
+        int* const out_cnt = cell_cnt + (size_t)b * P.total_cells + cg;
+        // cell view [iniX, maxX) x [iniY, maxY) (reference :819-839)
+        const int iniY = ORB_WIN + ci * G.h_cell, iniX = ORB_WIN + cj * G.w_cell;
+        const int maxY = min(iniY + G.h_cell + 6, G.max_by), maxX = min(iniX + G.w_cell + 6, G.max_bx);
+        const int tw = maxX - iniX, th = maxY - iniY;
+        const int iw = tw - 6, ih = th - 6;  // interior = tested pixels
+        if (iniY >= G.max_by - 3 || iniX >= G.max_bx - 6 || iw <= 0 || ih <= 0) { if (lane == 0) *out_cnt = 0; continue; }
+
+        // (1) stage with aligned 16-byte loads (the view starts at byte `shift` of the tile rows)
+        const int shift = iniX & 15;
+        __syncwarp();   // the previous cell's readers are done with the tile, the score map and the list
+        {
+            const uint8_t* S = pyr + G.off + (size_t)b * G.img_stride + (size_t)iniY * G.pitch + (iniX - shift);
+            const int nq = (tw + shift + 15) >> 4;          // <= 5
+            const int q = lane & 7;
+            if (q < nq)
+                for (int y = lane >> 3; y < th; y += 4) cp_async16(wt + y * TP + q * 16, S + (size_t)y * G.pitch + q * 16);
+            uint4* sc4 = reinterpret_cast<uint4*>(sc);
+            for (int i = lane; i < (ih + 2) * (SP / 16); i += 32) sc4[i] = make_uint4(0u, 0u, 0u, 0u);
+            cp_async_wait_all();
+        }
+        __syncwarp();
+        const uint8_t* tile = wt + shift;
+        // interior words of a row: word wx holds interior pixels xi = 4 * wx - shift - 3 + k, k = 0..3
+        const int w0 = (shift + 3) >> 2, nwi = ((shift + 3 + iw - 1) >> 2) - w0 + 1;
+        const unsigned gmagic = c_div_magic[nwi];
+        const int ngroups = nwi * ih;
+
+        // (2) necessary test: both ring pixels of the vertical pair (1, 9) and of the horizontal pair
+        // (5, 13) within t of the centre => no 9-arc
+        int n_a = 0;
+        {
+            const int xfirst = 4 * w0 - shift - 3;                       // <= 0: interior x of byte 0 of the first word
+            const unsigned mfirst = 0x80808080u << (8 * -xfirst);
+            const int over = xfirst + 4 * nwi - iw;                      // bytes of the last word beyond the interior (0..3)
+            const unsigned mlast = 0x80808080u >> (8 * over);
+#pragma unroll 1
+            for (int g0 = 0; g0 < ngroups; g0 += 32) {
+                const int gi = g0 + lane;
+                unsigned m = 0, i0 = 0;
+                if (gi < ngroups) {
+                    const int y = (int)(((unsigned)gi * gmagic) >> 20), wxi = gi - y * nwi;
+                    const uint32_t* cw = tw32 + (y + 3) * TPW + w0 + wxi;
+                    const unsigned C = cw[0], N = cw[-3 * TPW], S = cw[3 * TPW], L = cw[-1], R = cw[1];
+                    const unsigned E = __byte_perm(C, R, 0x6543), Wp = __byte_perm(L, C, 0x4321);  // x + 3, x - 3
+                    const unsigned pv = gt_bytes(__vabsdiffu4(N, C), kk) | gt_bytes(__vabsdiffu4(S, C), kk);
+                    const unsigned ph = gt_bytes(__vabsdiffu4(E, C), kk) | gt_bytes(__vabsdiffu4(Wp, C), kk);
+                    m = pv & ph & 0x80808080u;
+                    if (wxi == 0) m &= mfirst;
+                    if (wxi == nwi - 1) m &= mlast;
+                    i0 = (unsigned)((y << 8) + xfirst + 4 * wxi);
+                }
+                const int cnt = __popc(m);
+                const unsigned b0 = __ballot_sync(full, cnt & 1), b1 = __ballot_sync(full, cnt & 2), b2 = __ballot_sync(full, cnt & 4);
+                if (b0 | b1 | b2) {
+                    int o = n_a + __popc(b0 & lt) + 2 * __popc(b1 & lt);
+                    if (b2) o += 4 * __popc(b2 & lt);
+                    n_a = __shfl_sync(full, o + cnt, 31);
+                    if (m & 0x80u) seg[o++] = (uint16_t)i0;
+                    if (m & 0x8000u) seg[o++] = (uint16_t)(i0 + 1);
+                    if (m & 0x800000u) seg[o++] = (uint16_t)(i0 + 2);
+                    if (m & 0x80000000u) seg[o] = (uint16_t)(i0 + 3);
+                }
             }
         }
-    }
-    __syncwarp();
+        __syncwarp();
 
-    // (3) exact score, two survivors per thread; corners (s >= minTh) compacted in place
-    int n_c = 0;
-    for (int k0 = 0; k0 < n_a; k0 += 64) {
-        const int k = k0 + 2 * lane;
-        const bool va = k < n_a, vb = k + 1 < n_a;
-        const unsigned pr = va ? reinterpret_cast<const uint32_t*>(seg)[k >> 1] : 0u;  // segments start 8-byte aligned
-        const int ia = (int)(pr & 0xffffu), ib = vb ? (int)(pr >> 16) : ia;
-        const int ya = ia >> 8, xa = ia & 0xff, yb = ib >> 8, xb = ib & 0xff;
-        const uint8_t* ca = tile + (ya + 3) * TP + xa + 3;
-        const uint8_t* cb = tile + (yb + 3) * TP + xb + 3;
-        const unsigned cen = (unsigned)ca[0] | ((unsigned)cb[0] << 16);
-        unsigned e[16];
+        // (3) exact score, two survivors per lane; corners (s >= minTh) compacted in place
+        int n_c = 0;
+#pragma unroll 1
+        for (int k0 = 0; k0 < n_a; k0 += 64) {
+            const int k = k0 + 2 * lane;
+            const bool va = k < n_a, vb = k + 1 < n_a;
+            const unsigned pr = va ? reinterpret_cast<const uint32_t*>(seg)[k >> 1] : 0u;  // the list is 16-byte aligned
+            const int ia = (int)(pr & 0xffffu), ib = vb ? (int)(pr >> 16) : ia;
+            const int ya = ia >> 8, xa = ia & 0xff, yb = ib >> 8, xb = ib & 0xff;
+            const uint8_t* ca = tile + (ya + 3) * TP + xa + 3;
+            const uint8_t* cb = tile + (yb + 3) * TP + xb + 3;
+            const unsigned cen = (unsigned)ca[0] | ((unsigned)cb[0] << 16);
+            unsigned e[16];
 #define RING(k_, off_) e[k_] = (unsigned)ca[off_] | ((unsigned)cb[off_] << 16)
-        RING(0, 3 * TP);       RING(1, 3 * TP + 1);   RING(2, 2 * TP + 2);    RING(3, TP + 3);
-        RING(4, 3);            RING(5, -TP + 3);      RING(6, -2 * TP + 2);   RING(7, -3 * TP + 1);
-        RING(8, -3 * TP);      RING(9, -3 * TP - 1);  RING(10, -2 * TP - 2);  RING(11, -TP - 3);
-        RING(12, -3);          RING(13, TP - 3);      RING(14, 2 * TP - 2);   RING(15, 3 * TP - 1);
+            RING(0, 3 * TP);       RING(1, 3 * TP + 1);   RING(2, 2 * TP + 2);    RING(3, TP + 3);
+            RING(4, 3);            RING(5, -TP + 3);      RING(6, -2 * TP + 2);   RING(7, -3 * TP + 1);
+            RING(8, -3 * TP);      RING(9, -3 * TP - 1);  RING(10, -2 * TP - 2);  RING(11, -TP - 3);
+            RING(12, -3);          RING(13, TP - 3);      RING(14, 2 * TP - 2);   RING(15, 3 * TP - 1);
 #undef RING
-        const unsigned s2 = fast_score_x2(e, cen);
-        const int sa = (int)(short)(s2 & 0xffffu), sb = (int)(short)(s2 >> 16);
-        const bool fa = va && sa >= t, fb = vb && sb >= t;
-        if (fa) sc[(ya + 1) * SP + xa + 1] = (uint8_t)sa;
-        if (fb) sc[(yb + 1) * SP + xb + 1] = (uint8_t)sb;
-        const unsigned ba = __ballot_sync(0xffffffffu, fa), bb = __ballot_sync(0xffffffffu, fb);  // also orders the reads above before the writes below
-        int o = n_c + __popc(ba & lt) + __popc(bb & lt);
-        if (fa) seg[o++] = (uint16_t)ia;
-        if (fb) seg[o] = (uint16_t)ib;
-        n_c += __popc(ba) + __popc(bb);
-        __syncwarp();
-    }
-    __syncthreads();   // score map complete
+            const unsigned s2 = fast_score_x2(e, cen);
+            const int sa = (int)(short)(s2 & 0xffffu), sb = (int)(short)(s2 >> 16);
+            const bool fa = va && sa >= t, fb = vb && sb >= t;
+            if (fa) sc[(ya + 1) * SP + xa + 1] = (uint8_t)sa;
+            if (fb) sc[(yb + 1) * SP + xb + 1] = (uint8_t)sb;
+            const unsigned ba = __ballot_sync(full, fa), bb = __ballot_sync(full, fb);  // also orders the reads above before the writes below
+            int o = n_c + __popc(ba & lt) + __popc(bb & lt);
+            if (fa) seg[o++] = (uint16_t)ia;
+            if (fb) seg[o] = (uint16_t)ib;
+            n_c += __popc(ba) + __popc(bb);
+            __syncwarp();
+        }
 
-    // (4) strict local maxima inside the own cell's interior, compacted in place (in order); per-lane
-    // counts per cell in 16-bit fields (cells 0,1 | cells 2,3), reduced once per warp
-    unsigned ca01 = 0, ca23 = 0, cs01 = 0, cs23 = 0;
-    int n_m = 0;
-    for (int k0 = 0; k0 < n_c; k0 += 32) {
-        const int k = k0 + lane;
-        bool mx = false;
-        int i = 0;
-        if (k < n_c) {
-            i = seg[k];
-            const int y = i >> 8, x = i & 0xff;
-            const uint8_t* q = sc + (y + 1) * SP + x + 1;
-            const int s = q[0];
-            const int c = (int)(((unsigned)x * G.wcell_magic) >> 20);
-            const int lx = x - c * w_cell;
-            const int cw = (c == nv - 1) ? iw - c * w_cell : w_cell;
-            const int nb0 = max(q[-SP], q[SP]);
-            const int nbl = max(max(q[-1], q[-SP - 1]), q[SP - 1]);
-            const int nbr = max(max(q[1], q[-SP + 1]), q[SP + 1]);
-            mx = s > nb0 && (lx == 0 || s > nbl) && (lx == cw - 1 || s > nbr);
-            if (mx) {
-                const unsigned inc = 1u << ((c & 1) << 4), incs = s >= ini_th ? inc : 0u;
-                if (c < 2) { ca01 += inc; cs01 += incs; } else { ca23 += inc; cs23 += incs; }
+        // (4) strict local maxima over the 8 neighbours (the zero frame stands for "outside the cell"), compacted in place
+        int n_m = 0, n_ini = 0;
+#pragma unroll 1
+        for (int k0 = 0; k0 < n_c; k0 += 32) {
+            const int k = k0 + lane;
+            bool mx = false;
+            int i = 0, s = 0;
+            if (k < n_c) {
+                i = seg[k];
+                const uint8_t* q = sc + ((i >> 8) + 1) * SP + (i & 0xff) + 1;
+                s = q[0];
+                const unsigned r0 = __vimax3_u32(q[-SP - 1], q[-SP], q[-SP + 1]), r1 = __vimax3_u32(q[-1], q[1], q[SP - 1]);
+                mx = (unsigned)s > __vimax3_u32(r0, r1, max((unsigned)q[SP], (unsigned)q[SP + 1]));
             }
+            const unsigned bm = __ballot_sync(full, mx), bi = __ballot_sync(full, mx && s >= ini_th);   // also orders this iteration's reads before the writes
+            if (mx) seg[n_m + __popc(bm & lt)] = (uint16_t)i;
+            n_m += __popc(bm);
+            n_ini += __popc(bi);
+            __syncwarp();
         }
-        const unsigned bm = __ballot_sync(0xffffffffu, mx);   // also orders this iteration's reads before the writes
-        if (mx) seg[n_m + __popc(bm & lt)] = (uint16_t)i;
-        n_m += __popc(bm);
-        __syncwarp();
-    }
-#pragma unroll
-    for (int o = 16; o; o >>= 1) {
-        ca01 += __shfl_xor_sync(0xffffffffu, ca01, o); ca23 += __shfl_xor_sync(0xffffffffu, ca23, o);
-        cs01 += __shfl_xor_sync(0xffffffffu, cs01, o); cs23 += __shfl_xor_sync(0xffffffffu, cs23, o);
-    }
-    if (lane < ORB_FAST_G) {
-        const unsigned a = lane < 2 ? ca01 : ca23, st = lane < 2 ? cs01 : cs23;
-        const int sh = (lane & 1) << 4;
-        s_wc[warp][lane] = (int)(((a >> sh) & 0xffffu) | (((st >> sh) & 0xffffu) << 16));
-    }
-    __syncthreads();
 
-    // (5) threshold per cell (reference :843-850), offsets of this warp's segment, ordered write.
-    // lane = 4 * w' + c holds the counts of warp w' for cell c (FAST_WARPS * ORB_FAST_G == 32)
-    int tot = s_wc[lane >> 2][lane & 3];
-    int before = (lane >> 2) < warp ? tot : 0;
-#pragma unroll
-    for (int o = 4; o < 32; o <<= 1) {
-        tot += __shfl_xor_sync(0xffffffffu, tot, o);
-        before += __shfl_xor_sync(0xffffffffu, before, o);
-    }
-    const bool use_ini = (tot >> 16) > 0;
-    if (warp == 0 && lane < nv) out_cnt[lane] = use_ini ? (tot >> 16) : (tot & 0xffff);
-    const int my_base = use_ini ? (before >> 16) : (before & 0xffff), my_th = use_ini ? ini_th : 0;
-    int base_c[ORB_FAST_G], th_c[ORB_FAST_G];
-#pragma unroll
-    for (int c = 0; c < ORB_FAST_G; ++c) {
-        base_c[c] = __shfl_sync(0xffffffffu, my_base, c);
-        th_c[c] = __shfl_sync(0xffffffffu, my_th, c);
-    }
-    const int ky0 = 3 + ci * G.h_cell, kx00 = 3 + cj0 * w_cell;
-    uint32_t* out0 = stage + (size_t)b * P.stage_per_image + G.stage_off + (size_t)cell0 * G.cell_cap;
-    for (int k0 = 0; k0 < n_m; k0 += 32) {
-        const int k = k0 + lane;
-        int c = -1, s = 0, y = 0, x = 0;
-        if (k < n_m) {
-            const int i = seg[k];
-            y = i >> 8; x = i & 0xff;
-            s = sc[(y + 1) * SP + x + 1];
-            c = (int)(((unsigned)x * G.wcell_magic) >> 20);
-        }
-#pragma unroll
-        for (int cc = 0; cc < ORB_FAST_G; ++cc) {
-            const bool mine = c == cc && s >= th_c[cc];
-            const unsigned bm = __ballot_sync(0xffffffffu, mine);
-            if (mine) out0[cc * G.cell_cap + base_c[cc] + __popc(bm & lt)] = ((uint32_t)s << 24) | ((uint32_t)(y + ky0) << 12) | (uint32_t)(x + kx00);
-            base_c[cc] += __popc(bm);
+        // (5) threshold of the cell (reference :843-850), ordered write
+        const int th_sel = n_ini > 0 ? ini_th : 0;
+        if (lane == 0) *out_cnt = n_ini > 0 ? n_ini : n_m;
+        const int ky0 = 3 + ci * G.h_cell, kx0 = 3 + cj * G.w_cell;
+        uint32_t* out0 = stage + (size_t)b * P.stage_per_image + G.stage_off + (size_t)c * G.cell_cap;
+        int n_out = 0;
+#pragma unroll 1
+        for (int k0 = 0; k0 < n_m; k0 += 32) {
+            const int k = k0 + lane;
+            bool keep = false;
+            uint32_t rec = 0;
+            if (k < n_m) {
+                const int i = seg[k], y = i >> 8, x = i & 0xff;
+                const int s = sc[(y + 1) * SP + x + 1];
+                keep = s >= th_sel;
+                rec = ((uint32_t)s << 24) | ((uint32_t)(y + ky0) << 12) | (uint32_t)(x + kx0);
+            }
+            const unsigned bk = __ballot_sync(full, keep);
+            if (keep) out0[n_out + __popc(bk & lt)] = rec;
+            n_out += __popc(bk);
         }
     }
 }
@@ -597,37 +556,32 @@ void launch_resize_untiled(cudaStream_t s, uint8_t* pyr, const LevelGeom& src, c
     dim3 block(64, 4), grid((dst.w + 255) / 256, (dst.h + 4 * RESIZE_ROWS - 1) / (4 * RESIZE_ROWS), batch);
     k_resize_level<<<grid, block, 0, s>>>(pyr, src, dst);
 }
-// Tile pitch variant: 192 bytes covers w_cell <= 39 (every level with >= 4 cell columns), 272 the rest (w_cell <= 59).
-static int fast_tile_pitch(const Plan& P) {
-    int wc = 0;
-    for (int l = 0; l < P.nlevels; ++l) if (P.lv[l].n_cols > 0) wc = max(wc, P.lv[l].w_cell);
-    return (ORB_FAST_G * wc + 6 + 15 + 15 <= 192 + 15) && (ORB_FAST_G * wc + 2 + 3 <= 160 + 3) ? 192 : 272;
-}
-static void fast_smem(const Plan& P, int tp, int* tile_bytes, int* score_bytes, int* total) {
-    int mh = 0, mv = 0;
+// Per-warp shared-memory layout of k_fast_cells for the largest cell of any level.
+static bool fast_smem(const Plan& P, int* sp, int* warp_bytes, int* score_off, int* list_off) {
+    int mh = 0, mw = 0;
     for (int l = 0; l < P.nlevels; ++l) {
         const LevelGeom& G = P.lv[l];
         if (G.n_cols == 0) continue;
-        mh = max(mh, G.h_cell);
-        // 4-pixel words per strip row (+2 for alignment) x rows, rounded up per warp, 4 entries each
-        mv = max(mv, 4 * ((ORB_FAST_G * G.w_cell / 4 + 2) * G.h_cell + FAST_WARPS));
+        mh = max(mh, G.h_cell); mw = max(mw, G.w_cell);
     }
-    *tile_bytes = tp * (mh + 6);
-    *score_bytes = (tp - 32) * (mh + 2);
-    *total = *tile_bytes + *score_bytes + 2 * mv + 16;
+    if (mw > 59 || mh > 59) return false;       // cannot happen: a cell is ceil(window / floor(window / 30)) <= 59 pixels
+    *sp = mw + 2 <= 48 ? 48 : 64;               // score pitch: interior + zero frame
+    *score_off = FC_TP * (mh + 6);
+    *list_off = *score_off + *sp * (mh + 2);
+    *warp_bytes = (*list_off + 2 * mw * mh + 4 + 15) & ~15;
+    return true;
 }
 cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch) {
-    const int tp = fast_tile_pitch(P);
-    int tb, sb, tot;
-    fast_smem(P, tp, &tb, &sb, &tot);
-    if (tot > 200 * 1024) return cudaErrorInvalidConfiguration;
-    auto kern = tp == 192 ? k_fast_cells<192> : k_fast_cells<272>;
+    int sp, wb, so, lo;
+    if (!fast_smem(P, &sp, &wb, &so, &lo)) return cudaErrorInvalidConfiguration;
+    const int tot = wb * FC_WARPS;
+    auto kern = sp == 48 ? k_fast_cells<48> : k_fast_cells<64>;
     if (tot > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tot);
         if (e != cudaSuccess) return e;
     }
-    dim3 grid(P.total_groups, batch);
-    kern<<<grid, FAST_THREADS, tot, s>>>(pyr, cell_cnt, stage, P, tb, sb);
+    dim3 grid((P.total_cells + FC_WARPS * FC_CELLS - 1) / (FC_WARPS * FC_CELLS), batch);
+    kern<<<grid, FC_WARPS * 32, tot, s>>>(pyr, cell_cnt, stage, P, wb, so, lo);
     return cudaSuccess;
 }
 void launch_orient_describe(cudaStream_t s, const uint8_t* pyr, const uint8_t* blur, const uint32_t* lvl_kp, const int* lvl_cnt,

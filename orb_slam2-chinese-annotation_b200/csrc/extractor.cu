@@ -97,7 +97,7 @@ int build_plan(const orb_extractor& e, int w, int h, Plan& P, Needs& need, std::
     P.nlevels = e.nlevels; P.w = w; P.h = h; P.ini_th = e.ini_th; P.min_th = e.min_th;
     for (int v = 0; v < 16; ++v) P.umax[v] = e.umax[v];
     size_t off = 0, stage = 0, tbytes = 0;
-    int cells = 0, tiles = 0, kp = 0, ncap_max = 0, groups = 0;
+    int cells = 0, tiles = 0, kp = 0, ncap_max = 0;
     if (tabs) tabs->assign(e.nlevels, HostTables());
     for (int l = 0; l < e.nlevels; ++l) {
         LevelGeom& G = P.lv[l];
@@ -132,12 +132,7 @@ int build_plan(const orb_extractor& e, int w, int h, Plan& P, Needs& need, std::
         } else {  // level too small for a single cell: the reference's loops do not execute
             G.n_cols = G.n_rows = 0; G.w_cell = G.h_cell = 1; G.cell_cap = 0; G.n_ini = 1; G.h_x = 1.f; G.node_cap = 1;
         }
-        G.n_grp_x = (G.n_cols + ORB_FAST_G - 1) / ORB_FAST_G;
-        G.grp_off = groups;
-        G.grp_magic = (1u << 20) / (unsigned)std::max(G.n_grp_x, 1) + 1u;   // exact for q < 2^20 / n_grp_x (q < 4096 * 4096 / 900)
-        G.wcell_magic = (1u << 20) / (unsigned)G.w_cell + 1u;                 // exact for x < 2^20 / w_cell (x < 256)
-        if ((long long)G.n_grp_x * G.n_rows * G.n_grp_x >= (1 << 20)) return ORB_ERR_BAD_ARG;
-        groups += G.n_grp_x * G.n_rows;
+        G.ncols_magic = (unsigned)((1ull << 32) / (unsigned)std::max(G.n_cols, 1)) + 1u;   // exact for c < 2^32 / n_cols
         G.tiles_x = (G.w + 127) / 128;
         G.tiles_y = (G.h + 63) / 64;
         cells += G.n_cols * G.n_rows;
@@ -157,7 +152,7 @@ int build_plan(const orb_extractor& e, int w, int h, Plan& P, Needs& need, std::
             }
         }
     }
-    P.total_cells = cells; P.total_tiles = tiles; P.total_groups = groups; P.kp_cap = kp; P.stage_per_image = stage;
+    P.total_cells = cells; P.total_tiles = tiles; P.kp_cap = kp; P.stage_per_image = stage;
     need.pyr_bytes = off; need.cells = (size_t)cells; need.stage = stage; need.kp_cap = kp;
     need.node_cap_max = ncap_max; need.tables_bytes = tbytes + 256;
     return ORB_OK;

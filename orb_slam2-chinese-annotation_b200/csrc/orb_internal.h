@@ -16,7 +16,6 @@
 #define ORB_HALF_PATCH 15  // HALF_PATCH_SIZE  (:73)
 #define ORB_PATCH 31       // PATCH_SIZE       (:72)
 #define ORB_WIN 16         // minBorderX = EDGE_THRESHOLD - 3 (:797)
-#define ORB_FAST_G 4       // cells per CTA of the FAST kernel
 
 // Candidate / keypoint packing used between FAST, the quadtree and the descriptor stage:
 // bits 0..11 x, 12..23 y (window-relative level coordinates), 24..31 FAST score (<= 254).
@@ -34,8 +33,7 @@ struct LevelGeom {
     int max_bx, max_by;         // maxBorderX, maxBorderY
     int cell_off;               // first cell of this level in the per-image cell arrays
     int cell_cap;               // staging slots per cell
-    int n_grp_x, grp_off;       // FAST cell groups (ORB_FAST_G consecutive cells of a cell row) per cell row / first group of the level
-    unsigned grp_magic, wcell_magic;  // q / n_grp_x == (q * grp_magic) >> 20, x / w_cell == (x * wcell_magic) >> 20 for the ranges used
+    unsigned ncols_magic;       // c / n_cols == __umulhi(c, ncols_magic) for every cell index of the level
     unsigned long long stage_off;   // first staging slot (u32 units) of this level within one image
     // quadtree (reference :558-782)
     int win_w, win_h;           // maxBorderX-minBorderX, maxBorderY-minBorderY
@@ -58,7 +56,7 @@ struct LevelGeom {
 
 struct Plan {
     int nlevels, w, h;
-    int total_cells, total_tiles, kp_cap, total_groups;
+    int total_cells, total_tiles, kp_cap;
     unsigned long long stage_per_image;   // u32 slots
     unsigned long long pyr_bytes_per_batch_unit;  // unused by kernels
     int ini_th, min_th;

@@ -395,35 +395,43 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     return a;
 }
 
-#define OD_WARPS 8
-#define OD_KP_PER_CTA 32   // keypoint slots per CTA: each warp walks OD_KP_PER_CTA / OD_WARPS of them
-#define OD_DW 11           // words per staged row of the 37 x 37 blurred patch (37 + 3 bytes of alignment slack)
-#define OD_RW 9            // words per staged row of the 31 x 31 raw patch
-// pattern copy in global memory: the CTA prologue reads it coalesced (constant memory would
-// serialise the per-thread indices)
+#define OD_WARPS 4         // warps per CTA (independent of each other after the prologue)
+#define OD_KPW 8           // keypoints walked by one warp: the patches of keypoint j + 1 are in flight while j is described
+// Both patches of a keypoint arrive by TMA (one cp.async.bulk.tensor per patch, issued by lane 0, SASS UTMALDG): the innermost box
+// coordinate of a u8 tensor must be a multiple of 16 bytes (tools/tma_align_test.cu: anything else is an illegal instruction), so
+// the boxes are wider than the patches and start at the 16-byte boundary below the patch.
+#define OD_BB_W 64         // blurred patch: 37 x 37 around the keypoint (rBRIEF reaches |13| rotated, < 18.4) + up to 15 bytes of alignment
+#define OD_BB_H 37
+#define OD_RB_W 48         // raw patch: 31 x 31 (IC_Angle disc) + up to 15 bytes of alignment
+#define OD_RB_H 31
+#define OD_BLUR_BYTES 2432 // 64 * 37 rounded up to the 128-byte destination alignment of TMA
+#define OD_RAW_BYTES 1536  // 48 * 31 rounded up (exactly 384 words: 12 per lane)
+#define OD_BUF_BYTES (OD_BLUR_BYTES + OD_RAW_BYTES)
+// pattern copy in global memory: every lane reads the 32 bytes of ITS descriptor byte (16 points) once per warp
 __device__ __align__(16) signed char g_pattern[1024] = {
 #include "../../include/orb_pattern_31.inc"
 };
 
-// Weights of the intensity-centroid moments for the raw patch as it is fetched: 31 rows x OD_RW aligned words, the patch starting
-// at byte rsh = 0..3 of the first word.  Entry [rsh][row * OD_RW + word] = (x: the four u = column - 15 as signed bytes, 0 outside
-// the radius-15 disc (|u| <= umax[|v|]); y: 1 inside the disc, 0 outside).  m10 += dp4a(pixels, x); m01 += v * dp4a(pixels, y).
-// Filled by orb_upload_moment_table() when an extractor is created (umax comes from the reference's table code, :466-489).
-__device__ uint2 g_moment_w[4 * 32 * OD_RW];
+// Weights of the intensity-centroid moments for the raw box as it is staged: 31 rows x 12 aligned words, the patch starting at byte
+// rsh = 0..15 of a row.  Entry [rsh][row * 12 + word] = (x: the four u = column - 15 as signed bytes, 0 outside the radius-15 disc
+// (|u| <= umax[|v|]); y: v = row - 15 inside the disc, 0 outside).  m10 += dp4a(pixels, x); m01 += dp4a(pixels, y): exact integers,
+// any summation order.  Filled by orb_upload_moment_table() when an extractor is created (umax comes from the reference's table
+// code, :466-489).
+__device__ uint2 g_moment_w[16 * 384];
 cudaError_t orb_upload_moment_table(const int* umax) {
-    uint2 h[4 * 32 * OD_RW];   // same contents from every caller (the disc is a constant of the algorithm)
-    for (int rsh = 0; rsh < 4; ++rsh)
-        for (int i = 0; i < 32 * OD_RW; ++i) {
-            const int r = i / OD_RW, c = i % OD_RW, v = r - ORB_HALF_PATCH;
-            uint32_t wu = 0, wm = 0;
-            for (int j = 0; j < 4 && r < 31; ++j) {
+    static uint2 h[16 * 384];   // same contents from every caller (the disc is a constant of the algorithm)
+    for (int rsh = 0; rsh < 16; ++rsh)
+        for (int i = 0; i < 384; ++i) {
+            const int r = i / 12, c = i % 12, v = r - ORB_HALF_PATCH;
+            uint32_t wu = 0, wv = 0;
+            for (int j = 0; j < 4 && r < OD_RB_H; ++j) {
                 const int u = 4 * c + j - rsh - ORB_HALF_PATCH;
                 if (u >= -ORB_HALF_PATCH && u <= ORB_HALF_PATCH && (u < 0 ? -u : u) <= umax[v < 0 ? -v : v]) {
                     wu |= (uint32_t)(uint8_t)(signed char)u << (8 * j);
-                    wm |= 1u << (8 * j);
+                    wv |= (uint32_t)(uint8_t)(signed char)v << (8 * j);
                 }
             }
-            h[rsh * 32 * OD_RW + i] = make_uint2(wu, wm);
+            h[rsh * 384 + i] = make_uint2(wu, wv);
         }
     return cudaMemcpyToSymbol(g_moment_w, h, sizeof(h));
 }
@@ -432,80 +440,114 @@ __device__ __forceinline__ int dp4a_u8_s8(unsigned px, unsigned w, int acc) {
     asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(px), "r"(w), "r"(acc));
     return d;
 }
+// mbarrier / TMA PTX (same forms as pyramid_kernels.cu)
+__device__ __forceinline__ unsigned od_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void od_mbar_init(uint64_t* bar) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(od_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void od_mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(od_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void od_mbar_wait(uint64_t* bar, unsigned phase) {
+    unsigned ok;
+    do {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(ok) : "r"(od_smem_u32(bar)), "r"(phase) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ unsigned od_lds_u8(unsigned addr) {
+    unsigned v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void od_tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int x, int y, int z) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(od_smem_u32(smem_dst)), "l"(map), "r"(od_smem_u32(bar)), "r"(x), "r"(y), "r"(z) : "memory");
+}
 
-// Both patches are fetched with aligned 32-bit loads (all of them in flight together) and keep
-// the level's word alignment in shared memory; the rBRIEF gathers and the moment columns then
-// read bytes from shared memory only.
-__global__ void __launch_bounds__(OD_WARPS * 32, 4)
-k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur, const uint32_t* __restrict__ lvl_kp,
+// One warp walks OD_KPW consecutive keypoints of the image's final (level-concatenated) order, double-buffered: lane 0 issues the
+// two TMA boxes of keypoint j + 1, then the warp waits for keypoint j's mbarrier and computes on shared memory only.  The 16 pattern
+// points of a lane's descriptor byte live in registers as floats.
+__global__ void __launch_bounds__(OD_WARPS * 32, 7)
+k_orient_describe(const __grid_constant__ TmaMaps tm_raw, const __grid_constant__ TmaMaps tm_blur, const uint32_t* __restrict__ lvl_kp,
                   const int* __restrict__ lvl_cnt, orb_keypoint* __restrict__ kps, uint8_t* __restrict__ desc,
-                  int* __restrict__ counts, const Plan P) {
-    __shared__ float2 s_pat[512];
-    __shared__ uint32_t s_desc[OD_WARPS][37 * OD_DW];
-    __shared__ int s_cnt[ORB_MAX_LEVELS], s_pre[ORB_MAX_LEVELS];
+                  int* __restrict__ counts, const Plan P, const int b0) {
+    extern __shared__ __align__(128) uint8_t od_smem[];
+    __shared__ uint64_t s_bar[OD_WARPS][2];
+    __shared__ int s_pre[ORB_MAX_LEVELS + 1];
     const int b = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int* cnt = lvl_cnt + b * ORB_MAX_LEVELS;
-    for (int i = threadIdx.x; i < 512; i += OD_WARPS * 32) {  // point i = byte (i / 16), sample (i % 16); stored [sample][byte]: conflict-free
-        const char2 p = reinterpret_cast<const char2*>(g_pattern)[i];
-        s_pat[(i & 15) * 32 + (i >> 4)] = make_float2((float)p.x, (float)p.y);
-    }
     if (threadIdx.x == 0) {
+        const int* cnt = lvl_cnt + b * ORB_MAX_LEVELS;
         int t = 0;
-        for (int l = 0; l < P.nlevels; ++l) { const int c = cnt[l]; s_cnt[l] = c; s_pre[l] = t; t += c; }
+        for (int l = 0; l < P.nlevels; ++l) { s_pre[l] = t; t += cnt[l]; }
+        for (int l = P.nlevels; l <= ORB_MAX_LEVELS; ++l) s_pre[l] = t;
         if (blockIdx.x == 0) counts[b] = t;
     }
+    if (lane == 0) {
+        od_mbar_init(&s_bar[warp][0]); od_mbar_init(&s_bar[warp][1]);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");   // make the init visible to the async proxy
+    }
     __syncthreads();
+    const int o0 = (blockIdx.x * OD_WARPS + warp) * OD_KPW;
+    const int n = min(OD_KPW, s_pre[ORB_MAX_LEVELS] - o0);
+    if (n <= 0) return;
 
-    uint32_t* sd = s_desc[warp];
+    // lane j < n looks up keypoint o0 + j: level, quadtree slot, packed key
+    uint32_t my_key = 0;
+    int my_l = 0;
+    if (lane < n) {
+        const int o = o0 + lane;
+        while (my_l + 1 < P.nlevels && o >= s_pre[my_l + 1]) ++my_l;
+        my_key = lvl_kp[(size_t)b * P.kp_cap + P.lv[my_l].kp_off + (o - s_pre[my_l])];
+    }
+    // the 16 pattern points of this lane's descriptor byte
+    float ptx[16], pty[16];
+    {
+        const uint4 q0 = reinterpret_cast<const uint4*>(g_pattern)[2 * lane], q1 = reinterpret_cast<const uint4*>(g_pattern)[2 * lane + 1];
+        const unsigned w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            ptx[2 * i] = (float)(signed char)(w[i] & 0xff);            pty[2 * i] = (float)(signed char)((w[i] >> 8) & 0xff);
+            ptx[2 * i + 1] = (float)(signed char)((w[i] >> 16) & 0xff); pty[2 * i + 1] = (float)(signed char)(w[i] >> 24);
+        }
+    }
+    uint8_t* const wbuf = od_smem + warp * (2 * OD_BUF_BYTES);
+    const int img = b0 + b;
+
+    auto prefetch = [&](int j) {
+        const uint32_t key = __shfl_sync(0xffffffffu, my_key, j);
+        const int l = __shfl_sync(0xffffffffu, my_l, j);
+        if (lane == 0) {
+            const int px = ORB_KEY_X(key) + ORB_WIN, py = ORB_KEY_Y(key) + ORB_WIN;
+            uint8_t* buf = wbuf + (j & 1) * OD_BUF_BYTES;
+            uint64_t* bar = &s_bar[warp][j & 1];
+            od_mbar_expect_tx(bar, OD_BB_W * OD_BB_H + OD_RB_W * OD_RB_H);
+            od_tma_load_3d(buf, &tm_blur.lv[l], bar, (px - 18) & ~15, py - 18, img);
+            od_tma_load_3d(buf + OD_BLUR_BYTES, &tm_raw.lv[l], bar, (px - ORB_HALF_PATCH) & ~15, py - ORB_HALF_PATCH, img);
+        }
+    };
+    prefetch(0);
 #pragma unroll 1
-    for (int it = 0; it < OD_KP_PER_CTA / OD_WARPS; ++it) {
-        const int slot = blockIdx.x * OD_KP_PER_CTA + it * OD_WARPS + warp;
-        if (slot >= P.kp_cap) break;
-        int l = 0;
-        while (l + 1 < P.nlevels && slot >= P.lv[l + 1].kp_off) ++l;
-        const LevelGeom& G = P.lv[l];
-        const int idx = slot - G.kp_off;
-        if (idx >= s_cnt[l]) continue;
-        const int out_idx = idx + s_pre[l];
-
-        const uint32_t key = lvl_kp[(size_t)b * P.kp_cap + slot];
+    for (int j = 0; j < n; ++j) {
+        if (j + 1 < n) prefetch(j + 1);   // its buffer was last read by keypoint j - 1, which ended with __syncwarp
+        const uint32_t key = __shfl_sync(0xffffffffu, my_key, j);
+        const int l = __shfl_sync(0xffffffffu, my_l, j);
         const int px = ORB_KEY_X(key) + ORB_WIN, py = ORB_KEY_Y(key) + ORB_WIN;
-        const int pitch = G.pitch;
-        const size_t img_off = G.off + (size_t)b * G.img_stride;
-        // rows are 64-byte aligned, so the alignment of a patch row is that of its first column
-        const int dsh = (px - 18) & 3, rsh = (px - 15) & 3;
-        const uint8_t* dbase = blur + img_off + (size_t)(py - 18) * pitch + (px - 18 - dsh);
-        const uint8_t* rbase = pyr + img_off + (size_t)(py - 15) * pitch + (px - 15 - rsh);
-        __syncwarp();  // the previous keypoint's readers are done with sd / sr
-        uint32_t vr[9], vd[13];
-#pragma unroll
-        for (int k = 0; k < 9; ++k) {
-            const int i = k * 32 + lane;
-            const int r = (i * 57) >> 9, c = i - r * OD_RW;   // i / 9 for i < 288
-            vr[k] = i < 31 * OD_RW ? __ldg(reinterpret_cast<const uint32_t*>(rbase + r * pitch) + c) : 0u;
-        }
-#pragma unroll
-        for (int k = 0; k < 13; ++k) {
-            const int i = k * 32 + lane;
-            const int r = (i * 745) >> 13, c = i - r * OD_DW;  // i / 11 for i < 416
-            vd[k] = i < 37 * OD_DW ? __ldg(reinterpret_cast<const uint32_t*>(dbase + r * pitch) + c) : 0u;
-        }
-#pragma unroll
-        for (int k = 0; k < 13; ++k) { const int i = k * 32 + lane; if (i < 37 * OD_DW) sd[i] = vd[k]; }
-        __syncwarp();
+        const uint8_t* buf = wbuf + (j & 1) * OD_BUF_BYTES;
+        od_mbar_wait(&s_bar[warp][j & 1], (unsigned)((j >> 1) & 1));
 
-        // IC_Angle (reference :77-113): integer moments over the radius-15 disc, straight from the fetched words (exact integers,
-        // any summation order): per word one byte dot product with the u weights and one with the disc mask
+        // IC_Angle (reference :77-113): integer moments over the radius-15 disc, two byte dot products per staged word
         int m10 = 0, m01 = 0;
         {
-            const uint2* wt = g_moment_w + rsh * (32 * OD_RW) + lane;
+            const uint32_t* rw = reinterpret_cast<const uint32_t*>(buf + OD_BLUR_BYTES) + lane;
+            const uint2* wt = g_moment_w + ((px - ORB_HALF_PATCH) & 15) * 384 + lane;
 #pragma unroll
-            for (int k = 0; k < 9; ++k) {
+            for (int k = 0; k < 12; ++k) {
                 const uint2 wq = __ldg(wt + k * 32);
-                const int v = (((k * 32 + lane) * 57) >> 9) - ORB_HALF_PATCH;
-                m10 = dp4a_u8_s8(vr[k], wq.x, m10);
-                m01 += v * dp4a_u8_s8(vr[k], wq.y, 0);
+                const unsigned v = rw[k * 32];
+                m10 = dp4a_u8_s8(v, wq.x, m10);
+                m01 = dp4a_u8_s8(v, wq.y, m01);
             }
         }
 #pragma unroll
@@ -515,24 +557,29 @@ k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ b
         }
         const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-        // rBRIEF (reference :119-164): lane = descriptor byte, 8 comparisons on the staged patch
+        // rBRIEF (reference :119-164): lane = descriptor byte, 8 comparisons on the staged blurred patch.  cvRound of the rotated
+        // coordinates as "add 1.5 * 2^23, read the mantissa" (round half to even like cvRound's cvtss2si / F2I.RN; |value| < 2^22)
         const float rad = __fmul_rn(angle, 0.017453292519943295f);  // factorPI = (float)(CV_PI/180.f)
         float a, bsin;
         orb_sincosf(rad, &bsin, &a);
-        const uint8_t* spc = reinterpret_cast<const uint8_t*>(sd) + 18 * (OD_DW * 4) + 18 + dsh;
+        const float magic = 12582912.0f;
+        // byte (row r, column q) of the patch sits at 64 * (18 + r) + 18 + dsh + q; the two mantissa offsets 0x4B400000 are folded
+        // into the base (32-bit shared-window address arithmetic, modulo 2^32)
+        const unsigned spc = od_smem_u32(buf) + 18u * OD_BB_W + 18u + (unsigned)((px - 18) & 15) - 0x4B400000u * (unsigned)(OD_BB_W + 1);
         int val = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            const float2 p0 = s_pat[(2 * k) * 32 + lane], p1 = s_pat[(2 * k + 1) * 32 + lane];
-            const int r0 = __float2int_rn(__fmaf_rn(p0.x, bsin, __fmul_rn(p0.y, a)));
-            const int q0 = __float2int_rn(__fmaf_rn(p0.x, a, -__fmul_rn(p0.y, bsin)));
-            const int r1 = __float2int_rn(__fmaf_rn(p1.x, bsin, __fmul_rn(p1.y, a)));
-            const int q1 = __float2int_rn(__fmaf_rn(p1.x, a, -__fmul_rn(p1.y, bsin)));
-            const int t0 = spc[r0 * (OD_DW * 4) + q0], t1 = spc[r1 * (OD_DW * 4) + q1];
+            const unsigned r0 = __float_as_uint(__fadd_rn(__fmaf_rn(ptx[2 * k], bsin, __fmul_rn(pty[2 * k], a)), magic));
+            const unsigned q0 = __float_as_uint(__fadd_rn(__fmaf_rn(ptx[2 * k], a, -__fmul_rn(pty[2 * k], bsin)), magic));
+            const unsigned r1 = __float_as_uint(__fadd_rn(__fmaf_rn(ptx[2 * k + 1], bsin, __fmul_rn(pty[2 * k + 1], a)), magic));
+            const unsigned q1 = __float_as_uint(__fadd_rn(__fmaf_rn(ptx[2 * k + 1], a, -__fmul_rn(pty[2 * k + 1], bsin)), magic));
+            const unsigned t0 = od_lds_u8(spc + r0 * OD_BB_W + q0), t1 = od_lds_u8(spc + r1 * OD_BB_W + q1);
             val |= (t0 < t1) << k;
         }
+        const int out_idx = o0 + j;
         desc[((size_t)b * P.kp_cap + out_idx) * 32 + lane] = (uint8_t)val;
         if (lane < 7) {  // one 4-byte field of the 28-byte record per lane
+            const LevelGeom& G = P.lv[l];
             float fx = (float)px, fy = (float)py;
             if (l != 0) { fx = __fmul_rn(fx, G.sf); fy = __fmul_rn(fy, G.sf); }
             uint32_t f;
@@ -547,6 +594,7 @@ k_orient_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ b
             }
             reinterpret_cast<uint32_t*>(kps + (size_t)b * P.kp_cap + out_idx)[lane] = f;
         }
+        __syncwarp();   // every lane is done with this buffer before lane 0 re-arms it
     }
 }
 
@@ -584,10 +632,14 @@ cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint3
     kern<<<grid, FC_WARPS * 32, tot, s>>>(pyr, cell_cnt, stage, P, wb, so, lo);
     return cudaSuccess;
 }
-void launch_orient_describe(cudaStream_t s, const uint8_t* pyr, const uint8_t* blur, const uint32_t* lvl_kp, const int* lvl_cnt,
-                            orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int batch) {
-    dim3 grid((P.kp_cap + OD_KP_PER_CTA - 1) / OD_KP_PER_CTA, batch);
-    k_orient_describe<<<grid, OD_WARPS * 32, 0, s>>>(pyr, blur, lvl_kp, lvl_cnt, kps, desc, counts, P);
+cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const TmaMaps& tm_blur, const uint32_t* lvl_kp, const int* lvl_cnt,
+                                   orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int b0, int batch) {
+    const int smem = OD_WARPS * 2 * OD_BUF_BYTES;
+    cudaError_t e = cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
+    if (e != cudaSuccess) return e;
+    dim3 grid((P.kp_cap + OD_WARPS * OD_KPW - 1) / (OD_WARPS * OD_KPW), batch);
+    k_orient_describe<<<grid, OD_WARPS * 32, smem, s>>>(tm_raw, tm_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, b0);
+    return cudaSuccess;
 }
 
 // ------------------------------------------------------------------------------------------

@@ -14,8 +14,8 @@ cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint3
 cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefix, const uint32_t* stage, uint32_t* keys,
                             uint32_t* lvl_kp, int* lvl_cnt, int* lvl_ncand, int* status, const Plan& P, int batch);
 size_t quadtree_smem(int cap, int* p2_out);
-void launch_orient_describe(cudaStream_t s, const uint8_t* pyr, const uint8_t* blur, const uint32_t* lvl_kp, const int* lvl_cnt,
-                            orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int batch);
+cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const TmaMaps& tm_blur, const uint32_t* lvl_kp, const int* lvl_cnt,
+                                   orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int b0, int batch);
 
 static thread_local std::string g_err;
 void orb_set_error(const std::string& s) { g_err = s; }
@@ -191,12 +191,20 @@ int build_tma_maps(orb_extractor* e, int batch) {
         const cuuint64_t strides[2] = {(cuuint64_t)G.pitch, (cuuint64_t)G.img_stride};
         const cuuint32_t estr[3] = {1, 1, 1};
         const cuuint32_t box_blur[3] = {ORB_BLUR_BOXW, ORB_BLUR_BOXH, 1}, box_rz[3] = {ORB_RZ_BOXW, ORB_RZ_BOXH, 1};
+        const cuuint32_t box_od_raw[3] = {ORB_OD_RAW_BOXW, ORB_OD_RAW_BOXH, 1}, box_od_blur[3] = {ORB_OD_BLUR_BOXW, ORB_OD_BLUR_BOXH, 1};
         void* base = e->d_pyr + G.off;
         CUresult r = enc(&e->tm_blur.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box_blur, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r == CUDA_SUCCESS)
             r = enc(&e->tm_resize.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box_rz, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        // the two patches of k_orient_describe: raw level and blurred level (same geometry, other buffer)
+        if (r == CUDA_SUCCESS)
+            r = enc(&e->tm_od_raw.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box_od_raw, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r == CUDA_SUCCESS)
+            r = enc(&e->tm_od_blur.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, e->d_blur + G.off, dims, strides, box_od_blur, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) { orb_set_error("cuTensorMapEncodeTiled failed (code " + std::to_string((int)r) + ")"); return ORB_ERR_CUDA; }
         // the staged source box of k_resize_tma covers scales up to 1.35 (x) and 1.33 (y); anything else takes the untiled kernel
         e->rz_tma[l] = false;
@@ -311,7 +319,7 @@ int run_pipeline(orb_extractor* e, int b0, int batch) {
     if (T) cudaEventRecord(e->ev_stage[4], s);
     {
         ORB_NVTX("orb:orient_describe");
-        launch_orient_describe(s, e->d_pyr, e->d_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, batch);
+        ORB_CUDA(launch_orient_describe(s, e->tm_od_raw, e->tm_od_blur, lvl_kp, lvl_cnt, kps, desc, counts, Q, b0, batch));
         e->launches++;
     }
     if (T) { cudaEventRecord(e->ev_stage[5], s); for (int i = 0; i < 5; ++i) e->stage_valid[i] = true; }

@@ -75,6 +75,10 @@ struct Plan {
 #define ORB_RZ_DH 64
 #define ORB_RZ_BOXW 192
 #define ORB_RZ_BOXH 88
+#define ORB_OD_BLUR_BOXW 64                 // orient + describe: 37 x 37 blurred patch / 31 x 31 raw patch, x rounded down to 16 bytes
+#define ORB_OD_BLUR_BOXH 37
+#define ORB_OD_RAW_BOXW 48
+#define ORB_OD_RAW_BOXH 31
 struct TmaMaps { CUtensorMap lv[ORB_MAX_LEVELS]; };
 
 struct orb_extractor {
@@ -92,6 +96,7 @@ struct orb_extractor {
     int plan_w = -1, plan_h = -1;
     int last_batch = 0;
     TmaMaps tm_blur, tm_resize;     // rebuilt with the plan / batch layout
+    TmaMaps tm_od_raw, tm_od_blur;  // patch boxes of k_orient_describe over d_pyr / d_blur
     bool rz_tma[ORB_MAX_LEVELS] = {false};   // level l is resampled from l-1 by the TMA-staged kernel
 
     // device buffers (sized for max geometry x max_batch)

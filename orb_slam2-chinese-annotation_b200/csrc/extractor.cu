@@ -191,6 +191,7 @@ int build_tma_maps(orb_extractor* e, int batch) {
         const cuuint64_t strides[2] = {(cuuint64_t)G.pitch, (cuuint64_t)G.img_stride};
         const cuuint32_t estr[3] = {1, 1, 1};
         const cuuint32_t box_blur[3] = {ORB_BLUR_BOXW, ORB_BLUR_BOXH, 1}, box_rz[3] = {ORB_RZ_BOXW, ORB_RZ_BOXH, 1};
+        const cuuint32_t box_st_l[3] = {32, 11, 1}, box_st_r[3] = {48, 11, 1};
         const cuuint32_t box_od_raw[3] = {ORB_OD_RAW_BOXW, ORB_OD_RAW_BOXH, 1}, box_od_blur[3] = {ORB_OD_BLUR_BOXW, ORB_OD_BLUR_BOXH, 1};
         void* base = e->d_pyr + G.off;
         CUresult r = enc(&e->tm_blur.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box_blur, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -204,6 +205,13 @@ int build_tma_maps(orb_extractor* e, int batch) {
                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r == CUDA_SUCCESS)
             r = enc(&e->tm_od_blur.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, e->d_blur + G.off, dims, strides, box_od_blur, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        // the SAD windows of k_stereo_refine
+        if (r == CUDA_SUCCESS)
+            r = enc(&e->tm_st_l.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box_st_l, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r == CUDA_SUCCESS)
+            r = enc(&e->tm_st_r.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box_st_r, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) { orb_set_error("cuTensorMapEncodeTiled failed (code " + std::to_string((int)r) + ")"); return ORB_ERR_CUDA; }
         // the staged source box of k_resize_tma covers scales up to 1.35 (x) and 1.33 (y); anything else takes the untiled kernel
@@ -220,7 +228,7 @@ void free_buffers(orb_extractor* e) {
     orb_dev_free(e->d_pyr); orb_dev_free(e->d_blur); orb_dev_free(e->d_cell_cnt); orb_dev_free(e->d_cell_prefix); orb_dev_free(e->d_stage);
     orb_dev_free(e->d_keys); orb_dev_free(e->d_lvl_kp); orb_dev_free(e->d_lvl_cnt); orb_dev_free(e->d_lvl_ncand); orb_dev_free(e->d_kps);
     orb_dev_free(e->d_desc); orb_dev_free(e->d_counts); orb_dev_free(e->d_status); orb_dev_free(e->d_tables); orb_dev_free(e->d_u_right);
-    orb_dev_free(e->d_depth); orb_dev_free(e->d_sad); orb_dev_free(e->d_in); orb_dev_free(e->d_row_start); orb_dev_free(e->d_row_items);
+    orb_dev_free(e->d_depth); orb_dev_free(e->d_sad); orb_dev_free(e->d_st_jobs); orb_dev_free(e->d_in); orb_dev_free(e->d_row_start); orb_dev_free(e->d_row_items);
     if (e->ev_done) cudaEventDestroy(e->ev_done);
     for (int i = 0; i < ORB_N_STAGES + 4; ++i) if (e->ev_stage[i]) cudaEventDestroy(e->ev_stage[i]);
     if (e->h_pin) cudaFreeHost(e->h_pin);
@@ -475,6 +483,7 @@ int orb_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini
     ALLOC(e->d_u_right, (size_t)e->kp_cap_max * B * sizeof(float));
     ALLOC(e->d_depth, (size_t)e->kp_cap_max * B * sizeof(float));
     ALLOC(e->d_sad, (size_t)e->kp_cap_max * B * sizeof(int));
+    ALLOC(e->d_st_jobs, (size_t)e->kp_cap_max * B * sizeof(int2));
     e->row_items_cap = e->kp_cap_max * (2 * (int)std::ceil(2.0f * e->sf[nlevels - 1]) + 3);
     ALLOC(e->d_row_start, B * (ORB_MAX_DIM + 1) * sizeof(int));
     ALLOC(e->d_row_items, B * (size_t)e->row_items_cap * sizeof(int2));

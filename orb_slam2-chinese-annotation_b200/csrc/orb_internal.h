@@ -97,6 +97,7 @@ struct orb_extractor {
     int last_batch = 0;
     TmaMaps tm_blur, tm_resize;     // rebuilt with the plan / batch layout
     TmaMaps tm_od_raw, tm_od_blur;  // patch boxes of k_orient_describe over d_pyr / d_blur
+    TmaMaps tm_st_l, tm_st_r;       // SAD window boxes of k_stereo_refine over d_pyr: 32 x 11 (a left handle's), 48 x 11 (a right handle's)
     bool rz_tma[ORB_MAX_LEVELS] = {false};   // level l is resampled from l-1 by the TMA-staged kernel
 
     // device buffers (sized for max geometry x max_batch)
@@ -123,6 +124,7 @@ struct orb_extractor {
     float* d_u_right = nullptr;     // [batch][kp_cap]
     float* d_depth = nullptr;
     int* d_sad = nullptr;           // [batch][kp_cap] best SAD per left keypoint (-1 none)
+    int2* d_st_jobs = nullptr;      // [batch][kp_cap] refinement jobs between k_stereo_search and k_stereo_refine
     int* d_row_start = nullptr;     // [batch][ORB_MAX_DIM + 1] vRowIndices as CSR
     int2* d_row_items = nullptr;    // [batch][row_items_cap]  (x bits of the right keypoint, index | octave << 24)
     int row_items_cap = 0;

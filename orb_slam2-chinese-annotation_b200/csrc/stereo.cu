@@ -2,8 +2,10 @@
 // two extractor handles.
 //
 //   k_stereo_rows    vRowIndices: right keypoint -> rows floor(y - 2 sf) .. ceil(y + 2 sf)      :527-544
-//   k_stereo_match   per left keypoint (one warp): row-band Hamming search, 11x11 SAD over
-//                    +-5 px on the pyramid level of the left keypoint, parabola sub-pixel fit    :558-689
+//   k_stereo_search  per left keypoint (one warp): row-band Hamming search; writes the refinement job
+//                    (window centres on the left keypoint's pyramid level)                        :558-633
+//   k_stereo_refine  a warp walks 16 left keypoints: both SAD windows of a job arrive by TMA (double-buffered
+//                    across jobs), 11x11 SAD over +-5 px on packed 16-bit lanes, parabola sub-pixel fit  :634-689
 //   k_stereo_median  threshold 1.5 * 1.4 * median(SAD), invalidate outliers                      :690-703
 //
 // The per-row lists are built with atomics (unordered): the reference keeps the first candidate
@@ -84,19 +86,18 @@ k_stereo_rows(const orb_keypoint* __restrict__ kps_r, const int* __restrict__ co
 }
 
 #define SM_WARPS 8
+// Refinement job of one left keypoint: x = su | sv << 16 (window centre on level `oct` of the left image), y = sr | oct << 16 | 1 << 31
+// (centre column in the right image; bit 31 = job valid).  y == 0: no match / rejected before the SAD.
 __global__ void __launch_bounds__(SM_WARPS * 32, 6)   // latency-bound (a chain of dependent loads per keypoint): as many resident warps as fit
-k_stereo_match(const orb_keypoint* __restrict__ kps_l, const uint8_t* __restrict__ desc_l, const int* __restrict__ counts_l,
-               const orb_keypoint* __restrict__ kps_r, const uint8_t* __restrict__ desc_r, const uint8_t* __restrict__ pyr_l,
-               const uint8_t* __restrict__ pyr_r, const int* __restrict__ row_start, const int2* __restrict__ row_items,
-               float* __restrict__ u_right, float* __restrict__ depth, int* __restrict__ sad, const StereoGeom S, const float mbf,
-               const float min_d, const float max_d) {
-    __shared__ int s_l[SM_WARPS][11][12];
-    __shared__ int s_r[SM_WARPS][11][22];
+k_stereo_search(const orb_keypoint* __restrict__ kps_l, const uint8_t* __restrict__ desc_l, const int* __restrict__ counts_l,
+                const uint8_t* __restrict__ desc_r, const int* __restrict__ row_start, const int2* __restrict__ row_items,
+                float* __restrict__ u_right, float* __restrict__ depth, int* __restrict__ sad, int2* __restrict__ jobs, const StereoGeom S,
+                const float min_d, const float max_d) {
     const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int iL = blockIdx.x * SM_WARPS + warp;
     if (iL >= counts_l[b]) return;
     const size_t oL = (size_t)b * S.kp_cap_l + iL;
-    if (lane == 0) { u_right[oL] = -1.0f; depth[oL] = -1.0f; sad[oL] = -1; }
+    if (lane == 0) { u_right[oL] = -1.0f; depth[oL] = -1.0f; sad[oL] = -1; jobs[oL] = make_int2(0, 0); }
     const orb_keypoint kl = kps_l[oL];
     const float uL = kl.x, vL = kl.y;
     const int row = (int)vL;
@@ -133,7 +134,7 @@ k_stereo_match(const orb_keypoint* __restrict__ kps_l, const uint8_t* __restrict
     // the winning lane hands over its candidate's x (keys are unique: they carry the candidate index)
     const float uR0 = __shfl_sync(0xffffffffu, best_x, __ffs(__ballot_sync(0xffffffffu, mine == best)) - 1);
 
-    // sub-pixel refinement by sliding an 11x11 window on the left keypoint's pyramid level
+    // window centres on the left keypoint's pyramid level (reference :620-633)
     const int oct = kl.octave;
     const float isf = S.inv_sf[oct];
     const int su = (int)roundf(__fmul_rn(kl.x, isf)), sv = (int)roundf(__fmul_rn(kl.y, isf)), sr = (int)roundf(__fmul_rn(uR0, isf));
@@ -144,41 +145,157 @@ k_stereo_match(const orb_keypoint* __restrict__ kps_l, const uint8_t* __restrict
     // the reference would throw from cv::Mat::rowRange/colRange on these; they cannot occur for
     // keypoints produced by the extractor (>= 19 px from every level edge)
     if (sv - w < 0 || sv + w >= GL.h || sv + w >= GR.h || su - w < 0 || su + w >= GL.w || sr - L - w < 0 || sr + L + w >= GR.w) return;
-    const uint8_t* PL = pyr_l + GL.off + (size_t)b * GL.img_stride + (size_t)(sv - w) * GL.pitch + (su - w);
-    const uint8_t* PR = pyr_r + GR.off + (size_t)b * GR.img_stride + (size_t)(sv - w) * GR.pitch + (sr - L - w);
-    for (int i = lane; i < 11 * 11; i += 32) { const int y = i / 11, x = i - y * 11; s_l[warp][y][x] = PL[(size_t)y * GL.pitch + x]; }
-    for (int i = lane; i < 11 * 21; i += 32) { const int y = i / 21, x = i - y * 21; s_r[warp][y][x] = PR[(size_t)y * GR.pitch + x]; }
-    __syncwarp();
-    int dist = 0;
-    if (lane < 22) {
-        const int s = lane >> 1, half = lane & 1;  // shift index 0..10 (incR = s - 5)
-        const int cl = s_l[warp][5][5], cr = s_r[warp][5][s + 5];
-        const int y0 = half ? 6 : 0, y1 = half ? 11 : 6;
-        for (int y = y0; y < y1; ++y)
-#pragma unroll
-            for (int x = 0; x < 11; ++x) dist += abs((s_l[warp][y][x] - cl) - (s_r[warp][y][s + x] - cr));
+    if (lane == 0) jobs[oL] = make_int2(su | (sv << 16), sr | (oct << 16) | (int)0x80000000);
+}
+
+#define SR_WARPS 4
+#define SR_KPW 16          // left keypoints walked by one warp
+#define SR_LBOX 384        // left window box: 32 x 11 bytes (11 + up to 15 bytes of TMA alignment), rounded up to 128
+#define SR_RBOX 640        // right window box: 48 x 11 bytes (21 + 15)
+#define SR_BUF (SR_LBOX + SR_RBOX)
+__device__ __forceinline__ unsigned st_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void st_mbar_wait(uint64_t* bar, unsigned phase) {
+    unsigned ok;
+    do {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(ok) : "r"(st_smem_u32(bar)), "r"(phase) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void st_tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int x, int y, int z) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(st_smem_u32(smem_dst)), "l"(map), "r"(st_smem_u32(bar)), "r"(x), "r"(y), "r"(z) : "memory");
+}
+
+// SAD of the mean-offset windows (reference :640-659): dist(s) = sum |(L - cl) - (R(s) - cr_s)| over 11 x 11, s = 0..10.
+// Lane 2 y + par owns window row y and the shifts of parity par: the row's 11 left pixels and 22 right pixels are unpacked once into
+// zero-extended byte pairs (PRMT), every |difference| is one IADD3 (biased so that no borrow crosses the 16-bit lanes), one subtract
+// and one VIMNMX.U16x2; row partials meet in shared memory.
+__global__ void __launch_bounds__(SR_WARPS * 32)
+k_stereo_refine(const __grid_constant__ TmaMaps tm_l, const __grid_constant__ TmaMaps tm_r, const orb_keypoint* __restrict__ kps_l,
+                const int* __restrict__ counts_l, const int2* __restrict__ jobs, float* __restrict__ u_right, float* __restrict__ depth,
+                int* __restrict__ sad, const StereoGeom S, const float mbf, const float min_d, const float max_d, const int b0) {
+    __shared__ __align__(128) uint8_t s_buf[SR_WARPS][2][SR_BUF];
+    __shared__ int s_part[SR_WARPS][11 * 12];
+    __shared__ uint64_t s_bar[SR_WARPS][2];
+    const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(st_smem_u32(&s_bar[warp][0])) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(st_smem_u32(&s_bar[warp][1])) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    dist += __shfl_xor_sync(0xffffffffu, dist, 1);  // lanes 2s, 2s+1 now hold SAD(s)
-    // first minimum over s = 0..10
-    unsigned key = lane < 22 ? (((unsigned)dist << 8) | (unsigned)(lane >> 1)) : 0xffffffffu;
+    __syncwarp();
+    const int i0 = (blockIdx.x * SR_WARPS + warp) * SR_KPW;
+    const int iL = i0 + lane;
+    int2 job = make_int2(0, 0);
+    float uL = 0.f;
+    if (lane < SR_KPW && iL < counts_l[b]) {
+        job = __ldg(&jobs[(size_t)b * S.kp_cap_l + iL]);
+        uL = kps_l[(size_t)b * S.kp_cap_l + iL].x;
+    }
+    unsigned todo = __ballot_sync(0xffffffffu, job.y < 0);
+    if (todo == 0) return;
+    const int img = b0 + b;
+
+    auto prefetch = [&](int j, int slot) {
+        const int jx = __shfl_sync(0xffffffffu, job.x, j), jy = __shfl_sync(0xffffffffu, job.y, j);
+        if (lane == 0) {
+            const int su = jx & 0xffff, sv = jx >> 16, sr = jy & 0xffff, oct = (jy >> 16) & 0xff;
+            uint64_t* bar = &s_bar[warp][slot];
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(st_smem_u32(bar)), "r"(32 * 11 + 48 * 11) : "memory");
+            st_tma_load_3d(&s_buf[warp][slot][0], &tm_l.lv[oct], bar, (su - 5) & ~15, sv - 5, img);
+            st_tma_load_3d(&s_buf[warp][slot][SR_LBOX], &tm_r.lv[oct], bar, (sr - 10) & ~15, sv - 5, img);
+        }
+    };
+    int cur = __ffs(todo) - 1;
+    todo &= todo - 1;
+    prefetch(cur, 0);
+    int* part = s_part[warp];
+#pragma unroll 1
+    for (int it = 0; cur >= 0; ++it) {
+        const int nxt = todo ? __ffs(todo) - 1 : -1;
+        todo &= todo - 1;
+        if (nxt >= 0) prefetch(nxt, (it + 1) & 1);   // its buffer was last read by job it - 1, which ended with __syncwarp
+        const int jx = __shfl_sync(0xffffffffu, job.x, cur), jy = __shfl_sync(0xffffffffu, job.y, cur);
+        const float uLc = __shfl_sync(0xffffffffu, uL, cur);
+        const int su = jx & 0xffff, sr = jy & 0xffff, oct = (jy >> 16) & 0xff;
+        const uint8_t* bl = &s_buf[warp][it & 1][0];
+        const uint8_t* br = bl + SR_LBOX;
+        const int alL = (su - 5) & 15, alR = (sr - 10) & 15;
+        st_mbar_wait(&s_bar[warp][it & 1], (unsigned)((it >> 1) & 1));
+
+        if (lane < 22) {
+            const int y = lane >> 1, par = lane & 1;
+            unsigned a[6], bp[11];
+            {
+                const uint32_t* lw = reinterpret_cast<const uint32_t*>(bl + y * 32) + (alL >> 2);
+                const unsigned l0 = lw[0], l1 = lw[1], l2 = lw[2], l3 = lw[3], sh = (unsigned)(alL & 3) * 8u;
+                const unsigned A0 = __funnelshift_r(l0, l1, sh), A1 = __funnelshift_r(l1, l2, sh), A2 = __funnelshift_r(l2, l3, sh);
+                a[0] = __byte_perm(A0, 0u, 0x4140); a[1] = __byte_perm(A0, 0u, 0x4342);
+                a[2] = __byte_perm(A1, 0u, 0x4140); a[3] = __byte_perm(A1, 0u, 0x4342);
+                a[4] = __byte_perm(A2, 0u, 0x4140); a[5] = __byte_perm(A2, 0u, 0x4442);   // pixel 10 alone
+            }
+            {
+                const int off = alR + par;
+                const uint32_t* rw = reinterpret_cast<const uint32_t*>(br + y * 48) + (off >> 2);
+                const unsigned sh = (unsigned)(off & 3) * 8u;
+                unsigned r[7];
 #pragma unroll
-    for (int o = 16; o; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
-    const int bs = (int)(key & 0xffu), bestSad = (int)(key >> 8);
-    const int bestinc = bs - L;
-    const float d1 = (float)__shfl_sync(0xffffffffu, dist, max(2 * (bs - 1), 0));
-    const float d2 = (float)bestSad;
-    const float d3 = (float)__shfl_sync(0xffffffffu, dist, min(2 * (bs + 1), 20));
-    if (bestinc == -L || bestinc == L) return;
-    if (lane != 0) return;
-    const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
-    if (deltaR < -1 || deltaR > 1) return;
-    float bestuR = __fmul_rn(S.sf[oct], __fadd_rn(__fadd_rn((float)sr, (float)bestinc), deltaR));
-    float disparity = __fsub_rn(uL, bestuR);
-    if (disparity >= min_d && disparity < max_d) {
-        if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }
-        depth[oL] = __fdiv_rn(mbf, disparity);
-        u_right[oL] = bestuR;
-        sad[oL] = bestSad;
+                for (int i = 0; i < 7; ++i) r[i] = rw[i];
+#pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    const unsigned B = __funnelshift_r(r[i], r[i + 1], sh);   // bytes par + 4 i .. par + 4 i + 3 of the row
+                    bp[2 * i] = __byte_perm(B, 0u, 0x4140);
+                    if (2 * i + 1 < 11) bp[2 * i + 1] = __byte_perm(B, 0u, 0x4342);
+                }
+            }
+            const int cl = bl[5 * 32 + alL + 5];
+            const uint8_t* crp = br + 5 * 48 + alR + 5 + par;
+#pragma unroll
+            for (int sp = 0; sp < 6; ++sp) {   // shift s = 2 sp + par (s = 11 of the odd lanes is not a shift: discarded below)
+                const unsigned bias = (unsigned)(1024 - cl + (int)crp[2 * sp]) * 0x10001u;
+                unsigned acc = 0;
+#pragma unroll
+                for (int j = 0; j < 6; ++j) {
+                    const unsigned u = a[j] + bias - bp[sp + j];          // 1024 + (L - cl) - (R - cr) on both 16-bit lanes
+                    unsigned m = __vmaxu2(u, 0x08000800u - u);            // 1024 + |.|
+                    if (j == 5) m &= 0xffffu;
+                    acc += m;
+                }
+                if (2 * sp + par < 11) part[(2 * sp + par) * 12 + y] = (int)((acc & 0xffffu) + (acc >> 16)) - 11 * 1024;
+            }
+        }
+        __syncwarp();
+        int dist = 0;
+        if (lane < 11) {
+#pragma unroll
+            for (int y = 0; y < 11; ++y) dist += part[lane * 12 + y];
+        }
+        // first minimum over s = 0..10
+        unsigned key = lane < 11 ? (((unsigned)dist << 8) | (unsigned)lane) : 0xffffffffu;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
+        const int L = 5;
+        const int bs = (int)(key & 0xffu), bestSad = (int)(key >> 8);
+        const int bestinc = bs - L;
+        const float d1 = (float)__shfl_sync(0xffffffffu, dist, max(bs - 1, 0));
+        const float d2 = (float)bestSad;
+        const float d3 = (float)__shfl_sync(0xffffffffu, dist, min(bs + 1, 10));
+        if (lane == 0 && bestinc != -L && bestinc != L) {
+            const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+            if (!(deltaR < -1 || deltaR > 1)) {
+                float bestuR = __fmul_rn(S.sf[oct], __fadd_rn(__fadd_rn((float)sr, (float)bestinc), deltaR));
+                float disparity = __fsub_rn(uLc, bestuR);
+                if (disparity >= min_d && disparity < max_d) {
+                    if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uLc - 0.01); }
+                    const size_t oL = (size_t)b * S.kp_cap_l + i0 + cur;
+                    depth[oL] = __fdiv_rn(mbf, disparity);
+                    u_right[oL] = bestuR;
+                    sad[oL] = bestSad;
+                }
+            }
+        }
+        __syncwarp();   // every lane is done with this buffer and with `part`
+        cur = nxt;
     }
 }
 
@@ -256,16 +373,19 @@ static int stereo_launch(orb_extractor* l, orb_extractor* r, int b0, int batch, 
     if (T) cudaEventRecord(l->ev_stage[7], l->stream);
     nvtxRangePushA("orb:stereo_match");
     dim3 grid((l->plan.kp_cap + SM_WARPS - 1) / SM_WARPS, batch);
-    k_stereo_match<<<grid, SM_WARPS * 32, 0, l->stream>>>(l->d_kps + kl, l->d_desc + kl * 32, l->d_counts + b0, r->d_kps + kr, r->d_desc + kr * 32,
-                                                         l->d_pyr, r->d_pyr, row_start, row_items, l->d_u_right + kl, l->d_depth + kl,
-                                                         l->d_sad + kl, S, mbf, min_d, max_d);
+    int2* jobs = l->d_st_jobs + kl;
+    k_stereo_search<<<grid, SM_WARPS * 32, 0, l->stream>>>(l->d_kps + kl, l->d_desc + kl * 32, l->d_counts + b0, r->d_desc + kr * 32, row_start, row_items,
+                                                          l->d_u_right + kl, l->d_depth + kl, l->d_sad + kl, jobs, S, min_d, max_d);
+    dim3 grid2((l->plan.kp_cap + SR_WARPS * SR_KPW - 1) / (SR_WARPS * SR_KPW), batch);
+    k_stereo_refine<<<grid2, SR_WARPS * 32, 0, l->stream>>>(l->tm_st_l, r->tm_st_r, l->d_kps + kl, l->d_counts + b0, jobs, l->d_u_right + kl, l->d_depth + kl,
+                                                           l->d_sad + kl, S, mbf, min_d, max_d, b0);
     nvtxRangePop();
     if (T) cudaEventRecord(l->ev_stage[8], l->stream);
     nvtxRangePushA("orb:stereo_median");
     k_stereo_median<<<batch, 512, 0, l->stream>>>(l->d_counts + b0, l->d_u_right + kl, l->d_depth + kl, l->d_sad + kl, l->plan.kp_cap);
     nvtxRangePop();
     if (T) { cudaEventRecord(l->ev_stage[9], l->stream); l->stage_valid[5] = l->stage_valid[6] = l->stage_valid[7] = true; }
-    l->launches += 3;
+    l->launches += 4;
     ORB_CUDA(cudaGetLastError());
     if (fence_right) {
         // later work on the right stream must not overwrite its buffers before we are done

@@ -154,9 +154,9 @@ __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr,
 // One WARP per cell, FC_CELLS consecutive cells per warp, no CTA-wide barrier anywhere: every warp owns a private
 // shared-memory region (tile | score map with a zero frame | list) and every list stays in row-major order, so the
 // final write needs no sort, no atomics and no prefix over warps, and the per-cell threshold choice is a warp vote:
-//   (1) stage the cell view (w_cell + 6) x (h_cell + 6) with 16-byte LDGSTS, zero the score map;
-//   (2) byte-SIMD necessary test at minTh on one 4-pixel word per lane, survivors appended in order
-//       (offsets from three bit-sliced ballots of the per-lane count);
+//   (1) stage the cell view (w_cell + 6) x (h_cell + 6) with 16-byte LDGSTS;
+//   (2) byte-SIMD necessary test at minTh, 4 pixels per word, every lane on its own contiguous run of words: test + count,
+//       one warp scan, ordered write (no ballot, no POPC per word);
 //   (3) exact score of the survivors, two pixels per lane on packed 16-bit lanes (VIMNMX3.S16x2), into the score
 //       map; corners compacted in place;
 //   (4) strict local maxima (VIMNMX3 over the 8 neighbours), compacted in place, counted with and without iniTh;
@@ -245,8 +245,6 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
             const int q = lane & 7;
             if (q < nq)
                 for (int y = lane >> 3; y < th; y += 4) cp_async16(wt + y * TP + q * 16, S + (size_t)y * G.pitch + q * 16);
-            uint4* sc4 = reinterpret_cast<uint4*>(sc);
-            for (int i = lane; i < (ih + 2) * (SP / 16); i += 32) sc4[i] = make_uint4(0u, 0u, 0u, 0u);
             cp_async_wait_all();
         }
         __syncwarp();
@@ -257,41 +255,57 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
         const int ngroups = nwi * ih;
 
         // (2) necessary test: both ring pixels of the vertical pair (1, 9) and of the horizontal pair
-        // (5, 13) within t of the centre => no 9-arc
-        int n_a = 0;
+        // (5, 13) within t of the centre => no 9-arc.  Two passes over lane-contiguous runs of words (lane order == row-major
+        // order): pass 1 tests and counts, one warp scan turns the counts into offsets, pass 2 writes the survivors in order.
+        // No ballot and no POPC per word; the masks wait in the (not yet zeroed) score-map region.
+        int n_a;
         {
             const int xfirst = 4 * w0 - shift - 3;                       // <= 0: interior x of byte 0 of the first word
             const unsigned mfirst = 0x80808080u << (8 * -xfirst);
             const int over = xfirst + 4 * nwi - iw;                      // bytes of the last word beyond the interior (0..3)
             const unsigned mlast = 0x80808080u >> (8 * over);
+            const int R = (ngroups + 31) >> 5;                           // words per lane
+            const int f0 = lane * R, nrun = min(R, ngroups - f0);
+            uint32_t* const mk = reinterpret_cast<uint32_t*>(sc) + lane;
+            unsigned c4 = 0;                                             // survivors of this lane, one counter per byte position
+            if (nrun > 0) {
+                const int y0 = (int)(((unsigned)f0 * gmagic) >> 20);
+                int wxi = f0 - y0 * nwi;
+                const uint32_t* cw = tw32 + (y0 + 3) * TPW + w0 + wxi;
+                unsigned ib = (unsigned)((y0 << 8) + 4 * wxi);           // y << 8 | 4 * word: bits 0..6 and 8..13, the mask uses 7, 15, 23, 31
 #pragma unroll 1
-            for (int g0 = 0; g0 < ngroups; g0 += 32) {
-                const int gi = g0 + lane;
-                unsigned m = 0, i0 = 0;
-                if (gi < ngroups) {
-                    const int y = (int)(((unsigned)gi * gmagic) >> 20), wxi = gi - y * nwi;
-                    const uint32_t* cw = tw32 + (y + 3) * TPW + w0 + wxi;
-                    const unsigned C = cw[0], N = cw[-3 * TPW], S = cw[3 * TPW], L = cw[-1], R = cw[1];
-                    const unsigned E = __byte_perm(C, R, 0x6543), Wp = __byte_perm(L, C, 0x4321);  // x + 3, x - 3
+                for (int st = 0; st < nrun; ++st) {
+                    const unsigned C = cw[0], N = cw[-3 * TPW], S = cw[3 * TPW], L = cw[-1], Rr = cw[1];
+                    const unsigned E = __byte_perm(C, Rr, 0x6543), Wp = __byte_perm(L, C, 0x4321);  // x + 3, x - 3
                     const unsigned pv = gt_bytes(__vabsdiffu4(N, C), kk) | gt_bytes(__vabsdiffu4(S, C), kk);
                     const unsigned ph = gt_bytes(__vabsdiffu4(E, C), kk) | gt_bytes(__vabsdiffu4(Wp, C), kk);
-                    m = pv & ph & 0x80808080u;
+                    unsigned m = pv & ph & 0x80808080u;
                     if (wxi == 0) m &= mfirst;
                     if (wxi == nwi - 1) m &= mlast;
-                    i0 = (unsigned)((y << 8) + xfirst + 4 * wxi);
-                }
-                const int cnt = __popc(m);
-                const unsigned b0 = __ballot_sync(full, cnt & 1), b1 = __ballot_sync(full, cnt & 2), b2 = __ballot_sync(full, cnt & 4);
-                if (b0 | b1 | b2) {
-                    int o = n_a + __popc(b0 & lt) + 2 * __popc(b1 & lt);
-                    if (b2) o += 4 * __popc(b2 & lt);
-                    n_a = __shfl_sync(full, o + cnt, 31);
-                    if (m & 0x80u) seg[o++] = (uint16_t)i0;
-                    if (m & 0x8000u) seg[o++] = (uint16_t)(i0 + 1);
-                    if (m & 0x800000u) seg[o++] = (uint16_t)(i0 + 2);
-                    if (m & 0x80000000u) seg[o] = (uint16_t)(i0 + 3);
+                    mk[st * 32] = m | ib;
+                    c4 += m >> 7;
+                    ++wxi; ++cw; ib += 4u;
+                    if (wxi == nwi) { wxi = 0; cw += TPW - nwi; ib += 256u - 4u * (unsigned)nwi; }
                 }
             }
+            const int cnt = (int)((c4 * 0x01010101u) >> 24);             // <= 4 R < 256
+            int inc = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(full, inc, o); if (lane >= o) inc += v; }
+            n_a = __shfl_sync(full, inc, 31);
+            uint16_t* o = seg + (inc - cnt);
+#pragma unroll 1
+            for (int st = 0; st < nrun; ++st) {
+                const unsigned v = mk[st * 32];
+                const unsigned i0 = (v & 0x3f7fu) + (unsigned)xfirst;
+                if (v & 0x80u) *o++ = (uint16_t)i0;
+                if (v & 0x8000u) *o++ = (uint16_t)(i0 + 1);
+                if (v & 0x800000u) *o++ = (uint16_t)(i0 + 2);
+                if (v & 0x80000000u) *o++ = (uint16_t)(i0 + 3);
+            }
+            __syncwarp();
+            uint4* sc4 = reinterpret_cast<uint4*>(sc);
+            for (int i = lane; i < (ih + 2) * (SP / 16); i += 32) sc4[i] = make_uint4(0u, 0u, 0u, 0u);
         }
         __syncwarp();
 
@@ -615,7 +629,9 @@ static bool fast_smem(const Plan& P, int* sp, int* warp_bytes, int* score_off, i
     if (mw > 59 || mh > 59) return false;       // cannot happen: a cell is ceil(window / floor(window / 30)) <= 59 pixels
     *sp = mw + 2 <= 48 ? 48 : 64;               // score pitch: interior + zero frame
     *score_off = FC_TP * (mh + 6);
-    *list_off = *score_off + *sp * (mh + 2);
+    // the score-map region first holds the masks of the necessary test: 32 lanes x ceil(words / 32) u32
+    const int ng_max = ((mw + 6) / 4 + 1) * mh, scratch = 128 * ((ng_max + 31) / 32);
+    *list_off = *score_off + max(*sp * (mh + 2), scratch);
     *warp_bytes = (*list_off + 2 * mw * mh + 4 + 15) & ~15;
     return true;
 }

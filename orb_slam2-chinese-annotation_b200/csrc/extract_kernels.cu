@@ -165,6 +165,8 @@ __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr,
 #define FC_WARPS 4     // warps per CTA (independent of each other)
 #define FC_CELLS 4     // consecutive cells walked by one warp
 #define FC_TP 80       // tile pitch: view width (<= 59 + 6) + alignment shift (<= 15); 20 words: consecutive rows land in different banks
+                       // (a 64-byte pitch was measured for cells <= 43 wide: 28 instead of 24 resident warps, but rows alias every
+                       // second row and the ring gathers conflict: 1.93 -> 2.91 ms)
 
 __device__ __forceinline__ unsigned gt_bytes(unsigned ad, unsigned k) {  // bit 7 of byte j set <=> ad.j > 127 - k.j  (k.j <= 127)
     return ad | ((ad & 0x7f7f7f7fu) + k);

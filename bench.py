@@ -490,6 +490,17 @@ def load_json(path, default):
         return default
 
 
+def kernel_counts(counts, names):
+    """ncu counts of one stage: one kernel, or the sum over the kernels the stage launches."""
+    ks = counts.get("kernels", {})
+    if isinstance(names, str):
+        return ks.get(names)
+    got = [ks[n] for n in names if n in ks]
+    if len(got) != len(names):
+        return None
+    return {f: sum(g[f] for g in got) for f in ("alu_lane_ops_per_unit", "thread_inst_per_unit", "dram_bytes_per_unit")}
+
+
 def roofline_block(cfg, B, stages, n_kp, clocks):
     """Every stage against its own measured roof.  HBM: algorithmic bytes / event time / measured copy bandwidth.  INT: ALU-pipe
     lane-operations counted by ncu at this batch size / event time / (measured ALU-pipe lanes per clock per SM x SMs x clock)."""
@@ -505,7 +516,7 @@ def roofline_block(cfg, B, stages, n_kp, clocks):
     issue_peak = 128.0 * sms * sm_mhz * 1e6 / 1e9    # 4 schedulers x 32 lanes per clock per SM
     _, bytes_k, _ = algorithmic_bytes(cfg, n_kp)
     kernel_of = {"pyramid": "k_resize_tma", "fast_cells": "k_fast_cells", "quadtree": "k_quadtree", "blur": "k_gauss7_tma",
-                 "orient_describe": "k_orient_describe", "stereo_match": "k_stereo_match", "stereo_rows": "k_stereo_rows",
+                 "orient_describe": "k_orient_describe", "stereo_match": ("k_stereo_search", "k_stereo_refine"), "stereo_rows": "k_stereo_rows",
                  "stereo_median": "k_stereo_median"}
     bound_of = {"pyramid": "hbm", "blur": "hbm"}
     per = {}
@@ -518,7 +529,7 @@ def roofline_block(cfg, B, stages, n_kp, clocks):
         if k in bytes_k:
             a = bytes_k[k] * images / (ms * 1e-3) / 1e9
             ent["hbm"] = {"alg_bytes_per_image": int(bytes_k[k]), "achieved_GBs": a, "frac": a / hbm}
-        cn = counts.get("kernels", {}).get(kernel_of.get(k, ""), None)
+        cn = kernel_counts(counts, kernel_of.get(k, ""))
         if cn and counts.get("workload") == cfg["workload"]:
             a = cn["alu_lane_ops_per_unit"] * images / (ms * 1e-3) / 1e9
             t = cn["thread_inst_per_unit"] * images / (ms * 1e-3) / 1e9
@@ -535,7 +546,7 @@ def roofline_block(cfg, B, stages, n_kp, clocks):
     else:
         top = {"bound": "int", "kernel": dom, "achieved": None, "peak": alu_peak, "unit": "G lane-ops/s on the ALU pipe", "frac": None,
                "note": "profiles/r2_ncu_counts.json has no counts for this workload"}
-    cn = counts.get("kernels", {}).get(kernel_of.get(dom, ""), {}) if counts.get("workload") == cfg["workload"] else {}
+    cn = (kernel_counts(counts, kernel_of.get(dom, "")) or {}) if counts.get("workload") == cfg["workload"] else {}
     units = B * (1 if dom.startswith("stereo") else 1)   # per launch: one handle, B images
     top["traffic"] = (cn.get("dram_bytes_per_unit") * units) if cn.get("dram_bytes_per_unit") else None
     top["traffic_source"] = counts.get("source")

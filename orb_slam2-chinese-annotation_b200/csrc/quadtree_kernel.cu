@@ -94,7 +94,9 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
            int* __restrict__ status, const Plan P, const int cap, const int p2) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ QtShared sh;
-    const int l = blockIdx.x, b = blockIdx.y;
+    // blocks are dispatched in linear order (x fastest): image = x, level = y starts every image's level 0 (the longest CTA by far:
+    // it sweeps the most candidates per pass) before any level 1, i.e. longest-processing-time-first over the whole batch
+    const int b = blockIdx.x, l = blockIdx.y;
     const LevelGeom& G = P.lv[l];
     const int tid = threadIdx.x;
     int sp = 0;   // scan parity
@@ -391,7 +393,7 @@ cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefi
     if (bytes > 200 * 1024) return cudaErrorInvalidConfiguration;
     cudaError_t e = cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
-    dim3 grid(P.nlevels, batch);
+    dim3 grid(batch, P.nlevels);
     k_quadtree<<<grid, QT_THREADS, bytes, s>>>(cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, status, P, cap, p2);
     return cudaSuccess;
 }

@@ -211,7 +211,9 @@ __global__ void __launch_bounds__(B2_WARPS * 32) k_gauss7_tma(const __grid_const
     const int ox = tx + 4 * lane, r0 = warp * B2_ROWS;
     if (ox >= W || ty + r0 >= H) return;
     uint8_t* D = blur + G.off + (size_t)img * G.img_stride + ox;
-    uint32_t hs[7][4];
+    // Column pass on vertical PAIRS of row sums (each < 2^16): q[j] = (row a + j, row a + j + 1) of the 7-row window starting at row a,
+    // one PRMT per new row, so that a column costs three IDP.2A + one IMAD instead of three adds + four IMAD.
+    uint32_t q[6][4], hl[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
     for (int i = 0; i < B2_ROWS + 6; ++i) {
         const uint32_t w0 = raw[r0 + i][lane + 3], w1 = raw[r0 + i][lane + 4], w2 = raw[r0 + i][lane + 5];   // pixels ox-4.., ox.., ox+4..
@@ -223,16 +225,17 @@ __global__ void __launch_bounds__(B2_WARPS * 32) k_gauss7_tma(const __grid_const
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
 #pragma unroll
-            for (int j = 0; j < 6; ++j) hs[j][k] = hs[j + 1][k];
-            hs[6][k] = hn[k];
+            for (int j = 0; j < 5; ++j) q[j][k] = q[j + 1][k];
+            q[5][k] = __byte_perm(hl[k], hn[k], 0x5410);   // (row i - 1, row i)
+            hl[k] = hn[k];
         }
         if (i >= 6) {
             const int oy = ty + r0 + i - 6;
             if (oy >= H) break;
             uint32_t v[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                v[k] = 18u * (hs[0][k] + hs[6][k]) + 34u * (hs[1][k] + hs[5][k]) + 48u * (hs[2][k] + hs[4][k]) + 56u * hs[3][k] + 32768u;
+            for (int k = 0; k < 4; ++k)   // rows i-6 .. i with taps 18 34 48 56 48 34 18
+                v[k] = __dp2a_lo(q[0][k], 18u | (34u << 8), __dp2a_lo(q[2][k], 48u | (56u << 8), __dp2a_lo(q[4][k], 48u | (34u << 8), 18u * hn[k] + 32768u)));
             // byte 2 of each 24-bit sum is the rounded result
             const uint32_t t01 = __byte_perm(v[0], v[1], 0x0062), t23 = __byte_perm(v[2], v[3], 0x0062);
             *reinterpret_cast<uint32_t*>(D + (size_t)oy * G.pitch) = __byte_perm(t01, t23, 0x5410);

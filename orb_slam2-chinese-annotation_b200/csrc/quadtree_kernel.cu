@@ -18,8 +18,10 @@
 // address) use the canonical rule "later-created node first" == higher index in R.
 #include "orb_internal.h"
 
-#define QT_THREADS 256
-#define QT_WARPS (QT_THREADS / 32)
+// CTA size NT is a template parameter: 256 threads when the batch fills the GPU anyway (throughput: fewest barrier stalls per unit of
+// work), 512 for very large levels (3840 x 2160 / 8000 features: level 0 sweeps ~10^5 candidates per pass), 1024 when only a few CTAs
+// exist at all (a live camera, batch 1: the level-0 CTA IS the latency of the stage).
+#define QT_MAX_WARPS 32
 
 struct QNode {
     int count;
@@ -28,13 +30,15 @@ struct QNode {
 };
 
 struct QtShared {
-    int warp_sums[2][QT_WARPS + 1];
+    int warp_sums[2][QT_MAX_WARPS + 1];
     int scal[4];
 };
 
 // exclusive scan over the CTA of one value per thread; returns the exclusive prefix, total in *total.  `par`
 // alternates between consecutive calls (two copies of the warp totals: no trailing barrier needed).
+template <int NT>
 __device__ __forceinline__ int block_excl_scan(int v, int* total, QtShared& sh, int& par) {
+    constexpr int QT_WARPS = NT / 32;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int* ws = sh.warp_sums[par];
     par ^= 1;
@@ -46,7 +50,7 @@ __device__ __forceinline__ int block_excl_scan(int v, int* total, QtShared& sh, 
     }
     if (lane == 31) ws[warp] = inc;
     __syncthreads();
-    int w = lane < QT_WARPS ? ws[lane] : 0;   // every warp scans the 8 warp totals itself
+    int w = lane < QT_WARPS ? ws[lane] : 0;   // every warp scans the warp totals itself
     int winc = w;
 #pragma unroll
     for (int o = 1; o < QT_WARPS; o <<= 1) {
@@ -69,6 +73,7 @@ __device__ __forceinline__ void warp_count(int* counter, int target) {
 }
 
 // bitonic sort, descending, of n (power of two) 64-bit keys in shared memory
+template <int QT_THREADS>
 __device__ void block_sort_desc(unsigned long long* a, int n) {
     for (int k = 2; k <= n; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
@@ -88,6 +93,7 @@ __device__ void block_sort_desc(unsigned long long* a, int n) {
 // Dynamic shared memory layout (cap = node_cap_max, p2 = next pow2 >= cap):
 //   QNode nodeA[cap] | QNode nodeB[cap] | int cnt4[4 cap] | int nid[4 cap] | int par[cap] | int pre_ne[cap + 1] | int pre_g[cap] |
 //   int flag[cap] | u64 sortk[p2]
+template <int QT_THREADS>
 __global__ void __launch_bounds__(QT_THREADS)
 k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, const uint32_t* __restrict__ stage,
            uint32_t* __restrict__ keys, uint32_t* __restrict__ lvl_kp, int* __restrict__ lvl_cnt, int* __restrict__ lvl_ncand,
@@ -125,7 +131,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
         const int c = c0 + tid;
         const int v = c < n_cells ? ccnt[c] : 0;
         int tot;
-        const int ex = block_excl_scan(v, &tot, sh, sp);
+        const int ex = block_excl_scan<QT_THREADS>(v, &tot, sh, sp);
         if (c < n_cells) cpre[c] = carry + ex;
         carry += tot;
     }
@@ -206,7 +212,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
                 const int f = (i < size && cur[i].count > 1) ? 1 : 0;
                 const int g = (i < size && !f) ? 1 : 0;
                 int tot;
-                const int ex = block_excl_scan(f | (g << 16), &tot, sh, sp);
+                const int ex = block_excl_scan<QT_THREADS>(f | (g << 16), &tot, sh, sp);
                 if (f) {
                     if (sorted_phase) sortk[c_par + (ex & 0xffff)] = ((unsigned long long)(unsigned)cur[i].count << 32) | (unsigned)i;
                     else flag[i] = c_par + (ex & 0xffff);  // ascending rank, flipped below
@@ -226,7 +232,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
             while (np2 < np) np2 <<= 1;
             for (int i = np + tid; i < np2; i += QT_THREADS) sortk[i] = 0ull;
             __syncthreads();
-            block_sort_desc(sortk, np2);
+            block_sort_desc<QT_THREADS>(sortk, np2);
             for (int i = tid; i < np; i += QT_THREADS) par[i] = (int)(sortk[i] & 0xffffffffu);
         }
         __syncthreads();
@@ -241,7 +247,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
                 ne = (c.x > 0) + (c.y > 0) + (c.z > 0) + (c.w > 0);
             }
             int tot;
-            const int ex = block_excl_scan(ne, &tot, sh, sp);
+            const int ex = block_excl_scan<QT_THREADS>(ne, &tot, sh, sp);
             if (k < np) {
                 pre_ne[k] = carry_ne + ex;
                 pre_g[k] = carry_ne + ex + ne - (k + 1);   // size growth after dividing parents 0..k (inclusive)
@@ -279,7 +285,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
                 const int i = i0 + tid;
                 const int g = i < size ? flag[i] : 0;
                 int tot;
-                const int ex = block_excl_scan(g, &tot, sh, sp);
+                const int ex = block_excl_scan<QT_THREADS>(g, &tot, sh, sp);
                 if (g) {
                     const int pos = c_keep + ex;
                     nxt[pos] = cur[i];
@@ -321,7 +327,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
             reinterpret_cast<int4*>(nid)[pi] = make_int4(ids[0], ids[1], ids[2], ids[3]);
         }
         int n_expand;
-        block_excl_scan(my_expand, &n_expand, sh, sp);
+        block_excl_scan<QT_THREADS>(my_expand, &n_expand, sh, sp);
         { QNode* t = cur; cur = nxt; nxt = t; }   // nxt = the list before this pass (boxes still needed by the sweep)
 
         // e. termination (reference :688-757)
@@ -391,9 +397,13 @@ cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefi
     int p2;
     const size_t bytes = quadtree_smem(cap, &p2);
     if (bytes > 200 * 1024) return cudaErrorInvalidConfiguration;
-    cudaError_t e = cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    int nfeat = 0;
+    for (int l = 0; l < P.nlevels; ++l) nfeat = max(nfeat, P.lv[l].n_feat);
+    const int nt = batch * P.nlevels <= 2 * 148 ? 1024 : (nfeat >= 1200 ? 512 : 256);
+    auto kern = nt == 1024 ? k_quadtree<1024> : (nt == 512 ? k_quadtree<512> : k_quadtree<256>);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
     dim3 grid(batch, P.nlevels);
-    k_quadtree<<<grid, QT_THREADS, bytes, s>>>(cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, status, P, cap, p2);
+    kern<<<grid, nt, bytes, s>>>(cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, status, P, cap, p2);
     return cudaSuccess;
 }

@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr,
 //   (5) ordered write of the maxima that pass the cell's threshold.
 // The tile pitch TP and score pitch SP are compile-time so that every ring / neighbour offset is an immediate.
 #define FC_WARPS 4     // warps per CTA (independent of each other)
-#define FC_CELLS 4     // consecutive cells walked by one warp
+#define FC_CELLS 4     // consecutive cells walked by one warp when the batch fills the GPU (1 for small batches: latency)
 #define FC_TP 80       // tile pitch: view width (<= 59 + 6) + alignment shift (<= 15); 20 words: consecutive rows land in different banks
                        // (a 64-byte pitch was measured for cells <= 43 wide: 28 instead of 24 resident warps, but rows alias every
                        // second row and the ring gathers conflict: 1.93 -> 2.91 ms)
@@ -208,7 +208,7 @@ __constant__ unsigned c_div_magic[20] = {0u, (1u << 20) / 1 + 1, (1u << 20) / 2 
 template <int SP>
 __global__ void __launch_bounds__(FC_WARPS * 32)
 k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
-             const int warp_bytes, const int score_off, const int list_off) {
+             const int warp_bytes, const int score_off, const int list_off, const int cells_per_warp) {
     constexpr int TP = FC_TP, TPW = TP / 4;
     extern __shared__ __align__(16) uint8_t smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -221,8 +221,8 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
     const int t = P.min_th, ini_th = P.ini_th;
     const unsigned kk = (unsigned)(127 - min(t, 126)) * 0x01010101u;
 
-    int cg = (blockIdx.x * FC_WARPS + warp) * FC_CELLS;
-    const int cg_end = min(cg + FC_CELLS, P.total_cells);
+    int cg = (blockIdx.x * FC_WARPS + warp) * cells_per_warp;
+    const int cg_end = min(cg + cells_per_warp, P.total_cells);
     int l = 0;
 #pragma unroll 1
     for (; cg < cg_end; ++cg) {
@@ -412,7 +412,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 #define OD_WARPS 4         // warps per CTA (independent of each other after the prologue)
-#define OD_KPW 8           // keypoints walked by one warp: the patches of keypoint j + 1 are in flight while j is described
+#define OD_KPW 8           // keypoints walked by one warp (2 for small batches): the patches of keypoint j + 1 are in flight while j is described
 // Both patches of a keypoint arrive by TMA (one cp.async.bulk.tensor per patch, issued by lane 0, SASS UTMALDG): the innermost box
 // coordinate of a u8 tensor must be a multiple of 16 bytes (tools/tma_align_test.cu: anything else is an illegal instruction), so
 // the boxes are wider than the patches and start at the 16-byte boundary below the patch.
@@ -487,7 +487,7 @@ __device__ __forceinline__ void od_tma_load_3d(void* smem_dst, const CUtensorMap
 __global__ void __launch_bounds__(OD_WARPS * 32, 7)
 k_orient_describe(const __grid_constant__ TmaMaps tm_raw, const __grid_constant__ TmaMaps tm_blur, const uint32_t* __restrict__ lvl_kp,
                   const int* __restrict__ lvl_cnt, orb_keypoint* __restrict__ kps, uint8_t* __restrict__ desc,
-                  int* __restrict__ counts, const Plan P, const int b0) {
+                  int* __restrict__ counts, const Plan P, const int b0, const int kpw) {
     extern __shared__ __align__(128) uint8_t od_smem[];
     __shared__ uint64_t s_bar[OD_WARPS][2];
     __shared__ int s_pre[ORB_MAX_LEVELS + 1];
@@ -505,8 +505,8 @@ k_orient_describe(const __grid_constant__ TmaMaps tm_raw, const __grid_constant_
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");   // make the init visible to the async proxy
     }
     __syncthreads();
-    const int o0 = (blockIdx.x * OD_WARPS + warp) * OD_KPW;
-    const int n = min(OD_KPW, s_pre[ORB_MAX_LEVELS] - o0);
+    const int o0 = (blockIdx.x * OD_WARPS + warp) * kpw;
+    const int n = min(kpw, s_pre[ORB_MAX_LEVELS] - o0);
     if (n <= 0) return;
 
     // lane j < n looks up keypoint o0 + j: level, quadtree slot, packed key
@@ -646,8 +646,10 @@ cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint3
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tot);
         if (e != cudaSuccess) return e;
     }
-    dim3 grid((P.total_cells + FC_WARPS * FC_CELLS - 1) / (FC_WARPS * FC_CELLS), batch);
-    kern<<<grid, FC_WARPS * 32, tot, s>>>(pyr, cell_cnt, stage, P, wb, so, lo);
+    // a small batch cannot fill 148 SMs x 24 warps with 4 cells per warp: one cell per warp then (per-frame latency)
+    const int cpw = (long long)batch * P.total_cells >= 4LL * 148 * 24 * FC_CELLS ? FC_CELLS : 1;
+    dim3 grid((P.total_cells + FC_WARPS * cpw - 1) / (FC_WARPS * cpw), batch);
+    kern<<<grid, FC_WARPS * 32, tot, s>>>(pyr, cell_cnt, stage, P, wb, so, lo, cpw);
     return cudaSuccess;
 }
 cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const TmaMaps& tm_blur, const uint32_t* lvl_kp, const int* lvl_cnt,
@@ -655,8 +657,10 @@ cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const 
     const int smem = OD_WARPS * 2 * OD_BUF_BYTES;
     cudaError_t e = cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
     if (e != cudaSuccess) return e;
-    dim3 grid((P.kp_cap + OD_WARPS * OD_KPW - 1) / (OD_WARPS * OD_KPW), batch);
-    k_orient_describe<<<grid, OD_WARPS * 32, smem, s>>>(tm_raw, tm_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, b0);
+    // small batches: fewer keypoints per warp, so that the frame's ~2000 keypoints spread over all SMs (per-frame latency)
+    const int kpw = (long long)batch * P.kp_cap >= 2LL * 148 * 28 * OD_KPW ? OD_KPW : 2;
+    dim3 grid((P.kp_cap + OD_WARPS * kpw - 1) / (OD_WARPS * kpw), batch);
+    k_orient_describe<<<grid, OD_WARPS * 32, smem, s>>>(tm_raw, tm_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, b0, kpw);
     return cudaSuccess;
 }
 

@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr,
 // One WARP per cell, FC_CELLS consecutive cells per warp, no CTA-wide barrier anywhere: every warp owns a private
 // shared-memory region (tile | score map with a zero frame | list) and every list stays in row-major order, so the
 // final write needs no sort, no atomics and no prefix over warps, and the per-cell threshold choice is a warp vote:
-//   (1) stage the cell view (w_cell + 6) x (h_cell + 6) with 16-byte LDGSTS;
+//   (1) the cell view (w_cell + 6) x (h_cell + 6) arrives by TMA (one box per cell, requested one cell ahead);
 //   (2) byte-SIMD necessary test at minTh, 4 pixels per word, every lane on its own contiguous run of words: test + count,
 //       one warp scan, ordered write (no ballot, no POPC per word);
 //   (3) exact score of the survivors, two pixels per lane on packed 16-bit lanes (VIMNMX3.S16x2), into the score
@@ -205,12 +205,14 @@ __constant__ unsigned c_div_magic[20] = {0u, (1u << 20) / 1 + 1, (1u << 20) / 2 
 
 // Dynamic shared memory, per warp (warp_bytes apart): tile (rows x FC_TP bytes, 16-byte aligned like the level) |
 // score map ((ih + 2) x SP bytes, zero frame) at score_off | list (u16: y << 8 | x) at list_off
+struct FcCell { int l, c, ci, cj, iniX, iniY, tw, th; bool valid; };
 template <int SP>
 __global__ void __launch_bounds__(FC_WARPS * 32)
-k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
-             const int warp_bytes, const int score_off, const int list_off, const int cells_per_warp) {
+k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
+             const int warp_bytes, const int score_off, const int list_off, const int cells_per_warp, const int box_h, const int b0) {
     constexpr int TP = FC_TP, TPW = TP / 4;
-    extern __shared__ __align__(16) uint8_t smem[];
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ uint64_t s_bar[FC_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1, full = 0xffffffffu;
     uint8_t* const wt = smem + warp * warp_bytes;
@@ -220,36 +222,67 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
     const int b = blockIdx.y;
     const int t = P.min_th, ini_th = P.ini_th;
     const unsigned kk = (unsigned)(127 - min(t, 126)) * 0x01010101u;
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned)__cvta_generic_to_shared(&s_bar[warp])) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");   // make the init visible to the async proxy
+    }
+    __syncwarp();
 
     int cg = (blockIdx.x * FC_WARPS + warp) * cells_per_warp;
     const int cg_end = min(cg + cells_per_warp, P.total_cells);
-    int l = 0;
+    int lv = 0;
+    // cell view [iniX, maxX) x [iniY, maxY) (reference :819-839)
+    auto geom = [&](int cgi) {
+        FcCell g;
+        while (lv + 1 < P.nlevels && cgi >= P.lv[lv + 1].cell_off) ++lv;
+        const LevelGeom& G = P.lv[lv];
+        g.l = lv;
+        g.c = cgi - G.cell_off;
+        g.ci = (int)__umulhi((unsigned)g.c, G.ncols_magic); g.cj = g.c - g.ci * G.n_cols;
+        g.iniY = ORB_WIN + g.ci * G.h_cell; g.iniX = ORB_WIN + g.cj * G.w_cell;
+        g.tw = min(g.iniX + G.w_cell + 6, G.max_bx) - g.iniX; g.th = min(g.iniY + G.h_cell + 6, G.max_by) - g.iniY;
+        g.valid = !(g.iniY >= G.max_by - 3 || g.iniX >= G.max_bx - 6 || g.tw - 6 <= 0 || g.th - 6 <= 0);
+        return g;
+    };
+    // (1) the view (80 x box_h bytes from the 16-byte boundary left of it: the tile rows keep the level's alignment) arrives by TMA;
+    // the box of the NEXT cell is requested as soon as the last reader of the tile (the score phase) is done, so that it flies
+    // under the neighbourhood test and the output phase
+    auto request = [&](const FcCell& g) {
+        if (lane == 0) {
+            const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(TP * box_h) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                         ::"r"((unsigned)__cvta_generic_to_shared(wt)), "l"(&tm.lv[g.l]), "r"(bar), "r"(g.iniX & ~15), "r"(g.iniY), "r"(b0 + b) : "memory");
+        }
+    };
+    if (cg >= cg_end) return;
+    FcCell g = geom(cg);
+    if (g.valid) request(g);
+    unsigned phase = 0;
 #pragma unroll 1
     for (; cg < cg_end; ++cg) {
-        while (l + 1 < P.nlevels && cg >= P.lv[l + 1].cell_off) ++l;
-        const LevelGeom& G = P.lv[l];
-        const int c = cg - G.cell_off;
-        const int ci = (int)__umulhi((unsigned)c, G.ncols_magic), cj = c - ci * G.n_cols;
+        FcCell gn;
+        gn.valid = false;
         int* const out_cnt = cell_cnt + (size_t)b * P.total_cells + cg;
-        // cell view [iniX, maxX) x [iniY, maxY) (reference :819-839)
-        const int iniY = ORB_WIN + ci * G.h_cell, iniX = ORB_WIN + cj * G.w_cell;
-        const int maxY = min(iniY + G.h_cell + 6, G.max_by), maxX = min(iniX + G.w_cell + 6, G.max_bx);
-        const int tw = maxX - iniX, th = maxY - iniY;
-        const int iw = tw - 6, ih = th - 6;  // interior = tested pixels
-        if (iniY >= G.max_by - 3 || iniX >= G.max_bx - 6 || iw <= 0 || ih <= 0) { if (lane == 0) *out_cnt = 0; continue; }
-
-        // (1) stage with aligned 16-byte loads (the view starts at byte `shift` of the tile rows)
-        const int shift = iniX & 15;
-        __syncwarp();   // the previous cell's readers are done with the tile, the score map and the list
-        {
-            const uint8_t* S = pyr + G.off + (size_t)b * G.img_stride + (size_t)iniY * G.pitch + (iniX - shift);
-            const int nq = (tw + shift + 15) >> 4;          // <= 5
-            const int q = lane & 7;
-            if (q < nq)
-                for (int y = lane >> 3; y < th; y += 4) cp_async16(wt + y * TP + q * 16, S + (size_t)y * G.pitch + q * 16);
-            cp_async_wait_all();
+        if (!g.valid) {
+            if (lane == 0) *out_cnt = 0;
+            if (cg + 1 < cg_end) { gn = geom(cg + 1); if (gn.valid) request(gn); }
+            g = gn;
+            continue;
         }
-        __syncwarp();
+        const LevelGeom& G = P.lv[g.l];
+        const int c = g.c, ci = g.ci, cj = g.cj, iniX = g.iniX;
+        const int iw = g.tw - 6, ih = g.th - 6;  // interior = tested pixels
+        const int shift = iniX & 15;
+        {
+            const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
+            unsigned ok;
+            do {
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                             : "=r"(ok) : "r"(bar), "r"(phase) : "memory");
+            } while (!ok);
+            phase ^= 1u;
+        }
         const uint8_t* tile = wt + shift;
         // interior words of a row: word wx holds interior pixels xi = 4 * wx - shift - 3 + k, k = 0..3
         const int w0 = (shift + 3) >> 2, nwi = ((shift + 3 + iw - 1) >> 2) - w0 + 1;
@@ -343,6 +376,9 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
             __syncwarp();
         }
 
+        __syncwarp();   // every lane is done reading the tile
+        if (cg + 1 < cg_end) { gn = geom(cg + 1); if (gn.valid) request(gn); }
+
         // (4) strict local maxima over the 8 neighbours (the zero frame stands for "outside the cell"), compacted in place
         int n_m = 0, n_ini = 0;
 #pragma unroll 1
@@ -385,6 +421,8 @@ k_fast_cells(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32
             if (keep) out0[n_out + __popc(bk & lt)] = rec;
             n_out += __popc(bk);
         }
+        __syncwarp();   // the score map and the list are free for the next cell
+        g = gn;
     }
 }
 
@@ -634,23 +672,27 @@ static bool fast_smem(const Plan& P, int* sp, int* warp_bytes, int* score_off, i
     // the score-map region first holds the masks of the necessary test: 32 lanes x ceil(words / 32) u32
     const int ng_max = ((mw + 6) / 4 + 1) * mh, scratch = 128 * ((ng_max + 31) / 32);
     *list_off = *score_off + max(*sp * (mh + 2), scratch);
-    *warp_bytes = (*list_off + 2 * mw * mh + 4 + 15) & ~15;
+    *warp_bytes = (*list_off + 2 * mw * mh + 4 + 127) & ~127;   // the tile is a TMA destination: 128-byte aligned
     return true;
 }
-cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch) {
+int fast_box_rows(const Plan& P) {   // rows of the TMA box of k_fast_cells: the tallest cell view of any level
+    int mh = 0;
+    for (int l = 0; l < P.nlevels; ++l) if (P.lv[l].n_cols > 0) mh = max(mh, P.lv[l].h_cell);
+    return mh + 6;
+}
+cudaError_t launch_fast(cudaStream_t s, const TmaMaps& tm, int* cell_cnt, uint32_t* stage, const Plan& P, int b0, int batch) {
     int sp, wb, so, lo;
     if (!fast_smem(P, &sp, &wb, &so, &lo)) return cudaErrorInvalidConfiguration;
     const int tot = wb * FC_WARPS;
     auto kern = sp == 48 ? k_fast_cells<48> : k_fast_cells<64>;
-    if (tot > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tot);
-        if (e != cudaSuccess) return e;
-    }
+    // always: static (mbarriers) + dynamic shared memory can cross the 48 KB default even when the dynamic part alone does not
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tot);
+    if (e != cudaSuccess) return e;
     // a small batch cannot fill 148 SMs x 24 warps with 4 cells per warp: one cell per warp then (per-frame latency)
     const int cpw = (long long)batch * P.total_cells >= 4LL * 148 * 24 * FC_CELLS ? FC_CELLS : 1;
     dim3 grid((P.total_cells + FC_WARPS * cpw - 1) / (FC_WARPS * cpw), batch);
-    kern<<<grid, FC_WARPS * 32, tot, s>>>(pyr, cell_cnt, stage, P, wb, so, lo, cpw);
-    return cudaSuccess;
+    kern<<<grid, FC_WARPS * 32, tot, s>>>(tm, cell_cnt, stage, P, wb, so, lo, cpw, fast_box_rows(P), b0);
+    return cudaGetLastError();   // a refused launch must fail loudly, not leave stale candidate lists behind
 }
 cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const TmaMaps& tm_blur, const uint32_t* lvl_kp, const int* lvl_cnt,
                                    orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int b0, int batch) {
@@ -661,7 +703,7 @@ cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const 
     const int kpw = (long long)batch * P.kp_cap >= 2LL * 148 * 28 * OD_KPW ? OD_KPW : 2;
     dim3 grid((P.kp_cap + OD_WARPS * kpw - 1) / (OD_WARPS * kpw), batch);
     k_orient_describe<<<grid, OD_WARPS * 32, smem, s>>>(tm_raw, tm_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, b0, kpw);
-    return cudaSuccess;
+    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------

@@ -10,7 +10,8 @@ void launch_resize(cudaStream_t s, uint8_t* pyr, const CUtensorMap* src_map, boo
 cudaError_t orb_upload_moment_table(const int* umax);
 void launch_ingest(cudaStream_t s, const uint8_t* src, uint8_t* dst, int w, int h, int stride, size_t img_stride, int dst_pitch, size_t dst_img_stride, int batch);
 void launch_gauss(cudaStream_t s, const TmaMaps& maps, const uint8_t* pyr, uint8_t* blur, const Plan& P, int b0, int batch);
-cudaError_t launch_fast(cudaStream_t s, const uint8_t* pyr, int* cell_cnt, uint32_t* stage, const Plan& P, int batch);
+cudaError_t launch_fast(cudaStream_t s, const TmaMaps& tm, int* cell_cnt, uint32_t* stage, const Plan& P, int b0, int batch);
+int fast_box_rows(const Plan& P);
 cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefix, const uint32_t* stage, uint32_t* keys,
                             uint32_t* lvl_kp, int* lvl_cnt, int* lvl_ncand, int* status, const Plan& P, int batch);
 size_t quadtree_smem(int cap, int* p2_out);
@@ -192,6 +193,7 @@ int build_tma_maps(orb_extractor* e, int batch) {
         const cuuint32_t estr[3] = {1, 1, 1};
         const cuuint32_t box_blur[3] = {ORB_BLUR_BOXW, ORB_BLUR_BOXH, 1}, box_rz[3] = {ORB_RZ_BOXW, ORB_RZ_BOXH, 1};
         const cuuint32_t box_st_l[3] = {32, 11, 1}, box_st_r[3] = {48, 11, 1};
+        const cuuint32_t box_fast[3] = {80, (cuuint32_t)fast_box_rows(P), 1};
         const cuuint32_t box_od_raw[3] = {ORB_OD_RAW_BOXW, ORB_OD_RAW_BOXH, 1}, box_od_blur[3] = {ORB_OD_BLUR_BOXW, ORB_OD_BLUR_BOXH, 1};
         void* base = e->d_pyr + G.off;
         CUresult r = enc(&e->tm_blur.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box_blur, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -205,6 +207,10 @@ int build_tma_maps(orb_extractor* e, int batch) {
                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r == CUDA_SUCCESS)
             r = enc(&e->tm_od_blur.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, e->d_blur + G.off, dims, strides, box_od_blur, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        // the cell views of k_fast_cells
+        if (r == CUDA_SUCCESS)
+            r = enc(&e->tm_fast.lv[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box_fast, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         // the SAD windows of k_stereo_refine
         if (r == CUDA_SUCCESS)
@@ -314,7 +320,7 @@ int run_pipeline(orb_extractor* e, int b0, int batch) {
     if (T) cudaEventRecord(e->ev_stage[1], s);
     if (P.total_cells > 0) {
         ORB_NVTX("orb:fast_cells");
-        ORB_CUDA(launch_fast(s, e->d_pyr, cell_cnt, stage, P, batch)); e->launches++;
+        ORB_CUDA(launch_fast(s, e->tm_fast, cell_cnt, stage, Q, b0, batch)); e->launches++;
     }
     if (T) cudaEventRecord(e->ev_stage[2], s);
     {

@@ -97,6 +97,7 @@ struct orb_extractor {
     int last_batch = 0;
     TmaMaps tm_blur, tm_resize;     // rebuilt with the plan / batch layout
     TmaMaps tm_od_raw, tm_od_blur;  // patch boxes of k_orient_describe over d_pyr / d_blur
+    TmaMaps tm_fast;                // cell-view boxes of k_fast_cells over d_pyr: 80 x (tallest cell + 6)
     TmaMaps tm_st_l, tm_st_r;       // SAD window boxes of k_stereo_refine over d_pyr: 32 x 11 (a left handle's), 48 x 11 (a right handle's)
     bool rz_tma[ORB_MAX_LEVELS] = {false};   // level l is resampled from l-1 by the TMA-staged kernel
 

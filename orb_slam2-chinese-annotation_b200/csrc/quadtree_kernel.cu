@@ -405,5 +405,5 @@ cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefi
     if (e != cudaSuccess) return e;
     dim3 grid(batch, P.nlevels);
     kern<<<grid, nt, bytes, s>>>(cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, status, P, cap, p2);
-    return cudaSuccess;
+    return cudaGetLastError();
 }

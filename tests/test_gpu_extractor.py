@@ -16,6 +16,10 @@ CONFIGS = [  # (w, h, nfeatures)  BASELINE.json configs 1, 2, 3 + small/odd shap
     (752, 480, 1200),
     (333, 257, 500),
     (200, 120, 300),
+    # small levels make single very wide / tall FAST cells (window / floor(window / 30) up to 59 pixels): the per-warp shared memory
+    # of k_fast_cells plus its static mbarriers crosses the 48 KB default here (a refused launch once left stale lists behind)
+    (257, 193, 1000),
+    (179, 134, 1000),
 ]
 
 

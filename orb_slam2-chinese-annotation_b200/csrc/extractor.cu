@@ -415,6 +415,24 @@ int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w
     }
     return ORB_OK;
 }
+// The same in two steps for pipelines that keep the copy stream free of kernels (orb_stereo_frames_enqueue): the dense host batch
+// goes to the staging area on the copy stream; the ingest kernel that re-pitches it into level 0 runs on the handle's kernel
+// stream.  The copy then only depends on the PREVIOUS ingest of the same staging slots, not on every kernel that still reads level 0,
+// so uploads run a whole call ahead.  Returns 1 when the split form applies (dense images and a staging area), 0 otherwise.
+int orb_upload_can_split(const orb_extractor* e, int w, int h, int stride, size_t img_stride) {
+    return img_stride == (size_t)stride * h && stride == w && e->d_in != nullptr;
+}
+int orb_upload_copy_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, cudaStream_t st) {
+    ORB_CUDA(cudaMemcpyAsync(e->d_in + (size_t)b0 * w * h, imgs + (size_t)b0 * w * h, (size_t)n * w * h, cudaMemcpyHostToDevice, st));
+    return ORB_OK;
+}
+int orb_ingest_slots(orb_extractor* e, int b0, int n, int w, int h, cudaStream_t st) {
+    ORB_NVTX("orb:ingest");
+    const LevelGeom& G0 = e->plan.lv[0];
+    launch_ingest(st, e->d_in + (size_t)b0 * w * h, e->d_pyr + G0.off + (size_t)b0 * G0.img_stride, w, h, w, (size_t)w * h, G0.pitch, G0.img_stride, n);
+    e->launches++;
+    return ORB_OK;
+}
 // Results of slots [b0, b0 + n) -> the caller's [batch][cap] arrays; counts land in e->h_counts.
 // Whole slot rows are copied (one strided copy per array): the tail beyond counts[b] is unspecified.
 int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st, int* h_counts) {

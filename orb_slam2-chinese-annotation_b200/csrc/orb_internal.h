@@ -148,6 +148,7 @@ struct orb_extractor {
     int* h_status = nullptr;        // pinned [4]: device status words (left, right) per ticket parity
     // asynchronous stereo batches (orb_stereo_frames_enqueue / _wait); state lives in the LEFT handle
     int inflight = 0, next_ticket = 0, pipe_chunks = 0;
+    bool pipe_split = false;        // the last enqueued call kept its ingest kernels on the kernel streams (dense images)
     int pipe_batch[2] = {0, 0}, pipe_cap[2] = {0, 0};
     cudaEvent_t ev_call[2] = {nullptr, nullptr};
     bool copy_only = false;         // diagnostic: host-buffer entry points skip the kernels (copy ceiling of the pipeline)
@@ -163,6 +164,9 @@ int orb_chunk_size(int batch);
 // chunk boundaries of a host batch: bounds[0] = 0 < ... < bounds[n] = batch (ramped sizes, see extractor.cu)
 std::vector<int> orb_chunk_bounds(int batch);
 int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, int stride, size_t img_stride, cudaStream_t st);
+int orb_upload_can_split(const orb_extractor* e, int w, int h, int stride, size_t img_stride);
+int orb_upload_copy_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, cudaStream_t st);
+int orb_ingest_slots(orb_extractor* e, int b0, int n, int w, int h, cudaStream_t st);
 int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st, int* h_counts = nullptr);
 // NVTX ranges around the stages (host-side enqueue; profilers project them onto the stream).  Header-only NVTX3: no-ops unless a
 // tool injects itself.

@@ -461,8 +461,11 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
     if (st != ORB_OK) return st;
     const std::vector<int> cb = orb_chunk_bounds(batch);
     const int nch = (int)cb.size() - 1;
-    // events per chunk: upload left / right done, kernels done, downloads done; + 2 for the call
-    if (!orb_pool_event(l, 4 * nch + 4)) { orb_set_error("event"); return ORB_ERR_CUDA; }
+    // events per chunk: upload left / right done, kernels done, downloads done; + 2 for the call; then ingest left / right done per chunk
+    if (!orb_pool_event(l, 6 * nch + 4)) { orb_set_error("event"); return ORB_ERR_CUDA; }
+    // dense images + staging area: copies on the copy stream, ingest kernels on the kernel streams (uploads run a call ahead)
+    const bool split = orb_upload_can_split(l, w, h, stride, img_stride) && orb_upload_can_split(r, w, h, stride, img_stride);
+    const bool was_split = l->pipe_split;
     const int tk = l->next_ticket & 1;
     // uploads must not overtake work already queued on the two kernel streams by other entry points
     if (l->inflight == 0) {
@@ -483,21 +486,44 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
     for (int c = 0; c < nch; ++c) {
         const int b0 = cb[c], n = cb[c + 1] - cb[c];
         cudaEvent_t up_l = l->ev_pool[4 * c], up_r = l->ev_pool[4 * c + 1], done = l->ev_pool[4 * c + 2], dl = l->ev_pool[4 * c + 3];
+        cudaEvent_t ing_l = l->ev_pool[4 * nch + 4 + 2 * c], ing_r = l->ev_pool[4 * nch + 5 + 2 * c];
         if (chained) {   // events still hold the previous call's records for this chunk
-            ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, done, 0));     // its kernels have read the slot's images
+            if (split && was_split) {   // the copy only overwrites the staging slots: their previous ingest must be done
+                ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, ing_l, 0));
+                ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, ing_r, 0));
+                ORB_CUDA(cudaStreamWaitEvent(l->stream, done, 0));   // the ingest overwrites level 0: every reader of the slot must be done
+                ORB_CUDA(cudaStreamWaitEvent(r->stream, done, 0));
+            } else {
+                ORB_CUDA(cudaStreamWaitEvent(l->s_h2d, done, 0));     // its kernels have read the slot's images
+            }
             ORB_CUDA(cudaStreamWaitEvent(l->stream, dl, 0));      // its results have left the slot
             ORB_CUDA(cudaStreamWaitEvent(r->stream, dl, 0));
         }
         // Frame::Frame: ExtractORB(0, left) and ExtractORB(1, right) run side by side (src/Frame.cc:81-84) ...
-        if ((st = orb_upload_slots(l, imgs_l, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
-        ORB_CUDA(cudaEventRecord(up_l, l->s_h2d));
-        if ((st = orb_upload_slots(r, imgs_r, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
-        ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
-        ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
         const bool skip = l->copy_only;
-        if (!skip && (st = orb_run_slots(l, b0, n)) != ORB_OK) break;
-        ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
-        if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
+        if (split) {
+            if ((st = orb_upload_copy_slots(l, imgs_l, b0, n, w, h, l->s_h2d)) != ORB_OK) break;
+            ORB_CUDA(cudaEventRecord(up_l, l->s_h2d));
+            if ((st = orb_upload_copy_slots(r, imgs_r, b0, n, w, h, l->s_h2d)) != ORB_OK) break;
+            ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
+            ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
+            if ((st = orb_ingest_slots(l, b0, n, w, h, l->stream)) != ORB_OK) break;
+            ORB_CUDA(cudaEventRecord(ing_l, l->stream));
+            if (!skip && (st = orb_run_slots(l, b0, n)) != ORB_OK) break;
+            ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
+            if ((st = orb_ingest_slots(r, b0, n, w, h, r->stream)) != ORB_OK) break;
+            ORB_CUDA(cudaEventRecord(ing_r, r->stream));
+            if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
+        } else {
+            if ((st = orb_upload_slots(l, imgs_l, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
+            ORB_CUDA(cudaEventRecord(up_l, l->s_h2d));
+            if ((st = orb_upload_slots(r, imgs_r, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
+            ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
+            ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
+            if (!skip && (st = orb_run_slots(l, b0, n)) != ORB_OK) break;
+            ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
+            if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
+        }
         // ... then ComputeStereoMatches (:95)
         if (!skip && (st = stereo_launch(l, r, b0, n, mbf, min_d, max_d, false)) != ORB_OK) break;
         if (skip) {   // copy-only diagnostic: keep the stream dependencies of the real pipeline
@@ -524,7 +550,7 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
     ORB_CUDA(cudaMemcpyAsync(&l->h_status[2 * tk], l->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->s_d2h));
     ORB_CUDA(cudaMemcpyAsync(&l->h_status[2 * tk + 1], r->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->s_d2h));
     ORB_CUDA(cudaEventRecord(l->ev_call[tk], l->s_d2h));
-    l->pipe_chunks = nch;
+    l->pipe_chunks = nch; l->pipe_split = split;
     l->pipe_batch[tk] = batch; l->pipe_cap[tk] = cap;
     *ticket = l->next_ticket++;
     l->inflight++;

@@ -686,7 +686,7 @@ def run_ours(args):
     n_kp = float(np.mean(counts))
 
     # ---- e2e through the C ABI with pinned host buffers
-    e_steps = max(3, args.steps // 2)
+    e_steps = max(3, args.steps // 2, int(math.ceil(1000.0 / (ms_total / args.steps))))   # >= 1 s of host-buffer steps: the link settles
     e_ms, h2d, d2h = job.e2e(e_steps)
     e_val = world * B * e_steps / (e_ms * 1e-3)
     parity = check_parity(job, [0, 1, B // 2, B - 1]) if rank == 0 else 0

@@ -900,6 +900,42 @@ def bench_matching(local):
         n_sp, _ = one.SearchByProjection(frames[0], mps, 3.0, occ1)
     sp_ms = (time.perf_counter() - t0) / reps * 1e3
     out["search_by_projection_single_call"] = {"ms_per_frame": sp_ms, "frames_per_s": 1e3 / sp_ms, "matches": int(n_sp), "th": 3.0}
+
+    # ---- M7 SearchByBoW(KF, F) (src/ORBmatcher.cc:164-306) and M8 SearchForTriangulation (:718-900): one call per keyframe pair as
+    # Tracking / LocalMapping make it (host merge-join of the feature vectors + device distances + resolve), beside the oracle port
+    def single(call, reps=30):
+        for _ in range(3):
+            call()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            r = call()
+        return (time.perf_counter() - t0) / reps * 1e3, r
+    bow = [synth.make_bow_scenario(N, N - 100, i) for i in range(4)]
+    bf = [(views.Frame(a["x"], a["y"], a["octave"], a["angle"], a["desc"], a["sf"], a["bounds"], a["u_right"]),
+           views.Frame(b["x"], b["y"], b["octave"], b["angle"], b["desc"], b["sf"], b["bounds"], b["u_right"]),
+           views.FeatureVector(fva), views.FeatureVector(fvb), ha, hb, a) for a, fva, b, fvb, ha, hb in bow]
+    one.mfNNratio = 0.7
+    kf, fr, va, vb, ha, hb, _ = bf[0]
+    ms7, (n7, m7) = single(lambda: one.SearchByBoW(kf, va, ha, fr, vb))
+    n7o, m7o = orc.search_by_bow(kf, va, ha, fr, vb, 0.7, True)
+    if n7 != n7o or not np.array_equal(m7, m7o):
+        raise SystemExit("bench.py: SearchByBoW differs from the oracle")
+    cpu7 = cpu_rate(lambda i: orc.search_by_bow(bf[i % 4][0], bf[i % 4][2], bf[i % 4][4], bf[i % 4][1], bf[i % 4][3], 0.7, True), 16 * cores)
+    out["SearchByBoW_single_call"] = {"ms_per_call": ms7, "calls_per_s": 1e3 / ms7, "matches": int(n7), "parity_checked": 1,
+                                      "cpu_baseline": {"value": cpu7, "unit": "calls/s", "cores": cores, "kind": "port",
+                                                       "sample": "%d calls of the oracle port on %d host threads" % (16 * cores, cores)}}
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32)   # pure x-translation: horizontal epipolar lines
+    sig2 = (bf[0][6]["sf"] * bf[0][6]["sf"]).astype(np.float32)
+    hb_t = [np.zeros(len(x[5]), bool) if x[5] is None else x[5] for x in bf]
+    ms8, (n8, p8) = single(lambda: one.SearchForTriangulation(kf, va, ha, fr, vb, hb_t[0], F12, (2000.0, 188.0), sig2, False))
+    n8o, m8o = orc.search_for_triangulation(kf, va, ha, fr, vb, hb_t[0], F12, (2000.0, 188.0), sig2, False, True)
+    if n8 != n8o or p8 != [(int(i), int(m8o[i])) for i in np.nonzero(m8o >= 0)[0]]:
+        raise SystemExit("bench.py: SearchForTriangulation differs from the oracle")
+    cpu8 = cpu_rate(lambda i: orc.search_for_triangulation(bf[i % 4][0], bf[i % 4][2], bf[i % 4][4], bf[i % 4][1], bf[i % 4][3], hb_t[i % 4], F12,
+                                                             (2000.0, 188.0), sig2, False, True), 16 * cores)
+    out["SearchForTriangulation_single_call"] = {"ms_per_call": ms8, "calls_per_s": 1e3 / ms8, "matches": int(n8), "parity_checked": 1,
+                                                 "cpu_baseline": {"value": cpu8, "unit": "calls/s", "cores": cores, "kind": "port",
+                                                                  "sample": "%d calls of the oracle port on %d host threads" % (16 * cores, cores)}}
     return out
 
 

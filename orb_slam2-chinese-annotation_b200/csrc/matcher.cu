@@ -659,16 +659,20 @@ k_bow_distances(int n_entries, const BowEntry* __restrict__ e, const uint8_t* __
     }
 }
 
-__global__ void __launch_bounds__(32)
-k_resolve_bow(int n_entries, const BowEntry* __restrict__ e, const uint32_t* __restrict__ cands, const float* __restrict__ kf_angle,
-              const float* __restrict__ f_angle, int n_f, float nn_ratio, int check_ori, int* __restrict__ match_f,
-              int* __restrict__ hist_idx, int* __restrict__ hist_bin, int* __restrict__ nmatches_out) {
-    __shared__ int s_cnt[32];
-    const int lane = threadIdx.x;
-    for (int i = lane; i < n_f; i += 32) match_f[i] = -1;
-    __syncwarp();
-    int nmatches = 0, n_hist = 0;
-    for (int w = 0; w < n_entries; ++w) {
+// Resolve of the BoW searches.  A keypoint of the second frame belongs to exactly one vocabulary node, so the claims of the reference's
+// loop (vpMapPointMatches[realIdxF] / vbMatched2[idx2]: a feature taken by an earlier query is skipped by later ones) never cross
+// node pairs: one warp per node pair walks that pair's queries in the reference's order; node pairs run side by side.  The accepted
+// matches land in hist_idx[entry] (-1: none; memset by the caller), k_bow_finish compacts them, counts and applies the rotation
+// histogram (whose outcome does not depend on the order in which matches were found).
+#define BOW_WARPS 8
+__global__ void __launch_bounds__(BOW_WARPS * 32)
+k_resolve_bow(int n_nodes, const int* __restrict__ node_start, const BowEntry* __restrict__ e, const uint32_t* __restrict__ cands,
+              const float* __restrict__ kf_angle, const float* __restrict__ f_angle, float nn_ratio, int check_ori, int* __restrict__ match_f,
+              int* __restrict__ hist_idx, int* __restrict__ hist_bin) {
+    const int lane = threadIdx.x & 31, k = blockIdx.x * BOW_WARPS + (threadIdx.x >> 5);
+    if (k >= n_nodes) return;
+    const int w1 = node_start[k + 1];
+    for (int w = node_start[k]; w < w1; ++w) {
         const BowEntry E = e[w];
         const int cnt = E.f1 - E.f0;
         Best2 v; v.b = 0xffffffffu; v.s = 0xffffffffu;
@@ -685,32 +689,25 @@ k_resolve_bow(int n_entries, const BowEntry* __restrict__ e, const uint32_t* __r
             const int idxF = (int)(cands[E.c_start + (v.b & 0xffffu)] & 0xffffu);
             if (lane == 0) {
                 match_f[idxF] = E.q_idx;
-                if (check_ori) { hist_idx[n_hist] = idxF; hist_bin[n_hist] = rot_bin(kf_angle[E.q_idx], f_angle[idxF]); }
+                hist_idx[w] = idxF;
+                if (check_ori) hist_bin[w] = rot_bin(kf_angle[E.q_idx], f_angle[idxF]);
             }
-            ++nmatches; ++n_hist;
         }
         __syncwarp();
     }
-    if (lane == 0) *nmatches_out = nmatches;
-    __syncwarp();
-    if (check_ori) rot_cull_warp(hist_idx, hist_bin, n_hist, match_f, nmatches_out, s_cnt);
 }
 
 // SearchByBoW(KF1, KF2) (reference :581-716): as k_resolve_bow but both features need a MapPoint, KF2
 // features are claimed through vbMatched2 (which the rotation cull does NOT release), the threshold is
 // strict (< TH_LOW) and the result is indexed by the KF1 feature.
-__global__ void __launch_bounds__(32)
-k_resolve_bow_kf(int n_entries, const BowEntry* __restrict__ e, const uint32_t* __restrict__ cands, const float* __restrict__ angle1,
-                 const float* __restrict__ angle2, int n1, int n2, const uint8_t* __restrict__ has2, uint8_t* __restrict__ closed2,
-                 float nn_ratio, int check_ori, int* __restrict__ match12, int* __restrict__ hist_idx, int* __restrict__ hist_bin,
-                 int* __restrict__ nmatches_out) {
-    __shared__ int s_cnt[32];
-    const int lane = threadIdx.x;
-    for (int i = lane; i < n1; i += 32) match12[i] = -1;
-    for (int i = lane; i < n2; i += 32) closed2[i] = has2[i] ? 0 : 1;   // !pMP2 (or bad) -> never a candidate
-    __syncwarp();
-    int nmatches = 0, n_hist = 0;
-    for (int w = 0; w < n_entries; ++w) {
+__global__ void __launch_bounds__(BOW_WARPS * 32)
+k_resolve_bow_kf(int n_nodes, const int* __restrict__ node_start, const BowEntry* __restrict__ e, const uint32_t* __restrict__ cands,
+                 const float* __restrict__ angle1, const float* __restrict__ angle2, uint8_t* __restrict__ closed2, float nn_ratio,
+                 int check_ori, int* __restrict__ match12, int* __restrict__ hist_idx, int* __restrict__ hist_bin) {
+    const int lane = threadIdx.x & 31, k = blockIdx.x * BOW_WARPS + (threadIdx.x >> 5);
+    if (k >= n_nodes) return;
+    const int w1 = node_start[k + 1];
+    for (int w = node_start[k]; w < w1; ++w) {
         const BowEntry E = e[w];
         const int cnt = E.f1 - E.f0;
         Best2 v; v.b = 0xffffffffu; v.s = 0xffffffffu;
@@ -727,15 +724,36 @@ k_resolve_bow_kf(int n_entries, const BowEntry* __restrict__ e, const uint32_t* 
             const int idx2 = (int)(cands[E.c_start + (v.b & 0xffffu)] & 0xffffu);
             if (lane == 0) {
                 match12[E.q_idx] = idx2; closed2[idx2] = 1;
-                if (check_ori) { hist_idx[n_hist] = E.q_idx; hist_bin[n_hist] = rot_bin(angle1[E.q_idx], angle2[idx2]); }
+                hist_idx[w] = E.q_idx;
+                if (check_ori) hist_bin[w] = rot_bin(angle1[E.q_idx], angle2[idx2]);
             }
-            ++nmatches; ++n_hist;
         }
         __syncwarp();
     }
-    if (lane == 0) *nmatches_out = nmatches;
+}
+__global__ void k_bow_closed_init(int n2, const uint8_t* __restrict__ has2, uint8_t* __restrict__ closed2) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n2) closed2[i] = has2[i] ? 0 : 1;   // !pMP2 (or bad) -> never a candidate
+}
+// One warp: compacts the per-entry matches (ascending entry == the reference's order), counts them, rotation histogram.
+__global__ void __launch_bounds__(32)
+k_bow_finish(int n_entries, int* __restrict__ hist_idx, int* __restrict__ hist_bin, int check_ori, int* __restrict__ match,
+             int* __restrict__ nmatches_out) {
+    __shared__ int s_cnt[32];
+    const int lane = threadIdx.x;
+    int n = 0;
+    for (int w0 = 0; w0 < n_entries; w0 += 32) {
+        const int w = w0 + lane;
+        const int idx = w < n_entries ? hist_idx[w] : -1;
+        const int bin = (check_ori && idx >= 0) ? hist_bin[w] : 0;
+        const unsigned m = __ballot_sync(0xffffffffu, idx >= 0);   // also orders this round's reads before the writes below
+        if (idx >= 0) { const int o = n + __popc(m & ((1u << lane) - 1)); hist_idx[o] = idx; hist_bin[o] = bin; }
+        n += __popc(m);
+        __syncwarp();
+    }
+    if (lane == 0) *nmatches_out = n;
     __syncwarp();
-    if (check_ori) rot_cull_warp(hist_idx, hist_bin, n_hist, match12, nmatches_out, s_cnt);
+    if (check_ori) rot_cull_warp(hist_idx, hist_bin, n, match, nmatches_out, s_cnt);
 }
 
 // SearchForInitialization (reference :429-578): sequential over the level-0 keypoints of F1; a candidate i2 is
@@ -1335,9 +1353,11 @@ int orb_search_by_bow(orb_matcher* m, const orb_frame_view* kf, const orb_featve
     std::vector<std::pair<int, int>> nodes;
     merge_join(kf_fv, f_fv, nodes);
     std::vector<BowEntry> entries;
+    std::vector<int> node_start;   // first entry of every node pair that has entries, then the total
     size_t total = 0;
     for (auto& ab : nodes) {
         const int f0 = f_fv->start[ab.second], f1 = f_fv->start[ab.second + 1];
+        const size_t first = entries.size();
         for (int p = kf_fv->start[ab.first]; p < kf_fv->start[ab.first + 1]; ++p) {
             const int qi = (int)kf_fv->items[p];
             if (qi < 0 || qi >= kf->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
@@ -1346,17 +1366,27 @@ int orb_search_by_bow(orb_matcher* m, const orb_frame_view* kf, const orb_featve
             entries.push_back(e);
             total += (size_t)(f1 - f0);
         }
+        if (entries.size() > first) node_start.push_back((int)first);
     }
     if ((st = ensure_cands(m, total)) != ORB_OK) return st;
-    const int ne = (int)entries.size();
+    const int ne = (int)entries.size(), nn = (int)node_start.size();
+    node_start.push_back(ne);
     const int n_items2 = f_fv->n_nodes ? f_fv->start[f_fv->n_nodes] : 0;
     for (int i = 0; i < n_items2; ++i) if (f_fv->items[i] >= (uint32_t)f->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
-    const BowEntry* de; const uint32_t* ditems; int *dmatch, *hidx, *hbin;
+    const BowEntry* de; const uint32_t* ditems; const int* dns; int *dmatch, *hidx, *hbin;
     if ((st = ws_upload(m, &de, entries.data(), ne)) != ORB_OK || (st = ws_upload(m, &ditems, f_fv->items, n_items2)) != ORB_OK ||
+        (st = ws_upload(m, &dns, node_start.data(), nn + 1)) != ORB_OK ||
         (st = ws_alloc(m, &dmatch, std::max(f->n, 1))) != ORB_OK || (st = ws_alloc(m, &hidx, std::max(ne, 1))) != ORB_OK ||
         (st = ws_alloc(m, &hbin, std::max(ne, 1))) != ORB_OK) return st;
-    if (ne > 0) { k_bow_distances<<<(ne * 32 + 255) / 256, 256, 0, m->stream>>>(ne, de, K.desc, F.desc, ditems, m->d_cands); m->launches++; }
-    k_resolve_bow<<<1, 32, 0, m->stream>>>(ne, de, m->d_cands, K.angle, F.angle, f->n, nn_ratio, check_orientation, dmatch, hidx, hbin, m->d_scal);
+    ORB_CUDA(cudaMemsetAsync(dmatch, 0xff, (size_t)std::max(f->n, 1) * 4, m->stream));
+    ORB_CUDA(cudaMemsetAsync(hidx, 0xff, (size_t)std::max(ne, 1) * 4, m->stream));
+    if (ne > 0) {
+        k_bow_distances<<<(ne * 32 + 255) / 256, 256, 0, m->stream>>>(ne, de, K.desc, F.desc, ditems, m->d_cands);
+        k_resolve_bow<<<(nn + BOW_WARPS - 1) / BOW_WARPS, BOW_WARPS * 32, 0, m->stream>>>(nn, dns, de, m->d_cands, K.angle, F.angle, nn_ratio,
+                                                                                          check_orientation, dmatch, hidx, hbin);
+        m->launches += 2;
+    }
+    k_bow_finish<<<1, 32, 0, m->stream>>>(ne, hidx, hbin, check_orientation, dmatch, m->d_scal);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
     if (f->n > 0) ORB_CUDA(cudaMemcpyAsync(match_f, dmatch, (size_t)f->n * 4, cudaMemcpyDeviceToHost, m->stream));
@@ -1559,9 +1589,11 @@ int orb_search_by_bow_keyframes(orb_matcher* m, const orb_frame_view* kf1, const
     std::vector<std::pair<int, int>> nodes;
     merge_join(fv1, fv2, nodes);
     std::vector<BowEntry> entries;
+    std::vector<int> node_start;   // first entry of every node pair that has entries, then the total
     size_t total = 0;
     for (auto& ab : nodes) {
         const int f0 = fv2->start[ab.second], f1 = fv2->start[ab.second + 1];
+        const size_t first = entries.size();
         for (int p = fv1->start[ab.first]; p < fv1->start[ab.first + 1]; ++p) {
             const int qi = (int)fv1->items[p];
             if (qi < 0 || qi >= kf1->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
@@ -1570,19 +1602,29 @@ int orb_search_by_bow_keyframes(orb_matcher* m, const orb_frame_view* kf1, const
             entries.push_back(e);
             total += (size_t)(f1 - f0);
         }
+        if (entries.size() > first) node_start.push_back((int)first);
     }
     if ((st = ensure_cands(m, total)) != ORB_OK) return st;
-    const int ne = (int)entries.size();
+    const int ne = (int)entries.size(), nn = (int)node_start.size();
+    node_start.push_back(ne);
     const int n_items2 = fv2->n_nodes ? fv2->start[fv2->n_nodes] : 0;
     for (int i = 0; i < n_items2; ++i) if (fv2->items[i] >= (uint32_t)kf2->n) { orb_set_error("FeatureVector index out of range"); return ORB_ERR_BAD_ARG; }
-    const BowEntry* de; const uint32_t* ditems; const uint8_t* dhas2; uint8_t* dclosed; int *dmatch, *hidx, *hbin;
+    const BowEntry* de; const uint32_t* ditems; const uint8_t* dhas2; const int* dns; uint8_t* dclosed; int *dmatch, *hidx, *hbin;
     if ((st = ws_upload(m, &de, entries.data(), ne)) != ORB_OK || (st = ws_upload(m, &ditems, fv2->items, n_items2)) != ORB_OK ||
+        (st = ws_upload(m, &dns, node_start.data(), nn + 1)) != ORB_OK ||
         (st = ws_upload(m, &dhas2, kf2_has_mappoint, kf2->n)) != ORB_OK || (st = ws_alloc(m, &dclosed, std::max(kf2->n, 1))) != ORB_OK ||
         (st = ws_alloc(m, &dmatch, std::max(kf1->n, 1))) != ORB_OK || (st = ws_alloc(m, &hidx, std::max(ne, 1))) != ORB_OK ||
         (st = ws_alloc(m, &hbin, std::max(ne, 1))) != ORB_OK) return st;
-    if (ne > 0) { k_bow_distances<<<(ne * 32 + 255) / 256, 256, 0, m->stream>>>(ne, de, K1.desc, K2.desc, ditems, m->d_cands); m->launches++; }
-    k_resolve_bow_kf<<<1, 32, 0, m->stream>>>(ne, de, m->d_cands, K1.angle, K2.angle, kf1->n, kf2->n, dhas2, dclosed, nn_ratio,
-                                              check_orientation, dmatch, hidx, hbin, m->d_scal);
+    ORB_CUDA(cudaMemsetAsync(dmatch, 0xff, (size_t)std::max(kf1->n, 1) * 4, m->stream));
+    ORB_CUDA(cudaMemsetAsync(hidx, 0xff, (size_t)std::max(ne, 1) * 4, m->stream));
+    if (ne > 0) {
+        k_bow_closed_init<<<(kf2->n + 255) / 256, 256, 0, m->stream>>>(kf2->n, dhas2, dclosed);
+        k_bow_distances<<<(ne * 32 + 255) / 256, 256, 0, m->stream>>>(ne, de, K1.desc, K2.desc, ditems, m->d_cands);
+        k_resolve_bow_kf<<<(nn + BOW_WARPS - 1) / BOW_WARPS, BOW_WARPS * 32, 0, m->stream>>>(nn, dns, de, m->d_cands, K1.angle, K2.angle, dclosed, nn_ratio,
+                                                                                             check_orientation, dmatch, hidx, hbin);
+        m->launches += 3;
+    }
+    k_bow_finish<<<1, 32, 0, m->stream>>>(ne, hidx, hbin, check_orientation, dmatch, m->d_scal);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
     if (kf1->n > 0) ORB_CUDA(cudaMemcpyAsync(match12, dmatch, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, m->stream));

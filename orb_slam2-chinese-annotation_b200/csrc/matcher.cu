@@ -29,6 +29,14 @@ struct orb_matcher {
     size_t cands_cap = 0;
     int* d_scal = nullptr;     // small device scalars
     long long last_cands = 0;  // candidates examined by the last projection search (bench: popc work)
+    // Small host arrays of a call (a frame's SoA fields, the points' fields: a dozen of them) are copied into a pinned mirror of the
+    // workspace first; runs of adjacent ones then cross the link as ONE cudaMemcpyAsync, issued right before the first kernel that can
+    // read them (ws_stream).  A dozen pageable copies of a few KB each cost more than the kernels of a single-frame search.
+    uint8_t* h_stage = nullptr;
+    size_t h_stage_cap = 0;
+    std::vector<std::pair<size_t, size_t>> pend;   // staged, not yet copied: (workspace offset, bytes), ascending
+    cudaEvent_t ev_stage = nullptr;
+    bool stage_busy = false;
 };
 
 namespace {
@@ -87,11 +95,30 @@ int ws_alloc(orb_matcher* m, T** p, size_t count) {
 template <typename T>
 int ws_upload(orb_matcher* m, const T** dp, const T* host, size_t count) {
     T* p = nullptr;
+    const size_t off = m->ws_off;
     int st = ws_alloc(m, &p, std::max<size_t>(count, 1));
     if (st != ORB_OK) return st;
-    if (count) ORB_CUDA(cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, m->stream));
+    const size_t bytes = count * sizeof(T);
+    if (count && m->h_stage && bytes <= (1u << 20) && m->ws_off <= m->h_stage_cap) {
+        std::memcpy(m->h_stage + off, host, bytes);
+        const size_t padded = m->ws_off - off;   // the allocation's padding travels along (it belongs to nobody else)
+        if (!m->pend.empty() && m->pend.back().first + m->pend.back().second == off) m->pend.back().second += padded;
+        else m->pend.push_back(std::make_pair(off, padded));
+    } else if (count) {
+        ORB_CUDA(cudaMemcpyAsync(p, host, bytes, cudaMemcpyHostToDevice, m->stream));
+    }
     *dp = p;
     return ORB_OK;
+}
+// The stream argument of every kernel launch of this file: staged uploads go out first.
+static cudaStream_t ws_stream(orb_matcher* m) {
+    if (!m->pend.empty()) {
+        for (const auto& sg : m->pend) cudaMemcpyAsync(m->d_ws + sg.first, m->h_stage + sg.first, sg.second, cudaMemcpyHostToDevice, m->stream);
+        cudaEventRecord(m->ev_stage, m->stream);
+        m->stage_busy = true;
+        m->pend.clear();
+    }
+    return m->stream;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -139,19 +166,26 @@ k_bruteforce(const uint8_t* __restrict__ A, const uint8_t* __restrict__ Bm, int 
 
 // ------------------------------------------------------------------------------------------
 // Frame::AssignFeaturesToGrid: cell = round((x - minX) * invW), round((y - minY) * invH); lists in
-// ascending keypoint index (insertion order).  One CTA: bitonic sort of (cell << 16 | index).
+// ascending keypoint index (insertion order).  One CTA.  Counting sort by cell (shared-memory atomics, a block-wide scan of the 3072
+// cell counts, unordered scatter), then every cell's short list is put in ascending index order by one thread (insertion sort).
+// A cell with more than GRID_SMALL keypoints (degenerate: all features in a few cells) takes the bitonic sort of (cell << 16 | index).
+#define GRID_SMALL 48
 __global__ void __launch_bounds__(1024)
 k_grid_build(const float* __restrict__ x, const float* __restrict__ y, int n, int p2, orb_grid_params g, int* __restrict__ cell_start,
              int* __restrict__ cell_items, int* __restrict__ n_items, int stride = 0, const int* __restrict__ n_arr = nullptr) {
     extern __shared__ uint32_t keys[];
     __shared__ int cnt[GRID_CELLS + 1];
-    const int tid = threadIdx.x;
+    __shared__ int cur[GRID_CELLS];
+    __shared__ int s_warp[33];
+    __shared__ int s_max;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (stride) {   // one CTA per frame of a batch
         const size_t o = (size_t)blockIdx.x * stride;
         x += o; y += o; cell_items += o; cell_start += (size_t)blockIdx.x * (GRID_CELLS + 1); n_items += blockIdx.x;
         n = n_arr[blockIdx.x];
     }
     for (int i = tid; i <= GRID_CELLS; i += 1024) cnt[i] = 0;
+    if (tid == 0) s_max = 0;
     __syncthreads();
     for (int i = tid; i < p2; i += 1024) {
         uint32_t k = 0xffffffffu;
@@ -161,34 +195,72 @@ k_grid_build(const float* __restrict__ x, const float* __restrict__ y, int n, in
             if (px >= 0 && px < GRID_COLS && py >= 0 && py < GRID_ROWS) {
                 const int c = px * GRID_ROWS + py;
                 k = ((uint32_t)c << 16) | (uint32_t)i;
-                atomicAdd(&cnt[c], 1);
+                atomicMax(&s_max, atomicAdd(&cnt[c], 1) + 1);
             }
         }
         keys[i] = k;
     }
     __syncthreads();
-    for (int k = 2; k <= p2; k <<= 1)
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = tid; i < p2; i += 1024) {
-                const int ixj = i ^ j;
-                if (ixj > i) {
-                    const uint32_t a = keys[i], b = keys[ixj];
-                    const bool up = (i & k) == 0;
-                    if (up ? (a > b) : (a < b)) { keys[i] = b; keys[ixj] = a; }
+    const bool small = s_max <= GRID_SMALL;
+    if (!small) {
+        for (int k = 2; k <= p2; k <<= 1)
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int i = tid; i < p2; i += 1024) {
+                    const int ixj = i ^ j;
+                    if (ixj > i) {
+                        const uint32_t a = keys[i], b = keys[ixj];
+                        const bool up = (i & k) == 0;
+                        if (up ? (a > b) : (a < b)) { keys[i] = b; keys[ixj] = a; }
+                    }
                 }
+                __syncthreads();
             }
-            __syncthreads();
+    }
+    // exclusive scan of the 3072 counts: three consecutive cells per thread, warp scan, scan of the 32 warp totals
+    static_assert(GRID_CELLS == 3 * 1024, "three cells per thread");
+    {
+        const int c0 = cnt[3 * tid], c1 = cnt[3 * tid + 1], c2 = cnt[3 * tid + 2];
+        const int mine = c0 + c1 + c2;
+        int inc = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            const int w = s_warp[lane];
+            int wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += v; }
+            s_warp[lane] = wi - w;
+            if (lane == 31) s_warp[32] = wi;
         }
-    if (tid == 0) {  // 3072-entry exclusive scan
-        int run = 0;
-        for (int c = 0; c < GRID_CELLS; ++c) { const int v = cnt[c]; cnt[c] = run; run += v; }
-        cnt[GRID_CELLS] = run;
-        *n_items = run;
+        __syncthreads();
+        const int ex = s_warp[warp] + inc - mine;
+        cnt[3 * tid] = ex; cnt[3 * tid + 1] = ex + c0; cnt[3 * tid + 2] = ex + c0 + c1;
+        cur[3 * tid] = ex; cur[3 * tid + 1] = ex + c0; cur[3 * tid + 2] = ex + c0 + c1;
+        if (tid == 0) { cnt[GRID_CELLS] = s_warp[32]; *n_items = s_warp[32]; }
     }
     __syncthreads();
     for (int i = tid; i <= GRID_CELLS; i += 1024) cell_start[i] = cnt[i];
     const int total = cnt[GRID_CELLS];
-    for (int i = tid; i < total; i += 1024) cell_items[i] = (int)(keys[i] & 0xffffu);
+    if (!small) {
+        for (int i = tid; i < total; i += 1024) cell_items[i] = (int)(keys[i] & 0xffffu);
+        return;
+    }
+    for (int i = tid; i < n; i += 1024) {
+        const uint32_t k = keys[i];
+        if (k != 0xffffffffu) cell_items[atomicAdd(&cur[k >> 16], 1)] = i;
+    }
+    __syncthreads();
+    for (int c = tid; c < GRID_CELLS; c += 1024) {   // ascending index inside the cell
+        const int a = cnt[c], b = cnt[c + 1];
+        for (int i = a + 1; i < b; ++i) {
+            const int v = cell_items[i];
+            int j = i - 1;
+            while (j >= a && cell_items[j] > v) { cell_items[j + 1] = cell_items[j]; --j; }
+            cell_items[j + 1] = v;
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -613,6 +685,89 @@ k_resolve_projection(int mode, int nq, const Query* __restrict__ q, const int* _
     if (mode >= 1 && check_ori) rot_cull_warp(hist_idx, hist_bin, n_hist, match, nmatches_out, s_cnt);
 }
 
+// The same resolve for ONE frame pair per call (a live Tracking thread), in parallel.  The reference's loop is sequential only through
+// the claims: point w sees a keypoint as closed iff the caller closed it or an EARLIER point u < w claimed it.  So the decisions are the
+// fixpoint of  decision[w] = f(first_claim[k] < w for the candidates k of w),  first_claim[k] = min { u : decision[u] claims k }:
+// every round all points decide side by side against the claims of the previous round (one thread per point: lists hold a few
+// candidates), the claims are rebuilt with atomicMin, and the loop ends when no decision changed.  After round r the decisions of the
+// points 0 .. r - 1 are final, so it terminates; on real data three to five rounds.  match[k] is the LAST accepted point on k (a later
+// point overwrites an earlier, non-closing one), the rotation histogram does not depend on the order of the matches.
+#define RPP_THREADS 1024
+__global__ void __launch_bounds__(RPP_THREADS)
+k_resolve_projection_par(int mode, int nq, const int* __restrict__ starts, const uint32_t* __restrict__ cands, const uint8_t* __restrict__ blocks,
+                         const float* __restrict__ q_angle, DFrame F, const uint8_t* __restrict__ occupied, float nn_ratio, int check_ori,
+                         int max_dist, int* __restrict__ match, int* __restrict__ q_best_idx, int* __restrict__ q_best_dist,
+                         int* __restrict__ hist_idx, int* __restrict__ hist_bin, int* __restrict__ nmatches_out, int* __restrict__ first_claim,
+                         int* __restrict__ decision) {
+    __shared__ int s_cnt[32];
+    __shared__ int s_changed, s_nm, s_nh;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < F.n; i += RPP_THREADS) { first_claim[i] = 0x7fffffff; match[i] = -1; }
+    for (int w = tid; w < nq; w += RPP_THREADS) decision[w] = -2;   // no decision yet
+    if (tid == 0) { s_nm = 0; s_nh = 0; }
+    __syncthreads();
+    for (;;) {
+        if (tid == 0) s_changed = 0;
+        __syncthreads();
+        for (int w = tid; w < nq; w += RPP_THREADS) {
+            const int c0 = starts[w], c1 = starts[w + 1];
+            unsigned b = 0xffffffffu, sc = 0xffffffffu;
+            for (int p = c0; p < c1; ++p) {
+                const uint32_t c = cands[p];
+                const int k = (int)(c & 0xffffu);
+                if ((occupied && occupied[k]) || first_claim[k] < w) continue;
+                const unsigned key = (((c >> 16) & 0x1ffu) << 16) | (unsigned)(p - c0);
+                if (key < b) { sc = b; b = key; } else if (key < sc) sc = key;
+            }
+            int dec = -1;
+            if (b != 0xffffffffu) {
+                const int bestDist = (int)(b >> 16);
+                const uint32_t cb = cands[c0 + (b & 0xffffu)];
+                bool accept;
+                if (mode == 0) {
+                    accept = bestDist <= M_TH_HIGH;
+                    if (accept && sc != 0xffffffffu) {
+                        const uint32_t cs = cands[c0 + (sc & 0xffffu)];
+                        if ((cb >> 25) == (cs >> 25) && (float)bestDist > __fmul_rn(nn_ratio, (float)(int)(sc >> 16))) accept = false;
+                    }
+                } else if (mode == 1) accept = bestDist <= M_TH_HIGH;
+                else accept = bestDist <= max_dist;
+                if (accept) {
+                    const int blk = mode == 2 ? 1 : (int)blocks[w];
+                    dec = (int)(cb & 0xffffu) | (blk ? 0x40000000 : 0) | (bestDist << 16);   // keypoint | distance (9 bits) | closing flag
+                }
+            }
+            if (dec != decision[w]) { decision[w] = dec; s_changed = 1; }
+        }
+        __syncthreads();
+        if (!s_changed) break;
+        for (int i = tid; i < F.n; i += RPP_THREADS) first_claim[i] = 0x7fffffff;
+        __syncthreads();
+        for (int w = tid; w < nq; w += RPP_THREADS) {
+            const int dec = decision[w];
+            if (dec >= 0 && (dec & 0x40000000)) atomicMin(&first_claim[dec & 0xffff], w);
+        }
+        __syncthreads();
+    }
+    // outputs
+    for (int w = tid; w < nq; w += RPP_THREADS) {
+        const int dec = decision[w];
+        if (mode == 2) { q_best_idx[w] = dec >= 0 ? (dec & 0xffff) : -1; q_best_dist[w] = dec >= 0 ? ((dec >> 16) & 0x1ff) : 256; }
+        if (dec < 0) continue;
+        const int k = dec & 0xffff;
+        atomicMax(&match[k], w);
+        atomicAdd(&s_nm, 1);
+        if (mode >= 1 && check_ori) {
+            const int slot = atomicAdd(&s_nh, 1);
+            hist_idx[slot] = k; hist_bin[slot] = rot_bin(q_angle[w], F.angle[k]);
+        }
+    }
+    __syncthreads();
+    if (tid == 0) *nmatches_out = s_nm;
+    __syncthreads();
+    if (tid < 32 && mode >= 1 && check_ori) rot_cull_warp(hist_idx, hist_bin, s_nh, match, nmatches_out, s_cnt);
+}
+
 // Projected points WITHOUT claiming (SearchBySim3 :1212-1455 per direction, Fuse :903-1207): every point is
 // independent; one warp per point takes the first minimum-distance candidate (strict <).
 __global__ void __launch_bounds__(256)
@@ -928,7 +1083,7 @@ int upload_frame(orb_matcher* m, const orb_frame_view* f, DFrame* D, bool need_g
         while (p2 < std::max(f->n, 1)) p2 <<= 1;
         const size_t smem = (size_t)p2 * 4;
         if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_grid_build<<<1, 1024, smem, m->stream>>>(D->x, D->y, f->n, p2, f->grid, cs, ci, ni);
+        k_grid_build<<<1, 1024, smem, ws_stream(m)>>>(D->x, D->y, f->n, p2, f->grid, cs, ci, ni);
         m->launches++;
         D->cell_start = cs; D->cell_items = ci;
     }
@@ -960,6 +1115,8 @@ int begin_call(orb_matcher* m) {
     if (!m) return ORB_ERR_BAD_ARG;
     ORB_CUDA(cudaSetDevice(m->device));
     m->ws_off = 0;
+    m->pend.clear();
+    if (m->stage_busy) { ORB_CUDA(cudaEventSynchronize(m->ev_stage)); m->stage_busy = false; }   // the mirror is about to be rewritten
     return ORB_OK;
 }
 
@@ -991,6 +1148,14 @@ int orb_matcher_create(int max_pairs, int max_n, int device, orb_matcher** out) 
         orb_matcher_destroy(m);
         return ORB_ERR_CUDA;
     }
+    // pinned mirror of the head of the workspace (single-frame calls place their uploads there); optional: without it uploads go direct
+    m->h_stage_cap = std::min<size_t>(m->ws_cap, 4u << 20);
+    if (cudaMallocHost((void**)&m->h_stage, m->h_stage_cap) != cudaSuccess ||
+        cudaEventCreateWithFlags(&m->ev_stage, cudaEventDisableTiming) != cudaSuccess) {
+        cudaGetLastError();
+        if (m->h_stage) { cudaFreeHost(m->h_stage); m->h_stage = nullptr; }
+        m->h_stage_cap = 0;
+    }
     *out = m;
     return ORB_OK;
 }
@@ -999,6 +1164,8 @@ void orb_matcher_destroy(orb_matcher* m) {
     if (!m) return;
     cudaSetDevice(m->device);
     if (m->stream) cudaStreamSynchronize(m->stream);
+    if (m->h_stage) cudaFreeHost(m->h_stage);
+    if (m->ev_stage) cudaEventDestroy(m->ev_stage);
     orb_dev_free(m->d_ws); orb_dev_free(m->d_cands); orb_dev_free(m->d_scal);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
@@ -1024,7 +1191,7 @@ int orb_descriptor_distance(orb_matcher* m, const uint8_t* a, const uint8_t* b, 
     if ((st = ws_upload(m, &da, a, (size_t)n * 32)) != ORB_OK) return st;
     if ((st = ws_upload(m, &db, b, (size_t)n * 32)) != ORB_OK) return st;
     if ((st = ws_alloc(m, &dd, n)) != ORB_OK) return st;
-    k_distance_pairs<<<(n + 255) / 256, 256, 0, m->stream>>>(da, db, n, dd);
+    k_distance_pairs<<<(n + 255) / 256, 256, 0, ws_stream(m)>>>(da, db, n, dd);
     m->launches++;
     ORB_CUDA(cudaMemcpyAsync(dist, dd, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
     ORB_CUDA(cudaStreamSynchronize(m->stream));
@@ -1037,7 +1204,7 @@ int orb_match_bruteforce_device(orb_matcher* m, const uint8_t* d_a, const uint8_
     if (!m || !d_a || !d_b || !d_best_idx || !d_best_dist || !d_second_dist || pairs < 1 || n_a < 1 || n_b < 0) return ORB_ERR_BAD_ARG;
     ORB_CUDA(cudaSetDevice(m->device));
     dim3 grid((n_a + BF_THREADS - 1) / BF_THREADS, pairs);
-    k_bruteforce<<<grid, BF_THREADS, 0, m->stream>>>(d_a, d_b, n_a, n_b, d_best_idx, d_best_dist, d_second_dist);
+    k_bruteforce<<<grid, BF_THREADS, 0, ws_stream(m)>>>(d_a, d_b, n_a, n_b, d_best_idx, d_best_dist, d_second_dist);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
     return ORB_OK;
@@ -1075,7 +1242,7 @@ int orb_assign_features_to_grid(orb_matcher* m, const float* kp_x, const float* 
     while (p2 < std::max(n, 1)) p2 <<= 1;
     const size_t smem = (size_t)p2 * 4;
     if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_grid_build<<<1, 1024, smem, m->stream>>>(dx, dy, n, p2, *g, cs, ci, ni);
+    k_grid_build<<<1, 1024, smem, ws_stream(m)>>>(dx, dy, n, p2, *g, cs, ci, ni);
     m->launches++;
     ORB_CUDA(cudaMemcpyAsync(cell_start, cs, (GRID_CELLS + 1) * 4, cudaMemcpyDeviceToHost, m->stream));
     ORB_CUDA(cudaMemcpyAsync(n_items, ni, 4, cudaMemcpyDeviceToHost, m->stream));
@@ -1114,14 +1281,14 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
     const int filter = o.filter; const float* d_inv_sigma2 = o.d_inv_sigma2;
     if (nq > 0) {
         const int blocks = (nq * 32 + 255) / 256;
-        k_area_candidates<false><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, counts, nullptr, nullptr, Batch{0, nullptr, nullptr});
-        k_scan<<<1, 1024, 0, m->stream>>>(counts, nq, starts, Batch{0, nullptr, nullptr}, nullptr);
+        k_area_candidates<false><<<blocks, 256, 0, ws_stream(m)>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, counts, nullptr, nullptr, Batch{0, nullptr, nullptr});
+        k_scan<<<1, 1024, 0, ws_stream(m)>>>(counts, nq, starts, Batch{0, nullptr, nullptr}, nullptr);
         int total = 0;
         ORB_CUDA(cudaMemcpyAsync(&total, starts + nq, 4, cudaMemcpyDeviceToHost, m->stream));
         ORB_CUDA(cudaStreamSynchronize(m->stream));
         if ((st = ensure_cands(m, (size_t)total)) != ORB_OK) return st;
         m->last_cands = total;
-        k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, nullptr, starts, m->d_cands, Batch{0, nullptr, nullptr});
+        k_area_candidates<true><<<blocks, 256, 0, ws_stream(m)>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, nullptr, starts, m->d_cands, Batch{0, nullptr, nullptr});
         m->launches += 3;
     } else {
         ORB_CUDA(cudaMemsetAsync(starts, 0, 4, m->stream));
@@ -1129,13 +1296,16 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
     if (o.mode == -1) {
         ORB_CUDA(cudaMemsetAsync(m->d_scal, 0, 4, m->stream));
         if (nq > 0) {
-            k_best_independent<<<(nq * 32 + 255) / 256, 256, 0, m->stream>>>(nq, starts, m->d_cands, d_occupied, o.max_dist, qbi, qbd, m->d_scal);
+            k_best_independent<<<(nq * 32 + 255) / 256, 256, 0, ws_stream(m)>>>(nq, starts, m->d_cands, d_occupied, o.max_dist, qbi, qbd, m->d_scal);
             m->launches++;
         }
     } else {
-        const int occ_shared = F.n <= 40 * 1024;
-        k_resolve_projection<<<1, 32, occ_shared ? (size_t)((F.n + 15) & ~15) : 0, m->stream>>>(o.mode, nq, dq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied,
-                                                      occ, o.nn_ratio, o.check_ori, o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal, occ_shared, Batch{0, nullptr, nullptr});
+        // one frame pair per call: the parallel fixpoint resolve (the one-warp kernel serves the batched entry points, one warp per pair)
+        int *first_claim, *decision;
+        if ((st = ws_alloc(m, &first_claim, std::max(F.n, 1))) != ORB_OK || (st = ws_alloc(m, &decision, std::max(nq, 1))) != ORB_OK) return st;
+        (void)occ;
+        k_resolve_projection_par<<<1, RPP_THREADS, 0, ws_stream(m)>>>(o.mode, nq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied, o.nn_ratio, o.check_ori,
+                                                                   o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal, first_claim, decision);
         m->launches++;
     }
     ORB_CUDA(cudaGetLastError());
@@ -1163,7 +1333,7 @@ int orb_search_by_projection_mappoints(orb_matcher* m, const orb_frame_view* f, 
         (st = ws_upload(m, &dvc, mps->view_cos, nq)) != ORB_OK || (st = ws_upload(m, &dd, mps->desc, (size_t)nq * 32)) != ORB_OK ||
         (st = ws_upload(m, &db, mps->blocks, nq)) != ORB_OK || (st = ws_alloc(m, &dq, std::max(nq, 1))) != ORB_OK) return st;
     if (mps->proj_xr) { if ((st = ws_upload(m, &dxr, mps->proj_xr, nq)) != ORB_OK) return st; }
-    if (nq > 0) { k_prep_mappoints<<<(nq + 255) / 256, 256, 0, m->stream>>>(nq, dv, dx, dy, dxr, dl, dvc, th, F, dq, Batch{0, nullptr, nullptr}); m->launches++; }
+    if (nq > 0) { k_prep_mappoints<<<(nq + 255) / 256, 256, 0, ws_stream(m)>>>(nq, dv, dx, dy, dxr, dl, dvc, th, F, dq, Batch{0, nullptr, nullptr}); m->launches++; }
     ProjOpts o; o.mode = 0; o.nn_ratio = nn_ratio;
     return projection_common(m, o, nq, dq, dd, db, nullptr, F, occupied, match, nmatches);
 }
@@ -1185,7 +1355,7 @@ int orb_search_by_projection_lastframe(orb_matcher* m, const orb_frame_view* cur
         (st = ws_upload(m, &doct, last->octave, nq)) != ORB_OK || (st = ws_upload(m, &da, last->angle, nq)) != ORB_OK ||
         (st = ws_upload(m, &dd, last->desc, (size_t)nq * 32)) != ORB_OK || (st = ws_upload(m, &db, last->blocks, nq)) != ORB_OK ||
         (st = ws_alloc(m, &dq, std::max(nq, 1))) != ORB_OK) return st;
-    if (nq > 0) { k_prep_lastframe<<<(nq + 255) / 256, 256, 0, m->stream>>>(nq, dv, dx, dy, dz, doct, *cam, th, forward, backward, F, dq, Batch{0, nullptr, nullptr}, nullptr, nullptr); m->launches++; }
+    if (nq > 0) { k_prep_lastframe<<<(nq + 255) / 256, 256, 0, ws_stream(m)>>>(nq, dv, dx, dy, dz, doct, *cam, th, forward, backward, F, dq, Batch{0, nullptr, nullptr}, nullptr, nullptr); m->launches++; }
     ProjOpts o; o.mode = 1; o.check_ori = check_orientation;
     return projection_common(m, o, nq, dq, dd, db, da, F, occupied, match, nmatches);
 }
@@ -1233,7 +1403,7 @@ int upload_frame_batch(orb_matcher* m, const orb_frame_batch_view* f, DFrame* D,
     while (p2 < f->stride) p2 <<= 1;
     const size_t smem = (size_t)p2 * 4;
     if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_grid_build<<<f->pairs, 1024, smem, m->stream>>>(D->x, D->y, 0, p2, f->grid, cs, ci, ni, f->stride, D->n_arr);
+    k_grid_build<<<f->pairs, 1024, smem, ws_stream(m)>>>(D->x, D->y, 0, p2, f->grid, cs, ci, ni, f->stride, D->n_arr);
     m->launches++;
     D->cell_start = cs; D->cell_items = ci;
     return ORB_OK;
@@ -1253,9 +1423,9 @@ int projection_batch(orb_matcher* m, int mode, int pairs, int qstride, const int
     if (occupied) { if ((st = ws_upload_any(m, &d_occupied, occupied, ftot)) != ORB_OK) return st; }
     Batch B{qstride, d_nq, nullptr};
     const dim3 grid((unsigned)((qstride * 32 + 255) / 256), (unsigned)pairs);
-    k_area_candidates<false><<<grid, 256, 0, m->stream>>>(0, dq, d_qdesc, F, FILTER_STEREO_WINDOW, nullptr, counts, nullptr, nullptr, B);
-    k_scan<<<pairs, 1024, 0, m->stream>>>(counts, 0, starts, B, totals);
-    k_pair_bases<<<1, 32, 0, m->stream>>>(totals, pairs, bases);
+    k_area_candidates<false><<<grid, 256, 0, ws_stream(m)>>>(0, dq, d_qdesc, F, FILTER_STEREO_WINDOW, nullptr, counts, nullptr, nullptr, B);
+    k_scan<<<pairs, 1024, 0, ws_stream(m)>>>(counts, 0, starts, B, totals);
+    k_pair_bases<<<1, 32, 0, ws_stream(m)>>>(totals, pairs, bases);
     int total = 0;
     ORB_CUDA(cudaMemcpyAsync(&total, bases + pairs, 4, cudaMemcpyDeviceToHost, m->stream));
     ORB_CUDA(cudaStreamSynchronize(m->stream));
@@ -1263,9 +1433,9 @@ int projection_batch(orb_matcher* m, int mode, int pairs, int qstride, const int
     if ((st = ensure_cands(m, (size_t)total)) != ORB_OK) return st;
     m->last_cands = total;
     B.cand_base = bases;
-    k_area_candidates<true><<<grid, 256, 0, m->stream>>>(0, dq, d_qdesc, F, FILTER_STEREO_WINDOW, nullptr, nullptr, starts, m->d_cands, B);
+    k_area_candidates<true><<<grid, 256, 0, ws_stream(m)>>>(0, dq, d_qdesc, F, FILTER_STEREO_WINDOW, nullptr, nullptr, starts, m->d_cands, B);
     const int occ_shared = F.stride <= 40 * 1024;
-    k_resolve_projection<<<pairs, 32, occ_shared ? (size_t)((F.stride + 15) & ~15) : 0, m->stream>>>(mode, 0, dq, starts, m->d_cands, d_blocks, d_qangle, F,
+    k_resolve_projection<<<pairs, 32, occ_shared ? (size_t)((F.stride + 15) & ~15) : 0, ws_stream(m)>>>(mode, 0, dq, starts, m->d_cands, d_blocks, d_qangle, F,
                                                   d_occupied, occ, nn_ratio, check_ori, M_TH_HIGH, dmatch, nullptr, nullptr, hidx, hbin, dn, occ_shared, B);
     m->launches += 5;
     ORB_CUDA(cudaGetLastError());
@@ -1300,7 +1470,7 @@ int orb_search_by_projection_mappoints_batch(orb_matcher* m, const orb_frame_bat
     ORB_CUDA(cudaStreamSynchronize(m->stream));
     for (int p = 0; p < pairs; ++p)
         if (nf[p] < 0 || nf[p] > f->stride || nq[p] < 0 || nq[p] > qs) { orb_set_error("batch view: n[p] outside [0, stride]"); return ORB_ERR_BAD_ARG; }
-    k_prep_mappoints<<<dim3((unsigned)((qs + 255) / 256), (unsigned)pairs), 256, 0, m->stream>>>(0, dv, dx, dy, dxr, dl, dvc, th, F, dq, Batch{qs, dnq, nullptr});
+    k_prep_mappoints<<<dim3((unsigned)((qs + 255) / 256), (unsigned)pairs), 256, 0, ws_stream(m)>>>(0, dv, dx, dy, dxr, dl, dvc, th, F, dq, Batch{qs, dnq, nullptr});
     m->launches++;
     return projection_batch(m, 0, pairs, qs, dnq, dq, dd, db, nullptr, F, occupied, nn_ratio, 0, match, nmatches);
 }
@@ -1330,7 +1500,7 @@ int orb_search_by_projection_lastframe_batch(orb_matcher* m, const orb_frame_bat
     ORB_CUDA(cudaStreamSynchronize(m->stream));
     for (int p = 0; p < pairs; ++p)
         if (nf[p] < 0 || nf[p] > cur->stride || nq[p] < 0 || nq[p] > qs) { orb_set_error("batch view: n[p] outside [0, stride]"); return ORB_ERR_BAD_ARG; }
-    k_prep_lastframe<<<dim3((unsigned)((qs + 255) / 256), (unsigned)pairs), 256, 0, m->stream>>>(0, dv, dx, dy, dz, doct, *cam, th, 0, 0, F, dq, Batch{qs, dnq, nullptr},
+    k_prep_lastframe<<<dim3((unsigned)((qs + 255) / 256), (unsigned)pairs), 256, 0, ws_stream(m)>>>(0, dv, dx, dy, dz, doct, *cam, th, 0, 0, F, dq, Batch{qs, dnq, nullptr},
                                                                                               dfw, dbw);
     m->launches++;
     return projection_batch(m, 1, pairs, qs, dnq, dq, dd, db, da, F, occupied, 0.f, check_orientation, match, nmatches);
@@ -1381,12 +1551,12 @@ int orb_search_by_bow(orb_matcher* m, const orb_frame_view* kf, const orb_featve
     ORB_CUDA(cudaMemsetAsync(dmatch, 0xff, (size_t)std::max(f->n, 1) * 4, m->stream));
     ORB_CUDA(cudaMemsetAsync(hidx, 0xff, (size_t)std::max(ne, 1) * 4, m->stream));
     if (ne > 0) {
-        k_bow_distances<<<(ne * 32 + 255) / 256, 256, 0, m->stream>>>(ne, de, K.desc, F.desc, ditems, m->d_cands);
-        k_resolve_bow<<<(nn + BOW_WARPS - 1) / BOW_WARPS, BOW_WARPS * 32, 0, m->stream>>>(nn, dns, de, m->d_cands, K.angle, F.angle, nn_ratio,
+        k_bow_distances<<<(ne * 32 + 255) / 256, 256, 0, ws_stream(m)>>>(ne, de, K.desc, F.desc, ditems, m->d_cands);
+        k_resolve_bow<<<(nn + BOW_WARPS - 1) / BOW_WARPS, BOW_WARPS * 32, 0, ws_stream(m)>>>(nn, dns, de, m->d_cands, K.angle, F.angle, nn_ratio,
                                                                                           check_orientation, dmatch, hidx, hbin);
         m->launches += 2;
     }
-    k_bow_finish<<<1, 32, 0, m->stream>>>(ne, hidx, hbin, check_orientation, dmatch, m->d_scal);
+    k_bow_finish<<<1, 32, 0, ws_stream(m)>>>(ne, hidx, hbin, check_orientation, dmatch, m->d_scal);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
     if (f->n > 0) ORB_CUDA(cudaMemcpyAsync(match_f, dmatch, (size_t)f->n * 4, cudaMemcpyDeviceToHost, m->stream));
@@ -1433,8 +1603,8 @@ int orb_search_for_triangulation(orb_matcher* m, const orb_frame_view* kf1, cons
     for (int i = 0; i < 9; ++i) T.f12[i] = f12[i];
     T.ex = ex; T.ey = ey; T.only_stereo = only_stereo;
     for (int i = 0; i < ORB_MAX_LEVELS; ++i) T.sigma2[i] = i < kf2->n_levels ? level_sigma2[i] : 1.f;
-    if (ne > 0) { k_triangulation<<<(ne * 32 + 255) / 256, 256, 0, m->stream>>>(ne, de, K1, K2, ditems, dmp2, T, dmatch); m->launches++; }
-    k_tri_rot_cull<<<1, 32, 0, m->stream>>>(kf1->n, K1.angle, K2.angle, check_orientation, dmatch, hidx, hbin, m->d_scal);
+    if (ne > 0) { k_triangulation<<<(ne * 32 + 255) / 256, 256, 0, ws_stream(m)>>>(ne, de, K1, K2, ditems, dmp2, T, dmatch); m->launches++; }
+    k_tri_rot_cull<<<1, 32, 0, ws_stream(m)>>>(kf1->n, K1.angle, K2.angle, check_orientation, dmatch, hidx, hbin, m->d_scal);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
     if (kf1->n > 0) ORB_CUDA(cudaMemcpyAsync(match12, dmatch, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, m->stream));
@@ -1517,7 +1687,7 @@ int orb_search_by_sim3(orb_matcher* m, const orb_frame_view* kf1, const orb_proj
         (st = ws_alloc(m, &d12, std::max(kf1->n, 1))) != ORB_OK) return st;
     ORB_CUDA(cudaMemsetAsync(m->d_scal, 0, 4, m->stream));
     if (kf1->n > 0) {
-        k_mutual_check<<<(kf1->n + 255) / 256, 256, 0, m->stream>>>(kf1->n, kf2->n, d1, d2, d12, m->d_scal);
+        k_mutual_check<<<(kf1->n + 255) / 256, 256, 0, ws_stream(m)>>>(kf1->n, kf2->n, d1, d2, d12, m->d_scal);
         m->launches++;
         ORB_CUDA(cudaGetLastError());
         ORB_CUDA(cudaMemcpyAsync(match12, d12, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, m->stream));
@@ -1555,18 +1725,18 @@ int orb_search_for_initialization(orb_matcher* m, const orb_frame_view* f1, cons
     if (f1->angle) { if ((st = ws_upload(m, &da1, f1->angle, (size_t)nq)) != ORB_OK) return st; }
     if (nq > 0) {
         const int blocks = (nq * 32 + 255) / 256;
-        k_area_candidates<false><<<blocks, 256, 0, m->stream>>>(nq, dq, dd, F2, FILTER_NONE, nullptr, counts, nullptr, nullptr, Batch{0, nullptr, nullptr});
-        k_scan<<<1, 1024, 0, m->stream>>>(counts, nq, starts, Batch{0, nullptr, nullptr}, nullptr);
+        k_area_candidates<false><<<blocks, 256, 0, ws_stream(m)>>>(nq, dq, dd, F2, FILTER_NONE, nullptr, counts, nullptr, nullptr, Batch{0, nullptr, nullptr});
+        k_scan<<<1, 1024, 0, ws_stream(m)>>>(counts, nq, starts, Batch{0, nullptr, nullptr}, nullptr);
         int total = 0;
         ORB_CUDA(cudaMemcpyAsync(&total, starts + nq, 4, cudaMemcpyDeviceToHost, m->stream));
         ORB_CUDA(cudaStreamSynchronize(m->stream));
         if ((st = ensure_cands(m, (size_t)total)) != ORB_OK) return st;
-        k_area_candidates<true><<<blocks, 256, 0, m->stream>>>(nq, dq, dd, F2, FILTER_NONE, nullptr, nullptr, starts, m->d_cands, Batch{0, nullptr, nullptr});
+        k_area_candidates<true><<<blocks, 256, 0, ws_stream(m)>>>(nq, dq, dd, F2, FILTER_NONE, nullptr, nullptr, starts, m->d_cands, Batch{0, nullptr, nullptr});
         m->launches += 3;
     } else {
         ORB_CUDA(cudaMemsetAsync(starts, 0, 4, m->stream));
     }
-    k_resolve_initialization<<<1, 32, 0, m->stream>>>(nq, starts, m->d_cands, da1, F2.angle, f2->n, nn_ratio, check_orientation, d12, d21, dmd,
+    k_resolve_initialization<<<1, 32, 0, ws_stream(m)>>>(nq, starts, m->d_cands, da1, F2.angle, f2->n, nn_ratio, check_orientation, d12, d21, dmd,
                                                       hidx, hbin, m->d_scal);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
@@ -1618,13 +1788,13 @@ int orb_search_by_bow_keyframes(orb_matcher* m, const orb_frame_view* kf1, const
     ORB_CUDA(cudaMemsetAsync(dmatch, 0xff, (size_t)std::max(kf1->n, 1) * 4, m->stream));
     ORB_CUDA(cudaMemsetAsync(hidx, 0xff, (size_t)std::max(ne, 1) * 4, m->stream));
     if (ne > 0) {
-        k_bow_closed_init<<<(kf2->n + 255) / 256, 256, 0, m->stream>>>(kf2->n, dhas2, dclosed);
-        k_bow_distances<<<(ne * 32 + 255) / 256, 256, 0, m->stream>>>(ne, de, K1.desc, K2.desc, ditems, m->d_cands);
-        k_resolve_bow_kf<<<(nn + BOW_WARPS - 1) / BOW_WARPS, BOW_WARPS * 32, 0, m->stream>>>(nn, dns, de, m->d_cands, K1.angle, K2.angle, dclosed, nn_ratio,
+        k_bow_closed_init<<<(kf2->n + 255) / 256, 256, 0, ws_stream(m)>>>(kf2->n, dhas2, dclosed);
+        k_bow_distances<<<(ne * 32 + 255) / 256, 256, 0, ws_stream(m)>>>(ne, de, K1.desc, K2.desc, ditems, m->d_cands);
+        k_resolve_bow_kf<<<(nn + BOW_WARPS - 1) / BOW_WARPS, BOW_WARPS * 32, 0, ws_stream(m)>>>(nn, dns, de, m->d_cands, K1.angle, K2.angle, dclosed, nn_ratio,
                                                                                              check_orientation, dmatch, hidx, hbin);
         m->launches += 3;
     }
-    k_bow_finish<<<1, 32, 0, m->stream>>>(ne, hidx, hbin, check_orientation, dmatch, m->d_scal);
+    k_bow_finish<<<1, 32, 0, ws_stream(m)>>>(ne, hidx, hbin, check_orientation, dmatch, m->d_scal);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
     if (kf1->n > 0) ORB_CUDA(cudaMemcpyAsync(match12, dmatch, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, m->stream));
@@ -1742,7 +1912,7 @@ int orb_is_in_frustum(orb_matcher* m, const float* rcw, const float* tcw, const 
         (st = ws_upload(m, &dmin, min_distance, n)) != ORB_OK || (st = ws_upload(m, &dmax, max_distance, n)) != ORB_OK ||
         (st = ws_alloc(m, &du, n)) != ORB_OK || (st = ws_alloc(m, &dv, n)) != ORB_OK || (st = ws_alloc(m, &dur, n)) != ORB_OK ||
         (st = ws_alloc(m, &dc, n)) != ORB_OK || (st = ws_alloc(m, &dd, n)) != ORB_OK || (st = ws_alloc(m, &dok, n)) != ORB_OK) return st;
-    k_is_in_frustum<<<(n + 255) / 256, 256, 0, m->stream>>>(n, dx, dn, dmin, dmax, rcw[0], rcw[1], rcw[2], rcw[3], rcw[4], rcw[5], rcw[6], rcw[7], rcw[8],
+    k_is_in_frustum<<<(n + 255) / 256, 256, 0, ws_stream(m)>>>(n, dx, dn, dmin, dmax, rcw[0], rcw[1], rcw[2], rcw[3], rcw[4], rcw[5], rcw[6], rcw[7], rcw[8],
                                                             tcw[0], tcw[1], tcw[2], ow[0], ow[1], ow[2], *cam, bounds->min_x, bounds->min_y, bounds->max_x,
                                                             bounds->max_y, viewing_cos_limit, dok, du, dv, dur, dc, dd);
     m->launches++;
@@ -1769,7 +1939,7 @@ int orb_distinctive_descriptors(orb_matcher* m, int n_points, const int32_t* sta
     const int* ds; const uint8_t* dd; int* db;
     if ((st = ws_upload(m, &ds, start, (size_t)n_points + 1)) != ORB_OK || (st = ws_upload(m, &dd, desc, (size_t)total * 32)) != ORB_OK ||
         (st = ws_alloc(m, &db, n_points)) != ORB_OK) return st;
-    k_distinctive<<<n_points, DD_THREADS, 0, m->stream>>>(ds, dd, db);
+    k_distinctive<<<n_points, DD_THREADS, 0, ws_stream(m)>>>(ds, dd, db);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
     ORB_CUDA(cudaMemcpyAsync(best_idx, db, (size_t)n_points * 4, cudaMemcpyDeviceToHost, m->stream));

@@ -175,27 +175,37 @@ __device__ __forceinline__ unsigned gt_bytes(unsigned ad, unsigned k) {  // bit 
 // FAST score of two pixels at once.  e[k] = ring[k] (raw bytes) on packed 16-bit lanes, c = the two centres.
 // min / max commute with the subtraction of the centre, so the arc network runs on the raw ring:
 // dark = (max over the 16 arcs of min over 9 contiguous e) - c; bright = c - (min over arcs of max over 9).
+// The network runs on HMNMX2: a 16-bit lane holding 0..255 IS a (subnormal) half with the same order, min / max return one of their
+// inputs bit for bit, and HMNMX2 issues at 128 lanes per clock per SM against 64 for VIMNMX3.S16x2 (tools/peaks_int.cu).  With
+// two-input operations the cheapest network is the pairwise one: for even k, M8[k] = min e[k+1 .. k+8] from pair and quad minima,
+// and the better of the two 9-arcs that contain it is min(M8[k], max(e[k], e[k+9])): 47 operations per polarity.
+__device__ __forceinline__ unsigned hmin2u(unsigned a, unsigned b) { unsigned r; asm("min.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+__device__ __forceinline__ unsigned hmax2u(unsigned a, unsigned b) { unsigned r; asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
 __device__ __forceinline__ unsigned fast_score_x2(const unsigned (&e)[16], const unsigned c) {
-    unsigned lo3[16], hi3[16];
+    unsigned plo[8], phi[8];      // pairs (e[j], e[j+1]), j = 1, 3, .., 15
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        lo3[k] = __vimin3_s16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
-        hi3[k] = __vimax3_s16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+    for (int i = 0; i < 8; ++i) {
+        plo[i] = hmin2u(e[(2 * i + 1) & 15], e[(2 * i + 2) & 15]);
+        phi[i] = hmax2u(e[(2 * i + 1) & 15], e[(2 * i + 2) & 15]);
     }
-    unsigned a9[16], z9[16];
+    unsigned qlo[8], qhi[8];      // quads e[j .. j+3], j = 1, 3, .., 15
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        a9[k] = __vimin3_s16x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
-        z9[k] = __vimax3_s16x2(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
+    for (int i = 0; i < 8; ++i) {
+        qlo[i] = hmin2u(plo[i], plo[(i + 1) & 7]);
+        qhi[i] = hmax2u(phi[i], phi[(i + 1) & 7]);
     }
-    unsigned dk = __vimax3_s16x2(a9[0], a9[1], a9[2]), br = __vimin3_s16x2(z9[0], z9[1], z9[2]);
+    unsigned dk = 0u, br = 0u;
 #pragma unroll
-    for (int k = 3; k < 15; k += 2) {
-        dk = __vimax3_s16x2(dk, a9[k], a9[k + 1]);
-        br = __vimin3_s16x2(br, z9[k], z9[k + 1]);
+    for (int i = 0; i < 8; ++i) {   // k = 2 i: M8 = e[k+1 .. k+8] = quads at k+1 and k+5; arcs [k, k+8] and [k+1, k+9]
+        const unsigned m8lo = hmin2u(qlo[i], qlo[(i + 2) & 7]), m8hi = hmax2u(qhi[i], qhi[(i + 2) & 7]);
+        const unsigned ends_hi = hmax2u(e[2 * i], e[(2 * i + 9) & 15]), ends_lo = hmin2u(e[2 * i], e[(2 * i + 9) & 15]);
+        const unsigned tlo = hmin2u(m8lo, ends_hi);   // the larger of the two arc minima
+        const unsigned thi = hmax2u(m8hi, ends_lo);   // the smaller of the two arc maxima
+        dk = i == 0 ? tlo : hmax2u(dk, tlo);
+        br = i == 0 ? thi : hmin2u(br, thi);
     }
     // max(dark, bright) - 1 on both lanes
-    return __vsub2(__vmaxs2(__vsub2(__vmaxs2(dk, a9[15]), c), __vsub2(c, __vmins2(br, z9[15]))), 0x00010001u);
+    return __vsub2(__vmaxs2(__vsub2(dk, c), __vsub2(c, br)), 0x00010001u);
 }
 
 // g / n == (g * c_div_magic[n]) >> 20 for g < 2^20 / n (words of a cell view: n <= 17, g < 17 * 59)
@@ -473,7 +483,7 @@ __device__ __align__(16) signed char g_pattern[1024] = {
 // code, :466-489).
 __device__ uint2 g_moment_w[16 * 384];
 cudaError_t orb_upload_moment_table(const int* umax) {
-    static uint2 h[16 * 384];   // same contents from every caller (the disc is a constant of the algorithm)
+    std::vector<uint2> h(16 * 384);   // same contents from every caller (the disc is a constant of the algorithm)
     for (int rsh = 0; rsh < 16; ++rsh)
         for (int i = 0; i < 384; ++i) {
             const int r = i / 12, c = i % 12, v = r - ORB_HALF_PATCH;
@@ -487,7 +497,7 @@ cudaError_t orb_upload_moment_table(const int* umax) {
             }
             h[rsh * 384 + i] = make_uint2(wu, wv);
         }
-    return cudaMemcpyToSymbol(g_moment_w, h, sizeof(h));
+    return cudaMemcpyToSymbol(g_moment_w, h.data(), h.size() * sizeof(uint2));
 }
 __device__ __forceinline__ int dp4a_u8_s8(unsigned px, unsigned w, int acc) {
     int d;
@@ -688,8 +698,8 @@ cudaError_t launch_fast(cudaStream_t s, const TmaMaps& tm, int* cell_cnt, uint32
     // always: static (mbarriers) + dynamic shared memory can cross the 48 KB default even when the dynamic part alone does not
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tot);
     if (e != cudaSuccess) return e;
-    // a small batch cannot fill 148 SMs x 24 warps with 4 cells per warp: one cell per warp then (per-frame latency)
-    const int cpw = (long long)batch * P.total_cells >= 4LL * 148 * 24 * FC_CELLS ? FC_CELLS : 1;
+    // a small batch cannot fill every SM's 24 resident warps with 4 cells per warp: one cell per warp then (per-frame latency)
+    const int cpw = (long long)batch * P.total_cells >= 4LL * orb_sm_count() * 24 * FC_CELLS ? FC_CELLS : 1;
     dim3 grid((P.total_cells + FC_WARPS * cpw - 1) / (FC_WARPS * cpw), batch);
     kern<<<grid, FC_WARPS * 32, tot, s>>>(tm, cell_cnt, stage, P, wb, so, lo, cpw, fast_box_rows(P), b0);
     return cudaGetLastError();   // a refused launch must fail loudly, not leave stale candidate lists behind
@@ -700,7 +710,7 @@ cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const 
     cudaError_t e = cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
     if (e != cudaSuccess) return e;
     // small batches: fewer keypoints per warp, so that the frame's ~2000 keypoints spread over all SMs (per-frame latency)
-    const int kpw = (long long)batch * P.kp_cap >= 2LL * 148 * 28 * OD_KPW ? OD_KPW : 2;
+    const int kpw = (long long)batch * P.kp_cap >= 2LL * orb_sm_count() * 28 * OD_KPW ? OD_KPW : 2;
     dim3 grid((P.kp_cap + OD_WARPS * kpw - 1) / (OD_WARPS * kpw), batch);
     k_orient_describe<<<grid, OD_WARPS * 32, smem, s>>>(tm_raw, tm_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, b0, kpw);
     return cudaGetLastError();

@@ -20,6 +20,16 @@ cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const 
 
 static thread_local std::string g_err;
 void orb_set_error(const std::string& s) { g_err = s; }
+int orb_sm_count() {
+    static int cached[64] = {0};   // 0: not asked yet; plain ints: a racing second query writes the same value
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        cached[dev] = (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) ? n : 148;
+    }
+    return cached[dev];
+}
 extern "C" const char* orb_last_error(void) { return g_err.c_str(); }
 extern "C" int orb_device_count(void) {
     int n = 0;

@@ -155,6 +155,7 @@ struct orb_extractor {
 };
 
 void orb_set_error(const std::string& s);
+int orb_sm_count();   // multiprocessors of the current device (cached per device; launch heuristics only)
 // slot-wise building blocks (extractor.cu) used by the chunk-pipelined host entry points
 int orb_ensure_plan(orb_extractor* e, int w, int h, int batch);
 int orb_run_slots(orb_extractor* e, int b0, int n);

@@ -399,7 +399,7 @@ cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefi
     if (bytes > 200 * 1024) return cudaErrorInvalidConfiguration;
     int nfeat = 0;
     for (int l = 0; l < P.nlevels; ++l) nfeat = max(nfeat, P.lv[l].n_feat);
-    const int nt = batch * P.nlevels <= 2 * 148 ? 1024 : (nfeat >= 1200 ? 512 : 256);
+    const int nt = batch * P.nlevels <= 2 * orb_sm_count() ? 1024 : (nfeat >= 1200 ? 512 : 256);
     auto kern = nt == 1024 ? k_quadtree<1024> : (nt == 512 ? k_quadtree<512> : k_quadtree<256>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;

@@ -73,6 +73,13 @@ DEFINE_TEST(t_dp4a_imad,     x[c] = op_imad(__dp4a(a, b, x[c]), a, b);)
 DEFINE_TEST(t_prmt_dp4a,     x[c] = __dp4a(op_prmt(x[c], a, b), b, x[c]);)
 DEFINE_TEST(t_vimnmx3_lop3,  x[c] = op_lop3(__vimax3_s16x2(x[c], a, b), a, b);)
 DEFINE_TEST(t_vimnmx3_imad,  x[c] = op_imad(__vimax3_s16x2(x[c], a, b), a, b);)
+// half2 min / max (HMNMX2): could carry half of the FAST arc network (pixel values are exact in fp16) IF it issued on another pipe
+__device__ __forceinline__ unsigned op_hmax2(unsigned x, unsigned a) { unsigned r; asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(a)); return r; }
+DEFINE_TEST(t_hmnmx2,        x[c] = op_hmax2(x[c], a);)
+DEFINE_TEST(t_vimnmx3_hmnmx2, x[c] = op_hmax2(__vimax3_s16x2(x[c], a, b), a);)
+DEFINE_TEST(t_hmnmx2_imad,   x[c] = op_imad(op_hmax2(x[c], a), a, b);)
+DEFINE_TEST(t_vhmnmx,        x[c] = op_hmax2(op_hmax2(x[c], a), b);)        // ptxas fuses the pair into one three-input VHMNMX (counted as ONE operation)
+DEFINE_TEST(t_hmnmx2_lop3,   x[c] = op_lop3(op_hmax2(x[c], a), a, b);)
 
 // Hamming distance of 256-bit descriptors exactly as the matcher kernels do it (8 x (LOP3 + POPC + IADD));
 // operations counted = POPCs.
@@ -166,6 +173,11 @@ int main(int argc, char** argv) {
         {"mix_prmt_dp4a", t_prmt_dp4a, 2 * per, "PRMT + IDP.4A alternating (counts both)"},
         {"mix_vimnmx3_lop3", t_vimnmx3_lop3, 2 * per, "VIMNMX3 + LOP3 alternating (counts both)"},
         {"mix_vimnmx3_imad", t_vimnmx3_imad, 2 * per, "VIMNMX3 + IMAD alternating (counts both)"},
+        {"hmnmx2", t_hmnmx2, per, "HMNMX2 (half2 max)"},
+        {"mix_vimnmx3_hmnmx2", t_vimnmx3_hmnmx2, 2 * per, "VIMNMX3 + HMNMX2 alternating (counts both)"},
+        {"mix_hmnmx2_imad", t_hmnmx2_imad, 2 * per, "HMNMX2 + IMAD alternating (counts both)"},
+        {"vhmnmx", t_vhmnmx, per, "VHMNMX (three-input half2 max, fused by ptxas from two max.f16x2; one operation each)"},
+        {"mix_hmnmx2_lop3", t_hmnmx2_lop3, 2 * per, "HMNMX2 + LOP3 alternating (counts both)"},
         {"hamming256_popc", t_hamming256, 16.0 * 8.0, "256-bit Hamming distance as the matcher does it: 2 LDS.128 + 8 x (LOP3 + POPC + IADD); counts POPCs"},
         {"lds32", t_lds<0>, per, "LDS.32, consecutive words (conflict-free); counts 4-byte lanes"},
         {"lds32_broadcast", t_lds<1>, per, "LDS.32, one word per warp (broadcast)"},

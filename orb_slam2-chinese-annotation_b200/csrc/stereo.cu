@@ -166,10 +166,12 @@ __device__ __forceinline__ void st_tma_load_3d(void* smem_dst, const CUtensorMap
                  ::"r"(st_smem_u32(smem_dst)), "l"(map), "r"(st_smem_u32(bar)), "r"(x), "r"(y), "r"(z) : "memory");
 }
 
+// max of two packed 16-bit lanes as HMNMX2 (128 lanes/clk/SM, VIMNMX.U16x2: 64): valid for lanes below 0x7c00, bit-exact
+__device__ __forceinline__ unsigned st_hmax2(unsigned a, unsigned b) { unsigned r; asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
 // SAD of the mean-offset windows (reference :640-659): dist(s) = sum |(L - cl) - (R(s) - cr_s)| over 11 x 11, s = 0..10.
 // Lane 2 y + par owns window row y and the shifts of parity par: the row's 11 left pixels and 22 right pixels are unpacked once into
 // zero-extended byte pairs (PRMT), every |difference| is one IADD3 (biased so that no borrow crosses the 16-bit lanes), one subtract
-// and one VIMNMX.U16x2; row partials meet in shared memory.
+// and one HMNMX2; row partials meet in shared memory.
 __global__ void __launch_bounds__(SR_WARPS * 32)
 k_stereo_refine(const __grid_constant__ TmaMaps tm_l, const __grid_constant__ TmaMaps tm_r, const orb_keypoint* __restrict__ kps_l,
                 const int* __restrict__ counts_l, const int2* __restrict__ jobs, float* __restrict__ u_right, float* __restrict__ depth,
@@ -257,7 +259,7 @@ k_stereo_refine(const __grid_constant__ TmaMaps tm_l, const __grid_constant__ Tm
 #pragma unroll
                 for (int j = 0; j < 6; ++j) {
                     const unsigned u = a[j] + bias - bp[sp + j];          // 1024 + (L - cl) - (R - cr) on both 16-bit lanes
-                    unsigned m = __vmaxu2(u, 0x08000800u - u);            // 1024 + |.|
+                    unsigned m = st_hmax2(u, 0x08000800u - u);            // 1024 + |.| (lanes in [514, 1534]: positive halves, same order as integers)
                     if (j == 5) m &= 0xffffu;
                     acc += m;
                 }

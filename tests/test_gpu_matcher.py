@@ -216,3 +216,30 @@ def test_projection_searches_with_competing_neighbours(gm, idx, k):
     n_g, m_g, b_g = gm.SearchByProjectionClaiming(F3, pk, occ3, 100, check_ori=True)
     n_o, m_o, b_o = orc.search_by_projection_claiming(F3, pk, occ3, 100, True)
     assert n_g == n_o and np.array_equal(m_g, m_o) and np.array_equal(b_g, b_o), (idx, k, n_g, n_o)
+
+
+@pytest.mark.parametrize("idx,n_src", [(0, 40), (1, 12), (2, 200)])
+def test_projection_search_with_long_claim_chains(gm, idx, n_src):
+    """Every MapPoint projects onto one of only n_src keypoints with near-identical descriptors, all points closing: point w's answer
+    depends on the claims of MANY earlier points (the parallel fixpoint resolve of the single-frame call needs one round per link of
+    the longest chain; the batched one-warp kernel replays serially).  Both must equal the sequential loop of src/ORBmatcher.cc:47-141."""
+    f, mps, occ = synth.make_projection_scenario(2000, 2000, 30 + idx, coarse_desc=True)
+    F = _frame(f)
+    rng = np.random.default_rng(100 + idx)
+    src = rng.integers(0, n_src, 2000)                                  # few targets: heavy competition
+    mps["proj_x"] = (f["x"][src] + rng.normal(0, 1.0, 2000)).astype(np.float32)
+    mps["proj_y"] = (f["y"][src] + rng.normal(0, 1.0, 2000)).astype(np.float32)
+    mps["desc"] = f["desc"][src].copy()
+    mps["level"] = f["octave"][src].astype(np.int32)
+    mps["valid"] = np.ones(2000, bool)
+    mps["blocks"] = rng.random(2000) < 0.8
+    occ = np.zeros(2000, bool)
+    for th in (3.0, 5.0):
+        n_g, m_g = gm.SearchByProjection(F, mps, th, occupied=occ)
+        n_o, m_o = orc.search_by_projection_mps(F, mps, th, gm.mfNNratio, occ)
+        assert n_g == n_o and np.array_equal(m_g, m_o), (idx, th, n_g, n_o, int((m_g != m_o).sum()))
+    # the same points through the batched entry point (one resolve warp per pair): identical
+    res = gm.SearchByProjectionBatch([F, F], [mps, mps], 3.0, occupied=[occ, occ])
+    n_o, m_o = orc.search_by_projection_mps(F, mps, 3.0, gm.mfNNratio, occ)
+    for p in range(2):
+        assert res[p][0] == n_o and np.array_equal(res[p][1], m_o), (idx, p)

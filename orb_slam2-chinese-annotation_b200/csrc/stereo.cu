@@ -88,56 +88,69 @@ k_stereo_rows(const orb_keypoint* __restrict__ kps_r, const int* __restrict__ co
 #define SM_WARPS 8
 // Refinement job of one left keypoint: x = su | sv << 16 (window centre on level `oct` of the left image), y = sr | oct << 16 | 1 << 31
 // (centre column in the right image; bit 31 = job valid).  y == 0: no match / rejected before the SAD.
-__global__ void __launch_bounds__(SM_WARPS * 32, 6)   // latency-bound (a chain of dependent loads per keypoint): as many resident warps as fit
+// Eight lanes per left keypoint, four keypoints per warp: a row band holds a few dozen candidates of which the octave / disparity filter
+// keeps about ten, so a whole warp per keypoint idles most lanes in the Hamming part; the chain of dependent loads (keypoint ->
+// row range -> items -> descriptors) is the same length, but four of them are in flight per warp.
+#define SM_GROUP 8
+#define SM_KP_PER_WARP (32 / SM_GROUP)
+__global__ void __launch_bounds__(SM_WARPS * 32)
 k_stereo_search(const orb_keypoint* __restrict__ kps_l, const uint8_t* __restrict__ desc_l, const int* __restrict__ counts_l,
                 const uint8_t* __restrict__ desc_r, const int* __restrict__ row_start, const int2* __restrict__ row_items,
                 float* __restrict__ u_right, float* __restrict__ depth, int* __restrict__ sad, int2* __restrict__ jobs, const StereoGeom S,
                 const float min_d, const float max_d) {
     const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int iL = blockIdx.x * SM_WARPS + warp;
-    if (iL >= counts_l[b]) return;
-    const size_t oL = (size_t)b * S.kp_cap_l + iL;
-    if (lane == 0) { u_right[oL] = -1.0f; depth[oL] = -1.0f; sad[oL] = -1; jobs[oL] = make_int2(0, 0); }
-    const orb_keypoint kl = kps_l[oL];
-    const float uL = kl.x, vL = kl.y;
+    const int sub = lane & (SM_GROUP - 1);
+    const int iL = (blockIdx.x * SM_WARPS + warp) * SM_KP_PER_WARP + (lane / SM_GROUP);
+    const int nL = counts_l[b];
+    bool act = iL < nL;
+    const size_t oL = (size_t)b * S.kp_cap_l + (act ? iL : 0);
+    if (act && sub == 0) { u_right[oL] = -1.0f; depth[oL] = -1.0f; sad[oL] = -1; jobs[oL] = make_int2(0, 0); }
+    float klx = 0.f, kly = 0.f;
+    int oct = 0;
+    if (act) { const orb_keypoint kl = kps_l[oL]; klx = kl.x; kly = kl.y; oct = kl.octave; }
+    const float uL = klx, vL = kly;
     const int row = (int)vL;
-    if (row < 0 || row >= S.h0) return;
-    const int* rs = row_start + (size_t)b * (ORB_MAX_DIM + 1);
-    const int c0 = rs[row], c1 = rs[row + 1];
-    if (c0 == c1) return;
+    act = act && row >= 0 && row < S.h0;
+    int c0 = 0, c1 = 0;
+    if (act) {
+        const int* rs = row_start + (size_t)b * (ORB_MAX_DIM + 1);
+        c0 = rs[row]; c1 = rs[row + 1];
+    }
     const float minU = __fsub_rn(uL, max_d), maxU = __fsub_rn(uL, min_d);
-    if (maxU < 0) return;
+    act = act && c0 != c1 && !(maxU < 0);
 
-    const uint4* dl = reinterpret_cast<const uint4*>(desc_l + oL * 32);
-    const uint4 a0 = dl[0], a1 = dl[1];
-    const int2* items = row_items + (size_t)b * S.items_cap;
-    const uint8_t* DR = desc_r + (size_t)b * S.kp_cap_r * 32;
     unsigned best = ((unsigned)ST_TH_HIGH << 20);  // (dist << 20) | iR ; strict < against TH_HIGH
     float best_x = 0.f;                             // x of this lane's best candidate
-    for (int c = c0 + lane; c < c1; c += 32) {
-        const int2 it = __ldg(&items[c]);
-        const int iR = it.y & 0xffffff, octR = it.y >> 24;
-        const float xR = __int_as_float(it.x);
-        if (octR < kl.octave - 1 || octR > kl.octave + 1) continue;
-        if (xR >= minU && xR <= maxU) {
-            const uint4* dr = reinterpret_cast<const uint4*>(DR + (size_t)iR * 32);
-            const unsigned d = (unsigned)orb_hamming256(a0, a1, dr[0], dr[1]);
-            const unsigned key = (d << 20) | (unsigned)iR;
-            if (key < best) { best = key; best_x = xR; }
+    if (act) {
+        const uint4* dl = reinterpret_cast<const uint4*>(desc_l + oL * 32);
+        const uint4 a0 = dl[0], a1 = dl[1];
+        const int2* items = row_items + (size_t)b * S.items_cap;
+        const uint8_t* DR = desc_r + (size_t)b * S.kp_cap_r * 32;
+        for (int c = c0 + sub; c < c1; c += SM_GROUP) {
+            const int2 it = __ldg(&items[c]);
+            const int iR = it.y & 0xffffff, octR = it.y >> 24;
+            const float xR = __int_as_float(it.x);
+            if (octR < oct - 1 || octR > oct + 1) continue;
+            if (xR >= minU && xR <= maxU) {
+                const uint4* dr = reinterpret_cast<const uint4*>(DR + (size_t)iR * 32);
+                const unsigned d = (unsigned)orb_hamming256(a0, a1, dr[0], dr[1]);
+                const unsigned key = (d << 20) | (unsigned)iR;
+                if (key < best) { best = key; best_x = xR; }
+            }
         }
     }
     const unsigned mine = best;
 #pragma unroll
-    for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    for (int o = SM_GROUP / 2; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
     const int bestDist = (int)(best >> 20);
-    if (bestDist >= ST_TH_ORB) return;
-    // the winning lane hands over its candidate's x (keys are unique: they carry the candidate index)
-    const float uR0 = __shfl_sync(0xffffffffu, best_x, __ffs(__ballot_sync(0xffffffffu, mine == best)) - 1);
+    // the winning lane of the group hands over its candidate's x (keys are unique: they carry the candidate index)
+    const unsigned win = (__ballot_sync(0xffffffffu, mine == best) >> (lane & ~(SM_GROUP - 1))) & ((1u << SM_GROUP) - 1u);
+    const float uR0 = __shfl_sync(0xffffffffu, best_x, (lane & ~(SM_GROUP - 1)) + __ffs(win) - 1);
+    if (!act || sub != 0 || bestDist >= ST_TH_ORB) return;
 
     // window centres on the left keypoint's pyramid level (reference :620-633)
-    const int oct = kl.octave;
     const float isf = S.inv_sf[oct];
-    const int su = (int)roundf(__fmul_rn(kl.x, isf)), sv = (int)roundf(__fmul_rn(kl.y, isf)), sr = (int)roundf(__fmul_rn(uR0, isf));
+    const int su = (int)roundf(__fmul_rn(klx, isf)), sv = (int)roundf(__fmul_rn(kly, isf)), sr = (int)roundf(__fmul_rn(uR0, isf));
     const LevelGeom& GL = S.lvl_l[oct];
     const LevelGeom& GR = S.lvl_r[oct];
     const int w = 5, L = 5;
@@ -145,7 +158,7 @@ k_stereo_search(const orb_keypoint* __restrict__ kps_l, const uint8_t* __restric
     // the reference would throw from cv::Mat::rowRange/colRange on these; they cannot occur for
     // keypoints produced by the extractor (>= 19 px from every level edge)
     if (sv - w < 0 || sv + w >= GL.h || sv + w >= GR.h || su - w < 0 || su + w >= GL.w || sr - L - w < 0 || sr + L + w >= GR.w) return;
-    if (lane == 0) jobs[oL] = make_int2(su | (sv << 16), sr | (oct << 16) | (int)0x80000000);
+    jobs[oL] = make_int2(su | (sv << 16), sr | (oct << 16) | (int)0x80000000);
 }
 
 #define SR_WARPS 4
@@ -374,7 +387,7 @@ static int stereo_launch(orb_extractor* l, orb_extractor* r, int b0, int batch, 
     nvtxRangePop();
     if (T) cudaEventRecord(l->ev_stage[7], l->stream);
     nvtxRangePushA("orb:stereo_match");
-    dim3 grid((l->plan.kp_cap + SM_WARPS - 1) / SM_WARPS, batch);
+    dim3 grid((l->plan.kp_cap + SM_WARPS * SM_KP_PER_WARP - 1) / (SM_WARPS * SM_KP_PER_WARP), batch);
     int2* jobs = l->d_st_jobs + kl;
     k_stereo_search<<<grid, SM_WARPS * 32, 0, l->stream>>>(l->d_kps + kl, l->d_desc + kl * 32, l->d_counts + b0, r->d_desc + kr * 32, row_start, row_items,
                                                           l->d_u_right + kl, l->d_depth + kl, l->d_sad + kl, jobs, S, min_d, max_d);

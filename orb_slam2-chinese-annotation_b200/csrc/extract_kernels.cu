@@ -526,6 +526,11 @@ __device__ __forceinline__ unsigned od_lds_u8(unsigned addr) {
     asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
     return v;
 }
+// packed single precision (Blackwell FMUL2 / FFMA2 / FADD2): two IEEE operations per instruction, each rounded like the scalar one
+__device__ __forceinline__ unsigned long long f2_pack(float lo, float hi) { unsigned long long r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ unsigned long long f2_mul(unsigned long long a, unsigned long long b) { unsigned long long r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ unsigned long long f2_fma(unsigned long long a, unsigned long long b, unsigned long long c) { unsigned long long r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ unsigned long long f2_add(unsigned long long a, unsigned long long b) { unsigned long long r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ void od_tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int x, int y, int z) {
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
                  ::"r"(od_smem_u32(smem_dst)), "l"(map), "r"(od_smem_u32(bar)), "r"(x), "r"(y), "r"(z) : "memory");
@@ -567,15 +572,15 @@ k_orient_describe(const __grid_constant__ TmaMaps tm_raw, const __grid_constant_
         while (my_l + 1 < P.nlevels && o >= s_pre[my_l + 1]) ++my_l;
         my_key = lvl_kp[(size_t)b * P.kp_cap + P.lv[my_l].kp_off + (o - s_pre[my_l])];
     }
-    // the 16 pattern points of this lane's descriptor byte
-    float ptx[16], pty[16];
+    // the 16 pattern points of this lane's descriptor byte, as packed pairs (the two points of comparison k): x's and y's
+    unsigned long long ptx2[8], pty2[8];
     {
         const uint4 q0 = reinterpret_cast<const uint4*>(g_pattern)[2 * lane], q1 = reinterpret_cast<const uint4*>(g_pattern)[2 * lane + 1];
         const unsigned w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            ptx[2 * i] = (float)(signed char)(w[i] & 0xff);            pty[2 * i] = (float)(signed char)((w[i] >> 8) & 0xff);
-            ptx[2 * i + 1] = (float)(signed char)((w[i] >> 16) & 0xff); pty[2 * i + 1] = (float)(signed char)(w[i] >> 24);
+        for (int i = 0; i < 8; ++i) {   // word i = (x0, y0, x1, y1) of comparison i
+            ptx2[i] = f2_pack((float)(signed char)(w[i] & 0xff), (float)(signed char)((w[i] >> 16) & 0xff));
+            pty2[i] = f2_pack((float)(signed char)((w[i] >> 8) & 0xff), (float)(signed char)(w[i] >> 24));
         }
     }
     uint8_t* const wbuf = od_smem + warp * (2 * OD_BUF_BYTES);
@@ -628,17 +633,19 @@ k_orient_describe(const __grid_constant__ TmaMaps tm_raw, const __grid_constant_
         const float rad = __fmul_rn(angle, 0.017453292519943295f);  // factorPI = (float)(CV_PI/180.f)
         float a, bsin;
         orb_sincosf(rad, &bsin, &a);
-        const float magic = 12582912.0f;
+        const unsigned long long magic2 = f2_pack(12582912.0f, 12582912.0f);
+        const unsigned long long sin2 = f2_pack(bsin, bsin), cos2 = f2_pack(a, a), nsin2 = f2_pack(-bsin, -bsin);
         // byte (row r, column q) of the patch sits at 64 * (18 + r) + 18 + dsh + q; the two mantissa offsets 0x4B400000 are folded
         // into the base (32-bit shared-window address arithmetic, modulo 2^32)
         const unsigned spc = od_smem_u32(buf) + 18u * OD_BB_W + 18u + (unsigned)((px - 18) & 15) - 0x4B400000u * (unsigned)(OD_BB_W + 1);
         int val = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            const unsigned r0 = __float_as_uint(__fadd_rn(__fmaf_rn(ptx[2 * k], bsin, __fmul_rn(pty[2 * k], a)), magic));
-            const unsigned q0 = __float_as_uint(__fadd_rn(__fmaf_rn(ptx[2 * k], a, -__fmul_rn(pty[2 * k], bsin)), magic));
-            const unsigned r1 = __float_as_uint(__fadd_rn(__fmaf_rn(ptx[2 * k + 1], bsin, __fmul_rn(pty[2 * k + 1], a)), magic));
-            const unsigned q1 = __float_as_uint(__fadd_rn(__fmaf_rn(ptx[2 * k + 1], a, -__fmul_rn(pty[2 * k + 1], bsin)), magic));
+            // row = cvRound(x sin + y cos) = fma(x, sin, rn(y cos)), column = cvRound(x cos - y sin) = fma(x, cos, -rn(y sin)) (reference :129-131
+            // as GCC contracts it); rn(y * -sin) == -rn(y * sin).  Both points of the comparison in one packed instruction each.
+            const unsigned long long r2 = f2_add(f2_fma(ptx2[k], sin2, f2_mul(pty2[k], cos2)), magic2);
+            const unsigned long long q2 = f2_add(f2_fma(ptx2[k], cos2, f2_mul(pty2[k], nsin2)), magic2);
+            const unsigned r0 = (unsigned)r2, r1 = (unsigned)(r2 >> 32), q0 = (unsigned)q2, q1 = (unsigned)(q2 >> 32);
             const unsigned t0 = od_lds_u8(spc + r0 * OD_BB_W + q0), t1 = od_lds_u8(spc + r1 * OD_BB_W + q1);
             val |= (t0 < t1) << k;
         }

@@ -472,7 +472,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 #define OD_RB_H 31
 #define OD_BLUR_BYTES 2432 // 64 * 37 rounded up to the 128-byte destination alignment of TMA
 #define OD_RAW_BYTES 1536  // 48 * 31 rounded up (exactly 384 words: 12 per lane)
-#define OD_BUF_BYTES (OD_BLUR_BYTES + OD_RAW_BYTES)
+#define OD_SLOT_BYTES OD_BLUR_BYTES   // a slot holds one box at a time: the raw boxes first (moments), then the blurred ones (rBRIEF)
 // pattern copy in global memory: every lane reads the 32 bytes of ITS descriptor byte (16 points) once per warp
 __device__ __align__(16) signed char g_pattern[1024] = {
 #include "../../include/orb_pattern_31.inc"
@@ -537,7 +537,7 @@ __device__ __forceinline__ void od_tma_load_3d(void* smem_dst, const CUtensorMap
 }
 
 // One warp walks OD_KPW consecutive keypoints of the image's final (level-concatenated) order, double-buffered: lane 0 issues the
-// two TMA boxes of keypoint j + 1, then the warp waits for keypoint j's mbarrier and computes on shared memory only.  The 16 pattern
+// TMA box of keypoint j + 1, then the warp waits for keypoint j's mbarrier and computes on shared memory only.  The 16 pattern
 // points of a lane's descriptor byte live in registers as floats.
 __global__ void __launch_bounds__(OD_WARPS * 32, 7)
 k_orient_describe(const __grid_constant__ TmaMaps tm_raw, const __grid_constant__ TmaMaps tm_blur, const uint32_t* __restrict__ lvl_kp,
@@ -583,61 +583,91 @@ k_orient_describe(const __grid_constant__ TmaMaps tm_raw, const __grid_constant_
             pty2[i] = f2_pack((float)(signed char)((w[i] >> 8) & 0xff), (float)(signed char)(w[i] >> 24));
         }
     }
-    uint8_t* const wbuf = od_smem + warp * (2 * OD_BUF_BYTES);
+    uint8_t* const wbuf = od_smem + warp * (2 * OD_SLOT_BYTES);
     const int img = b0 + b;
 
-    auto prefetch = [&](int j) {
+    // Three phases per warp, so that the orientation arithmetic (fastAtan2, sincosf: warp-uniform per keypoint, ~85 instructions) is
+    // done ONCE for the warp's keypoints, lane j working on keypoint j, instead of once per keypoint by 32 identical lanes:
+    //   1. moments: the raw boxes of the keypoints stream through the two slots (TMA, one keypoint ahead); lane j keeps (m10, m01) of
+    //      keypoint j;
+    //   2. lane j: angle, sine, cosine and the 28-byte keypoint record of keypoint j;
+    //   3. rBRIEF: the blurred boxes stream through the same two slots; sine / cosine of keypoint j come by shuffle.
+    auto prefetch = [&](int j, bool blurred) {
         const uint32_t key = __shfl_sync(0xffffffffu, my_key, j);
         const int l = __shfl_sync(0xffffffffu, my_l, j);
         if (lane == 0) {
             const int px = ORB_KEY_X(key) + ORB_WIN, py = ORB_KEY_Y(key) + ORB_WIN;
-            uint8_t* buf = wbuf + (j & 1) * OD_BUF_BYTES;
+            uint8_t* buf = wbuf + (j & 1) * OD_SLOT_BYTES;
             uint64_t* bar = &s_bar[warp][j & 1];
-            od_mbar_expect_tx(bar, OD_BB_W * OD_BB_H + OD_RB_W * OD_RB_H);
-            od_tma_load_3d(buf, &tm_blur.lv[l], bar, (px - 18) & ~15, py - 18, img);
-            od_tma_load_3d(buf + OD_BLUR_BYTES, &tm_raw.lv[l], bar, (px - ORB_HALF_PATCH) & ~15, py - ORB_HALF_PATCH, img);
+            if (blurred) {
+                od_mbar_expect_tx(bar, OD_BB_W * OD_BB_H);
+                od_tma_load_3d(buf, &tm_blur.lv[l], bar, (px - 18) & ~15, py - 18, img);
+            } else {
+                od_mbar_expect_tx(bar, OD_RB_W * OD_RB_H);
+                od_tma_load_3d(buf, &tm_raw.lv[l], bar, (px - ORB_HALF_PATCH) & ~15, py - ORB_HALF_PATCH, img);
+            }
         }
     };
-    prefetch(0);
+    // ---- 1. IC_Angle moments (reference :77-113): integer sums over the radius-15 disc, two byte dot products per staged word
+    int my_m10 = 0, my_m01 = 0;
+    prefetch(0, false);
 #pragma unroll 1
     for (int j = 0; j < n; ++j) {
-        if (j + 1 < n) prefetch(j + 1);   // its buffer was last read by keypoint j - 1, which ended with __syncwarp
+        if (j + 1 < n) prefetch(j + 1, false);   // its slot was last read by keypoint j - 1, which ended with __syncwarp
         const uint32_t key = __shfl_sync(0xffffffffu, my_key, j);
-        const int l = __shfl_sync(0xffffffffu, my_l, j);
-        const int px = ORB_KEY_X(key) + ORB_WIN, py = ORB_KEY_Y(key) + ORB_WIN;
-        const uint8_t* buf = wbuf + (j & 1) * OD_BUF_BYTES;
+        const int px = ORB_KEY_X(key) + ORB_WIN;
+        const uint32_t* rw = reinterpret_cast<const uint32_t*>(wbuf + (j & 1) * OD_SLOT_BYTES) + lane;
+        const uint2* wt = g_moment_w + ((px - ORB_HALF_PATCH) & 15) * 384 + lane;
         od_mbar_wait(&s_bar[warp][j & 1], (unsigned)((j >> 1) & 1));
-
-        // IC_Angle (reference :77-113): integer moments over the radius-15 disc, two byte dot products per staged word
         int m10 = 0, m01 = 0;
-        {
-            const uint32_t* rw = reinterpret_cast<const uint32_t*>(buf + OD_BLUR_BYTES) + lane;
-            const uint2* wt = g_moment_w + ((px - ORB_HALF_PATCH) & 15) * 384 + lane;
 #pragma unroll
-            for (int k = 0; k < 12; ++k) {
-                const uint2 wq = __ldg(wt + k * 32);
-                const unsigned v = rw[k * 32];
-                m10 = dp4a_u8_s8(v, wq.x, m10);
-                m01 = dp4a_u8_s8(v, wq.y, m01);
-            }
+        for (int k = 0; k < 12; ++k) {
+            const uint2 wq = __ldg(wt + k * 32);
+            const unsigned v = rw[k * 32];
+            m10 = dp4a_u8_s8(v, wq.x, m10);
+            m01 = dp4a_u8_s8(v, wq.y, m01);
         }
 #pragma unroll
         for (int o = 16; o; o >>= 1) {
             m10 += __shfl_xor_sync(0xffffffffu, m10, o);
             m01 += __shfl_xor_sync(0xffffffffu, m01, o);
         }
-        const float angle = fast_atan2_deg((float)m01, (float)m10);
+        if (lane == j) { my_m10 = m10; my_m01 = m01; }
+        __syncwarp();   // every lane is done with this slot before lane 0 re-arms it
+    }
+    const int used0 = (n + 1) >> 1, used1 = n >> 1;   // completed phases of the two slots' barriers so far
+    prefetch(0, true);
 
-        // rBRIEF (reference :119-164): lane = descriptor byte, 8 comparisons on the staged blurred patch.  cvRound of the rotated
-        // coordinates as "add 1.5 * 2^23, read the mantissa" (round half to even like cvRound's cvtss2si / F2I.RN; |value| < 2^22)
+    // ---- 2. orientation and keypoint record, lane j for keypoint j
+    float my_sin = 0.f, my_cos = 1.f;
+    if (lane < n) {
+        const float angle = fast_atan2_deg((float)my_m01, (float)my_m10);
         const float rad = __fmul_rn(angle, 0.017453292519943295f);  // factorPI = (float)(CV_PI/180.f)
-        float a, bsin;
-        orb_sincosf(rad, &bsin, &a);
-        const unsigned long long magic2 = f2_pack(12582912.0f, 12582912.0f);
+        orb_sincosf(rad, &my_sin, &my_cos);
+        const LevelGeom& G = P.lv[my_l];
+        const int px = ORB_KEY_X(my_key) + ORB_WIN, py = ORB_KEY_Y(my_key) + ORB_WIN;
+        float fx = (float)px, fy = (float)py;
+        if (my_l != 0) { fx = __fmul_rn(fx, G.sf); fy = __fmul_rn(fy, G.sf); }
+        uint32_t* rec = reinterpret_cast<uint32_t*>(kps + (size_t)b * P.kp_cap + o0 + lane);   // 28 bytes = cv::KeyPoint
+        rec[0] = __float_as_uint(fx); rec[1] = __float_as_uint(fy); rec[2] = __float_as_uint(G.patch_size); rec[3] = __float_as_uint(angle);
+        rec[4] = __float_as_uint((float)ORB_KEY_S(my_key)); rec[5] = (uint32_t)my_l; rec[6] = 0xffffffffu;   // class_id = -1
+    }
+
+    // ---- 3. rBRIEF (reference :119-164): lane = descriptor byte, 8 comparisons on the staged blurred patch.  cvRound of the rotated
+    // coordinates as "add 1.5 * 2^23, read the mantissa" (round half to even like cvRound's cvtss2si / F2I.RN; |value| < 2^22)
+    const unsigned long long magic2 = f2_pack(12582912.0f, 12582912.0f);
+#pragma unroll 1
+    for (int j = 0; j < n; ++j) {
+        if (j + 1 < n) prefetch(j + 1, true);
+        const uint32_t key = __shfl_sync(0xffffffffu, my_key, j);
+        const float bsin = __shfl_sync(0xffffffffu, my_sin, j), a = __shfl_sync(0xffffffffu, my_cos, j);
+        const int px = ORB_KEY_X(key) + ORB_WIN;
+        const uint8_t* buf = wbuf + (j & 1) * OD_SLOT_BYTES;
         const unsigned long long sin2 = f2_pack(bsin, bsin), cos2 = f2_pack(a, a), nsin2 = f2_pack(-bsin, -bsin);
         // byte (row r, column q) of the patch sits at 64 * (18 + r) + 18 + dsh + q; the two mantissa offsets 0x4B400000 are folded
         // into the base (32-bit shared-window address arithmetic, modulo 2^32)
         const unsigned spc = od_smem_u32(buf) + 18u * OD_BB_W + 18u + (unsigned)((px - 18) & 15) - 0x4B400000u * (unsigned)(OD_BB_W + 1);
+        od_mbar_wait(&s_bar[warp][j & 1], (unsigned)(((j >> 1) + ((j & 1) ? used1 : used0)) & 1));
         int val = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -649,25 +679,8 @@ k_orient_describe(const __grid_constant__ TmaMaps tm_raw, const __grid_constant_
             const unsigned t0 = od_lds_u8(spc + r0 * OD_BB_W + q0), t1 = od_lds_u8(spc + r1 * OD_BB_W + q1);
             val |= (t0 < t1) << k;
         }
-        const int out_idx = o0 + j;
-        desc[((size_t)b * P.kp_cap + out_idx) * 32 + lane] = (uint8_t)val;
-        if (lane < 7) {  // one 4-byte field of the 28-byte record per lane
-            const LevelGeom& G = P.lv[l];
-            float fx = (float)px, fy = (float)py;
-            if (l != 0) { fx = __fmul_rn(fx, G.sf); fy = __fmul_rn(fy, G.sf); }
-            uint32_t f;
-            switch (lane) {
-                case 0: f = __float_as_uint(fx); break;
-                case 1: f = __float_as_uint(fy); break;
-                case 2: f = __float_as_uint(G.patch_size); break;
-                case 3: f = __float_as_uint(angle); break;
-                case 4: f = __float_as_uint((float)ORB_KEY_S(key)); break;
-                case 5: f = (uint32_t)l; break;
-                default: f = 0xffffffffu; break;  // class_id = -1
-            }
-            reinterpret_cast<uint32_t*>(kps + (size_t)b * P.kp_cap + out_idx)[lane] = f;
-        }
-        __syncwarp();   // every lane is done with this buffer before lane 0 re-arms it
+        desc[((size_t)b * P.kp_cap + o0 + j) * 32 + lane] = (uint8_t)val;
+        __syncwarp();   // every lane is done with this slot before lane 0 re-arms it
     }
 }
 
@@ -715,7 +728,7 @@ cudaError_t launch_fast(cudaStream_t s, const TmaMaps& tm, int* cell_cnt, uint32
 }
 cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const TmaMaps& tm_blur, const uint32_t* lvl_kp, const int* lvl_cnt,
                                    orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int b0, int batch) {
-    const int smem = OD_WARPS * 2 * OD_BUF_BYTES;
+    const int smem = OD_WARPS * 2 * OD_SLOT_BYTES;
     cudaError_t e = cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
     if (e != cudaSuccess) return e;
     // small batches: fewer keypoints per warp, so that the frame's ~2000 keypoints spread over all SMs (per-frame latency)

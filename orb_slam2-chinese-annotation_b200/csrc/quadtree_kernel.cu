@@ -26,8 +26,11 @@
 struct QNode {
     int count;
     short x0, x1, y0, y1;  // UL.x, UR.x, UL.y, BL.y
-    int pad;
+    int split;             // where DivideNode would cut this box: sx | sy << 16 (set when the node is created)
 };
+__device__ __forceinline__ int node_split(int x0, int x1, int y0, int y1) {   // ceil(half), reference :502-503
+    return (x0 + ((x1 - x0 + 1) >> 1)) | ((y0 + ((y1 - y0 + 1) >> 1)) << 16);
+}
 
 struct QtShared {
     int warp_sums[2][QT_MAX_WARPS + 1];
@@ -62,8 +65,7 @@ __device__ __forceinline__ int block_excl_scan(int v, int* total, QtShared& sh, 
 }
 
 __device__ __forceinline__ int node_quadrant(const QNode& nd, uint32_t k) {
-    const int sx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), sy = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);   // ceil(half), reference :502-503
-    return (ORB_KEY_X(k) < sx ? 0 : 1) + (ORB_KEY_Y(k) < sy ? 0 : 2);
+    return (ORB_KEY_X(k) < (nd.split & 0xffff) ? 0 : 1) + (ORB_KEY_Y(k) < (nd.split >> 16) ? 0 : 2);
 }
 
 // counter[target] += 1 for every lane with target >= 0; lanes of a warp with the same target add once (all 32 lanes call)
@@ -174,7 +176,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
                 nd.x1 = (short)(int)(hX * (float)(r + 1));
                 nd.y0 = 0;
                 nd.y1 = (short)G.win_h;
-                nd.pad = 0;
+                nd.split = node_split(nd.x0, nd.x1, nd.y0, nd.y1);
                 par[r] = m;
                 cur[m++] = nd;
             }
@@ -319,7 +321,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
                     ch.x1 = (short)((q & 1) ? nd.x1 : sx);
                     ch.y0 = (short)((q & 2) ? sy : nd.y0);
                     ch.y1 = (short)((q & 2) ? nd.y1 : sy);
-                    ch.pad = 0;
+                    ch.split = node_split(ch.x0, ch.x1, ch.y0, ch.y1);
                     nxt[pos++] = ch;
                     my_expand += c > 1;
                 }

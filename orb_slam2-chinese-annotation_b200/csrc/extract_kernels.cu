@@ -159,8 +159,9 @@ __global__ void __launch_bounds__(256) k_resize_level(uint8_t* __restrict__ pyr,
 //       one warp scan, ordered write (no ballot, no POPC per word);
 //   (3) exact score of the survivors, two pixels per lane on packed 16-bit lanes (VIMNMX3.S16x2), into the score
 //       map; corners compacted in place;
-//   (4) strict local maxima (VIMNMX3 over the 8 neighbours), compacted in place, counted with and without iniTh;
-//   (5) ordered write of the maxima that pass the cell's threshold.
+//   (4) strict local maxima (VIMNMX3 over the 8 neighbours), compacted in place;
+//   (5) ordered write of the maxima.
+// (2) - (4) run at iniTh first and are repeated at minTh only for a cell that came back empty, like the reference's retry.
 // The tile pitch TP and score pitch SP are compile-time so that every ring / neighbour offset is an immediate.
 #define FC_WARPS 4     // warps per CTA (independent of each other)
 #define FC_CELLS 4     // consecutive cells walked by one warp when the batch fills the GPU (1 for small batches: latency)
@@ -217,7 +218,7 @@ __constant__ unsigned c_div_magic[20] = {0u, (1u << 20) / 1 + 1, (1u << 20) / 2 
 // score map ((ih + 2) x SP bytes, zero frame) at score_off | list (u16: y << 8 | x) at list_off
 struct FcCell { int l, c, ci, cj, iniX, iniY, tw, th; bool valid; };
 template <int SP>
-__global__ void __launch_bounds__(FC_WARPS * 32)
+__global__ void __launch_bounds__(FC_WARPS * 32, 6)   // shared memory allows six CTAs per SM: keep the registers within that
 k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
              const int warp_bytes, const int score_off, const int list_off, const int cells_per_warp, const int box_h, const int b0) {
     constexpr int TP = FC_TP, TPW = TP / 4;
@@ -230,8 +231,6 @@ k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uin
     uint16_t* const seg = reinterpret_cast<uint16_t*>(wt + list_off);
     const uint32_t* const tw32 = reinterpret_cast<const uint32_t*>(wt);
     const int b = blockIdx.y;
-    const int t = P.min_th, ini_th = P.ini_th;
-    const unsigned kk = (unsigned)(127 - min(t, 126)) * 0x01010101u;
     if (lane == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned)__cvta_generic_to_shared(&s_bar[warp])) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");   // make the init visible to the async proxy
@@ -299,6 +298,14 @@ k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uin
         const unsigned gmagic = c_div_magic[nwi];
         const int ngroups = nwi * ih;
 
+        // The reference runs FAST at iniThFAST and, when a cell comes back empty, again at minThFAST (:843-850).  Same here: the first
+        // attempt tests, scores and suppresses at iniTh - far fewer pixels pass the necessary test and reach the arc network than at
+        // minTh - and only a cell without a single maximum is done again at minTh (the tile is still in shared memory).
+        int n_m = 0;
+#pragma unroll 1
+        for (int attempt = 0; attempt < 2; ++attempt) {
+        const int t = attempt == 0 ? P.ini_th : P.min_th;
+        const unsigned kk = (unsigned)(127 - min(t, 126)) * 0x01010101u;
         // (2) necessary test: both ring pixels of the vertical pair (1, 9) and of the horizontal pair
         // (5, 13) within t of the centre => no 9-arc.  Two passes over lane-contiguous runs of words (lane order == row-major
         // order): pass 1 tests and counts, one warp scan turns the counts into offsets, pass 2 writes the survivors in order.
@@ -389,49 +396,40 @@ k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uin
         }
 
         __syncwarp();   // every lane is done reading the tile
-        if (cg + 1 < cg_end) { gn = geom(cg + 1); if (gn.valid) request(gn); }
+        if (attempt == 1 && cg + 1 < cg_end) { gn = geom(cg + 1); if (gn.valid) request(gn); }   // no further attempt: the tile is free
 
         // (4) strict local maxima over the 8 neighbours (the zero frame stands for "outside the cell"), compacted in place
-        int n_m = 0, n_ini = 0;
+        n_m = 0;
 #pragma unroll 1
         for (int k0 = 0; k0 < n_c; k0 += 32) {
             const int k = k0 + lane;
             bool mx = false;
-            int i = 0, s = 0;
+            int i = 0;
             if (k < n_c) {
                 i = seg[k];
                 const uint8_t* q = sc + ((i >> 8) + 1) * SP + (i & 0xff) + 1;
-                s = q[0];
                 const unsigned r0 = __vimax3_u32(q[-SP - 1], q[-SP], q[-SP + 1]), r1 = __vimax3_u32(q[-1], q[1], q[SP - 1]);
-                mx = (unsigned)s > __vimax3_u32(r0, r1, max((unsigned)q[SP], (unsigned)q[SP + 1]));
+                mx = (unsigned)q[0] > __vimax3_u32(r0, r1, max((unsigned)q[SP], (unsigned)q[SP + 1]));
             }
-            const unsigned bm = __ballot_sync(full, mx), bi = __ballot_sync(full, mx && s >= ini_th);   // also orders this iteration's reads before the writes
+            const unsigned bm = __ballot_sync(full, mx);   // also orders this iteration's reads before the writes
             if (mx) seg[n_m + __popc(bm & lt)] = (uint16_t)i;
             n_m += __popc(bm);
-            n_ini += __popc(bi);
             __syncwarp();
         }
+        if (n_m > 0 || P.ini_th == P.min_th) {
+            if (attempt == 0 && cg + 1 < cg_end) { gn = geom(cg + 1); if (gn.valid) request(gn); }
+            break;
+        }
+        }   // attempt
 
-        // (5) threshold of the cell (reference :843-850), ordered write
-        const int th_sel = n_ini > 0 ? ini_th : 0;
-        if (lane == 0) *out_cnt = n_ini > 0 ? n_ini : n_m;
+        // (5) ordered write of the maxima (all of them passed the threshold of the attempt that found them)
+        if (lane == 0) *out_cnt = n_m;
         const int ky0 = 3 + ci * G.h_cell, kx0 = 3 + cj * G.w_cell;
         uint32_t* out0 = stage + (size_t)b * P.stage_per_image + G.stage_off + (size_t)c * G.cell_cap;
-        int n_out = 0;
-#pragma unroll 1
-        for (int k0 = 0; k0 < n_m; k0 += 32) {
-            const int k = k0 + lane;
-            bool keep = false;
-            uint32_t rec = 0;
-            if (k < n_m) {
-                const int i = seg[k], y = i >> 8, x = i & 0xff;
-                const int s = sc[(y + 1) * SP + x + 1];
-                keep = s >= th_sel;
-                rec = ((uint32_t)s << 24) | ((uint32_t)(y + ky0) << 12) | (uint32_t)(x + kx0);
-            }
-            const unsigned bk = __ballot_sync(full, keep);
-            if (keep) out0[n_out + __popc(bk & lt)] = rec;
-            n_out += __popc(bk);
+        for (int k = lane; k < n_m; k += 32) {
+            const int i = seg[k], y = i >> 8, x = i & 0xff;
+            const int s = sc[(y + 1) * SP + x + 1];
+            out0[k] = ((uint32_t)s << 24) | ((uint32_t)(y + ky0) << 12) | (uint32_t)(x + kx0);
         }
         __syncwarp();   // the score map and the list are free for the next cell
         g = gn;

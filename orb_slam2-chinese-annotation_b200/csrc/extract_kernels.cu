@@ -320,6 +320,7 @@ k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uin
             const int f0 = lane * R, nrun = min(R, ngroups - f0);
             uint32_t* const mk = reinterpret_cast<uint32_t*>(sc) + lane;
             unsigned c4 = 0;                                             // survivors of this lane, one counter per byte position
+            int nw = 0;                                                  // words of this lane's run that hold a survivor
             if (nrun > 0) {
                 // (Starting lane i's run at word i / 8, cyclically, makes these loads conflict-free for cells up to 32 rows - lanes i and
                 // i + 8 otherwise sit 8 rows apart, i.e. in the same banks - but measured no faster: 1.742 vs 1.758 ms.)
@@ -336,7 +337,7 @@ k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uin
                     unsigned m = pv & ph & 0x80808080u;
                     if (wxi == 0) m &= mfirst;
                     if (wxi == nwi - 1) m &= mlast;
-                    mk[st * 32] = m | ib;
+                    if (m) { mk[nw * 32] = m | ib; ++nw; }   // words without a survivor (most of them at iniTh) are not revisited
                     c4 += m >> 7;
                     ++wxi; ++cw; ib += 4u;
                     if (wxi == nwi) { wxi = 0; cw += TPW - nwi; ib += 256u - 4u * (unsigned)nwi; }
@@ -349,7 +350,7 @@ k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uin
             n_a = __shfl_sync(full, inc, 31);
             uint16_t* o = seg + (inc - cnt);
 #pragma unroll 1
-            for (int st = 0; st < nrun; ++st) {
+            for (int st = 0; st < nw; ++st) {
                 const unsigned v = mk[st * 32];
                 const unsigned i0 = (v & 0x3f7fu) + (unsigned)xfirst;
                 if (v & 0x80u) *o++ = (uint16_t)i0;

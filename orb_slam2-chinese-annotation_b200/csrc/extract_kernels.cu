@@ -295,8 +295,6 @@ k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uin
         const uint8_t* tile = wt + shift;
         // interior words of a row: word wx holds interior pixels xi = 4 * wx - shift - 3 + k, k = 0..3
         const int w0 = (shift + 3) >> 2, nwi = ((shift + 3 + iw - 1) >> 2) - w0 + 1;
-        const unsigned gmagic = c_div_magic[nwi];
-        const int ngroups = nwi * ih;
 
         // The reference runs FAST at iniThFAST and, when a cell comes back empty, again at minThFAST (:843-850).  Same here: the first
         // attempt tests, scores and suppresses at iniTh - far fewer pixels pass the necessary test and reach the arc network than at
@@ -307,43 +305,55 @@ k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uin
         const int t = attempt == 0 ? P.ini_th : P.min_th;
         const unsigned kk = (unsigned)(127 - min(t, 126)) * 0x01010101u;
         // (2) necessary test: both ring pixels of the vertical pair (1, 9) and of the horizontal pair
-        // (5, 13) within t of the centre => no 9-arc.  Two passes over lane-contiguous runs of words (lane order == row-major
-        // order): pass 1 tests and counts, one warp scan turns the counts into offsets, pass 2 writes the survivors in order.
-        // No ballot and no POPC per word; the masks wait in the (not yet zeroed) score-map region.
+        // (5, 13) within t of the centre => no 9-arc.  Two passes over lane-contiguous runs of word PAIRS (8 pixels, aligned to 8 bytes:
+        // three LDS.64 + two LDS.32 per step; lane order == row-major order): pass 1 tests and counts, one warp scan turns the counts
+        // into offsets, pass 2 writes the survivors in order.  No ballot and no POPC per word; the masks wait in the (not yet zeroed)
+        // score-map region; which bytes of a tile word are interior pixels comes from a 20-entry table at the head of the list.
         int n_a;
         {
             const int xfirst = 4 * w0 - shift - 3;                       // <= 0: interior x of byte 0 of the first word
             const unsigned mfirst = 0x80808080u << (8 * -xfirst);
             const int over = xfirst + 4 * nwi - iw;                      // bytes of the last word beyond the interior (0..3)
             const unsigned mlast = 0x80808080u >> (8 * over);
-            const int R = (ngroups + 31) >> 5;                           // words per lane
-            const int f0 = lane * R, nrun = min(R, ngroups - f0);
+            const int wl = w0 + nwi - 1;                                 // last interior word of a tile row
+            uint32_t* const wmask = reinterpret_cast<uint32_t*>(seg);    // the list is written by pass 2 only
+            if (lane < TPW) wmask[lane] = (lane < w0 || lane > wl) ? 0u : ((lane == w0 ? mfirst : 0x80808080u) & (lane == wl ? mlast : 0x80808080u));
+            __syncwarp();
+            const int p0 = w0 >> 1, npairs = (wl >> 1) - p0 + 1;
+            const int np_tot = npairs * ih;
+            const int R = (np_tot + 31) >> 5;                            // pairs per lane
+            const int f0 = lane * R, nrun = min(R, np_tot - f0);
             uint32_t* const mk = reinterpret_cast<uint32_t*>(sc) + lane;
             unsigned c4 = 0;                                             // survivors of this lane, one counter per byte position
             int nw = 0;                                                  // words of this lane's run that hold a survivor
             if (nrun > 0) {
-                // (Starting lane i's run at word i / 8, cyclically, makes these loads conflict-free for cells up to 32 rows - lanes i and
-                // i + 8 otherwise sit 8 rows apart, i.e. in the same banks - but measured no faster: 1.742 vs 1.758 ms.)
-                const int y0 = (int)(((unsigned)f0 * gmagic) >> 20);
-                int wxi = f0 - y0 * nwi;
-                const uint32_t* cw = tw32 + (y0 + 3) * TPW + w0 + wxi;
-                unsigned ib = (unsigned)((y0 << 8) + 4 * wxi);           // y << 8 | 4 * word: bits 0..6 and 8..13, the mask uses 7, 15, 23, 31
+                // (Starting lane i's run at offset i / 8, cyclically, makes these loads conflict-free for cells up to 32 rows - lanes i
+                // and i + 8 otherwise sit 8 rows apart, i.e. in the same banks - but measured no faster: 1.742 vs 1.758 ms.)
+                const int y0 = (int)(((unsigned)f0 * c_div_magic[npairs]) >> 20);
+                int pi = f0 - y0 * npairs;
+                const uint32_t* cw = tw32 + (y0 + 3) * TPW + 2 * (p0 + pi);
+                int ib = (y0 << 8) + 4 * (2 * (p0 + pi) - w0);           // y << 8 | 4 * word (bits 0..6, 8..13; the mask uses 7, 15, 23, 31)
 #pragma unroll 1
                 for (int st = 0; st < nrun; ++st) {
-                    const unsigned C = cw[0], N = cw[-3 * TPW], S = cw[3 * TPW], L = cw[-1], Rr = cw[1];
-                    const unsigned E = __byte_perm(C, Rr, 0x6543), Wp = __byte_perm(L, C, 0x4321);  // x + 3, x - 3
-                    const unsigned pv = gt_bytes(__vabsdiffu4(N, C), kk) | gt_bytes(__vabsdiffu4(S, C), kk);
-                    const unsigned ph = gt_bytes(__vabsdiffu4(E, C), kk) | gt_bytes(__vabsdiffu4(Wp, C), kk);
-                    unsigned m = pv & ph & 0x80808080u;
-                    if (wxi == 0) m &= mfirst;
-                    if (wxi == nwi - 1) m &= mlast;
-                    if (m) { mk[nw * 32] = m | ib; ++nw; }   // words without a survivor (most of them at iniTh) are not revisited
-                    c4 += m >> 7;
-                    ++wxi; ++cw; ib += 4u;
-                    if (wxi == nwi) { wxi = 0; cw += TPW - nwi; ib += 256u - 4u * (unsigned)nwi; }
+                    const uint2 C = *reinterpret_cast<const uint2*>(cw), N = *reinterpret_cast<const uint2*>(cw - 3 * TPW),
+                                S = *reinterpret_cast<const uint2*>(cw + 3 * TPW);
+                    const unsigned L = cw[-1], Rr = cw[2];
+                    const uint2 wm = *reinterpret_cast<const uint2*>(wmask + 2 * (p0 + pi));
+                    const unsigned E0 = __byte_perm(C.x, C.y, 0x6543), W0 = __byte_perm(L, C.x, 0x4321);   // x + 3, x - 3
+                    const unsigned E1 = __byte_perm(C.y, Rr, 0x6543), W1 = __byte_perm(C.x, C.y, 0x4321);
+                    const unsigned m0 = (gt_bytes(__vabsdiffu4(N.x, C.x), kk) | gt_bytes(__vabsdiffu4(S.x, C.x), kk)) &
+                                        (gt_bytes(__vabsdiffu4(E0, C.x), kk) | gt_bytes(__vabsdiffu4(W0, C.x), kk)) & wm.x;
+                    const unsigned m1 = (gt_bytes(__vabsdiffu4(N.y, C.y), kk) | gt_bytes(__vabsdiffu4(S.y, C.y), kk)) &
+                                        (gt_bytes(__vabsdiffu4(E1, C.y), kk) | gt_bytes(__vabsdiffu4(W1, C.y), kk)) & wm.y;
+                    // words without a survivor (most of them at iniTh) are not revisited
+                    if (m0) { mk[nw * 32] = m0 | (unsigned)ib; ++nw; }
+                    if (m1) { mk[nw * 32] = m1 | (unsigned)(ib + 4); ++nw; }
+                    c4 += (m0 >> 7) + (m1 >> 7);
+                    ++pi; cw += 2; ib += 8;
+                    if (pi == npairs) { pi = 0; cw += TPW - 2 * npairs; ib += 256 - 8 * npairs; }
                 }
             }
-            const int cnt = (int)((c4 * 0x01010101u) >> 24);             // <= 4 R < 256
+            const int cnt = (int)((c4 * 0x01010101u) >> 24);             // <= 8 R < 256
             int inc = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(full, inc, o); if (lane >= o) inc += v; }
@@ -700,8 +710,8 @@ static bool fast_smem(const Plan& P, int* sp, int* warp_bytes, int* score_off, i
     if (mw > 59 || mh > 59) return false;       // cannot happen: a cell is ceil(window / floor(window / 30)) <= 59 pixels
     *sp = mw + 2 <= 48 ? 48 : 64;               // score pitch: interior + zero frame
     *score_off = FC_TP * (mh + 6);
-    // the score-map region first holds the masks of the necessary test: 32 lanes x ceil(words / 32) u32
-    const int ng_max = ((mw + 6) / 4 + 1) * mh, scratch = 128 * ((ng_max + 31) / 32);
+    // the score-map region first holds the masks of the necessary test: 32 lanes x (2 words per pair of a lane's run) u32
+    const int np_max = (((mw + 6) / 4 + 1) / 2 + 1) * mh, scratch = 128 * 2 * ((np_max + 31) / 32);
     *list_off = *score_off + max(*sp * (mh + 2), scratch);
     *warp_bytes = (*list_off + 2 * mw * mh + 4 + 127) & ~127;   // the tile is a TMA destination: 128-byte aligned
     return true;

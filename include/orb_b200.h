@@ -73,6 +73,14 @@ int orb_extract(orb_extractor* e, const uint8_t* img, int w, int h, int stride, 
  * desc + b*cap*32, counts[b]. */
 int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, int h, int stride, size_t img_stride,
                       orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts);
+/* Streaming form of orb_extract_batch (a caller that feeds batch after batch, e.g. a monocular sequence processed offline:
+ * Examples/Monocular/mono_tum.cc:60-100 loops over the frames one by one): enqueue() returns as soon as the batch is queued, wait()
+ * when its outputs are in the caller's buffers.  Two batches may be in flight on one handle (same geometry and batch size);
+ * uploads run a whole call ahead of the kernels.  Tickets are waited for in issue order; the buffers of an enqueued batch stay
+ * alive and untouched until its wait() returns; orb_extract_batch must not be called on the handle while a ticket is out. */
+int orb_extract_enqueue(orb_extractor* e, const uint8_t* imgs, int batch, int w, int h, int stride, size_t img_stride,
+                        orb_keypoint* kps, uint8_t* desc, int cap, int* ticket);
+int orb_extract_wait(orb_extractor* e, int ticket, int32_t* counts);
 /* Same, but the images are already in device memory and the results stay in the handle's device
  * buffers (see orb_extractor_device_results).  Asynchronous on the handle's stream.  The images are
  * read in aligned 16-byte blocks that hold at least one pixel, i.e. up to 15 bytes before the first and past the last

@@ -23,7 +23,7 @@ EXPORTS = [
     "orb_stereo_match", "orb_stereo_match_batch", "orb_stereo_match_device", "orb_stereo_device_results", "orb_stereo_frames",
     "orb_multi_create", "orb_multi_destroy", "orb_multi_device_count", "orb_multi_max_keypoints", "orb_multi_slice",
     "orb_multi_stereo_frames", "orb_multi_extract_batch",
-    "orb_stereo_frames_enqueue", "orb_stereo_frames_wait", "orb_extractor_set_copy_only",
+    "orb_stereo_frames_enqueue", "orb_stereo_frames_wait", "orb_extract_enqueue", "orb_extract_wait", "orb_extractor_set_copy_only",
     "orb_matcher_create", "orb_matcher_destroy", "orb_matcher_stream", "orb_matcher_launch_count", "orb_matcher_sync",
     "orb_descriptor_distance", "orb_match_bruteforce", "orb_match_bruteforce_device", "orb_assign_features_to_grid",
     "orb_search_by_projection_mappoints", "orb_search_by_projection_lastframe", "orb_search_by_bow",

@@ -643,6 +643,7 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, i
         return ORB_OK;
     }
     if (!imgs || !kps || !desc || w < 0 || h < 0 || stride < w) return ORB_ERR_BAD_ARG;
+    if (e->inflight > 0) { orb_set_error("an enqueued batch is still in flight on this handle"); return ORB_ERR_BAD_ARG; }
     ORB_CUDA(cudaSetDevice(e->device));
     int st = ensure_plan(e, w, h, batch);
     if (st != ORB_OK) return st;
@@ -673,6 +674,101 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, i
     if (dst != 0) { cudaMemsetAsync(e->d_status, 0, sizeof(int), e->stream); orb_set_error("device-side bound exceeded"); return dst; }
     int rc = ORB_OK;
     for (int b = 0; b < batch; ++b) { counts[b] = e->h_counts[b]; if (counts[b] > cap) rc = ORB_ERR_CAPACITY; }
+    if (rc != ORB_OK) orb_set_error("keypoint capacity too small");
+    return rc;
+}
+
+// Streaming form of orb_extract_batch (mirror of orb_stereo_frames_enqueue / _wait for one handle): enqueue() queues uploads, kernels
+// and downloads of the whole batch on the handle's three streams and returns; wait() blocks until that call's outputs are in the
+// caller's buffers.  Two calls may be in flight (tickets alternate): chunk c of the next call only waits for chunk c of the previous
+// one, and with dense images the copy stream carries copies only (ingest on the kernel stream), so uploads run a whole call ahead.
+int orb_extract_enqueue(orb_extractor* e, const uint8_t* imgs, int batch, int w, int h, int stride, size_t img_stride, orb_keypoint* kps,
+                        uint8_t* desc, int cap, int* ticket) {
+    if (!e || !imgs || !kps || !desc || !ticket || batch < 1 || w < 1 || h < 1 || stride < w) return ORB_ERR_BAD_ARG;
+    if (e->inflight >= 2) { orb_set_error("two batches are already in flight on this handle: wait for one"); return ORB_ERR_CAPACITY; }
+    ORB_CUDA(cudaSetDevice(e->device));
+    if (e->inflight > 0 && (e->plan_w != w || e->plan_h != h || e->last_batch != batch)) {
+        orb_set_error("batches in flight together must share image size and batch size");
+        return ORB_ERR_BAD_ARG;
+    }
+    int st = ensure_plan(e, w, h, batch);
+    if (st == ORB_OK) st = orb_pipe_streams(e);
+    if (st != ORB_OK) return st;
+    const std::vector<int> cb = orb_chunk_bounds(batch);
+    const int nch = (int)cb.size() - 1;
+    // events per chunk: upload done, kernels done, downloads done, ingest done; + 1 for the call
+    if (!orb_pool_event(e, 4 * nch + 1)) { orb_set_error("event"); return ORB_ERR_CUDA; }
+    const int tk = e->next_ticket & 1;
+    if (e->inflight == 0) {   // uploads must not overtake work already queued on the kernel stream by other entry points
+        ORB_CUDA(cudaEventRecord(e->ev_pool[4 * nch], e->stream));
+        ORB_CUDA(cudaStreamWaitEvent(e->s_h2d, e->ev_pool[4 * nch], 0));
+    }
+    if (!e->ev_call[0]) for (int i = 0; i < 2; ++i) ORB_CUDA(cudaEventCreateWithFlags(&e->ev_call[i], cudaEventDisableTiming));
+    const bool chained = e->inflight > 0 && e->pipe_chunks == nch;
+    if (e->inflight > 0 && !chained) {
+        ORB_CUDA(cudaStreamWaitEvent(e->s_h2d, e->ev_call[tk ^ 1], 0));
+        ORB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_call[tk ^ 1], 0));
+    }
+    const bool split = orb_upload_can_split(e, w, h, stride, img_stride) != 0;
+    const bool was_split = e->pipe_split;
+    int* hc = e->h_counts + (size_t)tk * e->max_batch;
+    for (int c = 0; c < nch; ++c) {
+        const int b0 = cb[c], n = cb[c + 1] - cb[c];
+        cudaEvent_t up = e->ev_pool[4 * c], done = e->ev_pool[4 * c + 1], dl = e->ev_pool[4 * c + 2], ing = e->ev_pool[4 * c + 3];
+        if (chained) {   // events still hold the previous call's records for this chunk
+            if (split && was_split) ORB_CUDA(cudaStreamWaitEvent(e->s_h2d, ing, 0));   // the copy only overwrites the staging slots
+            else ORB_CUDA(cudaStreamWaitEvent(e->s_h2d, done, 0));                    // the copy stream writes level 0 itself
+            ORB_CUDA(cudaStreamWaitEvent(e->stream, dl, 0));                          // the slot's previous results have left
+        }
+        if (split) {
+            if ((st = orb_upload_copy_slots(e, imgs, b0, n, w, h, e->s_h2d)) != ORB_OK) break;
+            ORB_CUDA(cudaEventRecord(up, e->s_h2d));
+            ORB_CUDA(cudaStreamWaitEvent(e->stream, up, 0));
+            if ((st = orb_ingest_slots(e, b0, n, w, h, e->stream)) != ORB_OK) break;
+            ORB_CUDA(cudaEventRecord(ing, e->stream));
+        } else {
+            if ((st = orb_upload_slots(e, imgs, b0, n, w, h, stride, img_stride, e->s_h2d)) != ORB_OK) break;
+            ORB_CUDA(cudaEventRecord(up, e->s_h2d));
+            ORB_CUDA(cudaStreamWaitEvent(e->stream, up, 0));
+        }
+        if (!e->copy_only && (st = run_pipeline(e, b0, n)) != ORB_OK) break;
+        ORB_CUDA(cudaEventRecord(done, e->stream));
+        ORB_CUDA(cudaStreamWaitEvent(e->s_d2h, done, 0));
+        if ((st = orb_download_slots(e, b0, n, kps, desc, cap, e->s_d2h, hc)) != ORB_OK) break;
+        ORB_CUDA(cudaEventRecord(dl, e->s_d2h));
+    }
+    if (st != ORB_OK) {   // nothing of this call may stay in flight once the caller is told it failed (its buffers may go away)
+        cudaStreamSynchronize(e->s_h2d); cudaStreamSynchronize(e->stream); cudaStreamSynchronize(e->s_d2h);
+        e->inflight = 0; e->pipe_chunks = 0;
+        return st;
+    }
+    if (!e->h_status) ORB_CUDA(cudaMallocHost((void**)&e->h_status, 4 * sizeof(int)));
+    ORB_CUDA(cudaMemcpyAsync(&e->h_status[2 * tk], e->d_status, sizeof(int), cudaMemcpyDeviceToHost, e->s_d2h));
+    ORB_CUDA(cudaEventRecord(e->ev_call[tk], e->s_d2h));
+    e->pipe_chunks = nch; e->pipe_split = split;
+    e->pipe_batch[tk] = batch; e->pipe_cap[tk] = cap;
+    *ticket = e->next_ticket++;
+    e->inflight++;
+    return ORB_OK;
+}
+
+int orb_extract_wait(orb_extractor* e, int ticket, int32_t* counts) {
+    if (!e || !counts) return ORB_ERR_BAD_ARG;
+    if (e->inflight < 1 || ticket != e->next_ticket - e->inflight) { orb_set_error("tickets are waited for in the order they were issued"); return ORB_ERR_BAD_ARG; }
+    ORB_CUDA(cudaSetDevice(e->device));
+    const int tk = ticket & 1;
+    ORB_CUDA(cudaEventSynchronize(e->ev_call[tk]));
+    e->inflight--;
+    if (e->h_status[2 * tk] != 0) {
+        const int dst = e->h_status[2 * tk];
+        cudaMemsetAsync(e->d_status, 0, sizeof(int), e->stream);
+        orb_set_error("device-side bound exceeded");
+        return dst;
+    }
+    const int batch = e->pipe_batch[tk], cap = e->pipe_cap[tk];
+    const int* hc = e->h_counts + (size_t)tk * e->max_batch;
+    int rc = ORB_OK;
+    for (int b = 0; b < batch; ++b) { counts[b] = hc[b]; if (counts[b] > cap) rc = ORB_ERR_CAPACITY; }
     if (rc != ORB_OK) orb_set_error("keypoint capacity too small");
     return rc;
 }

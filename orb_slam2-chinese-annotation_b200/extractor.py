@@ -81,6 +81,24 @@ class ORBextractor:
         self._last = (B, W, H)
         return kps, desc, counts
 
+    def extract_enqueue(self, images, out=None):
+        """Streaming form: queue a (B, H, W) uint8 host batch, return (ticket, out); out = dict(kps, desc, counts) owns the host
+        buffers (pass the dict of an earlier, finished call to reuse them).  Keep `images` alive until extract_wait(ticket, out)."""
+        assert images.dtype == np.uint8 and images.ndim == 3 and images.flags.c_contiguous
+        B, H, W = images.shape
+        cap = self.kp_cap
+        if out is None:
+            out = dict(kps=np.empty((B, cap), KP_DTYPE), desc=np.empty((B, cap, 32), np.uint8), counts=np.zeros(B, np.int32))
+        t = C.c_int(0)
+        check(lib().orb_extract_enqueue(self._h, ptr(images), B, W, H, images.strides[1], C.c_size_t(images.strides[0]),
+                                        ptr(out["kps"]), ptr(out["desc"]), cap, C.byref(t)))
+        self._last = (B, W, H)
+        return t.value, out
+
+    def extract_wait(self, ticket, out):
+        check(lib().orb_extract_wait(self._h, int(ticket), ptr(out["counts"])))
+        return out["kps"], out["desc"], out["counts"]
+
     def extract_device(self, d_ptr, batch, w, h, stride=None, img_stride=None):
         """Images already resident in HBM (raw device pointer); results stay on the device."""
         stride = stride or w

@@ -123,6 +123,33 @@ def test_batch_equals_single():
         assert np.array_equal(desc[b][:counts[b]], od)
 
 
+def test_streaming_batches_equal_the_synchronous_call():
+    """orb_extract_enqueue / _wait: two batches in flight on one handle (three issued back to back, waited for in order) give exactly
+    what orb_extract_batch gives for the same images; the synchronous call is refused while a ticket is out."""
+    capi = importlib.import_module("orb_slam2-chinese-annotation_b200.capi")
+    w, h, nf, B = 640, 480, 1000, 20
+    g = _gpu_extractor(w, h, nf, batch=B)
+    batches = [np.stack([synth.make_image(w, h, 100 * r + i) for i in range(B)]) for r in range(3)]
+    ref = [tuple(a.copy() for a in g.extract_batch(im)) for im in batches]
+    t0, o0 = g.extract_enqueue(batches[0])
+    t1, o1 = g.extract_enqueue(batches[1])
+    with pytest.raises(capi.OrbError):
+        g.extract_enqueue(batches[2])                      # a third one has to wait
+    with pytest.raises(capi.OrbError):
+        g.extract_batch(batches[2])                        # the synchronous call would reuse the slots of the tickets in flight
+    got0 = g.extract_wait(t0, o0)
+    t2, o2 = g.extract_enqueue(batches[2])
+    got1 = g.extract_wait(t1, o1)
+    got2 = g.extract_wait(t2, o2)
+    for (rk, rd, rc), (gk, gd, gc) in zip(ref, (got0, got1, got2)):
+        assert np.array_equal(rc, gc)
+        for b in range(B):
+            n = rc[b]
+            assert np.array_equal(rk[b][:n], gk[b][:n]) and np.array_equal(rd[b][:n], gd[b][:n])
+    kps, desc, counts = g.extract_batch(batches[0])        # and the handle is usable synchronously again
+    assert np.array_equal(counts, ref[0][2])
+
+
 def test_bordered_pyramid_matches_reference_layout():
     w, h = 333, 257
     g = _gpu_extractor(w, h, 500)

@@ -636,11 +636,8 @@ k_orient_describe(const __grid_constant__ TmaMaps tm_raw, const __grid_constant_
             m10 = dp4a_u8_s8(v, wq.x, m10);
             m01 = dp4a_u8_s8(v, wq.y, m01);
         }
-#pragma unroll
-        for (int o = 16; o; o >>= 1) {
-            m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-            m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-        }
+        m10 = __reduce_add_sync(0xffffffffu, m10);   // REDUX.SUM: one instruction instead of five shuffle + add steps
+        m01 = __reduce_add_sync(0xffffffffu, m01);
         if (lane == j) { my_m10 = m10; my_m01 = m01; }
         __syncwarp();   // every lane is done with this slot before lane 0 re-arms it
     }

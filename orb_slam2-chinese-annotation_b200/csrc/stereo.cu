@@ -287,8 +287,7 @@ k_stereo_refine(const __grid_constant__ TmaMaps tm_l, const __grid_constant__ Tm
         }
         // first minimum over s = 0..10
         unsigned key = lane < 11 ? (((unsigned)dist << 8) | (unsigned)lane) : 0xffffffffu;
-#pragma unroll
-        for (int o = 16; o; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
+        key = __reduce_min_sync(0xffffffffu, key);   // REDUX.MIN
         const int L = 5;
         const int bs = (int)(key & 0xffu), bestSad = (int)(key >> 8);
         const int bestinc = bs - L;

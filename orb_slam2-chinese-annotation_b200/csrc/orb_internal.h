@@ -133,6 +133,8 @@ struct orb_extractor {
     // host-buffer batches are cut into chunks of image slots: upload (s_h2d), kernels (stream) and
     // download (s_d2h) of consecutive chunks overlap
     cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+    cudaStream_t s_aux = nullptr;   // the blur runs here, beside FAST + quadtree (it only needs the pyramid)
+    cudaEvent_t ev_pyr = nullptr, ev_blur = nullptr;
     std::vector<cudaEvent_t> ev_pool;
     uint8_t* d_in = nullptr;        // dense upload staging [max_batch][max_w * max_h]
     // optional per-stage event timing of the last pipeline run (bench.py roofline numbers)

@@ -170,6 +170,9 @@ k_bruteforce(const uint8_t* __restrict__ A, const uint8_t* __restrict__ Bm, int 
 // cell counts, unordered scatter), then every cell's short list is put in ascending index order by one thread (insertion sort).
 // A cell with more than GRID_SMALL keypoints (degenerate: all features in a few cells) takes the bitonic sort of (cell << 16 | index).
 #define GRID_SMALL 48
+// The kernel's static shared memory (two 3072-entry tables: 24720 bytes, see build/matcher.ptxas.log) counts against the 48 KB a launch
+// gets without opting in: beyond this many bytes of keys the launchers raise cudaFuncAttributeMaxDynamicSharedMemorySize.
+#define GRID_BUILD_DYN_DEFAULT (48 * 1024 - 25 * 1024)
 __global__ void __launch_bounds__(1024)
 k_grid_build(const float* __restrict__ x, const float* __restrict__ y, int n, int p2, orb_grid_params g, int* __restrict__ cell_start,
              int* __restrict__ cell_items, int* __restrict__ n_items, int stride = 0, const int* __restrict__ n_arr = nullptr) {
@@ -1082,7 +1085,7 @@ int upload_frame(orb_matcher* m, const orb_frame_view* f, DFrame* D, bool need_g
         int p2 = 1;
         while (p2 < std::max(f->n, 1)) p2 <<= 1;
         const size_t smem = (size_t)p2 * 4;
-        if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (smem > GRID_BUILD_DYN_DEFAULT) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_grid_build<<<1, 1024, smem, ws_stream(m)>>>(D->x, D->y, f->n, p2, f->grid, cs, ci, ni);
         m->launches++;
         D->cell_start = cs; D->cell_items = ci;
@@ -1241,9 +1244,10 @@ int orb_assign_features_to_grid(orb_matcher* m, const float* kp_x, const float* 
     int p2 = 1;
     while (p2 < std::max(n, 1)) p2 <<= 1;
     const size_t smem = (size_t)p2 * 4;
-    if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (smem > GRID_BUILD_DYN_DEFAULT) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_grid_build<<<1, 1024, smem, ws_stream(m)>>>(dx, dy, n, p2, *g, cs, ci, ni);
     m->launches++;
+    ORB_CUDA(cudaGetLastError());
     ORB_CUDA(cudaMemcpyAsync(cell_start, cs, (GRID_CELLS + 1) * 4, cudaMemcpyDeviceToHost, m->stream));
     ORB_CUDA(cudaMemcpyAsync(n_items, ni, 4, cudaMemcpyDeviceToHost, m->stream));
     ORB_CUDA(cudaStreamSynchronize(m->stream));
@@ -1402,7 +1406,7 @@ int upload_frame_batch(orb_matcher* m, const orb_frame_batch_view* f, DFrame* D,
     int p2 = 1;
     while (p2 < f->stride) p2 <<= 1;
     const size_t smem = (size_t)p2 * 4;
-    if (smem > 48 * 1024) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (smem > GRID_BUILD_DYN_DEFAULT) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_grid_build<<<f->pairs, 1024, smem, ws_stream(m)>>>(D->x, D->y, 0, p2, f->grid, cs, ci, ni, f->stride, D->n_arr);
     m->launches++;
     D->cell_start = cs; D->cell_items = ci;

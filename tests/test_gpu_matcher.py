@@ -57,6 +57,23 @@ def test_grid_assignment(gm):
         assert np.array_equal(gs, os_) and np.array_equal(gi, oi)
 
 
+def test_grid_assignment_between_4096_and_8192_keypoints():
+    """8192 sort keys (32 KB of dynamic shared memory) beside the kernel's 24 KB of static tables pass the 48 KB a launch gets
+    without the opt-in attribute: the launch was refused for these sizes."""
+    big = matcher.ORBmatcher(0.8, True, max_n=8192)
+    for idx, n in [(3, 4097), (4, 6000), (5, 8192)]:
+        f = _frame(synth.make_frame_arrays(n, idx))
+        gs, gi = big.assign_features_to_grid(f)
+        os_, oi = orc.assign_features_to_grid(f)
+        assert np.array_equal(gs, os_) and np.array_equal(gi, oi)
+    f, mps, occ = synth.make_projection_scenario(6000, 6000, 7)
+    F = _frame(f)
+    n_g, m_g = big.SearchByProjection(F, mps, 3.0)
+    n_o, m_o = orc.search_by_projection_mps(F, mps, 3.0, big.mfNNratio, None)
+    assert n_g == n_o and np.array_equal(m_g, m_o) and n_o > 100
+    big.close()
+
+
 @pytest.mark.parametrize("idx,th,coarse", [(0, 1.0, False), (1, 3.0, False), (2, 5.0, False), (3, 3.0, True), (4, 1.0, True)])
 def test_search_by_projection_mappoints(gm, idx, th, coarse):
     f, mps, occ = synth.make_projection_scenario(2000, 2000, idx, coarse_desc=coarse)

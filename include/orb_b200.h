@@ -200,6 +200,23 @@ typedef struct {
 int orb_assign_features_to_grid(orb_matcher* m, const float* kp_x, const float* kp_y, int n, const orb_grid_params* g,
                                 int32_t* cell_start, int32_t* cell_items, int32_t* n_items);
 
+/* The same grid, for callers that may not allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  This entry point has NO counterpart in the reference.
+ * It takes no handle and calls no cudaMalloc / cudaFree or any allocating routine: the device copies of the keypoint
+ * coordinates and of the results that the kernel works on live in one file-scope __device__ array of 108 KB (csrc/matcher.cu,
+ * g_grid_static) that every GPU loading the library holds until the process exits.
+ *   - limit: n <= ORB_GRID_STATIC_MAX_N keypoints; a larger n returns ORB_ERR_CAPACITY with a message in orb_last_error();
+ *   - kp_x / kp_y / cell_start / cell_items / n_items may each be host or device memory of the CURRENT device
+ *     (cudaMemcpyDefault); same layout and capacities as orb_assign_features_to_grid (cell_items: room for n entries, the first
+ *     *n_items are written);
+ *   - stream: a cudaStream_t of the current device, NULL = the default stream; the call returns after the stream has drained;
+ *   - all calls on one device share the array: calls that overlap on the GPU (two host threads, or two streams) race and
+ *     return garbage or ORB_ERR_INTERNAL; serialise them.  Nothing in the array has to be zero on entry (the kernel
+ *     overwrites all it reads back; the count word is cleared per call). */
+#define ORB_GRID_STATIC_MAX_N 8192
+int orb_assign_features_to_grid_static(const float* kp_x, const float* kp_y, int n, const orb_grid_params* g,
+                                       int32_t* cell_start, int32_t* cell_items, int32_t* n_items, void* stream);
+
 /* One frame's features as SoA (undistorted keypoints mvKeysUn, mvuRight, mDescriptors). */
 typedef struct {
     int32_t n;

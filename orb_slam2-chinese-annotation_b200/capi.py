@@ -26,6 +26,7 @@ EXPORTS = [
     "orb_stereo_frames_enqueue", "orb_stereo_frames_wait", "orb_extract_enqueue", "orb_extract_wait", "orb_extractor_set_copy_only",
     "orb_matcher_create", "orb_matcher_destroy", "orb_matcher_stream", "orb_matcher_launch_count", "orb_matcher_sync",
     "orb_descriptor_distance", "orb_match_bruteforce", "orb_match_bruteforce_device", "orb_assign_features_to_grid",
+    "orb_assign_features_to_grid_static",
     "orb_search_by_projection_mappoints", "orb_search_by_projection_lastframe", "orb_search_by_bow",
     "orb_search_by_projection_mappoints_batch", "orb_search_by_projection_lastframe_batch", "orb_matcher_last_candidates",
     "orb_search_for_triangulation", "orb_search_by_bow_keyframes", "orb_search_by_projection_claiming",

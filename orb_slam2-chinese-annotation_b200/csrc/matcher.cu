@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #define GRID_COLS 64
@@ -1952,3 +1953,82 @@ int orb_distinctive_descriptors(orb_matcher* m, int n_points, const int32_t* sta
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// orb_assign_features_to_grid_static: Frame::AssignFeaturesToGrid for callers that may not allocate (CUDA graph capture around
+// them, serving loops, harnesses that forbid cudaMalloc).  No handle and no workspace: the device copies of the keypoint
+// coordinates and of the three results that k_grid_build works on (the bump-allocated workspace of the entry point above) live in
+// one file-scope __device__ array, 108 KB, held by every device that loads the library until the process exits.
+// In host code the array's NAME is only a stand-in: its device address comes from cudaGetSymbolAddress, once per device.
+#define GRID_STATIC_MAX_N ORB_GRID_STATIC_MAX_N
+#define GRID_STATIC_MAX_DEVICES 64
+namespace {
+struct GridStaticScratch {   // every member is a multiple of 256 bytes
+    float x[GRID_STATIC_MAX_N];
+    float y[GRID_STATIC_MAX_N];
+    int cell_items[GRID_STATIC_MAX_N];
+    int cell_start[GRID_CELLS + 64];   // GRID_CELLS + 1 in use
+    int n_items[64];                   // [0] in use
+};
+}  // namespace
+static __device__ __align__(256) unsigned char g_grid_static[sizeof(GridStaticScratch)];
+
+static GridStaticScratch* g_grid_static_ptr[GRID_STATIC_MAX_DEVICES];   // per device, filled at first use
+static std::mutex g_grid_static_mu;
+
+// Device address of the scratch array on the CURRENT device (looked up and cached at the first call per device).
+static int grid_static_scratch(GridStaticScratch** out) {
+    int dev = -1;
+    ORB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= GRID_STATIC_MAX_DEVICES) { orb_set_error("orb_assign_features_to_grid_static: device ordinal out of range"); return ORB_ERR_BAD_ARG; }
+    std::lock_guard<std::mutex> lk(g_grid_static_mu);
+    if (!g_grid_static_ptr[dev]) {
+        void* p = nullptr;
+        ORB_CUDA(cudaGetSymbolAddress(&p, g_grid_static));
+        if (!p) { orb_set_error("cudaGetSymbolAddress(g_grid_static) returned a null address"); return ORB_ERR_CUDA; }
+        // 8192 keys (32 KB of dynamic shared memory) beside the kernel's static 25 KB pass the 48 KB a launch gets by default
+        ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_STATIC_MAX_N * 4));
+        g_grid_static_ptr[dev] = static_cast<GridStaticScratch*>(p);
+    }
+    *out = g_grid_static_ptr[dev];
+    return ORB_OK;
+}
+
+extern "C" int orb_assign_features_to_grid_static(const float* kp_x, const float* kp_y, int n, const orb_grid_params* g, int32_t* cell_start,
+                                                  int32_t* cell_items, int32_t* n_items, void* stream) {
+    ORB_NVTX("orb:assign_features_to_grid_static");
+    if (!g || !cell_start || !cell_items || !n_items || n < 0 || (n > 0 && (!kp_x || !kp_y))) {
+        orb_set_error("orb_assign_features_to_grid_static: null argument or negative n");
+        return ORB_ERR_BAD_ARG;
+    }
+    if (n > GRID_STATIC_MAX_N) {
+        orb_set_error("orb_assign_features_to_grid_static: n = " + std::to_string(n) + " keypoints exceeds the static scratch's maximum of " +
+                      std::to_string(GRID_STATIC_MAX_N) + " (use orb_assign_features_to_grid)");
+        return ORB_ERR_CAPACITY;
+    }
+    GridStaticScratch* S = nullptr;
+    int st = grid_static_scratch(&S);
+    if (st != ORB_OK) return st;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // The array keeps the last call's contents.  k_grid_build overwrites everything it later reads (its counters live in shared
+    // memory and are zeroed there; cell_start is written in full, cell_items up to n_items); only the count is cleared here, so
+    // that a launch that did not run cannot hand back the previous call's.
+    ORB_CUDA(cudaMemsetAsync(S->n_items, 0, sizeof(int), s));
+    if (n > 0) {
+        ORB_CUDA(cudaMemcpyAsync(S->x, kp_x, (size_t)n * 4, cudaMemcpyDefault, s));
+        ORB_CUDA(cudaMemcpyAsync(S->y, kp_y, (size_t)n * 4, cudaMemcpyDefault, s));
+    }
+    int p2 = 1;
+    while (p2 < std::max(n, 1)) p2 <<= 1;
+    k_grid_build<<<1, 1024, (size_t)p2 * 4, s>>>(S->x, S->y, n, p2, *g, S->cell_start, S->cell_items, S->n_items);
+    ORB_CUDA(cudaGetLastError());
+    int total = 0;
+    ORB_CUDA(cudaMemcpyAsync(&total, S->n_items, sizeof(int), cudaMemcpyDeviceToHost, s));
+    ORB_CUDA(cudaStreamSynchronize(s));
+    if (total < 0 || total > n) { orb_set_error("orb_assign_features_to_grid_static: the scratch array was overwritten (overlapping calls?)"); return ORB_ERR_INTERNAL; }
+    ORB_CUDA(cudaMemcpyAsync(cell_start, S->cell_start, (size_t)(GRID_CELLS + 1) * 4, cudaMemcpyDefault, s));
+    ORB_CUDA(cudaMemcpyAsync(n_items, S->n_items, sizeof(int), cudaMemcpyDefault, s));
+    if (total > 0) ORB_CUDA(cudaMemcpyAsync(cell_items, S->cell_items, (size_t)total * 4, cudaMemcpyDefault, s));
+    ORB_CUDA(cudaStreamSynchronize(s));
+    return ORB_OK;
+}

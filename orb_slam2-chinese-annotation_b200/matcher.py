@@ -279,3 +279,14 @@ def _proj_view(d):
                 desc=np.ascontiguousarray(d["desc"], np.uint8), angle=f32(d.get("angle")))
     v = ProjectedView(len(keep["valid"]), *[_addr(keep[k]) for k in ("valid", "u", "v", "ur", "radius", "min_level", "max_level", "desc", "angle")])
     return v, keep
+
+
+GRID_STATIC_MAX_N = 8192   # include/orb_b200.h: ORB_GRID_STATIC_MAX_N
+
+
+def assign_features_to_grid_static(x, y, n, grid, cell_start, cell_items, n_items, stream=0):
+    """orb_assign_features_to_grid_static: Frame::AssignFeaturesToGrid through the allocation-free entry point (no handle; the
+    kernel's device buffers are a static __device__ array of the library).  Every array argument is a numpy array (host) or
+    an integer address (host or device memory of the current device); n_items likewise.  Calls must not overlap on the GPU."""
+    check(lib().orb_assign_features_to_grid_static(ptr(x), ptr(y), int(n), C.byref(grid), ptr(cell_start), ptr(cell_items),
+                                                   ptr(n_items), C.c_void_p(stream)))

@@ -76,6 +76,27 @@ def test_extractor_matches_oracle(w, h, nf):
         assert n > 0
 
 
+SETTINGS = [  # (w, h, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST): every reference yaml uses 1.2 / 8 / 20 / 7; the class takes any
+    (640, 480, 700, 1.1, 5, 12, 5),
+    (640, 480, 400, 1.5, 3, 30, 10),
+    (752, 480, 1500, 1.2, 12, 20, 7),
+    (500, 375, 600, 1.3, 6, 20, 20),
+    (640, 480, 300, 1.2, 1, 40, 7),
+]
+
+
+@pytest.mark.parametrize("w,h,nf,sf,nl,ini,mn", SETTINGS)
+def test_other_extractor_settings(w, h, nf, sf, nl, ini, mn):
+    ext = importlib.import_module("orb_slam2-chinese-annotation_b200.extractor")
+    g = ext.ORBextractor(nf, sf, nl, ini, mn, max_width=w, max_height=h, max_batch=1)
+    o = orc.Extractor(nf, sf, nl, ini, mn)
+    tg, to = g._tables(), o.tables()
+    for k in to:
+        assert np.array_equal(tg[k], to[k]), k
+    for idx in range(2):
+        assert _compare(synth.make_image(w, h, 10 + idx), g, o, nlevels=nl) > 0
+
+
 def test_tables_match_oracle():
     g = _gpu_extractor(640, 480, 1000)
     o = orc.Extractor(1000, 1.2, 8, 20, 7)

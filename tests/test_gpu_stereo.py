@@ -10,22 +10,24 @@ ext = importlib.import_module("orb_slam2-chinese-annotation_b200.extractor")
 stereo = importlib.import_module("orb_slam2-chinese-annotation_b200.stereo")
 pytestmark = pytest.mark.gpu
 
-CASES = [  # w, h, nfeatures, mbf, fx   (KITTI00-02.yaml, EuRoC.yaml)
-    (1241, 376, 2000, 386.1448, 718.856),
-    (752, 480, 1200, 47.90639384423901, 435.2046959714599),
+CASES = [  # w, h, nfeatures, mbf, fx, (scaleFactor, nlevels, iniThFAST, minThFAST)   (KITTI00-02.yaml, EuRoC.yaml, two non-default pyramids)
+    (1241, 376, 2000, 386.1448, 718.856, (1.2, 8, 20, 7)),
+    (752, 480, 1200, 47.90639384423901, 435.2046959714599, (1.2, 8, 20, 7)),
+    (640, 480, 900, 40.0, 500.0, (1.1, 5, 12, 5)),       # search radius and window scale follow mvScaleFactors / mvInvScaleFactors
+    (752, 480, 1000, 47.90639384423901, 435.2046959714599, (1.2, 12, 20, 7)),
 ]
 
 
-@pytest.mark.parametrize("w,h,nf,mbf,fx", CASES)
-def test_stereo_matches_oracle(w, h, nf, mbf, fx):
+@pytest.mark.parametrize("w,h,nf,mbf,fx,cfg", CASES)
+def test_stereo_matches_oracle(w, h, nf, mbf, fx, cfg):
     B = 3
-    gl = ext.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B)
-    gr = ext.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B)
+    gl = ext.ORBextractor(nf, *cfg, max_width=w, max_height=h, max_batch=B)
+    gr = ext.ORBextractor(nf, *cfg, max_width=w, max_height=h, max_batch=B)
     pairs = [synth.make_stereo_pair(w, h, i, fx=fx) for i in range(B)]
     kl, dl, nl = gl.extract_batch(np.stack([p[0] for p in pairs]))
     kr, dr, nr = gr.extract_batch(np.stack([p[1] for p in pairs]))
     ur, dp, n = stereo.compute_stereo_matches(gl, gr, mbf, fx, 0.0, batch=B)
-    ol = orc.Extractor(nf, 1.2, 8, 20, 7); orr = orc.Extractor(nf, 1.2, 8, 20, 7)
+    ol = orc.Extractor(nf, *cfg); orr = orc.Extractor(nf, *cfg)
     total = 0
     for b in range(B):
         okl, odl = ol.extract(pairs[b][0]); okr, odr = orr.extract(pairs[b][1])

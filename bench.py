@@ -585,6 +585,8 @@ def run_latency(cfg_name, local):
                 "200", "20"]
         out["ours"] = json.loads(subprocess.run(base + ["0", "1"], capture_output=True, text=True, env=env, timeout=120).stdout)
         out["ours_with_host_pyramid"] = json.loads(subprocess.run(base + ["1", "1"], capture_output=True, text=True, env=env, timeout=120).stdout)
+        if cfg["stereo"]:   # ORBextractor::ExtractStereo: the same front end as one orb_stereo_frames call from one thread
+            out["ours_single_call"] = json.loads(subprocess.run(base + ["0", "2"], capture_output=True, text=True, env=env, timeout=120).stdout)
     except Exception as e:   # noqa
         out["error"] = repr(e)
     finally:
@@ -595,8 +597,9 @@ def run_latency(cfg_name, local):
     out["reference_cpu"] = cpu_stereo_latency(cfg, 12, left, right)
     out["workload"] = cfg["workload"]
     out["how"] = ("per frame, steady clock, 200 frames after 20 warm-ups (Examples/Stereo/stereo_kitti.cc:80-122); ours = ORB_SLAM2::ORBextractor::operator() "
-                  "on two threads + orb_stereo_match, host cv::Mat in, std::vector<cv::KeyPoint> / cv::Mat out; reference = two extraction threads + "
-                  "ComputeStereoMatches on the host CPU")
+                  "on two threads + orb_stereo_match, host cv::Mat in, std::vector<cv::KeyPoint> / cv::Mat out; ours_single_call = "
+                  "ORB_SLAM2::ORBextractor::ExtractStereo (both extractions and the stereo match queued by one thread, no thread per frame); "
+                  "reference = two extraction threads + ComputeStereoMatches on the host CPU")
     return out
 
 

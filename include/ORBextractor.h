@@ -95,6 +95,30 @@ public:
         }
     }
 
+    // The front end of the stereo Frame constructor in ONE call (src/Frame.cc:81-95: ExtractORB on both images from two threads, join,
+    // ComputeStereoMatches): both extractions are queued from the calling thread on the two handles' streams, so no thread is created
+    // per frame and the two host threads do not take turns at the driver's lock.  Outputs as two operator() calls followed by
+    // ComputeStereoMatches: keypoints / descriptors of both sides, mvuRight and mvDepth (-1 = no match).  maxD = mbf / mb (:549).
+    static void ExtractStereo(ORBextractor& left, ORBextractor& right, const cv::Mat& imLeft, const cv::Mat& imRight, float mbf, float minD,
+                              float maxD, std::vector<cv::KeyPoint>& keysLeft, cv::Mat& descLeft, std::vector<cv::KeyPoint>& keysRight,
+                              cv::Mat& descRight, std::vector<float>& uRight, std::vector<float>& depth) {
+        if (imLeft.empty() || imRight.empty()) return;
+        if (imLeft.type() != CV_8UC1 || imRight.type() != CV_8UC1 || imLeft.cols != imRight.cols || imLeft.rows != imRight.rows ||
+            (size_t)imLeft.step != (size_t)imRight.step)
+            throw std::invalid_argument("ExtractStereo: two CV_8UC1 images of one size and step");
+        left.Reserve(imLeft.cols, imLeft.rows, 1); right.Reserve(imLeft.cols, imLeft.rows, 1);
+        const int cap = orb_extractor_max_keypoints(left.mHandle);
+        if (orb_extractor_max_keypoints(right.mHandle) != cap) throw std::invalid_argument("ExtractStereo: extractors differ in settings");
+        left.mKp.resize(cap); left.mDesc.resize((size_t)cap * 32); right.mKp.resize(cap); right.mDesc.resize((size_t)cap * 32);
+        uRight.resize(cap); depth.resize(cap);
+        int32_t nl = 0, nr = 0;
+        Check(orb_stereo_frames(left.mHandle, right.mHandle, imLeft.data, imRight.data, 1, imLeft.cols, imLeft.rows, (int)imLeft.step,
+                                (size_t)imLeft.step * imLeft.rows, mbf, minD, maxD, left.mKp.data(), left.mDesc.data(), &nl, right.mKp.data(),
+                                right.mDesc.data(), &nr, uRight.data(), depth.data(), cap));
+        left.Deliver(nl, keysLeft, descLeft); right.Deliver(nr, keysRight, descRight);
+        uRight.resize(nl); depth.resize(nl);
+    }
+
     int inline GetLevels() { return nlevels; }
     float inline GetScaleFactor() { return (float)scaleFactor; }
     std::vector<float> inline GetScaleFactors() { return mvScaleFactor; }
@@ -156,6 +180,18 @@ public:
     orb_extractor* Handle() { return mHandle; }  // for orb_stereo_match / orb_stereo_frames
 
 protected:
+    void Deliver(int n, std::vector<cv::KeyPoint>& keys, cv::Mat& desc) {
+        keys.resize(n);
+        if (n == 0) desc.release();
+        else {
+            std::memcpy(static_cast<void*>(keys.data()), mKp.data(), (size_t)n * sizeof(orb_keypoint));
+            desc.create(n, 32, CV_8U);
+            if (desc.isContinuous()) std::memcpy(desc.data, mDesc.data(), (size_t)n * 32);
+            else for (int i = 0; i < n; ++i) std::memcpy(desc.ptr<unsigned char>(i), &mDesc[(size_t)i * 32], 32);
+        }
+        mvImagePyramid.Invalidate();
+        if (mKeepPyramid) DownloadPyramid(0);
+    }
     void Recreate() {
         if (mHandle) { orb_extractor_destroy(mHandle); mHandle = nullptr; }
         Check(orb_extractor_create(nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST, mMaxW, mMaxH, mMaxBatch, mDevice, &mHandle));

@@ -449,6 +449,13 @@ int orb_stereo_match_batch(orb_extractor* l, orb_extractor* r, int batch, float 
     return rc;
 }
 
+// true for ordinary (pageable) host memory: an "asynchronous" copy out of it returns only when the bytes are staged
+static bool host_pageable(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
 // Asynchronous form of the stereo Frame constructor: enqueue() queues uploads, kernels and downloads of the whole batch on the
 // handle pair's three streams and returns; wait() blocks until that call's outputs are in the caller's buffers.  Two calls may be in
 // flight on one handle pair (tickets alternate): chunk c of the next call only waits for chunk c of the previous one (its kernels
@@ -475,8 +482,9 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
     if (st != ORB_OK) return st;
     const std::vector<int> cb = orb_chunk_bounds(batch);
     const int nch = (int)cb.size() - 1;
-    // events per chunk: upload left / right done, kernels done, downloads done; + 2 for the call; then ingest left / right done per chunk
-    if (!orb_pool_event(l, 6 * nch + 4)) { orb_set_error("event"); return ORB_ERR_CUDA; }
+    // events per chunk: upload left / right done, kernels done, downloads done; + 2 for the call; then ingest left / right done per chunk;
+    // then one for "left extraction done" of a one-chunk call
+    if (!orb_pool_event(l, 6 * nch + 5)) { orb_set_error("event"); return ORB_ERR_CUDA; }
     // dense images + staging area: copies on the copy stream, ingest kernels on the kernel streams (uploads run a call ahead)
     const bool split = orb_upload_can_split(l, w, h, stride, img_stride) && orb_upload_can_split(r, w, h, stride, img_stride);
     const bool was_split = l->pipe_split;
@@ -516,25 +524,44 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
         // Frame::Frame: ExtractORB(0, left) and ExtractORB(1, right) run side by side (src/Frame.cc:81-84) ...
         const bool skip = l->copy_only;
         if (split) {
+            // A call of one chunk (a pair or a few: the per-frame use) queues the left kernels BEFORE the right copy: a copy from pageable
+            // memory holds the calling thread until the bytes are staged, and that time is now spent while the left image is being worked on.
+            // The copies keep their order on the copy stream either way; pinned buffers and long batches (copies a call ahead) are unchanged.
+            const bool left_first = nch == 1 && host_pageable(imgs_r);
             if ((st = orb_upload_copy_slots(l, imgs_l, b0, n, w, h, l->s_h2d)) != ORB_OK) break;
             ORB_CUDA(cudaEventRecord(up_l, l->s_h2d));
-            if ((st = orb_upload_copy_slots(r, imgs_r, b0, n, w, h, l->s_h2d)) != ORB_OK) break;
-            ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
+            if (!left_first) {
+                if ((st = orb_upload_copy_slots(r, imgs_r, b0, n, w, h, l->s_h2d)) != ORB_OK) break;
+                ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
+            }
             ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
             if ((st = orb_ingest_slots(l, b0, n, w, h, l->stream)) != ORB_OK) break;
             ORB_CUDA(cudaEventRecord(ing_l, l->stream));
             if (!skip && (st = orb_run_slots(l, b0, n)) != ORB_OK) break;
+            if (nch == 1) ORB_CUDA(cudaEventRecord(l->ev_pool[6 * nch + 4], l->stream));
+            if (left_first) {
+                if ((st = orb_upload_copy_slots(r, imgs_r, b0, n, w, h, l->s_h2d)) != ORB_OK) break;
+                ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
+            }
             ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
             if ((st = orb_ingest_slots(r, b0, n, w, h, r->stream)) != ORB_OK) break;
             ORB_CUDA(cudaEventRecord(ing_r, r->stream));
             if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
         } else {
+            const bool left_first = nch == 1 && host_pageable(imgs_r);   // as above
             if ((st = orb_upload_slots(l, imgs_l, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
             ORB_CUDA(cudaEventRecord(up_l, l->s_h2d));
-            if ((st = orb_upload_slots(r, imgs_r, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
-            ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
+            if (!left_first) {
+                if ((st = orb_upload_slots(r, imgs_r, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
+                ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
+            }
             ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
             if (!skip && (st = orb_run_slots(l, b0, n)) != ORB_OK) break;
+            if (nch == 1) ORB_CUDA(cudaEventRecord(l->ev_pool[6 * nch + 4], l->stream));
+            if (left_first) {
+                if ((st = orb_upload_slots(r, imgs_r, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
+                ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
+            }
             ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
             if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
         }
@@ -545,9 +572,19 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
             ORB_CUDA(cudaStreamWaitEvent(l->stream, l->ev_done, 0));
         }
         ORB_CUDA(cudaEventRecord(done, l->stream));
+        if (nch == 1 && !skip) {
+            // one chunk: the keypoints and descriptors of a side leave as soon as that side's extraction is done, beside the stereo kernels
+            // (ext_l: recorded below the left extraction; r->ev_done: recorded by stereo_launch behind the right one)
+            ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, l->ev_pool[6 * nch + 4], 0));
+            if ((st = orb_download_slots(l, b0, n, kps_l, desc_l, cap, l->s_d2h, hc_l)) != ORB_OK) break;
+            ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, r->ev_done, 0));
+            if ((st = orb_download_slots(r, b0, n, kps_r, desc_r, cap, l->s_d2h, hc_r)) != ORB_OK) break;
+            ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, done, 0));
+        } else {
         ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, done, 0));
         if ((st = orb_download_slots(l, b0, n, kps_l, desc_l, cap, l->s_d2h, hc_l)) != ORB_OK) break;
         if ((st = orb_download_slots(r, b0, n, kps_r, desc_r, cap, l->s_d2h, hc_r)) != ORB_OK) break;
+        }
         if (m > 0) {
             ORB_CUDA(cudaMemcpy2DAsync(u_right + (size_t)b0 * cap, (size_t)cap * 4, l->d_u_right + (size_t)b0 * kc, (size_t)kc * 4, (size_t)m * 4, n,
                                        cudaMemcpyDeviceToHost, l->s_d2h));

@@ -159,7 +159,7 @@ int main(int argc, char** argv) {
             ext(cv::Mat(), cv::Mat(), ke, de);
             int untouched = ke.size() == 7;
             w.put("empty_untouched", "i4", &untouched, 1);
-        } else if (mode == "stereo") {
+        } else if (mode == "stereo" || mode == "stereo1") {
             // The stereo Frame constructor as the reference runs it (src/Frame.cc:81-95): ExtractORB left / right on two threads, joined,
             // then ComputeStereoMatches (= orb_stereo_match on the two handles, patches/Frame_ComputeStereoMatches.patch).  Output names
             // and layout of oracle/ref_match_driver.cpp's "stereo" mode (the reference's own code on the same input).
@@ -170,14 +170,19 @@ int main(int argc, char** argv) {
             cv::Mat imL(p[1], p[0], CV_8UC1, const_cast<unsigned char*>(b.get<unsigned char>("left")));
             cv::Mat imR(p[1], p[0], CV_8UC1, const_cast<unsigned char*>(b.get<unsigned char>("right")));
             std::vector<cv::KeyPoint> kl, kr; cv::Mat dl, dr;
-            std::thread tl([&] { eL(imL, cv::Mat(), kl, dl); });
-            std::thread tr([&] { eR(imR, cv::Mat(), kr, dr); });
-            tl.join(); tr.join();
-            const int N = (int)kl.size();
-            std::vector<float> uR(N > 0 ? N : 1, -1.f), depth(N > 0 ? N : 1, -1.f);
             const float mb = mbf / fx, maxd = mbf / mb;   // :117, :529-531
+            std::vector<float> uR, depth;
+            if (mode == "stereo1") {   // the same front end as ONE call from one thread (ORBextractor::ExtractStereo)
+                ORB_SLAM2::ORBextractor::ExtractStereo(eL, eR, imL, imR, mbf, 0.f, maxd, kl, dl, kr, dr, uR, depth);
+            } else {
+                std::thread tl([&] { eL(imL, cv::Mat(), kl, dl); });
+                std::thread tr([&] { eR(imR, cv::Mat(), kr, dr); });
+                tl.join(); tr.join();
+            }
+            const int N = (int)kl.size();
+            if (mode == "stereo") { uR.assign(N > 0 ? N : 1, -1.f); depth.assign(N > 0 ? N : 1, -1.f); }
             int32_t n = 0;
-            if (N > 0 && orb_stereo_match(eL.Handle(), eR.Handle(), 0, mbf, 0.f, maxd, uR.data(), depth.data(), N, &n) != ORB_OK) throw std::runtime_error(orb_last_error());
+            if (mode == "stereo" && N > 0 && orb_stereo_match(eL.Handle(), eR.Handle(), 0, mbf, 0.f, maxd, uR.data(), depth.data(), N, &n) != ORB_OK) throw std::runtime_error(orb_last_error());
             struct RefKp { float x, y, size, angle, response; int32_t octave; };
             std::vector<RefKp> ol(kl.size()), orr(kr.size());
             for (size_t i = 0; i < kl.size(); ++i) { const RefKp q = {kl[i].pt.x, kl[i].pt.y, kl[i].size, kl[i].angle, kl[i].response, kl[i].octave}; ol[i] = q; }

@@ -373,11 +373,13 @@ REFKP = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
 
 
 @pytest.mark.parametrize("w,h,nf,mbf,fx,seed", [(1241, 376, 2000, 386.1448, 718.856, 0), (752, 480, 1200, 47.90639384423901, 435.2046959714599, 1)])
-def test_stereo_frame_on_two_threads(dropin, tmp_path, w, h, nf, mbf, fx, seed):
+@pytest.mark.parametrize("mode", ["stereo", "stereo1"])
+def test_stereo_frame_on_two_threads(dropin, tmp_path, w, h, nf, mbf, fx, seed, mode):
     """The stereo Frame constructor's hot path as the reference runs it (src/Frame.cc:81-95): operator() of the left and right
-    drop-in extractor on two threads, joined, then ComputeStereoMatches = orb_stereo_match on the two handles; against the oracle."""
+    drop-in extractor on two threads, joined, then ComputeStereoMatches = orb_stereo_match on the two handles; against the oracle.
+    stereo1: the same through ORBextractor::ExtractStereo (one orb_stereo_frames call from one thread)."""
     left, right = synth.make_stereo_pair(w, h, seed, fx=fx)
-    out = dropin("stereo", {"params": np.array([w, h, nf, 8, 20, 7], np.int32), "scale": _f32(1.2), "left": np.ascontiguousarray(left).reshape(-1),
+    out = dropin(mode, {"params": np.array([w, h, nf, 8, 20, 7], np.int32), "scale": _f32(1.2), "left": np.ascontiguousarray(left).reshape(-1),
                             "right": np.ascontiguousarray(right).reshape(-1), "stereo": np.array([mbf, fx], np.float32)}, tmp_path)
     ol = orc.Extractor(nf, 1.2, 8, 20, 7); orr = orc.Extractor(nf, 1.2, 8, 20, 7)
     okl, odl = ol.extract(left); okr, odr = orr.extract(right)

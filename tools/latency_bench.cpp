@@ -6,7 +6,7 @@
 //           (= orb_stereo_match on the device-resident pyramids).
 //   mono:   ORBextractor::operator() on one image (src/Frame.cc:187).
 //
-//   latency_bench <mode stereo|mono> <images.bin> <w> <h> <pool> <nfeatures> <mbf> <fx> <frames> <warmup> [keep_pyramid 0|1] [threads 0|1]
+//   latency_bench <mode stereo|mono> <images.bin> <w> <h> <pool> <nfeatures> <mbf> <fx> <frames> <warmup> [keep_pyramid 0|1] [threads 0|1|2]
 // images.bin: <pool> left images then <pool> right images (mono: <pool> images), w*h bytes each.  Prints one JSON object.
 #include <algorithm>
 #include <chrono>
@@ -25,6 +25,7 @@ int main(int argc, char** argv) {
     const int frames = atoi(argv[9]), warm = atoi(argv[10]);
     const bool keep = argc > 11 && atoi(argv[11]) != 0;
     const bool use_threads = !(argc > 12 && atoi(argv[12]) == 0);
+    const bool single_call = argc > 12 && atoi(argv[12]) == 2;   // ORBextractor::ExtractStereo: one orb_stereo_frames call per pair
     const bool stereo = mode == "stereo";
     const size_t px = (size_t)w * h, nimg = (size_t)pool * (stereo ? 2 : 1);
     std::vector<unsigned char> buf(px * nimg);
@@ -46,6 +47,10 @@ int main(int argc, char** argv) {
             const auto t0 = std::chrono::steady_clock::now();
             int nl = 0;
             if (stereo) {
+                if (single_call) {
+                    ORB_SLAM2::ORBextractor::ExtractStereo(left, right, iml, imr, mbf, 0.f, fx, kl, dl, kr, dr, u_right, depth);
+                    nl = (int)kl.size();
+                } else {
                 if (use_threads) {
                     std::thread tl([&] { left(iml, cv::Mat(), kl, dl); });
                     std::thread tr([&] { right(imr, cv::Mat(), kr, dr); });
@@ -62,6 +67,7 @@ int main(int argc, char** argv) {
                     return 1;
                 }
                 nl = n;
+                }
             } else {
                 left(iml, cv::Mat(), kl, dl);
                 nl = (int)kl.size();
@@ -79,9 +85,9 @@ int main(int argc, char** argv) {
         mean /= ms.size();
         printf("{\"mode\": \"%s\", \"frames\": %d, \"warmup\": %d, \"median_ms\": %.4f, \"mean_ms\": %.4f, \"p95_ms\": %.4f, \"min_ms\": %.4f, "
                "\"frames_per_s\": %.1f, \"avg_keypoints_left\": %.1f, \"avg_stereo_matches\": %.1f, \"keep_pyramid_on_host\": %s, "
-               "\"extractor_threads\": %d}\n",
+               "\"extractor_threads\": %d, \"single_call\": %s}\n",
                mode.c_str(), frames, warm, ms[ms.size() / 2], mean, ms[(size_t)(ms.size() * 0.95)], ms[0], 1e3 / mean,
-               (double)kp_sum / frames, (double)match_sum / frames, keep ? "true" : "false", stereo && use_threads ? 2 : 1);
+               (double)kp_sum / frames, (double)match_sum / frames, keep ? "true" : "false", stereo && use_threads && !single_call ? 2 : 1, single_call ? "true" : "false");
     } catch (const std::exception& e) {
         fprintf(stderr, "latency_bench: %s\n", e.what());
         return 1;

@@ -251,6 +251,8 @@ void free_buffers(orb_extractor* e) {
     if (e->s_aux) cudaStreamDestroy(e->s_aux);
     for (int i = 0; i < ORB_N_STAGES + 4; ++i) if (e->ev_stage[i]) cudaEventDestroy(e->ev_stage[i]);
     if (e->h_pin) cudaFreeHost(e->h_pin);
+    if (e->h_in) cudaFreeHost(e->h_in);
+    if (e->ev_hin) cudaEventDestroy(e->ev_hin);
     if (e->h_counts) cudaFreeHost(e->h_counts);
     if (e->h_status) cudaFreeHost(e->h_status);
     if (e->h_pyr) cudaFreeHost(e->h_pyr);
@@ -387,8 +389,53 @@ int orb_run_slots(orb_extractor* e, int b0, int n) { return run_pipeline(e, b0, 
 int orb_pipe_streams(orb_extractor* e) {
     if (!e->s_h2d) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_h2d, cudaStreamNonBlocking));
     if (!e->s_d2h) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_d2h, cudaStreamNonBlocking));
-    if (!e->d_in && e->max_batch > 1 && !getenv("ORB_B200_NO_STAGING"))
+    if (!e->d_in && !getenv("ORB_B200_NO_STAGING"))
         ORB_CUDA(orb_dev_alloc((void**)&e->d_in, (size_t)e->max_batch * e->max_w * e->max_h + 64));
+    if (e->d_in && !e->h_in && !getenv("ORB_B200_NO_PINNED_MIRROR")) {
+        const size_t one = (size_t)e->max_w * e->max_h, all = one * e->max_batch, lim = (size_t)16 << 20;
+        const size_t cap = all <= lim ? all : (one <= lim ? (lim / one) * one : 0);
+        if (cap) {
+            ORB_CUDA(cudaHostAlloc((void**)&e->h_in, cap, cudaHostAllocDefault));
+            ORB_CUDA(cudaEventCreateWithFlags(&e->ev_hin, cudaEventDisableTiming));
+            e->h_in_cap = cap;
+        }
+    }
+    return ORB_OK;
+}
+bool orb_host_pageable(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+// Images [0, n) at src (pageable host memory, any row stride) -> dense at d_dst through the pinned mirror: CPU copy in pieces, each piece
+// queued on `st` as soon as it is in place, so that the link works while the next piece is copied.  *done = false: not applicable
+// (no mirror, too large, or the source is pinned / device memory), nothing was queued.
+static int upload_through_mirror(orb_extractor* e, const uint8_t* src, int n, int w, int h, int stride, size_t img_stride, uint8_t* d_dst,
+                                 cudaStream_t st, bool* done) {
+    *done = false;
+    const size_t bytes = (size_t)n * w * h;
+    if (!e->h_in || bytes == 0 || bytes > e->h_in_cap || !orb_host_pageable(src)) return ORB_OK;
+    if (e->hin_used) ORB_CUDA(cudaEventSynchronize(e->ev_hin));   // the previous copy out of the mirror (normally long done)
+    const size_t piece = (size_t)192 << 10;
+    const bool dense = stride == w && img_stride == (size_t)w * h;
+    size_t sent = 0, filled = 0;
+    int b = 0, y = 0;
+    while (sent < bytes) {
+        const size_t upto = std::min(bytes, sent + piece);
+        if (dense) { std::memcpy(e->h_in + filled, src + filled, upto - filled); filled = upto; }
+        else {
+            while (filled < upto) {   // whole rows; a piece ends at the first row boundary at or beyond `upto`
+                std::memcpy(e->h_in + filled, src + (size_t)b * img_stride + (size_t)y * stride, (size_t)w);
+                filled += (size_t)w;
+                if (++y == h) { y = 0; ++b; }
+            }
+        }
+        ORB_CUDA(cudaMemcpyAsync(d_dst + sent, e->h_in + sent, filled - sent, cudaMemcpyHostToDevice, st));
+        sent = filled;
+    }
+    ORB_CUDA(cudaEventRecord(e->ev_hin, st));
+    e->hin_used = true;
+    *done = true;
     return ORB_OK;
 }
 cudaEvent_t orb_pool_event(orb_extractor* e, int i) {
@@ -424,6 +471,17 @@ int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w
     const LevelGeom& G0 = e->plan.lv[0];
     uint8_t* dst = e->d_pyr + G0.off + (size_t)b0 * G0.img_stride;
     const uint8_t* src = imgs + (size_t)b0 * img_stride;
+    if (e->d_in) {
+        uint8_t* stg = e->d_in + (size_t)b0 * w * h;
+        bool done = false;
+        const int st_m = upload_through_mirror(e, src, n, w, h, stride, img_stride, stg, st, &done);
+        if (st_m != ORB_OK) return st_m;
+        if (done) {
+            launch_ingest(st, stg, dst, w, h, w, (size_t)w * h, G0.pitch, G0.img_stride, n);
+            e->launches++;
+            return ORB_OK;
+        }
+    }
     if (img_stride == (size_t)stride * h && stride == w && e->d_in) {
         // dense host batch: one linear copy at full PCIe rate into the staging area, then the ingest kernel
         // re-pitches it on the device (strided copies of w-byte rows are DMA-descriptor bound, host or device)
@@ -447,6 +505,9 @@ int orb_upload_can_split(const orb_extractor* e, int w, int h, int stride, size_
     return img_stride == (size_t)stride * h && stride == w && e->d_in != nullptr;
 }
 int orb_upload_copy_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, cudaStream_t st) {
+    bool done = false;
+    const int st_m = upload_through_mirror(e, imgs + (size_t)b0 * w * h, n, w, h, w, (size_t)w * h, e->d_in + (size_t)b0 * w * h, st, &done);
+    if (st_m != ORB_OK || done) return st_m;
     ORB_CUDA(cudaMemcpyAsync(e->d_in + (size_t)b0 * w * h, imgs + (size_t)b0 * w * h, (size_t)n * w * h, cudaMemcpyHostToDevice, st));
     return ORB_OK;
 }

@@ -137,6 +137,12 @@ struct orb_extractor {
     cudaEvent_t ev_pyr = nullptr, ev_blur = nullptr;
     std::vector<cudaEvent_t> ev_pool;
     uint8_t* d_in = nullptr;        // dense upload staging [max_batch][max_w * max_h]
+    // Pinned mirror of the head of d_in.  A small call (one chunk) whose images lie in ordinary pageable memory is copied here by the CPU and
+    // crosses the link asynchronously from here: cudaMemcpy2DAsync of 376 pageable rows of 1241 bytes held the calling thread for 120 us.
+    uint8_t* h_in = nullptr;
+    size_t h_in_cap = 0;
+    cudaEvent_t ev_hin = nullptr;   // behind the last copy out of h_in
+    bool hin_used = false;
     // optional per-stage event timing of the last pipeline run (bench.py roofline numbers)
     bool timing = false;
     cudaEvent_t ev_stage[ORB_N_STAGES + 4] = {nullptr};
@@ -168,6 +174,7 @@ int orb_chunk_size(int batch);
 std::vector<int> orb_chunk_bounds(int batch);
 int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, int stride, size_t img_stride, cudaStream_t st);
 int orb_upload_can_split(const orb_extractor* e, int w, int h, int stride, size_t img_stride);
+bool orb_host_pageable(const void* p);   // ordinary host memory: an "asynchronous" copy out of it returns only when the bytes are staged
 int orb_upload_copy_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, cudaStream_t st);
 int orb_ingest_slots(orb_extractor* e, int b0, int n, int w, int h, cudaStream_t st);
 int orb_download_slots(orb_extractor* e, int b0, int n, orb_keypoint* kps, uint8_t* desc, int cap, cudaStream_t st, int* h_counts = nullptr);

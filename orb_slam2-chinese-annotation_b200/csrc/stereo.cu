@@ -449,13 +449,6 @@ int orb_stereo_match_batch(orb_extractor* l, orb_extractor* r, int batch, float 
     return rc;
 }
 
-// true for ordinary (pageable) host memory: an "asynchronous" copy out of it returns only when the bytes are staged
-static bool host_pageable(const void* p) {
-    cudaPointerAttributes a;
-    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
-    return a.type == cudaMemoryTypeUnregistered;
-}
-
 // Asynchronous form of the stereo Frame constructor: enqueue() queues uploads, kernels and downloads of the whole batch on the
 // handle pair's three streams and returns; wait() blocks until that call's outputs are in the caller's buffers.  Two calls may be in
 // flight on one handle pair (tickets alternate): chunk c of the next call only waits for chunk c of the previous one (its kernels
@@ -527,7 +520,7 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
             // A call of one chunk (a pair or a few: the per-frame use) queues the left kernels BEFORE the right copy: a copy from pageable
             // memory holds the calling thread until the bytes are staged, and that time is now spent while the left image is being worked on.
             // The copies keep their order on the copy stream either way; pinned buffers and long batches (copies a call ahead) are unchanged.
-            const bool left_first = nch == 1 && host_pageable(imgs_r);
+            const bool left_first = nch == 1 && orb_host_pageable(imgs_r);
             if ((st = orb_upload_copy_slots(l, imgs_l, b0, n, w, h, l->s_h2d)) != ORB_OK) break;
             ORB_CUDA(cudaEventRecord(up_l, l->s_h2d));
             if (!left_first) {
@@ -548,7 +541,7 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
             ORB_CUDA(cudaEventRecord(ing_r, r->stream));
             if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
         } else {
-            const bool left_first = nch == 1 && host_pageable(imgs_r);   // as above
+            const bool left_first = nch == 1 && orb_host_pageable(imgs_r);   // as above
             if ((st = orb_upload_slots(l, imgs_l, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
             ORB_CUDA(cudaEventRecord(up_l, l->s_h2d));
             if (!left_first) {

@@ -252,6 +252,7 @@ void free_buffers(orb_extractor* e) {
     for (int i = 0; i < ORB_N_STAGES + 4; ++i) if (e->ev_stage[i]) cudaEventDestroy(e->ev_stage[i]);
     if (e->h_pin) cudaFreeHost(e->h_pin);
     if (e->h_in) cudaFreeHost(e->h_in);
+    if (e->h_out) cudaFreeHost(e->h_out);
     if (e->ev_hin) cudaEventDestroy(e->ev_hin);
     if (e->h_counts) cudaFreeHost(e->h_counts);
     if (e->h_status) cudaFreeHost(e->h_status);
@@ -407,6 +408,66 @@ bool orb_host_pageable(const void* p) {
     if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
     return a.type == cudaMemoryTypeUnregistered;
 }
+// ---- pinned mirror of a small call's results (see orb_internal.h) ----
+static size_t out_section(size_t bytes) { return (bytes + 255) & ~(size_t)255; }
+static void out_offsets(const orb_extractor* e, int n, size_t* desc, size_t* ur, size_t* dp, size_t* total) {
+    const size_t kc = (size_t)e->plan.kp_cap;
+    *desc = out_section((size_t)n * kc * sizeof(orb_keypoint));
+    *ur = *desc + out_section((size_t)n * kc * 32);
+    *dp = *ur + out_section((size_t)n * kc * 4);
+    *total = *dp + out_section((size_t)n * kc * 4);
+}
+bool orb_out_mirror_ready(orb_extractor* e, int n, bool with_stereo) {
+    (void)with_stereo;
+    if (getenv("ORB_B200_NO_PINNED_MIRROR")) return false;
+    size_t o_desc, o_ur, o_dp, total;
+    out_offsets(e, n, &o_desc, &o_ur, &o_dp, &total);
+    if (total > ((size_t)8 << 20)) return false;
+    if (e->h_out_cap < 2 * total) {
+        if (e->inflight > 0) return false;   // a half may still be in use
+        if (e->h_out) { cudaFreeHost(e->h_out); e->h_out = nullptr; e->h_out_cap = 0; }
+        if (cudaHostAlloc((void**)&e->h_out, 2 * total, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); e->h_out = nullptr; return false; }
+        e->h_out_cap = 2 * total;
+    }
+    return true;
+}
+int orb_download_mirror(orb_extractor* e, int n, int tk, cudaStream_t st, int* h_counts) {
+    size_t o_desc, o_ur, o_dp, total;
+    out_offsets(e, n, &o_desc, &o_ur, &o_dp, &total);
+    uint8_t* base = e->h_out + (size_t)tk * (e->h_out_cap / 2);
+    const size_t kc = (size_t)e->plan.kp_cap;
+    if (!h_counts) h_counts = e->h_counts;
+    ORB_CUDA(cudaMemcpyAsync(h_counts, e->d_counts, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, st));
+    ORB_CUDA(cudaMemcpyAsync(base, e->d_kps, (size_t)n * kc * sizeof(orb_keypoint), cudaMemcpyDeviceToHost, st));
+    ORB_CUDA(cudaMemcpyAsync(base + o_desc, e->d_desc, (size_t)n * kc * 32, cudaMemcpyDeviceToHost, st));
+    return ORB_OK;
+}
+int orb_download_mirror_stereo(orb_extractor* e, int n, int tk, cudaStream_t st) {
+    size_t o_desc, o_ur, o_dp, total;
+    out_offsets(e, n, &o_desc, &o_ur, &o_dp, &total);
+    uint8_t* base = e->h_out + (size_t)tk * (e->h_out_cap / 2);
+    const size_t kc = (size_t)e->plan.kp_cap;
+    ORB_CUDA(cudaMemcpyAsync(base + o_ur, e->d_u_right, (size_t)n * kc * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA(cudaMemcpyAsync(base + o_dp, e->d_depth, (size_t)n * kc * 4, cudaMemcpyDeviceToHost, st));
+    return ORB_OK;
+}
+void orb_deliver_mirror(orb_extractor* e, int tk, const int* h_counts) {
+    orb_extractor::OutPlan& O = e->out_plan[tk];
+    if (!O.on) return;
+    O.on = false;
+    size_t o_desc, o_ur, o_dp, total;
+    out_offsets(e, O.n, &o_desc, &o_ur, &o_dp, &total);
+    const uint8_t* base = e->h_out + (size_t)tk * (e->h_out_cap / 2);
+    const size_t kc = (size_t)e->plan.kp_cap;
+    for (int b = 0; b < O.n; ++b) {
+        const size_t m = (size_t)std::max(0, std::min(std::min(h_counts[b], O.cap), (int)kc));
+        if (O.kps) std::memcpy(O.kps + (size_t)b * O.cap, base + (size_t)b * kc * sizeof(orb_keypoint), m * sizeof(orb_keypoint));
+        if (O.desc) std::memcpy(O.desc + (size_t)b * O.cap * 32, base + o_desc + (size_t)b * kc * 32, m * 32);
+        if (O.u_right) std::memcpy(O.u_right + (size_t)b * O.cap, base + o_ur + (size_t)b * kc * 4, m * 4);
+        if (O.depth) std::memcpy(O.depth + (size_t)b * O.cap, base + o_dp + (size_t)b * kc * 4, m * 4);
+    }
+}
+
 // Images [0, n) at src (pageable host memory, any row stride) -> dense at d_dst through the pinned mirror: CPU copy in pieces, each piece
 // queued on `st` as soon as it is in place, so that the link works while the next piece is copied.  *done = false: not applicable
 // (no mirror, too large, or the source is pinned / device memory), nothing was queued.
@@ -733,7 +794,8 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, i
     ORB_CUDA(cudaEventRecord(e->ev_pool[2 * nch], e->stream));
     ORB_CUDA(cudaStreamWaitEvent(e->s_h2d, e->ev_pool[2 * nch], 0));
     // on an error after the first enqueue nothing may stay in flight: the caller is free to release its buffers
-    auto fail = [&](int code) { cudaStreamSynchronize(e->s_h2d); cudaStreamSynchronize(e->stream); cudaStreamSynchronize(e->s_d2h); return code; };
+    auto fail = [&](int code) { cudaStreamSynchronize(e->s_h2d); cudaStreamSynchronize(e->stream); cudaStreamSynchronize(e->s_d2h); e->out_plan[0].on = false; return code; };
+    const bool mirror = nch == 1 && orb_host_pageable(kps) && orb_host_pageable(desc) && orb_out_mirror_ready(e, batch, false);
     for (int c = 0; c < nch; ++c) {
         const int b0 = cb[c], n = cb[c + 1] - cb[c];
         st = orb_upload_slots(e, imgs, b0, n, w, h, stride, img_stride, e->s_h2d);
@@ -742,13 +804,21 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* imgs, int batch, int w, i
         st = e->copy_only ? ORB_OK : run_pipeline(e, b0, n);
         if (st != ORB_OK) return fail(st);
         if (cudaEventRecord(e->ev_pool[2 * c + 1], e->stream) != cudaSuccess || cudaStreamWaitEvent(e->s_d2h, e->ev_pool[2 * c + 1], 0) != cudaSuccess) return fail(ORB_ERR_CUDA);
-        st = orb_download_slots(e, b0, n, kps, desc, cap, e->s_d2h);
+        if (mirror) {
+            st = orb_download_mirror(e, n, 0, e->s_d2h, nullptr);
+            orb_extractor::OutPlan& O = e->out_plan[0];
+            O.on = st == ORB_OK; O.n = n; O.cap = cap; O.kps = kps; O.desc = desc; O.u_right = nullptr; O.depth = nullptr;
+        } else {
+            st = orb_download_slots(e, b0, n, kps, desc, cap, e->s_d2h);
+        }
         if (st != ORB_OK) return fail(st);
     }
-    int dst = 0;
-    ORB_CUDA(cudaMemcpyAsync(&dst, e->d_status, sizeof(int), cudaMemcpyDeviceToHost, e->s_d2h));
+    if (!e->h_status) ORB_CUDA(cudaMallocHost((void**)&e->h_status, 4 * sizeof(int)));
+    ORB_CUDA(cudaMemcpyAsync(&e->h_status[0], e->d_status, sizeof(int), cudaMemcpyDeviceToHost, e->s_d2h));
     ORB_CUDA(cudaStreamSynchronize(e->s_d2h));
-    if (dst != 0) { cudaMemsetAsync(e->d_status, 0, sizeof(int), e->stream); orb_set_error("device-side bound exceeded"); return dst; }
+    const int dst = e->h_status[0];
+    if (dst != 0) { e->out_plan[0].on = false; cudaMemsetAsync(e->d_status, 0, sizeof(int), e->stream); orb_set_error("device-side bound exceeded"); return dst; }
+    if (mirror) orb_deliver_mirror(e, 0, e->h_counts);
     int rc = ORB_OK;
     for (int b = 0; b < batch; ++b) { counts[b] = e->h_counts[b]; if (counts[b] > cap) rc = ORB_ERR_CAPACITY; }
     if (rc != ORB_OK) orb_set_error("keypoint capacity too small");

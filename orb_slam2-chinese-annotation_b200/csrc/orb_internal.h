@@ -143,6 +143,16 @@ struct orb_extractor {
     size_t h_in_cap = 0;
     cudaEvent_t ev_hin = nullptr;   // behind the last copy out of h_in
     bool hin_used = false;
+    // The same for the results of a one-chunk call into pageable buffers: every device-to-host copy into such memory returns only when
+    // it is done (eight of them per stereo pair, one after the other).  They go into this pinned mirror asynchronously (one half per
+    // ticket parity) and the valid rows are handed to the caller by the CPU once the call's event has fired.
+    uint8_t* h_out = nullptr;
+    size_t h_out_cap = 0;
+    struct OutPlan {
+        bool on = false;
+        int n = 0, cap = 0;
+        orb_keypoint* kps = nullptr; uint8_t* desc = nullptr; float* u_right = nullptr; float* depth = nullptr;
+    } out_plan[2];
     // optional per-stage event timing of the last pipeline run (bench.py roofline numbers)
     bool timing = false;
     cudaEvent_t ev_stage[ORB_N_STAGES + 4] = {nullptr};
@@ -174,6 +184,12 @@ int orb_chunk_size(int batch);
 std::vector<int> orb_chunk_bounds(int batch);
 int orb_upload_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, int stride, size_t img_stride, cudaStream_t st);
 int orb_upload_can_split(const orb_extractor* e, int w, int h, int stride, size_t img_stride);
+// results of slots [0, n) -> mirror half tk, asynchronously on st (with_stereo: also d_u_right / d_depth); false = mirror not usable now
+bool orb_out_mirror_ready(orb_extractor* e, int n, bool with_stereo);
+int orb_download_mirror(orb_extractor* e, int n, int tk, cudaStream_t st, int* h_counts);
+int orb_download_mirror_stereo(orb_extractor* e, int n, int tk, cudaStream_t st);
+// after the call's event: valid rows of the mirror half -> the buffers recorded in out_plan[tk]
+void orb_deliver_mirror(orb_extractor* e, int tk, const int* h_counts);
 bool orb_host_pageable(const void* p);   // ordinary host memory: an "asynchronous" copy out of it returns only when the bytes are staged
 int orb_upload_copy_slots(orb_extractor* e, const uint8_t* imgs, int b0, int n, int w, int h, cudaStream_t st);
 int orb_ingest_slots(orb_extractor* e, int b0, int n, int w, int h, cudaStream_t st);

@@ -498,6 +498,10 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
     const int kc = l->plan.kp_cap, m = cap < kc ? cap : kc;
     int* hc_l = l->h_counts + (size_t)tk * l->max_batch;
     int* hc_r = r->h_counts + (size_t)tk * r->max_batch;
+    // one chunk, results into pageable memory, nothing else in flight: the downloads go through the handles' pinned mirrors (orb_internal.h)
+    const bool mirror = nch == 1 && !l->copy_only && l->inflight == 0 && orb_host_pageable(kps_l) && orb_host_pageable(desc_l) && orb_host_pageable(kps_r) &&
+                        orb_host_pageable(desc_r) && orb_host_pageable(u_right) && orb_host_pageable(depth) && orb_out_mirror_ready(l, batch, true) &&
+                        orb_out_mirror_ready(r, batch, false);
     for (int c = 0; c < nch; ++c) {
         const int b0 = cb[c], n = cb[c + 1] - cb[c];
         cudaEvent_t up_l = l->ev_pool[4 * c], up_r = l->ev_pool[4 * c + 1], done = l->ev_pool[4 * c + 2], dl = l->ev_pool[4 * c + 3];
@@ -569,16 +573,22 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
             // one chunk: the keypoints and descriptors of a side leave as soon as that side's extraction is done, beside the stereo kernels
             // (ext_l: recorded below the left extraction; r->ev_done: recorded by stereo_launch behind the right one)
             ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, l->ev_pool[6 * nch + 4], 0));
-            if ((st = orb_download_slots(l, b0, n, kps_l, desc_l, cap, l->s_d2h, hc_l)) != ORB_OK) break;
+            if ((st = mirror ? orb_download_mirror(l, n, tk, l->s_d2h, hc_l) : orb_download_slots(l, b0, n, kps_l, desc_l, cap, l->s_d2h, hc_l)) != ORB_OK) break;
             ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, r->ev_done, 0));
-            if ((st = orb_download_slots(r, b0, n, kps_r, desc_r, cap, l->s_d2h, hc_r)) != ORB_OK) break;
+            if ((st = mirror ? orb_download_mirror(r, n, tk, l->s_d2h, hc_r) : orb_download_slots(r, b0, n, kps_r, desc_r, cap, l->s_d2h, hc_r)) != ORB_OK) break;
             ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, done, 0));
         } else {
         ORB_CUDA(cudaStreamWaitEvent(l->s_d2h, done, 0));
         if ((st = orb_download_slots(l, b0, n, kps_l, desc_l, cap, l->s_d2h, hc_l)) != ORB_OK) break;
         if ((st = orb_download_slots(r, b0, n, kps_r, desc_r, cap, l->s_d2h, hc_r)) != ORB_OK) break;
         }
-        if (m > 0) {
+        if (mirror) {
+            if ((st = orb_download_mirror_stereo(l, n, tk, l->s_d2h)) != ORB_OK) break;
+            orb_extractor::OutPlan& OL = l->out_plan[tk];
+            OL.on = true; OL.n = n; OL.cap = cap; OL.kps = kps_l; OL.desc = desc_l; OL.u_right = u_right; OL.depth = depth;
+            orb_extractor::OutPlan& OR = r->out_plan[tk];
+            OR.on = true; OR.n = n; OR.cap = cap; OR.kps = kps_r; OR.desc = desc_r; OR.u_right = nullptr; OR.depth = nullptr;
+        } else if (m > 0) {
             ORB_CUDA(cudaMemcpy2DAsync(u_right + (size_t)b0 * cap, (size_t)cap * 4, l->d_u_right + (size_t)b0 * kc, (size_t)kc * 4, (size_t)m * 4, n,
                                        cudaMemcpyDeviceToHost, l->s_d2h));
             ORB_CUDA(cudaMemcpy2DAsync(depth + (size_t)b0 * cap, (size_t)cap * 4, l->d_depth + (size_t)b0 * kc, (size_t)kc * 4, (size_t)m * 4, n,
@@ -589,6 +599,7 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
     if (st != ORB_OK) {   // nothing of this call may stay in flight once the caller is told it failed (its buffers may go away)
         cudaStreamSynchronize(l->s_h2d); cudaStreamSynchronize(l->stream); cudaStreamSynchronize(r->stream); cudaStreamSynchronize(l->s_d2h);
         l->inflight = 0; l->pipe_chunks = 0;
+        l->out_plan[tk].on = r->out_plan[tk].on = false;
         return st;
     }
     ORB_CUDA(cudaMemcpyAsync(&l->h_status[2 * tk], l->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->s_d2h));
@@ -615,6 +626,7 @@ int orb_stereo_frames_wait(orb_extractor* l, orb_extractor* r, int ticket, int32
     }
     const int st_l = l->h_status[2 * tk], st_r = l->h_status[2 * tk + 1];
     if (st_l != 0 || st_r != 0) {
+        l->out_plan[tk].on = r->out_plan[tk].on = false;
         cudaMemsetAsync(l->d_status, 0, sizeof(int), l->stream); cudaMemsetAsync(r->d_status, 0, sizeof(int), r->stream);
         orb_set_error("device-side bound exceeded");
         return st_l ? st_l : st_r;
@@ -622,6 +634,8 @@ int orb_stereo_frames_wait(orb_extractor* l, orb_extractor* r, int ticket, int32
     const int batch = l->pipe_batch[tk], cap = l->pipe_cap[tk];
     const int* hc_l = l->h_counts + (size_t)tk * l->max_batch;
     const int* hc_r = r->h_counts + (size_t)tk * r->max_batch;
+    orb_deliver_mirror(l, tk, hc_l);
+    orb_deliver_mirror(r, tk, hc_r);
     int rc = ORB_OK;
     for (int b = 0; b < batch; ++b) {
         n_l[b] = hc_l[b]; n_r[b] = hc_r[b];

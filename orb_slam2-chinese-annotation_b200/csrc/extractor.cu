@@ -312,7 +312,9 @@ int ensure_plan(orb_extractor* e, int w, int h, int batch) {
 // Runs the extractor stages for image slots [b0, b0 + batch) of the handle's buffers (planned for
 // e->last_batch images) on e->stream.  Slot addressing is done on the host: level offsets and the
 // per-image arrays are shifted, the kernels always see "their" batch starting at 0.
-int run_pipeline(orb_extractor* e, int b0, int batch) {
+// phase 0: everything; 1: the pyramid (and the blur when it runs on the side stream) only; 2: the rest.  A caller that feeds two handles
+// from one thread queues phase 1 of both before phase 2 of either (orb_stereo_frames_enqueue, one-chunk calls).
+int run_pipeline(orb_extractor* e, int b0, int batch, int phase = 0) {
     Plan P = e->plan;
     for (int l = 0; l < P.nlevels; ++l) P.lv[l].off += (unsigned long long)b0 * P.lv[l].img_stride;
     const Plan& Q = e->plan;
@@ -329,21 +331,25 @@ int run_pipeline(orb_extractor* e, int b0, int batch) {
     cudaStream_t s = e->stream;
     const bool T = e->timing;
     // event i is recorded BEFORE stage i; event 5 after the last extractor stage
+    const bool first = phase != 2, second = phase != 1;
+    if (first) {
     if (T) cudaEventRecord(e->ev_stage[0], s);
     nvtxRangePushA("orb:pyramid");
     for (int l = 1; l < P.nlevels; ++l) { launch_resize(s, e->d_pyr, &e->tm_resize.lv[l - 1], e->rz_tma[l], Q.lv[l - 1], Q.lv[l], b0, batch); e->launches++; }
     nvtxRangePop();
     if (T) cudaEventRecord(e->ev_stage[1], s);
+    }
     // The blur depends on the pyramid only: for a small batch (a live camera: the kernels cannot fill the GPU) it runs on a side stream
     // beside FAST and the quadtree, and orient + describe waits for both.  With a large batch the two handles of a stereo pair already
     // keep every SM busy and the side stream was measured to change nothing (74.4 k vs 74.8 k frames/s), so it is not used there.
     const bool side = !T && e->s_aux && batch * P.nlevels <= 2 * orb_sm_count() && !getenv("ORB_B200_NO_SIDE_BLUR");
-    if (side) {
+    if (side && first) {
         ORB_CUDA(cudaEventRecord(e->ev_pyr, s));
         ORB_CUDA(cudaStreamWaitEvent(e->s_aux, e->ev_pyr, 0));
         { ORB_NVTX("orb:gauss7"); launch_gauss(e->s_aux, e->tm_blur, e->d_pyr, e->d_blur, Q, b0, batch); e->launches++; }
         ORB_CUDA(cudaEventRecord(e->ev_blur, e->s_aux));
     }
+    if (!second) { ORB_CUDA(cudaGetLastError()); return ORB_OK; }
     if (P.total_cells > 0) {
         ORB_NVTX("orb:fast_cells");
         ORB_CUDA(launch_fast(s, e->tm_fast, cell_cnt, stage, Q, b0, batch)); e->launches++;
@@ -385,7 +391,7 @@ int check_status(orb_extractor* e) {
 
 // ---- slot-wise building blocks of the host-buffer entry points (shared with stereo.cu) ----
 int orb_ensure_plan(orb_extractor* e, int w, int h, int batch) { return ensure_plan(e, w, h, batch); }
-int orb_run_slots(orb_extractor* e, int b0, int n) { return run_pipeline(e, b0, n); }
+int orb_run_slots(orb_extractor* e, int b0, int n, int phase) { return run_pipeline(e, b0, n, phase); }
 
 int orb_pipe_streams(orb_extractor* e) {
     if (!e->s_h2d) ORB_CUDA(cudaStreamCreateWithFlags(&e->s_h2d, cudaStreamNonBlocking));

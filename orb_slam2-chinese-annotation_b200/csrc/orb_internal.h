@@ -176,7 +176,7 @@ void orb_set_error(const std::string& s);
 int orb_sm_count();   // multiprocessors of the current device (cached per device; launch heuristics only)
 // slot-wise building blocks (extractor.cu) used by the chunk-pipelined host entry points
 int orb_ensure_plan(orb_extractor* e, int w, int h, int batch);
-int orb_run_slots(orb_extractor* e, int b0, int n);
+int orb_run_slots(orb_extractor* e, int b0, int n, int phase = 0);   // phase: see run_pipeline (extractor.cu)
 int orb_pipe_streams(orb_extractor* e);
 cudaEvent_t orb_pool_event(orb_extractor* e, int i);
 int orb_chunk_size(int batch);

@@ -534,8 +534,10 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
             ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
             if ((st = orb_ingest_slots(l, b0, n, w, h, l->stream)) != ORB_OK) break;
             ORB_CUDA(cudaEventRecord(ing_l, l->stream));
-            if (!skip && (st = orb_run_slots(l, b0, n)) != ORB_OK) break;
-            if (nch == 1) ORB_CUDA(cudaEventRecord(l->ev_pool[6 * nch + 4], l->stream));
+            // left_first: only the left pyramid goes out before the right copy, then the right pyramid, then the rest of both, so that the
+            // right image's kernel chain (the longer wait: it starts last) begins as early as the calling thread allows
+            if (!skip && (st = orb_run_slots(l, b0, n, left_first ? 1 : 0)) != ORB_OK) break;
+            if (nch == 1 && !left_first) ORB_CUDA(cudaEventRecord(l->ev_pool[6 * nch + 4], l->stream));
             if (left_first) {
                 if ((st = orb_upload_copy_slots(r, imgs_r, b0, n, w, h, l->s_h2d)) != ORB_OK) break;
                 ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
@@ -543,7 +545,11 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
             ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
             if ((st = orb_ingest_slots(r, b0, n, w, h, r->stream)) != ORB_OK) break;
             ORB_CUDA(cudaEventRecord(ing_r, r->stream));
-            if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
+            if (left_first) {
+                if (!skip && ((st = orb_run_slots(r, b0, n, 1)) != ORB_OK || (st = orb_run_slots(l, b0, n, 2)) != ORB_OK)) break;
+                ORB_CUDA(cudaEventRecord(l->ev_pool[6 * nch + 4], l->stream));
+                if (!skip && (st = orb_run_slots(r, b0, n, 2)) != ORB_OK) break;
+            } else if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
         } else {
             const bool left_first = nch == 1 && orb_host_pageable(imgs_r);   // as above
             if ((st = orb_upload_slots(l, imgs_l, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
@@ -553,14 +559,18 @@ int orb_stereo_frames_enqueue(orb_extractor* l, orb_extractor* r, const uint8_t*
                 ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
             }
             ORB_CUDA(cudaStreamWaitEvent(l->stream, up_l, 0));
-            if (!skip && (st = orb_run_slots(l, b0, n)) != ORB_OK) break;
-            if (nch == 1) ORB_CUDA(cudaEventRecord(l->ev_pool[6 * nch + 4], l->stream));
+            if (!skip && (st = orb_run_slots(l, b0, n, left_first ? 1 : 0)) != ORB_OK) break;
+            if (nch == 1 && !left_first) ORB_CUDA(cudaEventRecord(l->ev_pool[6 * nch + 4], l->stream));
             if (left_first) {
                 if ((st = orb_upload_slots(r, imgs_r, b0, n, w, h, stride, img_stride, l->s_h2d)) != ORB_OK) break;
                 ORB_CUDA(cudaEventRecord(up_r, l->s_h2d));
             }
             ORB_CUDA(cudaStreamWaitEvent(r->stream, up_r, 0));
-            if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
+            if (left_first) {
+                if (!skip && ((st = orb_run_slots(r, b0, n, 1)) != ORB_OK || (st = orb_run_slots(l, b0, n, 2)) != ORB_OK)) break;
+                ORB_CUDA(cudaEventRecord(l->ev_pool[6 * nch + 4], l->stream));
+                if (!skip && (st = orb_run_slots(r, b0, n, 2)) != ORB_OK) break;
+            } else if (!skip && (st = orb_run_slots(r, b0, n)) != ORB_OK) break;
         }
         // ... then ComputeStereoMatches (:95)
         if (!skip && (st = stereo_launch(l, r, b0, n, mbf, min_d, max_d, false)) != ORB_OK) break;

@@ -179,3 +179,51 @@ def test_bordered_pyramid_matches_reference_layout():
     o = orc.Extractor(500, 1.2, 8, 20, 7); o.extract(img)
     for l in (0, 3, 7):
         assert np.array_equal(g.image_pyramid(l, border=19), orc.border101(o.level(l), 19))
+
+
+def _abi_extract(g, imgs_view, cap):
+    """orb_extract_batch straight through the C ABI on a (B, H, W) view with arbitrary row / image strides."""
+    import ctypes as C
+    capi = importlib.import_module("orb_slam2-chinese-annotation_b200.capi")
+    B, H, W = imgs_view.shape
+    kps = np.zeros((B, cap), capi.KP_DTYPE); desc = np.zeros((B, cap, 32), np.uint8); cnt = np.zeros(B, np.int32)
+    capi.check(capi.lib().orb_extract_batch(g._h, C.c_void_p(imgs_view.ctypes.data), B, W, H, imgs_view.strides[1], C.c_size_t(imgs_view.strides[0]),
+                                            capi.ptr(kps), capi.ptr(desc), cap, capi.ptr(cnt)))
+    return kps, desc, cnt
+
+
+@pytest.mark.parametrize("B", [1, 3, 12])
+def test_strided_pinned_and_pageable_sources_give_the_same_bytes(B):
+    """Small calls from pageable memory go through the pinned mirrors (CPU copy in, asynchronous copies, CPU copy out); row-strided
+    views (a cv::Mat ROI), pinned sources and larger batches take the other upload paths.  All must equal the dense call; the output
+    rows are `cap` apart with cap != the handle's own capacity."""
+    import torch
+    w, h, nf = 333, 257, 500
+    g = _gpu_extractor(w, h, nf, batch=B)
+    dense = np.stack([synth.make_image(w, h, 20 + i) for i in range(B)])
+    ref_k, ref_d, ref_n = g.extract_batch(dense)
+    o = orc.Extractor(nf, 1.2, 8, 20, 7)
+    ok0, od0 = o.extract(dense[0])
+    assert ref_n[0] == len(ok0) and np.array_equal(ref_d[0][:ref_n[0]], od0)
+    cap = g.kp_cap + 37
+    # (a) ROI of a larger pageable array: row stride > w, gap between images
+    big = np.full((B, h + 9, w + 23), 77, np.uint8)
+    big[:, 4:4 + h, 11:11 + w] = dense
+    # (b) the same in pinned memory; (c) dense pinned
+    pin_big = torch.from_numpy(big.copy()).pin_memory().numpy()
+    pin_dense = torch.from_numpy(dense.copy()).pin_memory().numpy()
+    for name, view in (("pageable roi", big[:, 4:4 + h, 11:11 + w]), ("pinned roi", pin_big[:, 4:4 + h, 11:11 + w]), ("pinned dense", pin_dense),
+                       ("pageable dense", dense)):
+        for rep in range(2):   # twice: the mirrors are reused
+            k, d, n = _abi_extract(g, view, cap)
+            assert np.array_equal(n, ref_n), name
+            for b in range(B):
+                assert np.array_equal(d[b][:n[b]], ref_d[b][:n[b]]), (name, b)
+                assert np.array_equal(k[b][:n[b]], ref_k[b][:n[b]]), (name, b)
+    # a capacity below the keypoint count is reported, not overrun
+    capi = importlib.import_module("orb_slam2-chinese-annotation_b200.capi")
+    with pytest.raises(capi.OrbError) as e:
+        _abi_extract(g, dense, int(ref_n.max()) - 5)
+    assert e.value.status == capi.ORB_ERR_CAPACITY
+    k, d, n = _abi_extract(g, dense, cap)
+    assert np.array_equal(n, ref_n) and np.array_equal(d[0][:n[0]], ref_d[0][:n[0]])

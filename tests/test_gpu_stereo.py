@@ -133,3 +133,53 @@ def test_multi_gpu_front_end_equals_single_handle():
         nl = want["n_l"][b]
         for f in ("kps_l", "desc_l", "u_right", "depth"):
             assert np.array_equal(got[f][b][:nl], want[f][b][:nl]), (b, f)
+
+
+@pytest.mark.parametrize("B", [1, 2])
+def test_stereo_frames_from_strided_and_pinned_views(B):
+    """orb_stereo_frames on one-chunk calls: pageable dense (pinned mirrors both ways), pageable ROI views (row-wise CPU copy into the
+    mirror), pinned sources and pinned outputs (direct copies) all give the bytes of the stepwise path."""
+    import ctypes as C
+    import torch
+    capi = importlib.import_module("orb_slam2-chinese-annotation_b200.capi")
+    w, h, nf, mbf, fx = 640, 360, 800, 40.0, 500.0
+    gl = ext.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B)
+    gr = ext.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B)
+    pairs = [synth.make_stereo_pair(w, h, 30 + i, fx=fx) for i in range(B)]
+    L = np.ascontiguousarray(np.stack([p[0] for p in pairs])); R = np.ascontiguousarray(np.stack([p[1] for p in pairs]))
+    kl, dl, nl = gl.extract_batch(L); kr, dr, nr = gr.extract_batch(R)
+    ur, dp, n = stereo.compute_stereo_matches(gl, gr, mbf, fx, 0.0, batch=B)
+    assert (ur[0][:n[0]] >= 0).sum() > 50
+    cap = gl.kp_cap
+
+    def run(vl, vr, pinned_out):
+        mk = (lambda s, dt: torch.zeros(s, dtype=torch.uint8).pin_memory().numpy().view(dt).reshape(s[:-1] + (-1,))) if pinned_out else None
+        if pinned_out:
+            o = dict(kps_l=mk((B, cap * 28), capi.KP_DTYPE), desc_l=mk((B, cap * 32), np.uint8).reshape(B, cap, 32),
+                     kps_r=mk((B, cap * 28), capi.KP_DTYPE), desc_r=mk((B, cap * 32), np.uint8).reshape(B, cap, 32),
+                     u_right=mk((B, cap * 4), np.float32), depth=mk((B, cap * 4), np.float32))
+        else:
+            o = dict(kps_l=np.zeros((B, cap), capi.KP_DTYPE), desc_l=np.zeros((B, cap, 32), np.uint8), kps_r=np.zeros((B, cap), capi.KP_DTYPE),
+                     desc_r=np.zeros((B, cap, 32), np.uint8), u_right=np.zeros((B, cap), np.float32), depth=np.zeros((B, cap), np.float32))
+        o["n_l"] = np.zeros(B, np.int32); o["n_r"] = np.zeros(B, np.int32)
+        assert vl.strides == vr.strides
+        capi.check(capi.lib().orb_stereo_frames(gl.handle, gr.handle, C.c_void_p(vl.ctypes.data), C.c_void_p(vr.ctypes.data), B, w, h, vl.strides[1],
+                                                C.c_size_t(vl.strides[0]), C.c_float(mbf), C.c_float(0.0), C.c_float(fx), capi.ptr(o["kps_l"]),
+                                                capi.ptr(o["desc_l"]), capi.ptr(o["n_l"]), capi.ptr(o["kps_r"]), capi.ptr(o["desc_r"]), capi.ptr(o["n_r"]),
+                                                capi.ptr(o["u_right"]), capi.ptr(o["depth"]), cap))
+        return o
+
+    bigL = np.full((B, h + 6, w + 40), 9, np.uint8); bigR = bigL.copy()
+    bigL[:, 3:3 + h, 17:17 + w] = L; bigR[:, 3:3 + h, 17:17 + w] = R
+    pinL = torch.from_numpy(L.copy()).pin_memory().numpy(); pinR = torch.from_numpy(R.copy()).pin_memory().numpy()
+    cases = [("pageable dense", L, R, False), ("pageable roi", bigL[:, 3:3 + h, 17:17 + w], bigR[:, 3:3 + h, 17:17 + w], False),
+             ("pinned in, pageable out", pinL, pinR, False), ("pageable in, pinned out", L, R, True), ("pinned both", pinL, pinR, True)]
+    for name, vl, vr, po in cases:
+        for rep in range(2):
+            o = run(vl, vr, po)
+            assert np.array_equal(o["n_l"], nl) and np.array_equal(o["n_r"], nr), name
+            for b in range(B):
+                a, c = nl[b], nr[b]
+                assert np.array_equal(o["desc_l"][b][:a], dl[b][:a]) and np.array_equal(o["desc_r"][b][:c], dr[b][:c]), (name, b)
+                assert np.array_equal(o["kps_l"][b][:a], kl[b][:a]) and np.array_equal(o["kps_r"][b][:c], kr[b][:c]), (name, b)
+                assert np.array_equal(o["u_right"][b][:a], ur[b][:a]) and np.array_equal(o["depth"][b][:a], dp[b][:a]), (name, b)

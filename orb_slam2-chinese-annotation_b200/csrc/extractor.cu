@@ -457,6 +457,17 @@ int orb_download_mirror_stereo(orb_extractor* e, int n, int tk, cudaStream_t st)
     ORB_CUDA(cudaMemcpyAsync(base + o_dp, e->d_depth, (size_t)n * kc * 4, cudaMemcpyDeviceToHost, st));
     return ORB_OK;
 }
+// uRight / depth of ONE image of the last batch -> half 0 of the mirror (layout of a one-image call); host addresses in *h_ur, *h_dp
+int orb_download_mirror_stereo_row(orb_extractor* e, int image, cudaStream_t st, const float** h_ur, const float** h_dp) {
+    size_t o_desc, o_ur, o_dp, total;
+    out_offsets(e, 1, &o_desc, &o_ur, &o_dp, &total);
+    const size_t kc = (size_t)e->plan.kp_cap;
+    ORB_CUDA(cudaMemcpyAsync(e->h_out + o_ur, e->d_u_right + (size_t)image * kc, kc * 4, cudaMemcpyDeviceToHost, st));
+    ORB_CUDA(cudaMemcpyAsync(e->h_out + o_dp, e->d_depth + (size_t)image * kc, kc * 4, cudaMemcpyDeviceToHost, st));
+    *h_ur = reinterpret_cast<const float*>(e->h_out + o_ur);
+    *h_dp = reinterpret_cast<const float*>(e->h_out + o_dp);
+    return ORB_OK;
+}
 void orb_deliver_mirror(orb_extractor* e, int tk, const int* h_counts) {
     orb_extractor::OutPlan& O = e->out_plan[tk];
     if (!O.on) return;

@@ -188,6 +188,7 @@ int orb_upload_can_split(const orb_extractor* e, int w, int h, int stride, size_
 bool orb_out_mirror_ready(orb_extractor* e, int n, bool with_stereo);
 int orb_download_mirror(orb_extractor* e, int n, int tk, cudaStream_t st, int* h_counts);
 int orb_download_mirror_stereo(orb_extractor* e, int n, int tk, cudaStream_t st);
+int orb_download_mirror_stereo_row(orb_extractor* e, int image, cudaStream_t st, const float** h_ur, const float** h_dp);
 // after the call's event: valid rows of the mirror half -> the buffers recorded in out_plan[tk]
 void orb_deliver_mirror(orb_extractor* e, int tk, const int* h_counts);
 bool orb_host_pageable(const void* p);   // ordinary host memory: an "asynchronous" copy out of it returns only when the bytes are staged

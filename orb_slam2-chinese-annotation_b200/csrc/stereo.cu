@@ -11,6 +11,7 @@
 // The per-row lists are built with atomics (unordered): the reference keeps the first candidate
 // on equal distance, i.e. the lowest right index, which a (distance, index) minimum reproduces.
 #include "orb_internal.h"
+#include <cstring>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -686,6 +687,21 @@ int orb_stereo_match(orb_extractor* l, orb_extractor* r, int image, float mbf, f
     if (!l || !u_right || !depth || !n_left || image < 0 || image >= l->last_batch) return ORB_ERR_BAD_ARG;
     int st = stereo_launch(l, r, l->last_batch, mbf, min_d, max_d);
     if (st != ORB_OK) return st;
+    if (l->inflight == 0 && l->h_status && l->h_counts && orb_host_pageable(u_right) && orb_host_pageable(depth) && orb_out_mirror_ready(l, 1, true)) {
+        // results into pageable memory: count, status and both rows are queued behind the kernels into pinned memory (four blocking
+        // copies otherwise), one wait, then the CPU hands the n valid floats of each row over
+        const float *h_ur = nullptr, *h_dp = nullptr;
+        ORB_CUDA(cudaMemcpyAsync(l->h_counts + image, l->d_counts + image, sizeof(int), cudaMemcpyDeviceToHost, l->stream));
+        ORB_CUDA(cudaMemcpyAsync(&l->h_status[0], l->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->stream));
+        if ((st = orb_download_mirror_stereo_row(l, image, l->stream, &h_ur, &h_dp)) != ORB_OK) return st;
+        ORB_CUDA(cudaStreamSynchronize(l->stream));
+        const int n = l->h_counts[image], dst = l->h_status[0];
+        if (dst != 0) { cudaMemsetAsync(l->d_status, 0, sizeof(int), l->stream); orb_set_error("device-side bound exceeded"); return dst; }
+        *n_left = n;
+        if (n > cap) { orb_set_error("stereo output capacity too small"); return ORB_ERR_CAPACITY; }
+        if (n > 0) { std::memcpy(u_right, h_ur, (size_t)n * sizeof(float)); std::memcpy(depth, h_dp, (size_t)n * sizeof(float)); }
+        return ORB_OK;
+    }
     int n = 0, dst = 0;
     ORB_CUDA(cudaMemcpyAsync(&n, l->d_counts + image, sizeof(int), cudaMemcpyDeviceToHost, l->stream));
     ORB_CUDA(cudaMemcpyAsync(&dst, l->d_status, sizeof(int), cudaMemcpyDeviceToHost, l->stream));

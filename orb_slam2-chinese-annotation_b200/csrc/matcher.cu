@@ -38,6 +38,11 @@ struct orb_matcher {
     std::vector<std::pair<size_t, size_t>> pend;   // staged, not yet copied: (workspace offset, bytes), ascending
     cudaEvent_t ev_stage = nullptr;
     bool stage_busy = false;
+    // Results into pageable memory take the same way back: queued into the mirror (d_scal: into h_scal), handed to the caller by the CPU
+    // after ONE wait (ws_download / ws_finish); every such copy made directly holds the calling thread until it is done.
+    struct Deliver { void* dst; const uint8_t* src; size_t bytes; };
+    std::vector<Deliver> deliver;
+    uint8_t* h_scal = nullptr;   // pinned mirror of d_scal (64 bytes)
 };
 
 namespace {
@@ -120,6 +125,28 @@ static cudaStream_t ws_stream(orb_matcher* m) {
         m->pend.clear();
     }
     return m->stream;
+}
+
+// A result of the call: `dev` (inside the workspace or d_scal) -> `dst`.  Pageable dst: queued into the pinned mirror at the same offset, delivered
+// by ws_finish; anything else: copied directly.
+static cudaError_t ws_download(orb_matcher* m, void* dst, const void* dev, size_t bytes) {
+    const uint8_t* d = static_cast<const uint8_t*>(dev);
+    const uint8_t* sc = reinterpret_cast<const uint8_t*>(m->d_scal);
+    uint8_t* mirror = nullptr;
+    if (bytes == 0) return cudaSuccess;
+    if (m->h_stage && d >= m->d_ws && d + bytes <= m->d_ws + m->h_stage_cap) mirror = m->h_stage + (d - m->d_ws);
+    else if (m->h_scal && d >= sc && d + bytes <= sc + 64) mirror = m->h_scal + (d - sc);
+    if (!mirror || bytes > (1u << 20) || !orb_host_pageable(dst)) return cudaMemcpyAsync(dst, dev, bytes, cudaMemcpyDeviceToHost, m->stream);
+    const cudaError_t e = cudaMemcpyAsync(mirror, dev, bytes, cudaMemcpyDeviceToHost, m->stream);
+    if (e == cudaSuccess) { orb_matcher::Deliver dl = {dst, mirror, bytes}; m->deliver.push_back(dl); }
+    return e;
+}
+// Waits for the call's stream and hands the mirrored results over.
+static cudaError_t ws_finish(orb_matcher* m) {
+    const cudaError_t e = cudaStreamSynchronize(m->stream);
+    if (e == cudaSuccess) for (const auto& dl : m->deliver) std::memcpy(dl.dst, dl.src, dl.bytes);
+    m->deliver.clear();
+    return e;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1120,6 +1147,7 @@ int begin_call(orb_matcher* m) {
     ORB_CUDA(cudaSetDevice(m->device));
     m->ws_off = 0;
     m->pend.clear();
+    m->deliver.clear();
     if (m->stage_busy) { ORB_CUDA(cudaEventSynchronize(m->ev_stage)); m->stage_busy = false; }   // the mirror is about to be rewritten
     return ORB_OK;
 }
@@ -1160,6 +1188,7 @@ int orb_matcher_create(int max_pairs, int max_n, int device, orb_matcher** out) 
         if (m->h_stage) { cudaFreeHost(m->h_stage); m->h_stage = nullptr; }
         m->h_stage_cap = 0;
     }
+    if (cudaMallocHost((void**)&m->h_scal, 64) != cudaSuccess) { cudaGetLastError(); m->h_scal = nullptr; }
     *out = m;
     return ORB_OK;
 }
@@ -1169,6 +1198,7 @@ void orb_matcher_destroy(orb_matcher* m) {
     cudaSetDevice(m->device);
     if (m->stream) cudaStreamSynchronize(m->stream);
     if (m->h_stage) cudaFreeHost(m->h_stage);
+    if (m->h_scal) cudaFreeHost(m->h_scal);
     if (m->ev_stage) cudaEventDestroy(m->ev_stage);
     orb_dev_free(m->d_ws); orb_dev_free(m->d_cands); orb_dev_free(m->d_scal);
     if (m->stream) cudaStreamDestroy(m->stream);
@@ -1197,8 +1227,8 @@ int orb_descriptor_distance(orb_matcher* m, const uint8_t* a, const uint8_t* b, 
     if ((st = ws_alloc(m, &dd, n)) != ORB_OK) return st;
     k_distance_pairs<<<(n + 255) / 256, 256, 0, ws_stream(m)>>>(da, db, n, dd);
     m->launches++;
-    ORB_CUDA(cudaMemcpyAsync(dist, dd, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    ORB_CUDA(ws_download(m, dist, dd, (size_t)n * 4));
+    ORB_CUDA(ws_finish(m));
     return ORB_OK;
 }
 
@@ -1227,10 +1257,10 @@ int orb_match_bruteforce(orb_matcher* m, const uint8_t* a, const uint8_t* b, int
     if ((st = ws_alloc(m, &bi, na)) != ORB_OK || (st = ws_alloc(m, &bd, na)) != ORB_OK || (st = ws_alloc(m, &sd, na)) != ORB_OK) return st;
     st = orb_match_bruteforce_device(m, da, db, pairs, n_a, n_b, bi, bd, sd);
     if (st != ORB_OK) return st;
-    ORB_CUDA(cudaMemcpyAsync(best_idx, bi, na * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(best_dist, bd, na * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(second_dist, sd, na * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    ORB_CUDA(ws_download(m, best_idx, bi, na * 4));
+    ORB_CUDA(ws_download(m, best_dist, bd, na * 4));
+    ORB_CUDA(ws_download(m, second_dist, sd, na * 4));
+    ORB_CUDA(ws_finish(m));
     return ORB_OK;
 }
 
@@ -1314,11 +1344,11 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
         m->launches++;
     }
     ORB_CUDA(cudaGetLastError());
-    if (match && o.mode != -1 && F.n > 0) ORB_CUDA(cudaMemcpyAsync(match, dmatch, (size_t)F.n * 4, cudaMemcpyDeviceToHost, m->stream));
-    if (o.q_best_idx && nq > 0) ORB_CUDA(cudaMemcpyAsync(o.q_best_idx, qbi, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
-    if (o.q_best_dist && nq > 0) ORB_CUDA(cudaMemcpyAsync(o.q_best_dist, qbd, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    if (match && o.mode != -1 && F.n > 0) ORB_CUDA(ws_download(m, match, dmatch, (size_t)F.n * 4));
+    if (o.q_best_idx && nq > 0) ORB_CUDA(ws_download(m, o.q_best_idx, qbi, (size_t)nq * 4));
+    if (o.q_best_dist && nq > 0) ORB_CUDA(ws_download(m, o.q_best_dist, qbd, (size_t)nq * 4));
+    ORB_CUDA(ws_download(m, nmatches, m->d_scal, 4));
+    ORB_CUDA(ws_finish(m));
     return ORB_OK;
 }
 
@@ -1564,9 +1594,9 @@ int orb_search_by_bow(orb_matcher* m, const orb_frame_view* kf, const orb_featve
     k_bow_finish<<<1, 32, 0, ws_stream(m)>>>(ne, hidx, hbin, check_orientation, dmatch, m->d_scal);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
-    if (f->n > 0) ORB_CUDA(cudaMemcpyAsync(match_f, dmatch, (size_t)f->n * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    if (f->n > 0) ORB_CUDA(ws_download(m, match_f, dmatch, (size_t)f->n * 4));
+    ORB_CUDA(ws_download(m, nmatches, m->d_scal, 4));
+    ORB_CUDA(ws_finish(m));
     return ORB_OK;
 }
 
@@ -1612,9 +1642,9 @@ int orb_search_for_triangulation(orb_matcher* m, const orb_frame_view* kf1, cons
     k_tri_rot_cull<<<1, 32, 0, ws_stream(m)>>>(kf1->n, K1.angle, K2.angle, check_orientation, dmatch, hidx, hbin, m->d_scal);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
-    if (kf1->n > 0) ORB_CUDA(cudaMemcpyAsync(match12, dmatch, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    if (kf1->n > 0) ORB_CUDA(ws_download(m, match12, dmatch, (size_t)kf1->n * 4));
+    ORB_CUDA(ws_download(m, nmatches, m->d_scal, 4));
+    ORB_CUDA(ws_finish(m));
     return ORB_OK;
 }
 
@@ -1695,10 +1725,10 @@ int orb_search_by_sim3(orb_matcher* m, const orb_frame_view* kf1, const orb_proj
         k_mutual_check<<<(kf1->n + 255) / 256, 256, 0, ws_stream(m)>>>(kf1->n, kf2->n, d1, d2, d12, m->d_scal);
         m->launches++;
         ORB_CUDA(cudaGetLastError());
-        ORB_CUDA(cudaMemcpyAsync(match12, d12, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, m->stream));
+        ORB_CUDA(ws_download(m, match12, d12, (size_t)kf1->n * 4));
     }
-    ORB_CUDA(cudaMemcpyAsync(nfound, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    ORB_CUDA(ws_download(m, nfound, m->d_scal, 4));
+    ORB_CUDA(ws_finish(m));
     return ORB_OK;
 }
 
@@ -1745,9 +1775,9 @@ int orb_search_for_initialization(orb_matcher* m, const orb_frame_view* f1, cons
                                                       hidx, hbin, m->d_scal);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
-    if (nq > 0) ORB_CUDA(cudaMemcpyAsync(match12, d12, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    if (nq > 0) ORB_CUDA(ws_download(m, match12, d12, (size_t)nq * 4));
+    ORB_CUDA(ws_download(m, nmatches, m->d_scal, 4));
+    ORB_CUDA(ws_finish(m));
     return ORB_OK;
 }
 
@@ -1802,9 +1832,9 @@ int orb_search_by_bow_keyframes(orb_matcher* m, const orb_frame_view* kf1, const
     k_bow_finish<<<1, 32, 0, ws_stream(m)>>>(ne, hidx, hbin, check_orientation, dmatch, m->d_scal);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
-    if (kf1->n > 0) ORB_CUDA(cudaMemcpyAsync(match12, dmatch, (size_t)kf1->n * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(nmatches, m->d_scal, 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    if (kf1->n > 0) ORB_CUDA(ws_download(m, match12, dmatch, (size_t)kf1->n * 4));
+    ORB_CUDA(ws_download(m, nmatches, m->d_scal, 4));
+    ORB_CUDA(ws_finish(m));
     return ORB_OK;
 }
 }  // extern "C"
@@ -1922,13 +1952,13 @@ int orb_is_in_frustum(orb_matcher* m, const float* rcw, const float* tcw, const 
                                                             bounds->max_y, viewing_cos_limit, dok, du, dv, dur, dc, dd);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
-    ORB_CUDA(cudaMemcpyAsync(in_view, dok, n, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(u, du, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(v, dv, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(ur, dur, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(view_cos, dc, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaMemcpyAsync(dist, dd, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    ORB_CUDA(ws_download(m, in_view, dok, n));
+    ORB_CUDA(ws_download(m, u, du, (size_t)n * 4));
+    ORB_CUDA(ws_download(m, v, dv, (size_t)n * 4));
+    ORB_CUDA(ws_download(m, ur, dur, (size_t)n * 4));
+    ORB_CUDA(ws_download(m, view_cos, dc, (size_t)n * 4));
+    ORB_CUDA(ws_download(m, dist, dd, (size_t)n * 4));
+    ORB_CUDA(ws_finish(m));
     return ORB_OK;
 }
 
@@ -1947,8 +1977,8 @@ int orb_distinctive_descriptors(orb_matcher* m, int n_points, const int32_t* sta
     k_distinctive<<<n_points, DD_THREADS, 0, ws_stream(m)>>>(ds, dd, db);
     m->launches++;
     ORB_CUDA(cudaGetLastError());
-    ORB_CUDA(cudaMemcpyAsync(best_idx, db, (size_t)n_points * 4, cudaMemcpyDeviceToHost, m->stream));
-    ORB_CUDA(cudaStreamSynchronize(m->stream));
+    ORB_CUDA(ws_download(m, best_idx, db, (size_t)n_points * 4));
+    ORB_CUDA(ws_finish(m));
     return ORB_OK;
 }
 

@@ -30,6 +30,7 @@ __constant__ __align__(16) signed char c_pattern[1024] = {
 __global__ void __launch_bounds__(256) k_ingest(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, const int w, const int h,
                                                 const int stride, const unsigned long long img_stride, const int dst_pitch,
                                                 const unsigned long long dst_img_stride, const int nch, const unsigned magic) {
+    ORB_PDL_SYNC();
     const unsigned idx = blockIdx.x * 256u + threadIdx.x;
     const int y = nch == 1 ? (int)idx : (int)__umulhi(idx, magic);   // idx / nch (idx < 2^20, nch <= 256)
     if (y >= h) return;
@@ -60,7 +61,7 @@ void launch_ingest(cudaStream_t s, const uint8_t* src, uint8_t* dst, int w, int 
     const int nch = (w + 15) / 16;
     const unsigned magic = (unsigned)((1ull << 32) / (unsigned)nch) + 1u;
     dim3 grid((unsigned)(((size_t)nch * h + 255) / 256), batch);
-    k_ingest<<<grid, 256, 0, s>>>(src, dst, w, h, stride, img_stride, dst_pitch, dst_img_stride, nch, magic);
+    orb_launch(orb_pdl(batch), k_ingest, grid, dim3(256), 0, s, src, dst, w, h, stride, (unsigned long long)img_stride, dst_pitch, (unsigned long long)dst_img_stride, nch, magic);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -221,6 +222,7 @@ template <int SP>
 __global__ void __launch_bounds__(FC_WARPS * 32, 6)   // shared memory allows six CTAs per SM: keep the registers within that
 k_fast_cells(const __grid_constant__ TmaMaps tm, int* __restrict__ cell_cnt, uint32_t* __restrict__ stage, const Plan P,
              const int warp_bytes, const int score_off, const int list_off, const int cells_per_warp, const int box_h, const int b0) {
+    ORB_PDL_SYNC();
     constexpr int TP = FC_TP, TPW = TP / 4;
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ uint64_t s_bar[FC_WARPS];
@@ -552,6 +554,7 @@ __global__ void __launch_bounds__(OD_WARPS * 32, 7)
 k_orient_describe(const __grid_constant__ TmaMaps tm_raw, const __grid_constant__ TmaMaps tm_blur, const uint32_t* __restrict__ lvl_kp,
                   const int* __restrict__ lvl_cnt, orb_keypoint* __restrict__ kps, uint8_t* __restrict__ desc,
                   int* __restrict__ counts, const Plan P, const int b0, const int kpw) {
+    ORB_PDL_SYNC();
     extern __shared__ __align__(128) uint8_t od_smem[];
     __shared__ uint64_t s_bar[OD_WARPS][2];
     __shared__ int s_pre[ORB_MAX_LEVELS + 1];
@@ -729,8 +732,8 @@ cudaError_t launch_fast(cudaStream_t s, const TmaMaps& tm, int* cell_cnt, uint32
     // a small batch cannot fill every SM's 24 resident warps with 4 cells per warp: one cell per warp then (per-frame latency)
     const int cpw = (long long)batch * P.total_cells >= 4LL * orb_sm_count() * 24 * FC_CELLS ? FC_CELLS : 1;
     dim3 grid((P.total_cells + FC_WARPS * cpw - 1) / (FC_WARPS * cpw), batch);
-    kern<<<grid, FC_WARPS * 32, tot, s>>>(tm, cell_cnt, stage, P, wb, so, lo, cpw, fast_box_rows(P), b0);
-    return cudaGetLastError();   // a refused launch must fail loudly, not leave stale candidate lists behind
+    e = orb_launch(orb_pdl(batch), kern, grid, dim3(FC_WARPS * 32), (size_t)tot, s, tm, cell_cnt, stage, P, wb, so, lo, cpw, fast_box_rows(P), b0);
+    return e != cudaSuccess ? e : cudaGetLastError();   // a refused launch must fail loudly, not leave stale candidate lists behind
 }
 cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const TmaMaps& tm_blur, const uint32_t* lvl_kp, const int* lvl_cnt,
                                    orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int b0, int batch) {
@@ -740,8 +743,8 @@ cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const 
     // small batches: fewer keypoints per warp, so that the frame's ~2000 keypoints spread over all SMs (per-frame latency)
     const int kpw = (long long)batch * P.kp_cap >= 2LL * orb_sm_count() * 28 * OD_KPW ? OD_KPW : 2;
     dim3 grid((P.kp_cap + OD_WARPS * kpw - 1) / (OD_WARPS * kpw), batch);
-    k_orient_describe<<<grid, OD_WARPS * 32, smem, s>>>(tm_raw, tm_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, b0, kpw);
-    return cudaGetLastError();
+    e = orb_launch(orb_pdl(batch), k_orient_describe, grid, dim3(OD_WARPS * 32), (size_t)smem, s, tm_raw, tm_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, b0, kpw);
+    return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------

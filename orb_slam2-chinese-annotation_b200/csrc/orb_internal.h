@@ -5,6 +5,8 @@
 #include <stdint.h>
 #include <stddef.h>
 #include <string>
+#include <utility>
+#include <cstdlib>
 #include <vector>
 #include "../../include/orb_b200.h"
 
@@ -220,6 +222,27 @@ cudaError_t orb_dev_free(void* p);
             return ORB_ERR_CUDA;                                                            \
         }                                                                                   \
     } while (0)
+
+// Programmatic dependent launch for calls of a few images (a live camera): the kernels of one image are a chain of launches none of which
+// fills the GPU, and the launch-to-launch gap is a large part of each link.  A kernel launched through orb_launch(pdl = true, ...) may be
+// scheduled while its predecessor in the stream still runs; ORB_PDL_SYNC() as the FIRST statement of the kernel lets the successor be
+// scheduled in turn and then waits until every predecessor has completed and its writes are visible, so nothing is read or written early.
+// Without the launch attribute both instructions do nothing.
+#define ORB_PDL_SYNC() asm volatile("griddepcontrol.launch_dependents;\n\tgriddepcontrol.wait;" ::: "memory")
+inline bool orb_pdl(int batch) {
+    static const bool off = getenv("ORB_B200_NO_PDL") != nullptr;
+    return batch <= 8 && !off;
+}
+template <typename... KA, typename... A>
+inline cudaError_t orb_launch(bool pdl, void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, A&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, std::forward<A>(args)...);
+}
 
 // Popcount Hamming distance of two 256-bit descriptors held as 8 x u32.
 __device__ __forceinline__ int orb_hamming256(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {

@@ -74,6 +74,7 @@ __global__ void __launch_bounds__(RZ_WARPS * 32) k_resize_tma(const __grid_const
     __shared__ __align__(128) uint8_t tile[ORB_RZ_BOXH * ORB_RZ_BOXW + 16];   // +16: the last lane's 8-byte window may overhang
     __shared__ uint2 rows[ORB_RZ_DH];   // per destination row: byte offsets of its two source rows in the tile | packed vertical weights
     __shared__ uint64_t bar;
+    ORB_PDL_SYNC();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int dx0 = blockIdx.x * ORB_RZ_DW, dy0 = blockIdx.y * ORB_RZ_DH;
     const int sx0 = (int)(((unsigned)dx0 * dst.rz_qx) >> 16) & ~15, sy0 = (int)(((unsigned)dy0 * dst.rz_qy) >> 16);
@@ -256,7 +257,7 @@ void launch_resize(cudaStream_t s, uint8_t* pyr, const CUtensorMap* src_map, boo
         return;
     }
     dim3 grid((dst.w + ORB_RZ_DW - 1) / ORB_RZ_DW, (dst.h + ORB_RZ_DH - 1) / ORB_RZ_DH, batch);
-    k_resize_tma<<<grid, RZ_WARPS * 32, 0, s>>>(*src_map, pyr, src, dst, b0);
+    orb_launch(orb_pdl(batch), k_resize_tma, grid, dim3(RZ_WARPS * 32), 0, s, *src_map, pyr, src, dst, b0);
 }
 void launch_gauss(cudaStream_t s, const TmaMaps& maps, const uint8_t* pyr, uint8_t* blur, const Plan& P, int b0, int batch) {
     dim3 grid(P.total_tiles, batch);

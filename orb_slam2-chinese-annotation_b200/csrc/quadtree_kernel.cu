@@ -102,6 +102,7 @@ k_quadtree(const int* __restrict__ cell_cnt, int* __restrict__ cell_prefix, cons
            int* __restrict__ status, const Plan P, const int cap, const int p2) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ QtShared sh;
+    ORB_PDL_SYNC();
     // blocks are dispatched in linear order (x fastest): image = x, level = y starts every image's level 0 (the longest CTA by far:
     // it sweeps the most candidates per pass) before any level 1, i.e. longest-processing-time-first over the whole batch
     const int b = blockIdx.x, l = blockIdx.y;
@@ -406,6 +407,6 @@ cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefi
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
     dim3 grid(batch, P.nlevels);
-    kern<<<grid, nt, bytes, s>>>(cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, status, P, cap, p2);
-    return cudaGetLastError();
+    e = orb_launch(orb_pdl(batch), kern, grid, dim3(nt), bytes, s, cell_cnt, cell_prefix, stage, keys, lvl_kp, lvl_cnt, lvl_ncand, status, P, cap, p2);
+    return e != cudaSuccess ? e : cudaGetLastError();
 }

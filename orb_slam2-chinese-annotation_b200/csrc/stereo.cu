@@ -33,6 +33,7 @@ k_stereo_rows(const orb_keypoint* __restrict__ kps_r, const int* __restrict__ co
               int2* __restrict__ row_items, int* __restrict__ status, const StereoGeom S) {
     extern __shared__ int s_rows[];  // h0 + 1 counters, then h0 + 1 cursors
     __shared__ int s_warp[17];
+    ORB_PDL_SYNC();
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int H = S.h0;
     int* cnt = s_rows;
@@ -99,6 +100,7 @@ k_stereo_search(const orb_keypoint* __restrict__ kps_l, const uint8_t* __restric
                 const uint8_t* __restrict__ desc_r, const int* __restrict__ row_start, const int2* __restrict__ row_items,
                 float* __restrict__ u_right, float* __restrict__ depth, int* __restrict__ sad, int2* __restrict__ jobs, const StereoGeom S,
                 const float min_d, const float max_d) {
+    ORB_PDL_SYNC();
     const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int sub = lane & (SM_GROUP - 1);
     const int iL = (blockIdx.x * SM_WARPS + warp) * SM_KP_PER_WARP + (lane / SM_GROUP);
@@ -193,6 +195,7 @@ k_stereo_refine(const __grid_constant__ TmaMaps tm_l, const __grid_constant__ Tm
     __shared__ __align__(128) uint8_t s_buf[SR_WARPS][2][SR_BUF];
     __shared__ int s_part[SR_WARPS][11 * 12];
     __shared__ uint64_t s_bar[SR_WARPS][2];
+    ORB_PDL_SYNC();
     const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (lane == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(st_smem_u32(&s_bar[warp][0])) : "memory");
@@ -319,6 +322,7 @@ k_stereo_median(const int* __restrict__ counts_l, float* __restrict__ u_right, f
                 const int kp_cap) {
     __shared__ int hist[256];
     __shared__ int s_sel[3];
+    ORB_PDL_SYNC();
     const int b = blockIdx.x, tid = threadIdx.x;
     const int n = counts_l[b];
     const int* sd = sad + (size_t)b * kp_cap;
@@ -383,21 +387,22 @@ static int stereo_launch(orb_extractor* l, orb_extractor* r, int b0, int batch, 
     const bool T = l->timing;
     if (T) cudaEventRecord(l->ev_stage[6], l->stream);
     nvtxRangePushA("orb:stereo_rows");
-    k_stereo_rows<<<batch, 512, smem, l->stream>>>(r->d_kps + kr, r->d_counts + b0, row_start, row_items, l->d_status, S);
+    const bool pdl = orb_pdl(batch);
+    orb_launch(pdl, k_stereo_rows, dim3(batch), dim3(512), smem, l->stream, r->d_kps + kr, r->d_counts + b0, row_start, row_items, l->d_status, S);
     nvtxRangePop();
     if (T) cudaEventRecord(l->ev_stage[7], l->stream);
     nvtxRangePushA("orb:stereo_match");
     dim3 grid((l->plan.kp_cap + SM_WARPS * SM_KP_PER_WARP - 1) / (SM_WARPS * SM_KP_PER_WARP), batch);
     int2* jobs = l->d_st_jobs + kl;
-    k_stereo_search<<<grid, SM_WARPS * 32, 0, l->stream>>>(l->d_kps + kl, l->d_desc + kl * 32, l->d_counts + b0, r->d_desc + kr * 32, row_start, row_items,
-                                                          l->d_u_right + kl, l->d_depth + kl, l->d_sad + kl, jobs, S, min_d, max_d);
+    orb_launch(pdl, k_stereo_search, grid, dim3(SM_WARPS * 32), 0, l->stream, l->d_kps + kl, l->d_desc + kl * 32, l->d_counts + b0, r->d_desc + kr * 32,
+               row_start, row_items, l->d_u_right + kl, l->d_depth + kl, l->d_sad + kl, jobs, S, min_d, max_d);
     dim3 grid2((l->plan.kp_cap + SR_WARPS * SR_KPW - 1) / (SR_WARPS * SR_KPW), batch);
-    k_stereo_refine<<<grid2, SR_WARPS * 32, 0, l->stream>>>(l->tm_st_l, r->tm_st_r, l->d_kps + kl, l->d_counts + b0, jobs, l->d_u_right + kl, l->d_depth + kl,
-                                                           l->d_sad + kl, S, mbf, min_d, max_d, b0);
+    orb_launch(pdl, k_stereo_refine, grid2, dim3(SR_WARPS * 32), 0, l->stream, l->tm_st_l, r->tm_st_r, l->d_kps + kl, l->d_counts + b0, jobs, l->d_u_right + kl,
+               l->d_depth + kl, l->d_sad + kl, S, mbf, min_d, max_d, b0);
     nvtxRangePop();
     if (T) cudaEventRecord(l->ev_stage[8], l->stream);
     nvtxRangePushA("orb:stereo_median");
-    k_stereo_median<<<batch, 512, 0, l->stream>>>(l->d_counts + b0, l->d_u_right + kl, l->d_depth + kl, l->d_sad + kl, l->plan.kp_cap);
+    orb_launch(pdl, k_stereo_median, dim3(batch), dim3(512), 0, l->stream, l->d_counts + b0, l->d_u_right + kl, l->d_depth + kl, l->d_sad + kl, l->plan.kp_cap);
     nvtxRangePop();
     if (T) { cudaEventRecord(l->ev_stage[9], l->stream); l->stage_valid[5] = l->stage_valid[6] = l->stage_valid[7] = true; }
     l->launches += 4;

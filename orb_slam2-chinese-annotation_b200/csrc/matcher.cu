@@ -366,7 +366,9 @@ template <bool FILL>
 __global__ void __launch_bounds__(256)
 k_area_candidates(int nq, const Query* __restrict__ q, const uint8_t* __restrict__ qdesc, DFrame F0, int filter,
                   const float* __restrict__ inv_sigma2, int* __restrict__ counts, const int* __restrict__ starts,
-                  uint32_t* __restrict__ cands, Batch B) {
+                  uint32_t* __restrict__ cands, Batch B, const int cap = 0) {
+    // cap > 0 (single-pair calls): the candidate buffer's capacity; a fill that would not fit does nothing (the host grows the buffer and repeats)
+    if (FILL && cap > 0 && starts[nq] > cap) return;
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (B.qstride) {
         const size_t o = (size_t)blockIdx.y * B.qstride;
@@ -729,9 +731,10 @@ k_resolve_projection_par(int mode, int nq, const int* __restrict__ starts, const
                          const float* __restrict__ q_angle, DFrame F, const uint8_t* __restrict__ occupied, float nn_ratio, int check_ori,
                          int max_dist, int* __restrict__ match, int* __restrict__ q_best_idx, int* __restrict__ q_best_dist,
                          int* __restrict__ hist_idx, int* __restrict__ hist_bin, int* __restrict__ nmatches_out, int* __restrict__ first_claim,
-                         int* __restrict__ decision) {
+                         int* __restrict__ decision, const int cap) {
     __shared__ int s_cnt[32];
     __shared__ int s_changed, s_nm, s_nh;
+    if (cap > 0 && starts[nq] > cap) return;   // the candidate lists were not written (see k_area_candidates)
     const int tid = threadIdx.x;
     for (int i = tid; i < F.n; i += RPP_THREADS) { first_claim[i] = 0x7fffffff; match[i] = -1; }
     for (int w = tid; w < nq; w += RPP_THREADS) decision[w] = -2;   // no decision yet
@@ -803,9 +806,9 @@ k_resolve_projection_par(int mode, int nq, const int* __restrict__ starts, const
 // independent; one warp per point takes the first minimum-distance candidate (strict <).
 __global__ void __launch_bounds__(256)
 k_best_independent(int nq, const int* __restrict__ starts, const uint32_t* __restrict__ cands, const uint8_t* __restrict__ occupied,
-                   int max_dist, int* __restrict__ q_best_idx, int* __restrict__ q_best_dist, int* __restrict__ nmatches_out) {
+                   int max_dist, int* __restrict__ q_best_idx, int* __restrict__ q_best_dist, int* __restrict__ nmatches_out, const int cap = 0) {
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (w >= nq) return;
+    if (w >= nq || (cap > 0 && starts[nq] > cap)) return;
     const int c0 = starts[w], c1 = starts[w + 1];
     unsigned best = 0xffffffffu;
     for (int p = c0 + lane; p < c1; p += 32) {
@@ -1314,41 +1317,53 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
     }
     if (occupied) { if ((st = ws_upload(m, &d_occupied, occupied, F.n)) != ORB_OK) return st; }
     const int filter = o.filter; const float* d_inv_sigma2 = o.d_inv_sigma2;
+    int *first_claim = nullptr, *decision = nullptr;
+    if (o.mode != -1) {
+        // one frame pair per call: the parallel fixpoint resolve (the one-warp kernel serves the batched entry points, one warp per pair)
+        if ((st = ws_alloc(m, &first_claim, std::max(F.n, 1))) != ORB_OK || (st = ws_alloc(m, &decision, std::max(nq, 1))) != ORB_OK) return st;
+    }
+    (void)occ;
+    const int blocks = (nq * 32 + 255) / 256;
     if (nq > 0) {
-        const int blocks = (nq * 32 + 255) / 256;
         k_area_candidates<false><<<blocks, 256, 0, ws_stream(m)>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, counts, nullptr, nullptr, Batch{0, nullptr, nullptr});
         k_scan<<<1, 1024, 0, ws_stream(m)>>>(counts, nq, starts, Batch{0, nullptr, nullptr}, nullptr);
-        int total = 0;
-        ORB_CUDA(cudaMemcpyAsync(&total, starts + nq, 4, cudaMemcpyDeviceToHost, m->stream));
-        ORB_CUDA(cudaStreamSynchronize(m->stream));
-        if ((st = ensure_cands(m, (size_t)total)) != ORB_OK) return st;
-        m->last_cands = total;
-        k_area_candidates<true><<<blocks, 256, 0, ws_stream(m)>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, nullptr, starts, m->d_cands, Batch{0, nullptr, nullptr});
-        m->launches += 3;
+        m->launches += 2;
     } else {
         ORB_CUDA(cudaMemsetAsync(starts, 0, 4, m->stream));
     }
-    if (o.mode == -1) {
-        ORB_CUDA(cudaMemsetAsync(m->d_scal, 0, 4, m->stream));
+    // The size of the candidate lists is only known on the device.  Instead of waiting for it in the middle of the call, the fill and the
+    // resolve are queued against the buffer's present capacity (they do nothing when the lists do not fit) and the total comes back with
+    // the results; only a call whose lists did not fit grows the buffer and queues the two steps again.
+    int32_t total = 0;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        const int cap = (int)std::min<size_t>(m->cands_cap, 0x7fffffff);
         if (nq > 0) {
-            k_best_independent<<<(nq * 32 + 255) / 256, 256, 0, ws_stream(m)>>>(nq, starts, m->d_cands, d_occupied, o.max_dist, qbi, qbd, m->d_scal);
+            k_area_candidates<true><<<blocks, 256, 0, ws_stream(m)>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, nullptr, starts, m->d_cands, Batch{0, nullptr, nullptr}, cap);
             m->launches++;
         }
-    } else {
-        // one frame pair per call: the parallel fixpoint resolve (the one-warp kernel serves the batched entry points, one warp per pair)
-        int *first_claim, *decision;
-        if ((st = ws_alloc(m, &first_claim, std::max(F.n, 1))) != ORB_OK || (st = ws_alloc(m, &decision, std::max(nq, 1))) != ORB_OK) return st;
-        (void)occ;
-        k_resolve_projection_par<<<1, RPP_THREADS, 0, ws_stream(m)>>>(o.mode, nq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied, o.nn_ratio, o.check_ori,
-                                                                   o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal, first_claim, decision);
-        m->launches++;
+        if (o.mode == -1) {
+            ORB_CUDA(cudaMemsetAsync(m->d_scal, 0, 4, m->stream));
+            if (nq > 0) {
+                k_best_independent<<<blocks, 256, 0, ws_stream(m)>>>(nq, starts, m->d_cands, d_occupied, o.max_dist, qbi, qbd, m->d_scal, cap);
+                m->launches++;
+            }
+        } else {
+            k_resolve_projection_par<<<1, RPP_THREADS, 0, ws_stream(m)>>>(o.mode, nq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied, o.nn_ratio, o.check_ori,
+                                                                       o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal, first_claim, decision, cap);
+            m->launches++;
+        }
+        ORB_CUDA(cudaGetLastError());
+        if (match && o.mode != -1 && F.n > 0) ORB_CUDA(ws_download(m, match, dmatch, (size_t)F.n * 4));
+        if (o.q_best_idx && nq > 0) ORB_CUDA(ws_download(m, o.q_best_idx, qbi, (size_t)nq * 4));
+        if (o.q_best_dist && nq > 0) ORB_CUDA(ws_download(m, o.q_best_dist, qbd, (size_t)nq * 4));
+        ORB_CUDA(ws_download(m, nmatches, m->d_scal, 4));
+        ORB_CUDA(ws_download(m, &total, starts + nq, 4));
+        ORB_CUDA(ws_finish(m));
+        if ((size_t)total <= m->cands_cap) break;
+        if (attempt == 1) { orb_set_error("candidate lists changed size between two passes"); return ORB_ERR_INTERNAL; }
+        if ((st = ensure_cands(m, (size_t)total)) != ORB_OK) return st;
     }
-    ORB_CUDA(cudaGetLastError());
-    if (match && o.mode != -1 && F.n > 0) ORB_CUDA(ws_download(m, match, dmatch, (size_t)F.n * 4));
-    if (o.q_best_idx && nq > 0) ORB_CUDA(ws_download(m, o.q_best_idx, qbi, (size_t)nq * 4));
-    if (o.q_best_dist && nq > 0) ORB_CUDA(ws_download(m, o.q_best_dist, qbd, (size_t)nq * 4));
-    ORB_CUDA(ws_download(m, nmatches, m->d_scal, 4));
-    ORB_CUDA(ws_finish(m));
+    m->last_cands = total;
     return ORB_OK;
 }
 

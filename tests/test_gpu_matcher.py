@@ -8,6 +8,7 @@ import orc
 synth = importlib.import_module("orb_slam2-chinese-annotation_b200.synth")
 views = importlib.import_module("orb_slam2-chinese-annotation_b200.views")
 matcher = importlib.import_module("orb_slam2-chinese-annotation_b200.matcher")
+capi = importlib.import_module("orb_slam2-chinese-annotation_b200.capi")
 pytestmark = pytest.mark.gpu
 
 
@@ -55,6 +56,22 @@ def test_grid_assignment(gm):
         gs, gi = gm.assign_features_to_grid(f)
         os_, oi = orc.assign_features_to_grid(f)
         assert np.array_equal(gs, os_) and np.array_equal(gi, oi)
+
+
+def test_projection_search_that_outgrows_the_candidate_buffer():
+    """A single-pair search queues the candidate fill and the resolve against the buffer's present capacity and learns the lists' size
+    with the results; lists that do not fit make it grow the buffer and queue both again.  A handle for 2000 features starts with
+    128 k candidate slots; a wide search window needs more."""
+    small = matcher.ORBmatcher(0.8, True, max_n=2000, max_pairs=1)
+    f, mps, occ = synth.make_projection_scenario(2000, 2000, 9)
+    F = _frame(f)
+    for th in (3.0, 80.0, 3.0):   # fits, outgrows (twice the work), fits again in the grown buffer
+        n_g, m_g = small.SearchByProjection(F, mps, th)
+        n_o, m_o = orc.search_by_projection_mps(F, mps, th, small.mfNNratio, None)
+        assert n_g == n_o and np.array_equal(m_g, m_o), th
+        if th > 10:
+            assert capi.lib().orb_matcher_last_candidates(small._h) > 2000 * 64
+    small.close()
 
 
 def test_grid_assignment_between_4096_and_8192_keypoints():

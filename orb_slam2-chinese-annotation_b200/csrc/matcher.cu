@@ -206,6 +206,7 @@ k_grid_build(const float* __restrict__ x, const float* __restrict__ y, int n, in
              int* __restrict__ cell_items, int* __restrict__ n_items, int stride = 0, const int* __restrict__ n_arr = nullptr) {
     extern __shared__ uint32_t keys[];
     __shared__ int cnt[GRID_CELLS + 1];
+    ORB_PDL_SYNC();
     __shared__ int cur[GRID_CELLS];
     __shared__ int s_warp[33];
     __shared__ int s_max;
@@ -299,6 +300,7 @@ k_grid_build(const float* __restrict__ x, const float* __restrict__ y, int n, in
 __global__ void k_prep_mappoints(int n, const uint8_t* __restrict__ valid, const float* __restrict__ px, const float* __restrict__ py,
                                  const float* __restrict__ pxr, const int* __restrict__ level, const float* __restrict__ view_cos,
                                  float th, DFrame F, Query* __restrict__ q, Batch B) {
+    ORB_PDL_SYNC();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (B.qstride) {
         const size_t o = (size_t)blockIdx.y * B.qstride;
@@ -322,6 +324,7 @@ __global__ void k_prep_lastframe(int n, const uint8_t* __restrict__ valid, const
                                  const float* __restrict__ zc, const int* __restrict__ octave, orb_camera cam, float th, int forward,
                                  int backward, DFrame F, Query* __restrict__ q, Batch B, const uint8_t* __restrict__ fwd_arr,
                                  const uint8_t* __restrict__ bwd_arr) {
+    ORB_PDL_SYNC();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (B.qstride) {
         const size_t o = (size_t)blockIdx.y * B.qstride;
@@ -367,6 +370,7 @@ __global__ void __launch_bounds__(256)
 k_area_candidates(int nq, const Query* __restrict__ q, const uint8_t* __restrict__ qdesc, DFrame F0, int filter,
                   const float* __restrict__ inv_sigma2, int* __restrict__ counts, const int* __restrict__ starts,
                   uint32_t* __restrict__ cands, Batch B, const int cap = 0) {
+    ORB_PDL_SYNC();
     // cap > 0 (single-pair calls): the candidate buffer's capacity; a fill that would not fit does nothing (the host grows the buffer and repeats)
     if (FILL && cap > 0 && starts[nq] > cap) return;
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -449,6 +453,7 @@ k_area_candidates(int nq, const Query* __restrict__ q, const uint8_t* __restrict
 // single-CTA exclusive scan: starts[0..n] from counts[0..n)
 __global__ void __launch_bounds__(1024) k_scan(const int* __restrict__ counts, int n, int* __restrict__ starts, Batch B, int* __restrict__ totals) {
     __shared__ int ws[33];
+    ORB_PDL_SYNC();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (B.qstride) { n = B.nq_arr[blockIdx.x]; counts += (size_t)blockIdx.x * B.qstride; starts += (size_t)blockIdx.x * (B.qstride + 1); }
     int carry = 0;
@@ -734,6 +739,7 @@ k_resolve_projection_par(int mode, int nq, const int* __restrict__ starts, const
                          int* __restrict__ decision, const int cap) {
     __shared__ int s_cnt[32];
     __shared__ int s_changed, s_nm, s_nh;
+    ORB_PDL_SYNC();
     if (cap > 0 && starts[nq] > cap) return;   // the candidate lists were not written (see k_area_candidates)
     const int tid = threadIdx.x;
     for (int i = tid; i < F.n; i += RPP_THREADS) { first_claim[i] = 0x7fffffff; match[i] = -1; }
@@ -807,6 +813,7 @@ k_resolve_projection_par(int mode, int nq, const int* __restrict__ starts, const
 __global__ void __launch_bounds__(256)
 k_best_independent(int nq, const int* __restrict__ starts, const uint32_t* __restrict__ cands, const uint8_t* __restrict__ occupied,
                    int max_dist, int* __restrict__ q_best_idx, int* __restrict__ q_best_dist, int* __restrict__ nmatches_out, const int cap = 0) {
+    ORB_PDL_SYNC();
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (w >= nq || (cap > 0 && starts[nq] > cap)) return;
     const int c0 = starts[w], c1 = starts[w + 1];
@@ -1117,7 +1124,7 @@ int upload_frame(orb_matcher* m, const orb_frame_view* f, DFrame* D, bool need_g
         while (p2 < std::max(f->n, 1)) p2 <<= 1;
         const size_t smem = (size_t)p2 * 4;
         if (smem > GRID_BUILD_DYN_DEFAULT) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_grid_build<<<1, 1024, smem, ws_stream(m)>>>(D->x, D->y, f->n, p2, f->grid, cs, ci, ni);
+        ORB_CUDA(orb_launch(true, k_grid_build, dim3(1), dim3(1024), smem, ws_stream(m), D->x, D->y, f->n, p2, f->grid, cs, ci, ni, 0, (const int*)nullptr));
         m->launches++;
         D->cell_start = cs; D->cell_items = ci;
     }
@@ -1325,8 +1332,9 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
     (void)occ;
     const int blocks = (nq * 32 + 255) / 256;
     if (nq > 0) {
-        k_area_candidates<false><<<blocks, 256, 0, ws_stream(m)>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, counts, nullptr, nullptr, Batch{0, nullptr, nullptr});
-        k_scan<<<1, 1024, 0, ws_stream(m)>>>(counts, nq, starts, Batch{0, nullptr, nullptr}, nullptr);
+        ORB_CUDA(orb_launch(true, k_area_candidates<false>, dim3(blocks), dim3(256), 0, ws_stream(m), nq, dq, d_qdesc, F, filter, d_inv_sigma2, counts, (const int*)nullptr,
+                            (uint32_t*)nullptr, Batch{0, nullptr, nullptr}, 0));
+        ORB_CUDA(orb_launch(true, k_scan, dim3(1), dim3(1024), 0, ws_stream(m), (const int*)counts, nq, starts, Batch{0, nullptr, nullptr}, (int*)nullptr));
         m->launches += 2;
     } else {
         ORB_CUDA(cudaMemsetAsync(starts, 0, 4, m->stream));
@@ -1338,18 +1346,20 @@ static int projection_common(orb_matcher* m, const ProjOpts& o, int nq, const Qu
     for (int attempt = 0; attempt < 2; ++attempt) {
         const int cap = (int)std::min<size_t>(m->cands_cap, 0x7fffffff);
         if (nq > 0) {
-            k_area_candidates<true><<<blocks, 256, 0, ws_stream(m)>>>(nq, dq, d_qdesc, F, filter, d_inv_sigma2, nullptr, starts, m->d_cands, Batch{0, nullptr, nullptr}, cap);
+            ORB_CUDA(orb_launch(true, k_area_candidates<true>, dim3(blocks), dim3(256), 0, ws_stream(m), nq, dq, d_qdesc, F, filter, d_inv_sigma2, (int*)nullptr, (const int*)starts,
+                                m->d_cands, Batch{0, nullptr, nullptr}, cap));
             m->launches++;
         }
         if (o.mode == -1) {
             ORB_CUDA(cudaMemsetAsync(m->d_scal, 0, 4, m->stream));
             if (nq > 0) {
-                k_best_independent<<<blocks, 256, 0, ws_stream(m)>>>(nq, starts, m->d_cands, d_occupied, o.max_dist, qbi, qbd, m->d_scal, cap);
+                ORB_CUDA(orb_launch(true, k_best_independent, dim3(blocks), dim3(256), 0, ws_stream(m), nq, (const int*)starts, (const uint32_t*)m->d_cands, d_occupied, o.max_dist, qbi, qbd,
+                                    m->d_scal, cap));
                 m->launches++;
             }
         } else {
-            k_resolve_projection_par<<<1, RPP_THREADS, 0, ws_stream(m)>>>(o.mode, nq, starts, m->d_cands, d_blocks, d_qangle, F, d_occupied, o.nn_ratio, o.check_ori,
-                                                                       o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal, first_claim, decision, cap);
+            ORB_CUDA(orb_launch(true, k_resolve_projection_par, dim3(1), dim3(RPP_THREADS), 0, ws_stream(m), o.mode, nq, (const int*)starts, (const uint32_t*)m->d_cands, d_blocks, d_qangle, F,
+                                d_occupied, o.nn_ratio, o.check_ori, o.max_dist, dmatch, qbi, qbd, hidx, hbin, m->d_scal, first_claim, decision, cap));
             m->launches++;
         }
         ORB_CUDA(cudaGetLastError());
@@ -1383,7 +1393,7 @@ int orb_search_by_projection_mappoints(orb_matcher* m, const orb_frame_view* f, 
         (st = ws_upload(m, &dvc, mps->view_cos, nq)) != ORB_OK || (st = ws_upload(m, &dd, mps->desc, (size_t)nq * 32)) != ORB_OK ||
         (st = ws_upload(m, &db, mps->blocks, nq)) != ORB_OK || (st = ws_alloc(m, &dq, std::max(nq, 1))) != ORB_OK) return st;
     if (mps->proj_xr) { if ((st = ws_upload(m, &dxr, mps->proj_xr, nq)) != ORB_OK) return st; }
-    if (nq > 0) { k_prep_mappoints<<<(nq + 255) / 256, 256, 0, ws_stream(m)>>>(nq, dv, dx, dy, dxr, dl, dvc, th, F, dq, Batch{0, nullptr, nullptr}); m->launches++; }
+    if (nq > 0) { ORB_CUDA(orb_launch(true, k_prep_mappoints, dim3((nq + 255) / 256), dim3(256), 0, ws_stream(m), nq, dv, dx, dy, dxr, dl, dvc, th, F, dq, Batch{0, nullptr, nullptr})); m->launches++; }
     ProjOpts o; o.mode = 0; o.nn_ratio = nn_ratio;
     return projection_common(m, o, nq, dq, dd, db, nullptr, F, occupied, match, nmatches);
 }
@@ -1405,7 +1415,7 @@ int orb_search_by_projection_lastframe(orb_matcher* m, const orb_frame_view* cur
         (st = ws_upload(m, &doct, last->octave, nq)) != ORB_OK || (st = ws_upload(m, &da, last->angle, nq)) != ORB_OK ||
         (st = ws_upload(m, &dd, last->desc, (size_t)nq * 32)) != ORB_OK || (st = ws_upload(m, &db, last->blocks, nq)) != ORB_OK ||
         (st = ws_alloc(m, &dq, std::max(nq, 1))) != ORB_OK) return st;
-    if (nq > 0) { k_prep_lastframe<<<(nq + 255) / 256, 256, 0, ws_stream(m)>>>(nq, dv, dx, dy, dz, doct, *cam, th, forward, backward, F, dq, Batch{0, nullptr, nullptr}, nullptr, nullptr); m->launches++; }
+    if (nq > 0) { ORB_CUDA(orb_launch(true, k_prep_lastframe, dim3((nq + 255) / 256), dim3(256), 0, ws_stream(m), nq, dv, dx, dy, dz, doct, *cam, th, forward, backward, F, dq, Batch{0, nullptr, nullptr}, (const uint8_t*)nullptr, (const uint8_t*)nullptr)); m->launches++; }
     ProjOpts o; o.mode = 1; o.check_ori = check_orientation;
     return projection_common(m, o, nq, dq, dd, db, da, F, occupied, match, nmatches);
 }

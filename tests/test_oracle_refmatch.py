@@ -85,6 +85,28 @@ def test_compute_stereo_matches(dropin, tmp_path, w, h, nf, mbf, fx, seed):
     assert np.array_equal(our2, our) and np.array_equal(odp2, odp)
 
 
+@pytest.mark.parametrize("w,h,nf,mbf,fx,seed,cfg", [(640, 480, 900, 40.0, 500.0, 3, (1.1, 5, 12, 5)),
+                                                   (752, 480, 1000, 47.90639384423901, 435.2046959714599, 4, (1.2, 12, 20, 7))])
+def test_compute_stereo_matches_at_other_settings(dropin, tmp_path, w, h, nf, mbf, fx, seed, cfg):
+    """The same with the non-default pyramids of tests/test_gpu_stereo.py (scale factor 1.1 x 5 levels, 1.2 x 12 levels): the search
+    radius and the window scale follow mvScaleFactors / mvInvScaleFactors in the verbatim Frame.cc and in the port alike."""
+    sf, nl, ini, mn = cfg
+    left, right = synth.make_stereo_pair(w, h, seed, fx=fx)
+    left = np.ascontiguousarray(left); right = np.ascontiguousarray(right)
+    out = dropin("stereo", {"params": np.array([w, h, nf, nl, ini, mn], np.int32), "scale": D._f32(sf), "left": left.reshape(-1), "right": right.reshape(-1),
+                            "stereo": np.array([mbf, fx], np.float32)}, tmp_path)
+    ol = orc.Extractor(nf, sf, nl, ini, mn); orr = orc.Extractor(nf, sf, nl, ini, mn)
+    okl, odl = ol.extract(left); okr, odr = orr.extract(right)
+    rkl = out["kl"].view(REFKP); rkr = out["kr"].view(REFKP)
+    assert len(rkl) == len(okl) and len(rkr) == len(okr)
+    for f in ("x", "y", "angle", "octave"):
+        assert np.array_equal(rkl[f], okl[f]) and np.array_equal(rkr[f], okr[f])
+    assert np.array_equal(out["dl"].reshape(-1, 32), odl) and np.array_equal(out["dr"].reshape(-1, 32), odr)
+    our, odp, _, _ = orc.stereo_match(ol, orr, okl, odl, okr, odr, np.float32(mbf), 0.0, float(out["max_d"][0]))
+    assert np.array_equal(out["u_right"], our) and np.array_equal(out["depth"], odp)
+    assert (our >= 0).sum() > 50
+
+
 @pytest.mark.parametrize("seed", [0, 1])
 def test_grid_and_features_in_area(dropin, tmp_path, seed):
     """Frame::AssignFeaturesToGrid / GetFeaturesInArea and KeyFrame::GetFeaturesInArea (verbatim) == oracle grid."""

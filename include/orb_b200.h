@@ -146,7 +146,10 @@ int orb_stereo_match_batch(orb_extractor* left, orb_extractor* right, int batch,
  * pairs held in HOST memory.  The batch is cut into chunks of image slots whose upload, kernels
  * and download overlap on three streams.  Outputs as orb_extract_batch (per side) and
  * orb_stereo_match_batch; all arrays are [batch][cap] and rows are written whole (the tail beyond
- * n_l[b] / n_r[b] is unspecified).  Pinned host buffers are needed for the copies to overlap. */
+ * n_l[b] / n_r[b] is unspecified).  Pinned host buffers are needed for the copies to overlap.  Calls of at most 8 pairs whose
+ * images / result arrays are ordinary pageable memory (a cv::Mat, a std::vector: the per-frame use) are staged through pinned
+ * mirrors inside the handles (CPU copy in and out, asynchronous copies across the link) and their kernels are launched as a
+ * programmatic dependent chain; results are the same bytes either way. */
 int orb_stereo_frames(orb_extractor* left, orb_extractor* right, const uint8_t* imgs_l, const uint8_t* imgs_r, int batch,
                       int w, int h, int stride, size_t img_stride, float mbf, float min_d, float max_d,
                       orb_keypoint* kps_l, uint8_t* desc_l, int32_t* n_l, orb_keypoint* kps_r, uint8_t* desc_r, int32_t* n_r,

@@ -61,7 +61,8 @@ void launch_ingest(cudaStream_t s, const uint8_t* src, uint8_t* dst, int w, int 
     const int nch = (w + 15) / 16;
     const unsigned magic = (unsigned)((1ull << 32) / (unsigned)nch) + 1u;
     dim3 grid((unsigned)(((size_t)nch * h + 255) / 256), batch);
-    orb_launch(orb_pdl(batch), k_ingest, grid, dim3(256), 0, s, src, dst, w, h, stride, (unsigned long long)img_stride, dst_pitch, (unsigned long long)dst_img_stride, nch, magic);
+    // plain launch: what precedes it in the stream is a copy or a cross-stream event wait, not a kernel of the chain
+    orb_launch(false, k_ingest, grid, dim3(256), 0, s, src, dst, w, h, stride, (unsigned long long)img_stride, dst_pitch, (unsigned long long)dst_img_stride, nch, magic);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -736,14 +737,15 @@ cudaError_t launch_fast(cudaStream_t s, const TmaMaps& tm, int* cell_cnt, uint32
     return e != cudaSuccess ? e : cudaGetLastError();   // a refused launch must fail loudly, not leave stale candidate lists behind
 }
 cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const TmaMaps& tm_blur, const uint32_t* lvl_kp, const int* lvl_cnt,
-                                   orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int b0, int batch) {
+                                   orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int b0, int batch, bool after_event_wait) {
     const int smem = OD_WARPS * 2 * OD_SLOT_BYTES;
     cudaError_t e = cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
     if (e != cudaSuccess) return e;
     // small batches: fewer keypoints per warp, so that the frame's ~2000 keypoints spread over all SMs (per-frame latency)
     const int kpw = (long long)batch * P.kp_cap >= 2LL * orb_sm_count() * 28 * OD_KPW ? OD_KPW : 2;
     dim3 grid((P.kp_cap + OD_WARPS * kpw - 1) / (OD_WARPS * kpw), batch);
-    e = orb_launch(orb_pdl(batch), k_orient_describe, grid, dim3(OD_WARPS * 32), (size_t)smem, s, tm_raw, tm_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, b0, kpw);
+    // behind a cross-stream event wait (the side-stream blur) the launch is a plain one
+    e = orb_launch(orb_pdl(batch) && !after_event_wait, k_orient_describe, grid, dim3(OD_WARPS * 32), (size_t)smem, s, tm_raw, tm_blur, lvl_kp, lvl_cnt, kps, desc, counts, P, b0, kpw);
     return e != cudaSuccess ? e : cudaGetLastError();
 }
 

@@ -16,7 +16,7 @@ cudaError_t launch_quadtree(cudaStream_t s, const int* cell_cnt, int* cell_prefi
                             uint32_t* lvl_kp, int* lvl_cnt, int* lvl_ncand, int* status, const Plan& P, int batch);
 size_t quadtree_smem(int cap, int* p2_out);
 cudaError_t launch_orient_describe(cudaStream_t s, const TmaMaps& tm_raw, const TmaMaps& tm_blur, const uint32_t* lvl_kp, const int* lvl_cnt,
-                                   orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int b0, int batch);
+                                   orb_keypoint* kps, uint8_t* desc, int* counts, const Plan& P, int b0, int batch, bool after_event_wait);
 
 static thread_local std::string g_err;
 void orb_set_error(const std::string& s) { g_err = s; }
@@ -366,7 +366,7 @@ int run_pipeline(orb_extractor* e, int b0, int batch, int phase = 0) {
     if (T) cudaEventRecord(e->ev_stage[4], s);
     {
         ORB_NVTX("orb:orient_describe");
-        ORB_CUDA(launch_orient_describe(s, e->tm_od_raw, e->tm_od_blur, lvl_kp, lvl_cnt, kps, desc, counts, Q, b0, batch));
+        ORB_CUDA(launch_orient_describe(s, e->tm_od_raw, e->tm_od_blur, lvl_kp, lvl_cnt, kps, desc, counts, Q, b0, batch, side));
         e->launches++;
     }
     if (T) { cudaEventRecord(e->ev_stage[5], s); for (int i = 0; i < 5; ++i) e->stage_valid[i] = true; }

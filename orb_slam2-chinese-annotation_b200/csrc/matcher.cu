@@ -1124,7 +1124,7 @@ int upload_frame(orb_matcher* m, const orb_frame_view* f, DFrame* D, bool need_g
         while (p2 < std::max(f->n, 1)) p2 <<= 1;
         const size_t smem = (size_t)p2 * 4;
         if (smem > GRID_BUILD_DYN_DEFAULT) ORB_CUDA(cudaFuncSetAttribute(k_grid_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ORB_CUDA(orb_launch(true, k_grid_build, dim3(1), dim3(1024), smem, ws_stream(m), D->x, D->y, f->n, p2, f->grid, cs, ci, ni, 0, (const int*)nullptr));
+        ORB_CUDA(orb_launch(false, k_grid_build, dim3(1), dim3(1024), smem, ws_stream(m), D->x, D->y, f->n, p2, f->grid, cs, ci, ni, 0, (const int*)nullptr));
         m->launches++;
         D->cell_start = cs; D->cell_items = ci;
     }

@@ -228,6 +228,8 @@ cudaError_t orb_dev_free(void* p);
 // scheduled while its predecessor in the stream still runs; ORB_PDL_SYNC() as the FIRST statement of the kernel lets the successor be
 // scheduled in turn and then waits until every predecessor has completed and its writes are visible, so nothing is read or written early.
 // Without the launch attribute both instructions do nothing.
+// Only links whose predecessor in the stream is a kernel of the same chain are launched this way: the first kernel behind a copy or a cross-stream
+// event wait (k_ingest, k_orient_describe behind the side-stream blur, k_stereo_rows behind the right handle's stream) is a plain launch.
 #define ORB_PDL_SYNC() asm volatile("griddepcontrol.launch_dependents;\n\tgriddepcontrol.wait;" ::: "memory")
 inline bool orb_pdl(int batch) {
     static const bool off = getenv("ORB_B200_NO_PDL") != nullptr;

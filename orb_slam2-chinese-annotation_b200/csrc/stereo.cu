@@ -388,7 +388,8 @@ static int stereo_launch(orb_extractor* l, orb_extractor* r, int b0, int batch, 
     if (T) cudaEventRecord(l->ev_stage[6], l->stream);
     nvtxRangePushA("orb:stereo_rows");
     const bool pdl = orb_pdl(batch);
-    orb_launch(pdl, k_stereo_rows, dim3(batch), dim3(512), smem, l->stream, r->d_kps + kr, r->d_counts + b0, row_start, row_items, l->d_status, S);
+    // the first kernel behind the cross-stream event wait above is launched plainly: only links whose predecessor is a kernel of this chain are relaxed
+    orb_launch(false, k_stereo_rows, dim3(batch), dim3(512), smem, l->stream, r->d_kps + kr, r->d_counts + b0, row_start, row_items, l->d_status, S);
     nvtxRangePop();
     if (T) cudaEventRecord(l->ev_stage[7], l->stream);
     nvtxRangePushA("orb:stereo_match");
